@@ -1,0 +1,321 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes bindings for the two checker libraries.
+
+``OracleForest``  -> oracle/_build/liboracle.so   (plain-C restatement, oracle/mcts_oracle.c)
+``RefForest``     -> oracle/_ref/libref_<v>.so    (compiled, unmodified reference + oracle/ref_harness*.cpp)
+
+Both expose the same numpy-level interface so tests can drive them (and the CUDA path) in lock-step.
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+VARIANTS = ("mz", "ez", "gmz", "sez")
+_VID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3}
+
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+
+
+def _ptr(a, ct):
+    return None if a is None else a.ctypes.data_as(C.POINTER(ct))
+
+
+def _f(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _i(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _csr(lists):
+    off = np.zeros(len(lists) + 1, np.int32)
+    for k, l in enumerate(lists):
+        off[k + 1] = off[k] + len(l)
+    flat = np.zeros(max(int(off[-1]), 1), np.int32)
+    for k, l in enumerate(lists):
+        flat[off[k]:off[k + 1]] = l
+    return flat, off
+
+
+def _csr_f(lists):
+    off = np.zeros(len(lists) + 1, np.int32)
+    for k, l in enumerate(lists):
+        off[k + 1] = off[k] + len(l)
+    flat = np.zeros(max(int(off[-1]), 1), np.float32)
+    for k, l in enumerate(lists):
+        flat[off[k]:off[k + 1]] = l
+    return flat, off
+
+
+_oracle_lib = None
+
+
+def oracle_lib():
+    global _oracle_lib
+    if _oracle_lib is None:
+        path = os.path.join(HERE, "_build", "liboracle.so")
+        if os.path.exists(os.path.join(HERE, "mcts_oracle.c")):
+            path = _build.build_oracle()
+        L = C.CDLL(path)
+        L.orc_new.restype = C.c_void_p
+        L.orc_expf.restype = C.c_float
+        L.orc_expf.argtypes = [C.c_float]
+        L.orc_logf.restype = C.c_float
+        L.orc_logf.argtypes = [C.c_float]
+        L.orc_tiebreak_hash.restype = C.c_uint32
+        L.orc_tiebreak_hash.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]
+        for name in ("orc_expf_mismatch_range", "orc_logf_mismatch_range"):
+            getattr(L, name).restype = C.c_long
+            getattr(L, name).argtypes = [C.c_uint32, C.c_uint32]
+        _oracle_lib = L
+    return _oracle_lib
+
+
+_ref_libs = {}
+
+
+def ref_lib(variant):
+    """Load oracle/_ref/libref_<variant>.so (building it first when /root/reference is present)."""
+    if variant not in _ref_libs:
+        built = _build.build_ref()
+        if variant not in built:
+            return None
+        L = C.CDLL(built[variant])
+        L.ref_new.restype = C.c_void_p
+        L.ref_rng_mode.argtypes = [C.c_int, C.c_uint64]
+        _ref_libs[variant] = L
+    return _ref_libs[variant]
+
+
+def ref_available(variant="mz"):
+    try:
+        return ref_lib(variant) is not None
+    except Exception:
+        return False
+
+
+class _ForestBase:
+    """Common numpy-level surface. legal_actions: list of per-root action lists."""
+
+    variant = "mz"
+    n = 0
+    A = 0
+
+    def traverse(self, pb_c_base, pb_c_init, discount, to_play, num_simulations=0, max_considered=0, path_stride=0):
+        raise NotImplementedError
+
+    def run_search(self, model_fn, S, pb_c_base, pb_c_init, discount, to_play, max_considered=0, lstm_horizon_len=5,
+                   record=None):
+        """Restates the reference driver loop (lzero/mcts/tree_search/mcts_ctree.py:255-321, EZ :733-827,
+        Gumbel :1054-1122) over a scripted model: model_fn(sim, ix, iy, last_action) -> dict(reward, value, logits)."""
+        tp = np.asarray(to_play, np.int32)
+        for s in range(S):
+            out = self.traverse(pb_c_base, pb_c_init, discount, tp, num_simulations=S, max_considered=max_considered,
+                                path_stride=S + 1 if record is not None else 0)
+            m = model_fn(s, out["ix"], out["iy"], out["last_action"])
+            is_reset = None
+            if self.variant in ("ez", "sez"):
+                is_reset = (out["search_len"] % lstm_horizon_len == 0).astype(np.int32)  # mcts_ctree.py:809-814
+            if record is not None:
+                record.append(dict(out, is_reset=is_reset))
+            self.backprop(s + 1, discount, m["reward"], m["value"], m["logits"], is_reset, out["vtp"],
+                          m.get("sampled_actions"))
+
+
+class OracleForest(_ForestBase):
+    def __init__(self, variant, n, A, legal_actions=None, K=0, D=0, continuous=False):
+        self.L = oracle_lib()
+        self.variant, self.n, self.A, self.K, self.D = variant, n, A, K, D
+        self.W = K if variant == "sez" else A
+        if legal_actions is None:
+            legal_actions = [[] for _ in range(n)]
+        flat, off = _csr(legal_actions)
+        self.h = C.c_void_p(self.L.orc_new(_VID[variant], n, A, _ptr(flat, C.c_int), _ptr(off, C.c_int), K, D,
+                                           int(continuous)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_free(self.h)
+            self.h = None
+
+    def set_delta(self, d):
+        self.L.orc_set_delta(self.h, C.c_float(d))
+
+    def set_rng(self, mode, seed, root_offset=0):
+        self.L.orc_set_rng(self.h, mode, C.c_uint64(seed), C.c_uint32(root_offset))
+
+    def prepare(self, noise_w, noises, rewards, logits, to_play, values=None, sampled_actions=None):
+        with_noise = noises is not None
+        nf, no = _csr_f(noises) if with_noise else (None, None)
+        rewards, values, logits, to_play = _f(rewards), _f(values), _f(logits), _i(to_play)
+        sa = _f(sampled_actions)
+        self.L.orc_prepare(self.h, int(with_noise), C.c_float(noise_w), _ptr(nf, C.c_float), _ptr(no, C.c_int),
+                           _ptr(rewards, C.c_float), _ptr(values, C.c_float), _ptr(logits, C.c_float),
+                           _ptr(to_play, C.c_int), _ptr(sa, C.c_float))
+
+    def traverse(self, pb_c_base, pb_c_init, discount, to_play, num_simulations=0, max_considered=0, path_stride=0):
+        n = self.n
+        tp = _i(to_play)
+        o = {k: np.zeros(n, np.int32) for k in ("ix", "iy", "last_action", "search_len", "vtp")}
+        paths = np.full((n, max(path_stride, 1)), -1, np.int32)
+        laf = np.zeros((n, max(self.D, 1)), np.float32) if self.variant == "sez" else None
+        self.L.orc_traverse(self.h, int(pb_c_base), C.c_float(pb_c_init), C.c_float(discount), int(num_simulations),
+                            int(max_considered), _ptr(tp, C.c_int), _ptr(o["ix"], C.c_int), _ptr(o["iy"], C.c_int),
+                            _ptr(o["last_action"], C.c_int), _ptr(laf, C.c_float), _ptr(o["search_len"], C.c_int),
+                            _ptr(o["vtp"], C.c_int), _ptr(paths, C.c_int) if path_stride else None, int(path_stride))
+        if path_stride:
+            o["paths"] = paths
+        if laf is not None:
+            o["last_action_f"] = laf
+        return o
+
+    def backprop(self, latent_index, discount, rewards, values, logits, is_reset, to_play, sampled_actions=None):
+        rewards, values, logits = _f(rewards), _f(values), _f(logits)
+        is_reset, to_play, sa = _i(is_reset), _i(to_play), _f(sampled_actions)
+        self.L.orc_backprop(self.h, int(latent_index), C.c_float(discount), _ptr(rewards, C.c_float),
+                            _ptr(values, C.c_float), _ptr(logits, C.c_float), _ptr(is_reset, C.c_int),
+                            _ptr(to_play, C.c_int), _ptr(sa, C.c_float))
+
+    def distributions(self):
+        d = np.zeros((self.n, self.W), np.int32)
+        ln = np.zeros(self.n, np.int32)
+        self.L.orc_distributions(self.h, _ptr(d, C.c_int), _ptr(ln, C.c_int))
+        return d, ln
+
+    def values(self):
+        v = np.zeros(self.n, np.float32)
+        self.L.orc_values(self.h, _ptr(v, C.c_float))
+        return v
+
+    def minmax(self):
+        mn, mx = np.zeros(self.n, np.float32), np.zeros(self.n, np.float32)
+        self.L.orc_minmax(self.h, _ptr(mn, C.c_float), _ptr(mx, C.c_float))
+        return mn, mx
+
+    def gumbel_outputs(self, discount):
+        p = np.zeros((self.n, self.A), np.float32)
+        v = np.zeros((self.n, self.A), np.float32)
+        self.L.orc_gumbel_outputs(self.h, C.c_float(discount), _ptr(p, C.c_float), _ptr(v, C.c_float))
+        return p, v
+
+    def root_stats(self):
+        vc, vs, rw = np.zeros(self.n, np.int32), np.zeros(self.n, np.float32), np.zeros(self.n, np.float32)
+        self.L.orc_root_stats(self.h, _ptr(vc, C.c_int), _ptr(vs, C.c_float), _ptr(rw, C.c_float))
+        return vc, vs, rw
+
+    def sampled_actions(self):
+        out = np.zeros((self.n, self.K, self.D), np.float32)
+        self.L.orc_sampled_actions(self.h, _ptr(out, C.c_float))
+        return out
+
+    def dump_tree(self, i, E):
+        return _dump(lambda *a: self.L.orc_dump_tree(self.h, *a), i, E, self.W)
+
+
+def _dump(fn, i, E, W):
+    visit = np.full(E * W, -1, np.int32)
+    vsum = np.zeros(E * W, np.float32)
+    prior = np.zeros(E * W, np.float32)
+    reward = np.zeros(E * W, np.float32)
+    child_e = np.full(E * W, -2, np.int32)
+    hdr = np.full(E * 4, -9, np.int32)
+    raw = np.zeros(E, np.float32)
+    fn(int(i), int(E), _ptr(visit, C.c_int), _ptr(vsum, C.c_float), _ptr(prior, C.c_float), _ptr(reward, C.c_float),
+       _ptr(child_e, C.c_int), _ptr(hdr, C.c_int), _ptr(raw, C.c_float))
+    return dict(visit=visit.reshape(E, W), value_sum=vsum.reshape(E, W), prior=prior.reshape(E, W),
+                reward=reward.reshape(E, W), child_e=child_e.reshape(E, W), hdr=hdr.reshape(E, 4), raw_value=raw)
+
+
+class RefForest(_ForestBase):
+    """The compiled reference tree (discrete variants mz / ez / gmz) behind the same surface."""
+
+    def __init__(self, variant, n, A, legal_actions=None, per_root=False):
+        self.L = ref_lib(variant)
+        if self.L is None:
+            raise RuntimeError("oracle/_ref/libref_%s.so is not built and /root/reference is absent" % variant)
+        self.variant, self.n, self.A, self.W = variant, n, A, A
+        if legal_actions is None:
+            legal_actions = [[] for _ in range(n)]
+        flat, off = _csr(legal_actions)
+        self.h = C.c_void_p(self.L.ref_new(n, A, _ptr(flat, C.c_int), _ptr(off, C.c_int), int(per_root)))
+        self.per_root = per_root
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_free(self.h)
+            self.h = None
+
+    def set_delta(self, d):
+        self.L.ref_set_delta(self.h, C.c_float(d))
+
+    def set_rng(self, mode, seed, root_offset=0):
+        """mode 0 = libc random (timing), 1 = batch-pinned, 2 = per-(root, depth) pinned (needs per_root=True)."""
+        assert root_offset == 0
+        assert mode != 2 or self.per_root
+        self.L.ref_rng_mode(int(mode), C.c_uint64(seed))
+
+    def prepare(self, noise_w, noises, rewards, logits, to_play, values=None, sampled_actions=None):
+        with_noise = noises is not None
+        nf, no = _csr_f(noises) if with_noise else (None, None)
+        rewards, values, logits, to_play = _f(rewards), _f(values), _f(logits), _i(to_play)
+        if self.variant == "gmz" and values is None:
+            values = np.zeros(self.n, np.float32)
+        self.L.ref_prepare(self.h, int(with_noise), C.c_float(noise_w), _ptr(nf, C.c_float), _ptr(no, C.c_int),
+                           _ptr(rewards, C.c_float), _ptr(values, C.c_float), _ptr(logits, C.c_float),
+                           _ptr(to_play, C.c_int))
+
+    def traverse(self, pb_c_base, pb_c_init, discount, to_play, num_simulations=0, max_considered=0, path_stride=0):
+        n = self.n
+        tp = _i(to_play)
+        o = {k: np.zeros(n, np.int32) for k in ("ix", "iy", "last_action", "search_len", "vtp")}
+        paths = np.full((n, max(path_stride, 1)), -1, np.int32)
+        self.L.ref_traverse(self.h, int(pb_c_base), C.c_float(pb_c_init), C.c_float(discount), int(num_simulations),
+                            int(max_considered), _ptr(tp, C.c_int), _ptr(o["ix"], C.c_int), _ptr(o["iy"], C.c_int),
+                            _ptr(o["last_action"], C.c_int), _ptr(o["search_len"], C.c_int), _ptr(o["vtp"], C.c_int),
+                            _ptr(paths, C.c_int) if path_stride else None, int(path_stride))
+        if path_stride:
+            o["paths"] = paths
+        return o
+
+    def backprop(self, latent_index, discount, rewards, values, logits, is_reset, to_play, sampled_actions=None):
+        rewards, values, logits = _f(rewards), _f(values), _f(logits)
+        is_reset, to_play = _i(is_reset), _i(to_play)
+        self.L.ref_backprop(self.h, int(latent_index), C.c_float(discount), _ptr(rewards, C.c_float),
+                            _ptr(values, C.c_float), _ptr(logits, C.c_float), _ptr(is_reset, C.c_int),
+                            _ptr(to_play, C.c_int))
+
+    def distributions(self):
+        d = np.zeros((self.n, self.A), np.int32)
+        ln = np.zeros(self.n, np.int32)
+        self.L.ref_distributions(self.h, _ptr(d, C.c_int), _ptr(ln, C.c_int))
+        return d, ln
+
+    def values(self):
+        v = np.zeros(self.n, np.float32)
+        self.L.ref_values(self.h, _ptr(v, C.c_float))
+        return v
+
+    def minmax(self):
+        mn, mx = np.zeros(self.n, np.float32), np.zeros(self.n, np.float32)
+        self.L.ref_minmax(self.h, _ptr(mn, C.c_float), _ptr(mx, C.c_float))
+        return mn, mx
+
+    def gumbel_outputs(self, discount):
+        p = np.zeros((self.n, self.A), np.float32)
+        v = np.zeros((self.n, self.A), np.float32)
+        self.L.ref_gumbel_outputs(self.h, C.c_float(discount), _ptr(p, C.c_float), _ptr(v, C.c_float))
+        return p, v
+
+    def root_stats(self):
+        vc, vs, rw = np.zeros(self.n, np.int32), np.zeros(self.n, np.float32), np.zeros(self.n, np.float32)
+        self.L.ref_root_stats(self.h, _ptr(vc, C.c_int), _ptr(vs, C.c_float), _ptr(rw, C.c_float))
+        return vc, vs, rw
+
+    def dump_tree(self, i, E):
+        return _dump(lambda *a: self.L.ref_dump_tree(self.h, *a), i, E, self.A)
