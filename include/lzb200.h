@@ -1,0 +1,152 @@
+/*
+ * lzb200.h - C ABI of the B200-native batched MCTS tree (liblzb200.so).
+ *
+ * This is the boundary a LightZero maintainer binds instead of the Cython modules
+ *   lzero/mcts/ctree/ctree_muzero/mz_tree.pyx            (Roots, MinMaxStatsList, ResultsWrapper,
+ *   lzero/mcts/ctree/ctree_efficientzero/ez_tree.pyx      batch_traverse, batch_backpropagate)
+ *   lzero/mcts/ctree/ctree_gumbel_muzero/gmz_tree.pyx
+ *   lzero/mcts/ctree/ctree_sampled_efficientzero/ezs_tree.pyx
+ * (citations below are relative to /root/reference).  All pointers named *_dev are DEVICE pointers
+ * on the current CUDA device; every call is asynchronous on `stream` (a cudaStream_t passed as
+ * void*), takes plain pointers and sizes, never throws, never allocates device memory and keeps no
+ * global state besides the thread-local error string.  Return value: 0 on success, negative
+ * LZB_E_* on error (lzb_last_error() describes it).
+ *
+ * The forest (all N search trees of one batch) lives in ONE caller-owned device workspace laid out
+ * as a structure-of-arrays node pool (see DESIGN.md "Data layout in HBM").  The caller (PyTorch)
+ * owns that memory; the handle only holds offsets.
+ *
+ * Tie-break stream.  The reference breaks pUCT ties with libc rand() reseeded from the wall clock
+ * (ctree_muzero/lib/cnode.cpp:592,770).  Here the stream is an explicit counter-based input:
+ *     r(seed, sim, root, depth) = lzb_tiebreak_hash(seed, sim, root, depth)      (31 bits)
+ *     pick = tie_set[r % n_ties]
+ * LZB_RNG_PER_ROOT keys it by (sim, global root index, depth); LZB_RNG_BATCH uses r(seed, sim, 0, 0)
+ * for every draw of one traverse, which is what the unmodified batched reference API can be pinned to.
+ */
+#ifndef LZB200_H
+#define LZB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LZB_ABI_VERSION 1
+
+/* tree flavours */
+#define LZB_MZ 0  /* ctree_muzero */
+#define LZB_EZ 1  /* ctree_efficientzero: value_prefix + is_reset */
+#define LZB_GMZ 2 /* ctree_gumbel_muzero */
+#define LZB_SEZ 3 /* ctree_sampled_efficientzero: K sampled actions per node */
+
+#define LZB_RNG_BATCH 1
+#define LZB_RNG_PER_ROOT 2
+
+#define LZB_OK 0
+#define LZB_E_ARG (-1)      /* bad argument (null pointer, size out of range) */
+#define LZB_E_STATE (-2)    /* call order violated (e.g. more simulations than the pool was sized for) */
+#define LZB_E_CUDA (-3)     /* a CUDA runtime call failed */
+#define LZB_E_UNSUPPORTED (-4)
+
+typedef struct lzb_forest lzb_forest_t; /* opaque, host memory */
+
+/* pUCT / Gumbel constants of one search: mcts_ctree.py:181-193,246 and :1074. */
+typedef struct {
+    int32_t pb_c_base;                  /* 19652 */
+    float pb_c_init;                    /* 1.25 */
+    float discount;                     /* discount_factor */
+    int32_t players;                    /* 0 = derive from max(to_play) as cnode.cpp:776-781 does (costs one
+                                           device reduction); 1 or 2 = caller states it */
+    int32_t num_simulations;            /* Gumbel: sequential-halving horizon */
+    int32_t max_num_considered_actions; /* Gumbel */
+    int32_t rng_mode;                   /* LZB_RNG_BATCH | LZB_RNG_PER_ROOT */
+    uint64_t rng_seed;
+} lzb_search_cfg_t;
+
+const char *lzb_last_error(void);
+int lzb_abi_version(void);
+uint32_t lzb_tiebreak_hash(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth);
+
+/* Bytes of device workspace needed for N trees, children stride A (action space size; K for the
+ * sampled tree), room for S simulations, D = action dimension (sampled tree only, else 0). */
+int lzb_forest_bytes(int variant, int num_roots, int action_space, int max_sims, int action_dim, size_t *bytes);
+
+/* Replaces Roots.__cinit__ (mz_tree.pyx:30-32 -> CRoots::CRoots, cnode.cpp:301-317) and
+ * MinMaxStatsList(num) (mz_tree.pyx:8-9).  legal_count_dev[N] / legal_actions_dev[N*A]: per-root
+ * legal-action lists (row i holds legal_count[i] action ids, list order preserved); both NULL = every
+ * action legal.  root_offset = global index of local root 0 when the batch is sharded over GPUs. */
+int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_bytes, int variant, int num_roots,
+                      int action_space, int max_sims, int action_dim, int root_offset, const int32_t *legal_count_dev,
+                      const int32_t *legal_actions_dev, void *stream);
+void lzb_forest_destroy(lzb_forest_t *f);
+
+/* MinMaxStatsList.set_delta (mz_tree.pyx:11-12); also clears min/max as a fresh list would be. */
+int lzb_set_delta(lzb_forest_t *f, float value_delta_max, void *stream);
+
+/* Roots.prepare / prepare_no_noise (mz_tree.pyx:34-39 -> cnode.cpp:321-358; gumbel adds values,
+ * gmz_tree.pyx:36-40).  logits [N,A]; noise [N,A] indexed by position in the legal list (NULL = no
+ * noise); reward [N] (value_prefix for EZ/SEZ); value [N] (Gumbel only, else NULL); to_play [N];
+ * sampled_actions [N,K,D] (sampled tree only: the injected action table of each root). */
+int lzb_prepare(lzb_forest_t *f, const float *logits_dev, const float *noise_dev, float noise_weight,
+                const float *reward_dev, const float *value_dev, const int32_t *to_play_dev,
+                const float *sampled_actions_dev, void *stream);
+
+/* One gather of leaf inputs: dst[i, :] = src[ix_i, i, :] for row_bytes bytes (multiple of 4).
+ * Replaces the Python loop + np.asarray + H2D copy of mcts_ctree.py:283-289 / :766-775. */
+typedef struct {
+    const void *src_dev; /* [E, N, row_bytes] pool, E = max_sims + 1 */
+    void *dst_dev;       /* [N, row_bytes] */
+    int64_t row_bytes;
+} lzb_gather_t;
+
+/* batch_traverse (mz_tree.pyx:95-100 -> cbatch_traverse, cnode.cpp:755-824; ez :886-963; gumbel
+ * :834-898; sampled :1110-1187) + the leaf gather.  Outputs [N]: ix (latent_state_index_in_search_path),
+ * iy (latent_state_index_in_batch, local index), search_len, vtp (virtual_to_play_batchs),
+ * last_action as int64 (what .long() produces, mcts_ctree.py:289); last_action_f [N,D] for the sampled
+ * tree.  Any output pointer may be NULL.  gathers/num_gathers may be 0. */
+int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const int32_t *to_play_dev, int32_t *ix_dev,
+                 int32_t *iy_dev, int64_t *last_action_dev, float *last_action_f_dev, int32_t *search_len_dev,
+                 int32_t *vtp_dev, const lzb_gather_t *gathers, int num_gathers, void *stream);
+
+/* batch_backpropagate / batch_back_propagate (mz_tree.pyx:74-82 -> cbatch_backpropagate,
+ * cnode.cpp:480-500; ez :577-601; gumbel :633-652).  latent_index = simulation_index + 1.
+ * reward/value [N], logits [N,A] straight from the model's device tensors; to_play [N] = the vtp
+ * returned by traverse.  EZ/SEZ reset handling (mcts_ctree.py:809-816): if is_reset_dev != NULL it is
+ * used as given; else if lstm_horizon_len > 0 is_reset = (search_len % lstm_horizon_len == 0) is
+ * computed on device, written to is_reset_out_dev when non-NULL. */
+int lzb_backprop(lzb_forest_t *f, int latent_index, float discount, const float *reward_dev, const float *value_dev,
+                 const float *logits_dev, const int32_t *to_play_dev, const int32_t *is_reset_dev,
+                 int lstm_horizon_len, int32_t *is_reset_out_dev, const float *sampled_actions_dev, void *stream);
+
+/* EZ hidden-state write-back with reset (mcts_ctree.py:809-816): dst[i,:] = is_reset[i] ? 0 : src[i,:]. */
+int lzb_store_hidden(const float *src_dev, float *dst_dev, const int32_t *is_reset_dev, int num_roots,
+                     int64_t row_floats, void *stream);
+
+/* get_distributions + get_values (cnode.cpp:387-417): visits [N,A] (first legal_count[i] entries of
+ * row i are the child visit counts in legal-action order, rest 0), legal_count [N], values [N].
+ * Gumbel extras (gmz cnode.cpp:506-541), each [N,A] or NULL: improved policies and completed child values. */
+int lzb_root_outputs(lzb_forest_t *f, int32_t *visits_dev, int32_t *legal_count_dev, float *values_dev,
+                     float discount, float *gumbel_policies_dev, float *gumbel_children_values_dev, void *stream);
+
+/* Introspection for parity tests: raw pool arrays of tree i copied into caller DEVICE buffers laid out
+ * as oracle/ref_harness.cpp:ref_dump_tree ([E,A] visit/value_sum/prior/reward/child_e, [E,4] hdr, [E] raw). */
+int lzb_dump_tree(lzb_forest_t *f, int tree, int32_t *visit_dev, float *value_sum_dev, float *prior_dev,
+                  float *reward_dev, int32_t *child_e_dev, int32_t *hdr_dev, float *raw_value_dev, void *stream);
+int lzb_dump_paths(lzb_forest_t *f, int32_t *path_actions_dev, int path_stride, void *stream);
+int lzb_minmax(lzb_forest_t *f, float *min_dev, float *max_dev, void *stream);
+int lzb_root_stats(lzb_forest_t *f, int32_t *visit_dev, float *value_sum_dev, float *reward_dev, void *stream);
+
+/* Gumbel constants exposed for tests (gmz_tree.pyx:134-152): host buffers. */
+int lzb_gumbel_table(int max_num_considered_actions, int num_simulations, int32_t *out_host);
+int lzb_gumbel_noise(float scale, int shape, float *out_host);
+
+/* Device-side libm used by the tree, exposed for the parity tests: out[i] = expf/logf(x[i]). */
+int lzb_test_expf(const float *x_dev, float *out_dev, int64_t n, void *stream);
+int lzb_test_logf(const float *x_dev, float *out_dev, int64_t n, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LZB200_H */

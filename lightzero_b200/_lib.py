@@ -1,0 +1,117 @@
+"""Loader (and in-tree build recipe) for liblzb200.so, the C-ABI CUDA library of include/lzb200.h.
+
+There is no CPU fallback: if the library cannot be loaded the import of any tree module fails loudly.
+"""
+import ctypes as C
+import os
+import shutil
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+LIB_PATH = os.path.join(HERE, "liblzb200.so")
+SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_pool.cuh", "lzb_math.cuh", "lzb_step.cuh"]
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",  # B200 only
+    "-fmad=false",  # the reference's x86-64 -O2 build never fuses float mul+add; fp64 fma() calls stay explicit
+    "-lineinfo", "-O3", "-std=c++17", "--shared", "-Xcompiler", "-fPIC",
+]
+
+
+def _stale():
+    if not os.path.exists(LIB_PATH):
+        return True
+    t = os.path.getmtime(LIB_PATH)
+    deps = [os.path.join(CSRC, s) for s in SOURCES] + [os.path.join(ROOT, "include", "lzb200.h")]
+    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
+
+
+def build(force=False, verbose=False):
+    """Compile lightzero_b200/csrc/lzb_api.cu for sm_100a into lightzero_b200/liblzb200.so."""
+    if not force and not _stale():
+        return LIB_PATH
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        if os.path.exists(LIB_PATH):
+            return LIB_PATH
+        raise RuntimeError("nvcc not found and %s is not built" % LIB_PATH)
+    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [os.path.join(CSRC, "lzb_api.cu"), "-o", LIB_PATH]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n%s\n%s" % (res.stdout, res.stderr))
+    if verbose:
+        print(res.stderr)
+    return LIB_PATH
+
+
+class SearchCfg(C.Structure):
+    """lzb_search_cfg_t"""
+    _fields_ = [
+        ("pb_c_base", C.c_int32), ("pb_c_init", C.c_float), ("discount", C.c_float), ("players", C.c_int32),
+        ("num_simulations", C.c_int32), ("max_num_considered_actions", C.c_int32), ("rng_mode", C.c_int32),
+        ("rng_seed", C.c_uint64),
+    ]
+
+
+class Gather(C.Structure):
+    """lzb_gather_t"""
+    _fields_ = [("src_dev", C.c_void_p), ("dst_dev", C.c_void_p), ("row_bytes", C.c_int64)]
+
+
+_P = C.c_void_p
+_PROTOS = {
+    "lzb_last_error": (C.c_char_p, []),
+    "lzb_abi_version": (C.c_int, []),
+    "lzb_tiebreak_hash": (C.c_uint32, [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "lzb_forest_bytes": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
+    "lzb_forest_create": (C.c_int, [C.POINTER(_P), _P, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                    _P, _P, _P]),
+    "lzb_forest_destroy": (None, [_P]),
+    "lzb_set_delta": (C.c_int, [_P, C.c_float, _P]),
+    "lzb_prepare": (C.c_int, [_P, _P, _P, C.c_float, _P, _P, _P, _P, _P]),
+    "lzb_traverse": (C.c_int, [_P, C.POINTER(SearchCfg), _P, _P, _P, _P, _P, _P, _P, C.POINTER(Gather), C.c_int, _P]),
+    "lzb_backprop": (C.c_int, [_P, C.c_int, C.c_float, _P, _P, _P, _P, _P, C.c_int, _P, _P, _P]),
+    "lzb_store_hidden": (C.c_int, [_P, _P, _P, C.c_int, C.c_int64, _P]),
+    "lzb_root_outputs": (C.c_int, [_P, _P, _P, _P, C.c_float, _P, _P, _P]),
+    "lzb_dump_tree": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "lzb_dump_paths": (C.c_int, [_P, _P, C.c_int, _P]),
+    "lzb_minmax": (C.c_int, [_P, _P, _P, _P]),
+    "lzb_root_stats": (C.c_int, [_P, _P, _P, _P, _P]),
+    "lzb_gumbel_table": (C.c_int, [C.c_int, C.c_int, _P]),
+    "lzb_gumbel_noise": (C.c_int, [C.c_float, C.c_int, _P]),
+    "lzb_test_expf": (C.c_int, [_P, _P, C.c_int64, _P]),
+    "lzb_test_logf": (C.c_int, [_P, _P, C.c_int64, _P]),
+}
+
+_lib = None
+
+
+def lib():
+    """The loaded library with prototypes declared; builds it first when the sources are newer."""
+    global _lib
+    if _lib is None:
+        path = build()
+        L = C.CDLL(path)
+        for name, (res, args) in _PROTOS.items():
+            fn = getattr(L, name)  # AttributeError here == header and library disagree
+            fn.restype = res
+            fn.argtypes = args
+        if L.lzb_abi_version() != 1:
+            raise RuntimeError("liblzb200.so ABI version mismatch")
+        _lib = L
+    return _lib
+
+
+def exported_symbols():
+    return sorted(_PROTOS)
+
+
+class LzbError(RuntimeError):
+    pass
+
+
+def check(rc):
+    if rc != 0:
+        raise LzbError("liblzb200 error %d: %s" % (rc, lib().lzb_last_error().decode()))

@@ -1,0 +1,553 @@
+// liblzb200.so: C ABI of include/lzb200.h over the kernels in lzb_expand.cuh / lzb_select.cuh.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo -O3 -std=c++17 --shared ...
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <random>
+#include <vector>
+
+#include "../../include/lzb200.h"
+#include "lzb_expand.cuh"
+#include "lzb_select.cuh"
+
+using namespace lzb;
+
+struct lzb_forest {
+    Pool pool;
+    size_t bytes;
+    float delta;
+    int sim;      // traverses issued since the last prepare (keys the tie-break stream)
+    int expanded; // highest latent_index expanded so far
+    int vt_m, vt_s;
+    std::vector<int> vtable_host;
+    std::vector<float> gumbel_host;
+};
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define LZB_CUDA(expr)                                                                                  \
+    do {                                                                                                \
+        cudaError_t err__ = (expr);                                                                     \
+        if (err__ != cudaSuccess) return fail(LZB_E_CUDA, "%s: %s", #expr, cudaGetErrorString(err__)); \
+    } while (0)
+
+constexpr int kWarpsPerBlock = 4;
+constexpr size_t kAlign = 256;
+
+inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
+
+struct Layout {
+    size_t child, hdr, root, legal, minmax, path_a, path_b, res, best, actions, gumbel, vtable, scratch, total;
+};
+
+Layout make_layout(int variant, int N, int A, int S, int D)
+{
+    const size_t E = (size_t)S + 1;
+    Layout l;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes); return at; };
+    l.child = take((size_t)N * E * A * sizeof(int4));
+    l.hdr = take((size_t)N * E * sizeof(int4));
+    l.root = take((size_t)N * sizeof(int4));
+    l.legal = take((size_t)N * A * sizeof(int));
+    l.minmax = take((size_t)N * sizeof(float2));
+    l.path_a = take((size_t)N * E * sizeof(int4));
+    l.path_b = take((size_t)N * E * sizeof(int2));
+    l.res = take((size_t)N * sizeof(int4));
+    l.best = take((size_t)N * E * sizeof(int));
+    l.actions = take(variant == LZB_SEZ ? (size_t)N * E * A * D * sizeof(float) : 0);
+    l.gumbel = take((size_t)A * sizeof(float));
+    l.vtable = take(E * sizeof(int));
+    l.scratch = take(4 * sizeof(int));
+    l.total = o;
+    return l;
+}
+
+int check_dims(int variant, int N, int A, int S, int D)
+{
+    if (variant < LZB_MZ || variant > LZB_SEZ) return fail(LZB_E_ARG, "unknown variant %d", variant);
+    if (N <= 0 || A <= 0 || S <= 0) return fail(LZB_E_ARG, "num_roots, action_space and max_sims must be positive");
+    if (S > 65000) return fail(LZB_E_UNSUPPORTED, "max_sims %d exceeds the 16-bit visit/expansion packing", S);
+    if (variant == LZB_SEZ && D <= 0) return fail(LZB_E_ARG, "sampled tree needs action_dim > 0");
+    if ((size_t)A * 28 > 200 * 1024) return fail(LZB_E_UNSUPPORTED, "action_space %d too large for shared-memory staging", A);
+    return LZB_OK;
+}
+
+// warps per block so that `bytes_per_warp` of dynamic shared memory fits the default 48 KB window
+int warps_for(size_t bytes_per_warp) { return (bytes_per_warp * kWarpsPerBlock <= 48 * 1024) ? kWarpsPerBlock : 1; }
+
+template <typename K>
+int launch_cfg(K kernel, size_t bytes_per_warp, int N, dim3 &grid, dim3 &block, size_t &smem)
+{
+    const int wpb = warps_for(bytes_per_warp);
+    smem = bytes_per_warp * wpb;
+    if (smem > 48 * 1024) LZB_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    block = dim3(32 * wpb);
+    grid = dim3((N + wpb - 1) / wpb);
+    return LZB_OK;
+}
+
+__global__ void k_init(Pool p, const int *legal_count, const int *legal_actions)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.N) return;
+    int n = legal_count ? legal_count[i] : 0;
+    const bool all = (n <= 0); // empty list == every action legal (cnode.cpp:101-107)
+    if (all) n = p.A;
+    for (int j = 0; j < p.A; ++j) p.legal[(size_t)i * p.A + j] = (all || !legal_actions) ? j : legal_actions[(size_t)i * p.A + j];
+    p.hdr[(size_t)i * p.E] = make_int4(n, 0, 0, 0);
+    p.root[i] = make_int4(0, 0, 0, 0);
+    p.minmax[i] = make_float2(kFloatMax, kFloatMin); // CMinMaxStats ctor (cminimax.cpp:7-11)
+    p.res[i] = make_int4(0, 0, 0, 0);
+}
+
+__global__ void k_reset_minmax(Pool p)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < p.N) p.minmax[i] = make_float2(kFloatMax, kFloatMin);
+}
+
+__global__ void k_max_to_play(const int *to_play, int n, int *out)
+{
+    __shared__ int s[32];
+    int m = INT_MIN;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) m = max(m, to_play[i]);
+    m = warp_max_i(m);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        m = (threadIdx.x < (blockDim.x >> 5)) ? s[threadIdx.x] : INT_MIN;
+        m = warp_max_i(m);
+        if (threadIdx.x == 0) out[0] = m;
+    }
+}
+
+__global__ void k_store_hidden(const float *src, float *dst, const int *is_reset, int n, long long row)
+{
+    const long long total = (long long)n * row;
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(t / row);
+        dst[t] = (is_reset && is_reset[i]) ? 0.0f : src[t];
+    }
+}
+
+// get_distributions / get_values (cnode.cpp:387-417) and the Gumbel extras (gmz :309-385,506-541).
+__global__ void k_root_outputs(Pool p, int *visits, int *legal_count, float *values, float discount, float *policies,
+                               float *child_values)
+{
+    extern __shared__ int4 smem4[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const int i = blockIdx.x * wpb + wib;
+    if (i >= p.N) return;
+    const int A = p.A;
+    const int4 h = p.hdr[(size_t)i * p.E];
+    const int n = h.x;
+    const int4 *kids = p.child + (size_t)i * p.E * A;
+    if (visits)
+        for (int j = lane; j < A; j += 32) visits[(size_t)i * A + j] = j < n ? child_visits(kids[j].x) : 0;
+    if (lane == 0) {
+        if (legal_count) legal_count[i] = n;
+        if (values) {
+            const int4 r = p.root[i];
+            values[i] = r.x ? __int_as_float(r.y) / (float)r.x : 0.0f; // CNode::value (cnode.cpp:219-235)
+        }
+    }
+    if (p.variant == LZB_GMZ && (policies || child_values)) {
+        int4 *s_child = smem4 + (size_t)wib * A;
+        float *fbase = reinterpret_cast<float *>(smem4 + (size_t)wpb * A) + (size_t)wib * 3 * A;
+        float *s_q = fbase, *s_p = fbase + A, *s_c = fbase + 2 * A;
+        for (int j = lane; j < n; j += 32) s_child[j] = kids[j];
+        __syncwarp();
+        gumbel_completed_q(s_child, s_q, s_p, s_c, n, __int_as_float(h.w), discount, lane);
+        const int *legal = p.legal + (size_t)i * A;
+        if (child_values) {
+            for (int a = lane; a < A; a += 32) child_values[(size_t)i * A + a] = -INFINITY;
+            __syncwarp();
+            for (int j = lane; j < n; j += 32) child_values[(size_t)i * A + legal[j]] = s_c[j];
+        }
+        if (policies) {
+            for (int a = lane; a < A; a += 32) s_q[a] = -INFINITY;
+            __syncwarp();
+            for (int j = lane; j < n; j += 32) s_q[legal[j]] = __int_as_float(s_child[j].z) + s_c[j];
+            __syncwarp();
+            warp_csoftmax(s_q, A, lane); // over the whole action space, -inf for illegal (gmz :374-382)
+            for (int a = lane; a < A; a += 32) policies[(size_t)i * A + a] = s_q[a];
+        }
+    }
+}
+
+__global__ void k_dump_tree(Pool p, int i, int upto, int *visit, float *vsum, float *prior, float *reward, int *child_e,
+                            int *hdr, float *raw)
+{
+    const int A = p.A;
+    for (int e = 0; e <= upto; ++e) {
+        const int4 h = p.hdr[(size_t)i * p.E + e];
+        if (threadIdx.x == 0) {
+            hdr[e * 4 + 0] = h.x;
+            hdr[e * 4 + 1] = h.y;
+            hdr[e * 4 + 2] = h.z;
+            if (e == 0) hdr[3] = -1;
+            if (raw && p.variant == LZB_GMZ) raw[e] = __int_as_float(h.w);
+        }
+        for (int j = threadIdx.x; j < h.x; j += blockDim.x) {
+            const int4 c = p.child[((size_t)i * p.E + e) * A + j];
+            const size_t o = (size_t)e * A + j;
+            const int ce = child_expansion(c.x);
+            visit[o] = child_visits(c.x);
+            vsum[o] = __int_as_float(c.y);
+            prior[o] = __int_as_float(c.z);
+            reward[o] = ce >= 0 ? __int_as_float(c.w) : 0.0f;
+            child_e[o] = ce;
+            if (ce >= 0) hdr[ce * 4 + 3] = e;
+        }
+    }
+}
+
+__global__ void k_dump_paths(Pool p, int *out, int stride)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.N) return;
+    const int depth = p.res[i].x;
+    for (int d = 0; d < depth && d < stride; ++d) {
+        const int slot = p.path_a[(size_t)i * (p.S + 1) + d].x;
+        const int e = slot / p.A, pos = slot % p.A;
+        out[(size_t)i * stride + d] = (e == 0 && p.variant != LZB_SEZ) ? p.legal[(size_t)i * p.A + pos] : pos;
+    }
+}
+
+__global__ void k_minmax(Pool p, float *mn, float *mx)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < p.N) { mn[i] = p.minmax[i].x; mx[i] = p.minmax[i].y; }
+}
+
+__global__ void k_root_stats(Pool p, int *visit, float *vsum, float *reward)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < p.N) {
+        const int4 r = p.root[i];
+        visit[i] = r.x; vsum[i] = __int_as_float(r.y); reward[i] = __int_as_float(r.z);
+    }
+}
+
+__global__ void k_test_expf(const float *x, float *out, long long n)
+{
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) out[t] = glibc_expf(x[t]);
+}
+__global__ void k_test_logf(const float *x, float *out, long long n)
+{
+    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) out[t] = glibc_logf(x[t]);
+}
+
+// get_sequence_of_considered_visits (gmz cnode.cpp:1042-1077)
+std::vector<int> considered_sequence(int m, int S)
+{
+    std::vector<int> seq;
+    if (m <= 1) {
+        for (int i = 0; i < S; ++i) seq.push_back(i);
+        return seq;
+    }
+    int log2max = 0;
+    while ((1 << log2max) < m) ++log2max;
+    std::vector<int> visits(m, 0);
+    int considered = m;
+    while ((int)seq.size() < S) {
+        const int extra = std::max(1, S / (log2max * considered));
+        for (int i = 0; i < extra; ++i) {
+            seq.insert(seq.end(), visits.begin(), visits.begin() + considered);
+            for (int j = 0; j < considered; ++j) visits[j] += 1;
+        }
+        considered = std::max(2, considered / 2);
+    }
+    seq.resize(S);
+    return seq;
+}
+
+// generate_gumbel (gmz cnode.cpp:1134-1152): the host C++ library's own mt19937 / extreme_value_distribution
+void gumbel_noise(float scale, int shape, float *out)
+{
+    std::mt19937 gen(0u);
+    std::extreme_value_distribution<float> d(0, 1);
+    for (int i = 0; i < shape; ++i) out[i] = scale * d(gen);
+}
+
+} // namespace
+
+extern "C" {
+
+const char *lzb_last_error(void) { return g_err; }
+int lzb_abi_version(void) { return LZB_ABI_VERSION; }
+uint32_t lzb_tiebreak_hash(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth) { return tiebreak_hash(seed, sim, root, depth); }
+
+int lzb_forest_bytes(int variant, int num_roots, int action_space, int max_sims, int action_dim, size_t *bytes)
+{
+    if (!bytes) return fail(LZB_E_ARG, "bytes is NULL");
+    if (int rc = check_dims(variant, num_roots, action_space, max_sims, action_dim)) return rc;
+    *bytes = make_layout(variant, num_roots, action_space, max_sims, action_dim).total;
+    return LZB_OK;
+}
+
+int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_bytes, int variant, int num_roots,
+                      int action_space, int max_sims, int action_dim, int root_offset, const int32_t *legal_count_dev,
+                      const int32_t *legal_actions_dev, void *stream)
+{
+    if (!out || !workspace_dev) return fail(LZB_E_ARG, "out / workspace is NULL");
+    if (int rc = check_dims(variant, num_roots, action_space, max_sims, action_dim)) return rc;
+    if (((uintptr_t)workspace_dev & (kAlign - 1)) != 0) return fail(LZB_E_ARG, "workspace must be %zu-byte aligned", kAlign);
+    const Layout l = make_layout(variant, num_roots, action_space, max_sims, action_dim);
+    if (workspace_bytes < l.total) return fail(LZB_E_ARG, "workspace too small: %zu < %zu", workspace_bytes, l.total);
+    if ((legal_count_dev == nullptr) != (legal_actions_dev == nullptr)) return fail(LZB_E_ARG, "legal_count / legal_actions must both be given or both NULL");
+    lzb_forest *f = new lzb_forest();
+    char *w = (char *)workspace_dev;
+    Pool &p = f->pool;
+    p.variant = variant; p.N = num_roots; p.A = action_space; p.S = max_sims; p.E = max_sims + 1; p.D = action_dim;
+    p.root_offset = root_offset;
+    p.child = (int4 *)(w + l.child); p.hdr = (int4 *)(w + l.hdr); p.root = (int4 *)(w + l.root);
+    p.legal = (int *)(w + l.legal); p.minmax = (float2 *)(w + l.minmax);
+    p.path_a = (int4 *)(w + l.path_a); p.path_b = (int2 *)(w + l.path_b); p.res = (int4 *)(w + l.res);
+    p.best = (int *)(w + l.best); p.actions = (float *)(w + l.actions); p.gumbel = (float *)(w + l.gumbel);
+    p.vtable = (int *)(w + l.vtable); p.scratch = (int *)(w + l.scratch);
+    f->bytes = l.total; f->delta = 0.0f; f->sim = 0; f->expanded = -1; f->vt_m = -1; f->vt_s = -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    k_init<<<(num_roots + 127) / 128, 128, 0, st>>>(p, legal_count_dev, legal_actions_dev);
+    if (variant == LZB_GMZ) {
+        f->gumbel_host.resize(action_space);
+        gumbel_noise(10.0f, action_space, f->gumbel_host.data()); // gumbel_scale = 10, gumbel_rng = 0 (gmz :87-89)
+        cudaError_t e = cudaMemcpyAsync(p.gumbel, f->gumbel_host.data(), sizeof(float) * action_space, cudaMemcpyHostToDevice, st);
+        if (e != cudaSuccess) { delete f; return fail(LZB_E_CUDA, "gumbel upload: %s", cudaGetErrorString(e)); }
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { delete f; return fail(LZB_E_CUDA, "forest init: %s", cudaGetErrorString(e)); }
+    *out = f;
+    return LZB_OK;
+}
+
+void lzb_forest_destroy(lzb_forest_t *f) { delete f; }
+
+int lzb_set_delta(lzb_forest_t *f, float value_delta_max, void *stream)
+{
+    if (!f) return fail(LZB_E_ARG, "forest is NULL");
+    f->delta = value_delta_max;
+    k_reset_minmax<<<(f->pool.N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(f->pool);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_prepare(lzb_forest_t *f, const float *logits_dev, const float *noise_dev, float noise_weight,
+                const float *reward_dev, const float *value_dev, const int32_t *to_play_dev,
+                const float *sampled_actions_dev, void *stream)
+{
+    if (!f) return fail(LZB_E_ARG, "forest is NULL");
+    const Pool &p = f->pool;
+    if (!reward_dev || !to_play_dev) return fail(LZB_E_ARG, "reward / to_play is NULL");
+    if (p.variant == LZB_SEZ ? !sampled_actions_dev : !logits_dev) return fail(LZB_E_ARG, "logits (or sampled_actions for the sampled tree) is NULL");
+    if (p.variant == LZB_GMZ && !value_dev) return fail(LZB_E_ARG, "the Gumbel tree needs root values");
+    PrepArgs a{logits_dev, noise_dev, reward_dev, value_dev, sampled_actions_dev, to_play_dev, noise_weight};
+    dim3 grid, block; size_t smem;
+    if (int rc = launch_cfg(k_prepare, (size_t)p.A * sizeof(float), p.N, grid, block, smem)) return rc;
+    k_prepare<<<grid, block, smem, (cudaStream_t)stream>>>(p, a);
+    LZB_CUDA(cudaGetLastError());
+    f->sim = 0;
+    f->expanded = 0;
+    return LZB_OK;
+}
+
+int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const int32_t *to_play_dev, int32_t *ix_dev,
+                 int32_t *iy_dev, int64_t *last_action_dev, float *last_action_f_dev, int32_t *search_len_dev,
+                 int32_t *vtp_dev, const lzb_gather_t *gathers, int num_gathers, void *stream)
+{
+    if (!f || !cfg || !to_play_dev) return fail(LZB_E_ARG, "forest / cfg / to_play is NULL");
+    if (f->expanded < 0) return fail(LZB_E_STATE, "traverse before prepare");
+    if (num_gathers < 0 || num_gathers > 3 || (num_gathers && !gathers)) return fail(LZB_E_ARG, "0..3 gathers supported");
+    if (cfg->rng_mode != LZB_RNG_BATCH && cfg->rng_mode != LZB_RNG_PER_ROOT) return fail(LZB_E_ARG, "rng_mode must be LZB_RNG_BATCH or LZB_RNG_PER_ROOT");
+    const Pool &p = f->pool;
+    cudaStream_t st = (cudaStream_t)stream;
+    SelectArgs a{};
+    a.c_base = cfg->pb_c_base; a.c_init = cfg->pb_c_init; a.discount = cfg->discount; a.delta = f->delta;
+    a.players = cfg->players; a.sim = f->sim; a.rng_mode = cfg->rng_mode; a.seed = cfg->rng_seed;
+    a.num_simulations = cfg->num_simulations; a.ng = num_gathers;
+    a.to_play = to_play_dev; a.ix = ix_dev; a.iy = iy_dev; a.search_len = search_len_dev; a.vtp = vtp_dev;
+    a.last_action = (long long *)last_action_dev; a.last_action_f = last_action_f_dev;
+    for (int k = 0; k < num_gathers; ++k) {
+        if (!gathers[k].src_dev || !gathers[k].dst_dev || gathers[k].row_bytes <= 0 || (gathers[k].row_bytes & 3))
+            return fail(LZB_E_ARG, "gather %d: NULL pointer or row_bytes not a positive multiple of 4", k);
+        a.g[k] = Gather{(const char *)gathers[k].src_dev, (char *)gathers[k].dst_dev, (long long)gathers[k].row_bytes};
+    }
+    if (p.variant != LZB_GMZ && cfg->players == 0) {
+        k_max_to_play<<<1, 256, 0, st>>>(to_play_dev, p.N, p.scratch);
+    } else if (cfg->players < 0 || cfg->players > 2) {
+        return fail(LZB_E_ARG, "players must be 0, 1 or 2");
+    }
+    dim3 grid, block; size_t smem;
+    if (p.variant == LZB_GMZ) {
+        const int S = cfg->num_simulations, m = cfg->max_num_considered_actions;
+        if (S <= 0 || m < 0) return fail(LZB_E_ARG, "Gumbel needs num_simulations > 0 and max_num_considered_actions >= 0");
+        if (f->sim >= S) return fail(LZB_E_STATE, "more traverses (%d) than num_simulations (%d)", f->sim + 1, S);
+        if (f->vt_m != m || f->vt_s != S) {
+            f->vtable_host = considered_sequence(std::min(m, S), S); // row min(m, S) of the table (gmz :724-729)
+            const int cnt = std::min(S, p.E);
+            LZB_CUDA(cudaMemcpyAsync(p.vtable, f->vtable_host.data(), sizeof(int) * cnt, cudaMemcpyHostToDevice, st));
+            f->vt_m = m; f->vt_s = S;
+        }
+        if (int rc = launch_cfg(k_select_gumbel, (size_t)p.A * 28, p.N, grid, block, smem)) return rc;
+        k_select_gumbel<<<grid, block, smem, st>>>(p, a);
+    } else {
+        const size_t bpw = (size_t)p.A * 20;
+        if (p.variant == LZB_MZ) {
+            if (int rc = launch_cfg(k_select_puct<LZB_MZ>, bpw, p.N, grid, block, smem)) return rc;
+            k_select_puct<LZB_MZ><<<grid, block, smem, st>>>(p, a);
+        } else if (p.variant == LZB_EZ) {
+            if (int rc = launch_cfg(k_select_puct<LZB_EZ>, bpw, p.N, grid, block, smem)) return rc;
+            k_select_puct<LZB_EZ><<<grid, block, smem, st>>>(p, a);
+        } else {
+            if (int rc = launch_cfg(k_select_puct<LZB_SEZ>, bpw, p.N, grid, block, smem)) return rc;
+            k_select_puct<LZB_SEZ><<<grid, block, smem, st>>>(p, a);
+        }
+    }
+    LZB_CUDA(cudaGetLastError());
+    f->sim += 1;
+    return LZB_OK;
+}
+
+int lzb_backprop(lzb_forest_t *f, int latent_index, float discount, const float *reward_dev, const float *value_dev,
+                 const float *logits_dev, const int32_t *to_play_dev, const int32_t *is_reset_dev,
+                 int lstm_horizon_len, int32_t *is_reset_out_dev, const float *sampled_actions_dev, void *stream)
+{
+    if (!f) return fail(LZB_E_ARG, "forest is NULL");
+    const Pool &p = f->pool;
+    if (!reward_dev || !value_dev || !to_play_dev) return fail(LZB_E_ARG, "reward / value / to_play is NULL");
+    if (p.variant == LZB_SEZ ? !sampled_actions_dev : !logits_dev) return fail(LZB_E_ARG, "logits (or sampled_actions for the sampled tree) is NULL");
+    if (f->sim <= 0) return fail(LZB_E_STATE, "backprop before traverse");
+    if (latent_index <= 0 || latent_index > p.S) return fail(LZB_E_STATE, "latent_index %d outside the pool (max_sims %d)", latent_index, p.S);
+    BackupArgs a{latent_index, lstm_horizon_len, discount, reward_dev, value_dev, logits_dev, sampled_actions_dev,
+                 to_play_dev, is_reset_dev, is_reset_out_dev};
+    dim3 grid, block; size_t smem;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t bpw = (size_t)p.A * sizeof(float);
+    switch (p.variant) {
+    case LZB_MZ:
+        if (int rc = launch_cfg(k_expand_backup<LZB_MZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_expand_backup<LZB_MZ><<<grid, block, smem, st>>>(p, a);
+        break;
+    case LZB_EZ:
+        if (int rc = launch_cfg(k_expand_backup<LZB_EZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_expand_backup<LZB_EZ><<<grid, block, smem, st>>>(p, a);
+        break;
+    case LZB_GMZ:
+        if (int rc = launch_cfg(k_expand_backup<LZB_GMZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_expand_backup<LZB_GMZ><<<grid, block, smem, st>>>(p, a);
+        break;
+    default:
+        if (int rc = launch_cfg(k_expand_backup<LZB_SEZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_expand_backup<LZB_SEZ><<<grid, block, smem, st>>>(p, a);
+        break;
+    }
+    LZB_CUDA(cudaGetLastError());
+    if (latent_index > f->expanded) f->expanded = latent_index;
+    return LZB_OK;
+}
+
+int lzb_store_hidden(const float *src_dev, float *dst_dev, const int32_t *is_reset_dev, int num_roots,
+                     int64_t row_floats, void *stream)
+{
+    if (!src_dev || !dst_dev || num_roots <= 0 || row_floats <= 0) return fail(LZB_E_ARG, "store_hidden: bad argument");
+    const long long total = (long long)num_roots * row_floats;
+    const int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
+    k_store_hidden<<<blocks, 256, 0, (cudaStream_t)stream>>>(src_dev, dst_dev, is_reset_dev, num_roots, row_floats);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_root_outputs(lzb_forest_t *f, int32_t *visits_dev, int32_t *legal_count_dev, float *values_dev,
+                     float discount, float *gumbel_policies_dev, float *gumbel_children_values_dev, void *stream)
+{
+    if (!f) return fail(LZB_E_ARG, "forest is NULL");
+    const Pool &p = f->pool;
+    if ((gumbel_policies_dev || gumbel_children_values_dev) && p.variant != LZB_GMZ)
+        return fail(LZB_E_ARG, "policies / children values exist only for the Gumbel tree");
+    dim3 grid, block; size_t smem;
+    if (int rc = launch_cfg(k_root_outputs, (size_t)p.A * 28, p.N, grid, block, smem)) return rc;
+    k_root_outputs<<<grid, block, smem, (cudaStream_t)stream>>>(p, visits_dev, legal_count_dev, values_dev, discount,
+                                                               gumbel_policies_dev, gumbel_children_values_dev);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_dump_tree(lzb_forest_t *f, int tree, int32_t *visit_dev, float *value_sum_dev, float *prior_dev,
+                  float *reward_dev, int32_t *child_e_dev, int32_t *hdr_dev, float *raw_value_dev, void *stream)
+{
+    if (!f || tree < 0 || tree >= f->pool.N) return fail(LZB_E_ARG, "dump_tree: bad tree index");
+    if (f->expanded < 0) return fail(LZB_E_STATE, "dump_tree before prepare");
+    k_dump_tree<<<1, 32, 0, (cudaStream_t)stream>>>(f->pool, tree, f->expanded, visit_dev, value_sum_dev, prior_dev,
+                                                   reward_dev, child_e_dev, hdr_dev, raw_value_dev);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_dump_paths(lzb_forest_t *f, int32_t *path_actions_dev, int path_stride, void *stream)
+{
+    if (!f || !path_actions_dev || path_stride <= 0) return fail(LZB_E_ARG, "dump_paths: bad argument");
+    k_dump_paths<<<(f->pool.N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(f->pool, path_actions_dev, path_stride);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_minmax(lzb_forest_t *f, float *min_dev, float *max_dev, void *stream)
+{
+    if (!f || !min_dev || !max_dev) return fail(LZB_E_ARG, "minmax: bad argument");
+    k_minmax<<<(f->pool.N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(f->pool, min_dev, max_dev);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_root_stats(lzb_forest_t *f, int32_t *visit_dev, float *value_sum_dev, float *reward_dev, void *stream)
+{
+    if (!f || !visit_dev || !value_sum_dev || !reward_dev) return fail(LZB_E_ARG, "root_stats: bad argument");
+    k_root_stats<<<(f->pool.N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(f->pool, visit_dev, value_sum_dev, reward_dev);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_gumbel_table(int m, int S, int32_t *out_host)
+{
+    if (m < 0 || S <= 0 || !out_host) return fail(LZB_E_ARG, "gumbel_table: bad argument");
+    for (int r = 0; r <= m; ++r) {
+        std::vector<int> seq = considered_sequence(r, S);
+        memcpy(out_host + (size_t)r * S, seq.data(), sizeof(int) * S);
+    }
+    return LZB_OK;
+}
+
+int lzb_gumbel_noise(float scale, int shape, float *out_host)
+{
+    if (shape < 0 || !out_host) return fail(LZB_E_ARG, "gumbel_noise: bad argument");
+    gumbel_noise(scale, shape, out_host);
+    return LZB_OK;
+}
+
+int lzb_test_expf(const float *x_dev, float *out_dev, int64_t n, void *stream)
+{
+    k_test_expf<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(x_dev, out_dev, (long long)n);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_test_logf(const float *x_dev, float *out_dev, int64_t n, void *stream)
+{
+    k_test_logf<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(x_dev, out_dev, (long long)n);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,44 @@
+// Node-pool layout shared by all kernels (see DESIGN.md "Data layout in HBM").
+//
+// One search expands exactly one node per tree per simulation (mcts_ctree.py:255-321), so node
+// allocation is arithmetic: the node expanded with current_latent_state_index e (0 = root,
+// e = simulation_index + 1 otherwise, cnode.cpp:497) owns the child block [e*A, e*A + A) of its
+// tree.  A child is addressed by its slot e*A + j, j = position in the parent's legal-action list
+// (== the action id for every non-root node, cnode.cpp:101-107,138-139).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/lzb200.h"
+
+namespace lzb {
+
+constexpr float kFloatMax = 1000000.0f; // common_lib/cminimax.h:9
+constexpr float kFloatMin = -kFloatMax;
+
+// child record, 16 B: one LDG.128 per lane per level
+//   x: visit_count (low 16 bits) | (expansion index + 1) << 16   (0 in the high half = not expanded)
+//   y: value_sum   z: prior   w: reward (mz, gmz) or value_prefix (ez, sez)
+__device__ __forceinline__ int child_visits(int x) { return x & 0xffff; }
+__device__ __forceinline__ int child_expansion(int x) { return (int)((unsigned)x >> 16) - 1; }
+__device__ __forceinline__ int child_pack(int visits, int expansion) { return (visits & 0xffff) | ((expansion + 1) << 16); }
+
+struct Pool {
+    int variant, N, A, S, E, D, root_offset;
+    int4 *child;    // [N][E*A]
+    int4 *hdr;      // [N][E]  {n_children, to_play, is_reset, raw_value bits} of the node expanded as e
+    int4 *root;     // [N]     {visit_count, value_sum bits, reward bits, unused}
+    int *legal;     // [N][A]  root legal-action ids by position
+    float2 *minmax; // [N]     {minimum, maximum} (cminimax.h:14-24)
+    int4 *path_a;   // [N][S+1] per level q of the current search path: the chosen child's record as read by
+                    //          select {slot, x, value_sum bits, reward bits} (node q+1 of the path)
+    int2 *path_b;   // [N][S+1] per level q: {to_play, is_reset} of the node the choice was made AT (node q)
+    int4 *res;      // [N]     {search_len, parent expansion (ix), last position, virtual_to_play}
+    int *best;      // [N][E]  best_action position chosen at each expanded node (cnode.cpp:806)
+    float *actions; // [N][E][A][D] sampled-action table (sez only)
+    float *gumbel;  // [A]     gumbel noise shared by every root (gmz cnode.cpp:87-89)
+    int *vtable;    // [S]     considered-visit sequence of the current Gumbel config
+    int *scratch;   // [4]     {max(to_play), ...}
+};
+
+} // namespace lzb

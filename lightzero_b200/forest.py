@@ -1,0 +1,199 @@
+"""Device-tensor front end of liblzb200.so: one ``Forest`` = the N search trees of one batch in HBM.
+
+This is the fast path used by the rewritten ``search()`` loops (lightzero_b200/tree_search); the
+list-based reference API (lightzero_b200/ctree/*.py) is a thin layer over it.  PyTorch only provides
+device memory and the CUDA stream here.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import Gather, SearchCfg, check
+
+VARIANT_ID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3}
+RNG_BATCH, RNG_PER_ROOT = 1, 2
+
+
+def _stream(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _dev(x, dtype, device):
+    """Bring a list / numpy array / tensor to a contiguous device tensor of ``dtype`` (one H2D copy at most)."""
+    if x is None:
+        return None
+    if isinstance(x, torch.Tensor):
+        return x.to(device=device, dtype=dtype, non_blocking=True).contiguous()
+    return torch.as_tensor(x, dtype=dtype).to(device, non_blocking=True).contiguous()
+
+
+class Forest:
+    def __init__(self, variant, num_roots, action_space, max_sims, legal_actions=None, action_dim=0, root_offset=0,
+                 device="cuda"):
+        if not torch.cuda.is_available():
+            raise RuntimeError("lightzero_b200 needs a CUDA device (there is no CPU fallback)")
+        self.L = _lib.lib()
+        self.device = torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.variant = variant
+        self.N, self.A, self.S, self.D = int(num_roots), int(action_space), int(max_sims), int(action_dim)
+        self.root_offset = int(root_offset)
+        nbytes = C.c_size_t(0)
+        check(self.L.lzb_forest_bytes(VARIANT_ID[variant], self.N, self.A, self.S, self.D, C.byref(nbytes)))
+        self.workspace = torch.empty(nbytes.value, dtype=torch.uint8, device=self.device)
+        cnt = idx = None
+        if legal_actions is not None and variant != "sez":
+            if isinstance(legal_actions, tuple):
+                cnt, idx = legal_actions
+                cnt, idx = _dev(cnt, torch.int32, self.device), _dev(idx, torch.int32, self.device)
+            else:
+                cnt_h = torch.tensor([len(l) for l in legal_actions], dtype=torch.int32)
+                idx_h = torch.zeros((self.N, self.A), dtype=torch.int32)
+                for i, l in enumerate(legal_actions):
+                    if len(l) > self.A:
+                        raise ValueError("root %d has more legal actions than the action space" % i)
+                    if len(l):
+                        idx_h[i, :len(l)] = torch.as_tensor(l, dtype=torch.int32)
+                cnt, idx = cnt_h.to(self.device), idx_h.to(self.device)
+        self._legal = (cnt, idx)
+        h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            check(self.L.lzb_forest_create(C.byref(h), _p(self.workspace), nbytes.value, VARIANT_ID[variant], self.N,
+                                           self.A, self.S, self.D, self.root_offset, _p(cnt), _p(idx),
+                                           _stream(self.device)))
+        self.h = h
+
+    def __del__(self):
+        h = getattr(self, "h", None)
+        if h:
+            self.L.lzb_forest_destroy(h)
+            self.h = None
+
+    # ------------------------------------------------------------------ reference surface, tensor flavoured
+    def set_delta(self, value_delta_max):
+        check(self.L.lzb_set_delta(self.h, float(value_delta_max), _stream(self.device)))
+
+    def prepare(self, logits, noise, noise_weight, reward, to_play, value=None, sampled_actions=None):
+        d = self.device
+        logits = _dev(logits, torch.float32, d)
+        noise = _dev(noise, torch.float32, d)
+        reward = _dev(reward, torch.float32, d)
+        value = _dev(value, torch.float32, d)
+        to_play = _dev(to_play, torch.int32, d)
+        sampled_actions = _dev(sampled_actions, torch.float32, d)
+        if logits is not None and tuple(logits.shape) != (self.N, self.A):
+            raise ValueError("logits must be [N, A]")
+        if noise is not None and tuple(noise.shape) != (self.N, self.A):
+            raise ValueError("noise must be [N, A] (row i: noise by position in root i's legal list)")
+        check(self.L.lzb_prepare(self.h, _p(logits), _p(noise), float(noise_weight), _p(reward), _p(value), _p(to_play),
+                                 _p(sampled_actions), _stream(d)))
+
+    def make_cfg(self, pb_c_base=19652, pb_c_init=1.25, discount=0.997, players=0, num_simulations=0,
+                 max_num_considered_actions=0, rng_mode=RNG_PER_ROOT, rng_seed=0):
+        return SearchCfg(int(pb_c_base), float(pb_c_init), float(discount), int(players), int(num_simulations),
+                         int(max_num_considered_actions), int(rng_mode), int(rng_seed))
+
+    def traverse(self, cfg, to_play, out=None, gathers=()):
+        """One batch_traverse. ``out``: optional dict of preallocated tensors (ix, iy, last_action, last_action_f,
+        search_len, vtp); missing ones are allocated. ``gathers``: [(pool[E,N,...], dst[N,...])]."""
+        d = self.device
+        N = self.N
+        to_play = _dev(to_play, torch.int32, d)
+        o = dict(out) if out else {}
+        for k in ("ix", "iy", "search_len", "vtp"):
+            if k not in o:
+                o[k] = torch.empty(N, dtype=torch.int32, device=d)
+        if "last_action" not in o:
+            o["last_action"] = torch.empty(N, dtype=torch.int64, device=d)
+        if self.variant == "sez" and "last_action_f" not in o:
+            o["last_action_f"] = torch.empty((N, self.D), dtype=torch.float32, device=d)
+        garr = (Gather * max(len(gathers), 1))()
+        for k, (src, dst) in enumerate(gathers):
+            if not (src.is_contiguous() and dst.is_contiguous()):
+                raise ValueError("gather tensors must be contiguous")
+            row = dst[0].numel() * dst.element_size()
+            if src.shape[1] != N or src[0, 0].numel() * src.element_size() != row:
+                raise ValueError("gather pool must be [E, N, row] matching dst [N, row]")
+            garr[k] = Gather(src.data_ptr(), dst.data_ptr(), row)
+        check(self.L.lzb_traverse(self.h, C.byref(cfg), _p(to_play), _p(o["ix"]), _p(o["iy"]), _p(o["last_action"]),
+                                  _p(o.get("last_action_f")), _p(o["search_len"]), _p(o["vtp"]), garr, len(gathers),
+                                  _stream(d)))
+        return o
+
+    def backprop(self, latent_index, discount, reward, value, logits, to_play, is_reset=None, lstm_horizon_len=0,
+                 is_reset_out=None, sampled_actions=None):
+        d = self.device
+        reward = _dev(reward, torch.float32, d).reshape(-1)
+        value = _dev(value, torch.float32, d).reshape(-1)
+        logits = _dev(logits, torch.float32, d)
+        to_play = _dev(to_play, torch.int32, d)
+        is_reset = _dev(is_reset, torch.int32, d)
+        sampled_actions = _dev(sampled_actions, torch.float32, d)
+        if reward.numel() != self.N or value.numel() != self.N:
+            raise ValueError("reward / value must have N elements")
+        if logits is not None and (logits.numel() != self.N * self.A and self.variant != "sez"):
+            raise ValueError("logits must be [N, A]")
+        check(self.L.lzb_backprop(self.h, int(latent_index), float(discount), _p(reward), _p(value), _p(logits),
+                                  _p(to_play), _p(is_reset), int(lstm_horizon_len), _p(is_reset_out),
+                                  _p(sampled_actions), _stream(d)))
+
+    def store_hidden(self, src, dst, is_reset):
+        check(self.L.lzb_store_hidden(_p(src), _p(dst), _p(is_reset), self.N, src.numel() // self.N, _stream(self.device)))
+
+    def root_outputs(self, discount=0.0, gumbel=False):
+        d = self.device
+        visits = torch.empty((self.N, self.A), dtype=torch.int32, device=d)
+        legal_count = torch.empty(self.N, dtype=torch.int32, device=d)
+        values = torch.empty(self.N, dtype=torch.float32, device=d)
+        pol = cv = None
+        if gumbel:
+            pol = torch.empty((self.N, self.A), dtype=torch.float32, device=d)
+            cv = torch.empty((self.N, self.A), dtype=torch.float32, device=d)
+        check(self.L.lzb_root_outputs(self.h, _p(visits), _p(legal_count), _p(values), float(discount), _p(pol), _p(cv),
+                                      _stream(d)))
+        out = dict(visits=visits, legal_count=legal_count, values=values)
+        if gumbel:
+            out.update(policies=pol, children_values=cv)
+        return out
+
+    # ------------------------------------------------------------------ introspection (tests)
+    def dump_tree(self, i):
+        d = self.device
+        E, A = self.S + 1, self.A
+        visit = torch.full((E, A), -1, dtype=torch.int32, device=d)
+        vsum = torch.zeros((E, A), dtype=torch.float32, device=d)
+        prior = torch.zeros((E, A), dtype=torch.float32, device=d)
+        reward = torch.zeros((E, A), dtype=torch.float32, device=d)
+        child_e = torch.full((E, A), -2, dtype=torch.int32, device=d)
+        hdr = torch.full((E, 4), -9, dtype=torch.int32, device=d)
+        raw = torch.zeros(E, dtype=torch.float32, device=d)
+        check(self.L.lzb_dump_tree(self.h, int(i), _p(visit), _p(vsum), _p(prior), _p(reward), _p(child_e), _p(hdr),
+                                   _p(raw), _stream(d)))
+        return dict(visit=visit.cpu().numpy(), value_sum=vsum.cpu().numpy(), prior=prior.cpu().numpy(),
+                    reward=reward.cpu().numpy(), child_e=child_e.cpu().numpy(), hdr=hdr.cpu().numpy(),
+                    raw_value=raw.cpu().numpy())
+
+    def dump_paths(self, stride):
+        out = torch.full((self.N, stride), -1, dtype=torch.int32, device=self.device)
+        check(self.L.lzb_dump_paths(self.h, _p(out), int(stride), _stream(self.device)))
+        return out.cpu().numpy()
+
+    def minmax(self):
+        mn = torch.empty(self.N, dtype=torch.float32, device=self.device)
+        mx = torch.empty(self.N, dtype=torch.float32, device=self.device)
+        check(self.L.lzb_minmax(self.h, _p(mn), _p(mx), _stream(self.device)))
+        return mn.cpu().numpy(), mx.cpu().numpy()
+
+    def root_stats(self):
+        d = self.device
+        vc = torch.empty(self.N, dtype=torch.int32, device=d)
+        vs = torch.empty(self.N, dtype=torch.float32, device=d)
+        rw = torch.empty(self.N, dtype=torch.float32, device=d)
+        check(self.L.lzb_root_stats(self.h, _p(vc), _p(vs), _p(rw), _stream(d)))
+        return vc.cpu().numpy(), vs.cpu().numpy(), rw.cpu().numpy()

@@ -1,0 +1,72 @@
+"""Shared scenario generator for the parity tests (seeded synthetic 'model' outputs)."""
+import numpy as np
+
+PB_C_BASE, PB_C_INIT = 19652, 1.25
+TICTACTOE_MASKS = [  # 16 x 9 action mask of lzero/mcts/tests/test_mcts_ctree.py:120-137
+    [0, 0, 0, 1, 0, 1, 1, 0, 0], [1, 0, 0, 1, 0, 0, 1, 0, 0], [1, 1, 0, 0, 0, 1, 0, 0, 1], [0, 0, 1, 0, 0, 1, 0, 0, 1],
+    [1, 0, 0, 1, 1, 0, 0, 0, 1], [1, 1, 0, 0, 0, 0, 1, 0, 1], [1, 0, 0, 1, 1, 0, 0, 0, 1], [1, 1, 0, 0, 0, 0, 1, 1, 0],
+    [1, 0, 1, 0, 0, 0, 1, 0, 1], [0, 1, 0, 0, 1, 1, 0, 0, 1], [1, 1, 0, 1, 0, 0, 0, 1, 0], [0, 0, 1, 0, 0, 1, 1, 1, 0],
+    [1, 0, 0, 1, 0, 0, 1, 0, 1], [0, 0, 1, 1, 0, 1, 0, 0, 1], [1, 0, 1, 0, 1, 0, 0, 1, 0], [0, 1, 0, 1, 0, 0, 1, 0, 1],
+]
+
+
+class Scenario:
+    """Seeded inputs of one search: root logits / rewards / values / noise and per-simulation model outputs."""
+
+    def __init__(self, variant, n, A, S, seed=0, legal=None, to_play=None, discount=0.997, max_considered=4,
+                 reward_scale=0.1, zero_model=False, K=0, D=0):
+        rng = np.random.default_rng(seed)
+        self.variant, self.n, self.A, self.S, self.discount, self.m = variant, n, A, S, discount, max_considered
+        self.K, self.D = K, D
+        self.legal = legal if legal is not None else [list(range(A)) for _ in range(n)]
+        self.to_play = np.asarray(to_play if to_play is not None else [-1] * n, np.int32)
+        z = 0.0 if zero_model else 1.0
+        self.root_logits = (rng.standard_normal((n, A)) * z).astype(np.float32)
+        self.root_reward = (rng.standard_normal(n) * reward_scale * z).astype(np.float32)
+        self.root_value = (rng.standard_normal(n) * z).astype(np.float32)
+        self.noises = [rng.dirichlet([0.3] * len(l)).astype(np.float32) for l in self.legal]
+        self.noise_pad = np.zeros((n, A), np.float32)
+        for i, nz in enumerate(self.noises):
+            self.noise_pad[i, :len(nz)] = nz
+        self.logits = (rng.standard_normal((S, n, A)) * z).astype(np.float32)
+        self.reward = (rng.standard_normal((S, n)) * reward_scale * z).astype(np.float32)
+        if variant in ("ez", "sez"):  # value prefixes accumulate along a path in a real model; any floats do here
+            self.reward = (rng.standard_normal((S, n)) * z).astype(np.float32)
+        self.value = (rng.standard_normal((S, n)) * z).astype(np.float32)
+        if variant == "sez":
+            self.root_actions = np.tanh(rng.standard_normal((n, K, D))).astype(np.float32)
+            self.actions = np.tanh(rng.standard_normal((S, n, K, D))).astype(np.float32)
+
+    def model_fn(self, s, ix, iy, last_action):
+        out = dict(reward=self.reward[s], value=self.value[s], logits=self.logits[s])
+        if self.variant == "sez":
+            out["sampled_actions"] = self.actions[s]
+        return out
+
+
+def bits(a):
+    a = np.ascontiguousarray(a)
+    return a.view(np.uint32) if a.dtype == np.float32 else a
+
+
+def assert_same(a, b, what):
+    x, y = bits(np.asarray(a)), bits(np.asarray(b))
+    assert x.shape == y.shape, "%s: shape %s vs %s" % (what, x.shape, y.shape)
+    if not np.array_equal(x, y):
+        bad = np.argwhere(x != y)
+        raise AssertionError("%s: %d mismatches, first at %s: %r vs %r" % (
+            what, len(bad), bad[0], np.asarray(a)[tuple(bad[0])], np.asarray(b)[tuple(bad[0])]))
+
+
+def run_cpu(forest, sc, rng_mode, seed, record=None, horizon=5):
+    """Drive an OracleForest / RefForest through one full search of scenario ``sc``."""
+    forest.set_delta(0.01)
+    forest.set_rng(rng_mode, seed)
+    kw = {}
+    if sc.variant == "sez":
+        kw["sampled_actions"] = sc.root_actions
+    forest.prepare(0.25, sc.noises if sc.variant != "sez" else None, sc.root_reward, sc.root_logits, sc.to_play,
+                   values=sc.root_value, **kw)
+    forest.run_search(sc.model_fn, sc.S, PB_C_BASE, PB_C_INIT, sc.discount, sc.to_play, max_considered=sc.m,
+                      lstm_horizon_len=horizon, record=record)
+    return forest

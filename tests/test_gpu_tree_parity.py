@@ -1,0 +1,199 @@
+"""GPU parity: the CUDA forest (through the C ABI) against the CPU oracle on identical seeded inputs.
+
+Bar (BASELINE.json north_star): selected actions, search paths and visit counts bit-exact;
+root values, value sums, priors and MinMax bounds compared as raw fp32 bits (the reference tree is fp32,
+so the tolerance is ZERO ulp, stricter than the 1e-5 relative fallback the north_star allows).
+"""
+import numpy as np
+import pytest
+
+from tests.common import PB_C_BASE, PB_C_INIT, TICTACTOE_MASKS, Scenario, assert_same, run_cpu
+
+pytestmark = pytest.mark.gpu
+
+
+def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0):
+    import torch
+    from lightzero_b200.forest import Forest
+    f = Forest(sc.variant, sc.n, sc.K if sc.variant == "sez" else sc.A, sc.S, legal_actions=sc.legal, action_dim=sc.D,
+               root_offset=root_offset)
+    f.set_delta(0.01)
+    dev = f.device
+    t = lambda a: torch.as_tensor(a).to(dev)
+    if sc.variant == "sez":
+        f.prepare(None, None, 0.25, t(sc.root_reward), t(sc.to_play), sampled_actions=t(sc.root_actions))
+    else:
+        f.prepare(t(sc.root_logits), t(sc.noise_pad), 0.25, t(sc.root_reward), t(sc.to_play),
+                  value=t(sc.root_value) if sc.variant == "gmz" else None)
+    players = 1 if int(sc.to_play.max()) == -1 else 2
+    cfg = f.make_cfg(PB_C_BASE, PB_C_INIT, sc.discount, players=players, num_simulations=sc.S,
+                     max_num_considered_actions=sc.m, rng_mode=rng_mode, rng_seed=seed)
+    tp = t(sc.to_play)
+    for s in range(sc.S):
+        o = f.traverse(cfg, tp)
+        m = sc.model_fn(s, None, None, None)
+        kw = {}
+        if sc.variant in ("ez", "sez"):
+            kw["lstm_horizon_len"] = horizon
+            kw["is_reset_out"] = torch.empty(sc.n, dtype=torch.int32, device=dev)
+        if sc.variant == "sez":
+            kw["sampled_actions"] = t(m["sampled_actions"])
+        if record is not None:
+            rec = {k: v.cpu().numpy() for k, v in o.items()}
+            rec["paths"] = f.dump_paths(sc.S + 1)
+            record.append(rec)
+        f.backprop(s + 1, sc.discount, t(m["reward"]), t(m["value"]), t(m["logits"]), o["vtp"], **kw)
+        if record is not None and "is_reset_out" in kw:
+            record[-1]["is_reset"] = kw["is_reset_out"].cpu().numpy()
+    torch.cuda.synchronize()
+    return f
+
+
+def compare(sc, rng_mode=2, seed=2024, trees=4):
+    from oracle.binding import OracleForest
+    orc = OracleForest(sc.variant, sc.n, sc.A, sc.legal, K=sc.K, D=sc.D)
+    rec_c, rec_g = [], []
+    run_cpu(orc, sc, rng_mode, seed, record=rec_c)
+    gpu = run_gpu(sc, rng_mode, seed, record=rec_g)
+    for s, (c, g) in enumerate(zip(rec_c, rec_g)):
+        for k in ("search_len", "ix", "iy", "vtp", "paths"):
+            assert_same(g[k], c[k], "sim %d %s" % (s, k))
+        if sc.variant == "sez":
+            assert_same(g["last_action_f"], c["last_action_f"], "sim %d last_action_f" % s)
+        else:
+            assert_same(g["last_action"].astype(np.int32), c["last_action"], "sim %d last_action" % s)
+        if c.get("is_reset") is not None:
+            assert_same(g["is_reset"], c["is_reset"], "sim %d is_reset" % s)
+    out = gpu.root_outputs(sc.discount, gumbel=sc.variant == "gmz")
+    dist, ln = orc.distributions()
+    W = dist.shape[1]
+    assert_same(out["legal_count"].cpu().numpy(), ln, "legal_count")
+    assert_same(out["visits"].cpu().numpy()[:, :W], np.where(dist < 0, 0, dist), "visit counts")
+    assert_same(out["values"].cpu().numpy(), orc.values(), "root values")
+    assert (out["visits"].cpu().numpy().sum(1) == sc.S).all()
+    mn, mx = gpu.minmax()
+    omn, omx = orc.minmax()
+    assert_same(mn, omn, "minmax.min")
+    assert_same(mx, omx, "minmax.max")
+    vc, vs, rw = gpu.root_stats()
+    ovc, ovs, orw = orc.root_stats()
+    assert_same(vc, ovc, "root visit_count")
+    assert (vc == sc.S + 1).all()
+    assert_same(vs, ovs, "root value_sum")
+    for i in range(min(trees, sc.n)):
+        tg, tc = gpu.dump_tree(i), orc.dump_tree(i, sc.S + 1)
+        for k in ("visit", "value_sum", "reward", "child_e", "hdr") + (("prior",) if sc.variant != "sez" else ()):
+            assert_same(tg[k], tc[k], "tree %d %s" % (i, k))
+        if sc.variant == "gmz":
+            assert_same(tg["raw_value"], tc["raw_value"], "tree %d raw_value" % i)
+    if sc.variant == "gmz":
+        p, v = orc.gumbel_outputs(sc.discount)
+        assert_same(out["policies"].cpu().numpy(), p, "gumbel improved policy")
+        assert_same(out["children_values"].cpu().numpy(), v, "gumbel completed child values")
+    return gpu, orc
+
+
+def test_device_libm_matches_oracle():
+    import torch
+    from lightzero_b200 import _lib
+    from lightzero_b200._lib import check
+    from oracle.binding import oracle_lib
+    import ctypes as C
+    L, O = _lib.lib(), oracle_lib()
+    rng = np.random.default_rng(0)
+    # softmax arguments are <= 0; pUCT log arguments are >= 1; plus raw bit patterns over the whole range
+    xs = np.concatenate([-np.abs(rng.standard_normal(1 << 20) * 8).astype(np.float32),
+                         rng.integers(0, 2 ** 32, 1 << 20, dtype=np.uint64).astype(np.uint32).view(np.float32),
+                         np.array([0.0, -0.0, -87.9, -88.0, -103.0, -103.9, -104.5, 88.7, 89.0, -np.inf, np.inf], np.float32)])
+    ls = np.concatenate([(1 + np.abs(rng.standard_normal(1 << 20)) * 3).astype(np.float32),
+                         rng.integers(0, 2 ** 32, 1 << 20, dtype=np.uint64).astype(np.uint32).view(np.float32),
+                         np.array([1.0, 1.0000001, 0.0, 1e-40, np.inf, 19653.0 / 19652.0], np.float32)])
+    for name, x, fn in (("expf", xs, "orc_expf_array"), ("logf", ls, "orc_logf_array")):
+        want = np.empty_like(x)
+        getattr(O, fn)(x.ctypes.data_as(C.c_void_p), want.ctypes.data_as(C.c_void_p), C.c_long(len(x)))
+        xd = torch.from_numpy(x).cuda()
+        od = torch.empty_like(xd)
+        check(getattr(L, "lzb_test_" + name)(xd.data_ptr(), od.data_ptr(), len(x), None))
+        got = od.cpu().numpy()
+        both_nan = np.isnan(got) & np.isnan(want)
+        bad = (got.view(np.uint32) != want.view(np.uint32)) & ~both_nan
+        assert not bad.any(), "%s: %d mismatches, e.g. x=%r got=%r want=%r" % (name, bad.sum(), x[bad][0], got[bad][0], want[bad][0])
+
+
+@pytest.mark.parametrize("rng_mode", [1, 2])
+def test_muzero_cartpole_shape(rng_mode):  # C1: 8 roots x 25 sims x A=2
+    compare(Scenario("mz", 8, 2, 25, seed=1), rng_mode=rng_mode)
+
+
+def test_muzero_synthetic_a18():  # C5 shape at a size the oracle finishes in seconds
+    compare(Scenario("mz", 512, 18, 50, seed=2))
+
+
+def test_muzero_zero_model_all_ties():  # the reference tests' fake model: every level is one big tie
+    gpu, _ = compare(Scenario("mz", 16, 9, 40, seed=3, zero_model=True))
+    assert (gpu.root_outputs()["values"].cpu().numpy() == 0.0).all()
+
+
+def test_muzero_legal_masks():  # the 16 x 9 mask of test_mcts_ctree.py:120-137
+    legal = [[a for a, x in enumerate(row) if x == 1] for row in TICTACTOE_MASKS]
+    compare(Scenario("mz", 16, 9, 50, seed=4, legal=legal))
+
+
+def test_muzero_two_player_sign_flips():  # C4': to_play alternation, gamma = 1
+    compare(Scenario("mz", 32, 9, 25, seed=5, to_play=[1, 2] * 16, discount=1.0))
+
+
+def test_muzero_to_play_zero_runs_two_player_branch():  # asserts are compiled out
+    compare(Scenario("mz", 16, 9, 25, seed=6, to_play=[0] * 16))
+
+
+def test_muzero_deep_paths_more_than_one_warp():  # A=2, 200 sims: search paths longer than 32 nodes
+    sc = Scenario("mz", 8, 2, 200, seed=7, reward_scale=0.0)
+    sc.value[:] = 0.0
+    sc.root_logits[:] = 0.0
+    sc.logits[:] = np.array([8.0, -8.0], np.float32)  # one dominant prior drives a deep chain
+    compare(sc)
+
+
+def test_muzero_wide_action_space_multi_chunk():  # A > 32 exercises the chunked warp loops
+    compare(Scenario("mz", 16, 80, 60, seed=8))
+
+
+def test_efficientzero_pong_shape():  # C2: A=6, 50 sims, value_prefix + lstm_horizon_len=5 resets
+    compare(Scenario("ez", 64, 6, 50, seed=9))
+
+
+def test_efficientzero_two_player():
+    compare(Scenario("ez", 32, 9, 25, seed=10, to_play=[2, 1] * 16, discount=1.0))
+
+
+def test_gumbel_tictactoe_masks():  # C4: bot mode, legal masks, m=3, 30 sims, gamma=1
+    legal = [[a for a, x in enumerate(row) if x == 1] for row in TICTACTOE_MASKS]
+    compare(Scenario("gmz", 16, 9, 30, seed=11, legal=legal, discount=1.0, max_considered=3))
+
+
+def test_gumbel_gomoku_shape():  # C4: 6x6 board, A=36, m=6, 50 sims
+    compare(Scenario("gmz", 32, 36, 50, seed=12, discount=1.0, max_considered=6))
+
+
+def test_gumbel_m16_a18():
+    compare(Scenario("gmz", 64, 18, 50, seed=13, max_considered=16))
+
+
+def test_sampled_continuous_halfcheetah_shape():  # C3: K=20, D=6, 50 sims
+    compare(Scenario("sez", 8, 12, 50, seed=14, K=20, D=6))
+
+
+def test_root_offset_keys_the_tiebreak_stream():
+    """Sharding invariance: roots [4, 8) searched as a shard with root_offset=4 equal the same roots of the full batch."""
+    full = Scenario("mz", 8, 6, 30, seed=15, zero_model=True)
+    g_full = run_gpu(full, 2, 77)
+    part = Scenario("mz", 8, 6, 30, seed=15, zero_model=True)
+    for name in ("root_logits", "root_reward", "root_value", "noise_pad", "to_play"):
+        setattr(part, name, getattr(full, name)[4:])
+    part.logits, part.reward, part.value = full.logits[:, 4:], full.reward[:, 4:], full.value[:, 4:]
+    part.legal, part.n = full.legal[4:], 4
+    g_part = run_gpu(part, 2, 77, root_offset=4)
+    a = g_full.root_outputs()["visits"].cpu().numpy()[4:]
+    b = g_part.root_outputs()["visits"].cpu().numpy()
+    assert_same(b, a, "sharded visits")

@@ -1,0 +1,126 @@
+"""Pins the CPU oracle (oracle/mcts_oracle.c) against the compiled, unmodified reference ctree
+(oracle/_ref, built from /root/reference by oracle/build.py) and against the committed golden fixtures
+(tests/golden/*.npz, generated from the compiled reference by tests/golden/make_golden.py).
+
+Everything is compared bit-for-bit: leaf indices, last actions, search paths, visit counts, and the raw
+fp32 bits of root values, MinMax bounds, priors and value sums.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle.binding import OracleForest, RefForest, ref_available
+from tests.common import TICTACTOE_MASKS, Scenario, assert_same, run_cpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LEGAL9 = [[a for a, x in enumerate(row) if x == 1] for row in TICTACTOE_MASKS]
+
+CASES = {
+    # name: (scenario kwargs, rng_mode)
+    "mz_cartpole": (dict(variant="mz", n=8, A=2, S=25, seed=1), 2),
+    "mz_a18_batch": (dict(variant="mz", n=64, A=18, S=50, seed=2), 1),
+    "mz_a18_per_root": (dict(variant="mz", n=32, A=18, S=50, seed=3), 2),
+    "mz_zero_model": (dict(variant="mz", n=16, A=9, S=40, seed=4, zero_model=True), 2),
+    "mz_masks": (dict(variant="mz", n=16, A=9, S=50, seed=5, legal=LEGAL9), 2),
+    "mz_two_player": (dict(variant="mz", n=32, A=9, S=25, seed=6, to_play=[1, 2] * 16, discount=1.0), 2),
+    "mz_to_play_zero": (dict(variant="mz", n=16, A=9, S=25, seed=7, to_play=[0] * 16), 2),
+    "mz_wide": (dict(variant="mz", n=8, A=80, S=60, seed=8), 2),
+    "ez_pong": (dict(variant="ez", n=32, A=6, S=50, seed=9), 2),
+    "ez_two_player": (dict(variant="ez", n=32, A=9, S=25, seed=10, to_play=[2, 1] * 16, discount=1.0), 1),
+    "gmz_tictactoe": (dict(variant="gmz", n=16, A=9, S=30, seed=11, legal=LEGAL9, discount=1.0, max_considered=3), 1),
+    "gmz_gomoku": (dict(variant="gmz", n=32, A=36, S=50, seed=12, discount=1.0, max_considered=6), 1),
+    "gmz_m16": (dict(variant="gmz", n=16, A=18, S=50, seed=13, max_considered=16), 1),
+}
+
+
+def search_summary(forest, sc, rec, trees=3):
+    """Everything a parity check looks at, as a flat dict of numpy arrays."""
+    out = {}
+    for k in ("ix", "iy", "last_action", "search_len", "vtp", "paths"):
+        out[k] = np.stack([r[k] for r in rec])
+    d, ln = forest.distributions()
+    out["dist"], out["dist_len"] = d, ln
+    out["values"] = forest.values()
+    out["mm_min"], out["mm_max"] = forest.minmax()
+    vc, vs, rw = forest.root_stats()
+    out["root_visits"], out["root_value_sum"] = vc, vs
+    for i in range(min(trees, sc.n)):
+        t = forest.dump_tree(i, sc.S + 1)
+        for k in ("visit", "value_sum", "prior", "reward", "child_e", "hdr"):
+            out["tree%d_%s" % (i, k)] = t[k]
+    if sc.variant == "gmz":
+        out["gmz_policies"], out["gmz_child_values"] = forest.gumbel_outputs(sc.discount)
+    return out
+
+
+def oracle_summary(name):
+    kw, mode = CASES[name]
+    sc = Scenario(**kw)
+    rec = []
+    f = run_cpu(OracleForest(sc.variant, sc.n, sc.A, sc.legal), sc, mode, 2024, record=rec)
+    return sc, search_summary(f, sc, rec)
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_oracle_matches_golden_fixture(name):
+    path = os.path.join(HERE, "golden", name + ".npz")
+    assert os.path.exists(path), "missing fixture %s (run tests/golden/make_golden.py where /root/reference exists)" % path
+    want = np.load(path)
+    sc, got = oracle_summary(name)
+    assert sorted(want.files) == sorted(got)
+    for k in want.files:
+        assert_same(got[k], want[k], "%s/%s" % (name, k))
+    assert (got["dist"].clip(min=0).sum(1) == sc.S).all()
+    assert (got["root_visits"] == sc.S + 1).all()
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_oracle_matches_compiled_reference(name):
+    kw, mode = CASES[name]
+    if not ref_available(kw["variant"]):
+        pytest.skip("oracle/_ref not built and /root/reference absent")
+    sc = Scenario(**kw)
+    rec = []
+    ref = run_cpu(RefForest(sc.variant, sc.n, sc.A, sc.legal, per_root=(mode == 2)), sc, mode, 2024, record=rec)
+    want = search_summary(ref, sc, rec)
+    _, got = oracle_summary(name)
+    for k in want:
+        assert_same(got[k], want[k], "%s/%s" % (name, k))
+
+
+def test_zero_model_values_are_exactly_zero():
+    _, got = oracle_summary("mz_zero_model")
+    assert (got["values"] == 0.0).all()
+
+
+def test_distribution_length_equals_legal_count():  # reference test_mcts_ctree.py:265-270
+    sc, got = oracle_summary("mz_masks")
+    assert got["dist_len"].tolist() == [len(l) for l in LEGAL9]
+    for i, l in enumerate(LEGAL9):
+        assert (got["dist"][i, len(l):] == -1).all()
+
+
+def test_gumbel_constants_match_reference():
+    if not ref_available("gmz"):
+        pytest.skip("oracle/_ref not built and /root/reference absent")
+    import ctypes as C
+    from oracle.binding import oracle_lib, ref_lib
+    O, R = oracle_lib(), ref_lib("gmz")
+    for m, S in ((3, 30), (6, 50), (16, 50), (4, 200), (1, 10), (16, 8)):
+        a = np.zeros((m + 1, S), np.int32)
+        b = np.zeros((m + 1, S), np.int32)
+        O.orc_gumbel_table(m, S, a.ctypes.data_as(C.c_void_p))
+        R.ref_gumbel_table(m, S, b.ctypes.data_as(C.c_void_p))
+        assert_same(a, b, "considered-visit table m=%d S=%d" % (m, S))
+    a = np.zeros(700, np.float32)  # > 624 words: crosses an mt19937 state refill
+    b = np.zeros(700, np.float32)
+    O.orc_gumbel_noise(C.c_float(10.0), 700, a.ctypes.data_as(C.c_void_p))
+    R.ref_gumbel_noise(C.c_float(10.0), C.c_float(0.0), 700, b.ctypes.data_as(C.c_void_p))
+    assert_same(a, b, "gumbel noise table")
+
+
+def test_no_stray_fixtures():
+    have = {os.path.basename(p)[:-4] for p in glob.glob(os.path.join(HERE, "golden", "*.npz"))}
+    assert have >= set(CASES)
