@@ -1,0 +1,504 @@
+#!/usr/bin/env python
+"""Headline benchmark: MCTS simulations/sec of the batched tree search (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--roots 8192] [--sims 50] [--actions 18] [--latent 1024]
+    python bench.py --impl reference ...      # the reference ctree on the host cores (oracle/_ref), same JSON line
+
+A "step" is ONE whole search: Roots -> prepare (Dirichlet noise as an input tensor) -> S x [select + leaf
+gather -> synthetic model (fixed table lookup, no NN time) -> latent store -> expand + backup] -> root visit
+counts + values.  `value` = roots * sims / step time with every input resident in HBM (the S rounds replayed
+as one CUDA graph); `e2e` = the same search through the reference-shaped public API
+(lightzero_b200.MuZeroMCTSCtree.search) with HOST inputs in pinned memory and the results read back to the host
+inside the timed region.  Multi-GPU: roots shard by env batch, one forest per rank, no collective inside the
+search loop, one NCCL all-gather of visit counts / values at the end of each search.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+PB_C_BASE, PB_C_INIT, DISCOUNT, DELTA, NOISE_W, ALPHA = 19652, 1.25, 0.997, 0.01, 0.25, 0.3
+TIE_SEED = 2024
+L2_FLUSH_BYTES = 512 << 20
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--roots", type=int, default=8192, help="roots PER GPU (weak scaling)")
+    ap.add_argument("--sims", type=int, default=50)
+    ap.add_argument("--actions", type=int, default=18)
+    ap.add_argument("--latent", type=int, default=1024, help="latent floats per root gathered / stored per simulation")
+    ap.add_argument("--variant", default="mz", choices=["mz", "ez"])
+    ap.add_argument("--no-graph", action="store_true", help="value leg: launch per call instead of one CUDA graph")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-sample-roots", type=int, default=1024)
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return "synthetic %s search: %d roots/GPU x %d sims x A=%d, latent %d f32" % (
+        {"mz": "MuZero", "ez": "EfficientZero"}[a.variant], a.roots, a.sims, a.actions, a.latent)
+
+
+# --------------------------------------------------------------------------------------------- synthetic inputs
+def make_inputs(a, rank, device):
+    """seeded N(0,1) logits / values, N(0,0.1^2) rewards, Dirichlet(0.3) root noise, to_play=-1."""
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(1234 + rank)
+    N, S, A, L = a.roots, a.sims, a.actions, a.latent
+    rn = lambda *shape: torch.randn(*shape, generator=g, device=device, dtype=torch.float32)
+    gam = torch._standard_gamma(torch.full((N, A), ALPHA, device=device), generator=g)
+    inp = dict(
+        root_logits=rn(N, A), root_reward=rn(N) * 0.1, root_value=rn(N),
+        noise=(gam / gam.sum(1, keepdim=True)).float().contiguous(),
+        to_play=torch.full((N,), -1, dtype=torch.int32, device=device),
+        logits=rn(S, N, A), reward=rn(S, N) * 0.1, value=rn(S, N),
+        latent_roots=rn(N, max(L, 1)), model_latent=rn(N, max(L, 1)),
+    )
+    if a.variant == "ez":
+        inp["reward"] = rn(S, N)  # value prefixes
+    return inp
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------- the synthetic "network"
+class NetOut:
+    __slots__ = ("latent_state", "policy_logits", "value", "reward", "value_prefix", "reward_hidden_state")
+
+
+class TableModel:
+    """recurrent_inference as a fixed table lookup (NN time excluded and stated as such): call s of a
+    search returns row s of pre-generated logits / value / reward tables and a fixed next-latent tensor, all in HBM."""
+
+    def __init__(self, inp, variant):
+        self.inp, self.variant, self.s = inp, variant, 0
+        N = inp["model_latent"].shape[0]
+        if variant == "ez":
+            H = 512
+            self.hidden = (inp["model_latent"][:, :1].expand(N, H).contiguous().unsqueeze(0),
+                           inp["model_latent"][:, :1].expand(N, H).contiguous().unsqueeze(0))
+
+    def eval(self):
+        self.s = 0  # search() calls model.eval() once per search (mcts_ctree.py:242)
+
+    def recurrent_inference(self, latent, *rest):
+        i, s = self.inp, self.s
+        self.s += 1
+        o = NetOut()
+        o.latent_state, o.policy_logits, o.value = i["model_latent"], i["logits"][s], i["value"][s].unsqueeze(1)
+        o.reward = o.value_prefix = i["reward"][s].unsqueeze(1)
+        o.reward_hidden_state = getattr(self, "hidden", None)
+        return o
+
+
+def make_driver(a, device, graph):
+    import lightzero_b200 as lzb
+    cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree}[a.variant]
+    mcts = cls(dict(num_simulations=a.sims, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=DISCOUNT,
+                    value_delta_max=DELTA, device=str(device), cuda_graph=graph, tie_break_seed=TIE_SEED,
+                    model=dict(support_scale=300, categorical_distribution=False)))
+    mcts.inverse_scalar_transform_handle = lambda x: x  # the synthetic model emits scalars, not categorical supports
+    return mcts
+
+
+def one_search(a, mcts, model, inp, host=None, rank=0):
+    """The call sequence of lzero/policy/muzero.py:680-690: roots -> prepare -> search -> distributions / values.
+    host=None: every input already in HBM, outputs stay in HBM.  host=dict of pinned tensors: inputs come from the
+    host and the results are read back to the host (the e2e leg)."""
+    src = host if host is not None else inp
+    roots = mcts.roots(a.roots, None)
+    roots.root_offset = rank * a.roots  # global root index keys the tie-break stream
+    roots.prepare(NOISE_W, src["noise"], src["root_reward"], src["root_logits"], src["to_play"])
+    if a.variant == "ez":
+        mcts.search(roots, model, src["latent_roots"], (src["hidden_c"], src["hidden_h"]), src["to_play"])
+    else:
+        mcts.search(roots, model, src["latent_roots"], src["to_play"])
+    visits, _ = roots.get_distributions_tensor()
+    values = roots.get_values_tensor()
+    if host is not None:
+        host["visits_out"].copy_(visits, non_blocking=True)
+        host["values_out"].copy_(values, non_blocking=True)
+    return roots, visits, values
+
+
+# --------------------------------------------------------------------------------------------- per-kernel timing
+class KernelTimer:
+    """CUDA events around each launch of our three per-simulation kernels (on torch's current stream, which is the
+    stream the C ABI launches on), plus the mean search depth the roofline byte model needs."""
+
+    def __init__(self):
+        self.ev = {"select_gather": [], "store_latent": [], "expand_backup": []}
+        self.depth = []
+
+    def install(self):
+        import torch
+        from lightzero_b200.forest import Forest
+        self._orig = (Forest.traverse, Forest.backprop, Forest.store_hidden)
+        timer = self
+
+        def wrap(fn, name, post=None):
+            def inner(self_, *args, **kw):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                r = fn(self_, *args, **kw)
+                e1.record()
+                timer.ev[name].append((e0, e1))
+                if post:
+                    post(r)
+                return r
+            return inner
+
+        Forest.traverse = wrap(self._orig[0], "select_gather", lambda o: timer.depth.append(o["search_len"].float().mean()))
+        Forest.backprop = wrap(self._orig[1], "expand_backup")
+        Forest.store_hidden = wrap(self._orig[2], "store_latent")
+
+    def remove(self):
+        from lightzero_b200.forest import Forest
+        Forest.traverse, Forest.backprop, Forest.store_hidden = self._orig
+
+    def summary(self):
+        import torch
+        torch.cuda.synchronize()
+        out = {k: ([a.elapsed_time(b) for a, b in v]) for k, v in self.ev.items()}
+        depth = float(torch.stack(self.depth).mean()) if self.depth else 0.0
+        return out, depth
+
+
+def roofline(a, per_kernel_ms, depth, peak_gbs, peak_src):
+    """Algorithmic bytes per launch (per root per simulation, x N roots per launch)."""
+    N, A, Lb = a.roots, a.actions, 8 * max(a.latent, 1)
+    alg = {
+        "select_gather": N * (depth * (16 * A + 16) + 8 + 4 * (depth + 1) + Lb),
+        "expand_backup": N * (4 * A + 16 * A + 28 + (depth + 1) * 20 + 8),
+        "store_latent": N * Lb,
+    }
+    tot = {k: sum(v) for k, v in per_kernel_ms.items() if v}
+    top = max(tot, key=tot.get)
+    avg_ms = tot[top] / len(per_kernel_ms[top])
+    achieved = alg[top] / (avg_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(top)
+        except Exception:
+            traffic = None
+    share = {k: round(v / sum(tot.values()), 4) for k, v in tot.items()}
+    return {"bound": "hbm", "kernel": top, "achieved": round(achieved, 2), "peak": peak_gbs, "unit": "GB/s",
+            "frac": round(achieved / peak_gbs, 4), "traffic": traffic, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": int(alg[top]), "avg_launch_us": round(avg_ms * 1e3, 2),
+            "mean_search_depth": round(depth, 3), "kernel_time_share": share,
+            "avg_launch_us_all": {k: round(1e3 * tot[k] / len(per_kernel_ms[k]), 2) for k in tot}}
+
+
+# --------------------------------------------------------------------------------------------- CPU side (checker only)
+def cpu_inputs(a, n, seed):
+    """Host copy of the same synthetic distributions for n roots (numpy; the CPU arm never touches the GPU)."""
+    rng = np.random.default_rng(seed)
+    S, A, L = a.sims, a.actions, max(a.latent, 1)
+    f = lambda *s: rng.standard_normal(s).astype(np.float32)
+    return dict(root_logits=f(n, A), root_reward=f(n) * np.float32(0.1), root_value=f(n),
+                noises=[r for r in rng.dirichlet([ALPHA] * A, size=n).astype(np.float32)],
+                to_play=np.full(n, -1, np.int32), logits=f(S, n, A),
+                reward=(f(S, n) if a.variant == "ez" else f(S, n) * np.float32(0.1)), value=f(S, n),
+                latent_roots=f(n, L), model_latent=f(n, L))
+
+
+def cpu_search(a, d):
+    """One whole search of the reference ctree on ONE host thread, driven the way mcts_ctree.py:241-321 drives it:
+    batch_traverse -> Python gather of leaf latents + np.asarray (:283-286) -> (table-lookup model) ->
+    batch_backpropagate.  Uses the compiled unmodified reference (oracle/_ref) when present, else the C port.
+    Returns (seconds, kind, visit counts)."""
+    from oracle.binding import OracleForest, RefForest, ref_available
+    n = len(d["to_play"])
+    kind = "reference" if ref_available(a.variant) else "port"
+    t0 = time.perf_counter()
+    f = RefForest(a.variant, n, a.actions, None) if kind == "reference" else OracleForest(a.variant, n, a.actions, None)
+    f.set_delta(DELTA)
+    f.set_rng(0 if kind == "reference" else 2, TIE_SEED)  # reference: its own libc rand() stream
+    f.prepare(NOISE_W, d["noises"], d["root_reward"], d["root_logits"], d["to_play"], values=d["root_value"])
+    pool = [d["latent_roots"]]
+    for s in range(a.sims):
+        o = f.traverse(PB_C_BASE, PB_C_INIT, DISCOUNT, d["to_play"], num_simulations=a.sims)
+        leaf = np.asarray([pool[ix][iy] for ix, iy in zip(o["ix"].tolist(), o["iy"].tolist())])  # noqa: F841
+        pool.append(d["model_latent"])
+        is_reset = (o["search_len"] % 5 == 0).astype(np.int32) if a.variant == "ez" else None
+        f.backprop(s + 1, DISCOUNT, d["reward"][s], d["value"][s], d["logits"][s], is_reset, o["vtp"])
+    dist, _ = f.distributions()
+    f.values()
+    return time.perf_counter() - t0, kind, dist
+
+
+def _cpu_worker(a, n, seed, conn):
+    d = cpu_inputs(a, n, seed)
+    conn.send("ready")
+    while True:
+        msg = conn.recv()
+        if msg == "stop":
+            return
+        dt, kind, _ = cpu_search(a, d)
+        conn.send((dt, kind))
+
+
+def run_reference_arm(a):
+    """--impl reference: the reference ctree on every host core (roots are independent, so the batch is sharded over
+    P processes, one single-threaded reference tree each); same metric / config / unit as the B200 arm."""
+    import multiprocessing as mp
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    P = max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1))
+    # bounded sample: at most the full per-GPU batch, at least 64 roots per process
+    total = a.roots
+    per = max(1, total // P)
+    P = min(P, total // per)
+    ctx = mp.get_context("fork")
+    procs = []
+    for r in range(P):
+        pc, cc = ctx.Pipe()
+        p = ctx.Process(target=_cpu_worker, args=(a, per, 1234 + r, cc), daemon=True)
+        p.start()
+        procs.append((p, pc))
+    for _, pc in procs:
+        pc.recv()
+    kind = "port"
+
+    def step():
+        nonlocal kind
+        t0 = time.perf_counter()
+        for _, pc in procs:
+            pc.send("go")
+        for _, pc in procs:
+            _, kind = pc.recv()
+        return time.perf_counter() - t0
+
+    for _ in range(min(a.warmup, 1)):
+        step()
+    times = [step() for _ in range(a.steps)]
+    for p, pc in procs:
+        pc.send("stop")
+        p.join(timeout=5)
+    sims = per * P * a.sims
+    ms = 1e3 * sum(times) / len(times)
+    v = sims / (ms * 1e-3)
+    cpu = ""
+    try:
+        cpu = [l.split(":", 1)[1].strip() for l in open("/proc/cpuinfo") if l.startswith("model name")][0]
+    except Exception:
+        pass
+    sample = "%d roots (%d processes x %d) x %d sims per step, tree + Python leaf gather, no NN, libc rand() ties" % (per * P, P, per, a.sims)
+    print(json.dumps({
+        "impl": "reference", "metric": "mcts_simulations_per_sec", "value": round(v, 1), "unit": "simulations/s",
+        "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "host_cpu": cpu},
+        "cpu_baseline": {"value": round(v, 1), "unit": "simulations/s", "cores": P, "kind": kind, "sample": sample},
+        "e2e": {"value": round(v, 1), "unit": "simulations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# --------------------------------------------------------------------------------------------- B200 arm
+def run_b200_arm(a):
+    import torch
+    import torch.distributed as dist
+    from lightzero_b200 import sharding
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    N, S, A = a.roots, a.sims, a.actions
+    inp = make_inputs(a, rank, device)
+    if a.variant == "ez":
+        inp["hidden_c"] = torch.zeros(1, N, 512, device=device)
+        inp["hidden_h"] = torch.zeros(1, N, 512, device=device)
+    model = TableModel(inp, a.variant)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=device)
+    counts = [N] * world
+
+    def exchange(visits, values):  # the one collective of a search; identity at world == 1
+        return sharding.gather_search_outputs(visits, values, counts) if world > 1 else (visits, values)
+
+    # ---- value leg: inputs resident in HBM, the whole search replayed as one CUDA graph
+    mcts = make_driver(a, device, graph=not a.no_graph)
+
+    def dev_step():
+        _, visits, values = one_search(a, mcts, model, inp, rank=rank)
+        return exchange(visits, values)
+
+    for _ in range(max(a.warmup, 3)):
+        dev_step()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    t_wall = time.perf_counter()
+    for e0, e1 in ev:
+        flush.fill_(1)  # L2 flush between timed steps (512 MB write > 126 MB L2), outside the event pair
+        e0.record()
+        visits, values = dev_step()
+        e1.record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall
+    dev_ms = sum(x.elapsed_time(y) for x, y in ev)
+    # sanity: a search spends exactly S visits below each root
+    assert bool((visits[:N].sum(1) == S).all()), "visit counts do not sum to the number of simulations"
+
+    # ---- e2e leg: reference-shaped API, HOST inputs (pinned), outputs read back to the host, wall clock
+    e2e_ms = None
+    h2d = d2h = 0
+    if not a.no_e2e:
+        pin = lambda t: t.detach().cpu().pin_memory()
+        host = {k: pin(inp[k]) for k in ("root_logits", "noise", "root_reward", "to_play", "latent_roots")}
+        if a.variant == "ez":
+            host["hidden_c"], host["hidden_h"] = pin(inp["hidden_c"]), pin(inp["hidden_h"])
+        host["visits_out"] = torch.empty((N, A), dtype=torch.int32).pin_memory()
+        host["values_out"] = torch.empty(N, dtype=torch.float32).pin_memory()
+        h2d = sum(host[k].numel() * host[k].element_size() for k in host if not k.endswith("_out")) + 4 * N  # to_play twice
+        d2h = host["visits_out"].numel() * 4 + host["values_out"].numel() * 4
+
+        def e2e_step():
+            _, visits, values = one_search(a, mcts, model, inp, host=host, rank=rank)
+            exchange(visits, values)
+            torch.cuda.synchronize()
+
+        for _ in range(3):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(a.steps):
+            e2e_step()
+        barrier()
+        e2e_ms = 1e3 * (time.perf_counter() - t0)
+        assert int(host["visits_out"].sum()) == N * S
+    clk = clocks.stop() if rank == 0 else None
+
+    # ---- per-kernel pass (eager launches bracketed by events) for the roofline of the dominant kernel
+    timer = KernelTimer()
+    eager = make_driver(a, device, graph=False)
+    one_search(a, eager, model, inp, rank=rank)  # warm the eager path
+    timer.install()
+    for _ in range(2):
+        flush.fill_(1)
+        one_search(a, eager, model, inp, rank=rank)
+    timer.remove()
+    per_kernel, depth = timer.summary()
+
+    # ---- reduce over ranks (max time), print on rank 0
+    t = torch.tensor([dev_ms, e2e_ms or 0.0], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_tot = float(t[0]), float(t[1])
+    if rank == 0:
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+        else:
+            peak, src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+        ms_step = dev_ms / a.steps
+        total_sims = N * world * S
+        line = {
+            "metric": "mcts_simulations_per_sec", "value": round(total_sims / (ms_step * 1e-3), 1), "unit": "simulations/s",
+            "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": round(ms_step, 4),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(a), "roots_total": N * world, "sims": S, "actions": A,
+                       "latent_f32": a.latent, "model": "table lookup in HBM (no NN time)", "scalar_transform": "identity",
+                       "cuda_graph": not a.no_graph, "l2": "512 MB flush between timed steps; working set > L2",
+                       "parallelism": "roots sharded x%d, all-gather of root outputs per search" % world,
+                       "wall_ms_per_step_incl_flush": round(1e3 * t_wall / a.steps, 3)},
+            "gpu_launches": a.steps * (3 + 3 * S + 1),
+            "clocks": clk,
+            "roofline": roofline(a, per_kernel, depth, peak, src),
+        }
+        if e2e_ms is not None:
+            line["e2e"] = {"value": round(total_sims / (e2e_tot / a.steps * 1e-3), 1), "unit": "simulations/s",
+                           "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                           "ms_per_step": round(e2e_tot / a.steps, 4), "clock": "host wall clock incl. Python, max over ranks"}
+        if world == 1 and not a.no_cpu_baseline:
+            n = min(a.cpu_sample_roots, N)
+            d = cpu_inputs(a, n, 1234)
+            cpu_search(a, d)  # warm-up
+            best, kind = None, "port"
+            for _ in range(3):
+                dt, kind, _ = cpu_search(a, d)
+                best = dt if best is None else min(best, dt)
+            line["cpu_baseline"] = {"value": round(n * S / best, 1), "unit": "simulations/s", "cores": 1, "kind": kind,
+                                    "sample": "%d of %d roots x %d sims, best of 3, tree + Python leaf gather, no NN" % (n, N, S)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_b200_arm(args)

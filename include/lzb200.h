@@ -82,6 +82,11 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
                       const int32_t *legal_actions_dev, void *stream);
 void lzb_forest_destroy(lzb_forest_t *f);
 
+/* Roots.clear() followed by a fresh Roots(...) over the SAME workspace (cnode.cpp:360-366 + :301-317): a new
+ * batch of roots with new legal-action lists, MinMax bounds cleared; nothing is reallocated, so one
+ * workspace serves every search of a collector / reanalyze loop (and a captured CUDA graph can replay it). */
+int lzb_forest_reset(lzb_forest_t *f, const int32_t *legal_count_dev, const int32_t *legal_actions_dev, void *stream);
+
 /* MinMaxStatsList.set_delta (mz_tree.pyx:11-12); also clears min/max as a fresh list would be. */
 int lzb_set_delta(lzb_forest_t *f, float value_delta_max, void *stream);
 
@@ -129,6 +134,10 @@ int lzb_store_hidden(const float *src_dev, float *dst_dev, const int32_t *is_res
  * Gumbel extras (gmz cnode.cpp:506-541), each [N,A] or NULL: improved policies and completed child values. */
 int lzb_root_outputs(lzb_forest_t *f, int32_t *visits_dev, int32_t *legal_count_dev, float *values_dev,
                      float discount, float *gumbel_policies_dev, float *gumbel_children_values_dev, void *stream);
+
+/* get_trajectories (cnode.cpp:237-257,369-385): the greedy best_action chain from each root; row i of
+ * actions [N, stride] holds len[i] action ids (entries beyond stride are dropped, len is the true length). */
+int lzb_trajectories(lzb_forest_t *f, int32_t *actions_dev, int stride, int32_t *len_dev, void *stream);
 
 /* Introspection for parity tests: raw pool arrays of tree i copied into caller DEVICE buffers laid out
  * as oracle/ref_harness.cpp:ref_dump_tree ([E,A] visit/value_sum/prior/reward/child_e, [E,4] hdr, [E] raw). */

@@ -1,0 +1,7 @@
+"""B200-native batched MCTS for LightZero: the reference's tree API over hand-written sm_100a CUDA.
+
+    from lightzero_b200 import MuZeroMCTSCtree as MCTSCtree      # instead of `from lzero.mcts import ...`
+
+Importing the package does not need a GPU; creating roots or searching does (there is no CPU fallback)."""
+from .tree_search import (EfficientZeroMCTSCtree, GumbelMuZeroMCTSCtree, MuZeroMCTSCtree,  # noqa: F401
+                          SampledEfficientZeroMCTSCtree)

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "liblzb200.so")
-SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_pool.cuh", "lzb_math.cuh", "lzb_step.cuh"]
+SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",  # B200 only
@@ -69,12 +69,14 @@ _PROTOS = {
     "lzb_forest_create": (C.c_int, [C.POINTER(_P), _P, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                     _P, _P, _P]),
     "lzb_forest_destroy": (None, [_P]),
+    "lzb_forest_reset": (C.c_int, [_P, _P, _P, _P]),
     "lzb_set_delta": (C.c_int, [_P, C.c_float, _P]),
     "lzb_prepare": (C.c_int, [_P, _P, _P, C.c_float, _P, _P, _P, _P, _P]),
     "lzb_traverse": (C.c_int, [_P, C.POINTER(SearchCfg), _P, _P, _P, _P, _P, _P, _P, C.POINTER(Gather), C.c_int, _P]),
     "lzb_backprop": (C.c_int, [_P, C.c_int, C.c_float, _P, _P, _P, _P, _P, C.c_int, _P, _P, _P]),
     "lzb_store_hidden": (C.c_int, [_P, _P, _P, C.c_int, C.c_int64, _P]),
     "lzb_root_outputs": (C.c_int, [_P, _P, _P, _P, C.c_float, _P, _P, _P]),
+    "lzb_trajectories": (C.c_int, [_P, _P, C.c_int, _P, _P]),
     "lzb_dump_tree": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P, _P, _P, _P]),
     "lzb_dump_paths": (C.c_int, [_P, _P, C.c_int, _P]),
     "lzb_minmax": (C.c_int, [_P, _P, _P, _P]),

@@ -110,6 +110,7 @@ __global__ void k_init(Pool p, const int *legal_count, const int *legal_actions)
     p.root[i] = make_int4(0, 0, 0, 0);
     p.minmax[i] = make_float2(kFloatMax, kFloatMin); // CMinMaxStats ctor (cminimax.cpp:7-11)
     p.res[i] = make_int4(0, 0, 0, 0);
+    p.best[(size_t)i * p.E] = -1; // CNode::best_action = -1 (cnode.cpp:55-66)
 }
 
 __global__ void k_reset_minmax(Pool p)
@@ -133,12 +134,23 @@ __global__ void k_max_to_play(const int *to_play, int n, int *out)
     }
 }
 
+// dst[i,:] = is_reset[i] ? 0 : src[i,:]; 16-byte accesses when VEC (row bytes and both bases 16-B aligned)
+template <bool VEC>
 __global__ void k_store_hidden(const float *src, float *dst, const int *is_reset, int n, long long row)
 {
-    const long long total = (long long)n * row;
-    for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-        const int i = (int)(t / row);
-        dst[t] = (is_reset && is_reset[i]) ? 0.0f : src[t];
+    if (VEC) {
+        const long long row4 = row >> 2, total = (long long)n * row4;
+        const int4 *s4 = reinterpret_cast<const int4 *>(src);
+        int4 *d4 = reinterpret_cast<int4 *>(dst);
+        for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+            int4 v = __ldg(s4 + t);
+            if (is_reset && is_reset[t / row4]) v = make_int4(0, 0, 0, 0);
+            d4[t] = v;
+        }
+    } else {
+        const long long total = (long long)n * row;
+        for (long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x)
+            dst[t] = (is_reset && is_reset[t / row]) ? 0.0f : src[t];
     }
 }
 
@@ -224,6 +236,22 @@ __global__ void k_dump_paths(Pool p, int *out, int stride)
         const int e = slot / p.A, pos = slot % p.A;
         out[(size_t)i * stride + d] = (e == 0 && p.variant != LZB_SEZ) ? p.legal[(size_t)i * p.A + pos] : pos;
     }
+}
+
+// CRoots::get_trajectories (cnode.cpp:237-257,369-385): follow best_action from the root while it is >= 0
+__global__ void k_trajectories(Pool p, int *out, int stride, int *len)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.N) return;
+    int e = 0, d = 0;
+    while (e >= 0) {
+        const int pos = p.best[(size_t)i * p.E + e];
+        if (pos < 0) break;
+        if (d < stride) out[(size_t)i * stride + d] = (e == 0 && p.variant != LZB_SEZ) ? p.legal[(size_t)i * p.A + pos] : pos;
+        d += 1;
+        e = child_expansion(p.child[((size_t)i * p.E + e) * p.A + pos].x);
+    }
+    len[i] = d;
 }
 
 __global__ void k_minmax(Pool p, float *mn, float *mx)
@@ -334,6 +362,17 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
 }
 
 void lzb_forest_destroy(lzb_forest_t *f) { delete f; }
+
+int lzb_forest_reset(lzb_forest_t *f, const int32_t *legal_count_dev, const int32_t *legal_actions_dev, void *stream)
+{
+    if (!f) return fail(LZB_E_ARG, "forest is NULL");
+    if ((legal_count_dev == nullptr) != (legal_actions_dev == nullptr)) return fail(LZB_E_ARG, "legal_count / legal_actions must both be given or both NULL");
+    k_init<<<(f->pool.N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(f->pool, legal_count_dev, legal_actions_dev);
+    LZB_CUDA(cudaGetLastError());
+    f->sim = 0;
+    f->expanded = -1;
+    return LZB_OK;
+}
 
 int lzb_set_delta(lzb_forest_t *f, float value_delta_max, void *stream)
 {
@@ -462,9 +501,11 @@ int lzb_store_hidden(const float *src_dev, float *dst_dev, const int32_t *is_res
                      int64_t row_floats, void *stream)
 {
     if (!src_dev || !dst_dev || num_roots <= 0 || row_floats <= 0) return fail(LZB_E_ARG, "store_hidden: bad argument");
-    const long long total = (long long)num_roots * row_floats;
-    const int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 16);
-    k_store_hidden<<<blocks, 256, 0, (cudaStream_t)stream>>>(src_dev, dst_dev, is_reset_dev, num_roots, row_floats);
+    const bool vec = (row_floats % 4 == 0) && ((((uintptr_t)src_dev) | ((uintptr_t)dst_dev)) & 15) == 0;
+    const long long total = (long long)num_roots * (vec ? row_floats / 4 : row_floats);
+    const int blocks = (int)std::min<long long>((total + 255) / 256, 148 * 8);
+    if (vec) k_store_hidden<true><<<blocks, 256, 0, (cudaStream_t)stream>>>(src_dev, dst_dev, is_reset_dev, num_roots, row_floats);
+    else k_store_hidden<false><<<blocks, 256, 0, (cudaStream_t)stream>>>(src_dev, dst_dev, is_reset_dev, num_roots, row_floats);
     LZB_CUDA(cudaGetLastError());
     return LZB_OK;
 }
@@ -499,6 +540,15 @@ int lzb_dump_paths(lzb_forest_t *f, int32_t *path_actions_dev, int path_stride, 
 {
     if (!f || !path_actions_dev || path_stride <= 0) return fail(LZB_E_ARG, "dump_paths: bad argument");
     k_dump_paths<<<(f->pool.N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(f->pool, path_actions_dev, path_stride);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_trajectories(lzb_forest_t *f, int32_t *actions_dev, int stride, int32_t *len_dev, void *stream)
+{
+    if (!f || !actions_dev || !len_dev || stride <= 0) return fail(LZB_E_ARG, "trajectories: bad argument");
+    if (f->expanded < 0) return fail(LZB_E_STATE, "trajectories before prepare");
+    k_trajectories<<<(f->pool.N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(f->pool, actions_dev, stride, len_dev);
     LZB_CUDA(cudaGetLastError());
     return LZB_OK;
 }

@@ -109,8 +109,10 @@ __global__ void k_expand_backup(Pool p, BackupArgs a)
     } else {
         expand_children(p, i, e_new, p.A, nullptr, a.logits + (size_t)i * p.A, nullptr, 0.0f, s_tmp, lane);
     }
-    if (lane == 0)
+    if (lane == 0) {
         p.hdr[(size_t)i * p.E + e_new] = make_int4(p.A, to_play, leaf_reset, __float_as_int(value));
+        p.best[(size_t)i * p.E + e_new] = -1;
+    }
 
     // ---- backup: node q = depth (leaf) ... 1 are path records q-1, node 0 is the root
     const int4 *pa = p.path_a + (size_t)i * (p.S + 1);

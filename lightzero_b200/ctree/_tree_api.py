@@ -1,0 +1,276 @@
+"""Shared implementation of the reference's tree modules over the CUDA forest.
+
+Mirrors the surface of lzero/mcts/ctree/ctree_*/{mz,ez,gmz,ezs}_tree.pyx (Roots, MinMaxStatsList,
+ResultsWrapper, batch_traverse, batch_backpropagate / batch_back_propagate) so that lzero/policy/* and
+lzero/mcts/buffer/* call it unchanged.  Every argument the reference takes as a Python list may also be a
+numpy array or a torch tensor (host or device); lists are converted with ONE host->device copy per argument.
+List-returning getters keep the reference's return types; ``*_tensor`` twins return device tensors without
+a host sync and are what the rewritten search() loops use.
+
+A forest needs its capacity (number of simulations) when it is created, which the reference API only
+reveals at search() time; Roots therefore keeps the prepared root inputs and materialises the forest on
+first use (search() passes cfg.num_simulations; a bare batch_traverse() uses DEFAULT_MAX_SIMULATIONS).
+"""
+import os
+
+import numpy as np
+import torch
+
+from ..forest import RNG_BATCH, RNG_PER_ROOT, Forest, _dev
+
+DEFAULT_MAX_SIMULATIONS = int(os.environ.get("LZB_DEFAULT_MAX_SIMULATIONS", "256"))
+# Tie-break stream (include/lzb200.h): the reference draws rand() reseeded from the wall clock on every
+# traverse (cnode.cpp:592,770), i.e. a fresh stream per call; here the seed is explicit and reproducible.
+_tie_seed = [int(os.environ.get("LZB_TIE_BREAK_SEED", "0"))]
+_rng_mode = [RNG_PER_ROOT]
+
+
+def set_tie_break(seed, mode="per_root"):
+    """Seed (and keying) of the tie-break stream used by every subsequent search of this process."""
+    _tie_seed[0] = int(seed)
+    _rng_mode[0] = RNG_BATCH if mode in ("batch", RNG_BATCH) else RNG_PER_ROOT
+
+
+def _device(device=None):
+    if not torch.cuda.is_available():
+        raise RuntimeError("lightzero_b200 needs a CUDA device: the tree has no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+
+
+def _rows_to_padded(rows, width, dtype):
+    """list of variable-length rows -> [len(rows), width] zero-padded host array (one pass, no per-element python)."""
+    if isinstance(rows, (np.ndarray, torch.Tensor)):
+        return rows
+    n = len(rows)
+    lens = np.fromiter((len(r) for r in rows), dtype=np.int64, count=n)
+    if n and (lens == width).all():
+        return np.asarray(rows, dtype=dtype)
+    out = np.zeros((n, width), dtype=dtype)
+    flat = np.fromiter((x for r in rows for x in r), dtype=dtype, count=int(lens.sum()))
+    mask = np.arange(width)[None, :] < lens[:, None]
+    out[mask] = flat
+    return out
+
+
+class MinMaxStatsList:
+    """common_lib/cminimax.h:27-37 through mz_tree.pyx:5-15.  The per-root {min, max} pairs live in the forest's
+    workspace; this object carries value_delta_max and is bound to a forest by the first batch_traverse."""
+
+    def __init__(self, num):
+        self.num = int(num)
+        self.value_delta_max = 0.0
+        self._bound = None
+
+    def set_delta(self, value_delta_max):
+        self.value_delta_max = float(value_delta_max)
+        if self._bound is not None:
+            self._bound.set_delta(self.value_delta_max)
+
+    def _bind(self, forest):
+        if self._bound is not forest:
+            forest.set_delta(self.value_delta_max)  # a fresh list: bounds cleared (cminimax.cpp:7-11)
+            self._bound = forest
+
+
+class ResultsWrapper:
+    """tree::CSearchResults (cnode.h:67-79) through mz_tree.pyx:17-24: the per-simulation hand-over from
+    batch_traverse to batch_backpropagate.  Holds device tensors; the search path itself stays in the workspace."""
+
+    def __init__(self, num):
+        self.num = int(num)
+        self.out = None
+
+    def get_search_len(self):
+        return [] if self.out is None else self.out["search_len"].tolist()
+
+    def get_search_len_tensor(self):
+        return None if self.out is None else self.out["search_len"]
+
+
+class RootsBase:
+    """CRoots (cnode.cpp:292-417) through mz_tree.pyx:26-58.  One object = the N roots of a batch; it owns the
+    CUDA forest (workspace in HBM) once materialised."""
+
+    variant = "mz"
+
+    def __init__(self, root_num, legal_actions_list, device=None):
+        self.root_num = int(root_num)
+        if legal_actions_list is not None and not isinstance(legal_actions_list, tuple) and len(legal_actions_list) != self.root_num:
+            raise ValueError("legal_actions_list must have root_num rows")
+        self._legal = legal_actions_list
+        self._device = _device(device)
+        self._prep = None
+        self.forest = None
+        self.root_offset = 0  # global index of root 0 when the env batch is sharded over GPUs
+        self._cleared = False
+
+    # ------------------------------------------------------------------ reference surface
+    @property
+    def num(self):
+        return self.root_num
+
+    def _store_prepare(self, noise_weight, noises, value_prefix_pool, policy_logits_pool, to_play_batch, values=None):
+        d = self._device
+        logits = _dev(policy_logits_pool, torch.float32, d)
+        if logits.dim() != 2 or logits.shape[0] != self.root_num:
+            raise ValueError("policy_logits_pool must be [root_num, action_space_size]")
+        A = logits.shape[1]
+        noise = None
+        if noises is not None:
+            noise = _dev(_rows_to_padded(noises, A, np.float32), torch.float32, d)
+            if tuple(noise.shape) != (self.root_num, A):
+                raise ValueError("noises must have one row per root with at most action_space_size entries")
+        to_play = _dev(to_play_batch, torch.int32, d)
+        self._prep = dict(logits=logits, noise=noise, noise_weight=float(noise_weight),
+                          reward=_dev(value_prefix_pool, torch.float32, d).reshape(-1), to_play=to_play.reshape(-1),
+                          value=None if values is None else _dev(values, torch.float32, d).reshape(-1))
+        self.action_space_size = A
+        self._cleared = False
+        if self.forest is not None:  # prepare() on a live object re-roots the same workspace
+            self._apply_prepare()
+
+    def prepare(self, root_noise_weight, noises, value_prefix_pool, policy_logits_pool, to_play_batch):
+        self._store_prepare(root_noise_weight, noises, value_prefix_pool, policy_logits_pool, to_play_batch)
+
+    def prepare_no_noise(self, value_prefix_pool, policy_logits_pool, to_play_batch):
+        self._store_prepare(0.0, None, value_prefix_pool, policy_logits_pool, to_play_batch)
+
+    def get_distributions(self):
+        """[N][n_legal_i] child visit counts in legal-action order (cnode.cpp:259-277,387-403); [] per root if unexpanded."""
+        if self._cleared:
+            return []
+        if self._prep is None:
+            return [[] for _ in range(self.root_num)]
+        out = self._outputs()
+        visits, cnt = out["visits"].cpu().numpy(), out["legal_count"].cpu().numpy()
+        if (cnt == visits.shape[1]).all():
+            return visits.tolist()
+        return [row[:c] for row, c in zip(visits.tolist(), cnt.tolist())]
+
+    def get_values(self):
+        if self._cleared:
+            return []
+        if self._prep is None:
+            return [0.0] * self.root_num
+        return self._outputs()["values"].tolist()
+
+    def get_trajectories(self):
+        if self._cleared:
+            return []
+        if self._prep is None:
+            return [[] for _ in range(self.root_num)]
+        acts, ln = self._materialize().trajectories()
+        acts, ln = acts.cpu().numpy(), ln.cpu().numpy()
+        return [acts[i, :ln[i]].tolist() for i in range(self.root_num)]
+
+    def clear(self):
+        self._cleared = True
+        self._prep = None
+        self.forest = None
+
+    # ------------------------------------------------------------------ device-tensor twins (no host sync)
+    def get_distributions_tensor(self):
+        """(visits [N, A] int32 with row i's first legal_count[i] entries valid, legal_count [N] int32)."""
+        out = self._outputs()
+        return out["visits"], out["legal_count"]
+
+    def get_values_tensor(self):
+        return self._outputs()["values"]
+
+    # ------------------------------------------------------------------ internals
+    def _forest_dims(self):
+        return self.action_space_size, 0
+
+    def _materialize(self, max_sims=None):
+        if self._prep is None:
+            raise RuntimeError("Roots.prepare / prepare_no_noise must be called before the roots are searched")
+        if max_sims is not None:
+            need = int(max_sims)
+        else:
+            need = self.forest.S if self.forest is not None else DEFAULT_MAX_SIMULATIONS
+        if self.forest is None or self.forest.S < need:
+            if self.forest is not None and self.forest.sims_done:
+                raise RuntimeError("search needs %d simulations but the forest was created for %d" % (need, self.forest.S))
+            A, D = self._forest_dims()
+            self.forest = Forest(self.variant, self.root_num, A, need, legal_actions=self._legal, action_dim=D,
+                                 root_offset=self.root_offset, device=self._device)
+            self.forest.sims_done = 0
+            self._apply_prepare(reset=False)
+        return self.forest
+
+    def _apply_prepare(self, reset=True):
+        p = self._prep
+        if reset:
+            self.forest.reset()
+        self.forest.prepare(p["logits"], p["noise"], p["noise_weight"], p["reward"], p["to_play"], value=p["value"],
+                            sampled_actions=p.get("sampled_actions"))
+        self.forest.sims_done = 0
+
+    def _outputs(self):
+        cached = getattr(self, "_cached_outputs", None)  # set by a CUDA-graph search (tree_search/mcts_ctree.py)
+        if cached is not None:
+            return cached
+        f = self._materialize()
+        return f.root_outputs()
+
+
+def _search_cfg(forest, pb_c_base, pb_c_init, discount, to_play, num_simulations=0, max_considered=0, players=None):
+    """players is batch-global (cnode.cpp:776-781): derived on the host when to_play came as a host object,
+    else by one device reduction inside lzb_traverse (players = 0)."""
+    if players is not None:
+        pass
+    elif forest.variant == "gmz":
+        players = 1
+    elif isinstance(to_play, torch.Tensor) and to_play.is_cuda:
+        players = 0
+    elif not isinstance(to_play, torch.Tensor):
+        tp = np.asarray(to_play)
+        players = 1 if (tp.size and int(tp.max()) == -1) else 2
+    elif not to_play.is_cuda:
+        players = 1 if (to_play.numel() and int(to_play.max()) == -1) else 2
+    return forest.make_cfg(pb_c_base, pb_c_init, discount, players=players, num_simulations=num_simulations,
+                           max_num_considered_actions=max_considered, rng_mode=_rng_mode[0], rng_seed=_tie_seed[0])
+
+
+def traverse_tensors(roots, cfg, to_play, results, min_max_stats_lst=None, gathers=(), out=None, max_sims=None):
+    """Device-tensor batch_traverse: returns the dict of [N] device tensors (ix, iy, last_action, search_len, vtp)."""
+    f = roots._materialize(max_sims)
+    if min_max_stats_lst is not None:
+        min_max_stats_lst._bind(f)
+    o = f.traverse(cfg, to_play, out=out, gathers=gathers)
+    results.out = o
+    results.forest = f
+    results.roots = roots
+    return o
+
+
+def backprop_tensors(results, latent_index, discount, reward, value, logits, to_play, **kw):
+    f = results.forest
+    f.backprop(latent_index, discount, reward, value, logits, to_play, **kw)
+    f.sims_done += 1
+
+
+def batch_traverse(roots, pb_c_base, pb_c_init, discount_factor, min_max_stats_lst, results, virtual_to_play_batch):
+    """mz_tree.pyx:95-100 / ez_tree.pyx:108-114 -> cbatch_traverse.  Returns four Python lists like the reference
+    (this list flavour costs one device->host sync per call; search() uses traverse_tensors instead)."""
+    f = roots._materialize()
+    cfg = _search_cfg(f, pb_c_base, pb_c_init, discount_factor, virtual_to_play_batch)
+    o = traverse_tensors(roots, cfg, virtual_to_play_batch, results, min_max_stats_lst)
+    return o["ix"].tolist(), o["iy"].tolist(), o["last_action"].tolist(), o["vtp"].tolist()
+
+
+def batch_backpropagate(current_latent_state_index, discount_factor, value_prefixs, values, policies, min_max_stats_lst,
+                        results, to_play_batch):
+    """mz_tree.pyx:74-82 -> cbatch_backpropagate (cnode.cpp:480-500)."""
+    if results.out is None:
+        raise RuntimeError("batch_backpropagate needs the ResultsWrapper of the preceding batch_traverse")
+    backprop_tensors(results, current_latent_state_index, discount_factor, value_prefixs, values, policies, to_play_batch)
+
+
+def batch_backpropagate_ez(current_latent_state_index, discount_factor, value_prefixs, values, policies,
+                           min_max_stats_lst, results, is_reset_list, to_play_batch):
+    """ez_tree.pyx:83-93 -> cbatch_backpropagate with is_reset_list (ctree_efficientzero/lib/cnode.cpp:577-601)."""
+    if results.out is None:
+        raise RuntimeError("batch_backpropagate needs the ResultsWrapper of the preceding batch_traverse")
+    backprop_tensors(results, current_latent_state_index, discount_factor, value_prefixs, values, policies, to_play_batch,
+                     is_reset=is_reset_list)

@@ -1,0 +1,8 @@
+"""Drop-in for lzero/mcts/ctree/ctree_muzero/mz_tree.pyx over the CUDA forest (variant LZB_MZ)."""
+from .._tree_api import (MinMaxStatsList, ResultsWrapper, RootsBase, batch_backpropagate, batch_traverse,  # noqa: F401
+                         set_tie_break)
+
+
+class Roots(RootsBase):
+    """mz_tree.pyx:26-58: Roots(root_num, legal_actions_list)."""
+    variant = "mz"

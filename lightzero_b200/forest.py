@@ -32,9 +32,33 @@ def _dev(x, dtype, device):
     return torch.as_tensor(x, dtype=dtype).to(device, non_blocking=True).contiguous()
 
 
+def legal_tensors(legal_actions, N, A, variant, device):
+    """Per-root legal-action lists (or a (count, ids) pair) -> (count [N], ids [N, A]) device tensors;
+    (None, None) = every action legal."""
+    cnt = idx = None
+    if legal_actions is not None and variant != "sez":
+        if isinstance(legal_actions, tuple):
+            cnt, idx = legal_actions
+            cnt, idx = _dev(cnt, torch.int32, device), _dev(idx, torch.int32, device)
+        else:
+            lens = [len(l) for l in legal_actions]
+            if max(lens, default=0) > A:
+                raise ValueError("a root has more legal actions than the action space")
+            cnt_h = torch.tensor(lens, dtype=torch.int32)
+            idx_h = torch.zeros((N, A), dtype=torch.int32)
+            if lens and min(lens) == max(lens) and lens[0] > 0:
+                idx_h[:, :lens[0]] = torch.as_tensor(legal_actions, dtype=torch.int32)
+            else:
+                for i, l in enumerate(legal_actions):
+                    if len(l):
+                        idx_h[i, :len(l)] = torch.as_tensor(l, dtype=torch.int32)
+            cnt, idx = cnt_h.to(device), idx_h.to(device)
+    return cnt, idx
+
+
 class Forest:
     def __init__(self, variant, num_roots, action_space, max_sims, legal_actions=None, action_dim=0, root_offset=0,
-                 device="cuda"):
+                 device="cuda", workspace=None):
         if not torch.cuda.is_available():
             raise RuntimeError("lightzero_b200 needs a CUDA device (there is no CPU fallback)")
         self.L = _lib.lib()
@@ -46,21 +70,10 @@ class Forest:
         self.root_offset = int(root_offset)
         nbytes = C.c_size_t(0)
         check(self.L.lzb_forest_bytes(VARIANT_ID[variant], self.N, self.A, self.S, self.D, C.byref(nbytes)))
-        self.workspace = torch.empty(nbytes.value, dtype=torch.uint8, device=self.device)
-        cnt = idx = None
-        if legal_actions is not None and variant != "sez":
-            if isinstance(legal_actions, tuple):
-                cnt, idx = legal_actions
-                cnt, idx = _dev(cnt, torch.int32, self.device), _dev(idx, torch.int32, self.device)
-            else:
-                cnt_h = torch.tensor([len(l) for l in legal_actions], dtype=torch.int32)
-                idx_h = torch.zeros((self.N, self.A), dtype=torch.int32)
-                for i, l in enumerate(legal_actions):
-                    if len(l) > self.A:
-                        raise ValueError("root %d has more legal actions than the action space" % i)
-                    if len(l):
-                        idx_h[i, :len(l)] = torch.as_tensor(l, dtype=torch.int32)
-                cnt, idx = cnt_h.to(self.device), idx_h.to(self.device)
+        if workspace is not None and (workspace.numel() < nbytes.value or workspace.device != self.device):
+            raise ValueError("workspace must be a uint8 tensor of >= %d bytes on %s" % (nbytes.value, self.device))
+        self.workspace = workspace if workspace is not None else torch.empty(nbytes.value, dtype=torch.uint8, device=self.device)
+        cnt, idx = self._legal_tensors(legal_actions)
         self._legal = (cnt, idx)
         h = C.c_void_p()
         with torch.cuda.device(self.device):
@@ -68,6 +81,16 @@ class Forest:
                                            self.A, self.S, self.D, self.root_offset, _p(cnt), _p(idx),
                                            _stream(self.device)))
         self.h = h
+
+    def _legal_tensors(self, legal_actions):
+        return legal_tensors(legal_actions, self.N, self.A, self.variant, self.device)
+
+    def reset(self, legal_actions="same"):
+        """A fresh batch of roots over the same workspace (Roots.clear() + Roots(...), cnode.cpp:301-317,360-366)."""
+        if not (isinstance(legal_actions, str) and legal_actions == "same"):
+            self._legal = self._legal_tensors(legal_actions)
+        cnt, idx = self._legal
+        check(self.L.lzb_forest_reset(self.h, _p(cnt), _p(idx), _stream(self.device)))
 
     def __del__(self):
         h = getattr(self, "h", None)
@@ -161,6 +184,13 @@ class Forest:
         if gumbel:
             out.update(policies=pol, children_values=cv)
         return out
+
+    def trajectories(self):
+        """(actions [N, S+1] int32, lengths [N] int32): greedy best_action chains (get_trajectories)."""
+        acts = torch.full((self.N, self.S + 1), -1, dtype=torch.int32, device=self.device)
+        ln = torch.empty(self.N, dtype=torch.int32, device=self.device)
+        check(self.L.lzb_trajectories(self.h, _p(acts), self.S + 1, _p(ln), _stream(self.device)))
+        return acts, ln
 
     # ------------------------------------------------------------------ introspection (tests)
     def dump_tree(self, i):

@@ -1,0 +1,2 @@
+from .mcts_ctree import EfficientZeroMCTSCtree, GumbelMuZeroMCTSCtree, MuZeroMCTSCtree  # noqa: F401
+from .mcts_ctree_sampled import SampledEfficientZeroMCTSCtree  # noqa: F401

@@ -1,0 +1,344 @@
+"""Search drivers with the reference's names and call signatures (lzero/mcts/tree_search/mcts_ctree.py:172-321
+MuZero, :623-827 EfficientZero, :956-1122 Gumbel MuZero), rewritten so that one search issues NO host<->device
+round trip: select + leaf gather -> model.recurrent_inference -> inverse scalar transform -> latent store ->
+expand + backup all consume and produce device tensors.  The reference moves the latent pool, the model
+outputs and four index lists through numpy / Python lists every simulation (mcts_ctree.py:283-310).
+
+`cfg` is the same object the reference takes (an EasyDict or any mapping with attribute access): keys read are
+num_simulations, pb_c_base, pb_c_init, discount_factor, value_delta_max, env_type, device, lstm_horizon_len,
+max_num_considered_actions, model.{support_scale, categorical_distribution}.  Optional extra keys:
+tie_break_seed (int), tie_break_mode ('per_root' | 'batch').
+"""
+import copy
+
+import numpy as np
+import torch
+
+from ..ctree import _tree_api as api
+from ..forest import _dev
+from .scaling import InverseScalarTransform
+
+
+class AttrDict(dict):
+    """Minimal stand-in for easydict.EasyDict (not installed here): nested attribute access over a dict."""
+
+    def __init__(self, d=None, **kw):
+        super().__init__()
+        for k, v in dict(d or {}, **kw).items():
+            self[k] = v
+
+    def __setitem__(self, k, v):
+        super().__setitem__(k, AttrDict(v) if isinstance(v, dict) and not isinstance(v, AttrDict) else v)
+
+    def __getattr__(self, k):
+        try:
+            return self[k]
+        except KeyError:
+            raise AttributeError(k)
+
+    __setattr__ = __setitem__
+
+    def update(self, other=None, **kw):
+        for k, v in dict(other or {}, **kw).items():
+            if isinstance(v, dict) and isinstance(self.get(k), dict):
+                self[k].update(v)
+            else:
+                self[k] = v
+
+
+def _get(cfg, key, default=None):
+    try:
+        return cfg[key] if key in cfg else default
+    except TypeError:
+        return getattr(cfg, key, default)
+
+
+class _CtreeDriver:
+    """What the three discrete drivers share: config handling and the device-resident simulation loop."""
+
+    config = dict(root_dirichlet_alpha=0.3, root_noise_weight=0.25, pb_c_base=19652, pb_c_init=1.25,
+                  value_delta_max=0.01, env_type='not_board_games')
+    tree = None  # the tree module (mz_tree / ez_tree / gmz_tree)
+
+    @classmethod
+    def default_config(cls):
+        cfg = AttrDict(copy.deepcopy(cls.config))
+        cfg.cfg_type = cls.__name__ + 'Dict'
+        return cfg
+
+    def __init__(self, cfg=None):
+        default_config = self.default_config()
+        default_config.update(cfg or {})
+        self._cfg = default_config
+        model_cfg = _get(self._cfg, "model", {}) or {}
+        self.inverse_scalar_transform_handle = InverseScalarTransform(
+            _get(model_cfg, "support_scale", 300), _get(self._cfg, "device", "cuda"),
+            _get(model_cfg, "categorical_distribution", True))
+        if _get(self._cfg, "tie_break_seed") is not None:
+            api.set_tie_break(self._cfg.tie_break_seed, _get(self._cfg, "tie_break_mode", "per_root"))
+
+    @classmethod
+    def roots(cls, active_collect_env_num, legal_actions):
+        """mcts_ctree.py:215-225: the CRoots of one batch."""
+        return cls.tree.Roots(active_collect_env_num, legal_actions)
+
+    # ------------------------------------------------------------------ pieces of the loop
+    def _latent_pool(self, forest, latent_state_roots, S):
+        """latent_state_batch_in_search_path as ONE device tensor [S+1, N, ...] (the reference keeps a Python list of
+        numpy arrays, mcts_ctree.py:247,305); slot e holds the latent of the node expanded with index e."""
+        lat0 = latent_state_roots if isinstance(latent_state_roots, torch.Tensor) else torch.as_tensor(np.asarray(latent_state_roots))
+        lat0 = lat0.to(forest.device, non_blocking=True)
+        pool = torch.empty((S + 1,) + tuple(lat0.shape), dtype=lat0.dtype, device=forest.device)
+        pool[0].copy_(lat0)
+        return pool
+
+    @staticmethod
+    def _rows_ok(t):
+        return (t[0, 0].numel() * t.element_size()) % 4 == 0
+
+    def _to_play(self, to_play_batch, forest):
+        # board games: the reference deep-copies the list per simulation because Cython mutates nothing here; a
+        # device tensor that the kernels only read serves both env types.
+        return _dev(to_play_batch, torch.int32, forest.device).reshape(-1)
+
+    def _store(self, forest, src, dst, is_reset=None):
+        """dst[i] = is_reset[i] ? 0 : src[i] for one pool slot (our copy kernel when rows are fp32, torch otherwise)."""
+        src = src.reshape(dst.shape)
+        if src.dtype == torch.float32 and dst.dtype == torch.float32 and src.is_contiguous() and dst.is_contiguous():
+            forest.store_hidden(src, dst, is_reset)
+        else:
+            dst.copy_(src)
+            if is_reset is not None:
+                dst[is_reset.bool()] = 0
+
+    def _begin(self, roots, model, to_play_batch, num_simulations=0, max_considered=0):
+        if hasattr(model, "eval"):
+            model.eval()
+        cfg = self._cfg
+        N, S = roots.num, int(cfg.num_simulations)
+        if isinstance(to_play_batch, int):
+            to_play_batch = [to_play_batch] * N
+        forest = roots._materialize(S)
+        mm = api.MinMaxStatsList(N)
+        mm.set_delta(cfg.value_delta_max)
+        mm._bind(forest)
+        scfg = api._search_cfg(forest, _get(cfg, "pb_c_base", 19652), _get(cfg, "pb_c_init", 1.25), cfg.discount_factor,
+                               to_play_batch, num_simulations=num_simulations, max_considered=max_considered,
+                               players=getattr(roots, "_players", None))
+        return forest, scfg, self._to_play(to_play_batch, forest), api.ResultsWrapper(N), S
+
+
+    # ------------------------------------------------------------------ whole-search CUDA graph (cfg.cuda_graph)
+    def _graphed(self, roots, model, latent_state_roots, hidden_roots, to_play_batch):
+        """Replays prepare + all S simulation rounds + root outputs as ONE CUDA graph.
+
+        A collector or reanalyze loop searches the same shape over and over; the first search of a shape runs eagerly
+        once (warm-up) and is then captured over static device buffers.  Later searches copy their inputs into those
+        buffers and replay, so the host issues one launch per search instead of ~4 per simulation.  The model must be
+        capturable (no host syncs, fixed shapes).  The Roots object receives a copy of the outputs."""
+        if roots.forest is not None:
+            raise RuntimeError("cuda_graph search needs roots that have not been traversed yet")
+        if self._sampled:
+            raise NotImplementedError("cuda_graph is not offered for the sampled tree (its sampler draws fresh numbers per search)")
+        p = roots._prep
+        if p is None:
+            raise RuntimeError("Roots.prepare / prepare_no_noise must be called before search")
+        N, S, dev = roots.num, int(self._cfg.num_simulations), roots._device
+        if isinstance(to_play_batch, int):
+            to_play_batch = [to_play_batch] * N
+        lat0 = _as_tensor(latent_state_roots)
+        hid = None if hidden_roots is None else [_as_tensor(h) for h in hidden_roots]
+        tp_host = to_play_batch if not (isinstance(to_play_batch, torch.Tensor) and to_play_batch.is_cuda) else None
+        players = 0 if tp_host is None else (1 if int(np.asarray(tp_host).max()) == -1 else 2)
+        key = (N, roots.action_space_size, S, tuple(lat0.shape), lat0.dtype, id(model), roots._legal is None,
+               p["noise"] is None, players, None if hid is None else tuple(hid[0].shape), str(dev))
+        cache = self.__dict__.setdefault("_graphs", {})
+        g = cache.get(key)
+        if g is None:
+            g = cache[key] = _SearchGraph(self, roots, model, lat0, hid, to_play_batch, dev)
+        g.run(roots, lat0, hid, to_play_batch)
+
+    _sampled = False
+
+
+class _SearchGraph:
+    """Static buffers + captured graph of one search shape (see _CtreeDriver._graphed)."""
+
+    def __init__(self, driver, roots, model, lat0, hid, to_play, dev):
+        from ..forest import legal_tensors
+        p = roots._prep
+        N, A = roots.num, roots.action_space_size
+        self.driver, self.model, self.dev = driver, model, dev
+        self.static = {k: (None if p[k] is None else torch.empty_like(p[k])) for k in ("logits", "noise", "reward", "to_play", "value")}
+        self.noise_weight = p["noise_weight"]
+        self.lat0 = torch.empty(tuple(lat0.shape), dtype=lat0.dtype, device=dev)
+        self.hid = None if hid is None else [torch.empty(tuple(h.shape), dtype=h.dtype, device=dev) for h in hid]
+        self.tp = torch.empty(N, dtype=torch.int32, device=dev)
+        self.legal = None
+        if roots._legal is not None:
+            cnt, idx = legal_tensors(roots._legal, N, A, roots.variant, dev)
+            self.legal = (torch.empty_like(cnt), torch.empty_like(idx))
+        self.shadow = type(roots).__new__(type(roots))
+        self.shadow.__dict__.update(roots.__dict__)
+        self.shadow._legal = self.legal
+        self.shadow.forest = None
+        self.shadow._prep = dict(self.static, noise_weight=self.noise_weight)
+        tp_known = not (isinstance(to_play, torch.Tensor) and to_play.is_cuda)
+        self.shadow._players = (1 if int(np.asarray(to_play).max()) == -1 else 2) if tp_known else None
+        self.graph = None
+        self.outs = None
+
+    def _load(self, roots, lat0, hid, to_play):
+        from ..forest import legal_tensors
+        p = roots._prep
+        if p["noise_weight"] != self.noise_weight:
+            raise RuntimeError("root_noise_weight changed between searches of one captured shape")
+        for k, t in self.static.items():
+            if t is not None:
+                t.copy_(p[k], non_blocking=True)
+        self.lat0.copy_(lat0, non_blocking=True)
+        if self.hid is not None:
+            for d, s in zip(self.hid, hid):
+                d.copy_(s.reshape(d.shape), non_blocking=True)
+        self.tp.copy_(_dev(to_play, torch.int32, self.dev).reshape(-1), non_blocking=True)
+        if self.legal is not None:
+            cnt, idx = legal_tensors(roots._legal, roots.num, roots.action_space_size, roots.variant, self.dev)
+            self.legal[0].copy_(cnt, non_blocking=True)
+            self.legal[1].copy_(idx, non_blocking=True)
+
+    def _body(self):
+        sh = self.shadow
+        if sh.forest is None:
+            sh._materialize(int(self.driver._cfg.num_simulations))
+        else:
+            sh.forest.reset()
+            sh._apply_prepare(reset=False)
+        hidden = None if self.hid is None else tuple(self.hid)
+        self.driver._search(sh, self.model, self.lat0, hidden, self.tp)
+        gum = sh.variant == "gmz"
+        return sh.forest.root_outputs(discount=float(self.driver._cfg.discount_factor) if gum else 0.0, gumbel=gum)
+
+    def run(self, roots, lat0, hid, to_play):
+        self._load(roots, lat0, hid, to_play)
+        if self.graph is None:
+            self._body()  # eager warm-up: allocator, lazy uploads (Gumbel tables), cudaFuncSetAttribute
+            torch.cuda.synchronize(self.dev)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.outs = self._body()
+            self.graph = g
+        self.graph.replay()
+        roots._cached_outputs = {k: v.clone() for k, v in self.outs.items()}
+        roots._graph_forest = self.shadow.forest
+
+
+def _mz_module():
+    from ..ctree.ctree_muzero import mz_tree
+    return mz_tree
+
+
+def _ez_module():
+    from ..ctree.ctree_efficientzero import ez_tree
+    return ez_tree
+
+
+def _gmz_module():
+    from ..ctree.ctree_gumbel_muzero import gmz_tree
+    return gmz_tree
+
+
+class MuZeroMCTSCtree(_CtreeDriver):
+    """lzero/mcts/tree_search/mcts_ctree.py:172-321."""
+    tree = _mz_module()
+    gumbel = False
+
+    def search(self, roots, model, latent_state_roots, to_play_batch):
+        if _get(self._cfg, "cuda_graph", False):
+            return self._graphed(roots, model, latent_state_roots, None, to_play_batch)
+        return self._search(roots, model, latent_state_roots, None, to_play_batch)
+
+    def _search(self, roots, model, latent_state_roots, hidden_roots, to_play_batch):
+        with torch.no_grad():
+            cfg = self._cfg
+            kw = dict(num_simulations=int(cfg.num_simulations), max_considered=int(cfg.max_num_considered_actions)) if self.gumbel else {}
+            forest, scfg, tp, results, S = self._begin(roots, model, to_play_batch, **kw)
+            discount = cfg.discount_factor
+            pool = self._latent_pool(forest, latent_state_roots, S)
+            leaf = torch.empty_like(pool[0])
+            fused = self._rows_ok(pool)
+            bufs = None
+            for simulation_index in range(S):
+                # stage 1: selection + (fused) gather of each leaf's parent latent (mcts_ctree.py:272-289)
+                o = api.traverse_tensors(roots, scfg, tp, results, gathers=[(pool, leaf)] if fused else (), out=bufs)
+                bufs = o
+                if not fused:
+                    leaf = pool[o["ix"].long(), o["iy"].long()]
+                # stage 2: expansion inputs from the model, still on the device (mcts_ctree.py:298-303);
+                # Gumbel MuZero passes the action as [N, 1] (:1090)
+                net = model.recurrent_inference(leaf, o["last_action"].unsqueeze(1) if self.gumbel else o["last_action"])
+                value = self.inverse_scalar_transform_handle(net.value)
+                reward = self.inverse_scalar_transform_handle(net.reward)
+                self._store(forest, net.latent_state, pool[simulation_index + 1])
+                # stage 3: expand + backup (mcts_ctree.py:316-321)
+                api.backprop_tensors(results, simulation_index + 1, discount, reward, value, net.policy_logits, o["vtp"])
+
+
+class GumbelMuZeroMCTSCtree(MuZeroMCTSCtree):
+    """lzero/mcts/tree_search/mcts_ctree.py:956-1122: same loop, Gumbel tree module, actions as [N, 1]."""
+    tree = _gmz_module()
+    config = dict(_CtreeDriver.config, max_num_considered_actions=6)
+    gumbel = True
+
+
+class EfficientZeroMCTSCtree(_CtreeDriver):
+    """lzero/mcts/tree_search/mcts_ctree.py:623-827 (value_prefix + LSTM hidden state with horizon reset)."""
+    tree = _ez_module()
+    config = dict(_CtreeDriver.config, lstm_horizon_len=5)
+
+    def search(self, roots, model, latent_state_roots, reward_hidden_state_roots, to_play_batch):
+        if _get(self._cfg, "cuda_graph", False):
+            return self._graphed(roots, model, latent_state_roots, reward_hidden_state_roots, to_play_batch)
+        return self._search(roots, model, latent_state_roots, reward_hidden_state_roots, to_play_batch)
+
+    def _leaf_action(self, roots, o):
+        return o["last_action"]
+
+    def _expand_inputs(self, roots, net):
+        return dict(logits=net.policy_logits)
+
+    def _search(self, roots, model, latent_state_roots, hidden_roots, to_play_batch):
+        with torch.no_grad():
+            forest, scfg, tp, results, S = self._begin(roots, model, to_play_batch)
+            discount, horizon = self._cfg.discount_factor, int(self._cfg.lstm_horizon_len)
+            assert horizon > 0
+            N = roots.num
+            pool = self._latent_pool(forest, latent_state_roots, S)
+            # reward_hidden_state_{c,h}_batch: [S+1, N, H] (the reference keeps lists of [1, N, H] arrays, :727-728)
+            c_pool = self._latent_pool(forest, _as_tensor(hidden_roots[0]).reshape(N, -1), S)
+            h_pool = self._latent_pool(forest, _as_tensor(hidden_roots[1]).reshape(N, -1), S)
+            leaf = torch.empty_like(pool[0])
+            leaf_c, leaf_h = torch.empty_like(c_pool[0]), torch.empty_like(h_pool[0])
+            is_reset = torch.empty(N, dtype=torch.int32, device=forest.device)
+            gathers = [(pool, leaf), (c_pool, leaf_c), (h_pool, leaf_h)]
+            if not all(self._rows_ok(p) for p, _ in gathers):
+                raise ValueError("latent / hidden-state rows must be a multiple of 4 bytes")
+            bufs = None
+            for simulation_index in range(S):
+                o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers, out=bufs)
+                bufs = o
+                net = model.recurrent_inference(leaf, (leaf_c.unsqueeze(0), leaf_h.unsqueeze(0)), self._leaf_action(roots, o))
+                value = self.inverse_scalar_transform_handle(net.value)
+                value_prefix = self.inverse_scalar_transform_handle(net.value_prefix)
+                self._store(forest, net.latent_state, pool[simulation_index + 1])
+                # is_reset = (search_len % lstm_horizon_len == 0) is computed by the kernel (mcts_ctree.py:809-814) ...
+                e = self._expand_inputs(roots, net)
+                api.backprop_tensors(results, simulation_index + 1, discount, value_prefix, value, e.get("logits"),
+                                     o["vtp"], lstm_horizon_len=horizon, is_reset_out=is_reset,
+                                     sampled_actions=e.get("sampled_actions"))
+                # ... and applied to the LSTM state as it enters the pool (:812-816)
+                self._store(forest, net.reward_hidden_state[0], c_pool[simulation_index + 1], is_reset)
+                self._store(forest, net.reward_hidden_state[1], h_pool[simulation_index + 1], is_reset)
+
+
+def _as_tensor(x):
+    return x if isinstance(x, torch.Tensor) else torch.as_tensor(np.asarray(x))
