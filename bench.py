@@ -68,7 +68,7 @@ def make_inputs(a, rank, device):
         noise=(gam / gam.sum(1, keepdim=True)).float().contiguous(),
         to_play=torch.full((N,), -1, dtype=torch.int32, device=device),
         logits=rn(S, N, A), reward=rn(S, N) * 0.1, value=rn(S, N),
-        latent_roots=rn(N, max(L, 1)), model_latent=rn(N, max(L, 1)),
+        latent_roots=rn(N, max(L, 1)), model_latent=rn(S, N, max(L, 1)),
     )
     if a.variant == "ez":
         inp["reward"] = rn(S, N)  # value prefixes
@@ -122,15 +122,15 @@ class NetOut:
 
 class TableModel:
     """recurrent_inference as a fixed table lookup (NN time excluded and stated as such): call s of a
-    search returns row s of pre-generated logits / value / reward tables and a fixed next-latent tensor, all in HBM."""
+    search returns row s of pre-generated logits / value / reward tables (a distinct next-latent tensor per simulation), all in HBM."""
 
     def __init__(self, inp, variant):
         self.inp, self.variant, self.s = inp, variant, 0
-        N = inp["model_latent"].shape[0]
+        N = inp["model_latent"].shape[1]
         if variant == "ez":
             H = 512
-            self.hidden = (inp["model_latent"][:, :1].expand(N, H).contiguous().unsqueeze(0),
-                           inp["model_latent"][:, :1].expand(N, H).contiguous().unsqueeze(0))
+            self.hidden = (inp["model_latent"][0, :, :1].expand(N, H).contiguous().unsqueeze(0),
+                           inp["model_latent"][0, :, :1].expand(N, H).contiguous().unsqueeze(0))
 
     def eval(self):
         self.s = 0  # search() calls model.eval() once per search (mcts_ctree.py:242)
@@ -139,7 +139,7 @@ class TableModel:
         i, s = self.inp, self.s
         self.s += 1
         o = NetOut()
-        o.latent_state, o.policy_logits, o.value = i["model_latent"], i["logits"][s], i["value"][s].unsqueeze(1)
+        o.latent_state, o.policy_logits, o.value = i["model_latent"][s], i["logits"][s], i["value"][s].unsqueeze(1)
         o.reward = o.value_prefix = i["reward"][s].unsqueeze(1)
         o.reward_hidden_state = getattr(self, "hidden", None)
         return o
@@ -177,38 +177,41 @@ def one_search(a, mcts, model, inp, host=None, rank=0):
 
 # --------------------------------------------------------------------------------------------- per-kernel timing
 class KernelTimer:
-    """CUDA events around each launch of our three per-simulation kernels (on torch's current stream, which is the
-    stream the C ABI launches on), plus the mean search depth the roofline byte model needs."""
+    """CUDA events around each launch of our per-simulation kernels (on torch's current stream, which is the stream
+    the C ABI launches on), plus the mean search depth the roofline byte model needs.  The caller first queues a
+    spin kernel (torch.cuda._sleep) so the host runs ahead and the launches execute back to back: the event pairs
+    then measure kernel durations, not Python launch latency."""
+    NAMES = {"step": "step (expand+backup s, select+gather s+1)", "traverse": "select+gather", "backprop": "expand+backup"}
 
     def __init__(self):
-        self.ev = {"select_gather": [], "store_latent": [], "expand_backup": []}
+        self.ev = {k: [] for k in self.NAMES}
         self.depth = []
 
     def install(self):
         import torch
         from lightzero_b200.forest import Forest
-        self._orig = (Forest.traverse, Forest.backprop, Forest.store_hidden)
+        self._orig = {k: getattr(Forest, k) for k in self.NAMES}
         timer = self
 
-        def wrap(fn, name, post=None):
+        def wrap(fn, name):
             def inner(self_, *args, **kw):
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
                 r = fn(self_, *args, **kw)
                 e1.record()
                 timer.ev[name].append((e0, e1))
-                if post:
-                    post(r)
+                if isinstance(r, dict) and "search_len" in r:
+                    timer.depth.append(r["search_len"].float().mean())
                 return r
             return inner
 
-        Forest.traverse = wrap(self._orig[0], "select_gather", lambda o: timer.depth.append(o["search_len"].float().mean()))
-        Forest.backprop = wrap(self._orig[1], "expand_backup")
-        Forest.store_hidden = wrap(self._orig[2], "store_latent")
+        for k, fn in self._orig.items():
+            setattr(Forest, k, wrap(fn, k))
 
     def remove(self):
         from lightzero_b200.forest import Forest
-        Forest.traverse, Forest.backprop, Forest.store_hidden = self._orig
+        for k, fn in self._orig.items():
+            setattr(Forest, k, fn)
 
     def summary(self):
         import torch
@@ -219,13 +222,13 @@ class KernelTimer:
 
 
 def roofline(a, per_kernel_ms, depth, peak_gbs, peak_src):
-    """Algorithmic bytes per launch (per root per simulation, x N roots per launch)."""
-    N, A, Lb = a.roots, a.actions, 8 * max(a.latent, 1)
-    alg = {
-        "select_gather": N * (depth * (16 * A + 16) + 8 + 4 * (depth + 1) + Lb),
-        "expand_backup": N * (4 * A + 16 * A + 28 + (depth + 1) * 20 + 8),
-        "store_latent": N * Lb,
-    }
+    """Algorithmic bytes per launch (per root per simulation, x N roots per launch).  The mean depth
+    is measured over the whole search; note the leaf rows are read in place from the model's output tensors, so the
+    gather moves 8 L bytes per root (4 L read + 4 L written) and there is no separate store into a pool."""
+    N, A, Lb = a.roots, a.actions, 8 * max(a.latent, 1) + (16 * 512 if a.variant == "ez" else 0)
+    sel = depth * (16 * A + 16) + 8 + 4 * (depth + 1) + Lb
+    bak = 4 * A + 16 * A + 28 + (depth + 1) * 20 + 8
+    alg = {"step": N * (sel + bak), "traverse": N * sel, "backprop": N * bak}
     tot = {k: sum(v) for k, v in per_kernel_ms.items() if v}
     top = max(tot, key=tot.get)
     avg_ms = tot[top] / len(per_kernel_ms[top])
@@ -238,7 +241,7 @@ def roofline(a, per_kernel_ms, depth, peak_gbs, peak_src):
         except Exception:
             traffic = None
     share = {k: round(v / sum(tot.values()), 4) for k, v in tot.items()}
-    return {"bound": "hbm", "kernel": top, "achieved": round(achieved, 2), "peak": peak_gbs, "unit": "GB/s",
+    return {"bound": "hbm", "kernel": KernelTimer.NAMES[top], "achieved": round(achieved, 2), "peak": peak_gbs, "unit": "GB/s",
             "frac": round(achieved / peak_gbs, 4), "traffic": traffic, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": int(alg[top]), "avg_launch_us": round(avg_ms * 1e3, 2),
             "mean_search_depth": round(depth, 3), "kernel_time_share": share,
@@ -255,7 +258,7 @@ def cpu_inputs(a, n, seed):
                 noises=[r for r in rng.dirichlet([ALPHA] * A, size=n).astype(np.float32)],
                 to_play=np.full(n, -1, np.int32), logits=f(S, n, A),
                 reward=(f(S, n) if a.variant == "ez" else f(S, n) * np.float32(0.1)), value=f(S, n),
-                latent_roots=f(n, L), model_latent=f(n, L))
+                latent_roots=f(n, L), model_latent=f(S, n, L))
 
 
 def cpu_search(a, d):
@@ -275,7 +278,7 @@ def cpu_search(a, d):
     for s in range(a.sims):
         o = f.traverse(PB_C_BASE, PB_C_INIT, DISCOUNT, d["to_play"], num_simulations=a.sims)
         leaf = np.asarray([pool[ix][iy] for ix, iy in zip(o["ix"].tolist(), o["iy"].tolist())])  # noqa: F841
-        pool.append(d["model_latent"])
+        pool.append(d["model_latent"][s])
         is_reset = (o["search_len"] % 5 == 0).astype(np.int32) if a.variant == "ez" else None
         f.backprop(s + 1, DISCOUNT, d["reward"][s], d["value"][s], d["logits"][s], is_reset, o["vtp"])
     dist, _ = f.distributions()
@@ -445,9 +448,11 @@ def run_b200_arm(a):
     eager = make_driver(a, device, graph=False)
     one_search(a, eager, model, inp, rank=rank)  # warm the eager path
     timer.install()
-    for _ in range(2):
+    for _ in range(3):
         flush.fill_(1)
+        torch.cuda._sleep(int(3e7))  # ~15 ms of spin: the host queues the whole search behind it
         one_search(a, eager, model, inp, rank=rank)
+        torch.cuda.synchronize()
     timer.remove()
     per_kernel, depth = timer.summary()
 
@@ -473,7 +478,7 @@ def run_b200_arm(a):
                        "cuda_graph": not a.no_graph, "l2": "512 MB flush between timed steps; working set > L2",
                        "parallelism": "roots sharded x%d, all-gather of root outputs per search" % world,
                        "wall_ms_per_step_incl_flush": round(1e3 * t_wall / a.steps, 3)},
-            "gpu_launches": a.steps * (3 + 3 * S + 1),
+            "gpu_launches": a.steps * (5 + S + 1),  # init, minmax, prepare, root slots, select, S-1 steps, backup, outputs
             "clocks": clk,
             "roofline": roofline(a, per_kernel, depth, peak, src),
         }

@@ -98,12 +98,29 @@ int lzb_prepare(lzb_forest_t *f, const float *logits_dev, const float *noise_dev
                 const float *reward_dev, const float *value_dev, const int32_t *to_play_dev,
                 const float *sampled_actions_dev, void *stream);
 
-/* One gather of leaf inputs: dst[i, :] = src[ix_i, i, :] for row_bytes bytes (multiple of 4).
+/* Where the rows gathered for a leaf live.  The reference keeps one array per expanded node generation
+ * (latent_state_batch_in_search_path.append(...), mcts_ctree.py:247,305; reward_hidden_state_{c,h}_batch :727-728,
+ * :817-818) and never copies it; neither does this library: up to three "slot tables" hold, per expansion index e,
+ * the base pointer of the caller's [N, row] device tensor for e (0: latent, 1: LSTM c, 2: LSTM h). */
+typedef struct {
+    const void *ptr[3];
+    int32_t n; /* how many of ptr[] are used */
+} lzb_slots_t;
+
+/* Slot pointers of expansion index `latent_index` (0 = the roots' own latents).  lzb_backprop / lzb_step set
+ * the slots of the node they expand themselves (lzb_backprop_io_t.new_slots). */
+int lzb_set_slots(lzb_forest_t *f, int latent_index, const lzb_slots_t *slots, void *stream);
+
+/* One gather of leaf inputs: dst[i, :] = row i of the tensor registered for the leaf's parent expansion ix_i
+ * (src_dev == NULL: slot table k, k = position of this gather in the array), or src[ix_i, i, :] of one dense
+ * [E, N, row_bytes] pool (src_dev != NULL).  row_bytes: multiple of 4.  zero_if_reset: rows whose parent was
+ * expanded with is_reset = 1 read as zeros (the LSTM-state reset of mcts_ctree.py:812-816).
  * Replaces the Python loop + np.asarray + H2D copy of mcts_ctree.py:283-289 / :766-775. */
 typedef struct {
-    const void *src_dev; /* [E, N, row_bytes] pool, E = max_sims + 1 */
-    void *dst_dev;       /* [N, row_bytes] */
+    const void *src_dev;
+    void *dst_dev;
     int64_t row_bytes;
+    int32_t zero_if_reset;
 } lzb_gather_t;
 
 /* batch_traverse (mz_tree.pyx:95-100 -> cbatch_traverse, cnode.cpp:755-824; ez :886-963; gumbel
@@ -111,21 +128,44 @@ typedef struct {
  * iy (latent_state_index_in_batch, local index), search_len, vtp (virtual_to_play_batchs),
  * last_action as int64 (what .long() produces, mcts_ctree.py:289); last_action_f [N,D] for the sampled
  * tree.  Any output pointer may be NULL.  gathers/num_gathers may be 0. */
-int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const int32_t *to_play_dev, int32_t *ix_dev,
-                 int32_t *iy_dev, int64_t *last_action_dev, float *last_action_f_dev, int32_t *search_len_dev,
-                 int32_t *vtp_dev, const lzb_gather_t *gathers, int num_gathers, void *stream);
+typedef struct {
+    const int32_t *to_play_dev;
+    int32_t *ix_dev, *iy_dev;
+    int64_t *last_action_dev;
+    float *last_action_f_dev;
+    int32_t *search_len_dev, *vtp_dev;
+    const lzb_gather_t *gathers;
+    int32_t num_gathers;
+} lzb_traverse_io_t;
+int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse_io_t *io, void *stream);
 
 /* batch_backpropagate / batch_back_propagate (mz_tree.pyx:74-82 -> cbatch_backpropagate,
  * cnode.cpp:480-500; ez :577-601; gumbel :633-652).  latent_index = simulation_index + 1.
  * reward/value [N], logits [N,A] straight from the model's device tensors; to_play [N] = the vtp
  * returned by traverse.  EZ/SEZ reset handling (mcts_ctree.py:809-816): if is_reset_dev != NULL it is
  * used as given; else if lstm_horizon_len > 0 is_reset = (search_len % lstm_horizon_len == 0) is
- * computed on device, written to is_reset_out_dev when non-NULL. */
-int lzb_backprop(lzb_forest_t *f, int latent_index, float discount, const float *reward_dev, const float *value_dev,
-                 const float *logits_dev, const int32_t *to_play_dev, const int32_t *is_reset_dev,
-                 int lstm_horizon_len, int32_t *is_reset_out_dev, const float *sampled_actions_dev, void *stream);
+ * computed on device, written to is_reset_out_dev when non-NULL.  sampled_actions [N,K,D]: the new
+ * nodes' action table (sampled tree).  new_slots: where the new nodes' latent / LSTM rows live. */
+typedef struct {
+    int32_t latent_index;
+    float discount;
+    const float *reward_dev, *value_dev, *logits_dev;
+    const int32_t *to_play_dev, *is_reset_dev;
+    int32_t lstm_horizon_len;
+    int32_t *is_reset_out_dev;
+    const float *sampled_actions_dev;
+    lzb_slots_t new_slots;
+} lzb_backprop_io_t;
+int lzb_backprop(lzb_forest_t *f, const lzb_backprop_io_t *io, void *stream);
 
-/* EZ hidden-state write-back with reset (mcts_ctree.py:809-816): dst[i,:] = is_reset[i] ? 0 : src[i,:]. */
+/* One simulation step in ONE launch: lzb_backprop(bio) of simulation s followed by lzb_traverse(tio) of
+ * simulation s + 1 (the reference runs the two back to back between model calls: mcts_ctree.py:318-321, then
+ * :272-280 of the next iteration).  Results are identical to the two separate calls. */
+int lzb_step(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_backprop_io_t *bio, const lzb_traverse_io_t *tio,
+             void *stream);
+
+/* Row copy with optional reset (mcts_ctree.py:809-816): dst[i,:] = is_reset[i] ? 0 : src[i,:]; for callers that keep
+ * a dense [E, N, row] pool instead of slot pointers. */
 int lzb_store_hidden(const float *src_dev, float *dst_dev, const int32_t *is_reset_dev, int num_roots,
                      int64_t row_floats, void *stream);
 

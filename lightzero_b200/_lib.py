@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "liblzb200.so")
-SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
+SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",  # B200 only
@@ -57,7 +57,27 @@ class SearchCfg(C.Structure):
 
 class Gather(C.Structure):
     """lzb_gather_t"""
-    _fields_ = [("src_dev", C.c_void_p), ("dst_dev", C.c_void_p), ("row_bytes", C.c_int64)]
+    _fields_ = [("src_dev", C.c_void_p), ("dst_dev", C.c_void_p), ("row_bytes", C.c_int64), ("zero_if_reset", C.c_int32)]
+
+
+class Slots(C.Structure):
+    """lzb_slots_t"""
+    _fields_ = [("ptr", C.c_void_p * 3), ("n", C.c_int32)]
+
+
+class TraverseIO(C.Structure):
+    """lzb_traverse_io_t"""
+    _fields_ = [("to_play_dev", C.c_void_p), ("ix_dev", C.c_void_p), ("iy_dev", C.c_void_p),
+                ("last_action_dev", C.c_void_p), ("last_action_f_dev", C.c_void_p), ("search_len_dev", C.c_void_p),
+                ("vtp_dev", C.c_void_p), ("gathers", C.POINTER(Gather)), ("num_gathers", C.c_int32)]
+
+
+class BackpropIO(C.Structure):
+    """lzb_backprop_io_t"""
+    _fields_ = [("latent_index", C.c_int32), ("discount", C.c_float), ("reward_dev", C.c_void_p),
+                ("value_dev", C.c_void_p), ("logits_dev", C.c_void_p), ("to_play_dev", C.c_void_p),
+                ("is_reset_dev", C.c_void_p), ("lstm_horizon_len", C.c_int32), ("is_reset_out_dev", C.c_void_p),
+                ("sampled_actions_dev", C.c_void_p), ("new_slots", Slots)]
 
 
 _P = C.c_void_p
@@ -72,8 +92,10 @@ _PROTOS = {
     "lzb_forest_reset": (C.c_int, [_P, _P, _P, _P]),
     "lzb_set_delta": (C.c_int, [_P, C.c_float, _P]),
     "lzb_prepare": (C.c_int, [_P, _P, _P, C.c_float, _P, _P, _P, _P, _P]),
-    "lzb_traverse": (C.c_int, [_P, C.POINTER(SearchCfg), _P, _P, _P, _P, _P, _P, _P, C.POINTER(Gather), C.c_int, _P]),
-    "lzb_backprop": (C.c_int, [_P, C.c_int, C.c_float, _P, _P, _P, _P, _P, C.c_int, _P, _P, _P]),
+    "lzb_set_slots": (C.c_int, [_P, C.c_int, C.POINTER(Slots), _P]),
+    "lzb_traverse": (C.c_int, [_P, C.POINTER(SearchCfg), C.POINTER(TraverseIO), _P]),
+    "lzb_backprop": (C.c_int, [_P, C.POINTER(BackpropIO), _P]),
+    "lzb_step": (C.c_int, [_P, C.POINTER(SearchCfg), C.POINTER(BackpropIO), C.POINTER(TraverseIO), _P]),
     "lzb_store_hidden": (C.c_int, [_P, _P, _P, C.c_int, C.c_int64, _P]),
     "lzb_root_outputs": (C.c_int, [_P, _P, _P, _P, C.c_float, _P, _P, _P]),
     "lzb_trajectories": (C.c_int, [_P, _P, C.c_int, _P, _P]),

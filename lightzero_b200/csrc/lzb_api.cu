@@ -7,8 +7,7 @@
 #include <vector>
 
 #include "../../include/lzb200.h"
-#include "lzb_expand.cuh"
-#include "lzb_select.cuh"
+#include "lzb_step.cuh"
 
 using namespace lzb;
 
@@ -17,6 +16,7 @@ struct lzb_forest {
     size_t bytes;
     float delta;
     int sim;      // traverses issued since the last prepare (keys the tie-break stream)
+    const void *players_for; // to_play pointer whose batch maximum is in pool.scratch[0] for this search
     int expanded; // highest latent_index expanded so far
     int vt_m, vt_s;
     std::vector<int> vtable_host;
@@ -48,7 +48,7 @@ constexpr size_t kAlign = 256;
 inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 
 struct Layout {
-    size_t child, hdr, root, legal, minmax, path_a, path_b, res, best, actions, gumbel, vtable, scratch, total;
+    size_t node, root, legal, minmax, path_a, path_b, res, best, actions, gumbel, vtable, scratch, slots, total;
 };
 
 Layout make_layout(int variant, int N, int A, int S, int D)
@@ -57,8 +57,7 @@ Layout make_layout(int variant, int N, int A, int S, int D)
     Layout l;
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes); return at; };
-    l.child = take((size_t)N * E * A * sizeof(int4));
-    l.hdr = take((size_t)N * E * sizeof(int4));
+    l.node = take((size_t)N * E * (A + 1) * sizeof(int4));
     l.root = take((size_t)N * sizeof(int4));
     l.legal = take((size_t)N * A * sizeof(int));
     l.minmax = take((size_t)N * sizeof(float2));
@@ -70,6 +69,7 @@ Layout make_layout(int variant, int N, int A, int S, int D)
     l.gumbel = take((size_t)A * sizeof(float));
     l.vtable = take(E * sizeof(int));
     l.scratch = take(4 * sizeof(int));
+    l.slots = take((size_t)kMaxGathers * E * sizeof(char *));
     l.total = o;
     return l;
 }
@@ -106,7 +106,7 @@ __global__ void k_init(Pool p, const int *legal_count, const int *legal_actions)
     const bool all = (n <= 0); // empty list == every action legal (cnode.cpp:101-107)
     if (all) n = p.A;
     for (int j = 0; j < p.A; ++j) p.legal[(size_t)i * p.A + j] = (all || !legal_actions) ? j : legal_actions[(size_t)i * p.A + j];
-    p.hdr[(size_t)i * p.E] = make_int4(n, 0, 0, 0);
+    p.block(i, 0)[0] = make_int4(n, 0, 0, 0);
     p.root[i] = make_int4(0, 0, 0, 0);
     p.minmax[i] = make_float2(kFloatMax, kFloatMin); // CMinMaxStats ctor (cminimax.cpp:7-11)
     p.res[i] = make_int4(0, 0, 0, 0);
@@ -119,19 +119,19 @@ __global__ void k_reset_minmax(Pool p)
     if (i < p.N) p.minmax[i] = make_float2(kFloatMax, kFloatMin);
 }
 
+// players = (max(to_play_batch) == -1) ? 1 : 2 is batch-global (cnode.cpp:776-781): out[0] = max over the batch
+__global__ void k_max_to_play_init(int *out) { out[0] = INT_MIN; }
 __global__ void k_max_to_play(const int *to_play, int n, int *out)
 {
-    __shared__ int s[32];
     int m = INT_MIN;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) m = max(m, to_play[i]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) m = max(m, to_play[i]);
     m = warp_max_i(m);
-    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = m;
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        m = (threadIdx.x < (blockDim.x >> 5)) ? s[threadIdx.x] : INT_MIN;
-        m = warp_max_i(m);
-        if (threadIdx.x == 0) out[0] = m;
-    }
+    if ((threadIdx.x & 31) == 0) atomicMax(out, m);
+}
+
+__global__ void k_set_slots(Pool p, int e, int n, const char *s0, const char *s1, const char *s2)
+{
+    if (threadIdx.x < n) p.slots[(size_t)threadIdx.x * p.E + e] = threadIdx.x == 0 ? s0 : (threadIdx.x == 1 ? s1 : s2);
 }
 
 // dst[i,:] = is_reset[i] ? 0 : src[i,:]; 16-byte accesses when VEC (row bytes and both bases 16-B aligned)
@@ -163,9 +163,9 @@ __global__ void k_root_outputs(Pool p, int *visits, int *legal_count, float *val
     const int i = blockIdx.x * wpb + wib;
     if (i >= p.N) return;
     const int A = p.A;
-    const int4 h = p.hdr[(size_t)i * p.E];
+    const int4 h = p.block(i, 0)[0];
     const int n = h.x;
-    const int4 *kids = p.child + (size_t)i * p.E * A;
+    const int4 *kids = p.block(i, 0) + 1;
     if (visits)
         for (int j = lane; j < A; j += 32) visits[(size_t)i * A + j] = j < n ? child_visits(kids[j].x) : 0;
     if (lane == 0) {
@@ -204,7 +204,7 @@ __global__ void k_dump_tree(Pool p, int i, int upto, int *visit, float *vsum, fl
 {
     const int A = p.A;
     for (int e = 0; e <= upto; ++e) {
-        const int4 h = p.hdr[(size_t)i * p.E + e];
+        const int4 h = p.block(i, e)[0];
         if (threadIdx.x == 0) {
             hdr[e * 4 + 0] = h.x;
             hdr[e * 4 + 1] = h.y;
@@ -213,7 +213,7 @@ __global__ void k_dump_tree(Pool p, int i, int upto, int *visit, float *vsum, fl
             if (raw && p.variant == LZB_GMZ) raw[e] = __int_as_float(h.w);
         }
         for (int j = threadIdx.x; j < h.x; j += blockDim.x) {
-            const int4 c = p.child[((size_t)i * p.E + e) * A + j];
+            const int4 c = p.block(i, e)[1 + j];
             const size_t o = (size_t)e * A + j;
             const int ce = child_expansion(c.x);
             visit[o] = child_visits(c.x);
@@ -233,7 +233,7 @@ __global__ void k_dump_paths(Pool p, int *out, int stride)
     const int depth = p.res[i].x;
     for (int d = 0; d < depth && d < stride; ++d) {
         const int slot = p.path_a[(size_t)i * (p.S + 1) + d].x;
-        const int e = slot / p.A, pos = slot % p.A;
+        const int e = slot / p.B, pos = slot % p.B - 1;
         out[(size_t)i * stride + d] = (e == 0 && p.variant != LZB_SEZ) ? p.legal[(size_t)i * p.A + pos] : pos;
     }
 }
@@ -249,7 +249,7 @@ __global__ void k_trajectories(Pool p, int *out, int stride, int *len)
         if (pos < 0) break;
         if (d < stride) out[(size_t)i * stride + d] = (e == 0 && p.variant != LZB_SEZ) ? p.legal[(size_t)i * p.A + pos] : pos;
         d += 1;
-        e = child_expansion(p.child[((size_t)i * p.E + e) * p.A + pos].x);
+        e = child_expansion(p.block(i, e)[1 + pos].x);
     }
     len[i] = d;
 }
@@ -340,13 +340,13 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
     char *w = (char *)workspace_dev;
     Pool &p = f->pool;
     p.variant = variant; p.N = num_roots; p.A = action_space; p.S = max_sims; p.E = max_sims + 1; p.D = action_dim;
-    p.root_offset = root_offset;
-    p.child = (int4 *)(w + l.child); p.hdr = (int4 *)(w + l.hdr); p.root = (int4 *)(w + l.root);
+    p.root_offset = root_offset; p.B = action_space + 1;
+    p.node = (int4 *)(w + l.node); p.root = (int4 *)(w + l.root); p.slots = (const char **)(w + l.slots);
     p.legal = (int *)(w + l.legal); p.minmax = (float2 *)(w + l.minmax);
     p.path_a = (int4 *)(w + l.path_a); p.path_b = (int2 *)(w + l.path_b); p.res = (int4 *)(w + l.res);
     p.best = (int *)(w + l.best); p.actions = (float *)(w + l.actions); p.gumbel = (float *)(w + l.gumbel);
     p.vtable = (int *)(w + l.vtable); p.scratch = (int *)(w + l.scratch);
-    f->bytes = l.total; f->delta = 0.0f; f->sim = 0; f->expanded = -1; f->vt_m = -1; f->vt_s = -1;
+    f->bytes = l.total; f->delta = 0.0f; f->sim = 0; f->expanded = -1; f->vt_m = -1; f->vt_s = -1; f->players_for = nullptr;
     cudaStream_t st = (cudaStream_t)stream;
     k_init<<<(num_roots + 127) / 128, 128, 0, st>>>(p, legal_count_dev, legal_actions_dev);
     if (variant == LZB_GMZ) {
@@ -371,6 +371,7 @@ int lzb_forest_reset(lzb_forest_t *f, const int32_t *legal_count_dev, const int3
     LZB_CUDA(cudaGetLastError());
     f->sim = 0;
     f->expanded = -1;
+    f->players_for = nullptr;
     return LZB_OK;
 }
 
@@ -399,36 +400,41 @@ int lzb_prepare(lzb_forest_t *f, const float *logits_dev, const float *noise_dev
     LZB_CUDA(cudaGetLastError());
     f->sim = 0;
     f->expanded = 0;
+    f->players_for = nullptr;
     return LZB_OK;
 }
 
-int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const int32_t *to_play_dev, int32_t *ix_dev,
-                 int32_t *iy_dev, int64_t *last_action_dev, float *last_action_f_dev, int32_t *search_len_dev,
-                 int32_t *vtp_dev, const lzb_gather_t *gathers, int num_gathers, void *stream)
+} // extern "C"
+
+namespace {
+
+// Validates the traverse arguments and fills the kernel-side struct; launches the batch max(to_play) reduction
+// the first time a search sees this to_play buffer (players is batch-global, cnode.cpp:776-781).
+int fill_select(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse_io_t *io, SelectArgs &a, cudaStream_t st)
 {
-    if (!f || !cfg || !to_play_dev) return fail(LZB_E_ARG, "forest / cfg / to_play is NULL");
+    if (!f || !cfg || !io || !io->to_play_dev) return fail(LZB_E_ARG, "forest / cfg / io / to_play is NULL");
     if (f->expanded < 0) return fail(LZB_E_STATE, "traverse before prepare");
-    if (num_gathers < 0 || num_gathers > 3 || (num_gathers && !gathers)) return fail(LZB_E_ARG, "0..3 gathers supported");
+    if (io->num_gathers < 0 || io->num_gathers > kMaxGathers || (io->num_gathers && !io->gathers)) return fail(LZB_E_ARG, "0..3 gathers supported");
     if (cfg->rng_mode != LZB_RNG_BATCH && cfg->rng_mode != LZB_RNG_PER_ROOT) return fail(LZB_E_ARG, "rng_mode must be LZB_RNG_BATCH or LZB_RNG_PER_ROOT");
+    if (cfg->players < 0 || cfg->players > 2) return fail(LZB_E_ARG, "players must be 0, 1 or 2");
     const Pool &p = f->pool;
-    cudaStream_t st = (cudaStream_t)stream;
-    SelectArgs a{};
+    a = SelectArgs{};
     a.c_base = cfg->pb_c_base; a.c_init = cfg->pb_c_init; a.discount = cfg->discount; a.delta = f->delta;
-    a.players = cfg->players; a.sim = f->sim; a.rng_mode = cfg->rng_mode; a.seed = cfg->rng_seed;
-    a.num_simulations = cfg->num_simulations; a.ng = num_gathers;
-    a.to_play = to_play_dev; a.ix = ix_dev; a.iy = iy_dev; a.search_len = search_len_dev; a.vtp = vtp_dev;
-    a.last_action = (long long *)last_action_dev; a.last_action_f = last_action_f_dev;
-    for (int k = 0; k < num_gathers; ++k) {
-        if (!gathers[k].src_dev || !gathers[k].dst_dev || gathers[k].row_bytes <= 0 || (gathers[k].row_bytes & 3))
-            return fail(LZB_E_ARG, "gather %d: NULL pointer or row_bytes not a positive multiple of 4", k);
-        a.g[k] = Gather{(const char *)gathers[k].src_dev, (char *)gathers[k].dst_dev, (long long)gathers[k].row_bytes};
+    a.players = (p.variant == LZB_GMZ) ? 1 : cfg->players; a.sim = f->sim; a.rng_mode = cfg->rng_mode; a.seed = cfg->rng_seed;
+    a.num_simulations = cfg->num_simulations; a.ng = io->num_gathers; a.new_e = -1;
+    a.to_play = io->to_play_dev; a.ix = io->ix_dev; a.iy = io->iy_dev; a.search_len = io->search_len_dev; a.vtp = io->vtp_dev;
+    a.last_action = (long long *)io->last_action_dev; a.last_action_f = io->last_action_f_dev;
+    for (int k = 0; k < io->num_gathers; ++k) {
+        const lzb_gather_t &g = io->gathers[k];
+        if (!g.dst_dev || g.row_bytes <= 0 || (g.row_bytes & 3))
+            return fail(LZB_E_ARG, "gather %d: NULL destination or row_bytes not a positive multiple of 4", k);
+        a.g[k] = Gather{(const char *)g.src_dev, (char *)g.dst_dev, (long long)g.row_bytes, g.zero_if_reset};
     }
-    if (p.variant != LZB_GMZ && cfg->players == 0) {
-        k_max_to_play<<<1, 256, 0, st>>>(to_play_dev, p.N, p.scratch);
-    } else if (cfg->players < 0 || cfg->players > 2) {
-        return fail(LZB_E_ARG, "players must be 0, 1 or 2");
+    if (a.players == 0 && f->players_for != (const void *)io->to_play_dev) {
+        k_max_to_play_init<<<1, 1, 0, st>>>(p.scratch);
+        k_max_to_play<<<std::min((p.N + 255) / 256, 148), 256, 0, st>>>(io->to_play_dev, p.N, p.scratch);
+        f->players_for = io->to_play_dev;
     }
-    dim3 grid, block; size_t smem;
     if (p.variant == LZB_GMZ) {
         const int S = cfg->num_simulations, m = cfg->max_num_considered_actions;
         if (S <= 0 || m < 0) return fail(LZB_E_ARG, "Gumbel needs num_simulations > 0 and max_num_considered_actions >= 0");
@@ -439,38 +445,79 @@ int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const int32_t *to
             LZB_CUDA(cudaMemcpyAsync(p.vtable, f->vtable_host.data(), sizeof(int) * cnt, cudaMemcpyHostToDevice, st));
             f->vt_m = m; f->vt_s = S;
         }
-        if (int rc = launch_cfg(k_select_gumbel, (size_t)p.A * 28, p.N, grid, block, smem)) return rc;
+    }
+    return LZB_OK;
+}
+
+int fill_backup(lzb_forest_t *f, const lzb_backprop_io_t *io, BackupArgs &b)
+{
+    if (!f || !io) return fail(LZB_E_ARG, "forest / io is NULL");
+    const Pool &p = f->pool;
+    if (!io->reward_dev || !io->value_dev || !io->to_play_dev) return fail(LZB_E_ARG, "reward / value / to_play is NULL");
+    if (p.variant == LZB_SEZ ? !io->sampled_actions_dev : !io->logits_dev) return fail(LZB_E_ARG, "logits (or sampled_actions for the sampled tree) is NULL");
+    if (f->sim <= 0) return fail(LZB_E_STATE, "backprop before traverse");
+    if (io->latent_index <= 0 || io->latent_index > p.S) return fail(LZB_E_STATE, "latent_index %d outside the pool (max_sims %d)", io->latent_index, p.S);
+    if (io->new_slots.n < 0 || io->new_slots.n > kMaxGathers) return fail(LZB_E_ARG, "0..3 slot pointers supported");
+    b = BackupArgs{io->latent_index, io->lstm_horizon_len, io->discount, io->reward_dev, io->value_dev, io->logits_dev,
+                   io->sampled_actions_dev, io->to_play_dev, io->is_reset_dev, io->is_reset_out_dev, io->new_slots.n, {}};
+    for (int k = 0; k < io->new_slots.n; ++k) b.new_slot[k] = (const char *)io->new_slots.ptr[k];
+    return LZB_OK;
+}
+
+// dynamic shared memory per warp: selection stages A child records + A scores (Gumbel: 3 A-vectors), backup A floats
+size_t select_bytes_per_warp(const Pool &p) { return (size_t)p.A * (p.variant == LZB_GMZ ? 28 : 20); }
+
+} // namespace
+
+extern "C" {
+
+int lzb_set_slots(lzb_forest_t *f, int latent_index, const lzb_slots_t *slots, void *stream)
+{
+    if (!f || !slots) return fail(LZB_E_ARG, "forest / slots is NULL");
+    if (latent_index < 0 || latent_index > f->pool.S) return fail(LZB_E_ARG, "latent_index outside the pool");
+    if (slots->n < 0 || slots->n > kMaxGathers) return fail(LZB_E_ARG, "0..3 slot pointers supported");
+    k_set_slots<<<1, 32, 0, (cudaStream_t)stream>>>(f->pool, latent_index, slots->n, (const char *)slots->ptr[0],
+                                                   (const char *)slots->ptr[1], (const char *)slots->ptr[2]);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse_io_t *io, void *stream)
+{
+    cudaStream_t st = (cudaStream_t)stream;
+    SelectArgs a;
+    if (int rc = fill_select(f, cfg, io, a, st)) return rc;
+    const Pool &p = f->pool;
+    dim3 grid, block; size_t smem;
+    const size_t bpw = select_bytes_per_warp(p);
+    switch (p.variant) {
+    case LZB_GMZ:
+        if (int rc = launch_cfg(k_select_gumbel, bpw, p.N, grid, block, smem)) return rc;
         k_select_gumbel<<<grid, block, smem, st>>>(p, a);
-    } else {
-        const size_t bpw = (size_t)p.A * 20;
-        if (p.variant == LZB_MZ) {
-            if (int rc = launch_cfg(k_select_puct<LZB_MZ>, bpw, p.N, grid, block, smem)) return rc;
-            k_select_puct<LZB_MZ><<<grid, block, smem, st>>>(p, a);
-        } else if (p.variant == LZB_EZ) {
-            if (int rc = launch_cfg(k_select_puct<LZB_EZ>, bpw, p.N, grid, block, smem)) return rc;
-            k_select_puct<LZB_EZ><<<grid, block, smem, st>>>(p, a);
-        } else {
-            if (int rc = launch_cfg(k_select_puct<LZB_SEZ>, bpw, p.N, grid, block, smem)) return rc;
-            k_select_puct<LZB_SEZ><<<grid, block, smem, st>>>(p, a);
-        }
+        break;
+    case LZB_MZ:
+        if (int rc = launch_cfg(k_select_puct<LZB_MZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_select_puct<LZB_MZ><<<grid, block, smem, st>>>(p, a);
+        break;
+    case LZB_EZ:
+        if (int rc = launch_cfg(k_select_puct<LZB_EZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_select_puct<LZB_EZ><<<grid, block, smem, st>>>(p, a);
+        break;
+    default:
+        if (int rc = launch_cfg(k_select_puct<LZB_SEZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_select_puct<LZB_SEZ><<<grid, block, smem, st>>>(p, a);
+        break;
     }
     LZB_CUDA(cudaGetLastError());
     f->sim += 1;
     return LZB_OK;
 }
 
-int lzb_backprop(lzb_forest_t *f, int latent_index, float discount, const float *reward_dev, const float *value_dev,
-                 const float *logits_dev, const int32_t *to_play_dev, const int32_t *is_reset_dev,
-                 int lstm_horizon_len, int32_t *is_reset_out_dev, const float *sampled_actions_dev, void *stream)
+int lzb_backprop(lzb_forest_t *f, const lzb_backprop_io_t *io, void *stream)
 {
-    if (!f) return fail(LZB_E_ARG, "forest is NULL");
+    BackupArgs a;
+    if (int rc = fill_backup(f, io, a)) return rc;
     const Pool &p = f->pool;
-    if (!reward_dev || !value_dev || !to_play_dev) return fail(LZB_E_ARG, "reward / value / to_play is NULL");
-    if (p.variant == LZB_SEZ ? !sampled_actions_dev : !logits_dev) return fail(LZB_E_ARG, "logits (or sampled_actions for the sampled tree) is NULL");
-    if (f->sim <= 0) return fail(LZB_E_STATE, "backprop before traverse");
-    if (latent_index <= 0 || latent_index > p.S) return fail(LZB_E_STATE, "latent_index %d outside the pool (max_sims %d)", latent_index, p.S);
-    BackupArgs a{latent_index, lstm_horizon_len, discount, reward_dev, value_dev, logits_dev, sampled_actions_dev,
-                 to_play_dev, is_reset_dev, is_reset_out_dev};
     dim3 grid, block; size_t smem;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t bpw = (size_t)p.A * sizeof(float);
@@ -493,7 +540,46 @@ int lzb_backprop(lzb_forest_t *f, int latent_index, float discount, const float 
         break;
     }
     LZB_CUDA(cudaGetLastError());
-    if (latent_index > f->expanded) f->expanded = latent_index;
+    if (io->latent_index > f->expanded) f->expanded = io->latent_index;
+    return LZB_OK;
+}
+
+int lzb_step(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_backprop_io_t *bio, const lzb_traverse_io_t *tio,
+             void *stream)
+{
+    cudaStream_t st = (cudaStream_t)stream;
+    BackupArgs b;
+    SelectArgs a;
+    if (int rc = fill_backup(f, bio, b)) return rc;
+    if (int rc = fill_select(f, cfg, tio, a, st)) return rc;
+    a.new_e = b.latent_index;
+    for (int k = 0; k < kMaxGathers; ++k) a.new_slot[k] = b.new_slot[k];
+    for (int k = 0; k < a.ng; ++k)
+        if (!a.g[k].src && k >= b.n_slots) return fail(LZB_E_ARG, "gather %d reads the slot table but the step carries no slot pointer for it", k);
+    const Pool &p = f->pool;
+    dim3 grid, block; size_t smem;
+    const size_t bpw = select_bytes_per_warp(p);
+    switch (p.variant) {
+    case LZB_MZ:
+        if (int rc = launch_cfg(k_step<LZB_MZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_step<LZB_MZ><<<grid, block, smem, st>>>(p, b, a);
+        break;
+    case LZB_EZ:
+        if (int rc = launch_cfg(k_step<LZB_EZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_step<LZB_EZ><<<grid, block, smem, st>>>(p, b, a);
+        break;
+    case LZB_GMZ:
+        if (int rc = launch_cfg(k_step<LZB_GMZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_step<LZB_GMZ><<<grid, block, smem, st>>>(p, b, a);
+        break;
+    default:
+        if (int rc = launch_cfg(k_step<LZB_SEZ>, bpw, p.N, grid, block, smem)) return rc;
+        k_step<LZB_SEZ><<<grid, block, smem, st>>>(p, b, a);
+        break;
+    }
+    LZB_CUDA(cudaGetLastError());
+    if (bio->latent_index > f->expanded) f->expanded = bio->latent_index;
+    f->sim += 1;
     return LZB_OK;
 }
 

@@ -22,7 +22,7 @@ __device__ __forceinline__ void expand_children(const Pool &p, int i, int e, int
     __syncwarp();
     float sum = 0.0f;
     for (int j = 0; j < n; ++j) sum += s_tmp[j]; // every lane, same order: bit-identical to the serial host loop
-    int4 *dst = p.child + ((size_t)i * p.E + e) * p.A;
+    int4 *dst = p.block(i, e) + 1;
     for (int j = lane; j < n; j += 32) {
         float prior = s_tmp[j] / sum;
         if (noise) prior = prior * (1 - frac) + noise[j] * frac;
@@ -48,20 +48,20 @@ __global__ void k_prepare(Pool p, PrepArgs a)
     int n;
     if (p.variant == LZB_SEZ) {
         n = p.A; // K sampled children, priors unused by selection (sez cnode.cpp:1054-1079)
-        int4 *dst = p.child + (size_t)i * p.E * p.A;
+        int4 *dst = p.block(i, 0) + 1;
         for (int j = lane; j < n; j += 32) dst[j] = make_int4(0, 0, 0, 0);
         const int KD = p.A * p.D;
         float *tab = p.actions + (size_t)i * p.E * KD;
         for (int t = lane; t < KD; t += 32) tab[t] = a.sampled_actions[(size_t)i * KD + t];
     } else {
         const int *legal = p.legal + (size_t)i * p.A;
-        n = p.hdr[(size_t)i * p.E].x; // legal count was stored by forest_create
+        n = p.block(i, 0)[0].x; // legal count was stored by forest_create
         expand_children(p, i, 0, n, legal, a.logits + (size_t)i * p.A, a.noise ? a.noise + (size_t)i * p.A : nullptr,
                         a.frac, s_tmp, lane);
     }
     if (lane == 0) {
         const float rv = a.value ? a.value[i] : 0.0f;
-        p.hdr[(size_t)i * p.E] = make_int4(n, a.to_play[i], 0, __float_as_int(rv));
+        p.block(i, 0)[0] = make_int4(n, a.to_play[i], 0, __float_as_int(rv));
         p.root[i] = make_int4(1, 0, __float_as_int(a.reward[i]), 0); // visit_count += 1 (cnode.cpp:338)
     }
 }
@@ -72,20 +72,16 @@ struct BackupArgs {
     const float *reward, *value, *logits, *sampled_actions;
     const int *to_play, *is_reset;
     int *is_reset_out;
+    int n_slots;                       // slot pointers of the new node (rows its children's leaves will gather)
+    const char *new_slot[kMaxGathers];
 };
 
 // cbatch_backpropagate: CNode::expand of the leaf + cbackpropagate along the recorded path
 // (cnode.cpp:419-500; ez :482-601; gmz :605-652; sez :860-971).
 template <int VAR>
-__global__ void k_expand_backup(Pool p, BackupArgs a)
+__device__ __forceinline__ void expand_backup_tree(const Pool &p, const BackupArgs &a, int i, int lane, float *s_tmp)
 {
-    extern __shared__ float smem[];
     constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const int i = blockIdx.x * (blockDim.x >> 5) + wib;
-    if (i >= p.N) return;
-    float *s_tmp = smem + (size_t)wib * p.A;
-
     const int4 res = p.res[i];
     const int depth = res.x; // search_len >= 1
     const int e_new = a.latent_index;
@@ -101,7 +97,7 @@ __global__ void k_expand_backup(Pool p, BackupArgs a)
 
     // ---- expand the leaf as expansion e_new
     if (VAR == LZB_SEZ) {
-        int4 *dst = p.child + ((size_t)i * p.E + e_new) * p.A;
+        int4 *dst = p.block(i, e_new) + 1;
         for (int j = lane; j < p.A; j += 32) dst[j] = make_int4(0, 0, 0, 0);
         const int KD = p.A * p.D;
         float *tab = p.actions + ((size_t)i * p.E + e_new) * KD;
@@ -110,7 +106,7 @@ __global__ void k_expand_backup(Pool p, BackupArgs a)
         expand_children(p, i, e_new, p.A, nullptr, a.logits + (size_t)i * p.A, nullptr, 0.0f, s_tmp, lane);
     }
     if (lane == 0) {
-        p.hdr[(size_t)i * p.E + e_new] = make_int4(p.A, to_play, leaf_reset, __float_as_int(value));
+        p.block(i, e_new)[0] = make_int4(p.A, to_play, leaf_reset, __float_as_int(value));
         p.best[(size_t)i * p.E + e_new] = -1;
     }
 
@@ -170,7 +166,7 @@ __global__ void k_expand_backup(Pool p, BackupArgs a)
             if (q == 0) {
                 p.root[i] = make_int4(visits, __float_as_int(vsum), __float_as_int(rew), 0);
             } else {
-                int4 *rec = p.child + (size_t)i * p.E * p.A + slot;
+                int4 *rec = p.tree(i) + slot;
                 const int exp_idx = (q == depth) ? e_new : child_expansion(x);
                 *reinterpret_cast<int2 *>(rec) = make_int2(child_pack(visits, exp_idx), __float_as_int(vsum));
                 if (q == depth) reinterpret_cast<int *>(rec)[3] = __float_as_int(rew);
@@ -185,6 +181,17 @@ __global__ void k_expand_backup(Pool p, BackupArgs a)
         mm.y = fmaxf(mm.y, cmax);
         p.minmax[i] = mm;
     }
+}
+
+template <int VAR>
+__global__ void k_expand_backup(Pool p, BackupArgs a)
+{
+    extern __shared__ float smem[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int i = blockIdx.x * (blockDim.x >> 5) + wib;
+    if (blockIdx.x == 0 && threadIdx.x < a.n_slots) p.slots[(size_t)threadIdx.x * p.E + a.latent_index] = pick3(a.new_slot, threadIdx.x);
+    if (i >= p.N) return;
+    expand_backup_tree<VAR>(p, a, i, lane, smem + (size_t)wib * p.A);
 }
 
 } // namespace lzb

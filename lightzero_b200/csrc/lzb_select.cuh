@@ -7,9 +7,10 @@
 namespace lzb {
 
 struct Gather {
-    const char *src; // [E][N][row_bytes]
+    const char *src; // [E][N][row_bytes] pool, or nullptr: rows come from the slot table (Pool::slots)
     char *dst;       // [N][row_bytes]
     long long row_bytes;
+    int zero_if_reset; // LSTM state: rows of a parent that was expanded with is_reset = 1 read as zeros (mcts_ctree.py:812-816)
 };
 
 struct SelectArgs {
@@ -20,33 +21,44 @@ struct SelectArgs {
     int *ix, *iy, *search_len, *vtp;
     long long *last_action;
     float *last_action_f;
-    Gather g[3];
+    Gather g[kMaxGathers];
+    int new_e;                        // fused step: the expansion index whose slot pointers are not in the table yet, else -1
+    const char *new_slot[kMaxGathers];
 };
 
-// dst[i,:] = src[ix,i,:] with 16-byte accesses when rows allow it
-__device__ __forceinline__ void gather_rows(const SelectArgs &a, int N, int i, int ix, int lane)
+// dst[i,:] = rows of the leaf's parent (expansion ix) with 16-byte accesses when rows allow it.  The source is
+// streamed (ld.global.cs): each row is read once per simulation and must not push the node pool out of L2.
+__device__ __forceinline__ void gather_rows(const Pool &p, const SelectArgs &a, int i, int ix, int parent_reset, int lane)
 {
     for (int k = 0; k < a.ng; ++k) {
         const long long rb = a.g[k].row_bytes;
-        const char *s = a.g[k].src + ((long long)ix * N + i) * rb;
+        const char *s;
+        if (a.g[k].src) s = a.g[k].src + ((long long)ix * p.N + i) * rb;
+        else s = ((ix == a.new_e) ? pick3(a.new_slot, k) : p.slots[(size_t)k * p.E + ix]) + (long long)i * rb;
         char *d = a.g[k].dst + (long long)i * rb;
+        const bool zero = a.g[k].zero_if_reset && parent_reset == 1;
         if ((rb & 15) == 0 && ((((unsigned long long)s) | ((unsigned long long)d)) & 15ull) == 0) {
             const int4 *s4 = reinterpret_cast<const int4 *>(s);
             int4 *d4 = reinterpret_cast<int4 *>(d);
-            const long long n4 = rb >> 4;
-            for (long long t = lane; t < n4; t += 32) d4[t] = __ldg(s4 + t);
+            const int n4 = (int)(rb >> 4);
+            if (zero) {
+                for (int t = lane; t < n4; t += 32) d4[t] = make_int4(0, 0, 0, 0);
+            } else {
+#pragma unroll 4
+                for (int t = lane; t < n4; t += 32) d4[t] = __ldcs(s4 + t);
+            }
         } else {
             const int *s1 = reinterpret_cast<const int *>(s);
             int *d1 = reinterpret_cast<int *>(d);
-            const long long n1 = rb >> 2;
-            for (long long t = lane; t < n1; t += 32) d1[t] = __ldg(s1 + t);
+            const int n1 = (int)(rb >> 2);
+            for (int t = lane; t < n1; t += 32) d1[t] = zero ? 0 : __ldcs(s1 + t);
         }
     }
 }
 
 // Leaf bookkeeping common to every flavour (cnode.cpp:814-822).
 __device__ __forceinline__ void write_leaf(const Pool &p, const SelectArgs &a, int i, int e, int pos, int action,
-                                           int depth, int vtp, int lane)
+                                           int depth, int vtp, int parent_reset, int lane)
 {
     if (lane == 0) {
         p.res[i] = make_int4(depth, e, pos, vtp);
@@ -62,53 +74,57 @@ __device__ __forceinline__ void write_leaf(const Pool &p, const SelectArgs &a, i
             for (int d = lane; d < p.D; d += 32) a.last_action_f[(size_t)i * p.D + d] = act[d];
         if (a.last_action && lane == 0) a.last_action[i] = (long long)act[0]; // discrete sampled: float(index)
     }
-    gather_rows(a, p.N, i, e, lane);
+    gather_rows(p, a, i, e, parent_reset, lane);
 }
 
-// pUCT traverse: compute_mean_q + cucb_score + cselect_child per level
+__device__ __forceinline__ int4 shfl4(int4 v, int src)
+{
+    return make_int4(__shfl_sync(kFull, v.x, src), __shfl_sync(kFull, v.y, src), __shfl_sync(kFull, v.z, src),
+                     __shfl_sync(kFull, v.w, src));
+}
+
+// pUCT traverse of tree i by one warp: compute_mean_q + cucb_score + cselect_child per level
 // (mz cnode.cpp:169-203,551-596,655-699,755-824; ez :173-212,651-695,756-814,886-963; sez :483-522,973-1187).
 // s_child / s_score: warp-private shared memory, A entries each.
 template <int VAR>
-__global__ void k_select_puct(Pool p, SelectArgs a)
+__device__ __forceinline__ void select_puct_tree(const Pool &p, const SelectArgs &a, int i, int lane, int4 *s_child,
+                                                 float *s_score)
 {
-    extern __shared__ int4 smem4[];
     constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-    const int i = blockIdx.x * wpb + wib;
-    if (i >= p.N) return;
-    const int A = p.A;
-    int4 *s_child = smem4 + (size_t)wib * A;
-    float *s_score = reinterpret_cast<float *>(smem4 + (size_t)wpb * A) + (size_t)wib * A;
-
-    const int4 *tree = p.child + (size_t)i * p.E * A;
-    const int4 *hdrs = p.hdr + (size_t)i * p.E;
+    const int B = p.B;
+    const int4 *tree = p.tree(i);
     int4 *pa = p.path_a + (size_t)i * (p.S + 1);
     int2 *pb = p.path_b + (size_t)i * (p.S + 1);
+    // independent loads, issued together with the root block below
     const float2 mm = p.minmax[i];
+    const int4 rt = p.root[i];
+    int vtp = a.to_play[i];
     const int players = a.players ? a.players : ((p.scratch[0] == -1) ? 1 : 2); // cnode.cpp:776-781
     const float g = a.discount;
     const float c_base = (float)a.c_base;
     const float mm_delta = mm.y - mm.x;
 
-    int vtp = a.to_play[i];
-    const int4 rt = p.root[i];
     int parent_visits = rt.x;
     float parent_reward = __int_as_float(rt.z);
-    int e = 0, depth = 0, pos = 0, action = 0;
+    int e = 0, depth = 0, pos = 0, action = 0, parent_reset = 0;
     float parent_q = 0.0f;
     bool is_root = true;
 
     while (true) {
-        const int4 h = hdrs[e];
+        // ---- ONE dependent read per level: record `lane` of block e (header in lane 0, children after it)
+        const int4 *blk = tree + (size_t)e * B;
+        const int4 first = (lane < B) ? blk[lane] : make_int4(0, 0, 0, 0);
+        const int4 h = shfl4(first, 0);
         const int n = h.x;
-        const int parent_reset = h.z;
+        parent_reset = h.z;
         // ---- stage children, mean-Q over visited children in legal order (compute_mean_q)
         float total = 0.0f;
         int nvis = 0;
-        for (int j0 = 0; j0 < n; j0 += 32) {
-            const int j = j0 + lane;
+        for (int r0 = 0; r0 <= n; r0 += 32) {
+            const int r = r0 + lane, j = r - 1;
+            const bool valid = (r >= 1) && (r <= n);
             int4 c = make_int4(0, 0, 0, 0);
-            if (j < n) { c = tree[(size_t)e * A + j]; s_child[j] = c; }
+            if (valid) { c = (r0 == 0) ? first : blk[r]; s_child[j] = c; }
             const int vc = child_visits(c.x);
             float qsa = 0.0f;
             if (vc > 0) {
@@ -117,7 +133,7 @@ __global__ void k_select_puct(Pool p, SelectArgs a)
                 if (VP) tr = (parent_reset == 1) ? rew : rew - parent_reward;
                 qsa = tr + g * (__int_as_float(c.y) / (float)vc);
             }
-            unsigned vm = __ballot_sync(kFull, j < n && vc > 0);
+            unsigned vm = __ballot_sync(kFull, valid && vc > 0);
             while (vm) {
                 const int src = __ffs(vm) - 1;
                 vm &= vm - 1;
@@ -177,26 +193,28 @@ __global__ void k_select_puct(Pool p, SelectArgs a)
                 const int j = j0 + lane;
                 later += __popc(__ballot_sync(kFull, j < n && j > jstar && s_score[j] >= thr));
             }
-            const unsigned r = (a.rng_mode == LZB_RNG_PER_ROOT)
-                                   ? tiebreak_hash(a.seed, (unsigned)a.sim, (unsigned)(p.root_offset + i), (unsigned)depth)
-                                   : tiebreak_hash(a.seed, (unsigned)a.sim, 0u, 0u);
-            int k = (int)(r % (unsigned)(later + 1));
             pos = jstar;
-            if (k > 0) {
-                for (int j0 = 0; j0 < n; j0 += 32) {
-                    const int j = j0 + lane;
-                    const unsigned m = __ballot_sync(kFull, j < n && j > jstar && s_score[j] >= thr);
-                    const int c = __popc(m);
-                    if (k <= c) { pos = j0 + (int)__fns(m, 0, k); break; }
-                    k -= c;
+            if (later > 0) {
+                const unsigned r = (a.rng_mode == LZB_RNG_PER_ROOT)
+                                       ? tiebreak_hash(a.seed, (unsigned)a.sim, (unsigned)(p.root_offset + i), (unsigned)depth)
+                                       : tiebreak_hash(a.seed, (unsigned)a.sim, 0u, 0u);
+                int k = (int)(r % (unsigned)(later + 1));
+                if (k > 0) {
+                    for (int j0 = 0; j0 < n; j0 += 32) {
+                        const int j = j0 + lane;
+                        const unsigned m = __ballot_sync(kFull, j < n && j > jstar && s_score[j] >= thr);
+                        const int c = __popc(m);
+                        if (k <= c) { pos = j0 + (int)__fns(m, 0, k); break; }
+                        k -= c;
+                    }
                 }
             }
         }
         const int4 ch = s_child[pos];
-        action = (VAR != LZB_SEZ && e == 0) ? p.legal[(size_t)i * A + pos] : pos;
+        action = (VAR != LZB_SEZ && e == 0) ? p.legal[(size_t)i * p.A + pos] : pos;
         if (players > 1) vtp = (vtp == 1) ? 2 : 1; // cnode.cpp:797-804
         if (lane == 0) {
-            pa[depth] = make_int4(e * A + pos, ch.x, ch.y, ch.w);
+            pa[depth] = make_int4(e * B + 1 + pos, ch.x, ch.y, ch.w);
             pb[depth] = make_int2(h.y, h.z);
             p.best[(size_t)i * p.E + e] = pos;
         }
@@ -210,7 +228,19 @@ __global__ void k_select_puct(Pool p, SelectArgs a)
         is_root = false;
         e = ce;
     }
-    write_leaf(p, a, i, e, pos, action, depth, vtp, lane);
+    write_leaf(p, a, i, e, pos, action, depth, vtp, parent_reset, lane);
+}
+
+template <int VAR>
+__global__ void k_select_puct(Pool p, SelectArgs a)
+{
+    extern __shared__ int4 smem4[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const int i = blockIdx.x * wpb + wib;
+    if (i >= p.N) return;
+    int4 *s_child = smem4 + (size_t)wib * p.A;
+    float *s_score = reinterpret_cast<float *>(smem4 + (size_t)wpb * p.A) + (size_t)wib * p.A;
+    select_puct_tree<VAR>(p, a, i, lane, s_child, s_score);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -303,19 +333,11 @@ __device__ __forceinline__ int warp_first_argmax(const float *s, int n, int lane
     return best == 0x7fffffff ? 0 : best;
 }
 
-__global__ void k_select_gumbel(Pool p, SelectArgs a)
+__device__ __forceinline__ void select_gumbel_tree(const Pool &p, const SelectArgs &a, int i, int lane, int4 *s_child,
+                                                   float *s_q, float *s_p, float *s_c)
 {
-    extern __shared__ int4 smem4[];
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-    const int i = blockIdx.x * wpb + wib;
-    if (i >= p.N) return;
-    const int A = p.A;
-    int4 *s_child = smem4 + (size_t)wib * A;
-    float *fbase = reinterpret_cast<float *>(smem4 + (size_t)wpb * A) + (size_t)wib * 3 * A;
-    float *s_q = fbase, *s_p = fbase + A, *s_c = fbase + 2 * A;
-
-    const int4 *tree = p.child + (size_t)i * p.E * A;
-    const int4 *hdrs = p.hdr + (size_t)i * p.E;
+    const int B = p.B;
+    const int4 *tree = p.tree(i);
     int4 *pa = p.path_a + (size_t)i * (p.S + 1);
     int2 *pb = p.path_b + (size_t)i * (p.S + 1);
     const float g = a.discount;
@@ -323,9 +345,12 @@ __global__ void k_select_gumbel(Pool p, SelectArgs a)
     int e = 0, depth = 0, pos = 0, action = 0;
 
     while (true) {
-        const int4 h = hdrs[e];
+        const int4 *blk = tree + (size_t)e * B;
+        const int4 first = (lane < B) ? blk[lane] : make_int4(0, 0, 0, 0);
+        const int4 h = shfl4(first, 0);
         const int n = h.x;
-        for (int j = lane; j < n; j += 32) s_child[j] = tree[(size_t)e * A + j];
+        for (int r = lane; r <= n; r += 32)
+            if (r >= 1) s_child[r - 1] = (r < 32) ? first : blk[r];
         __syncwarp();
         const int vsum_i = gumbel_completed_q(s_child, s_q, s_p, s_c, n, __int_as_float(h.w), g, lane);
         if (e == 0) {
@@ -353,9 +378,9 @@ __global__ void k_select_gumbel(Pool p, SelectArgs a)
         __syncwarp();
         pos = warp_first_argmax(s_q, n, lane);
         const int4 ch = s_child[pos];
-        action = (e == 0) ? p.legal[(size_t)i * A + pos] : pos;
+        action = (e == 0) ? p.legal[(size_t)i * p.A + pos] : pos;
         if (lane == 0) {
-            pa[depth] = make_int4(e * A + pos, ch.x, ch.y, ch.w);
+            pa[depth] = make_int4(e * B + 1 + pos, ch.x, ch.y, ch.w);
             pb[depth] = make_int2(h.y, h.z);
             p.best[(size_t)i * p.E + e] = pos;
         }
@@ -365,7 +390,19 @@ __global__ void k_select_gumbel(Pool p, SelectArgs a)
         __syncwarp();
         e = ce;
     }
-    write_leaf(p, a, i, e, pos, action, depth, vtp, lane);
+    write_leaf(p, a, i, e, pos, action, depth, vtp, 0, lane);
+}
+
+__global__ void k_select_gumbel(Pool p, SelectArgs a)
+{
+    extern __shared__ int4 smem4[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const int i = blockIdx.x * wpb + wib;
+    if (i >= p.N) return;
+    const int A = p.A;
+    int4 *s_child = smem4 + (size_t)wib * A;
+    float *fbase = reinterpret_cast<float *>(smem4 + (size_t)wpb * A) + (size_t)wib * 3 * A;
+    select_gumbel_tree(p, a, i, lane, s_child, fbase, fbase + A, fbase + 2 * A);
 }
 
 } // namespace lzb

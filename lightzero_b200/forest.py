@@ -9,7 +9,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import Gather, SearchCfg, check
+from ._lib import BackpropIO, Gather, SearchCfg, Slots, TraverseIO, check
 
 VARIANT_ID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3}
 RNG_BATCH, RNG_PER_ROOT = 1, 2
@@ -81,6 +81,7 @@ class Forest:
                                            self.A, self.S, self.D, self.root_offset, _p(cnt), _p(idx),
                                            _stream(self.device)))
         self.h = h
+        self._slot_keep = {}
 
     def _legal_tensors(self, legal_actions):
         return legal_tensors(legal_actions, self.N, self.A, self.variant, self.device)
@@ -91,6 +92,7 @@ class Forest:
             self._legal = self._legal_tensors(legal_actions)
         cnt, idx = self._legal
         check(self.L.lzb_forest_reset(self.h, _p(cnt), _p(idx), _stream(self.device)))
+        self._slot_keep = {}
 
     def __del__(self):
         h = getattr(self, "h", None)
@@ -122,9 +124,7 @@ class Forest:
         return SearchCfg(int(pb_c_base), float(pb_c_init), float(discount), int(players), int(num_simulations),
                          int(max_num_considered_actions), int(rng_mode), int(rng_seed))
 
-    def traverse(self, cfg, to_play, out=None, gathers=()):
-        """One batch_traverse. ``out``: optional dict of preallocated tensors (ix, iy, last_action, last_action_f,
-        search_len, vtp); missing ones are allocated. ``gathers``: [(pool[E,N,...], dst[N,...])]."""
+    def _traverse_io(self, to_play, out, gathers):
         d = self.device
         N = self.N
         to_play = _dev(to_play, torch.int32, d)
@@ -137,20 +137,46 @@ class Forest:
         if self.variant == "sez" and "last_action_f" not in o:
             o["last_action_f"] = torch.empty((N, self.D), dtype=torch.float32, device=d)
         garr = (Gather * max(len(gathers), 1))()
-        for k, (src, dst) in enumerate(gathers):
-            if not (src.is_contiguous() and dst.is_contiguous()):
-                raise ValueError("gather tensors must be contiguous")
+        for k, g in enumerate(gathers):
+            src, dst = g[0], g[1]
+            zero = int(bool(g[2])) if len(g) > 2 else 0
+            if not dst.is_contiguous() or dst.shape[0] != N:
+                raise ValueError("gather destination must be a contiguous [N, ...] tensor")
             row = dst[0].numel() * dst.element_size()
+            if src is None:  # rows come from slot table k (set_slots / backprop(new_slots=...))
+                garr[k] = Gather(None, dst.data_ptr(), row, zero)
+                continue
+            if not src.is_contiguous():
+                raise ValueError("gather tensors must be contiguous")
             if src.shape[1] != N or src[0, 0].numel() * src.element_size() != row:
                 raise ValueError("gather pool must be [E, N, row] matching dst [N, row]")
-            garr[k] = Gather(src.data_ptr(), dst.data_ptr(), row)
-        check(self.L.lzb_traverse(self.h, C.byref(cfg), _p(to_play), _p(o["ix"]), _p(o["iy"]), _p(o["last_action"]),
-                                  _p(o.get("last_action_f")), _p(o["search_len"]), _p(o["vtp"]), garr, len(gathers),
-                                  _stream(d)))
-        return o
+            garr[k] = Gather(src.data_ptr(), dst.data_ptr(), row, zero)
+        io = TraverseIO(to_play.data_ptr(), o["ix"].data_ptr(), o["iy"].data_ptr(), o["last_action"].data_ptr(),
+                        o["last_action_f"].data_ptr() if "last_action_f" in o else None, o["search_len"].data_ptr(),
+                        o["vtp"].data_ptr(), garr, len(gathers))
+        return io, (garr, to_play), o
 
-    def backprop(self, latent_index, discount, reward, value, logits, to_play, is_reset=None, lstm_horizon_len=0,
-                 is_reset_out=None, sampled_actions=None):
+    def _slots(self, e, tensors):
+        sl = Slots()
+        sl.n = 0
+        if tensors:
+            if len(tensors) > 3:
+                raise ValueError("at most 3 slot tensors (latent, LSTM c, LSTM h)")
+            for k, t in enumerate(tensors):
+                if not (t.is_cuda and t.is_contiguous()):
+                    raise ValueError("slot tensors must be contiguous device tensors")
+                sl.ptr[k] = t.data_ptr()
+            sl.n = len(tensors)
+            self._slot_keep[e] = tuple(tensors)  # the tree reads these rows until the search ends
+        return sl
+
+    def set_slots(self, latent_index, tensors):
+        """Register the [N, row] tensors whose rows leaves below expansion ``latent_index`` gather (0 = the roots)."""
+        sl = self._slots(int(latent_index), tensors)
+        check(self.L.lzb_set_slots(self.h, int(latent_index), C.byref(sl), _stream(self.device)))
+
+    def _backprop_io(self, latent_index, discount, reward, value, logits, to_play, is_reset, lstm_horizon_len,
+                     is_reset_out, sampled_actions, new_slots):
         d = self.device
         reward = _dev(reward, torch.float32, d).reshape(-1)
         value = _dev(value, torch.float32, d).reshape(-1)
@@ -162,9 +188,32 @@ class Forest:
             raise ValueError("reward / value must have N elements")
         if logits is not None and (logits.numel() != self.N * self.A and self.variant != "sez"):
             raise ValueError("logits must be [N, A]")
-        check(self.L.lzb_backprop(self.h, int(latent_index), float(discount), _p(reward), _p(value), _p(logits),
-                                  _p(to_play), _p(is_reset), int(lstm_horizon_len), _p(is_reset_out),
-                                  _p(sampled_actions), _stream(d)))
+        io = BackpropIO(int(latent_index), float(discount), _p(reward), _p(value), _p(logits), _p(to_play), _p(is_reset),
+                        int(lstm_horizon_len), _p(is_reset_out), _p(sampled_actions), self._slots(int(latent_index), new_slots))
+        return io, (reward, value, logits, to_play, is_reset, sampled_actions)
+
+    def traverse(self, cfg, to_play, out=None, gathers=()):
+        """One batch_traverse. ``out``: optional dict of preallocated tensors (ix, iy, last_action, last_action_f,
+        search_len, vtp); missing ones are allocated. ``gathers``: [(pool[E,N,...] | None, dst[N,...][, zero_if_reset])];
+        None = rows come from the slot table with the gather's index."""
+        io, keep, o = self._traverse_io(to_play, out, gathers)
+        check(self.L.lzb_traverse(self.h, C.byref(cfg), C.byref(io), _stream(self.device)))
+        return o
+
+    def backprop(self, latent_index, discount, reward, value, logits, to_play, is_reset=None, lstm_horizon_len=0,
+                 is_reset_out=None, sampled_actions=None, new_slots=None):
+        io, keep = self._backprop_io(latent_index, discount, reward, value, logits, to_play, is_reset, lstm_horizon_len,
+                                     is_reset_out, sampled_actions, new_slots)
+        check(self.L.lzb_backprop(self.h, C.byref(io), _stream(self.device)))
+
+    def step(self, cfg, latent_index, discount, reward, value, logits, vtp, to_play, out=None, gathers=(), is_reset=None,
+             lstm_horizon_len=0, is_reset_out=None, sampled_actions=None, new_slots=None):
+        """backprop(latent_index, ..., vtp) of simulation s and traverse(to_play) of simulation s + 1 in ONE launch."""
+        bio, keep_b = self._backprop_io(latent_index, discount, reward, value, logits, vtp, is_reset, lstm_horizon_len,
+                                        is_reset_out, sampled_actions, new_slots)
+        tio, keep_t, o = self._traverse_io(to_play, out, gathers)
+        check(self.L.lzb_step(self.h, C.byref(cfg), C.byref(bio), C.byref(tio), _stream(self.device)))
+        return o
 
     def store_hidden(self, src, dst, is_reset):
         check(self.L.lzb_store_hidden(_p(src), _p(dst), _p(is_reset), self.N, src.numel() // self.N, _stream(self.device)))

@@ -83,33 +83,31 @@ class _CtreeDriver:
         return cls.tree.Roots(active_collect_env_num, legal_actions)
 
     # ------------------------------------------------------------------ pieces of the loop
-    def _latent_pool(self, forest, latent_state_roots, S):
-        """latent_state_batch_in_search_path as ONE device tensor [S+1, N, ...] (the reference keeps a Python list of
-        numpy arrays, mcts_ctree.py:247,305); slot e holds the latent of the node expanded with index e."""
-        lat0 = latent_state_roots if isinstance(latent_state_roots, torch.Tensor) else torch.as_tensor(np.asarray(latent_state_roots))
-        lat0 = lat0.to(forest.device, non_blocking=True)
-        pool = torch.empty((S + 1,) + tuple(lat0.shape), dtype=lat0.dtype, device=forest.device)
-        pool[0].copy_(lat0)
-        return pool
+    @staticmethod
+    def _on_device(forest, x):
+        """Root latents / hidden states as one contiguous device tensor (one H2D copy when they come from the host)."""
+        t = x if isinstance(x, torch.Tensor) else torch.as_tensor(np.asarray(x))
+        return t.to(forest.device, non_blocking=True).contiguous()
+
+    @staticmethod
+    def _slot_tensor(t, leaf):
+        """A model output as a slot: contiguous, and never the gather destination itself (an identity dynamics
+        network may hand its input back)."""
+        t = t.contiguous()
+        if t.data_ptr() == leaf.data_ptr():
+            t = t.clone()
+        if t.numel() != leaf.numel() or t.dtype != leaf.dtype:
+            raise ValueError("recurrent_inference returned a latent / hidden state of a different size than the roots'")
+        return t
 
     @staticmethod
     def _rows_ok(t):
-        return (t[0, 0].numel() * t.element_size()) % 4 == 0
+        return (t[0].numel() * t.element_size()) % 4 == 0
 
     def _to_play(self, to_play_batch, forest):
         # board games: the reference deep-copies the list per simulation because Cython mutates nothing here; a
         # device tensor that the kernels only read serves both env types.
         return _dev(to_play_batch, torch.int32, forest.device).reshape(-1)
-
-    def _store(self, forest, src, dst, is_reset=None):
-        """dst[i] = is_reset[i] ? 0 : src[i] for one pool slot (our copy kernel when rows are fp32, torch otherwise)."""
-        src = src.reshape(dst.shape)
-        if src.dtype == torch.float32 and dst.dtype == torch.float32 and src.is_contiguous() and dst.is_contiguous():
-            forest.store_hidden(src, dst, is_reset)
-        else:
-            dst.copy_(src)
-            if is_reset is not None:
-                dst[is_reset.bool()] = 0
 
     def _begin(self, roots, model, to_play_batch, num_simulations=0, max_considered=0):
         if hasattr(model, "eval"):
@@ -263,24 +261,46 @@ class MuZeroMCTSCtree(_CtreeDriver):
             kw = dict(num_simulations=int(cfg.num_simulations), max_considered=int(cfg.max_num_considered_actions)) if self.gumbel else {}
             forest, scfg, tp, results, S = self._begin(roots, model, to_play_batch, **kw)
             discount = cfg.discount_factor
-            pool = self._latent_pool(forest, latent_state_roots, S)
-            leaf = torch.empty_like(pool[0])
-            fused = self._rows_ok(pool)
-            bufs = None
+            lat0 = self._on_device(forest, latent_state_roots)
+            if not self._rows_ok(lat0):
+                return self._search_dense(roots, model, lat0, forest, scfg, tp, results, S)
+            # latent_state_batch_in_search_path (mcts_ctree.py:247,305) is a table of S+1 base pointers in HBM: the
+            # model's output tensor of simulation s IS slot s+1, nothing is copied into a pool.
+            forest.set_slots(0, [lat0])
+            leaf = torch.empty_like(lat0)
+            gathers = [(None, leaf)]
+            # stage 1 of simulation 0: selection + gather of each leaf's parent latent (mcts_ctree.py:272-289)
+            o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers)
             for simulation_index in range(S):
-                # stage 1: selection + (fused) gather of each leaf's parent latent (mcts_ctree.py:272-289)
-                o = api.traverse_tensors(roots, scfg, tp, results, gathers=[(pool, leaf)] if fused else (), out=bufs)
-                bufs = o
-                if not fused:
-                    leaf = pool[o["ix"].long(), o["iy"].long()]
                 # stage 2: expansion inputs from the model, still on the device (mcts_ctree.py:298-303);
                 # Gumbel MuZero passes the action as [N, 1] (:1090)
                 net = model.recurrent_inference(leaf, o["last_action"].unsqueeze(1) if self.gumbel else o["last_action"])
                 value = self.inverse_scalar_transform_handle(net.value)
                 reward = self.inverse_scalar_transform_handle(net.reward)
-                self._store(forest, net.latent_state, pool[simulation_index + 1])
-                # stage 3: expand + backup (mcts_ctree.py:316-321)
-                api.backprop_tensors(results, simulation_index + 1, discount, reward, value, net.policy_logits, o["vtp"])
+                new_lat = self._slot_tensor(net.latent_state, leaf)
+                e = simulation_index + 1
+                if e < S:
+                    # stage 3 (expand + backup, :316-321) fused with stage 1 of the next simulation: one launch
+                    o = forest.step(scfg, e, discount, reward, value, net.policy_logits, o["vtp"], tp, out=o,
+                                    gathers=gathers, new_slots=[new_lat])
+                else:
+                    forest.backprop(e, discount, reward, value, net.policy_logits, o["vtp"], new_slots=[new_lat])
+                forest.sims_done += 1
+
+    def _search_dense(self, roots, model, lat0, forest, scfg, tp, results, S):
+        """Fallback for latent rows that are not a multiple of 4 bytes (e.g. odd-sized fp16): dense pool + torch gather."""
+        discount = self._cfg.discount_factor
+        pool = torch.empty((S + 1,) + tuple(lat0.shape), dtype=lat0.dtype, device=forest.device)
+        pool[0].copy_(lat0)
+        o = None
+        for simulation_index in range(S):
+            o = api.traverse_tensors(roots, scfg, tp, results, out=o)
+            leaf = pool[o["ix"].long(), o["iy"].long()]
+            net = model.recurrent_inference(leaf, o["last_action"].unsqueeze(1) if self.gumbel else o["last_action"])
+            value = self.inverse_scalar_transform_handle(net.value)
+            reward = self.inverse_scalar_transform_handle(net.reward)
+            pool[simulation_index + 1].copy_(net.latent_state.reshape(lat0.shape))
+            api.backprop_tensors(results, simulation_index + 1, discount, reward, value, net.policy_logits, o["vtp"])
 
 
 class GumbelMuZeroMCTSCtree(MuZeroMCTSCtree):
@@ -312,32 +332,37 @@ class EfficientZeroMCTSCtree(_CtreeDriver):
             discount, horizon = self._cfg.discount_factor, int(self._cfg.lstm_horizon_len)
             assert horizon > 0
             N = roots.num
-            pool = self._latent_pool(forest, latent_state_roots, S)
-            # reward_hidden_state_{c,h}_batch: [S+1, N, H] (the reference keeps lists of [1, N, H] arrays, :727-728)
-            c_pool = self._latent_pool(forest, _as_tensor(hidden_roots[0]).reshape(N, -1), S)
-            h_pool = self._latent_pool(forest, _as_tensor(hidden_roots[1]).reshape(N, -1), S)
-            leaf = torch.empty_like(pool[0])
-            leaf_c, leaf_h = torch.empty_like(c_pool[0]), torch.empty_like(h_pool[0])
-            is_reset = torch.empty(N, dtype=torch.int32, device=forest.device)
-            gathers = [(pool, leaf), (c_pool, leaf_c), (h_pool, leaf_h)]
-            if not all(self._rows_ok(p) for p, _ in gathers):
+            lat0 = self._on_device(forest, latent_state_roots)
+            # reward_hidden_state_{c,h}_batch (:727-728): [1, N, H] arrays, one per expanded generation -> slot tables 1, 2
+            c0 = self._on_device(forest, hidden_roots[0]).reshape(N, -1)
+            h0 = self._on_device(forest, hidden_roots[1]).reshape(N, -1)
+            if not all(self._rows_ok(t) for t in (lat0, c0, h0)):
                 raise ValueError("latent / hidden-state rows must be a multiple of 4 bytes")
-            bufs = None
+            forest.set_slots(0, [lat0, c0, h0])
+            leaf, leaf_c, leaf_h = torch.empty_like(lat0), torch.empty_like(c0), torch.empty_like(h0)
+            is_reset = torch.empty(N, dtype=torch.int32, device=forest.device)
+            # the LSTM state of a node expanded with is_reset = 1 reads as zeros (mcts_ctree.py:809-816): the gather
+            # applies the reset from the node's flag instead of rewriting the model's output tensor
+            gathers = [(None, leaf), (None, leaf_c, True), (None, leaf_h, True)]
+            o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers)
             for simulation_index in range(S):
-                o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers, out=bufs)
-                bufs = o
                 net = model.recurrent_inference(leaf, (leaf_c.unsqueeze(0), leaf_h.unsqueeze(0)), self._leaf_action(roots, o))
                 value = self.inverse_scalar_transform_handle(net.value)
                 value_prefix = self.inverse_scalar_transform_handle(net.value_prefix)
-                self._store(forest, net.latent_state, pool[simulation_index + 1])
-                # is_reset = (search_len % lstm_horizon_len == 0) is computed by the kernel (mcts_ctree.py:809-814) ...
-                e = self._expand_inputs(roots, net)
-                api.backprop_tensors(results, simulation_index + 1, discount, value_prefix, value, e.get("logits"),
-                                     o["vtp"], lstm_horizon_len=horizon, is_reset_out=is_reset,
-                                     sampled_actions=e.get("sampled_actions"))
-                # ... and applied to the LSTM state as it enters the pool (:812-816)
-                self._store(forest, net.reward_hidden_state[0], c_pool[simulation_index + 1], is_reset)
-                self._store(forest, net.reward_hidden_state[1], h_pool[simulation_index + 1], is_reset)
+                slots = [self._slot_tensor(net.latent_state, leaf),
+                         self._slot_tensor(net.reward_hidden_state[0].reshape(N, -1), leaf_c),
+                         self._slot_tensor(net.reward_hidden_state[1].reshape(N, -1), leaf_h)]
+                x = self._expand_inputs(roots, net)
+                e = simulation_index + 1
+                # is_reset = (search_len % lstm_horizon_len == 0) is computed by the kernel (mcts_ctree.py:809-814)
+                kw = dict(lstm_horizon_len=horizon, is_reset_out=is_reset, sampled_actions=x.get("sampled_actions"),
+                          new_slots=slots)
+                if e < S:
+                    o = forest.step(scfg, e, discount, value_prefix, value, x.get("logits"), o["vtp"], tp, out=o,
+                                    gathers=gathers, **kw)
+                else:
+                    forest.backprop(e, discount, value_prefix, value, x.get("logits"), o["vtp"], **kw)
+                forest.sims_done += 1
 
 
 def _as_tensor(x):

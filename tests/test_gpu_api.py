@@ -1,0 +1,239 @@
+"""GPU: the reference-shaped public API (Roots / MinMaxStatsList / ResultsWrapper / batch_traverse /
+batch_backpropagate modules and the XMCTSCtree.search drivers) against the CPU oracle, plus the shape / legality
+checks the reference's own tests make (lzero/mcts/tests/test_mcts_ctree.py:155-179,240-281, test_mcts_sampled_ctree.py)."""
+import numpy as np
+import pytest
+
+from tests.common import PB_C_BASE, PB_C_INIT, TICTACTOE_MASKS, Scenario, assert_same, run_cpu
+
+pytestmark = pytest.mark.gpu
+SEED = 2024
+
+
+class Out:
+    pass
+
+
+class ScenarioModel:
+    """model.recurrent_inference over a Scenario's per-simulation tables (device tensors)."""
+
+    def __init__(self, sc, dev, latent_dim=16, hidden=0):
+        import torch
+        self.t = lambda a: torch.as_tensor(a).to(dev)
+        self.sc, self.s, self.dev, self.L, self.H = sc, 0, dev, latent_dim, hidden
+        self.calls = []
+
+    def eval(self):
+        self.s = 0
+
+    def recurrent_inference(self, latent, *rest):
+        import torch
+        sc, s = self.sc, self.s
+        self.s += 1
+        self.calls.append((latent.clone(), rest))
+        o = Out()
+        o.latent_state = torch.full((sc.n, self.L), float(s + 1), device=self.dev)
+        o.policy_logits = self.t(sc.logits[s])
+        o.value = self.t(sc.value[s]).unsqueeze(1)
+        o.reward = o.value_prefix = self.t(sc.reward[s]).unsqueeze(1)
+        if self.H:
+            o.reward_hidden_state = (torch.full((1, sc.n, self.H), float(s + 1), device=self.dev),
+                                     torch.full((1, sc.n, self.H), -float(s + 1), device=self.dev))
+        return o
+
+
+def driver_cfg(sc, **extra):
+    cfg = dict(num_simulations=sc.S, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=sc.discount,
+               value_delta_max=0.01, device="cuda", tie_break_seed=SEED, lstm_horizon_len=5,
+               max_num_considered_actions=sc.m, model=dict(support_scale=300, categorical_distribution=False))
+    cfg.update(extra)
+    return cfg
+
+
+def identity(mcts):
+    mcts.inverse_scalar_transform_handle = lambda x: x
+    return mcts
+
+
+def oracle_run(sc):
+    from oracle.binding import OracleForest
+    orc = OracleForest(sc.variant, sc.n, sc.A, sc.legal, K=sc.K, D=sc.D)
+    rec = []
+    run_cpu(orc, sc, 2, SEED, record=rec)
+    return orc, rec
+
+
+def check_roots(roots, orc, sc):
+    dist, ln = orc.distributions()
+    got = roots.get_distributions()
+    assert [len(r) for r in got] == ln.tolist()
+    for i, r in enumerate(got):
+        assert r == dist[i, :ln[i]].tolist(), "root %d visit counts" % i
+        assert sum(r) == sc.S
+    assert_same(np.asarray(roots.get_values(), np.float32), orc.values(), "root values")
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_muzero_driver_matches_oracle(graph):
+    import torch
+    import lightzero_b200 as lzb
+    legal = [[a for a, x in enumerate(r) if x == 1] for r in TICTACTOE_MASKS]
+    sc = Scenario("mz", 16, 9, 30, seed=41, legal=legal)
+    orc, rec = oracle_run(sc)
+    mcts = identity(lzb.MuZeroMCTSCtree(driver_cfg(sc, cuda_graph=graph)))
+    model = ScenarioModel(sc, torch.device("cuda"))
+    for rep in range(2 if graph else 1):  # second search of a shape replays the captured graph
+        roots = lzb.MuZeroMCTSCtree.roots(sc.n, sc.legal)
+        roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_logits.tolist(), sc.to_play.tolist())
+        mcts.search(roots, model, np.zeros((sc.n, 16), np.float32), sc.to_play.tolist())
+        check_roots(roots, orc, sc)
+    if not graph:  # every model call received the parent latents of the oracle's leaves: slot e is filled with e
+        for s, (lat, rest) in enumerate(model.calls):
+            assert_same(lat[:, 0].cpu().numpy(), rec[s]["ix"].astype(np.float32), "sim %d gathered latents" % s)
+            assert_same(rest[0].cpu().numpy().astype(np.int32), rec[s]["last_action"], "sim %d last actions" % s)
+            assert rest[0].dtype == torch.int64
+
+
+def test_muzero_two_player_board_game_driver():
+    import torch
+    import lightzero_b200 as lzb
+    sc = Scenario("mz", 8, 9, 25, seed=42, to_play=[1, 2] * 4, discount=1.0)
+    orc, _ = oracle_run(sc)
+    mcts = identity(lzb.MuZeroMCTSCtree(driver_cfg(sc, env_type="board_games")))
+    roots = lzb.MuZeroMCTSCtree.roots(sc.n, sc.legal)
+    roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_logits.tolist(), sc.to_play.tolist())
+    tp = sc.to_play.tolist()
+    mcts.search(roots, ScenarioModel(sc, torch.device("cuda")), np.zeros((sc.n, 4, 2, 2), np.float32), tp)
+    assert tp == sc.to_play.tolist()  # the caller's list is not mutated
+    check_roots(roots, orc, sc)
+
+
+def test_efficientzero_driver_matches_oracle_and_resets_hidden_state():
+    import torch
+    import lightzero_b200 as lzb
+    sc = Scenario("ez", 32, 6, 40, seed=43)
+    orc, rec = oracle_run(sc)
+    mcts = identity(lzb.EfficientZeroMCTSCtree(driver_cfg(sc)))
+    model = ScenarioModel(sc, torch.device("cuda"), hidden=8)
+    roots = lzb.EfficientZeroMCTSCtree.roots(sc.n, sc.legal)
+    roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_logits.tolist(), sc.to_play.tolist())
+    hidden = (np.full((1, sc.n, 8), 0.5, np.float32), np.full((1, sc.n, 8), -0.5, np.float32))
+    mcts.search(roots, model, np.zeros((sc.n, 16), np.float32), hidden, sc.to_play.tolist())
+    check_roots(roots, orc, sc)
+    # hidden state handed to the model: the parent's (c, h), zeroed when the parent was expanded on a horizon boundary
+    reset = {0: np.zeros(sc.n, bool)}
+    for s in range(sc.S):
+        reset[s + 1] = rec[s]["is_reset"].astype(bool)
+    for s, (lat, rest) in enumerate(model.calls):
+        (c, h), act = rest
+        ix = rec[s]["ix"]
+        par_reset = np.array([reset[int(e)][i] for i, e in enumerate(ix)])
+        want_c = np.where(ix == 0, 0.5, ix.astype(np.float32))
+        want_c = np.where(par_reset, 0.0, want_c).astype(np.float32)
+        assert c.shape == (1, sc.n, 8) and h.shape == (1, sc.n, 8)
+        assert_same(c[0, :, 0].cpu().numpy(), want_c, "sim %d LSTM c" % s)
+        assert_same(h[0, :, 3].cpu().numpy(), -want_c, "sim %d LSTM h" % s)
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_gumbel_driver_matches_oracle(graph):
+    import torch
+    import lightzero_b200 as lzb
+    legal = [[a for a, x in enumerate(r) if x == 1] for r in TICTACTOE_MASKS]
+    sc = Scenario("gmz", 16, 9, 30, seed=44, legal=legal, discount=1.0, max_considered=3)
+    orc, _ = oracle_run(sc)
+    mcts = identity(lzb.GumbelMuZeroMCTSCtree(driver_cfg(sc, cuda_graph=graph)))
+    model = ScenarioModel(sc, torch.device("cuda"))
+    for rep in range(2 if graph else 1):
+        roots = lzb.GumbelMuZeroMCTSCtree.roots(sc.n, sc.legal)
+        roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_value.tolist(),
+                      sc.root_logits.tolist(), sc.to_play.tolist())
+        mcts.search(roots, model, np.zeros((sc.n, 16), np.float32), sc.to_play.tolist())
+        check_roots(roots, orc, sc)
+        p, v = orc.gumbel_outputs(sc.discount)
+        assert_same(np.asarray(roots.get_policies(sc.discount, sc.A), np.float32), p, "improved policies")
+        assert_same(np.asarray(roots.get_children_values(sc.discount, sc.A), np.float32), v, "children values")
+    if not graph:
+        assert model.calls[0][1][0].shape == (sc.n, 1)  # Gumbel passes actions as [N, 1] (mcts_ctree.py:1090)
+
+
+def test_list_api_module_level_calls_match_oracle():
+    """The tree modules driven exactly like the reference loop drives the Cython ones (Python lists in and out)."""
+    from lightzero_b200.ctree.ctree_muzero import mz_tree
+    sc = Scenario("mz", 8, 6, 20, seed=45)
+    orc, rec = oracle_run(sc)
+    mz_tree.set_tie_break(SEED)
+    roots = mz_tree.Roots(sc.n, sc.legal)
+    roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_logits.tolist(), sc.to_play.tolist())
+    mm = mz_tree.MinMaxStatsList(sc.n)
+    mm.set_delta(0.01)
+    for s in range(sc.S):
+        results = mz_tree.ResultsWrapper(sc.n)
+        ix, iy, last_actions, vtp = mz_tree.batch_traverse(roots, PB_C_BASE, PB_C_INIT, sc.discount, mm, results, sc.to_play.tolist())
+        assert isinstance(ix, list) and isinstance(last_actions[0], int)
+        assert ix == rec[s]["ix"].tolist() and iy == list(range(sc.n)) and last_actions == rec[s]["last_action"].tolist()
+        assert results.get_search_len() == rec[s]["search_len"].tolist()
+        mz_tree.batch_backpropagate(s + 1, sc.discount, sc.reward[s].tolist(), sc.value[s].tolist(), sc.logits[s].tolist(),
+                                    mm, results, vtp)
+    check_roots(roots, orc, sc)
+    traj = roots.get_trajectories()
+    assert len(traj) == sc.n and all(len(t) >= 1 for t in traj)
+    roots.clear()
+    assert roots.get_distributions() == []
+
+
+def test_reference_unit_test_shapes_with_zero_model():
+    """test_mcts_ctree.py:155-179,240-281: all-zero fake model, 16 x 9 mask; output shapes, per-root distribution
+    length == legal count, and argmax action is legal."""
+    import torch
+    import lightzero_b200 as lzb
+    legal = [[a for a, x in enumerate(r) if x == 1] for r in TICTACTOE_MASKS]
+    sc = Scenario("mz", 16, 9, 50, seed=46, legal=legal, zero_model=True)
+    mcts = identity(lzb.MuZeroMCTSCtree(driver_cfg(sc)))
+    roots = lzb.MuZeroMCTSCtree.roots(16, legal)
+    noises = [np.random.dirichlet([0.3] * len(l)).astype(np.float32).tolist() for l in legal]
+    roots.prepare(0.25, noises, [0.0] * 16, np.zeros((16, 9), np.float32).tolist(), [-1] * 16)
+    mcts.search(roots, ScenarioModel(sc, torch.device("cuda")), np.zeros((16, 8), np.float32), [-1] * 16)
+    dist, vals = roots.get_distributions(), roots.get_values()
+    assert len(dist) == 16 and len(vals) == 16 and all(v == 0.0 for v in vals)
+    for i, d in enumerate(dist):
+        assert len(d) == len(legal[i]) and sum(d) == 50
+        assert legal[i][int(np.argmax(d))] in legal[i]
+
+
+def test_sampled_driver_continuous_shapes():
+    """test_mcts_sampled_ctree.py:61-135: continuous K=6, D=2, 5 roots; distributions are (5, 6)."""
+    import torch
+    import lightzero_b200 as lzb
+    n, K, D, S = 5, 6, 2, 40
+    dev = torch.device("cuda")
+
+    class Model:
+        def eval(self):
+            pass
+
+        def recurrent_inference(self, latent, hidden, actions):
+            assert actions.shape == (n, D) and actions.dtype == torch.float32 and float(actions.abs().max()) <= 1.0
+            o = Out()
+            o.latent_state = latent + 1
+            o.policy_logits = torch.cat([torch.zeros(n, D, device=dev), torch.ones(n, D, device=dev)], 1)
+            o.value = torch.full((n, 1), 0.1, device=dev)
+            o.value_prefix = torch.full((n, 1), 0.05, device=dev)
+            o.reward_hidden_state = (hidden[0] + 1, hidden[1] + 1)
+            return o
+
+    cfg = dict(num_simulations=S, discount_factor=0.997, value_delta_max=0.01, device="cuda", lstm_horizon_len=5,
+               model=dict(support_scale=300, categorical_distribution=False, continuous_action_space=True,
+                          num_of_sampled_actions=K, action_space_size=D))
+    mcts = identity(lzb.SampledEfficientZeroMCTSCtree(cfg))
+    legal = [[-1] * K for _ in range(n)]
+    roots = lzb.SampledEfficientZeroMCTSCtree.roots(n, legal, D, K, True)
+    logits = np.concatenate([np.zeros((n, D)), np.ones((n, D))], 1).astype(np.float32)
+    roots.prepare(0.25, [np.random.dirichlet([0.3] * K).tolist() for _ in range(n)], [0.0] * n, logits.tolist(), [-1] * n)
+    hidden = (np.zeros((1, n, 4), np.float32), np.zeros((1, n, 4), np.float32))
+    mcts.search(roots, Model(), np.zeros((n, 3), np.float32), hidden, [-1] * n)
+    dist = np.asarray(roots.get_distributions())
+    assert dist.shape == (n, K) and (dist.sum(1) == S).all()
+    acts = np.asarray(roots.get_sampled_actions())
+    assert acts.shape == (n, K, D) and np.abs(acts).max() < 1.0
+    assert len(roots.get_values()) == n

@@ -12,7 +12,9 @@ from tests.common import PB_C_BASE, PB_C_INIT, TICTACTOE_MASKS, Scenario, assert
 pytestmark = pytest.mark.gpu
 
 
-def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0):
+def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=False):
+    """fused=False: lzb_traverse + lzb_backprop per simulation; fused=True: lzb_step (backprop s + traverse s+1 in one
+    launch), with the leaf rows gathered through the slot tables."""
     import torch
     from lightzero_b200.forest import Forest
     f = Forest(sc.variant, sc.n, sc.K if sc.variant == "sez" else sc.A, sc.S, legal_actions=sc.legal, action_dim=sc.D,
@@ -29,32 +31,65 @@ def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0):
     cfg = f.make_cfg(PB_C_BASE, PB_C_INIT, sc.discount, players=players, num_simulations=sc.S,
                      max_num_considered_actions=sc.m, rng_mode=rng_mode, rng_seed=seed)
     tp = t(sc.to_play)
-    for s in range(sc.S):
-        o = f.traverse(cfg, tp)
-        m = sc.model_fn(s, None, None, None)
-        kw = {}
-        if sc.variant in ("ez", "sez"):
-            kw["lstm_horizon_len"] = horizon
-            kw["is_reset_out"] = torch.empty(sc.n, dtype=torch.int32, device=dev)
-        if sc.variant == "sez":
-            kw["sampled_actions"] = t(m["sampled_actions"])
+    vp = sc.variant in ("ez", "sez")
+    # rows to gather: slot e holds rows filled with the value e (+ i / 1024), so a gathered row names its source
+    L = 12
+    rows = [(torch.arange(sc.n, device=dev).float().unsqueeze(1) / 1024 + e).expand(sc.n, L).contiguous() for e in range(sc.S + 1)]
+    leaf, leaf_z = torch.empty(sc.n, L, device=dev), torch.empty(sc.n, L, device=dev)
+    gathers = [(None, leaf), (None, leaf_z, True)] if fused else ()
+    if fused:
+        f.set_slots(0, [rows[0], rows[0]])
+    is_reset_out = torch.empty(sc.n, dtype=torch.int32, device=dev) if vp else None
+    reset_of = torch.zeros(sc.S + 1, sc.n, dtype=torch.int32, device=dev)
+
+    def note(o, s):
+        if fused:  # the gather delivered the parent's row; reset parents read as zeros through a zero_if_reset gather
+            ix = o["ix"].long()
+            want = ix.float().unsqueeze(1) + torch.arange(sc.n, device=dev).float().unsqueeze(1) / 1024
+            assert torch.equal(leaf, want.expand(sc.n, L)), "sim %d: slot gather delivered the wrong rows" % s
+            par_reset = reset_of[ix, torch.arange(sc.n, device=dev)].bool().unsqueeze(1)
+            assert torch.equal(leaf_z, torch.where(par_reset, torch.zeros_like(leaf), leaf)), "sim %d: zero_if_reset" % s
         if record is not None:
             rec = {k: v.cpu().numpy() for k, v in o.items()}
             rec["paths"] = f.dump_paths(sc.S + 1)
             record.append(rec)
-        f.backprop(s + 1, sc.discount, t(m["reward"]), t(m["value"]), t(m["logits"]), o["vtp"], **kw)
-        if record is not None and "is_reset_out" in kw:
-            record[-1]["is_reset"] = kw["is_reset_out"].cpu().numpy()
+
+    o = f.traverse(cfg, tp, gathers=gathers)
+    note(o, 0)
+    for s in range(sc.S):
+        m = sc.model_fn(s, None, None, None)
+        kw = {}
+        if vp:
+            kw["lstm_horizon_len"] = horizon
+            kw["is_reset_out"] = is_reset_out
+        if sc.variant == "sez":
+            kw["sampled_actions"] = t(m["sampled_actions"])
+        if fused:
+            kw["new_slots"] = [rows[s + 1], rows[s + 1]]
+        args = (s + 1, sc.discount, t(m["reward"]), t(m["value"]), t(m["logits"]), o["vtp"])
+        last = s + 1 == sc.S
+        if fused and not last:
+            o = f.step(cfg, *args, tp, out=o, gathers=gathers, **kw)
+        else:
+            f.backprop(*args, **kw)
+        if vp:
+            reset_of[s + 1] = is_reset_out
+            if record is not None:
+                record[-1]["is_reset"] = is_reset_out.cpu().numpy()
+        if not last:
+            if not fused:
+                o = f.traverse(cfg, tp, out=o)
+            note(o, s + 1)
     torch.cuda.synchronize()
     return f
 
 
-def compare(sc, rng_mode=2, seed=2024, trees=4):
+def compare(sc, rng_mode=2, seed=2024, trees=4, fused=False):
     from oracle.binding import OracleForest
     orc = OracleForest(sc.variant, sc.n, sc.A, sc.legal, K=sc.K, D=sc.D)
     rec_c, rec_g = [], []
     run_cpu(orc, sc, rng_mode, seed, record=rec_c)
-    gpu = run_gpu(sc, rng_mode, seed, record=rec_g)
+    gpu = run_gpu(sc, rng_mode, seed, record=rec_g, fused=fused)
     for s, (c, g) in enumerate(zip(rec_c, rec_g)):
         for k in ("search_len", "ix", "iy", "vtp", "paths"):
             assert_same(g[k], c[k], "sim %d %s" % (s, k))
@@ -182,6 +217,45 @@ def test_gumbel_m16_a18():
 
 def test_sampled_continuous_halfcheetah_shape():  # C3: K=20, D=6, 50 sims
     compare(Scenario("sez", 8, 12, 50, seed=14, K=20, D=6))
+
+
+FUSED_CASES = {
+    "mz_a18": lambda: Scenario("mz", 256, 18, 50, seed=21),
+    "mz_cartpole": lambda: Scenario("mz", 8, 2, 25, seed=22),
+    "mz_masks": lambda: Scenario("mz", 16, 9, 50, seed=23, legal=[[a for a, x in enumerate(r) if x == 1] for r in TICTACTOE_MASKS]),
+    "mz_two_player": lambda: Scenario("mz", 32, 9, 25, seed=24, to_play=[1, 2] * 16, discount=1.0),
+    "mz_wide": lambda: Scenario("mz", 16, 80, 40, seed=25),
+    "ez_pong": lambda: Scenario("ez", 64, 6, 50, seed=26),
+    "ez_two_player": lambda: Scenario("ez", 32, 9, 25, seed=27, to_play=[2, 1] * 16, discount=1.0),
+    "gmz_gomoku": lambda: Scenario("gmz", 32, 36, 50, seed=28, discount=1.0, max_considered=6),
+    "sez_halfcheetah": lambda: Scenario("sez", 8, 12, 50, seed=29, K=20, D=6),
+}
+
+
+@pytest.mark.parametrize("name", sorted(FUSED_CASES))
+def test_fused_step_matches_oracle(name):
+    """lzb_step (expand + backup of simulation s and selection + slot gather of s + 1 in one launch)."""
+    compare(FUSED_CASES[name](), fused=True)
+
+
+def test_fused_step_deep_paths():
+    sc = Scenario("mz", 8, 2, 120, seed=30, reward_scale=0.0)
+    sc.value[:] = 0.0
+    sc.root_logits[:] = 0.0
+    sc.logits[:] = np.array([8.0, -8.0], np.float32)
+    compare(sc, fused=True)
+
+
+def test_trajectories_follow_best_actions():
+    sc = Scenario("mz", 16, 6, 30, seed=31)
+    rec = []
+    gpu = run_gpu(sc, 2, 5, record=rec)
+    acts, ln = gpu.trajectories()
+    acts, ln = acts.cpu().numpy(), ln.cpu().numpy()
+    last = rec[-1]
+    for i in range(sc.n):  # the most recent traverse wrote best_action along its whole path
+        d = int(last["search_len"][i])
+        assert ln[i] >= d and (acts[i, :d] == last["paths"][i, :d]).all()
 
 
 def test_root_offset_keys_the_tiebreak_stream():
