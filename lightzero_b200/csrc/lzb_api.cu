@@ -2,11 +2,13 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo -O3 -std=c++17 --shared ...
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <random>
 #include <vector>
 
 #include "../../include/lzb200.h"
+#include "lzb_group.cuh"
 #include "lzb_step.cuh"
 
 using namespace lzb;
@@ -467,6 +469,45 @@ int fill_backup(lzb_forest_t *f, const lzb_backprop_io_t *io, BackupArgs &b)
 // dynamic shared memory per warp: selection stages A child records + A scores (Gumbel: 3 A-vectors), backup A floats
 size_t select_bytes_per_warp(const Pool &p) { return (size_t)p.A * (p.variant == LZB_GMZ ? 28 : 20); }
 
+// Lane-group kernels (lzb_group.cuh): G lanes per tree, R child records per lane, chosen from the action space size.
+enum { kSelect = 0, kBackup = 1, kStep = 2 };
+
+template <int VAR, int G, int R>
+void launch_group(int which, const Pool &p, const BackupArgs *b, const SelectArgs *a, cudaStream_t st)
+{
+    const int per_block = 128 / G;
+    const dim3 grid((p.N + per_block - 1) / per_block), block(128);
+    if (which == kSelect) k_select_g<VAR, G, R><<<grid, block, 0, st>>>(p, *a);
+    else if (which == kBackup) k_expand_backup_g<VAR, G, R><<<grid, block, 0, st>>>(p, *b);
+    else k_step_g<VAR, G, R><<<grid, block, 0, st>>>(p, *b, *a);
+}
+
+template <int VAR>
+bool launch_group_for(int which, const Pool &p, const BackupArgs *b, const SelectArgs *a, cudaStream_t st)
+{
+    const int A = p.A;
+    if (A <= 8) launch_group<VAR, 8, 1>(which, p, b, a, st);
+    else if (A <= 16) launch_group<VAR, 8, 2>(which, p, b, a, st);
+    else if (A <= 24) launch_group<VAR, 8, 3>(which, p, b, a, st);
+    else if (A <= 32) launch_group<VAR, 16, 2>(which, p, b, a, st);
+    else if (A <= 64) launch_group<VAR, 32, 2>(which, p, b, a, st);
+    else if (A <= 128) launch_group<VAR, 32, 4>(which, p, b, a, st);
+    else return false; // wider action spaces: warp-per-tree kernels with shared-memory staging
+    return true;
+}
+
+// true when a lane-group kernel was launched for this forest's flavour / width
+bool launch_grouped(int which, const Pool &p, const BackupArgs *b, const SelectArgs *a, cudaStream_t st)
+{
+    if (getenv("LZB_FORCE_WARP_PER_TREE")) return false; // test hook: exercise the generic kernels on small A
+    switch (p.variant) {
+    case LZB_MZ: return launch_group_for<LZB_MZ>(which, p, b, a, st);
+    case LZB_EZ: return launch_group_for<LZB_EZ>(which, p, b, a, st);
+    case LZB_SEZ: return launch_group_for<LZB_SEZ>(which, p, b, a, st);
+    default: return false; // Gumbel MuZero keeps its shared-memory selection
+    }
+}
+
 } // namespace
 
 extern "C" {
@@ -490,6 +531,11 @@ int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_travers
     const Pool &p = f->pool;
     dim3 grid, block; size_t smem;
     const size_t bpw = select_bytes_per_warp(p);
+    if (launch_grouped(kSelect, p, nullptr, &a, st)) {
+        LZB_CUDA(cudaGetLastError());
+        f->sim += 1;
+        return LZB_OK;
+    }
     switch (p.variant) {
     case LZB_GMZ:
         if (int rc = launch_cfg(k_select_gumbel, bpw, p.N, grid, block, smem)) return rc;
@@ -521,6 +567,11 @@ int lzb_backprop(lzb_forest_t *f, const lzb_backprop_io_t *io, void *stream)
     dim3 grid, block; size_t smem;
     cudaStream_t st = (cudaStream_t)stream;
     const size_t bpw = (size_t)p.A * sizeof(float);
+    if (launch_grouped(kBackup, p, &a, nullptr, st)) {
+        LZB_CUDA(cudaGetLastError());
+        if (io->latent_index > f->expanded) f->expanded = io->latent_index;
+        return LZB_OK;
+    }
     switch (p.variant) {
     case LZB_MZ:
         if (int rc = launch_cfg(k_expand_backup<LZB_MZ>, bpw, p.N, grid, block, smem)) return rc;
@@ -559,6 +610,12 @@ int lzb_step(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_backprop_io
     const Pool &p = f->pool;
     dim3 grid, block; size_t smem;
     const size_t bpw = select_bytes_per_warp(p);
+    if (launch_grouped(kStep, p, &b, &a, st)) {
+        LZB_CUDA(cudaGetLastError());
+        if (bio->latent_index > f->expanded) f->expanded = bio->latent_index;
+        f->sim += 1;
+        return LZB_OK;
+    }
     switch (p.variant) {
     case LZB_MZ:
         if (int rc = launch_cfg(k_step<LZB_MZ>, bpw, p.N, grid, block, smem)) return rc;

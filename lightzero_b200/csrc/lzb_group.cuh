@@ -1,0 +1,419 @@
+// Lane-group kernels: G lanes (8, 16 or 32) cooperate on one tree, so a warp walks 32/G trees at once.
+//
+// The tree work is a few hundred dependent scalar operations per level on at most A child records; with one
+// whole warp per tree (lzb_select.cuh) most issue slots carry 18 of 32 lanes through shuffles and reductions
+// and the kernel is instruction-issue bound (ncu: issue active 42 %, 1.8 k warp-instructions per tree-step).
+// Here lane k of a group keeps children j = k + G*r, r < R, in registers (no shared memory), every loop over
+// children is unrolled at compile time, and group-wide exchanges use shuffles of width G under the group's
+// member mask, so the 32/G trees of a warp share every instruction while staying free to diverge in depth.
+//
+// Arithmetic is identical to the warp-per-tree kernels (and hence to the reference): fp32, no FMA contraction,
+// serial left-to-right sums in legal-action order (adding +0.0f for skipped entries is exact because a running
+// sum that starts at +0.0f can never become -0.0f), glibc-exact expf / logf.
+#pragma once
+#include "lzb_expand.cuh"
+#include "lzb_select.cuh"
+
+namespace lzb {
+
+template <int G>
+struct Grp {
+    int lane;      // 0 .. G-1 within the group
+    int shift;     // first warp lane of the group
+    unsigned mask; // member mask of the group inside its warp
+    __device__ __forceinline__ Grp()
+    {
+        const int wl = threadIdx.x & 31;
+        lane = wl & (G - 1);
+        shift = wl - lane;
+        mask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << shift);
+    }
+    __device__ __forceinline__ unsigned ballot(bool pred) const { return __ballot_sync(mask, pred) >> shift; }
+    __device__ __forceinline__ float shfl(float v, int src) const { return __shfl_sync(mask, v, src, G); }
+    __device__ __forceinline__ int shfl(int v, int src) const { return __shfl_sync(mask, v, src, G); }
+    __device__ __forceinline__ int4 shfl(int4 v, int src) const
+    {
+        return make_int4(shfl(v.x, src), shfl(v.y, src), shfl(v.z, src), shfl(v.w, src));
+    }
+    __device__ __forceinline__ float fmax(float v) const
+    {
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(mask, v, o, G));
+        return v;
+    }
+    __device__ __forceinline__ float fmin(float v) const
+    {
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(mask, v, o, G));
+        return v;
+    }
+    __device__ __forceinline__ void sync() const { __syncwarp(mask); }
+};
+
+// Leaf rows of one tree moved by the G lanes of its group (same semantics as gather_rows in lzb_select.cuh).
+template <int G>
+__device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a, int i, int ix, int parent_reset, int lane)
+{
+    for (int k = 0; k < a.ng; ++k) {
+        const long long rb = a.g[k].row_bytes;
+        const char *s;
+        if (a.g[k].src) s = a.g[k].src + ((long long)ix * p.N + i) * rb;
+        else s = ((ix == a.new_e) ? pick3(a.new_slot, k) : p.slots[(size_t)k * p.E + ix]) + (long long)i * rb;
+        char *d = a.g[k].dst + (long long)i * rb;
+        const bool zero = a.g[k].zero_if_reset && parent_reset == 1;
+        if ((rb & 15) == 0 && ((((unsigned long long)s) | ((unsigned long long)d)) & 15ull) == 0) {
+            const int4 *s4 = reinterpret_cast<const int4 *>(s);
+            int4 *d4 = reinterpret_cast<int4 *>(d);
+            const int n4 = (int)(rb >> 4);
+            if (zero) {
+                for (int t = lane; t < n4; t += G) d4[t] = make_int4(0, 0, 0, 0);
+            } else {
+                int t = lane;
+                for (; t + 7 * G < n4; t += 8 * G) { // 8 independent 16-byte loads in flight per lane
+                    int4 v[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) v[u] = __ldcs(s4 + t + u * G);
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) d4[t + u * G] = v[u];
+                }
+                for (; t < n4; t += G) d4[t] = __ldcs(s4 + t);
+            }
+        } else {
+            const int *s1 = reinterpret_cast<const int *>(s);
+            int *d1 = reinterpret_cast<int *>(d);
+            const int n1 = (int)(rb >> 2);
+            for (int t = lane; t < n1; t += G) d1[t] = zero ? 0 : __ldcs(s1 + t);
+        }
+    }
+}
+
+// pUCT traverse of tree i by a lane group (semantics and citations: select_puct_tree in lzb_select.cuh).
+template <int VAR, int G, int R>
+__device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a, int i, const Grp<G> &grp)
+{
+    constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
+    const int B = p.B, A = p.A, lane = grp.lane;
+    const int4 *tree = p.tree(i);
+    int4 *pa = p.path_a + (size_t)i * (p.S + 1);
+    int2 *pb = p.path_b + (size_t)i * (p.S + 1);
+    const float2 mm = p.minmax[i];
+    const int4 rt = p.root[i];
+    int vtp = a.to_play[i];
+    const int players = a.players ? a.players : ((p.scratch[0] == -1) ? 1 : 2); // cnode.cpp:776-781
+    const float g = a.discount;
+    const float c_base = (float)a.c_base;
+    const float mm_delta = mm.y - mm.x;
+    const float mm_den = (mm_delta < a.delta) ? a.delta : mm_delta; // CMinMaxStats::normalize (cminimax.cpp:33-45)
+
+    int parent_visits = rt.x;
+    float parent_reward = __int_as_float(rt.z);
+    int e = 0, depth = 0, pos = 0, action = 0, parent_reset = 0;
+    float parent_q = 0.0f;
+    bool is_root = true;
+
+    while (true) {
+        // ---- one round of independent reads per level: the header (same address in every lane) and R records per lane
+        const int4 *blk = tree + (size_t)e * B;
+        const int4 h = blk[0];
+        int4 c[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int j = lane + G * r;
+            c[r] = (j < A) ? blk[1 + j] : make_int4(0, 0, 0, 0);
+        }
+        const int n = h.x;
+        parent_reset = h.z;
+
+        // ---- compute_mean_q: serial fp32 sum over visited children in legal order
+        float val[R], tr[R];
+        int nvis = 0;
+        float total = 0.0f;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int j = lane + G * r;
+            const int vc = child_visits(c[r].x);
+            const bool vis = (j < n) && vc > 0;
+            const float rew = __int_as_float(c[r].w);
+            tr[r] = rew;
+            if (VP) tr[r] = (parent_reset == 1) ? rew : rew - parent_reward;
+            val[r] = vis ? __int_as_float(c[r].y) / (float)vc : 0.0f; // CNode::value()
+            const float qsa = vis ? tr[r] + g * val[r] : 0.0f;
+            nvis += __popc(grp.ballot(vis));
+#pragma unroll
+            for (int l = 0; l < G; ++l) total += grp.shfl(qsa, l); // j = l + G*r ascending; +0.0f for the rest is exact
+        }
+        const float mean_q = (is_root && nvis > 0) ? total / (float)nvis : (parent_q + total) / (float)(nvis + 1);
+
+        // ---- cucb_score
+        const float T = (float)(parent_visits - 1);
+        const float pbc0 = glibc_logf((T + c_base + 1) / c_base) + a.c_init;
+        const float sqT = sqrtf(T);
+        float sc[R];
+        float lmax = -INFINITY;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int j = lane + G * r;
+            const int vc = child_visits(c[r].x);
+            const float pb_c = pbc0 * (sqT / (float)(vc + 1));
+            float prior_score;
+            if (VAR == LZB_SEZ) prior_score = pb_c / (float)n; // uniform branch, sez cnode.cpp:1078
+            else prior_score = pb_c * __int_as_float(c[r].z);
+            float vs;
+            if (vc == 0) vs = mean_q;
+            else vs = (players == 1) ? tr[r] + g * val[r] : tr[r] + g * (-val[r]);
+            if (mm_delta > 0) vs = (vs - mm.x) / mm_den;
+            if (vs < 0) vs = 0;
+            if (vs > 1) vs = 1;
+            sc[r] = (j < n) ? prior_score + vs : -INFINITY;
+            lmax = fmaxf(lmax, sc[r]);
+        }
+        const float gmax = grp.fmax(lmax);
+
+        // ---- order-dependent tie set + pinned draw (cselect_child, cnode.cpp:567-596)
+        pos = 0;
+        if (gmax > kFloatMin) {
+            int jstar = 0x7fffffff;
+#pragma unroll
+            for (int r = R - 1; r >= 0; --r) {
+                const unsigned m = grp.ballot(sc[r] == gmax);
+                if (m) jstar = (__ffs(m) - 1) + G * r;
+            }
+            const float thr = gmax - 0.000001f;
+            unsigned tie[R];
+            int later = 0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const int j = lane + G * r;
+                tie[r] = grp.ballot(j > jstar && sc[r] >= thr); // sc is -inf beyond n
+                later += __popc(tie[r]);
+            }
+            pos = jstar;
+            if (later > 0) {
+                const unsigned rnd = (a.rng_mode == LZB_RNG_PER_ROOT)
+                                         ? tiebreak_hash(a.seed, (unsigned)a.sim, (unsigned)(p.root_offset + i), (unsigned)depth)
+                                         : tiebreak_hash(a.seed, (unsigned)a.sim, 0u, 0u);
+                int k = (int)(rnd % (unsigned)(later + 1));
+                if (k > 0) {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        const int cnt = __popc(tie[r]);
+                        if (k > 0 && k <= cnt) { pos = (int)__fns(tie[r], 0, k) + G * r; k = 0; }
+                        else if (k > 0) k -= cnt;
+                    }
+                }
+            }
+        }
+        // ---- the chosen child's record lives in lane pos % G, register pos / G
+        const int rsel = pos / G;
+        int4 mine = c[0];
+#pragma unroll
+        for (int r = 1; r < R; ++r) {
+            mine.x = (rsel == r) ? c[r].x : mine.x;
+            mine.y = (rsel == r) ? c[r].y : mine.y;
+            mine.z = (rsel == r) ? c[r].z : mine.z;
+            mine.w = (rsel == r) ? c[r].w : mine.w;
+        }
+        const int4 ch = grp.shfl(mine, pos & (G - 1));
+        action = (VAR != LZB_SEZ && e == 0) ? p.legal[(size_t)i * A + pos] : pos;
+        if (players > 1) vtp = (vtp == 1) ? 2 : 1; // cnode.cpp:797-804
+        if (lane == 0) {
+            pa[depth] = make_int4(e * B + 1 + pos, ch.x, ch.y, ch.w);
+            pb[depth] = make_int2(h.y, h.z);
+            p.best[(size_t)i * p.E + e] = pos;
+        }
+        depth += 1;
+        const int ce = child_expansion(ch.x);
+        if (ce < 0) break;
+        parent_visits = child_visits(ch.x);
+        parent_reward = __int_as_float(ch.w);
+        parent_q = mean_q;
+        is_root = false;
+        e = ce;
+    }
+
+    // ---- leaf bookkeeping (cnode.cpp:814-822) + gather of the parent's rows
+    if (lane == 0) {
+        p.res[i] = make_int4(depth, e, pos, vtp);
+        if (a.ix) a.ix[i] = e;
+        if (a.iy) a.iy[i] = i;
+        if (a.search_len) a.search_len[i] = depth;
+        if (a.vtp) a.vtp[i] = vtp;
+        if (a.last_action) a.last_action[i] = (long long)action;
+    }
+    if (VAR == LZB_SEZ) {
+        const float *act = p.actions + (((size_t)i * p.E + e) * A + pos) * p.D;
+        if (a.last_action_f)
+            for (int d = lane; d < p.D; d += G) a.last_action_f[(size_t)i * p.D + d] = act[d];
+        if (a.last_action && lane == 0) a.last_action[i] = (long long)act[0]; // discrete sampled: float(index)
+    }
+    gather_rows_g<G>(p, a, i, e, parent_reset, lane);
+}
+
+// CNode::expand of the leaf + cbackpropagate along the recorded path by a lane group
+// (semantics and citations: expand_children / expand_backup_tree in lzb_expand.cuh).
+template <int VAR, int G, int R>
+__device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs &a, int i, const Grp<G> &grp)
+{
+    constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
+    const int A = p.A, lane = grp.lane;
+    const int4 res = p.res[i];
+    const int depth = res.x; // search_len >= 1
+    const int e_new = a.latent_index;
+    const int to_play = a.to_play[i];
+    const float value = a.value[i];
+    const float leaf_reward = a.reward[i];
+    // path records are independent of everything above: issue their loads now (first chunk)
+    const int4 *pa = p.path_a + (size_t)i * (p.S + 1);
+    const int2 *pb = p.path_b + (size_t)i * (p.S + 1);
+    int leaf_reset = 0;
+    if (VP) {
+        if (a.is_reset) leaf_reset = a.is_reset[i];
+        else if (a.horizon > 0) leaf_reset = (depth % a.horizon == 0) ? 1 : 0; // mcts_ctree.py:810
+        if (a.is_reset_out && lane == 0) a.is_reset_out[i] = leaf_reset;
+    }
+
+    // ---- expand the leaf as expansion e_new: masked softmax over all A actions (cnode.cpp:118-140)
+    int4 *dst = p.block(i, e_new) + 1;
+    if (VAR == LZB_SEZ) {
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if (lane + G * r < A) dst[lane + G * r] = make_int4(0, 0, 0, 0);
+        const int KD = A * p.D;
+        float *tab = p.actions + ((size_t)i * p.E + e_new) * KD;
+        for (int t = lane; t < KD; t += G) tab[t] = a.sampled_actions[(size_t)i * KD + t];
+    } else {
+        const float *logits = a.logits + (size_t)i * A;
+        float lg[R], t[R];
+        float mx = kFloatMin; // cnode.cpp:118
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int j = lane + G * r;
+            lg[r] = (j < A) ? __ldcs(logits + j) : 0.0f;
+            if (j < A) mx = fmaxf(mx, lg[r]);
+        }
+        mx = grp.fmax(mx);
+        float sum = 0.0f;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int j = lane + G * r;
+            t[r] = (j < A) ? glibc_expf(lg[r] - mx) : 0.0f;
+#pragma unroll
+            for (int l = 0; l < G; ++l) sum += grp.shfl(t[r], l); // strictly left to right in action order; +0.0f beyond A
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int j = lane + G * r;
+            if (j < A) dst[j] = make_int4(0, 0, __float_as_int(t[r] / sum), 0);
+        }
+    }
+    if (lane == 0) {
+        dst[-1] = make_int4(A, to_play, leaf_reset, __float_as_int(value));
+        p.best[(size_t)i * p.E + e_new] = -1;
+    }
+
+    // ---- backup: node q = depth (leaf) ... 1 are path records q-1, node 0 is the root
+    const bool two = (VAR != LZB_GMZ) && (to_play != -1); // cnode.cpp:432; gmz asserts -1 (compiled out)
+    const float g = a.discount;
+    float b = value; // bootstrap_value entering the current chunk
+    float cmin = kFloatMax, cmax = kFloatMin;
+    for (int qhi = depth; qhi >= 0; qhi -= G) {
+        const int q = qhi - lane;
+        const bool valid = q >= 0;
+        int x = 0, slot = -1, node_tp = 0, parent_reset = 0;
+        float vsum = 0.f, rew = 0.f, parent_vp = 0.f;
+        if (valid) {
+            if (q == 0) {
+                const int4 r = p.root[i];
+                x = r.x; vsum = __int_as_float(r.y); rew = __int_as_float(r.z);
+            } else {
+                const int4 r = pa[q - 1];
+                slot = r.x; x = r.y; vsum = __int_as_float(r.z); rew = __int_as_float(r.w);
+                if (q == depth) rew = leaf_reward; // expand() stamps the leaf's reward / value_prefix first
+            }
+            if (two) node_tp = (q == depth) ? to_play : pb[q].x;
+            if (VP && q >= 1) {
+                parent_vp = (q == 1) ? __int_as_float(p.root[i].z) : __int_as_float(pa[q - 2].w);
+                parent_reset = pb[q - 1].y;
+            }
+        }
+        float r_pre = rew, r_boot = rew;
+        if (VP) {
+            r_pre = rew - parent_vp;                    // ez cnode.cpp:515
+            r_boot = (parent_reset == 1) ? rew : r_pre; // :518-522
+        }
+        const bool same = two && (node_tp == to_play);
+        const float r_signed = same ? -r_boot : r_boot;
+        // serial leaf->root recurrence (cnode.cpp:447,473-475): lane l receives b_q, then b = r + g*b
+        float my_b = 0.f;
+        const int cnt = min(G, qhi + 1);
+        for (int l = 0; l < cnt; ++l) {
+            const float rl = grp.shfl(r_signed, l);
+            if (lane == l) my_b = b;
+            b = rl + g * b;
+        }
+        if (valid) {
+            const float add = (two && !same) ? -my_b : my_b;
+            vsum += add;
+            const int visits = (q == 0 ? x : child_visits(x)) + 1;
+            const float nv = vsum / (float)visits;
+            float cand;
+            if (VP) cand = r_pre + g * nv;      // ez :516,558 (value not negated)
+            else if (two) cand = rew + g * -nv; // mz :470
+            else cand = rew + g * nv;           // mz :445, gmz :627
+            cmin = fminf(cmin, cand);
+            cmax = fmaxf(cmax, cand);
+            if (q == 0) {
+                p.root[i] = make_int4(visits, __float_as_int(vsum), __float_as_int(rew), 0);
+            } else {
+                int4 *rec = p.tree(i) + slot;
+                const int exp_idx = (q == depth) ? e_new : child_expansion(x);
+                *reinterpret_cast<int2 *>(rec) = make_int2(child_pack(visits, exp_idx), __float_as_int(vsum));
+                if (q == depth) reinterpret_cast<int *>(rec)[3] = __float_as_int(rew);
+            }
+        }
+    }
+    cmin = grp.fmin(cmin);
+    cmax = grp.fmax(cmax);
+    if (lane == 0) {
+        float2 mm = p.minmax[i];
+        mm.x = fminf(mm.x, cmin); // CMinMaxStats::update (cminimax.cpp:23-31)
+        mm.y = fmaxf(mm.y, cmax);
+        p.minmax[i] = mm;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------- kernels
+// 128 threads = 128 / G trees per block
+template <int VAR, int G, int R>
+__global__ void __launch_bounds__(128) k_select_g(Pool p, SelectArgs a)
+{
+    const Grp<G> grp;
+    const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
+    if (i >= p.N) return;
+    select_puct_g<VAR, G, R>(p, a, i, grp);
+}
+
+template <int VAR, int G, int R>
+__global__ void __launch_bounds__(128) k_expand_backup_g(Pool p, BackupArgs b)
+{
+    const Grp<G> grp;
+    const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
+    if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
+    if (i >= p.N) return;
+    expand_backup_g<VAR, G, R>(p, b, i, grp);
+}
+
+// fused simulation step (see lzb_step.cuh): expand + backup of simulation s, then select + gather of s + 1
+template <int VAR, int G, int R>
+__global__ void __launch_bounds__(128) k_step_g(Pool p, BackupArgs b, SelectArgs a)
+{
+    const Grp<G> grp;
+    const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
+    if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
+    if (i >= p.N) return;
+    expand_backup_g<VAR, G, R>(p, b, i, grp);
+    grp.sync(); // the group's own global writes (records, root, MinMax) are ordered before its reads below
+    select_puct_g<VAR, G, R>(p, a, i, grp);
+}
+
+} // namespace lzb

@@ -22,6 +22,7 @@ class ScenarioModel:
         self.t = lambda a: torch.as_tensor(a).to(dev)
         self.sc, self.s, self.dev, self.L, self.H = sc, 0, dev, latent_dim, hidden
         self.calls = []
+        self.logits, self.value, self.reward = self.t(sc.logits), self.t(sc.value), self.t(sc.reward)  # tables in HBM
 
     def eval(self):
         self.s = 0
@@ -30,12 +31,13 @@ class ScenarioModel:
         import torch
         sc, s = self.sc, self.s
         self.s += 1
-        self.calls.append((latent.clone(), rest))
+        snap = lambda x: tuple(snap(y) for y in x) if isinstance(x, (tuple, list)) else x.clone()
+        self.calls.append((latent.clone(), snap(rest)))  # the driver reuses its output buffers every simulation
         o = Out()
-        o.latent_state = torch.full((sc.n, self.L), float(s + 1), device=self.dev)
-        o.policy_logits = self.t(sc.logits[s])
-        o.value = self.t(sc.value[s]).unsqueeze(1)
-        o.reward = o.value_prefix = self.t(sc.reward[s]).unsqueeze(1)
+        o.latent_state = torch.full_like(latent, float(s + 1))
+        o.policy_logits = self.logits[s]
+        o.value = self.value[s].unsqueeze(1)
+        o.reward = o.value_prefix = self.reward[s].unsqueeze(1)
         if self.H:
             o.reward_hidden_state = (torch.full((1, sc.n, self.H), float(s + 1), device=self.dev),
                                      torch.full((1, sc.n, self.H), -float(s + 1), device=self.dev))
@@ -132,7 +134,7 @@ def test_efficientzero_driver_matches_oracle_and_resets_hidden_state():
         want_c = np.where(par_reset, 0.0, want_c).astype(np.float32)
         assert c.shape == (1, sc.n, 8) and h.shape == (1, sc.n, 8)
         assert_same(c[0, :, 0].cpu().numpy(), want_c, "sim %d LSTM c" % s)
-        assert_same(h[0, :, 3].cpu().numpy(), -want_c, "sim %d LSTM h" % s)
+        assert_same(h[0, :, 3].cpu().numpy(), np.where(par_reset, 0.0, -want_c).astype(np.float32), "sim %d LSTM h" % s)
 
 
 @pytest.mark.parametrize("graph", [False, True])

@@ -194,6 +194,17 @@ def test_muzero_wide_action_space_multi_chunk():  # A > 32 exercises the chunked
     compare(Scenario("mz", 16, 80, 60, seed=8))
 
 
+def test_muzero_very_wide_warp_per_tree_kernels():  # A > 128: the shared-memory warp-per-tree kernels
+    compare(Scenario("mz", 8, 150, 40, seed=32))
+    compare(Scenario("ez", 8, 150, 30, seed=33), fused=True)
+
+
+def test_warp_per_tree_kernels_on_small_action_space(monkeypatch):
+    monkeypatch.setenv("LZB_FORCE_WARP_PER_TREE", "1")
+    compare(Scenario("mz", 64, 18, 50, seed=34), fused=True)
+    compare(Scenario("ez", 32, 6, 50, seed=35))
+
+
 def test_efficientzero_pong_shape():  # C2: A=6, 50 sims, value_prefix + lstm_horizon_len=5 resets
     compare(Scenario("ez", 64, 6, 50, seed=9))
 
