@@ -16,21 +16,28 @@
 
 namespace lzb {
 
+// All 32 lanes of a warp execute every instruction of these kernels together (warp-synchronous style): exchanges
+// are full-mask shuffles of width G and full-mask ballots shifted to the group's bits, and a group that has
+// finished (reached its leaf, or has no tree) keeps executing with its writes predicated off.  Sub-warp member
+// masks would let groups diverge, but the compiler then wraps every shuffle in a convergence protocol
+// (WARPSYNC.COLLECTIVE / REDUX / BSSY...BSYNC) that more than doubled the instruction count when measured.
 template <int G>
 struct Grp {
-    int lane;      // 0 .. G-1 within the group
-    int shift;     // first warp lane of the group
-    unsigned mask; // member mask of the group inside its warp
+    int lane;  // 0 .. G-1 within the group
+    int shift; // first warp lane of the group
     __device__ __forceinline__ Grp()
     {
         const int wl = threadIdx.x & 31;
         lane = wl & (G - 1);
         shift = wl - lane;
-        mask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << shift);
     }
-    __device__ __forceinline__ unsigned ballot(bool pred) const { return __ballot_sync(mask, pred) >> shift; }
-    __device__ __forceinline__ float shfl(float v, int src) const { return __shfl_sync(mask, v, src, G); }
-    __device__ __forceinline__ int shfl(int v, int src) const { return __shfl_sync(mask, v, src, G); }
+    __device__ __forceinline__ unsigned ballot(bool pred) const
+    {
+        const unsigned m = __ballot_sync(kFull, pred) >> shift;
+        return (G == 32) ? m : (m & ((1u << (G & 31)) - 1u));
+    }
+    __device__ __forceinline__ float shfl(float v, int src) const { return __shfl_sync(kFull, v, src, G); }
+    __device__ __forceinline__ int shfl(int v, int src) const { return __shfl_sync(kFull, v, src, G); }
     __device__ __forceinline__ int4 shfl(int4 v, int src) const
     {
         return make_int4(shfl(v.x, src), shfl(v.y, src), shfl(v.z, src), shfl(v.w, src));
@@ -38,16 +45,15 @@ struct Grp {
     __device__ __forceinline__ float fmax(float v) const
     {
 #pragma unroll
-        for (int o = G / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(mask, v, o, G));
+        for (int o = G / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o, G));
         return v;
     }
     __device__ __forceinline__ float fmin(float v) const
     {
 #pragma unroll
-        for (int o = G / 2; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(mask, v, o, G));
+        for (int o = G / 2; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(kFull, v, o, G));
         return v;
     }
-    __device__ __forceinline__ void sync() const { __syncwarp(mask); }
 };
 
 // Leaf rows of one tree moved by the G lanes of its group (same semantics as gather_rows in lzb_select.cuh).
@@ -88,8 +94,9 @@ __device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a
 }
 
 // pUCT traverse of tree i by a lane group (semantics and citations: select_puct_tree in lzb_select.cuh).
+// `live`: this group has a tree (i < N); dead groups run along on tree 0 with every write predicated off.
 template <int VAR, int G, int R>
-__device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a, int i, const Grp<G> &grp)
+__device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a, int i, bool live, const Grp<G> &grp)
 {
     constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
     const int B = p.B, A = p.A, lane = grp.lane;
@@ -104,14 +111,16 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     const float c_base = (float)a.c_base;
     const float mm_delta = mm.y - mm.x;
     const float mm_den = (mm_delta < a.delta) ? a.delta : mm_delta; // CMinMaxStats::normalize (cminimax.cpp:33-45)
+    const unsigned hroot = (a.rng_mode == LZB_RNG_PER_ROOT) ? (unsigned)(p.root_offset + i) : 0u;
 
     int parent_visits = rt.x;
     float parent_reward = __int_as_float(rt.z);
     int e = 0, depth = 0, pos = 0, action = 0, parent_reset = 0;
     float parent_q = 0.0f;
     bool is_root = true;
+    bool going = live; // this group is still descending
 
-    while (true) {
+    while (__any_sync(kFull, going)) {
         // ---- one round of independent reads per level: the header (same address in every lane) and R records per lane
         const int4 *blk = tree + (size_t)e * B;
         const int4 h = blk[0];
@@ -122,7 +131,6 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             c[r] = (j < A) ? blk[1 + j] : make_int4(0, 0, 0, 0);
         }
         const int n = h.x;
-        parent_reset = h.z;
 
         // ---- compute_mean_q: serial fp32 sum over visited children in legal order
         float val[R], tr[R];
@@ -135,7 +143,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             const bool vis = (j < n) && vc > 0;
             const float rew = __int_as_float(c[r].w);
             tr[r] = rew;
-            if (VP) tr[r] = (parent_reset == 1) ? rew : rew - parent_reward;
+            if (VP) tr[r] = (h.z == 1) ? rew : rew - parent_reward;
             val[r] = vis ? __int_as_float(c[r].y) / (float)vc : 0.0f; // CNode::value()
             const float qsa = vis ? tr[r] + g * val[r] : 0.0f;
             nvis += __popc(grp.ballot(vis));
@@ -169,42 +177,41 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         }
         const float gmax = grp.fmax(lmax);
 
-        // ---- order-dependent tie set + pinned draw (cselect_child, cnode.cpp:567-596)
-        pos = 0;
-        if (gmax > kFloatMin) {
-            int jstar = 0x7fffffff;
+        // ---- order-dependent tie set + pinned draw (cselect_child, cnode.cpp:567-596), branch-free:
+        // jstar = first index attaining the maximum; tie set = later indices within epsilon; draw k in [0, later]
+        const bool any_score = gmax > kFloatMin;
+        int jstar = 0;
 #pragma unroll
-            for (int r = R - 1; r >= 0; --r) {
-                const unsigned m = grp.ballot(sc[r] == gmax);
-                if (m) jstar = (__ffs(m) - 1) + G * r;
-            }
-            const float thr = gmax - 0.000001f;
-            unsigned tie[R];
-            int later = 0;
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const int j = lane + G * r;
-                tie[r] = grp.ballot(j > jstar && sc[r] >= thr); // sc is -inf beyond n
-                later += __popc(tie[r]);
-            }
-            pos = jstar;
-            if (later > 0) {
-                const unsigned rnd = (a.rng_mode == LZB_RNG_PER_ROOT)
-                                         ? tiebreak_hash(a.seed, (unsigned)a.sim, (unsigned)(p.root_offset + i), (unsigned)depth)
-                                         : tiebreak_hash(a.seed, (unsigned)a.sim, 0u, 0u);
-                int k = (int)(rnd % (unsigned)(later + 1));
-                if (k > 0) {
-#pragma unroll
-                    for (int r = 0; r < R; ++r) {
-                        const int cnt = __popc(tie[r]);
-                        if (k > 0 && k <= cnt) { pos = (int)__fns(tie[r], 0, k) + G * r; k = 0; }
-                        else if (k > 0) k -= cnt;
-                    }
-                }
-            }
+        for (int r = R - 1; r >= 0; --r) {
+            const unsigned m = grp.ballot(sc[r] == gmax);
+            jstar = m ? (__ffs(m) - 1) + G * r : jstar;
         }
-        // ---- the chosen child's record lives in lane pos % G, register pos / G
-        const int rsel = pos / G;
+        const float thr = gmax - 0.000001f;
+        unsigned tie[R];
+        int later = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int j = lane + G * r;
+            tie[r] = grp.ballot(j > jstar && sc[r] >= thr); // sc is -inf beyond n
+            later += __popc(tie[r]);
+        }
+        const unsigned rnd = tiebreak_hash(a.seed, (unsigned)a.sim, hroot, (a.rng_mode == LZB_RNG_PER_ROOT) ? (unsigned)depth : 0u);
+        const int k = (int)(rnd % (unsigned)(later + 1));
+        int newpos = jstar;
+        int before = 0; // tie-set members in earlier registers
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            // the lane whose tie bit is the k-th one of the set announces itself
+            const bool mybit = (tie[r] >> lane) & 1u;
+            const int rank = before + __popc(tie[r] & ((1u << lane) - 1u)) + 1;
+            const unsigned hit = grp.ballot(mybit && rank == k);
+            newpos = hit ? (__ffs(hit) - 1) + G * r : newpos;
+            before += __popc(tie[r]);
+        }
+        newpos = any_score ? newpos : 0;
+
+        // ---- the chosen child's record lives in lane newpos % G, register newpos / G
+        const int rsel = newpos / G;
         int4 mine = c[0];
 #pragma unroll
         for (int r = 1; r < R; ++r) {
@@ -213,26 +220,33 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             mine.z = (rsel == r) ? c[r].z : mine.z;
             mine.w = (rsel == r) ? c[r].w : mine.w;
         }
-        const int4 ch = grp.shfl(mine, pos & (G - 1));
-        action = (VAR != LZB_SEZ && e == 0) ? p.legal[(size_t)i * A + pos] : pos;
-        if (players > 1) vtp = (vtp == 1) ? 2 : 1; // cnode.cpp:797-804
-        if (lane == 0) {
-            pa[depth] = make_int4(e * B + 1 + pos, ch.x, ch.y, ch.w);
-            pb[depth] = make_int2(h.y, h.z);
-            p.best[(size_t)i * p.E + e] = pos;
+        const int4 ch = grp.shfl(mine, newpos & (G - 1));
+        if (going) {
+            pos = newpos;
+            parent_reset = h.z;
+            action = (VAR != LZB_SEZ && e == 0) ? p.legal[(size_t)i * A + pos] : pos;
+            if (players > 1) vtp = (vtp == 1) ? 2 : 1; // cnode.cpp:797-804
+            if (lane == 0) {
+                pa[depth] = make_int4(e * B + 1 + pos, ch.x, ch.y, ch.w);
+                pb[depth] = make_int2(h.y, h.z);
+                p.best[(size_t)i * p.E + e] = pos;
+            }
+            depth += 1;
+            const int ce = child_expansion(ch.x);
+            if (ce < 0) {
+                going = false;
+            } else {
+                parent_visits = child_visits(ch.x);
+                parent_reward = __int_as_float(ch.w);
+                parent_q = mean_q;
+                is_root = false;
+                e = ce;
+            }
         }
-        depth += 1;
-        const int ce = child_expansion(ch.x);
-        if (ce < 0) break;
-        parent_visits = child_visits(ch.x);
-        parent_reward = __int_as_float(ch.w);
-        parent_q = mean_q;
-        is_root = false;
-        e = ce;
     }
 
     // ---- leaf bookkeeping (cnode.cpp:814-822) + gather of the parent's rows
-    if (lane == 0) {
+    if (live && lane == 0) {
         p.res[i] = make_int4(depth, e, pos, vtp);
         if (a.ix) a.ix[i] = e;
         if (a.iy) a.iy[i] = i;
@@ -240,6 +254,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         if (a.vtp) a.vtp[i] = vtp;
         if (a.last_action) a.last_action[i] = (long long)action;
     }
+    if (!live) return;
     if (VAR == LZB_SEZ) {
         const float *act = p.actions + (((size_t)i * p.E + e) * A + pos) * p.D;
         if (a.last_action_f)
@@ -252,7 +267,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
 // CNode::expand of the leaf + cbackpropagate along the recorded path by a lane group
 // (semantics and citations: expand_children / expand_backup_tree in lzb_expand.cuh).
 template <int VAR, int G, int R>
-__device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs &a, int i, const Grp<G> &grp)
+__device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs &a, int i, bool live, const Grp<G> &grp)
 {
     constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
     const int A = p.A, lane = grp.lane;
@@ -269,18 +284,20 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     if (VP) {
         if (a.is_reset) leaf_reset = a.is_reset[i];
         else if (a.horizon > 0) leaf_reset = (depth % a.horizon == 0) ? 1 : 0; // mcts_ctree.py:810
-        if (a.is_reset_out && lane == 0) a.is_reset_out[i] = leaf_reset;
+        if (a.is_reset_out && lane == 0 && live) a.is_reset_out[i] = leaf_reset;
     }
 
     // ---- expand the leaf as expansion e_new: masked softmax over all A actions (cnode.cpp:118-140)
     int4 *dst = p.block(i, e_new) + 1;
     if (VAR == LZB_SEZ) {
+        if (live) {
 #pragma unroll
-        for (int r = 0; r < R; ++r)
-            if (lane + G * r < A) dst[lane + G * r] = make_int4(0, 0, 0, 0);
-        const int KD = A * p.D;
-        float *tab = p.actions + ((size_t)i * p.E + e_new) * KD;
-        for (int t = lane; t < KD; t += G) tab[t] = a.sampled_actions[(size_t)i * KD + t];
+            for (int r = 0; r < R; ++r)
+                if (lane + G * r < A) dst[lane + G * r] = make_int4(0, 0, 0, 0);
+            const int KD = A * p.D;
+            float *tab = p.actions + ((size_t)i * p.E + e_new) * KD;
+            for (int t = lane; t < KD; t += G) tab[t] = a.sampled_actions[(size_t)i * KD + t];
+        }
     } else {
         const float *logits = a.logits + (size_t)i * A;
         float lg[R], t[R];
@@ -303,10 +320,10 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int j = lane + G * r;
-            if (j < A) dst[j] = make_int4(0, 0, __float_as_int(t[r] / sum), 0);
+            if (j < A && live) dst[j] = make_int4(0, 0, __float_as_int(t[r] / sum), 0);
         }
     }
-    if (lane == 0) {
+    if (lane == 0 && live) {
         dst[-1] = make_int4(A, to_play, leaf_reset, __float_as_int(value));
         p.best[(size_t)i * p.E + e_new] = -1;
     }
@@ -316,9 +333,9 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     const float g = a.discount;
     float b = value; // bootstrap_value entering the current chunk
     float cmin = kFloatMax, cmax = kFloatMin;
-    for (int qhi = depth; qhi >= 0; qhi -= G) {
+    for (int qhi = depth; __any_sync(kFull, qhi >= 0); qhi -= G) { // every group runs as many chunks as the deepest one
         const int q = qhi - lane;
-        const bool valid = q >= 0;
+        const bool valid = live && q >= 0;
         int x = 0, slot = -1, node_tp = 0, parent_reset = 0;
         float vsum = 0.f, rew = 0.f, parent_vp = 0.f;
         if (valid) {
@@ -346,10 +363,11 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
         // serial leaf->root recurrence (cnode.cpp:447,473-475): lane l receives b_q, then b = r + g*b
         float my_b = 0.f;
         const int cnt = min(G, qhi + 1);
-        for (int l = 0; l < cnt; ++l) {
+#pragma unroll
+        for (int l = 0; l < G; ++l) {
             const float rl = grp.shfl(r_signed, l);
             if (lane == l) my_b = b;
-            b = rl + g * b;
+            b = (l < cnt) ? rl + g * b : b;
         }
         if (valid) {
             const float add = (two && !same) ? -my_b : my_b;
@@ -374,7 +392,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     }
     cmin = grp.fmin(cmin);
     cmax = grp.fmax(cmax);
-    if (lane == 0) {
+    if (lane == 0 && live) {
         float2 mm = p.minmax[i];
         mm.x = fminf(mm.x, cmin); // CMinMaxStats::update (cminimax.cpp:23-31)
         mm.y = fmaxf(mm.y, cmax);
@@ -383,14 +401,14 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 }
 
 // ---------------------------------------------------------------------------------------------- kernels
-// 128 threads = 128 / G trees per block
+// 128 threads = 128 / G trees per block; groups without a tree (tail of the last block) run along on tree 0, muted
 template <int VAR, int G, int R>
 __global__ void __launch_bounds__(128) k_select_g(Pool p, SelectArgs a)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
-    if (i >= p.N) return;
-    select_puct_g<VAR, G, R>(p, a, i, grp);
+    const bool live = i < p.N;
+    select_puct_g<VAR, G, R>(p, a, live ? i : 0, live, grp);
 }
 
 template <int VAR, int G, int R>
@@ -398,9 +416,9 @@ __global__ void __launch_bounds__(128) k_expand_backup_g(Pool p, BackupArgs b)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
+    const bool live = i < p.N;
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
-    if (i >= p.N) return;
-    expand_backup_g<VAR, G, R>(p, b, i, grp);
+    expand_backup_g<VAR, G, R>(p, b, live ? i : 0, live, grp);
 }
 
 // fused simulation step (see lzb_step.cuh): expand + backup of simulation s, then select + gather of s + 1
@@ -409,11 +427,11 @@ __global__ void __launch_bounds__(128) k_step_g(Pool p, BackupArgs b, SelectArgs
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
+    const bool live = i < p.N;
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
-    if (i >= p.N) return;
-    expand_backup_g<VAR, G, R>(p, b, i, grp);
-    grp.sync(); // the group's own global writes (records, root, MinMax) are ordered before its reads below
-    select_puct_g<VAR, G, R>(p, a, i, grp);
+    expand_backup_g<VAR, G, R>(p, b, live ? i : 0, live, grp);
+    __syncwarp(); // the warp's own global writes (records, root, MinMax) are ordered before its reads below
+    select_puct_g<VAR, G, R>(p, a, live ? i : 0, live, grp);
 }
 
 } // namespace lzb
