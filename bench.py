@@ -145,6 +145,28 @@ class TableModel:
         return o
 
 
+def measure_depth(a, mcts, model, inp, rank):
+    """Mean search_len over all simulations of one search (an untimed eager search with the depth read per call)."""
+    import torch
+    from lightzero_b200.forest import Forest
+    acc = []
+    orig_t, orig_s = Forest.traverse, Forest.step
+
+    def grab(fn):
+        def inner(self_, *args, **kw):
+            o = fn(self_, *args, **kw)
+            acc.append(o["search_len"].float().mean())
+            return o
+        return inner
+
+    Forest.traverse, Forest.step = grab(orig_t), grab(orig_s)
+    try:
+        one_search(a, mcts, model, inp, rank=rank)
+    finally:
+        Forest.traverse, Forest.step = orig_t, orig_s
+    return float(torch.stack(acc).mean())
+
+
 def make_driver(a, device, graph):
     import lightzero_b200 as lzb
     cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree}[a.variant]
@@ -177,15 +199,21 @@ def one_search(a, mcts, model, inp, host=None, rank=0):
 
 # --------------------------------------------------------------------------------------------- per-kernel timing
 class KernelTimer:
-    """CUDA events around each launch of our per-simulation kernels (on torch's current stream, which is the stream
-    the C ABI launches on), plus the mean search depth the roofline byte model needs.  The caller first queues a
-    spin kernel (torch.cuda._sleep) so the host runs ahead and the launches execute back to back: the event pairs
-    then measure kernel durations, not Python launch latency."""
+    """CUDA-event timing of our per-simulation kernels on torch's current stream (the stream the C ABI launches on).
+
+    A search issues S-1 fused step launches back to back (the table-lookup model launches nothing in between), so the
+    step kernel is timed as ONE event pair around the whole run of step launches divided by their count: an event
+    pair around every single launch costs more than the ~20 us kernel itself.  The caller first queues a spin kernel
+    (torch.cuda._sleep) so the host runs ahead and the launches execute back to back; the figure therefore includes
+    the launch-to-launch gap, i.e. it is an upper bound of the kernel's own duration.  The first select and the last
+    expand+backup are bracketed individually.  Mean search depth feeds the roofline byte model."""
     NAMES = {"step": "step (expand+backup s, select+gather s+1)", "traverse": "select+gather", "backprop": "expand+backup"}
 
-    def __init__(self):
+    def __init__(self, steps_per_search):
+        self.per_search = steps_per_search
         self.ev = {k: [] for k in self.NAMES}
         self.depth = []
+        self._n = 0
 
     def install(self):
         import torch
@@ -195,13 +223,18 @@ class KernelTimer:
 
         def wrap(fn, name):
             def inner(self_, *args, **kw):
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
+                first = last = True
+                if name == "step":
+                    first, last = timer._n == 0, timer._n == timer.per_search - 1
+                    timer._n = (timer._n + 1) % timer.per_search
+                if first:
+                    timer._e0 = torch.cuda.Event(enable_timing=True)
+                    timer._e0.record()
                 r = fn(self_, *args, **kw)
-                e1.record()
-                timer.ev[name].append((e0, e1))
-                if isinstance(r, dict) and "search_len" in r:
-                    timer.depth.append(r["search_len"].float().mean())
+                if last:
+                    e1 = torch.cuda.Event(enable_timing=True)
+                    e1.record()
+                    timer.ev[name].append((timer._e0, e1))
                 return r
             return inner
 
@@ -216,9 +249,8 @@ class KernelTimer:
     def summary(self):
         import torch
         torch.cuda.synchronize()
-        out = {k: ([a.elapsed_time(b) for a, b in v]) for k, v in self.ev.items()}
-        depth = float(torch.stack(self.depth).mean()) if self.depth else 0.0
-        return out, depth
+        out = {k: ([a.elapsed_time(b) / (self.per_search if k == "step" else 1) for a, b in v]) for k, v in self.ev.items()}
+        return out
 
 
 def roofline(a, per_kernel_ms, depth, peak_gbs, peak_src):
@@ -229,9 +261,11 @@ def roofline(a, per_kernel_ms, depth, peak_gbs, peak_src):
     sel = depth * (16 * A + 16) + 8 + 4 * (depth + 1) + Lb
     bak = 4 * A + 16 * A + 28 + (depth + 1) * 20 + 8
     alg = {"step": N * (sel + bak), "traverse": N * sel, "backprop": N * bak}
-    tot = {k: sum(v) for k, v in per_kernel_ms.items() if v}
+    launches = {"step": a.sims - 1, "traverse": 1, "backprop": 1}  # per search
+    avg = {k: sum(v) / len(v) for k, v in per_kernel_ms.items() if v}
+    tot = {k: avg[k] * launches[k] for k in avg}
     top = max(tot, key=tot.get)
-    avg_ms = tot[top] / len(per_kernel_ms[top])
+    avg_ms = avg[top]
     achieved = alg[top] / (avg_ms * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
@@ -245,7 +279,8 @@ def roofline(a, per_kernel_ms, depth, peak_gbs, peak_src):
             "frac": round(achieved / peak_gbs, 4), "traffic": traffic, "peak_source": peak_src,
             "algorithmic_bytes_per_launch": int(alg[top]), "avg_launch_us": round(avg_ms * 1e3, 2),
             "mean_search_depth": round(depth, 3), "kernel_time_share": share,
-            "avg_launch_us_all": {k: round(1e3 * tot[k] / len(per_kernel_ms[k]), 2) for k in tot}}
+            "avg_launch_us_all": {k: round(1e3 * avg[k], 2) for k in avg},
+            "timing": "CUDA events on the launch stream; step = one event pair around the S-1 back-to-back step launches / (S-1)"}
 
 
 # --------------------------------------------------------------------------------------------- CPU side (checker only)
@@ -444,9 +479,10 @@ def run_b200_arm(a):
     clk = clocks.stop() if rank == 0 else None
 
     # ---- per-kernel pass (eager launches bracketed by events) for the roofline of the dominant kernel
-    timer = KernelTimer()
+    timer = KernelTimer(S - 1)
     eager = make_driver(a, device, graph=False)
     one_search(a, eager, model, inp, rank=rank)  # warm the eager path
+    depth = measure_depth(a, eager, model, inp, rank)
     timer.install()
     for _ in range(3):
         flush.fill_(1)
@@ -454,7 +490,7 @@ def run_b200_arm(a):
         one_search(a, eager, model, inp, rank=rank)
         torch.cuda.synchronize()
     timer.remove()
-    per_kernel, depth = timer.summary()
+    per_kernel = timer.summary()
 
     # ---- reduce over ranks (max time), print on rank 0
     t = torch.tensor([dev_ms, e2e_ms or 0.0], dtype=torch.float64, device=device)
