@@ -18,6 +18,7 @@ struct lzb_forest {
     size_t bytes;
     float delta;
     int sim;      // traverses issued since the last prepare (keys the tie-break stream)
+    int pbc_base; float pbc_init; // pUCT constants the pbc table in the workspace was computed for
     const void *players_for; // to_play pointer whose batch maximum is in pool.scratch[0] for this search
     int expanded; // highest latent_index expanded so far
     int vt_m, vt_s;
@@ -50,7 +51,7 @@ constexpr size_t kAlign = 256;
 inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 
 struct Layout {
-    size_t node, root, legal, minmax, path_a, path_b, res, best, actions, gumbel, vtable, scratch, slots, total;
+    size_t node, root, legal, minmax, path_a, path_b, res, best, actions, gumbel, vtable, scratch, slots, pbc, total;
 };
 
 Layout make_layout(int variant, int N, int A, int S, int D)
@@ -72,6 +73,7 @@ Layout make_layout(int variant, int N, int A, int S, int D)
     l.vtable = take(E * sizeof(int));
     l.scratch = take(4 * sizeof(int));
     l.slots = take((size_t)kMaxGathers * E * sizeof(char *));
+    l.pbc = take((E + 1) * sizeof(float2));
     l.total = o;
     return l;
 }
@@ -129,6 +131,15 @@ __global__ void k_max_to_play(const int *to_play, int n, int *out)
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) m = max(m, to_play[i]);
     m = warp_max_i(m);
     if ((threadIdx.x & 31) == 0) atomicMax(out, m);
+}
+
+// pb_c factors of cucb_score (cnode.cpp:673-674) for every possible parent visit count, with the tree's own logf
+__global__ void k_pbc_table(Pool p, int c_base, float c_init)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > p.E) return;
+    const float T = (float)t, c2 = (float)c_base;
+    p.pbc[t] = make_float2(glibc_logf((T + c2 + 1) / c2) + c_init, sqrtf(T));
 }
 
 __global__ void k_set_slots(Pool p, int e, int n, const char *s0, const char *s1, const char *s2)
@@ -343,12 +354,12 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
     Pool &p = f->pool;
     p.variant = variant; p.N = num_roots; p.A = action_space; p.S = max_sims; p.E = max_sims + 1; p.D = action_dim;
     p.root_offset = root_offset; p.B = action_space + 1;
-    p.node = (int4 *)(w + l.node); p.root = (int4 *)(w + l.root); p.slots = (const char **)(w + l.slots);
+    p.node = (int4 *)(w + l.node); p.root = (int4 *)(w + l.root); p.slots = (const char **)(w + l.slots); p.pbc = (float2 *)(w + l.pbc);
     p.legal = (int *)(w + l.legal); p.minmax = (float2 *)(w + l.minmax);
     p.path_a = (int4 *)(w + l.path_a); p.path_b = (int2 *)(w + l.path_b); p.res = (int4 *)(w + l.res);
     p.best = (int *)(w + l.best); p.actions = (float *)(w + l.actions); p.gumbel = (float *)(w + l.gumbel);
     p.vtable = (int *)(w + l.vtable); p.scratch = (int *)(w + l.scratch);
-    f->bytes = l.total; f->delta = 0.0f; f->sim = 0; f->expanded = -1; f->vt_m = -1; f->vt_s = -1; f->players_for = nullptr;
+    f->bytes = l.total; f->delta = 0.0f; f->sim = 0; f->expanded = -1; f->vt_m = -1; f->vt_s = -1; f->players_for = nullptr; f->pbc_base = -1; f->pbc_init = 0.0f;
     cudaStream_t st = (cudaStream_t)stream;
     k_init<<<(num_roots + 127) / 128, 128, 0, st>>>(p, legal_count_dev, legal_actions_dev);
     if (variant == LZB_GMZ) {
@@ -432,6 +443,10 @@ int fill_select(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse
             return fail(LZB_E_ARG, "gather %d: NULL destination or row_bytes not a positive multiple of 4", k);
         a.g[k] = Gather{(const char *)g.src_dev, (char *)g.dst_dev, (long long)g.row_bytes, g.zero_if_reset};
     }
+    if (p.variant != LZB_GMZ && (f->pbc_base != cfg->pb_c_base || f->pbc_init != cfg->pb_c_init)) {
+        k_pbc_table<<<(p.E + 128) / 128, 128, 0, st>>>(p, cfg->pb_c_base, cfg->pb_c_init);
+        f->pbc_base = cfg->pb_c_base; f->pbc_init = cfg->pb_c_init;
+    }
     if (a.players == 0 && f->players_for != (const void *)io->to_play_dev) {
         k_max_to_play_init<<<1, 1, 0, st>>>(p.scratch);
         k_max_to_play<<<std::min((p.N + 255) / 256, 148), 256, 0, st>>>(io->to_play_dev, p.N, p.scratch);
@@ -482,17 +497,35 @@ void launch_group(int which, const Pool &p, const BackupArgs *b, const SelectArg
     else k_step_g<VAR, G, R><<<grid, block, 0, st>>>(p, *b, *a);
 }
 
+// Lanes per tree G and child records per lane R (G * R >= A).  Fewer records per lane = a shorter dependent chain
+// per tree level, more lanes per tree = more warps; past one resident wave (148 SMs x 32 warps of these kernels)
+// extra warps only queue, so the widest group that still fits one wave is taken, else the narrowest.
 template <int VAR>
 bool launch_group_for(int which, const Pool &p, const BackupArgs *b, const SelectArgs *a, cudaStream_t st)
 {
     const int A = p.A;
-    if (A <= 8) launch_group<VAR, 8, 1>(which, p, b, a, st);
-    else if (A <= 16) launch_group<VAR, 8, 2>(which, p, b, a, st);
-    else if (A <= 24) launch_group<VAR, 8, 3>(which, p, b, a, st);
-    else if (A <= 32) launch_group<VAR, 16, 2>(which, p, b, a, st);
-    else if (A <= 64) launch_group<VAR, 32, 2>(which, p, b, a, st);
-    else if (A <= 128) launch_group<VAR, 32, 4>(which, p, b, a, st);
-    else return false; // wider action spaces: warp-per-tree kernels with shared-memory staging
+    static const int forced = getenv("LZB_GROUP_LANES") ? atoi(getenv("LZB_GROUP_LANES")) : 0; // tuning hook: 8, 16 or 32
+    const long long one_wave = 148LL * 28; // warps: __launch_bounds__(128, 7) keeps 7 blocks of 4 warps resident per SM
+    auto fits = [&](int G) { return forced ? forced == G : ((long long)p.N * G + 31) / 32 <= one_wave; };
+    if (A <= 8) {
+        launch_group<VAR, 8, 1>(which, p, b, a, st);
+    } else if (A <= 16) {
+        if (fits(16)) launch_group<VAR, 16, 1>(which, p, b, a, st);
+        else launch_group<VAR, 8, 2>(which, p, b, a, st);
+    } else if (A <= 24) {
+        if (fits(32)) launch_group<VAR, 32, 1>(which, p, b, a, st);
+        else if (fits(16)) launch_group<VAR, 16, 2>(which, p, b, a, st);
+        else launch_group<VAR, 8, 3>(which, p, b, a, st);
+    } else if (A <= 32) {
+        if (fits(32)) launch_group<VAR, 32, 1>(which, p, b, a, st);
+        else launch_group<VAR, 16, 2>(which, p, b, a, st);
+    } else if (A <= 64) {
+        launch_group<VAR, 32, 2>(which, p, b, a, st);
+    } else if (A <= 128) {
+        launch_group<VAR, 32, 4>(which, p, b, a, st);
+    } else {
+        return false; // wider action spaces: warp-per-tree kernels with shared-memory staging
+    }
     return true;
 }
 

@@ -75,12 +75,19 @@ __device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a
                 for (int t = lane; t < n4; t += G) d4[t] = make_int4(0, 0, 0, 0);
             } else {
                 int t = lane;
-                for (; t + 7 * G < n4; t += 8 * G) { // 8 independent 16-byte loads in flight per lane
-                    int4 v[8];
+                for (; t + 11 * G < n4; t += 12 * G) { // 12 independent 16-byte loads in flight per lane
+                    int4 v[12];
 #pragma unroll
-                    for (int u = 0; u < 8; ++u) v[u] = __ldcs(s4 + t + u * G);
+                    for (int u = 0; u < 12; ++u) v[u] = __ldcs(s4 + t + u * G);
 #pragma unroll
-                    for (int u = 0; u < 8; ++u) d4[t + u * G] = v[u];
+                    for (int u = 0; u < 12; ++u) d4[t + u * G] = v[u];
+                }
+                for (; t + 3 * G < n4; t += 4 * G) {
+                    int4 v[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) v[u] = __ldcs(s4 + t + u * G);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) d4[t + u * G] = v[u];
                 }
                 for (; t < n4; t += G) d4[t] = __ldcs(s4 + t);
             }
@@ -108,7 +115,6 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     int vtp = a.to_play[i];
     const int players = a.players ? a.players : ((p.scratch[0] == -1) ? 1 : 2); // cnode.cpp:776-781
     const float g = a.discount;
-    const float c_base = (float)a.c_base;
     const float mm_delta = mm.y - mm.x;
     const float mm_den = (mm_delta < a.delta) ? a.delta : mm_delta; // CMinMaxStats::normalize (cminimax.cpp:33-45)
     const unsigned hroot = (a.rng_mode == LZB_RNG_PER_ROOT) ? (unsigned)(p.root_offset + i) : 0u;
@@ -144,18 +150,21 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             const float rew = __int_as_float(c[r].w);
             tr[r] = rew;
             if (VP) tr[r] = (h.z == 1) ? rew : rew - parent_reward;
-            val[r] = vis ? __int_as_float(c[r].y) / (float)vc : 0.0f; // CNode::value()
-            const float qsa = vis ? tr[r] + g * val[r] : 0.0f;
-            nvis += __popc(grp.ballot(vis));
+            val[r] = 0.0f;
+            const unsigned wvis = __ballot_sync(kFull, vis);
+            if (wvis) { // warp-uniform: slices without a visited child in any group add nothing
+                val[r] = vis ? __int_as_float(c[r].y) / (float)vc : 0.0f; // CNode::value()
+                const float qsa = vis ? tr[r] + g * val[r] : 0.0f;
+                nvis += __popc((wvis >> grp.shift) & ((G == 32) ? 0xffffffffu : ((1u << (G & 31)) - 1u)));
 #pragma unroll
-            for (int l = 0; l < G; ++l) total += grp.shfl(qsa, l); // j = l + G*r ascending; +0.0f for the rest is exact
+                for (int l = 0; l < G; ++l) total += grp.shfl(qsa, l); // j = l + G*r ascending; +0.0f for the rest is exact
+            }
         }
         const float mean_q = (is_root && nvis > 0) ? total / (float)nvis : (parent_q + total) / (float)(nvis + 1);
 
         // ---- cucb_score
-        const float T = (float)(parent_visits - 1);
-        const float pbc0 = glibc_logf((T + c_base + 1) / c_base) + a.c_init;
-        const float sqT = sqrtf(T);
+        const float2 pt = p.pbc[parent_visits - 1]; // {logf((T + c2 + 1) / c2) + c1, sqrtf(T)}, T = parent visits - 1
+        const float pbc0 = pt.x, sqT = pt.y;
         float sc[R];
         float lmax = -INFINITY;
 #pragma unroll
@@ -195,18 +204,20 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             tie[r] = grp.ballot(j > jstar && sc[r] >= thr); // sc is -inf beyond n
             later += __popc(tie[r]);
         }
-        const unsigned rnd = tiebreak_hash(a.seed, (unsigned)a.sim, hroot, (a.rng_mode == LZB_RNG_PER_ROOT) ? (unsigned)depth : 0u);
-        const int k = (int)(rnd % (unsigned)(later + 1));
         int newpos = jstar;
-        int before = 0; // tie-set members in earlier registers
+        if (__any_sync(kFull, later > 0)) { // warp-uniform: no group has a tie -> no draw
+            const unsigned rnd = tiebreak_hash(a.seed, (unsigned)a.sim, hroot, (a.rng_mode == LZB_RNG_PER_ROOT) ? (unsigned)depth : 0u);
+            const int k = (int)(rnd % (unsigned)(later + 1));
+            int before = 0; // tie-set members in earlier registers
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            // the lane whose tie bit is the k-th one of the set announces itself
-            const bool mybit = (tie[r] >> lane) & 1u;
-            const int rank = before + __popc(tie[r] & ((1u << lane) - 1u)) + 1;
-            const unsigned hit = grp.ballot(mybit && rank == k);
-            newpos = hit ? (__ffs(hit) - 1) + G * r : newpos;
-            before += __popc(tie[r]);
+            for (int r = 0; r < R; ++r) {
+                // the lane whose tie bit is the k-th one of the set announces itself
+                const bool mybit = (tie[r] >> lane) & 1u;
+                const int rank = before + __popc(tie[r] & ((1u << lane) - 1u)) + 1;
+                const unsigned hit = grp.ballot(mybit && rank == k);
+                newpos = hit ? (__ffs(hit) - 1) + G * r : newpos;
+                before += __popc(tie[r]);
+            }
         }
         newpos = any_score ? newpos : 0;
 
@@ -217,14 +228,16 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         for (int r = 1; r < R; ++r) {
             mine.x = (rsel == r) ? c[r].x : mine.x;
             mine.y = (rsel == r) ? c[r].y : mine.y;
-            mine.z = (rsel == r) ? c[r].z : mine.z;
             mine.w = (rsel == r) ? c[r].w : mine.w;
         }
-        const int4 ch = grp.shfl(mine, newpos & (G - 1));
+        int4 ch; // the prior (z) of the chosen child is not needed below
+        ch.x = grp.shfl(mine.x, newpos & (G - 1));
+        ch.y = grp.shfl(mine.y, newpos & (G - 1));
+        ch.w = grp.shfl(mine.w, newpos & (G - 1));
+        ch.z = 0;
         if (going) {
             pos = newpos;
             parent_reset = h.z;
-            action = (VAR != LZB_SEZ && e == 0) ? p.legal[(size_t)i * A + pos] : pos;
             if (players > 1) vtp = (vtp == 1) ? 2 : 1; // cnode.cpp:797-804
             if (lane == 0) {
                 pa[depth] = make_int4(e * B + 1 + pos, ch.x, ch.y, ch.w);
@@ -247,6 +260,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
 
     // ---- leaf bookkeeping (cnode.cpp:814-822) + gather of the parent's rows
     if (live && lane == 0) {
+        action = (VAR != LZB_SEZ && e == 0) ? p.legal[(size_t)i * A + pos] : pos; // root children sit in legal-list order
         p.res[i] = make_int4(depth, e, pos, vtp);
         if (a.ix) a.ix[i] = e;
         if (a.iy) a.iy[i] = i;
@@ -403,7 +417,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 // ---------------------------------------------------------------------------------------------- kernels
 // 128 threads = 128 / G trees per block; groups without a tree (tail of the last block) run along on tree 0, muted
 template <int VAR, int G, int R>
-__global__ void __launch_bounds__(128) k_select_g(Pool p, SelectArgs a)
+__global__ void __launch_bounds__(128, 7) k_select_g(Pool p, SelectArgs a)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
@@ -412,7 +426,7 @@ __global__ void __launch_bounds__(128) k_select_g(Pool p, SelectArgs a)
 }
 
 template <int VAR, int G, int R>
-__global__ void __launch_bounds__(128) k_expand_backup_g(Pool p, BackupArgs b)
+__global__ void __launch_bounds__(128, 7) k_expand_backup_g(Pool p, BackupArgs b)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
@@ -423,7 +437,7 @@ __global__ void __launch_bounds__(128) k_expand_backup_g(Pool p, BackupArgs b)
 
 // fused simulation step (see lzb_step.cuh): expand + backup of simulation s, then select + gather of s + 1
 template <int VAR, int G, int R>
-__global__ void __launch_bounds__(128) k_step_g(Pool p, BackupArgs b, SelectArgs a)
+__global__ void __launch_bounds__(128, 7) k_step_g(Pool p, BackupArgs b, SelectArgs a)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);

@@ -43,6 +43,7 @@ struct Pool {
     float *gumbel;  // [A]     gumbel noise shared by every root (gmz cnode.cpp:87-89)
     int *vtable;    // [S]     considered-visit sequence of the current Gumbel config
     int *scratch;   // [4]     {max(to_play), ...}
+    float2 *pbc;    // [S+2]   per parent visit count T: {logf((T + c2 + 1) / c2) + c1, sqrtf(T)} (cucb_score, cnode.cpp:673-674)
     const char **slots; // [kMaxGathers][E] base pointer of the [N, row] tensor that holds the rows gathered for
                         //          leaves whose parent was expanded as e (latent, LSTM c, LSTM h)
 
