@@ -41,7 +41,8 @@ def parse_args():
     ap.add_argument("--sims", type=int, default=50)
     ap.add_argument("--actions", type=int, default=18)
     ap.add_argument("--latent", type=int, default=1024, help="latent floats per root gathered / stored per simulation")
-    ap.add_argument("--variant", default="mz", choices=["mz", "ez"])
+    ap.add_argument("--variant", default="mz", choices=["mz", "ez", "gmz"])
+    ap.add_argument("--two-player", action="store_true", help="to_play alternates 1/2 (board-game sign flips)")
     ap.add_argument("--no-graph", action="store_true", help="value leg: launch per call instead of one CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -51,7 +52,8 @@ def parse_args():
 
 def workload_name(a):
     return "synthetic %s search: %d roots/GPU x %d sims x A=%d, latent %d f32" % (
-        {"mz": "MuZero", "ez": "EfficientZero"}[a.variant], a.roots, a.sims, a.actions, a.latent)
+        {"mz": "MuZero", "ez": "EfficientZero", "gmz": "Gumbel MuZero (m=16)"}[a.variant] + (" 2-player" if a.two_player else ""),
+        a.roots, a.sims, a.actions, a.latent)
 
 
 # --------------------------------------------------------------------------------------------- synthetic inputs
@@ -66,7 +68,8 @@ def make_inputs(a, rank, device):
     inp = dict(
         root_logits=rn(N, A), root_reward=rn(N) * 0.1, root_value=rn(N),
         noise=(gam / gam.sum(1, keepdim=True)).float().contiguous(),
-        to_play=torch.full((N,), -1, dtype=torch.int32, device=device),
+        to_play=(torch.arange(N, device=device, dtype=torch.int32) % 2 + 1) if a.two_player
+        else torch.full((N,), -1, dtype=torch.int32, device=device),
         logits=rn(S, N, A), reward=rn(S, N) * 0.1, value=rn(S, N),
         latent_roots=rn(N, max(L, 1)), model_latent=rn(S, N, max(L, 1)),
     )
@@ -169,8 +172,8 @@ def measure_depth(a, mcts, model, inp, rank):
 
 def make_driver(a, device, graph):
     import lightzero_b200 as lzb
-    cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree}[a.variant]
-    mcts = cls(dict(num_simulations=a.sims, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=DISCOUNT,
+    cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree, "gmz": lzb.GumbelMuZeroMCTSCtree}[a.variant]
+    mcts = cls(dict(num_simulations=a.sims, max_num_considered_actions=16, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=DISCOUNT,
                     value_delta_max=DELTA, device=str(device), cuda_graph=graph, tie_break_seed=TIE_SEED,
                     model=dict(support_scale=300, categorical_distribution=False)))
     mcts.inverse_scalar_transform_handle = lambda x: x  # the synthetic model emits scalars, not categorical supports
@@ -184,7 +187,10 @@ def one_search(a, mcts, model, inp, host=None, rank=0):
     src = host if host is not None else inp
     roots = mcts.roots(a.roots, None)
     roots.root_offset = rank * a.roots  # global root index keys the tie-break stream
-    roots.prepare(NOISE_W, src["noise"], src["root_reward"], src["root_logits"], src["to_play"])
+    if a.variant == "gmz":
+        roots.prepare(NOISE_W, src["noise"], src["root_reward"], src["root_value"], src["root_logits"], src["to_play"])
+    else:
+        roots.prepare(NOISE_W, src["noise"], src["root_reward"], src["root_logits"], src["to_play"])
     if a.variant == "ez":
         mcts.search(roots, model, src["latent_roots"], (src["hidden_c"], src["hidden_h"]), src["to_play"])
     else:
@@ -291,7 +297,8 @@ def cpu_inputs(a, n, seed):
     f = lambda *s: rng.standard_normal(s).astype(np.float32)
     return dict(root_logits=f(n, A), root_reward=f(n) * np.float32(0.1), root_value=f(n),
                 noises=[r for r in rng.dirichlet([ALPHA] * A, size=n).astype(np.float32)],
-                to_play=np.full(n, -1, np.int32), logits=f(S, n, A),
+                to_play=(np.arange(n, dtype=np.int32) % 2 + 1) if getattr(a, "two_player", False) else np.full(n, -1, np.int32),
+                logits=f(S, n, A),
                 reward=(f(S, n) if a.variant == "ez" else f(S, n) * np.float32(0.1)), value=f(S, n),
                 latent_roots=f(n, L), model_latent=f(S, n, L))
 
@@ -305,13 +312,14 @@ def cpu_search(a, d):
     n = len(d["to_play"])
     kind = "reference" if ref_available(a.variant) else "port"
     t0 = time.perf_counter()
-    f = RefForest(a.variant, n, a.actions, None) if kind == "reference" else OracleForest(a.variant, n, a.actions, None)
+    legal = [list(range(a.actions))] * n  # the policies always pass explicit legal-action lists (muzero.py:671)
+    f = RefForest(a.variant, n, a.actions, legal) if kind == "reference" else OracleForest(a.variant, n, a.actions, legal)
     f.set_delta(DELTA)
     f.set_rng(0 if kind == "reference" else 2, TIE_SEED)  # reference: its own libc rand() stream
     f.prepare(NOISE_W, d["noises"], d["root_reward"], d["root_logits"], d["to_play"], values=d["root_value"])
     pool = [d["latent_roots"]]
     for s in range(a.sims):
-        o = f.traverse(PB_C_BASE, PB_C_INIT, DISCOUNT, d["to_play"], num_simulations=a.sims)
+        o = f.traverse(PB_C_BASE, PB_C_INIT, DISCOUNT, d["to_play"], num_simulations=a.sims, max_considered=16)
         leaf = np.asarray([pool[ix][iy] for ix, iy in zip(o["ix"].tolist(), o["iy"].tolist())])  # noqa: F841
         pool.append(d["model_latent"][s])
         is_reset = (o["search_len"] % 5 == 0).astype(np.int32) if a.variant == "ez" else None
@@ -454,11 +462,13 @@ def run_b200_arm(a):
     h2d = d2h = 0
     if not a.no_e2e:
         pin = lambda t: t.detach().cpu().pin_memory()
-        host = {k: pin(inp[k]) for k in ("root_logits", "noise", "root_reward", "to_play", "latent_roots")}
+        host = {k: pin(inp[k]) for k in ("root_logits", "noise", "root_reward", "root_value", "to_play", "latent_roots")}
         if a.variant == "ez":
             host["hidden_c"], host["hidden_h"] = pin(inp["hidden_c"]), pin(inp["hidden_h"])
         host["visits_out"] = torch.empty((N, A), dtype=torch.int32).pin_memory()
         host["values_out"] = torch.empty(N, dtype=torch.float32).pin_memory()
+        if a.variant != "gmz":
+            host.pop("root_value")
         h2d = sum(host[k].numel() * host[k].element_size() for k in host if not k.endswith("_out")) + 4 * N  # to_play twice
         d2h = host["visits_out"].numel() * 4 + host["values_out"].numel() * 4
 
