@@ -43,6 +43,7 @@ def parse_args():
     ap.add_argument("--latent", type=int, default=1024, help="latent floats per root gathered / stored per simulation")
     ap.add_argument("--variant", default="mz", choices=["mz", "ez", "gmz"])
     ap.add_argument("--two-player", action="store_true", help="to_play alternates 1/2 (board-game sign flips)")
+    ap.add_argument("--streams", type=int, default=1, help="chunks of roots searched on concurrent CUDA streams (graph mode)")
     ap.add_argument("--no-graph", action="store_true", help="value leg: launch per call instead of one CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -138,6 +139,17 @@ class TableModel:
     def eval(self):
         self.s = 0  # search() calls model.eval() once per search (mcts_ctree.py:242)
 
+    def chunk(self, lo, hi):
+        """The same lookup restricted to roots [lo, hi) (a table is not a function of the latent it is handed)."""
+        sub = dict(self.inp)
+        for k in ("logits", "value", "reward", "model_latent"):
+            sub[k] = self.inp[k][:, lo:hi]
+        m = TableModel.__new__(TableModel)
+        m.inp, m.variant, m.s = sub, self.variant, 0
+        if hasattr(self, "hidden"):
+            m.hidden = tuple(h[:, lo:hi].contiguous() for h in self.hidden)
+        return m
+
     def recurrent_inference(self, latent, *rest):
         i, s = self.inp, self.s
         self.s += 1
@@ -175,6 +187,7 @@ def make_driver(a, device, graph):
     cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree, "gmz": lzb.GumbelMuZeroMCTSCtree}[a.variant]
     mcts = cls(dict(num_simulations=a.sims, max_num_considered_actions=16, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=DISCOUNT,
                     value_delta_max=DELTA, device=str(device), cuda_graph=graph, tie_break_seed=TIE_SEED,
+                    search_streams=a.streams if graph else 1,
                     model=dict(support_scale=300, categorical_distribution=False)))
     mcts.inverse_scalar_transform_handle = lambda x: x  # the synthetic model emits scalars, not categorical supports
     return mcts
@@ -521,10 +534,10 @@ def run_b200_arm(a):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(a), "roots_total": N * world, "sims": S, "actions": A,
                        "latent_f32": a.latent, "model": "table lookup in HBM (no NN time)", "scalar_transform": "identity",
-                       "cuda_graph": not a.no_graph, "l2": "512 MB flush between timed steps; working set > L2",
+                       "cuda_graph": not a.no_graph, "search_streams": 1 if a.no_graph else a.streams, "l2": "512 MB flush between timed steps; working set > L2",
                        "parallelism": "roots sharded x%d, all-gather of root outputs per search" % world,
                        "wall_ms_per_step_incl_flush": round(1e3 * t_wall / a.steps, 3)},
-            "gpu_launches": a.steps * (5 + S + 1),  # init, minmax, prepare, root slots, select, S-1 steps, backup, outputs
+            "gpu_launches": a.steps * (5 + S + 1) * (1 if a.no_graph else a.streams),  # init, minmax, prepare, root slots, select, S-1 steps, backup, outputs
             "clocks": clk,
             "roofline": roofline(a, per_kernel, depth, peak, src),
         }

@@ -128,12 +128,18 @@ class _CtreeDriver:
 
     # ------------------------------------------------------------------ whole-search CUDA graph (cfg.cuda_graph)
     def _graphed(self, roots, model, latent_state_roots, hidden_roots, to_play_batch):
-        """Replays prepare + all S simulation rounds + root outputs as ONE CUDA graph.
+        """Replays prepare + all S simulation rounds + root outputs as ONE CUDA graph (per chunk).
 
         A collector or reanalyze loop searches the same shape over and over; the first search of a shape runs eagerly
         once (warm-up) and is then captured over static device buffers.  Later searches copy their inputs into those
-        buffers and replay, so the host issues one launch per search instead of ~4 per simulation.  The model must be
-        capturable (no host syncs, fixed shapes).  The Roots object receives a copy of the outputs."""
+        buffers and replay, so the host issues one launch per search instead of ~2 per simulation.  The model must be
+        capturable (no host syncs, fixed shapes).  The Roots object receives a copy of the outputs.
+
+        cfg.search_streams = k > 1 cuts the batch into k contiguous chunks of roots, each with its own forest, graph and
+        CUDA stream: trees are independent, so chunk c's host->device copies overlap chunk c-1's simulations and the
+        latency-bound tree kernels of different chunks share the SMs.  Results do not depend on k (the tie-break stream
+        is keyed by the global root index).  A model that is not a pure function of its inputs (table lookups in tests
+        and the bench) must offer ``model.chunk(lo, hi)`` returning the model for roots [lo, hi)."""
         if roots.forest is not None:
             raise RuntimeError("cuda_graph search needs roots that have not been traversed yet")
         if self._sampled:
@@ -146,61 +152,87 @@ class _CtreeDriver:
             to_play_batch = [to_play_batch] * N
         lat0 = _as_tensor(latent_state_roots)
         hid = None if hidden_roots is None else [_as_tensor(h) for h in hidden_roots]
-        tp_host = to_play_batch if not (isinstance(to_play_batch, torch.Tensor) and to_play_batch.is_cuda) else None
-        players = 0 if tp_host is None else (1 if int(np.asarray(tp_host).max()) == -1 else 2)
+        tp = to_play_batch if isinstance(to_play_batch, torch.Tensor) else torch.as_tensor(np.asarray(to_play_batch), dtype=torch.int32)
+        k = max(1, min(int(_get(self._cfg, "search_streams", 1) or 1), N))
+        # players is batch-global (cnode.cpp:776-781): with several chunks it cannot be left to a per-chunk device reduction
+        players = 0 if (tp.is_cuda and k == 1) else (1 if int(tp.max()) == -1 else 2)
         key = (N, roots.action_space_size, S, tuple(lat0.shape), lat0.dtype, id(model), roots._legal is None,
-               p["noise"] is None, players, None if hid is None else tuple(hid[0].shape), str(dev))
+               p["noise"] is None, players, None if hid is None else tuple(hid[0].shape), str(dev), k)
         cache = self.__dict__.setdefault("_graphs", {})
-        g = cache.get(key)
-        if g is None:
-            g = cache[key] = _SearchGraph(self, roots, model, lat0, hid, to_play_batch, dev)
-        g.run(roots, lat0, hid, to_play_batch)
+        chunks = cache.get(key)
+        if chunks is None:
+            from ..sharding import shard_bounds
+            chunks = []
+            for c in range(k):
+                lo, hi = shard_bounds(N, k, c)
+                m = model.chunk(lo, hi) if (k > 1 and hasattr(model, "chunk")) else model
+                stream = torch.cuda.Stream(device=dev) if k > 1 else None
+                chunks.append(_SearchGraph(self, roots, m, lat0, hid, lo, hi, players, dev, stream))
+            cache[key] = chunks
+        main = torch.cuda.current_stream(dev)
+        for g in chunks:
+            g.run(roots, lat0, hid, tp, main)
+        for g in chunks:
+            if g.stream is not None:
+                main.wait_stream(g.stream)
+        if k == 1:
+            roots._cached_outputs = {n: v.clone() for n, v in chunks[0].outs.items()}
+        else:
+            roots._cached_outputs = {n: torch.cat([g.outs[n] for g in chunks], dim=0) for n in chunks[0].outs}
 
     _sampled = False
 
 
 class _SearchGraph:
-    """Static buffers + captured graph of one search shape (see _CtreeDriver._graphed)."""
+    """Static buffers + captured graph of one search shape for roots [lo, hi) (see _CtreeDriver._graphed)."""
 
-    def __init__(self, driver, roots, model, lat0, hid, to_play, dev):
+    def __init__(self, driver, roots, model, lat0, hid, lo, hi, players, dev, stream):
         from ..forest import legal_tensors
         p = roots._prep
-        N, A = roots.num, roots.action_space_size
-        self.driver, self.model, self.dev = driver, model, dev
-        self.static = {k: (None if p[k] is None else torch.empty_like(p[k])) for k in ("logits", "noise", "reward", "to_play", "value")}
+        A = roots.action_space_size
+        n = hi - lo
+        self.driver, self.model, self.dev, self.lo, self.hi, self.stream = driver, model, dev, lo, hi, stream
+        self.static = {k: (None if p[k] is None else torch.empty_like(p[k][lo:hi])) for k in ("logits", "noise", "reward", "to_play", "value")}
         self.noise_weight = p["noise_weight"]
-        self.lat0 = torch.empty(tuple(lat0.shape), dtype=lat0.dtype, device=dev)
-        self.hid = None if hid is None else [torch.empty(tuple(h.shape), dtype=h.dtype, device=dev) for h in hid]
-        self.tp = torch.empty(N, dtype=torch.int32, device=dev)
+        self.lat0 = torch.empty((n,) + tuple(lat0.shape[1:]), dtype=lat0.dtype, device=dev)
+        # hidden states come as [1, N, H] (mcts_ctree.py:727-728)
+        self.hid = None if hid is None else [torch.empty((n, h.numel() // roots.num), dtype=h.dtype, device=dev) for h in hid]
+        self.tp = torch.empty(n, dtype=torch.int32, device=dev)
         self.legal = None
         if roots._legal is not None:
-            cnt, idx = legal_tensors(roots._legal, N, A, roots.variant, dev)
+            cnt, idx = legal_tensors(self._legal_slice(roots), n, A, roots.variant, dev)
             self.legal = (torch.empty_like(cnt), torch.empty_like(idx))
         self.shadow = type(roots).__new__(type(roots))
         self.shadow.__dict__.update(roots.__dict__)
+        self.shadow.root_num = n
+        self.shadow.root_offset = roots.root_offset + lo
         self.shadow._legal = self.legal
         self.shadow.forest = None
         self.shadow._prep = dict(self.static, noise_weight=self.noise_weight)
-        tp_known = not (isinstance(to_play, torch.Tensor) and to_play.is_cuda)
-        self.shadow._players = (1 if int(np.asarray(to_play).max()) == -1 else 2) if tp_known else None
+        self.shadow._players = players if players else None
         self.graph = None
         self.outs = None
+
+    def _legal_slice(self, roots):
+        lg = roots._legal
+        return (lg[0][self.lo:self.hi], lg[1][self.lo:self.hi]) if isinstance(lg, tuple) else lg[self.lo:self.hi]
 
     def _load(self, roots, lat0, hid, to_play):
         from ..forest import legal_tensors
         p = roots._prep
+        lo, hi = self.lo, self.hi
         if p["noise_weight"] != self.noise_weight:
             raise RuntimeError("root_noise_weight changed between searches of one captured shape")
         for k, t in self.static.items():
             if t is not None:
-                t.copy_(p[k], non_blocking=True)
-        self.lat0.copy_(lat0, non_blocking=True)
+                t.copy_(p[k][lo:hi], non_blocking=True)
+        self.lat0.copy_(lat0[lo:hi], non_blocking=True)  # host -> device when the caller hands host latents over
         if self.hid is not None:
             for d, s in zip(self.hid, hid):
-                d.copy_(s.reshape(d.shape), non_blocking=True)
-        self.tp.copy_(_dev(to_play, torch.int32, self.dev).reshape(-1), non_blocking=True)
+                d.copy_(s.reshape(roots.num, -1)[lo:hi], non_blocking=True)
+        self.tp.copy_(to_play.reshape(-1)[lo:hi], non_blocking=True)
         if self.legal is not None:
-            cnt, idx = legal_tensors(roots._legal, roots.num, roots.action_space_size, roots.variant, self.dev)
+            cnt, idx = legal_tensors(self._legal_slice(roots), hi - lo, roots.action_space_size, roots.variant, self.dev)
             self.legal[0].copy_(cnt, non_blocking=True)
             self.legal[1].copy_(idx, non_blocking=True)
 
@@ -216,18 +248,27 @@ class _SearchGraph:
         gum = sh.variant == "gmz"
         return sh.forest.root_outputs(discount=float(self.driver._cfg.discount_factor) if gum else 0.0, gumbel=gum)
 
-    def run(self, roots, lat0, hid, to_play):
-        self._load(roots, lat0, hid, to_play)
-        if self.graph is None:
-            self._body()  # eager warm-up: allocator, lazy uploads (Gumbel tables), cudaFuncSetAttribute
-            torch.cuda.synchronize(self.dev)
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self.outs = self._body()
-            self.graph = g
-        self.graph.replay()
-        roots._cached_outputs = {k: v.clone() for k, v in self.outs.items()}
-        roots._graph_forest = self.shadow.forest
+    def run(self, roots, lat0, hid, to_play, main):
+        if self.stream is not None:
+            self.stream.wait_stream(main)  # the prepared root inputs were produced on the caller's stream
+        with torch.cuda.stream(self.stream) if self.stream is not None else _nullctx():
+            self._load(roots, lat0, hid, to_play)
+            if self.graph is None:
+                self._body()  # eager warm-up: allocator, lazy uploads (Gumbel tables), cudaFuncSetAttribute
+                torch.cuda.synchronize(self.dev)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self.outs = self._body()
+                self.graph = g
+            self.graph.replay()
+
+
+class _nullctx:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
 
 
 def _mz_module():

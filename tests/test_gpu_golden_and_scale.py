@@ -72,6 +72,9 @@ class _Tables:
         o.value, o.reward = self.value[s].unsqueeze(1), self.reward[s].unsqueeze(1)
         return o
 
+    def chunk(self, lo, hi):
+        return self.rows(lo, hi)
+
     def rows(self, lo, hi):
         import copy
         t = copy.copy(self)
@@ -82,11 +85,11 @@ class _Tables:
         return t
 
 
-def _search(T, n, S, graph=False, root_offset=0, seed=7):
+def _search(T, n, S, graph=False, root_offset=0, seed=7, streams=1):
     import torch
     import lightzero_b200 as lzb
     mcts = lzb.MuZeroMCTSCtree(dict(num_simulations=S, discount_factor=0.997, value_delta_max=0.01, device="cuda",
-                                    cuda_graph=graph, tie_break_seed=seed,
+                                    cuda_graph=graph, tie_break_seed=seed, search_streams=streams,
                                     model=dict(support_scale=300, categorical_distribution=False)))
     mcts.inverse_scalar_transform_handle = lambda x: x
     tp = torch.full((n,), -1, dtype=torch.int32)
@@ -116,6 +119,11 @@ def test_headline_size_properties_and_invariances():
     v3, x3 = _search(T, n, S, graph=True)
     assert_same(v3, visits, "graph visits")
     assert_same(x3, values, "graph values")
+    # ... also when the batch is cut into 4 chunks searched on concurrent streams (odd chunk count: ragged slices)
+    for k in (4, 3):
+        v5, x5 = _search(T, n, S, graph=True, streams=k)
+        assert_same(v5, visits, "%d-stream visits" % k)
+        assert_same(x5, values, "%d-stream values" % k)
     # sharding invariance: two half batches with global root offsets == the full batch
     h = n // 2
     va, xa = _search(T.rows(0, h), h, S, root_offset=0)
