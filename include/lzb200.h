@@ -187,6 +187,16 @@ int lzb_dump_paths(lzb_forest_t *f, int32_t *path_actions_dev, int path_stride, 
 int lzb_minmax(lzb_forest_t *f, float *min_dev, float *max_dev, void *stream);
 int lzb_root_stats(lzb_forest_t *f, int32_t *visit_dev, float *value_sum_dev, float *reward_dev, void *stream);
 
+/* The K actions a Sampled-EfficientZero node draws when it is expanded (sez cnode.cpp:236-283 continuous: tanh of a
+ * Gaussian per dimension, logits = {mu[D], sigma[D]}; :326-406 discrete: K of A without replacement, keys u^(1/p)).
+ * out [N, K, D] (D = 1 and the action id as float for discrete) is what lzb_prepare / lzb_backprop take as
+ * sampled_actions.  Counter-based: draws are a function of (seed, counter, root_offset + i, k) only; the reference
+ * seeds from the wall clock, so only the distribution is comparable.  uniforms_dev (tests, else NULL): u in (0,1),
+ * [N, K, D, 2] continuous (Box-Muller pairs) or [N, A] discrete. */
+int lzb_sample_actions(const float *logits_dev, const float *uniforms_dev, float *out_dev, int num_roots, int num_sampled,
+                       int action_dim, int action_space, int continuous, int root_offset, uint64_t seed, uint32_t counter,
+                       void *stream);
+
 /* Gumbel constants exposed for tests (gmz_tree.pyx:134-152): host buffers. */
 int lzb_gumbel_table(int max_num_considered_actions, int num_simulations, int32_t *out_host);
 int lzb_gumbel_noise(float scale, int shape, float *out_host);

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "liblzb200.so")
-SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_group.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
+SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_group.cuh", "lzb_sample.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",  # B200 only
@@ -103,6 +103,7 @@ _PROTOS = {
     "lzb_dump_paths": (C.c_int, [_P, _P, C.c_int, _P]),
     "lzb_minmax": (C.c_int, [_P, _P, _P, _P]),
     "lzb_root_stats": (C.c_int, [_P, _P, _P, _P, _P]),
+    "lzb_sample_actions": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint32, _P]),
     "lzb_gumbel_table": (C.c_int, [C.c_int, C.c_int, _P]),
     "lzb_gumbel_noise": (C.c_int, [C.c_float, C.c_int, _P]),
     "lzb_test_expf": (C.c_int, [_P, _P, C.c_int64, _P]),

@@ -9,6 +9,7 @@
 
 #include "../../include/lzb200.h"
 #include "lzb_group.cuh"
+#include "lzb_sample.cuh"
 #include "lzb_step.cuh"
 
 using namespace lzb;
@@ -741,6 +742,20 @@ int lzb_root_stats(lzb_forest_t *f, int32_t *visit_dev, float *value_sum_dev, fl
 {
     if (!f || !visit_dev || !value_sum_dev || !reward_dev) return fail(LZB_E_ARG, "root_stats: bad argument");
     k_root_stats<<<(f->pool.N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(f->pool, visit_dev, value_sum_dev, reward_dev);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_sample_actions(const float *logits_dev, const float *uniforms_dev, float *out_dev, int num_roots, int num_sampled,
+                       int action_dim, int action_space, int continuous, int root_offset, uint64_t seed, uint32_t counter,
+                       void *stream)
+{
+    if (!logits_dev || !out_dev || num_roots <= 0 || num_sampled <= 0) return fail(LZB_E_ARG, "sample_actions: bad argument");
+    if (continuous ? action_dim <= 0 : (action_space <= 0 || action_space > 256 || action_dim != 1))
+        return fail(LZB_E_ARG, "sample_actions: continuous needs action_dim > 0; discrete needs 0 < action_space <= 256 and action_dim == 1");
+    if (!continuous && num_sampled > action_space) return fail(LZB_E_ARG, "sample_actions: cannot draw %d of %d actions without replacement", num_sampled, action_space);
+    SampleArgs a{logits_dev, uniforms_dev, out_dev, num_roots, num_sampled, action_dim, action_space, continuous, root_offset, seed, counter};
+    k_sample_actions<<<(num_roots + 3) / 4, 128, 0, (cudaStream_t)stream>>>(a);
     LZB_CUDA(cudaGetLastError());
     return LZB_OK;
 }

@@ -30,10 +30,13 @@ class Roots(RootsBase):
     def _store_prepare(self, noise_weight, noises, value_prefix_pool, policy_logits_pool, to_play_batch, values=None,
                        sampled_actions=None):
         if sampled_actions is None:
-            from ...tree_search.sampling import sample_actions
+            from ...tree_search.sampling import new_sample_seed, sample_actions
+            from .._tree_api import _tie_seed
+            self.sample_seed = new_sample_seed(_tie_seed[0])
             sampled_actions = sample_actions(_dev(policy_logits_pool, torch.float32, self._device),
                                              self.env_action_space_size, self.num_of_sampled_actions,
-                                             self.continuous_action_space)
+                                             self.continuous_action_space, seed=self.sample_seed, counter=0,
+                                             root_offset=self.root_offset)
         sa = _dev(sampled_actions, torch.float32, self._device)
         if sa.dim() != 3 or sa.shape[0] != self.root_num or sa.shape[1] != self.num_of_sampled_actions:
             raise ValueError("sampled_actions must be [root_num, num_of_sampled_actions, action_dim]")
@@ -81,7 +84,9 @@ def batch_backpropagate(current_latent_state_index, discount_factor, value_prefi
     f = results.forest
     if sampled_actions is None:
         from ...tree_search.sampling import sample_actions
-        sampled_actions = sample_actions(_dev(policies, torch.float32, f.device), results.roots.env_action_space_size,
-                                         f.A, results.roots.continuous_action_space)
+        r = results.roots
+        sampled_actions = sample_actions(_dev(policies, torch.float32, f.device), r.env_action_space_size, f.A,
+                                         r.continuous_action_space, seed=getattr(r, "sample_seed", 0),
+                                         counter=int(current_latent_state_index), root_offset=r.root_offset)
     backprop_tensors(results, current_latent_state_index, discount_factor, value_prefixs, values, None, to_play_batch,
                      is_reset=is_reset_list, sampled_actions=sampled_actions)

@@ -30,5 +30,9 @@ class SampledEfficientZeroMCTSCtree(EfficientZeroMCTSCtree):
         return o["last_action_f"] if self._continuous(roots) else o["last_action"]
 
     def _expand_inputs(self, roots, net):
+        # draws are keyed by (search seed, expansion index, global root, k): csrc/lzb_sample.cuh
+        roots._expansions = getattr(roots, "_expansions", 0) + 1
         return dict(sampled_actions=sample_actions(net.policy_logits, roots.env_action_space_size,
-                                                   roots.num_of_sampled_actions, self._continuous(roots)))
+                                                   roots.num_of_sampled_actions, self._continuous(roots),
+                                                   seed=getattr(roots, "sample_seed", 0), counter=roots._expansions,
+                                                   root_offset=roots.root_offset))
