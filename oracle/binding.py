@@ -128,6 +128,35 @@ class _ForestBase:
                           m.get("sampled_actions"))
 
 
+    def run_search_reuse(self, model_fn, S, pb_c_base, pb_c_init, discount, to_play, true_action, reuse_value,
+                         lstm_horizon_len=5, record=None):
+        """Restates ``search_with_reuse`` (mcts_ctree.py:323-420; EZ :829-953): trees whose traverse stopped on an
+        already expanded root child skip inference, model outputs are COMPACTED over the others (``count_b``).
+        model_fn returns per-tree tables; row i is what the model would return for tree i's leaf.
+        ``is_reset`` is derived per TREE from its own search length; the reference driver builds that list from the
+        compacted lengths but cnode.cpp (ez:640) indexes it by tree, which only agrees when every tree infers."""
+        tp = np.asarray(to_play, np.int32)
+        ta = np.asarray(true_action, np.int32)
+        rv = np.asarray(reuse_value, np.float32)
+        infer_sum, length = 0, 0
+        for s in range(S):
+            out = self.traverse_reuse(pb_c_base, pb_c_init, discount, tp, ta, rv)
+            infer = out["ix"] != -1
+            no_inference_lst = [int(v) for v in out["iy"][~infer]] + [-1]
+            reuse_lst = [i for i in range(self.n) if out["ix"][i] == 0 and out["last_action"][i] == ta[i]] + [-1]
+            m = model_fn(s, out["ix"], out["iy"], out["last_action"])
+            is_reset = None
+            if self.variant == "ez":
+                is_reset = (out["search_len"] % lstm_horizon_len == 0).astype(np.int32)
+            if record is not None:
+                record.append(dict(out, is_reset=is_reset))
+            self.backprop_reuse(s + 1, discount, m["reward"][infer], m["value"][infer], m["logits"][infer], is_reset,
+                                out["vtp"], no_inference_lst, reuse_lst, rv)
+            length = int(infer.sum())
+            infer_sum += length
+        return length, infer_sum / S
+
+
 class OracleForest(_ForestBase):
     def __init__(self, variant, n, A, legal_actions=None, K=0, D=0, continuous=False):
         self.L = oracle_lib()
@@ -181,6 +210,23 @@ class OracleForest(_ForestBase):
         self.L.orc_backprop(self.h, int(latent_index), C.c_float(discount), _ptr(rewards, C.c_float),
                             _ptr(values, C.c_float), _ptr(logits, C.c_float), _ptr(is_reset, C.c_int),
                             _ptr(to_play, C.c_int), _ptr(sa, C.c_float))
+
+    def traverse_reuse(self, pb_c_base, pb_c_init, discount, to_play, true_action, reuse_value):
+        tp, ta, rv = _i(to_play), _i(true_action), _f(reuse_value)
+        o = {k: np.zeros(self.n, np.int32) for k in ("ix", "iy", "last_action", "search_len", "vtp")}
+        self.L.orc_traverse_reuse(self.h, int(pb_c_base), C.c_float(pb_c_init), C.c_float(discount), _ptr(tp, C.c_int),
+                                  _ptr(ta, C.c_int), _ptr(rv, C.c_float), _ptr(o["ix"], C.c_int), _ptr(o["iy"], C.c_int),
+                                  _ptr(o["last_action"], C.c_int), _ptr(o["search_len"], C.c_int), _ptr(o["vtp"], C.c_int))
+        return o
+
+    def backprop_reuse(self, latent_index, discount, rewards, values, logits, is_reset, to_play, no_inference_lst,
+                       reuse_lst, reuse_value):
+        rewards, values, logits = _f(rewards), _f(values), _f(logits)
+        is_reset, to_play, rv = _i(is_reset), _i(to_play), _f(reuse_value)
+        ni, ru = _i(no_inference_lst), _i(reuse_lst)
+        self.L.orc_backprop_reuse(self.h, int(latent_index), C.c_float(discount), _ptr(rewards, C.c_float),
+                                  _ptr(values, C.c_float), _ptr(logits, C.c_float), _ptr(is_reset, C.c_int),
+                                  _ptr(to_play, C.c_int), _ptr(ni, C.c_int), _ptr(ru, C.c_int), _ptr(rv, C.c_float))
 
     def distributions(self):
         d = np.zeros((self.n, self.W), np.int32)
@@ -289,6 +335,24 @@ class RefForest(_ForestBase):
         self.L.ref_backprop(self.h, int(latent_index), C.c_float(discount), _ptr(rewards, C.c_float),
                             _ptr(values, C.c_float), _ptr(logits, C.c_float), _ptr(is_reset, C.c_int),
                             _ptr(to_play, C.c_int))
+
+    def traverse_reuse(self, pb_c_base, pb_c_init, discount, to_play, true_action, reuse_value):
+        tp, ta, rv = _i(to_play), _i(true_action), _f(reuse_value)
+        o = {k: np.zeros(self.n, np.int32) for k in ("ix", "iy", "last_action", "search_len", "vtp")}
+        self.L.ref_traverse_reuse(self.h, int(pb_c_base), C.c_float(pb_c_init), C.c_float(discount), _ptr(tp, C.c_int),
+                                  _ptr(ta, C.c_int), _ptr(rv, C.c_float), _ptr(o["ix"], C.c_int), _ptr(o["iy"], C.c_int),
+                                  _ptr(o["last_action"], C.c_int), _ptr(o["search_len"], C.c_int), _ptr(o["vtp"], C.c_int))
+        return o
+
+    def backprop_reuse(self, latent_index, discount, rewards, values, logits, is_reset, to_play, no_inference_lst,
+                       reuse_lst, reuse_value):
+        rewards, values, logits = _f(rewards), _f(values), _f(logits)
+        is_reset, to_play, rv = _i(is_reset), _i(to_play), _f(reuse_value)
+        ni, ru = _i(no_inference_lst), _i(reuse_lst)
+        self.L.ref_backprop_reuse(self.h, int(latent_index), C.c_float(discount), _ptr(rewards, C.c_float),
+                                  _ptr(values, C.c_float), _ptr(logits, C.c_float), _ptr(is_reset, C.c_int),
+                                  _ptr(to_play, C.c_int), _ptr(ni, C.c_int), _ptr(ru, C.c_int), _ptr(rv, C.c_float),
+                                  int(len(values)))
 
     def distributions(self):
         d = np.zeros((self.n, self.A), np.int32)

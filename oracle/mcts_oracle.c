@@ -241,6 +241,60 @@ static int select_child(const OrcForest *f, const Node *nd, const MinMax *mm, in
     return pos;
 }
 
+/* carm_score (mz:700-753; ez:816-878): the root child on the trajectory's true action is scored with the value the
+ * NEXT state's search produced (ReZero, arXiv 2404.16364) and, once visited, loses its exploration term. */
+static float arm_score(const OrcForest *f, const Node *parent, const Node *child, const MinMax *mm, float parent_mean_q,
+                       float reuse_value, float total_children_visit_counts, float pb_c_base, float pb_c_init,
+                       float discount, int players)
+{
+    float pb_c = orc_logf((total_children_visit_counts + pb_c_base + 1) / pb_c_base) + pb_c_init;
+    pb_c *= (sqrtf(total_children_visit_counts) / (float)(child->visit_count + 1));
+    float prior_score = pb_c * child->prior;
+    float value_score = 0.0f;
+    if (child->visit_count == 0) {
+        value_score = parent_mean_q;
+    } else {
+        float r = true_reward(f, parent, child); /* ez:833-837 */
+        if (players == 1) value_score = r + discount * reuse_value;
+        else if (players == 2) value_score = r + discount * (-reuse_value);
+    }
+    value_score = mm_normalize(mm, value_score);
+    if (value_score < 0) value_score = 0;
+    if (value_score > 1) value_score = 1;
+    return (child->visit_count == 0) ? prior_score + value_score : value_score; /* mz:743-751 */
+}
+
+/* cselect_root_child (mz:598-653; ez:697-752). Returns child position. */
+static int select_root_child(const OrcForest *f, const Node *nd, const MinMax *mm, int pb_c_base, float pb_c_init,
+                             float discount, float mean_q, int players, int true_action, float reuse_value,
+                             uint32_t root, uint32_t depth)
+{
+    float max_score = FLOAT_MIN;
+    const float epsilon = 0.000001f;
+    int *ties = (int *)malloc(sizeof(int) * (size_t)(nd->n_legal > 0 ? nd->n_legal : 1));
+    int n_ties = 0;
+    for (int j = 0; j < nd->n_legal; ++j) {
+        float s;
+        if (nd->legal[j] == true_action)
+            s = arm_score(f, nd, &nd->children[j], mm, mean_q, reuse_value, (float)(nd->visit_count - 1),
+                          (float)pb_c_base, pb_c_init, discount, players);
+        else
+            s = ucb_score(f, nd, &nd->children[j], mm, mean_q, (float)(nd->visit_count - 1), (float)pb_c_base,
+                          pb_c_init, discount, players);
+        if (max_score < s) {
+            max_score = s;
+            n_ties = 0;
+            ties[n_ties++] = j;
+        } else if (s >= max_score - epsilon) {
+            ties[n_ties++] = j;
+        }
+    }
+    int pos = -1;
+    if (n_ties > 0) pos = ties[pinned_rand(f, root, depth) % n_ties];
+    free(ties);
+    return pos;
+}
+
 /* ------------------------------------------------------------------ Gumbel MuZero (gmz:701-790, 904-1152) */
 
 /* csoftmax (gmz:904-933): exp(x - m - log(sum)) form, float throughout. */
@@ -569,6 +623,94 @@ void orc_backprop(OrcForest *f, int latent_index, float discount, const float *r
             node_expand(leaf, to_play[i], latent_index, i, rewards[i], values[i], logits + (size_t)i * f->A, f->A);
         if (is_vp(f)) leaf->is_reset = is_reset ? is_reset[i] : 0;
         backpropagate(f, f->paths[i], f->path_len[i], &f->mm[i], to_play[i], values[i], discount);
+    }
+}
+
+/* cbatch_traverse_with_reuse (mz:826-928; ez:965-1073), MuZero / EfficientZero trees only. */
+void orc_traverse_reuse(OrcForest *f, int pb_c_base, float pb_c_init, float discount, const int *to_play,
+                        const int *true_action, const float *reuse_value, int *ix, int *iy, int *last_action,
+                        int *search_len, int *vtp)
+{
+    float parent_q = 0.0f;
+    int largest = to_play[0];
+    for (int i = 1; i < f->n; ++i)
+        if (to_play[i] > largest) largest = to_play[i];
+    int players = (largest == -1) ? 1 : 2;
+    int last = -1;
+    for (int i = 0; i < f->n; ++i) {
+        Node *node = &f->roots[i];
+        int is_root = 1, len = 0, cap = 8, v = to_play[i];
+        Node **path = (Node **)malloc(sizeof(Node *) * (size_t)cap);
+        int plen = 0;
+        path[plen++] = node;
+        if (f->rng_mode == 2) parent_q = 0.0f;
+        while (node->n_children > 0) {
+            float mean_q = compute_mean_q(f, node, is_root, parent_q, discount);
+            parent_q = mean_q;
+            int pos;
+            if (is_root)
+                pos = select_root_child(f, node, &f->mm[i], pb_c_base, pb_c_init, discount, mean_q, players,
+                                        true_action[i], reuse_value[i], (uint32_t)i, (uint32_t)len);
+            else
+                pos = select_child(f, node, &f->mm[i], pb_c_base, pb_c_init, discount, mean_q, players, (uint32_t)i,
+                                   (uint32_t)len);
+            if (pos < 0) pos = 0;
+            if (players > 1) v = (v == 1) ? 2 : 1;
+            int action = node->legal[pos];
+            node->best_action = action;
+            node = &node->children[pos];
+            last = action;
+            if (plen == cap) { cap *= 2; path = (Node **)realloc(path, sizeof(Node *) * (size_t)cap); }
+            path[plen++] = node;
+            len += 1;
+            if (is_root && action == true_action[i]) break; /* mz:895-898: stop on the trajectory's own action */
+            is_root = 0;
+        }
+        if (node->n_children > 0) { /* already expanded: nothing to infer (mz:904-913) */
+            ix[i] = -1;
+            iy[i] = i;
+        } else {
+            Node *parent = path[plen - 2];
+            ix[i] = parent->latent_index;
+            iy[i] = parent->batch_index;
+        }
+        last_action[i] = last;
+        search_len[i] = len;
+        vtp[i] = v;
+        free(f->paths[i]);
+        f->paths[i] = path;
+        f->path_len[i] = plen;
+    }
+    f->sim += 1;
+}
+
+/* cbatch_backpropagate_with_reuse (mz:502-549; ez:603-644).  rewards / values / logits are COMPACTED over the trees
+ * that needed inference (count_b); no_inference_lst and reuse_lst are ascending tree indices terminated by -1;
+ * reuse_value and is_reset are indexed by tree. */
+void orc_backprop_reuse(OrcForest *f, int latent_index, float discount, const float *rewards, const float *values,
+                        const float *logits, const int *is_reset, const int *to_play, const int *no_inference_lst,
+                        const int *reuse_lst, const float *reuse_value)
+{
+    int count_a = 0, count_b = 0, count_c = 0;
+    float value_propagate = 0.0f;
+    for (int i = 0; i < f->n; ++i) {
+        Node *leaf = f->paths[i][f->path_len[i] - 1];
+        if (i == no_inference_lst[count_a]) {
+            count_a += 1;
+            value_propagate = reuse_value[i];
+        } else {
+            node_expand(leaf, to_play[i], latent_index, count_b, rewards[count_b], values[count_b],
+                        logits + (size_t)count_b * f->A, f->A);
+            if (i == reuse_lst[count_c]) {
+                value_propagate = reuse_value[i];
+                count_c += 1;
+            } else {
+                value_propagate = values[count_b];
+            }
+            count_b += 1;
+        }
+        if (is_vp(f)) leaf->is_reset = is_reset ? is_reset[i] : 0; /* ez:640 */
+        backpropagate(f, f->paths[i], f->path_len[i], &f->mm[i], to_play[i], value_propagate, discount);
     }
 }
 

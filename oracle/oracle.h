@@ -42,6 +42,12 @@ void orc_traverse(OrcForest *f, int pb_c_base, float pb_c_init, float discount, 
                   float *last_action_f, int *search_len, int *vtp, int *path_actions, int path_stride);
 void orc_backprop(OrcForest *f, int latent_index, float discount, const float *rewards, const float *values,
                   const float *logits, const int *is_reset, const int *to_play, const float *sampled_actions);
+void orc_traverse_reuse(OrcForest *f, int pb_c_base, float pb_c_init, float discount, const int *to_play,
+                        const int *true_action, const float *reuse_value, int *ix, int *iy, int *last_action,
+                        int *search_len, int *vtp);
+void orc_backprop_reuse(OrcForest *f, int latent_index, float discount, const float *rewards, const float *values,
+                        const float *logits, const int *is_reset, const int *to_play, const int *no_inference_lst,
+                        const int *reuse_lst, const float *reuse_value);
 void orc_distributions(OrcForest *f, int *dist, int *len);
 void orc_values(OrcForest *f, float *out);
 void orc_minmax(OrcForest *f, float *mn, float *mx);

@@ -190,6 +190,92 @@ void ref_backprop(void *h, int latent_index, float discount, const float *reward
     }
 }
 
+#if !defined(REF_GMZ)
+// One cbatch_traverse_with_reuse (ctree_muzero cnode.cpp:826-928; ctree_efficientzero :965-1073).
+void ref_traverse_reuse(void *h, int pb_c_base, float pb_c_init, float discount, const int *to_play,
+                        const int *true_action, const float *reuse_value, int *ix, int *iy, int *last_action,
+                        int *search_len, int *vtp)
+{
+    Ref *r = (Ref *)h;
+    int G = r->groups(), gs = r->gsize();
+    for (int g = 0; g < G; ++g) {
+        delete r->res[g];
+        r->res[g] = new tree::CSearchResults(gs);
+        std::vector<int> tp(to_play + g * gs, to_play + (g + 1) * gs);
+        std::vector<int> ta(true_action + g * gs, true_action + (g + 1) * gs);
+        std::vector<float> rv(reuse_value + g * gs, reuse_value + (g + 1) * gs);
+        ref_rng_set((uint32_t)r->sim, (uint32_t)g);
+        tree::cbatch_traverse_with_reuse(r->roots[g], pb_c_base, pb_c_init, discount, r->mm[g], *r->res[g], tp, ta, rv);
+        tree::CSearchResults &s = *r->res[g];
+        for (int k = 0; k < gs; ++k) {
+            int i = g * gs + k;
+            ix[i] = s.latent_state_index_in_search_path[k];
+            iy[i] = s.latent_state_index_in_batch[k];
+            if (r->per_root && ix[i] <= 0) iy[i] = i; // roots and "no inference" entries report the tree's own index
+            last_action[i] = s.last_actions[k];
+            search_len[i] = s.search_lens[k];
+            vtp[i] = s.virtual_to_play_batchs[k];
+        }
+    }
+    r->sim += 1;
+}
+
+// One cbatch_backpropagate_with_reuse (ctree_muzero cnode.cpp:502-549; ctree_efficientzero :603-644).
+// rewards / values / logits are compacted over the trees that infer; the two lists end with -1.
+void ref_backprop_reuse(void *h, int latent_index, float discount, const float *rewards, const float *values,
+                        const float *logits, const int *is_reset, const int *to_play, const int *no_inference_lst,
+                        const int *reuse_lst, const float *reuse_value, int n_infer)
+{
+    Ref *r = (Ref *)h;
+    if (!r->per_root) {
+        std::vector<std::vector<float> > pol;
+        std::vector<float> rw(rewards, rewards + n_infer), vals(values, values + n_infer);
+        for (int k = 0; k < n_infer; ++k)
+            pol.push_back(std::vector<float>(logits + (size_t)k * r->A, logits + (size_t)(k + 1) * r->A));
+        std::vector<int> tp(to_play, to_play + r->n), rst, noinf, reuse;
+        for (int i = 0; i < r->n; ++i) rst.push_back(is_reset ? is_reset[i] : 0);
+        for (int k = 0;; ++k) { noinf.push_back(no_inference_lst[k]); if (no_inference_lst[k] == -1) break; }
+        for (int k = 0;; ++k) { reuse.push_back(reuse_lst[k]); if (reuse_lst[k] == -1) break; }
+        std::vector<float> rv(reuse_value, reuse_value + r->n);
+#if defined(REF_EZ)
+        tree::cbatch_backpropagate_with_reuse(latent_index, discount, rw, vals, pol, r->mm[0], *r->res[0], rst, tp, noinf, reuse, rv);
+#else
+        (void)rst;
+        tree::cbatch_backpropagate_with_reuse(latent_index, discount, rw, vals, pol, r->mm[0], *r->res[0], tp, noinf, reuse, rv);
+#endif
+        return;
+    }
+    int count_a = 0, count_b = 0, count_c = 0;
+    for (int i = 0; i < r->n; ++i) {
+        std::vector<std::vector<float> > pol;
+        std::vector<float> rw, vals, rv(1, reuse_value[i]);
+        std::vector<int> tp(1, to_play[i]), rst(1, is_reset ? is_reset[i] : 0), noinf, reuse;
+        bool infer = true;
+        if (i == no_inference_lst[count_a]) {
+            count_a += 1;
+            noinf.push_back(0);
+            infer = false;
+        } else {
+            rw.push_back(rewards[count_b]);
+            vals.push_back(values[count_b]);
+            pol.push_back(std::vector<float>(logits + (size_t)count_b * r->A, logits + (size_t)(count_b + 1) * r->A));
+            if (i == reuse_lst[count_c]) { count_c += 1; reuse.push_back(0); }
+        }
+        noinf.push_back(-1);
+        reuse.push_back(-1);
+#if defined(REF_EZ)
+        tree::cbatch_backpropagate_with_reuse(latent_index, discount, rw, vals, pol, r->mm[i], *r->res[i], rst, tp, noinf, reuse, rv);
+#else
+        tree::cbatch_backpropagate_with_reuse(latent_index, discount, rw, vals, pol, r->mm[i], *r->res[i], tp, noinf, reuse, rv);
+#endif
+        if (infer) {
+            r->res[i]->nodes[0]->batch_index = count_b; // the compacted index a whole-batch call would have stamped
+            count_b += 1;
+        }
+    }
+}
+#endif
+
 // get_distributions (cnode.cpp:387-403): child visit counts in legal order; dist is [n, A] padded with -1.
 void ref_distributions(void *h, int *dist, int *len)
 {

@@ -14,7 +14,7 @@ class Scenario:
     """Seeded inputs of one search: root logits / rewards / values / noise and per-simulation model outputs."""
 
     def __init__(self, variant, n, A, S, seed=0, legal=None, to_play=None, discount=0.997, max_considered=4,
-                 reward_scale=0.1, zero_model=False, K=0, D=0):
+                 reward_scale=0.1, zero_model=False, K=0, D=0, reuse=False):
         rng = np.random.default_rng(seed)
         self.variant, self.n, self.A, self.S, self.discount, self.m = variant, n, A, S, discount, max_considered
         self.K, self.D = K, D
@@ -36,6 +36,11 @@ class Scenario:
         if variant == "sez":
             self.root_actions = np.tanh(rng.standard_normal((n, K, D))).astype(np.float32)
             self.actions = np.tanh(rng.standard_normal((S, n, K, D))).astype(np.float32)
+
+        self.reuse = reuse
+        if reuse:  # ReZero: the action the trajectory took at each root and the value searched at the next state
+            self.true_action = np.asarray([l[rng.integers(len(l))] for l in self.legal], np.int32)
+            self.reuse_value = (rng.standard_normal(n) * z).astype(np.float32)
 
     def model_fn(self, s, ix, iy, last_action):
         out = dict(reward=self.reward[s], value=self.value[s], logits=self.logits[s])
@@ -67,6 +72,11 @@ def run_cpu(forest, sc, rng_mode, seed, record=None, horizon=5):
         kw["sampled_actions"] = sc.root_actions
     forest.prepare(0.25, sc.noises if sc.variant != "sez" else None, sc.root_reward, sc.root_logits, sc.to_play,
                    values=sc.root_value, **kw)
+    if getattr(sc, "reuse", False):
+        forest.infer_stats = forest.run_search_reuse(sc.model_fn, sc.S, PB_C_BASE, PB_C_INIT, sc.discount, sc.to_play,
+                                                     sc.true_action, sc.reuse_value, lstm_horizon_len=horizon,
+                                                     record=record)
+        return forest
     forest.run_search(sc.model_fn, sc.S, PB_C_BASE, PB_C_INIT, sc.discount, sc.to_play, max_considered=sc.m,
                       lstm_horizon_len=horizon, record=record)
     return forest

@@ -32,6 +32,14 @@ CASES = {
     "gmz_tictactoe": (dict(variant="gmz", n=16, A=9, S=30, seed=11, legal=LEGAL9, discount=1.0, max_considered=3), 1),
     "gmz_gomoku": (dict(variant="gmz", n=32, A=36, S=50, seed=12, discount=1.0, max_considered=6), 1),
     "gmz_m16": (dict(variant="gmz", n=16, A=18, S=50, seed=13, max_considered=16), 1),
+    # ReZero search_with_reuse (mcts_ctree.py:323-420, 829-953)
+    "mz_reuse_a6": (dict(variant="mz", n=32, A=6, S=50, seed=14, reuse=True), 2),
+    "mz_reuse_batch": (dict(variant="mz", n=16, A=18, S=50, seed=15, reuse=True), 1),
+    "mz_reuse_masks_two_player": (dict(variant="mz", n=16, A=9, S=30, seed=16, legal=LEGAL9, to_play=[1, 2] * 8,
+                                       discount=1.0, reuse=True), 2),
+    "ez_reuse_a6": (dict(variant="ez", n=32, A=6, S=50, seed=17, reuse=True), 2),
+    "ez_reuse_two_player": (dict(variant="ez", n=16, A=9, S=30, seed=18, to_play=[2, 1] * 8, discount=1.0,
+                                 reuse=True), 1),
 }
 
 
@@ -39,7 +47,10 @@ def search_summary(forest, sc, rec, trees=3):
     """Everything a parity check looks at, as a flat dict of numpy arrays."""
     out = {}
     for k in ("ix", "iy", "last_action", "search_len", "vtp", "paths"):
-        out[k] = np.stack([r[k] for r in rec])
+        if k in rec[0]:  # the ReZero traverse reports no paths
+            out[k] = np.stack([r[k] for r in rec])
+    if getattr(sc, "reuse", False):
+        out["infer_stats"] = np.asarray(forest.infer_stats, np.float64)
     d, ln = forest.distributions()
     out["dist"], out["dist_len"] = d, ln
     out["values"] = forest.values()
