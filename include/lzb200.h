@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define LZB_ABI_VERSION 1
+#define LZB_ABI_VERSION 2
 
 /* tree flavours */
 #define LZB_MZ 0  /* ctree_muzero */
@@ -123,6 +123,28 @@ typedef struct {
     int32_t zero_if_reset;
 } lzb_gather_t;
 
+/* ReZero search-with-reuse (arXiv 2404.16364): batch_traverse_with_reuse / batch_backpropagate_with_reuse
+ * (mz_tree.pyx:84-107 -> cnode.cpp:502-549, 826-928; ez_tree.pyx:95-121 -> ez cnode.cpp:603-644, 965-1073).
+ * A non-NULL `reuse` in lzb_traverse_io_t / lzb_backprop_io_t selects the reuse flavour of the call; MuZero and
+ * EfficientZero trees with action_space <= 128 only (LZB_E_UNSUPPORTED otherwise).
+ *   traverse: the root child on true_action[i] is scored by carm_score with reuse_value[i]; choosing it ends the
+ *     walk.  A tree that ends on an already expanded child needs no inference: ix[i] = -1, iy[i] = i, nothing is
+ *     gathered for it.  infer_count_dev (may be NULL): incremented by the number of trees that DO need inference.
+ *     iy[i] of the other trees is the batch_index recorded when their leaf's parent was expanded.
+ *   backprop: reward / value / logits stay [N]-row tensors indexed by TREE (rows of no-inference trees are
+ *     ignored), so a device-resident caller runs the model on the full batch.  flags_dev[i] bit 0 = tree i is in
+ *     the reference's no_inference_lst, bit 1 = in reuse_lst; NULL = derive both from the preceding traverse the
+ *     way the reference driver does (mcts_ctree.py:376-384).  batch_index_dev[i] (may be NULL = i): the row tree i
+ *     had in the caller's COMPACTED model batch (count_b, cnode.cpp:536), recorded in the new node so that later
+ *     traverses report it as iy. */
+typedef struct {
+    const int32_t *true_action_dev;
+    const float *reuse_value_dev;
+    int32_t *infer_count_dev;
+    const int32_t *flags_dev;
+    const int32_t *batch_index_dev;
+} lzb_reuse_t;
+
 /* batch_traverse (mz_tree.pyx:95-100 -> cbatch_traverse, cnode.cpp:755-824; ez :886-963; gumbel
  * :834-898; sampled :1110-1187) + the leaf gather.  Outputs [N]: ix (latent_state_index_in_search_path),
  * iy (latent_state_index_in_batch, local index), search_len, vtp (virtual_to_play_batchs),
@@ -136,6 +158,7 @@ typedef struct {
     int32_t *search_len_dev, *vtp_dev;
     const lzb_gather_t *gathers;
     int32_t num_gathers;
+    const lzb_reuse_t *reuse; /* NULL = plain batch_traverse */
 } lzb_traverse_io_t;
 int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse_io_t *io, void *stream);
 
@@ -155,6 +178,7 @@ typedef struct {
     int32_t *is_reset_out_dev;
     const float *sampled_actions_dev;
     lzb_slots_t new_slots;
+    const lzb_reuse_t *reuse; /* NULL = plain batch_backpropagate */
 } lzb_backprop_io_t;
 int lzb_backprop(lzb_forest_t *f, const lzb_backprop_io_t *io, void *stream);
 

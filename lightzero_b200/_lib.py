@@ -65,11 +65,18 @@ class Slots(C.Structure):
     _fields_ = [("ptr", C.c_void_p * 3), ("n", C.c_int32)]
 
 
+class Reuse(C.Structure):
+    """lzb_reuse_t"""
+    _fields_ = [("true_action_dev", C.c_void_p), ("reuse_value_dev", C.c_void_p), ("infer_count_dev", C.c_void_p),
+                ("flags_dev", C.c_void_p), ("batch_index_dev", C.c_void_p)]
+
+
 class TraverseIO(C.Structure):
     """lzb_traverse_io_t"""
     _fields_ = [("to_play_dev", C.c_void_p), ("ix_dev", C.c_void_p), ("iy_dev", C.c_void_p),
                 ("last_action_dev", C.c_void_p), ("last_action_f_dev", C.c_void_p), ("search_len_dev", C.c_void_p),
-                ("vtp_dev", C.c_void_p), ("gathers", C.POINTER(Gather)), ("num_gathers", C.c_int32)]
+                ("vtp_dev", C.c_void_p), ("gathers", C.POINTER(Gather)), ("num_gathers", C.c_int32),
+                ("reuse", C.POINTER(Reuse))]
 
 
 class BackpropIO(C.Structure):
@@ -77,7 +84,7 @@ class BackpropIO(C.Structure):
     _fields_ = [("latent_index", C.c_int32), ("discount", C.c_float), ("reward_dev", C.c_void_p),
                 ("value_dev", C.c_void_p), ("logits_dev", C.c_void_p), ("to_play_dev", C.c_void_p),
                 ("is_reset_dev", C.c_void_p), ("lstm_horizon_len", C.c_int32), ("is_reset_out_dev", C.c_void_p),
-                ("sampled_actions_dev", C.c_void_p), ("new_slots", Slots)]
+                ("sampled_actions_dev", C.c_void_p), ("new_slots", Slots), ("reuse", C.POINTER(Reuse))]
 
 
 _P = C.c_void_p
@@ -123,7 +130,7 @@ def lib():
             fn = getattr(L, name)  # AttributeError here == header and library disagree
             fn.restype = res
             fn.argtypes = args
-        if L.lzb_abi_version() != 1:
+        if L.lzb_abi_version() != 2:
             raise RuntimeError("liblzb200.so ABI version mismatch")
         _lib = L
     return _lib

@@ -52,7 +52,7 @@ constexpr size_t kAlign = 256;
 inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 
 struct Layout {
-    size_t node, root, legal, minmax, path_a, path_b, res, best, actions, gumbel, vtable, scratch, slots, pbc, total;
+    size_t node, root, legal, minmax, path_a, path_b, res, best, bidx, actions, gumbel, vtable, scratch, slots, pbc, total;
 };
 
 Layout make_layout(int variant, int N, int A, int S, int D)
@@ -69,6 +69,7 @@ Layout make_layout(int variant, int N, int A, int S, int D)
     l.path_b = take((size_t)N * E * sizeof(int2));
     l.res = take((size_t)N * sizeof(int4));
     l.best = take((size_t)N * E * sizeof(int));
+    l.bidx = take((size_t)N * E * sizeof(int));
     l.actions = take(variant == LZB_SEZ ? (size_t)N * E * A * D * sizeof(float) : 0);
     l.gumbel = take((size_t)A * sizeof(float));
     l.vtable = take(E * sizeof(int));
@@ -116,6 +117,7 @@ __global__ void k_init(Pool p, const int *legal_count, const int *legal_actions)
     p.minmax[i] = make_float2(kFloatMax, kFloatMin); // CMinMaxStats ctor (cminimax.cpp:7-11)
     p.res[i] = make_int4(0, 0, 0, 0);
     p.best[(size_t)i * p.E] = -1; // CNode::best_action = -1 (cnode.cpp:55-66)
+    p.bidx[(size_t)i * p.E] = i;  // roots expand with batch_index = i (cnode.cpp:335)
 }
 
 __global__ void k_reset_minmax(Pool p)
@@ -219,6 +221,7 @@ __global__ void k_dump_tree(Pool p, int i, int upto, int *visit, float *vsum, fl
     const int A = p.A;
     for (int e = 0; e <= upto; ++e) {
         const int4 h = p.block(i, e)[0];
+        if (h.x == 0) continue; // a ReZero simulation that needed no inference expanded nothing in this tree
         if (threadIdx.x == 0) {
             hdr[e * 4 + 0] = h.x;
             hdr[e * 4 + 1] = h.y;
@@ -358,7 +361,7 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
     p.node = (int4 *)(w + l.node); p.root = (int4 *)(w + l.root); p.slots = (const char **)(w + l.slots); p.pbc = (float2 *)(w + l.pbc);
     p.legal = (int *)(w + l.legal); p.minmax = (float2 *)(w + l.minmax);
     p.path_a = (int4 *)(w + l.path_a); p.path_b = (int2 *)(w + l.path_b); p.res = (int4 *)(w + l.res);
-    p.best = (int *)(w + l.best); p.actions = (float *)(w + l.actions); p.gumbel = (float *)(w + l.gumbel);
+    p.best = (int *)(w + l.best); p.bidx = (int *)(w + l.bidx); p.actions = (float *)(w + l.actions); p.gumbel = (float *)(w + l.gumbel);
     p.vtable = (int *)(w + l.vtable); p.scratch = (int *)(w + l.scratch);
     f->bytes = l.total; f->delta = 0.0f; f->sim = 0; f->expanded = -1; f->vt_m = -1; f->vt_s = -1; f->players_for = nullptr; f->pbc_base = -1; f->pbc_init = 0.0f;
     cudaStream_t st = (cudaStream_t)stream;
@@ -424,6 +427,14 @@ namespace {
 
 // Validates the traverse arguments and fills the kernel-side struct; launches the batch max(to_play) reduction
 // the first time a search sees this to_play buffer (players is batch-global, cnode.cpp:776-781).
+// ReZero reuse lives in the lane-group kernels of the two trees that have it in the reference (mz, ez)
+int check_reuse(const Pool &p)
+{
+    if (p.variant != LZB_MZ && p.variant != LZB_EZ) return fail(LZB_E_UNSUPPORTED, "reuse search exists for the MuZero and EfficientZero trees only");
+    if (p.A > 128 || getenv("LZB_FORCE_WARP_PER_TREE")) return fail(LZB_E_UNSUPPORTED, "reuse search supports action_space <= 128");
+    return LZB_OK;
+}
+
 int fill_select(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse_io_t *io, SelectArgs &a, cudaStream_t st)
 {
     if (!f || !cfg || !io || !io->to_play_dev) return fail(LZB_E_ARG, "forest / cfg / io / to_play is NULL");
@@ -443,6 +454,11 @@ int fill_select(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse
         if (!g.dst_dev || g.row_bytes <= 0 || (g.row_bytes & 3))
             return fail(LZB_E_ARG, "gather %d: NULL destination or row_bytes not a positive multiple of 4", k);
         a.g[k] = Gather{(const char *)g.src_dev, (char *)g.dst_dev, (long long)g.row_bytes, g.zero_if_reset};
+    }
+    if (io->reuse) {
+        if (int rc = check_reuse(p)) return rc;
+        if (!io->reuse->true_action_dev || !io->reuse->reuse_value_dev) return fail(LZB_E_ARG, "reuse: true_action / reuse_value is NULL");
+        a.true_action = io->reuse->true_action_dev; a.reuse_value = io->reuse->reuse_value_dev; a.infer_count = io->reuse->infer_count_dev;
     }
     if (p.variant != LZB_GMZ && (f->pbc_base != cfg->pb_c_base || f->pbc_init != cfg->pb_c_init)) {
         k_pbc_table<<<(p.E + 128) / 128, 128, 0, st>>>(p, cfg->pb_c_base, cfg->pb_c_init);
@@ -479,6 +495,13 @@ int fill_backup(lzb_forest_t *f, const lzb_backprop_io_t *io, BackupArgs &b)
     b = BackupArgs{io->latent_index, io->lstm_horizon_len, io->discount, io->reward_dev, io->value_dev, io->logits_dev,
                    io->sampled_actions_dev, io->to_play_dev, io->is_reset_dev, io->is_reset_out_dev, io->new_slots.n, {}};
     for (int k = 0; k < io->new_slots.n; ++k) b.new_slot[k] = (const char *)io->new_slots.ptr[k];
+    if (io->reuse) {
+        if (int rc = check_reuse(p)) return rc;
+        if (!io->reuse->reuse_value_dev || (!io->reuse->flags_dev && !io->reuse->true_action_dev))
+            return fail(LZB_E_ARG, "reuse: reuse_value is NULL, or neither flags nor true_action given");
+        b.true_action = io->reuse->true_action_dev; b.reuse_value = io->reuse->reuse_value_dev;
+        b.reuse_flags = io->reuse->flags_dev; b.batch_index = io->reuse->batch_index_dev;
+    }
     return LZB_OK;
 }
 
@@ -488,20 +511,20 @@ size_t select_bytes_per_warp(const Pool &p) { return (size_t)p.A * (p.variant ==
 // Lane-group kernels (lzb_group.cuh): G lanes per tree, R child records per lane, chosen from the action space size.
 enum { kSelect = 0, kBackup = 1, kStep = 2 };
 
-template <int VAR, int G, int R>
+template <int VAR, int G, int R, bool REUSE>
 void launch_group(int which, const Pool &p, const BackupArgs *b, const SelectArgs *a, cudaStream_t st)
 {
     const int per_block = 128 / G;
     const dim3 grid((p.N + per_block - 1) / per_block), block(128);
-    if (which == kSelect) k_select_g<VAR, G, R><<<grid, block, 0, st>>>(p, *a);
-    else if (which == kBackup) k_expand_backup_g<VAR, G, R><<<grid, block, 0, st>>>(p, *b);
-    else k_step_g<VAR, G, R><<<grid, block, 0, st>>>(p, *b, *a);
+    if (which == kSelect) k_select_g<VAR, G, R, REUSE><<<grid, block, 0, st>>>(p, *a);
+    else if (which == kBackup) k_expand_backup_g<VAR, G, R, REUSE><<<grid, block, 0, st>>>(p, *b);
+    else k_step_g<VAR, G, R, REUSE><<<grid, block, 0, st>>>(p, *b, *a);
 }
 
 // Lanes per tree G and child records per lane R (G * R >= A).  Fewer records per lane = a shorter dependent chain
 // per tree level, more lanes per tree = more warps; past one resident wave (148 SMs x 32 warps of these kernels)
 // extra warps only queue, so the widest group that still fits one wave is taken, else the narrowest.
-template <int VAR>
+template <int VAR, bool REUSE>
 bool launch_group_for(int which, const Pool &p, const BackupArgs *b, const SelectArgs *a, cudaStream_t st)
 {
     const int A = p.A;
@@ -509,21 +532,21 @@ bool launch_group_for(int which, const Pool &p, const BackupArgs *b, const Selec
     const long long one_wave = 148LL * 28; // warps: __launch_bounds__(128, 7) keeps 7 blocks of 4 warps resident per SM
     auto fits = [&](int G) { return forced ? forced == G : ((long long)p.N * G + 31) / 32 <= one_wave; };
     if (A <= 8) {
-        launch_group<VAR, 8, 1>(which, p, b, a, st);
+        launch_group<VAR, 8, 1, REUSE>(which, p, b, a, st);
     } else if (A <= 16) {
-        if (fits(16)) launch_group<VAR, 16, 1>(which, p, b, a, st);
-        else launch_group<VAR, 8, 2>(which, p, b, a, st);
+        if (fits(16)) launch_group<VAR, 16, 1, REUSE>(which, p, b, a, st);
+        else launch_group<VAR, 8, 2, REUSE>(which, p, b, a, st);
     } else if (A <= 24) {
-        if (fits(32)) launch_group<VAR, 32, 1>(which, p, b, a, st);
-        else if (fits(16)) launch_group<VAR, 16, 2>(which, p, b, a, st);
-        else launch_group<VAR, 8, 3>(which, p, b, a, st);
+        if (fits(32)) launch_group<VAR, 32, 1, REUSE>(which, p, b, a, st);
+        else if (fits(16)) launch_group<VAR, 16, 2, REUSE>(which, p, b, a, st);
+        else launch_group<VAR, 8, 3, REUSE>(which, p, b, a, st);
     } else if (A <= 32) {
-        if (fits(32)) launch_group<VAR, 32, 1>(which, p, b, a, st);
-        else launch_group<VAR, 16, 2>(which, p, b, a, st);
+        if (fits(32)) launch_group<VAR, 32, 1, REUSE>(which, p, b, a, st);
+        else launch_group<VAR, 16, 2, REUSE>(which, p, b, a, st);
     } else if (A <= 64) {
-        launch_group<VAR, 32, 2>(which, p, b, a, st);
+        launch_group<VAR, 32, 2, REUSE>(which, p, b, a, st);
     } else if (A <= 128) {
-        launch_group<VAR, 32, 4>(which, p, b, a, st);
+        launch_group<VAR, 32, 4, REUSE>(which, p, b, a, st);
     } else {
         return false; // wider action spaces: warp-per-tree kernels with shared-memory staging
     }
@@ -534,10 +557,11 @@ bool launch_group_for(int which, const Pool &p, const BackupArgs *b, const Selec
 bool launch_grouped(int which, const Pool &p, const BackupArgs *b, const SelectArgs *a, cudaStream_t st)
 {
     if (getenv("LZB_FORCE_WARP_PER_TREE")) return false; // test hook: exercise the generic kernels on small A
+    const bool reuse = (a && a->true_action) || (b && b->reuse_value);
     switch (p.variant) {
-    case LZB_MZ: return launch_group_for<LZB_MZ>(which, p, b, a, st);
-    case LZB_EZ: return launch_group_for<LZB_EZ>(which, p, b, a, st);
-    case LZB_SEZ: return launch_group_for<LZB_SEZ>(which, p, b, a, st);
+    case LZB_MZ: return reuse ? launch_group_for<LZB_MZ, true>(which, p, b, a, st) : launch_group_for<LZB_MZ, false>(which, p, b, a, st);
+    case LZB_EZ: return reuse ? launch_group_for<LZB_EZ, true>(which, p, b, a, st) : launch_group_for<LZB_EZ, false>(which, p, b, a, st);
+    case LZB_SEZ: return launch_group_for<LZB_SEZ, false>(which, p, b, a, st);
     default: return false; // Gumbel MuZero keeps its shared-memory selection
     }
 }
@@ -637,6 +661,7 @@ int lzb_step(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_backprop_io
     SelectArgs a;
     if (int rc = fill_backup(f, bio, b)) return rc;
     if (int rc = fill_select(f, cfg, tio, a, st)) return rc;
+    if ((bio->reuse != nullptr) != (tio->reuse != nullptr)) return fail(LZB_E_ARG, "step: reuse must be given for both halves or neither");
     a.new_e = b.latent_index;
     for (int k = 0; k < kMaxGathers; ++k) a.new_slot[k] = b.new_slot[k];
     for (int k = 0; k < a.ng; ++k)

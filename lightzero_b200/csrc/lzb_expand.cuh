@@ -74,6 +74,11 @@ struct BackupArgs {
     int *is_reset_out;
     int n_slots;                       // slot pointers of the new node (rows its children's leaves will gather)
     const char *new_slot[kMaxGathers];
+    // ReZero reuse backup (cbatch_backpropagate_with_reuse, cnode.cpp:502-549), lane-group kernels only
+    const int *true_action;    // [N]
+    const float *reuse_value;  // [N]
+    const int *reuse_flags;    // [N] bit 0: tree is in no_inference_lst, bit 1: in reuse_lst; nullptr: derived from the traverse
+    const int *batch_index;    // [N] count_b of tree i in the caller's compacted batch; nullptr: i
 };
 
 // cbatch_backpropagate: CNode::expand of the leaf + cbackpropagate along the recorded path

@@ -102,7 +102,10 @@ __device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a
 
 // pUCT traverse of tree i by a lane group (semantics and citations: select_puct_tree in lzb_select.cuh).
 // `live`: this group has a tree (i < N); dead groups run along on tree 0 with every write predicated off.
-template <int VAR, int G, int R>
+// REUSE = cbatch_traverse_with_reuse (ReZero, cnode.cpp:826-928; ez :965-1073): at the root the child on the
+// trajectory's true action is scored by carm_score (cnode.cpp:700-753) and, when chosen, ends the walk even if it
+// is already expanded; such a tree needs no inference and reports ix = -1.
+template <int VAR, int G, int R, bool REUSE = false>
 __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a, int i, bool live, const Grp<G> &grp)
 {
     constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
@@ -125,6 +128,18 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     float parent_q = 0.0f;
     bool is_root = true;
     bool going = live; // this group is still descending
+    bool no_inference = false;
+    bool is_true[R]; // root position j holds the trajectory's action
+    float reuse_v = 0.0f;
+    if (REUSE) {
+        const int ta = a.true_action[i];
+        reuse_v = a.reuse_value[i];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int j = lane + G * r;
+            is_true[r] = (j < A) && p.legal[(size_t)i * A + j] == ta;
+        }
+    }
 
     while (__any_sync(kFull, going)) {
         // ---- one round of independent reads per level: the header (same address in every lane) and R records per lane
@@ -175,13 +190,16 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             float prior_score;
             if (VAR == LZB_SEZ) prior_score = pb_c / (float)n; // uniform branch, sez cnode.cpp:1078
             else prior_score = pb_c * __int_as_float(c[r].z);
+            // carm_score: the visited arm takes the next state's searched value for its own and has no prior term
+            const bool arm = REUSE && is_root && is_true[r] && vc > 0;
+            const float cv = arm ? reuse_v : val[r];
             float vs;
             if (vc == 0) vs = mean_q;
-            else vs = (players == 1) ? tr[r] + g * val[r] : tr[r] + g * (-val[r]);
+            else vs = (players == 1) ? tr[r] + g * cv : tr[r] + g * (-cv);
             if (mm_delta > 0) vs = (vs - mm.x) / mm_den;
             if (vs < 0) vs = 0;
             if (vs > 1) vs = 1;
-            sc[r] = (j < n) ? prior_score + vs : -INFINITY;
+            sc[r] = (j < n) ? (arm ? vs : prior_score + vs) : -INFINITY;
             lmax = fmaxf(lmax, sc[r]);
         }
         const float gmax = grp.fmax(lmax);
@@ -224,11 +242,18 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         // ---- the chosen child's record lives in lane newpos % G, register newpos / G
         const int rsel = newpos / G;
         int4 mine = c[0];
+        bool mine_true = REUSE && is_true[0];
 #pragma unroll
         for (int r = 1; r < R; ++r) {
             mine.x = (rsel == r) ? c[r].x : mine.x;
             mine.y = (rsel == r) ? c[r].y : mine.y;
             mine.w = (rsel == r) ? c[r].w : mine.w;
+            if (REUSE) mine_true = (rsel == r) ? is_true[r] : mine_true;
+        }
+        bool chose_true = false; // cnode.cpp:895-898
+        if (REUSE) { // the shuffle is executed by every lane (no short-circuit around a full-mask exchange)
+            const int sel_true = grp.shfl((int)mine_true, newpos & (G - 1));
+            chose_true = is_root && sel_true != 0;
         }
         int4 ch; // the prior (z) of the chosen child is not needed below
         ch.x = grp.shfl(mine.x, newpos & (G - 1));
@@ -246,8 +271,9 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             }
             depth += 1;
             const int ce = child_expansion(ch.x);
-            if (ce < 0) {
+            if (ce < 0 || chose_true) {
                 going = false;
+                no_inference = ce >= 0; // cnode.cpp:904-913
             } else {
                 parent_visits = child_visits(ch.x);
                 parent_reward = __int_as_float(ch.w);
@@ -261,14 +287,18 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     // ---- leaf bookkeeping (cnode.cpp:814-822) + gather of the parent's rows
     if (live && lane == 0) {
         action = (VAR != LZB_SEZ && e == 0) ? p.legal[(size_t)i * A + pos] : pos; // root children sit in legal-list order
-        p.res[i] = make_int4(depth, e, pos, vtp);
-        if (a.ix) a.ix[i] = e;
-        if (a.iy) a.iy[i] = i;
+        p.res[i] = make_int4(depth, no_inference ? -1 : e, pos, vtp);
+        if (a.ix) a.ix[i] = no_inference ? -1 : e;
+        if (a.iy) a.iy[i] = (REUSE && !no_inference) ? p.bidx[(size_t)i * p.E + e] : i;
         if (a.search_len) a.search_len[i] = depth;
         if (a.vtp) a.vtp[i] = vtp;
         if (a.last_action) a.last_action[i] = (long long)action;
     }
-    if (!live) return;
+    if (REUSE && a.infer_count) { // one atomic per warp
+        const unsigned m = __ballot_sync(kFull, live && lane == 0 && !no_inference);
+        if ((threadIdx.x & 31) == 0 && m) atomicAdd(a.infer_count, __popc(m));
+    }
+    if (!live || no_inference) return; // nothing to infer: the tree's rows of the model batch are left as they are
     if (VAR == LZB_SEZ) {
         const float *act = p.actions + (((size_t)i * p.E + e) * A + pos) * p.D;
         if (a.last_action_f)
@@ -280,7 +310,10 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
 
 // CNode::expand of the leaf + cbackpropagate along the recorded path by a lane group
 // (semantics and citations: expand_children / expand_backup_tree in lzb_expand.cuh).
-template <int VAR, int G, int R>
+// REUSE = cbatch_backpropagate_with_reuse (cnode.cpp:502-549; ez :603-644): a tree whose traverse ended on an expanded
+// node is not expanded again and backs up reuse_value; a tree that expanded the root's true-action child backs up
+// reuse_value instead of the model's value.
+template <int VAR, int G, int R, bool REUSE = false>
 __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs &a, int i, bool live, const Grp<G> &grp)
 {
     constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
@@ -291,6 +324,21 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     const int to_play = a.to_play[i];
     const float value = a.value[i];
     const float leaf_reward = a.reward[i];
+    bool no_inference = false;
+    float value_propagate = value;
+    if (REUSE) {
+        bool reuse;
+        if (a.reuse_flags) {
+            const int fl = a.reuse_flags[i];
+            no_inference = fl & 1;
+            reuse = fl & 2;
+        } else { // what the reference driver derives from the traverse outputs (mcts_ctree.py:376-384)
+            no_inference = res.y == -1;
+            reuse = res.y == 0 && p.legal[(size_t)i * A + res.z] == a.true_action[i];
+        }
+        if (no_inference || reuse) value_propagate = a.reuse_value[i];
+    }
+    const bool grow = live && !no_inference; // this tree expands its leaf
     // path records are independent of everything above: issue their loads now (first chunk)
     const int4 *pa = p.path_a + (size_t)i * (p.S + 1);
     const int2 *pb = p.path_b + (size_t)i * (p.S + 1);
@@ -299,12 +347,16 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
         if (a.is_reset) leaf_reset = a.is_reset[i];
         else if (a.horizon > 0) leaf_reset = (depth % a.horizon == 0) ? 1 : 0; // mcts_ctree.py:810
         if (a.is_reset_out && lane == 0 && live) a.is_reset_out[i] = leaf_reset;
+        if (REUSE && no_inference && lane == 0 && live) { // results.nodes[i]->is_reset = is_reset_list[i] (ez :640)
+            const int ce = child_expansion(pa[depth - 1].y);
+            reinterpret_cast<int *>(p.block(i, ce))[2] = leaf_reset;
+        }
     }
 
     // ---- expand the leaf as expansion e_new: masked softmax over all A actions (cnode.cpp:118-140)
     int4 *dst = p.block(i, e_new) + 1;
     if (VAR == LZB_SEZ) {
-        if (live) {
+        if (grow) {
 #pragma unroll
             for (int r = 0; r < R; ++r)
                 if (lane + G * r < A) dst[lane + G * r] = make_int4(0, 0, 0, 0);
@@ -334,18 +386,20 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int j = lane + G * r;
-            if (j < A && live) dst[j] = make_int4(0, 0, __float_as_int(t[r] / sum), 0);
+            if (j < A && grow) dst[j] = make_int4(0, 0, __float_as_int(t[r] / sum), 0);
         }
     }
-    if (lane == 0 && live) {
+    if (lane == 0 && grow) {
         dst[-1] = make_int4(A, to_play, leaf_reset, __float_as_int(value));
         p.best[(size_t)i * p.E + e_new] = -1;
+        if (REUSE) p.bidx[(size_t)i * p.E + e_new] = a.batch_index ? a.batch_index[i] : i;
     }
+    if (REUSE && lane == 0 && live && no_inference) dst[-1] = make_int4(0, 0, 0, 0); // this tree has no node e_new (tree dumps skip it)
 
     // ---- backup: node q = depth (leaf) ... 1 are path records q-1, node 0 is the root
     const bool two = (VAR != LZB_GMZ) && (to_play != -1); // cnode.cpp:432; gmz asserts -1 (compiled out)
     const float g = a.discount;
-    float b = value; // bootstrap_value entering the current chunk
+    float b = value_propagate; // bootstrap_value entering the current chunk
     float cmin = kFloatMax, cmax = kFloatMin;
     for (int qhi = depth; __any_sync(kFull, qhi >= 0); qhi -= G) { // every group runs as many chunks as the deepest one
         const int q = qhi - lane;
@@ -359,7 +413,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
             } else {
                 const int4 r = pa[q - 1];
                 slot = r.x; x = r.y; vsum = __int_as_float(r.z); rew = __int_as_float(r.w);
-                if (q == depth) rew = leaf_reward; // expand() stamps the leaf's reward / value_prefix first
+                if (q == depth && !no_inference) rew = leaf_reward; // expand() stamps the leaf's reward / value_prefix first
             }
             if (two) node_tp = (q == depth) ? to_play : pb[q].x;
             if (VP && q >= 1) {
@@ -398,7 +452,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
                 p.root[i] = make_int4(visits, __float_as_int(vsum), __float_as_int(rew), 0);
             } else {
                 int4 *rec = p.tree(i) + slot;
-                const int exp_idx = (q == depth) ? e_new : child_expansion(x);
+                const int exp_idx = (q == depth && !no_inference) ? e_new : child_expansion(x);
                 *reinterpret_cast<int2 *>(rec) = make_int2(child_pack(visits, exp_idx), __float_as_int(vsum));
                 if (q == depth) reinterpret_cast<int *>(rec)[3] = __float_as_int(rew);
             }
@@ -416,36 +470,36 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 
 // ---------------------------------------------------------------------------------------------- kernels
 // 128 threads = 128 / G trees per block; groups without a tree (tail of the last block) run along on tree 0, muted
-template <int VAR, int G, int R>
+template <int VAR, int G, int R, bool REUSE>
 __global__ void __launch_bounds__(128, 7) k_select_g(Pool p, SelectArgs a)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
     const bool live = i < p.N;
-    select_puct_g<VAR, G, R>(p, a, live ? i : 0, live, grp);
+    select_puct_g<VAR, G, R, REUSE>(p, a, live ? i : 0, live, grp);
 }
 
-template <int VAR, int G, int R>
+template <int VAR, int G, int R, bool REUSE>
 __global__ void __launch_bounds__(128, 7) k_expand_backup_g(Pool p, BackupArgs b)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
     const bool live = i < p.N;
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
-    expand_backup_g<VAR, G, R>(p, b, live ? i : 0, live, grp);
+    expand_backup_g<VAR, G, R, REUSE>(p, b, live ? i : 0, live, grp);
 }
 
 // fused simulation step (see lzb_step.cuh): expand + backup of simulation s, then select + gather of s + 1
-template <int VAR, int G, int R>
+template <int VAR, int G, int R, bool REUSE>
 __global__ void __launch_bounds__(128, 7) k_step_g(Pool p, BackupArgs b, SelectArgs a)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
     const bool live = i < p.N;
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
-    expand_backup_g<VAR, G, R>(p, b, live ? i : 0, live, grp);
+    expand_backup_g<VAR, G, R, REUSE>(p, b, live ? i : 0, live, grp);
     __syncwarp(); // the warp's own global writes (records, root, MinMax) are ordered before its reads below
-    select_puct_g<VAR, G, R>(p, a, live ? i : 0, live, grp);
+    select_puct_g<VAR, G, R, REUSE>(p, a, live ? i : 0, live, grp);
 }
 
 } // namespace lzb

@@ -39,6 +39,8 @@ struct Pool {
     int2 *path_b;   // [N][S+1] per level q: {to_play, is_reset} of the node the choice was made AT (node q)
     int4 *res;      // [N]     {search_len, parent expansion (ix), last position, virtual_to_play}
     int *best;      // [N][E]  best_action position chosen at each expanded node (cnode.cpp:806)
+    int *bidx;      // [N][E]  batch_index of each expanded node (row in the caller's model batch; == tree index unless a
+                    //          ReZero caller compacts its batches, cnode.cpp:536); read and written by the reuse kernels only
     float *actions; // [N][E][A][D] sampled-action table (sez only)
     float *gumbel;  // [A]     gumbel noise shared by every root (gmz cnode.cpp:87-89)
     int *vtable;    // [S]     considered-visit sequence of the current Gumbel config

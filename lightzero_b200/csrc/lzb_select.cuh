@@ -24,6 +24,10 @@ struct SelectArgs {
     Gather g[kMaxGathers];
     int new_e;                        // fused step: the expansion index whose slot pointers are not in the table yet, else -1
     const char *new_slot[kMaxGathers];
+    // ReZero reuse traverse (cbatch_traverse_with_reuse, cnode.cpp:826-928), lane-group kernels only
+    const int *true_action;    // [N] the trajectory's action at each root
+    const float *reuse_value;  // [N] value found by the next state's search
+    int *infer_count;          // += trees that stopped on an unexpanded leaf (need inference), or nullptr
 };
 
 // dst[i,:] = rows of the leaf's parent (expansion ix) with 16-byte accesses when rows allow it.  The source is

@@ -232,12 +232,14 @@ def _search_cfg(forest, pb_c_base, pb_c_init, discount, to_play, num_simulations
                            max_num_considered_actions=max_considered, rng_mode=_rng_mode[0], rng_seed=_tie_seed[0])
 
 
-def traverse_tensors(roots, cfg, to_play, results, min_max_stats_lst=None, gathers=(), out=None, max_sims=None):
-    """Device-tensor batch_traverse: returns the dict of [N] device tensors (ix, iy, last_action, search_len, vtp)."""
+def traverse_tensors(roots, cfg, to_play, results, min_max_stats_lst=None, gathers=(), out=None, max_sims=None,
+                     reuse=None):
+    """Device-tensor batch_traverse: returns the dict of [N] device tensors (ix, iy, last_action, search_len, vtp).
+    ``reuse`` = dict(true_action, reuse_value[, infer_count]): batch_traverse_with_reuse."""
     f = roots._materialize(max_sims)
     if min_max_stats_lst is not None:
         min_max_stats_lst._bind(f)
-    o = f.traverse(cfg, to_play, out=out, gathers=gathers)
+    o = f.traverse(cfg, to_play, out=out, gathers=gathers, reuse=reuse)
     results.out = o
     results.forest = f
     results.roots = roots
@@ -274,3 +276,64 @@ def batch_backpropagate_ez(current_latent_state_index, discount_factor, value_pr
         raise RuntimeError("batch_backpropagate needs the ResultsWrapper of the preceding batch_traverse")
     backprop_tensors(results, current_latent_state_index, discount_factor, value_prefixs, values, policies, to_play_batch,
                      is_reset=is_reset_list)
+
+
+def batch_traverse_with_reuse(roots, pb_c_base, pb_c_init, discount_factor, min_max_stats_lst, results,
+                              virtual_to_play_batch, true_action, reuse_value):
+    """mz_tree.pyx:102-107 / ez_tree.pyx:116-121 -> cbatch_traverse_with_reuse (ReZero, cnode.cpp:826-928).  Same four
+    lists as batch_traverse; a tree that needs no inference reports ix = -1 and iy = its own index."""
+    f = roots._materialize()
+    cfg = _search_cfg(f, pb_c_base, pb_c_init, discount_factor, virtual_to_play_batch)
+    o = traverse_tensors(roots, cfg, virtual_to_play_batch, results, min_max_stats_lst,
+                         reuse=dict(true_action=true_action, reuse_value=reuse_value))
+    return o["ix"].tolist(), o["iy"].tolist(), o["last_action"].tolist(), o["vtp"].tolist()
+
+
+def _scatter_compacted(N, A, no_inference_lst, reuse_lst, value_prefixs, values, policies):
+    """The reference passes model outputs COMPACTED over the trees that inferred (count_b, cnode.cpp:527-545) plus two
+    ascending index lists ending in -1.  The library takes rows indexed by tree: scatter, and describe the lists as
+    per-tree flags (bit 0 no inference, bit 1 reuse) and the compacted row of every tree."""
+    skip = np.zeros(N, bool)
+    skip[[i for i in no_inference_lst if i >= 0]] = True
+    flags = skip.astype(np.int32)
+    flags[[i for i in reuse_lst if i >= 0]] |= 2
+    rows = np.flatnonzero(~skip)
+    vp = np.asarray(value_prefixs, np.float32).reshape(-1)
+    va = np.asarray(values, np.float32).reshape(-1)
+    po = np.asarray(policies, np.float32).reshape(-1, A) if len(rows) else np.zeros((0, A), np.float32)
+    if not (len(vp) == len(va) == len(po) == len(rows)):
+        raise ValueError("with_reuse: %d trees need inference but the batches hold %d / %d / %d rows"
+                         % (len(rows), len(vp), len(va), len(po)))
+    reward, value, logits = np.zeros(N, np.float32), np.zeros(N, np.float32), np.zeros((N, A), np.float32)
+    reward[rows], value[rows], logits[rows] = vp, va, po
+    batch_index = (np.cumsum(~skip) - 1).astype(np.int32)
+    return reward, value, logits, flags, batch_index
+
+
+def batch_backpropagate_with_reuse(current_latent_state_index, discount_factor, value_prefixs, values, policies,
+                                   min_max_stats_lst, results, to_play_batch, no_inference_lst, reuse_lst,
+                                   reuse_value_lst):
+    """mz_tree.pyx:84-93 -> cbatch_backpropagate_with_reuse (cnode.cpp:502-549); arguments as the reference's."""
+    if results.out is None:
+        raise RuntimeError("batch_backpropagate_with_reuse needs the ResultsWrapper of the preceding traverse")
+    f = results.forest
+    reward, value, logits, flags, bidx = _scatter_compacted(f.N, f.A, no_inference_lst, reuse_lst, value_prefixs, values,
+                                                            policies)
+    backprop_tensors(results, current_latent_state_index, discount_factor, reward, value, logits, to_play_batch,
+                     reuse=dict(reuse_value=reuse_value_lst, flags=flags, batch_index=bidx))
+
+
+def batch_backpropagate_with_reuse_ez(current_latent_state_index, discount_factor, value_prefixs, values, policies,
+                                      min_max_stats_lst, results, is_reset_list, to_play_batch, no_inference_lst,
+                                      reuse_lst, reuse_value_lst):
+    """ez_tree.pyx:95-106 -> cbatch_backpropagate_with_reuse (ctree_efficientzero/lib/cnode.cpp:603-644).
+    is_reset_list is indexed by TREE, as cnode.cpp:640 reads it."""
+    if results.out is None:
+        raise RuntimeError("batch_backpropagate_with_reuse needs the ResultsWrapper of the preceding traverse")
+    f = results.forest
+    if len(is_reset_list) != f.N:
+        raise ValueError("is_reset_list must have one entry per tree (cnode.cpp:640 indexes it by tree)")
+    reward, value, logits, flags, bidx = _scatter_compacted(f.N, f.A, no_inference_lst, reuse_lst, value_prefixs, values,
+                                                            policies)
+    backprop_tensors(results, current_latent_state_index, discount_factor, reward, value, logits, to_play_batch,
+                     is_reset=is_reset_list, reuse=dict(reuse_value=reuse_value_lst, flags=flags, batch_index=bidx))

@@ -1,6 +1,6 @@
 """Drop-in for lzero/mcts/ctree/ctree_muzero/mz_tree.pyx over the CUDA forest (variant LZB_MZ)."""
-from .._tree_api import (MinMaxStatsList, ResultsWrapper, RootsBase, batch_backpropagate, batch_traverse,  # noqa: F401
-                         set_tie_break)
+from .._tree_api import (MinMaxStatsList, ResultsWrapper, RootsBase, batch_backpropagate,  # noqa: F401
+                         batch_backpropagate_with_reuse, batch_traverse, batch_traverse_with_reuse, set_tie_break)
 
 
 class Roots(RootsBase):

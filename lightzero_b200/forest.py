@@ -9,7 +9,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import BackpropIO, Gather, SearchCfg, Slots, TraverseIO, check
+from ._lib import BackpropIO, Gather, Reuse, SearchCfg, Slots, TraverseIO, check
 
 VARIANT_ID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3}
 RNG_BATCH, RNG_PER_ROOT = 1, 2
@@ -124,7 +124,25 @@ class Forest:
         return SearchCfg(int(pb_c_base), float(pb_c_init), float(discount), int(players), int(num_simulations),
                          int(max_num_considered_actions), int(rng_mode), int(rng_seed))
 
-    def _traverse_io(self, to_play, out, gathers):
+    def _reuse(self, reuse):
+        """lzb_reuse_t from a dict(true_action, reuse_value[, infer_count, flags, batch_index]) of device tensors
+        (ReZero search-with-reuse); returns (pointer | None, keep-alive)."""
+        if reuse is None:
+            return None, None
+        d = self.device
+        ts = dict(true_action=_dev(reuse.get("true_action"), torch.int32, d),
+                  reuse_value=_dev(reuse.get("reuse_value"), torch.float32, d),
+                  infer_count=reuse.get("infer_count"),
+                  flags=_dev(reuse.get("flags"), torch.int32, d),
+                  batch_index=_dev(reuse.get("batch_index"), torch.int32, d))
+        for k in ("true_action", "reuse_value", "flags", "batch_index"):
+            if ts[k] is not None and ts[k].numel() != self.N:
+                raise ValueError("reuse.%s must have N elements" % k)
+        r = Reuse(_p(ts["true_action"]), _p(ts["reuse_value"]), _p(ts["infer_count"]), _p(ts["flags"]),
+                  _p(ts["batch_index"]))
+        return C.pointer(r), (r, ts)
+
+    def _traverse_io(self, to_play, out, gathers, reuse=None):
         d = self.device
         N = self.N
         to_play = _dev(to_play, torch.int32, d)
@@ -154,7 +172,10 @@ class Forest:
         io = TraverseIO(to_play.data_ptr(), o["ix"].data_ptr(), o["iy"].data_ptr(), o["last_action"].data_ptr(),
                         o["last_action_f"].data_ptr() if "last_action_f" in o else None, o["search_len"].data_ptr(),
                         o["vtp"].data_ptr(), garr, len(gathers))
-        return io, (garr, to_play), o
+        rp, rkeep = self._reuse(reuse)
+        if rp is not None:
+            io.reuse = rp
+        return io, (garr, to_play, rkeep), o
 
     def _slots(self, e, tensors):
         sl = Slots()
@@ -176,7 +197,7 @@ class Forest:
         check(self.L.lzb_set_slots(self.h, int(latent_index), C.byref(sl), _stream(self.device)))
 
     def _backprop_io(self, latent_index, discount, reward, value, logits, to_play, is_reset, lstm_horizon_len,
-                     is_reset_out, sampled_actions, new_slots):
+                     is_reset_out, sampled_actions, new_slots, reuse=None):
         d = self.device
         reward = _dev(reward, torch.float32, d).reshape(-1)
         value = _dev(value, torch.float32, d).reshape(-1)
@@ -190,28 +211,34 @@ class Forest:
             raise ValueError("logits must be [N, A]")
         io = BackpropIO(int(latent_index), float(discount), _p(reward), _p(value), _p(logits), _p(to_play), _p(is_reset),
                         int(lstm_horizon_len), _p(is_reset_out), _p(sampled_actions), self._slots(int(latent_index), new_slots))
-        return io, (reward, value, logits, to_play, is_reset, sampled_actions)
+        rp, rkeep = self._reuse(reuse)
+        if rp is not None:
+            io.reuse = rp
+        return io, (reward, value, logits, to_play, is_reset, sampled_actions, rkeep)
 
-    def traverse(self, cfg, to_play, out=None, gathers=()):
+    def traverse(self, cfg, to_play, out=None, gathers=(), reuse=None):
         """One batch_traverse. ``out``: optional dict of preallocated tensors (ix, iy, last_action, last_action_f,
         search_len, vtp); missing ones are allocated. ``gathers``: [(pool[E,N,...] | None, dst[N,...][, zero_if_reset])];
-        None = rows come from the slot table with the gather's index."""
-        io, keep, o = self._traverse_io(to_play, out, gathers)
+        None = rows come from the slot table with the gather's index.  ``reuse``: dict(true_action, reuse_value
+        [, infer_count]) of [N] device tensors = batch_traverse_with_reuse (ReZero)."""
+        io, keep, o = self._traverse_io(to_play, out, gathers, reuse)
         check(self.L.lzb_traverse(self.h, C.byref(cfg), C.byref(io), _stream(self.device)))
         return o
 
     def backprop(self, latent_index, discount, reward, value, logits, to_play, is_reset=None, lstm_horizon_len=0,
-                 is_reset_out=None, sampled_actions=None, new_slots=None):
+                 is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None):
+        """One batch_backpropagate; ``reuse``: dict(reuse_value, true_action | flags[, batch_index]) =
+        batch_backpropagate_with_reuse with reward / value / logits indexed by tree."""
         io, keep = self._backprop_io(latent_index, discount, reward, value, logits, to_play, is_reset, lstm_horizon_len,
-                                     is_reset_out, sampled_actions, new_slots)
+                                     is_reset_out, sampled_actions, new_slots, reuse)
         check(self.L.lzb_backprop(self.h, C.byref(io), _stream(self.device)))
 
     def step(self, cfg, latent_index, discount, reward, value, logits, vtp, to_play, out=None, gathers=(), is_reset=None,
-             lstm_horizon_len=0, is_reset_out=None, sampled_actions=None, new_slots=None):
+             lstm_horizon_len=0, is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None):
         """backprop(latent_index, ..., vtp) of simulation s and traverse(to_play) of simulation s + 1 in ONE launch."""
         bio, keep_b = self._backprop_io(latent_index, discount, reward, value, logits, vtp, is_reset, lstm_horizon_len,
-                                        is_reset_out, sampled_actions, new_slots)
-        tio, keep_t, o = self._traverse_io(to_play, out, gathers)
+                                        is_reset_out, sampled_actions, new_slots, reuse)
+        tio, keep_t, o = self._traverse_io(to_play, out, gathers, reuse)
         check(self.L.lzb_step(self.h, C.byref(cfg), C.byref(bio), C.byref(tio), _stream(self.device)))
         return o
 

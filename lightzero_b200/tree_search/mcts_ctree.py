@@ -126,6 +126,33 @@ class _CtreeDriver:
         return forest, scfg, self._to_play(to_play_batch, forest), api.ResultsWrapper(N), S
 
 
+    # ------------------------------------------------------------------ ReZero search-with-reuse
+    def _reuse_args(self, forest, S, true_action_list, reuse_value_list):
+        """Device copies of the trajectory's action / next state's searched value per root, plus the per-simulation
+        counter the traverse kernels add their inferring trees to."""
+        if true_action_list is None or reuse_value_list is None:
+            raise ValueError("search_with_reuse needs true_action_list and reuse_value_list")
+        dev = forest.device
+        return dict(true_action=_dev(true_action_list, torch.int32, dev).reshape(-1),
+                    reuse_value=_dev(reuse_value_list, torch.float32, dev).reshape(-1),
+                    infer_count=torch.zeros(S, dtype=torch.int32, device=dev))
+
+    @staticmethod
+    def _reuse_at(reuse, s):
+        """The reuse dict of the call whose traverse half belongs to simulation s (None = no traverse half)."""
+        if reuse is None:
+            return None
+        r = dict(reuse)
+        r["infer_count"] = reuse["infer_count"][s:] if s is not None else None
+        return r
+
+    @staticmethod
+    def _reuse_result(reuse):
+        """(length, average_infer) as search_with_reuse returns them (mcts_ctree.py:417-420): trees inferred in the
+        last simulation and the mean over simulations.  The one device->host read of the search."""
+        cnt = reuse["infer_count"].cpu()
+        return int(cnt[-1]), float(cnt.sum()) / cnt.numel()
+
     # ------------------------------------------------------------------ whole-search CUDA graph (cfg.cuda_graph)
     def _graphed(self, roots, model, latent_state_roots, hidden_roots, to_play_batch):
         """Replays prepare + all S simulation rounds + root outputs as ONE CUDA graph (per chunk).
@@ -296,14 +323,28 @@ class MuZeroMCTSCtree(_CtreeDriver):
             return self._graphed(roots, model, latent_state_roots, None, to_play_batch)
         return self._search(roots, model, latent_state_roots, None, to_play_batch)
 
-    def _search(self, roots, model, latent_state_roots, hidden_roots, to_play_batch):
+    def search_with_reuse(self, roots, model, latent_state_roots, to_play_batch, true_action_list=None,
+                          reuse_value_list=None):
+        """mcts_ctree.py:323-420 (ReZero): the root child on the trajectory's own action is scored with the value the
+        next state's search found and is never searched below.  Returns (length, average_infer).  The model runs on
+        the full [N] batch every simulation (rows of trees that need no inference are ignored) so that nothing
+        leaves the device inside the loop; the reference's saving in model rows becomes idle rows instead."""
+        if self.gumbel:
+            raise NotImplementedError("the reference has no search_with_reuse for Gumbel MuZero")
+        return self._search(roots, model, latent_state_roots, None, to_play_batch,
+                            reuse_lists=(true_action_list, reuse_value_list))
+
+    def _search(self, roots, model, latent_state_roots, hidden_roots, to_play_batch, reuse_lists=None):
         with torch.no_grad():
             cfg = self._cfg
             kw = dict(num_simulations=int(cfg.num_simulations), max_considered=int(cfg.max_num_considered_actions)) if self.gumbel else {}
             forest, scfg, tp, results, S = self._begin(roots, model, to_play_batch, **kw)
             discount = cfg.discount_factor
             lat0 = self._on_device(forest, latent_state_roots)
+            reuse = self._reuse_args(forest, S, *reuse_lists) if reuse_lists is not None else None
             if not self._rows_ok(lat0):
+                if reuse is not None:
+                    raise ValueError("search_with_reuse needs latent rows that are a multiple of 4 bytes")
                 return self._search_dense(roots, model, lat0, forest, scfg, tp, results, S)
             # latent_state_batch_in_search_path (mcts_ctree.py:247,305) is a table of S+1 base pointers in HBM: the
             # model's output tensor of simulation s IS slot s+1, nothing is copied into a pool.
@@ -311,7 +352,7 @@ class MuZeroMCTSCtree(_CtreeDriver):
             leaf = torch.empty_like(lat0)
             gathers = [(None, leaf)]
             # stage 1 of simulation 0: selection + gather of each leaf's parent latent (mcts_ctree.py:272-289)
-            o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers)
+            o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers, reuse=self._reuse_at(reuse, 0))
             for simulation_index in range(S):
                 # stage 2: expansion inputs from the model, still on the device (mcts_ctree.py:298-303);
                 # Gumbel MuZero passes the action as [N, 1] (:1090)
@@ -323,10 +364,13 @@ class MuZeroMCTSCtree(_CtreeDriver):
                 if e < S:
                     # stage 3 (expand + backup, :316-321) fused with stage 1 of the next simulation: one launch
                     o = forest.step(scfg, e, discount, reward, value, net.policy_logits, o["vtp"], tp, out=o,
-                                    gathers=gathers, new_slots=[new_lat])
+                                    gathers=gathers, new_slots=[new_lat], reuse=self._reuse_at(reuse, e))
                 else:
-                    forest.backprop(e, discount, reward, value, net.policy_logits, o["vtp"], new_slots=[new_lat])
+                    forest.backprop(e, discount, reward, value, net.policy_logits, o["vtp"], new_slots=[new_lat],
+                                    reuse=self._reuse_at(reuse, None))
                 forest.sims_done += 1
+            if reuse is not None:
+                return self._reuse_result(reuse)
 
     def _search_dense(self, roots, model, lat0, forest, scfg, tp, results, S):
         """Fallback for latent rows that are not a multiple of 4 bytes (e.g. odd-sized fp16): dense pool + torch gather."""
@@ -367,7 +411,16 @@ class EfficientZeroMCTSCtree(_CtreeDriver):
     def _expand_inputs(self, roots, net):
         return dict(logits=net.policy_logits)
 
-    def _search(self, roots, model, latent_state_roots, hidden_roots, to_play_batch):
+    def search_with_reuse(self, roots, model, latent_state_roots, reward_hidden_state_roots, to_play_batch,
+                          true_action_list=None, reuse_value_list=None):
+        """mcts_ctree.py:829-953 (ReZero).  Returns (length, average_infer); see MuZeroMCTSCtree.search_with_reuse.
+        is_reset of every leaf comes from that tree's own search length; the reference builds the list from the
+        compacted lengths but ctree_efficientzero/lib/cnode.cpp:640 indexes it by tree, so the two only agree there
+        when every tree infers."""
+        return self._search(roots, model, latent_state_roots, reward_hidden_state_roots, to_play_batch,
+                            reuse_lists=(true_action_list, reuse_value_list))
+
+    def _search(self, roots, model, latent_state_roots, hidden_roots, to_play_batch, reuse_lists=None):
         with torch.no_grad():
             forest, scfg, tp, results, S = self._begin(roots, model, to_play_batch)
             discount, horizon = self._cfg.discount_factor, int(self._cfg.lstm_horizon_len)
@@ -385,7 +438,8 @@ class EfficientZeroMCTSCtree(_CtreeDriver):
             # the LSTM state of a node expanded with is_reset = 1 reads as zeros (mcts_ctree.py:809-816): the gather
             # applies the reset from the node's flag instead of rewriting the model's output tensor
             gathers = [(None, leaf), (None, leaf_c, True), (None, leaf_h, True)]
-            o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers)
+            reuse = self._reuse_args(forest, S, *reuse_lists) if reuse_lists is not None else None
+            o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers, reuse=self._reuse_at(reuse, 0))
             for simulation_index in range(S):
                 net = model.recurrent_inference(leaf, (leaf_c.unsqueeze(0), leaf_h.unsqueeze(0)), self._leaf_action(roots, o))
                 value = self.inverse_scalar_transform_handle(net.value)
@@ -400,10 +454,13 @@ class EfficientZeroMCTSCtree(_CtreeDriver):
                           new_slots=slots)
                 if e < S:
                     o = forest.step(scfg, e, discount, value_prefix, value, x.get("logits"), o["vtp"], tp, out=o,
-                                    gathers=gathers, **kw)
+                                    gathers=gathers, reuse=self._reuse_at(reuse, e), **kw)
                 else:
-                    forest.backprop(e, discount, value_prefix, value, x.get("logits"), o["vtp"], **kw)
+                    forest.backprop(e, discount, value_prefix, value, x.get("logits"), o["vtp"],
+                                    reuse=self._reuse_at(reuse, None), **kw)
                 forest.sims_done += 1
+            if reuse is not None:
+                return self._reuse_result(reuse)
 
 
 def _as_tensor(x):

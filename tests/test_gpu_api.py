@@ -184,6 +184,90 @@ def test_list_api_module_level_calls_match_oracle():
     assert roots.get_distributions() == []
 
 
+@pytest.mark.parametrize("variant", ["mz", "ez"])
+def test_reuse_list_api_driven_like_the_reference_loop(variant):
+    """batch_traverse_with_reuse / batch_backpropagate_with_reuse with the reference's own bookkeeping around them
+    (mcts_ctree.py:359-416): compacted model batches, no_inference_lst / reuse_lst ending in -1."""
+    from lightzero_b200.ctree.ctree_efficientzero import ez_tree
+    from lightzero_b200.ctree.ctree_muzero import mz_tree
+    tree = mz_tree if variant == "mz" else ez_tree
+    sc = Scenario(variant, 24, 6, 40, seed=46, reuse=True)
+    orc, rec = oracle_run(sc)
+    tree.set_tie_break(SEED)
+    roots = tree.Roots(sc.n, sc.legal)
+    roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_logits.tolist(), sc.to_play.tolist())
+    mm = tree.MinMaxStatsList(sc.n)
+    mm.set_delta(0.01)
+    true_action, reuse_value = sc.true_action.tolist(), sc.reuse_value.tolist()
+    skipped = 0
+    for s in range(sc.S):
+        results = tree.ResultsWrapper(sc.n)
+        ix, iy, last_actions, vtp = tree.batch_traverse_with_reuse(roots, PB_C_BASE, PB_C_INIT, sc.discount, mm, results,
+                                                                  sc.to_play.tolist(), true_action, reuse_value)
+        assert ix == rec[s]["ix"].tolist() and iy == rec[s]["iy"].tolist()  # iy: the compacted batch index
+        assert last_actions == rec[s]["last_action"].tolist()
+        search_lens = results.get_search_len()
+        rows, no_inference_lst, reuse_lst = [], [], []
+        for count, (x, y) in enumerate(zip(ix, iy)):
+            if x != -1:
+                rows.append(count)
+            else:
+                no_inference_lst.append(y)
+            if x == 0 and last_actions[count] == true_action[count]:
+                reuse_lst.append(count)
+        skipped += len(no_inference_lst)
+        no_inference_lst.append(-1)
+        reuse_lst.append(-1)
+        args = (s + 1, sc.discount, sc.reward[s][rows].tolist(), sc.value[s][rows].tolist(), sc.logits[s][rows].tolist(),
+                mm, results)
+        if variant == "ez":
+            is_reset = (np.asarray(search_lens) % 5 == 0).astype(np.int32).tolist()
+            tree.batch_backpropagate_with_reuse(*args, is_reset, vtp, no_inference_lst, reuse_lst, reuse_value)
+        else:
+            tree.batch_backpropagate_with_reuse(*args, vtp, no_inference_lst, reuse_lst, reuse_value)
+    assert skipped > 0
+    check_roots(roots, orc, sc)
+
+
+@pytest.mark.parametrize("variant", ["mz", "ez"])
+def test_search_with_reuse_driver_matches_oracle(variant):
+    import torch
+    import lightzero_b200 as lzb
+    sc = Scenario(variant, 48, 6, 50, seed=47, reuse=True)
+    orc, rec = oracle_run(sc)
+    dev = torch.device("cuda")
+    if variant == "mz":
+        mcts = identity(lzb.MuZeroMCTSCtree(driver_cfg(sc)))
+        roots = lzb.MuZeroMCTSCtree.roots(sc.n, sc.legal)
+        model = ScenarioModel(sc, dev)
+    else:
+        mcts = identity(lzb.EfficientZeroMCTSCtree(driver_cfg(sc)))
+        roots = lzb.EfficientZeroMCTSCtree.roots(sc.n, sc.legal)
+        model = ScenarioModel(sc, dev, hidden=8)
+    roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_logits.tolist(), sc.to_play.tolist())
+    lat = np.zeros((sc.n, 16), np.float32)
+    if variant == "mz":
+        length, average_infer = mcts.search_with_reuse(roots, model, lat, sc.to_play.tolist(), sc.true_action.tolist(),
+                                                       sc.reuse_value.tolist())
+    else:
+        hid = (np.zeros((1, sc.n, 8), np.float32), np.zeros((1, sc.n, 8), np.float32))
+        length, average_infer = mcts.search_with_reuse(roots, model, lat, hid, sc.to_play.tolist(),
+                                                       sc.true_action.tolist(), sc.reuse_value.tolist())
+    assert (length, average_infer) == tuple(orc.infer_stats)
+    assert average_infer < sc.n  # some trees skipped inference
+    check_roots(roots, orc, sc)
+    for s, (lat_s, rest) in enumerate(model.calls):  # inferring trees received their parent's latent
+        need = rec[s]["ix"] != -1
+        assert_same(lat_s[:, 0].cpu().numpy()[need], rec[s]["ix"].astype(np.float32)[need], "sim %d gathered latents" % s)
+
+
+def test_search_with_reuse_is_not_offered_for_gumbel():
+    import lightzero_b200 as lzb
+    sc = Scenario("gmz", 4, 6, 8, seed=48)
+    with pytest.raises(NotImplementedError):
+        lzb.GumbelMuZeroMCTSCtree(driver_cfg(sc)).search_with_reuse(None, None, None, None, [0] * 4, [0.0] * 4)
+
+
 def test_reference_unit_test_shapes_with_zero_model():
     """test_mcts_ctree.py:155-179,240-281: all-zero fake model, 16 x 9 mask; output shapes, per-root distribution
     length == legal count, and argmax action is legal."""

@@ -12,9 +12,11 @@ from tests.common import PB_C_BASE, PB_C_INIT, TICTACTOE_MASKS, Scenario, assert
 pytestmark = pytest.mark.gpu
 
 
-def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=False):
+def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=False, compact=False):
     """fused=False: lzb_traverse + lzb_backprop per simulation; fused=True: lzb_step (backprop s + traverse s+1 in one
-    launch), with the leaf rows gathered through the slot tables."""
+    launch), with the leaf rows gathered through the slot tables.  Scenarios with ``reuse`` run the ReZero flavour of
+    the same calls; compact=True additionally hands over the reference's no_inference / reuse lists (as flags) and the
+    compacted batch index of every tree, the way a caller that compacts its model batches would."""
     import torch
     from lightzero_b200.forest import Forest
     f = Forest(sc.variant, sc.n, sc.K if sc.variant == "sez" else sc.A, sc.S, legal_actions=sc.legal, action_dim=sc.D,
@@ -42,19 +44,42 @@ def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=Fal
     is_reset_out = torch.empty(sc.n, dtype=torch.int32, device=dev) if vp else None
     reset_of = torch.zeros(sc.S + 1, sc.n, dtype=torch.int32, device=dev)
 
+    reuse = None
+    infer_count = torch.zeros(sc.S, dtype=torch.int32, device=dev)
+    if getattr(sc, "reuse", False):
+        reuse = dict(true_action=t(sc.true_action), reuse_value=t(sc.reuse_value))
+
+    def reuse_for(s_traverse, o_prev=None):
+        """reuse dict of one call: the traverse of simulation s_traverse counts its inferring trees; the backprop half
+        takes flags / batch_index derived from the previous traverse's outputs (mcts_ctree.py:376-384) when compact."""
+        if reuse is None:
+            return None
+        r = dict(reuse)
+        if s_traverse is not None:
+            r["infer_count"] = infer_count[s_traverse:]
+        if compact and o_prev is not None:
+            ix, la = o_prev["ix"].cpu().numpy(), o_prev["last_action"].cpu().numpy()
+            infer = ix != -1
+            flags = (~infer).astype(np.int32) | (((ix == 0) & (la == sc.true_action)).astype(np.int32) << 1)
+            r["flags"] = t(flags)
+            r["batch_index"] = t((np.cumsum(infer) - 1).astype(np.int32))
+        return r
+
     def note(o, s):
         if fused:  # the gather delivered the parent's row; reset parents read as zeros through a zero_if_reset gather
             ix = o["ix"].long()
+            inf = (ix >= 0).unsqueeze(1)  # trees that need no inference keep whatever their rows held
+            ix = ix.clamp(min=0)
             want = ix.float().unsqueeze(1) + torch.arange(sc.n, device=dev).float().unsqueeze(1) / 1024
-            assert torch.equal(leaf, want.expand(sc.n, L)), "sim %d: slot gather delivered the wrong rows" % s
+            assert torch.equal(torch.where(inf, leaf, want), want.expand(sc.n, L)), "sim %d: slot gather delivered the wrong rows" % s
             par_reset = reset_of[ix, torch.arange(sc.n, device=dev)].bool().unsqueeze(1)
-            assert torch.equal(leaf_z, torch.where(par_reset, torch.zeros_like(leaf), leaf)), "sim %d: zero_if_reset" % s
+            assert torch.equal(torch.where(inf, leaf_z, leaf), torch.where(par_reset & inf, torch.zeros_like(leaf), leaf)), "sim %d: zero_if_reset" % s
         if record is not None:
             rec = {k: v.cpu().numpy() for k, v in o.items()}
             rec["paths"] = f.dump_paths(sc.S + 1)
             record.append(rec)
 
-    o = f.traverse(cfg, tp, gathers=gathers)
+    o = f.traverse(cfg, tp, gathers=gathers, reuse=reuse_for(0))
     note(o, 0)
     for s in range(sc.S):
         m = sc.model_fn(s, None, None, None)
@@ -69,30 +94,37 @@ def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=Fal
         args = (s + 1, sc.discount, t(m["reward"]), t(m["value"]), t(m["logits"]), o["vtp"])
         last = s + 1 == sc.S
         if fused and not last:
-            o = f.step(cfg, *args, tp, out=o, gathers=gathers, **kw)
+            o = f.step(cfg, *args, tp, out=o, gathers=gathers, reuse=reuse_for(s + 1, o), **kw)
         else:
-            f.backprop(*args, **kw)
+            f.backprop(*args, reuse=reuse_for(None, o), **kw)
         if vp:
             reset_of[s + 1] = is_reset_out
             if record is not None:
                 record[-1]["is_reset"] = is_reset_out.cpu().numpy()
         if not last:
             if not fused:
-                o = f.traverse(cfg, tp, out=o)
+                o = f.traverse(cfg, tp, out=o, reuse=reuse_for(s + 1))
             note(o, s + 1)
     torch.cuda.synchronize()
+    f.infer_count = infer_count.cpu().numpy()
     return f
 
 
-def compare(sc, rng_mode=2, seed=2024, trees=4, fused=False):
+def compare(sc, rng_mode=2, seed=2024, trees=4, fused=False, compact=False):
     from oracle.binding import OracleForest
     orc = OracleForest(sc.variant, sc.n, sc.A, sc.legal, K=sc.K, D=sc.D)
     rec_c, rec_g = [], []
     run_cpu(orc, sc, rng_mode, seed, record=rec_c)
-    gpu = run_gpu(sc, rng_mode, seed, record=rec_g, fused=fused)
+    gpu = run_gpu(sc, rng_mode, seed, record=rec_g, fused=fused, compact=compact)
+    is_reuse = getattr(sc, "reuse", False)
     for s, (c, g) in enumerate(zip(rec_c, rec_g)):
         for k in ("search_len", "ix", "iy", "vtp", "paths"):
-            assert_same(g[k], c[k], "sim %d %s" % (s, k))
+            if k == "iy" and is_reuse and not compact:  # model batches indexed by tree: every node's batch_index is its tree
+                assert_same(g[k], np.arange(sc.n, dtype=np.int32), "sim %d iy" % s)
+            elif k in c:
+                assert_same(g[k], c[k], "sim %d %s" % (s, k))
+        if is_reuse:
+            assert gpu.infer_count[s] == int((c["ix"] != -1).sum()), "sim %d: inference count" % s
         if sc.variant == "sez":
             assert_same(g["last_action_f"], c["last_action_f"], "sim %d last_action_f" % s)
         else:
@@ -255,6 +287,46 @@ def test_fused_step_deep_paths():
     sc.root_logits[:] = 0.0
     sc.logits[:] = np.array([8.0, -8.0], np.float32)
     compare(sc, fused=True)
+
+
+LEGAL9 = [[a for a, x in enumerate(row) if x == 1] for row in TICTACTOE_MASKS]
+REUSE_CASES = {  # ReZero search_with_reuse (mcts_ctree.py:323-420, 829-953): scenario kwargs, rng_mode
+    "mz_a6": (dict(variant="mz", n=32, A=6, S=50, seed=14, reuse=True), 2),
+    "mz_a18_batch_rng": (dict(variant="mz", n=16, A=18, S=50, seed=15, reuse=True), 1),
+    "mz_a18_many_roots": (dict(variant="mz", n=700, A=18, S=40, seed=40, reuse=True), 2),
+    "mz_masks_two_player": (dict(variant="mz", n=16, A=9, S=30, seed=16, legal=LEGAL9, to_play=[1, 2] * 8, discount=1.0,
+                                 reuse=True), 2),
+    "mz_zero_model": (dict(variant="mz", n=16, A=9, S=40, seed=41, zero_model=True, reuse=True), 2),
+    "mz_a40": (dict(variant="mz", n=16, A=40, S=60, seed=42, reuse=True), 2),
+    "mz_a100": (dict(variant="mz", n=8, A=100, S=50, seed=43, reuse=True), 2),
+    "ez_a6": (dict(variant="ez", n=32, A=6, S=50, seed=17, reuse=True), 2),
+    "ez_two_player": (dict(variant="ez", n=16, A=9, S=30, seed=18, to_play=[2, 1] * 8, discount=1.0, reuse=True), 1),
+    "ez_a18": (dict(variant="ez", n=300, A=18, S=50, seed=44, reuse=True), 2),
+}
+
+
+@pytest.mark.parametrize("compact", [False, True])
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("name", sorted(REUSE_CASES))
+def test_reuse_search_matches_oracle(name, fused, compact):
+    kw, mode = REUSE_CASES[name]
+    gpu, orc = compare(Scenario(**kw), rng_mode=mode, fused=fused, compact=compact)
+    assert gpu.infer_count.sum() / kw["S"] == orc.infer_stats[1]  # average_infer of search_with_reuse
+
+
+def test_reuse_search_is_rejected_where_the_reference_has_none():
+    import torch
+    from lightzero_b200.forest import Forest
+    for variant, A, kw in (("gmz", 9, {}), ("mz", 150, {})):
+        f = Forest(variant, 4, A, 8)
+        dev = f.device
+        f.prepare(torch.zeros(4, A, device=dev), None, 0.0, torch.zeros(4, device=dev),
+                  torch.full((4,), -1, dtype=torch.int32, device=dev), value=torch.zeros(4, device=dev))
+        cfg = f.make_cfg(num_simulations=8, players=1)
+        with pytest.raises(RuntimeError, match="reuse"):
+            f.traverse(cfg, torch.full((4,), -1, dtype=torch.int32, device=dev),
+                       reuse=dict(true_action=torch.zeros(4, dtype=torch.int32, device=dev),
+                                  reuse_value=torch.zeros(4, device=dev)))
 
 
 def test_trajectories_follow_best_actions():
