@@ -221,6 +221,45 @@ int lzb_sample_actions(const float *logits_dev, const float *uniforms_dev, float
                        int action_dim, int action_space, int continuous, int root_offset, uint64_t seed, uint32_t counter,
                        void *stream);
 
+/* ---- Root-batch prologue / epilogue (what the callers of search() do per root in Python) ---- */
+
+/* legal_actions = [a for a, x in enumerate(action_mask[j]) if x == 1] (lzero/policy/muzero.py:671;
+ * lzero/mcts/buffer/game_buffer_muzero.py:552): mask [N, A] int8 -> legal_count [N], legal_actions [N, A] (ids in
+ * ascending order, row padded with 0), the pair lzb_forest_create / lzb_forest_reset take. */
+int lzb_legal_from_mask(const int8_t *mask_dev, int num_roots, int action_space, int32_t *legal_count_dev,
+                        int32_t *legal_actions_dev, void *stream);
+
+/* noises[j] = np.random.dirichlet([alpha] * n_legal_j).astype(np.float32) (lzero/policy/muzero.py:674-677) as the
+ * [N, A] tensor lzb_prepare takes (row j: n_legal_j draws by legal position, zeros beyond).  legal_count_dev NULL =
+ * every action legal.  Counter-based (seed, counter, root_offset + i, position): the reference draws from numpy's
+ * global generator, so the distribution is what is comparable. */
+int lzb_dirichlet_noise(float alpha, const int32_t *legal_count_dev, float *noise_dev, int num_roots, int action_space,
+                        int root_offset, uint64_t seed, uint32_t counter, void *stream);
+
+/* select_action(visit_counts, temperature, deterministic) for every root (lzero/policy/utils.py:515-539) followed by
+ * action = np.where(action_mask == 1)[0][action_pos] (lzero/policy/muzero.py:709).  visits / legal_count /
+ * legal_actions as lzb_root_outputs and lzb_legal_from_mask produce them (legal_actions NULL = identity).
+ * deterministic: first argmax of the visit counts; else one draw from visits^(1/T) normalised, by inverse CDF exactly
+ * as np.random.choice does it (uniforms_dev [N] in [0,1) injects the draws; NULL = counter-based generator).
+ * entropy [N] f64: base-2 entropy of the distribution.  Outputs may be NULL. */
+typedef struct {
+    const int32_t *visits_dev, *legal_count_dev, *legal_actions_dev;
+    const double *uniforms_dev;
+    int32_t *action_pos_dev, *action_dev;
+    double *entropy_dev;
+    double temperature;
+    int32_t num_roots, action_space, deterministic, root_offset;
+    uint64_t seed;
+    uint32_t counter;
+} lzb_select_action_t;
+int lzb_select_action(const lzb_select_action_t *args, void *stream);
+
+/* Reanalyze targets (lzero/mcts/buffer/game_buffer_muzero.py:617-656): policy [N, A] f32 = visits / sum(visits)
+ * (float64 division, then cast) at the legal action ids (legal_actions NULL = fixed action space: position ==
+ * action), all zeros where policy_mask[i] == 0 (NULL = every row valid). */
+int lzb_target_policies(const int32_t *visits_dev, const int32_t *legal_count_dev, const int32_t *legal_actions_dev,
+                        const int32_t *policy_mask_dev, int num_roots, int action_space, float *policy_dev, void *stream);
+
 /* Gumbel constants exposed for tests (gmz_tree.pyx:134-152): host buffers. */
 int lzb_gumbel_table(int max_num_considered_actions, int num_simulations, int32_t *out_host);
 int lzb_gumbel_noise(float scale, int shape, float *out_host);

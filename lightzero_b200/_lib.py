@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "liblzb200.so")
-SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_group.cuh", "lzb_sample.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
+SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_group.cuh", "lzb_sample.cuh", "lzb_collect.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",  # B200 only
@@ -71,6 +71,15 @@ class Reuse(C.Structure):
                 ("flags_dev", C.c_void_p), ("batch_index_dev", C.c_void_p)]
 
 
+class SelectAction(C.Structure):
+    """lzb_select_action_t"""
+    _fields_ = [("visits_dev", C.c_void_p), ("legal_count_dev", C.c_void_p), ("legal_actions_dev", C.c_void_p),
+                ("uniforms_dev", C.c_void_p), ("action_pos_dev", C.c_void_p), ("action_dev", C.c_void_p),
+                ("entropy_dev", C.c_void_p), ("temperature", C.c_double), ("num_roots", C.c_int32),
+                ("action_space", C.c_int32), ("deterministic", C.c_int32), ("root_offset", C.c_int32),
+                ("seed", C.c_uint64), ("counter", C.c_uint32)]
+
+
 class TraverseIO(C.Structure):
     """lzb_traverse_io_t"""
     _fields_ = [("to_play_dev", C.c_void_p), ("ix_dev", C.c_void_p), ("iy_dev", C.c_void_p),
@@ -111,6 +120,10 @@ _PROTOS = {
     "lzb_minmax": (C.c_int, [_P, _P, _P, _P]),
     "lzb_root_stats": (C.c_int, [_P, _P, _P, _P, _P]),
     "lzb_sample_actions": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint32, _P]),
+    "lzb_legal_from_mask": (C.c_int, [_P, C.c_int, C.c_int, _P, _P, _P]),
+    "lzb_dirichlet_noise": (C.c_int, [C.c_float, _P, _P, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint32, _P]),
+    "lzb_select_action": (C.c_int, [C.POINTER(SelectAction), _P]),
+    "lzb_target_policies": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
     "lzb_gumbel_table": (C.c_int, [C.c_int, C.c_int, _P]),
     "lzb_gumbel_noise": (C.c_int, [C.c_float, C.c_int, _P]),
     "lzb_test_expf": (C.c_int, [_P, _P, C.c_int64, _P]),

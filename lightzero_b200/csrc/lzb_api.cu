@@ -10,6 +10,7 @@
 #include "../../include/lzb200.h"
 #include "lzb_group.cuh"
 #include "lzb_sample.cuh"
+#include "lzb_collect.cuh"
 #include "lzb_step.cuh"
 
 using namespace lzb;
@@ -781,6 +782,48 @@ int lzb_sample_actions(const float *logits_dev, const float *uniforms_dev, float
     if (!continuous && num_sampled > action_space) return fail(LZB_E_ARG, "sample_actions: cannot draw %d of %d actions without replacement", num_sampled, action_space);
     SampleArgs a{logits_dev, uniforms_dev, out_dev, num_roots, num_sampled, action_dim, action_space, continuous, root_offset, seed, counter};
     k_sample_actions<<<(num_roots + 3) / 4, 128, 0, (cudaStream_t)stream>>>(a);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_legal_from_mask(const int8_t *mask_dev, int num_roots, int action_space, int32_t *legal_count_dev,
+                        int32_t *legal_actions_dev, void *stream)
+{
+    if (!mask_dev || !legal_count_dev || !legal_actions_dev || num_roots <= 0 || action_space <= 0) return fail(LZB_E_ARG, "legal_from_mask: bad argument");
+    k_legal_from_mask<<<(num_roots + 3) / 4, 128, 0, (cudaStream_t)stream>>>((const signed char *)mask_dev, num_roots, action_space,
+                                                                             legal_count_dev, legal_actions_dev);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_dirichlet_noise(float alpha, const int32_t *legal_count_dev, float *noise_dev, int num_roots, int action_space,
+                        int root_offset, uint64_t seed, uint32_t counter, void *stream)
+{
+    if (!noise_dev || num_roots <= 0 || action_space <= 0 || !(alpha > 0.0f)) return fail(LZB_E_ARG, "dirichlet_noise: bad argument");
+    k_dirichlet_noise<<<(num_roots + 3) / 4, 128, 0, (cudaStream_t)stream>>>(alpha, legal_count_dev, noise_dev, num_roots, action_space,
+                                                                             root_offset, seed, counter);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_select_action(const lzb_select_action_t *args, void *stream)
+{
+    if (!args || !args->visits_dev || args->num_roots <= 0 || args->action_space <= 0) return fail(LZB_E_ARG, "select_action: bad argument");
+    if (!(args->temperature > 0.0)) return fail(LZB_E_ARG, "select_action: temperature must be positive");
+    SelectActionArgs a{args->visits_dev, args->legal_count_dev, args->legal_actions_dev, args->uniforms_dev, args->action_pos_dev,
+                       args->action_dev, args->entropy_dev, args->temperature, args->num_roots, args->action_space,
+                       args->deterministic, args->root_offset, args->seed, args->counter};
+    k_select_action<<<(args->num_roots + 127) / 128, 128, 0, (cudaStream_t)stream>>>(a);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_target_policies(const int32_t *visits_dev, const int32_t *legal_count_dev, const int32_t *legal_actions_dev,
+                        const int32_t *policy_mask_dev, int num_roots, int action_space, float *policy_dev, void *stream)
+{
+    if (!visits_dev || !policy_dev || num_roots <= 0 || action_space <= 0) return fail(LZB_E_ARG, "target_policies: bad argument");
+    k_target_policies<<<(num_roots + 3) / 4, 128, 0, (cudaStream_t)stream>>>(visits_dev, legal_count_dev, legal_actions_dev, policy_mask_dev,
+                                                                             num_roots, action_space, policy_dev);
     LZB_CUDA(cudaGetLastError());
     return LZB_OK;
 }
