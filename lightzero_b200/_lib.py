@@ -137,7 +137,7 @@ def lib():
     """The loaded library with prototypes declared; builds it first when the sources are newer."""
     global _lib
     if _lib is None:
-        path = build()
+        path = os.environ.get("LZB200_LIB") or build()  # LZB200_LIB: tuning hook, load another build of the library
         L = C.CDLL(path)
         for name, (res, args) in _PROTOS.items():
             fn = getattr(L, name)  # AttributeError here == header and library disagree

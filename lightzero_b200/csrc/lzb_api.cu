@@ -516,10 +516,21 @@ template <int VAR, int G, int R, bool REUSE>
 void launch_group(int which, const Pool &p, const BackupArgs *b, const SelectArgs *a, cudaStream_t st)
 {
     const int per_block = 128 / G;
-    const dim3 grid((p.N + per_block - 1) / per_block), block(128);
-    if (which == kSelect) k_select_g<VAR, G, R, REUSE><<<grid, block, 0, st>>>(p, *a);
-    else if (which == kBackup) k_expand_backup_g<VAR, G, R, REUSE><<<grid, block, 0, st>>>(p, *b);
-    else k_step_g<VAR, G, R, REUSE><<<grid, block, 0, st>>>(p, *b, *a);
+    // programmatic dependent launch: the kernel may be scheduled while its predecessor drains; it reads nothing
+    // before its griddepcontrol.wait (LZB_NO_PDL=1 launches it the ordinary way)
+    static const bool pdl = getenv("LZB_NO_PDL") == nullptr;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((p.N + per_block - 1) / per_block);
+    cfg.blockDim = dim3(128);
+    cfg.stream = st;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    if (which == kSelect) cudaLaunchKernelEx(&cfg, k_select_g<VAR, G, R, REUSE>, p, *a);
+    else if (which == kBackup) cudaLaunchKernelEx(&cfg, k_expand_backup_g<VAR, G, R, REUSE>, p, *b);
+    else cudaLaunchKernelEx(&cfg, k_step_g<VAR, G, R, REUSE>, p, *b, *a);
 }
 
 // Lanes per tree G and child records per lane R (G * R >= A).  Fewer records per lane = a shorter dependent chain

@@ -56,6 +56,12 @@ struct Grp {
     }
 };
 
+// Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-serialization attribute may start
+// while its predecessor in the stream drains; pdl_wait() is the point past which the predecessor's writes are visible
+// (a no-op for a normally launched kernel), pdl_release() lets the successor's blocks be scheduled as ours exit.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // Leaf rows of one tree moved by the G lanes of its group (same semantics as gather_rows in lzb_select.cuh).
 template <int G>
 __device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a, int i, int ix, int parent_reset, int lane)
@@ -284,32 +290,37 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         }
     }
 
-    // ---- leaf bookkeeping (cnode.cpp:814-822) + gather of the parent's rows
-    if (live && lane == 0) {
-        action = (VAR != LZB_SEZ && e == 0) ? p.legal[(size_t)i * A + pos] : pos; // root children sit in legal-list order
-        p.res[i] = make_int4(depth, no_inference ? -1 : e, pos, vtp);
-        if (a.ix) a.ix[i] = no_inference ? -1 : e;
-        if (a.iy) a.iy[i] = (REUSE && !no_inference) ? p.bidx[(size_t)i * p.E + e] : i;
-        if (a.search_len) a.search_len[i] = depth;
-        if (a.vtp) a.vtp[i] = vtp;
-        if (a.last_action) a.last_action[i] = (long long)action;
-    }
+    // ---- gather of the parent's rows, then the leaf bookkeeping (cnode.cpp:814-822).  The loads the bookkeeping
+    // needs (legal-list entry, batch index) are issued first and consumed after the gather, so the row traffic does
+    // not queue behind them.
+    int root_action = 0, batch_index = i;
+    if (VAR != LZB_SEZ && e == 0) root_action = p.legal[(size_t)i * A + pos]; // root children sit in legal-list order
+    if (REUSE && !no_inference) batch_index = p.bidx[(size_t)i * p.E + e];
     if (REUSE && a.infer_count) { // one atomic per warp
         const unsigned m = __ballot_sync(kFull, live && lane == 0 && !no_inference);
         if ((threadIdx.x & 31) == 0 && m) atomicAdd(a.infer_count, __popc(m));
     }
-    if (!live || no_inference) return; // nothing to infer: the tree's rows of the model batch are left as they are
-    if (VAR == LZB_SEZ) {
-        const float *act = p.actions + (((size_t)i * p.E + e) * A + pos) * p.D;
-        if (a.last_action_f)
-            for (int d = lane; d < p.D; d += G) a.last_action_f[(size_t)i * p.D + d] = act[d];
-        if (a.last_action && lane == 0) a.last_action[i] = (long long)act[0]; // discrete sampled: float(index)
+    pdl_release(); // the walk is over: a dependent launch may begin to take the place of exiting blocks
+    if (live && !no_inference) { // nothing to infer: the tree's rows of the model batch are left as they are
+        if (VAR == LZB_SEZ) {
+            const float *act = p.actions + (((size_t)i * p.E + e) * A + pos) * p.D;
+            if (a.last_action_f)
+                for (int d = lane; d < p.D; d += G) a.last_action_f[(size_t)i * p.D + d] = act[d];
+            if (a.last_action && lane == 0) a.last_action[i] = (long long)act[0]; // discrete sampled: float(index)
+        }
+        gather_rows_g<G>(p, a, i, e, parent_reset, lane);
     }
-    gather_rows_g<G>(p, a, i, e, parent_reset, lane);
+    if (live && lane == 0) {
+        action = (VAR != LZB_SEZ && e == 0) ? root_action : pos;
+        p.res[i] = make_int4(depth, no_inference ? -1 : e, pos, vtp);
+        if (a.ix) a.ix[i] = no_inference ? -1 : e;
+        if (a.iy) a.iy[i] = batch_index;
+        if (a.search_len) a.search_len[i] = depth;
+        if (a.vtp) a.vtp[i] = vtp;
+        if (VAR != LZB_SEZ && a.last_action) a.last_action[i] = (long long)action;
+    }
 }
 
-// CNode::expand of the leaf + cbackpropagate along the recorded path by a lane group
-// (semantics and citations: expand_children / expand_backup_tree in lzb_expand.cuh).
 // REUSE = cbatch_backpropagate_with_reuse (cnode.cpp:502-549; ez :603-644): a tree whose traverse ended on an expanded
 // node is not expanded again and backs up reuse_value; a tree that expanded the root's true-action child backs up
 // reuse_value instead of the model's value.
@@ -339,9 +350,9 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
         if (no_inference || reuse) value_propagate = a.reuse_value[i];
     }
     const bool grow = live && !no_inference; // this tree expands its leaf
-    // path records are independent of everything above: issue their loads now (first chunk)
     const int4 *pa = p.path_a + (size_t)i * (p.S + 1);
     const int2 *pb = p.path_b + (size_t)i * (p.S + 1);
+    const int4 root_rec = p.root[i]; // independent of the depth: issued now
     int leaf_reset = 0;
     if (VP) {
         if (a.is_reset) leaf_reset = a.is_reset[i];
@@ -408,8 +419,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
         float vsum = 0.f, rew = 0.f, parent_vp = 0.f;
         if (valid) {
             if (q == 0) {
-                const int4 r = p.root[i];
-                x = r.x; vsum = __int_as_float(r.y); rew = __int_as_float(r.z);
+                x = root_rec.x; vsum = __int_as_float(root_rec.y); rew = __int_as_float(root_rec.z);
             } else {
                 const int4 r = pa[q - 1];
                 slot = r.x; x = r.y; vsum = __int_as_float(r.z); rew = __int_as_float(r.w);
@@ -417,7 +427,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
             }
             if (two) node_tp = (q == depth) ? to_play : pb[q].x;
             if (VP && q >= 1) {
-                parent_vp = (q == 1) ? __int_as_float(p.root[i].z) : __int_as_float(pa[q - 2].w);
+                parent_vp = (q == 1) ? __int_as_float(root_rec.z) : __int_as_float(pa[q - 2].w);
                 parent_reset = pb[q - 1].y;
             }
         }
@@ -476,6 +486,7 @@ __global__ void __launch_bounds__(128, 7) k_select_g(Pool p, SelectArgs a)
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
     const bool live = i < p.N;
+    pdl_wait();
     select_puct_g<VAR, G, R, REUSE>(p, a, live ? i : 0, live, grp);
 }
 
@@ -485,8 +496,10 @@ __global__ void __launch_bounds__(128, 7) k_expand_backup_g(Pool p, BackupArgs b
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
     const bool live = i < p.N;
+    pdl_wait();
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
     expand_backup_g<VAR, G, R, REUSE>(p, b, live ? i : 0, live, grp);
+    pdl_release();
 }
 
 // fused simulation step (see lzb_step.cuh): expand + backup of simulation s, then select + gather of s + 1
@@ -496,6 +509,7 @@ __global__ void __launch_bounds__(128, 7) k_step_g(Pool p, BackupArgs b, SelectA
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
     const bool live = i < p.N;
+    pdl_wait();
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
     expand_backup_g<VAR, G, R, REUSE>(p, b, live ? i : 0, live, grp);
     __syncwarp(); // the warp's own global writes (records, root, MinMax) are ordered before its reads below

@@ -329,6 +329,38 @@ def test_reuse_search_is_rejected_where_the_reference_has_none():
                                   reuse_value=torch.zeros(4, device=dev)))
 
 
+EDGE_SHAPES = {  # smallest / boundary sizes of every kernel flavour: (variant, n, A, S, extra scenario kwargs)
+    "one_root_one_action": ("mz", 1, 1, 12, {}),
+    "one_simulation": ("mz", 33, 18, 1, {}),
+    "two_simulations_ez": ("ez", 5, 6, 2, {}),
+    "a8_group_boundary": ("mz", 40, 8, 30, {}),
+    "a16_group_boundary": ("ez", 40, 16, 30, {}),
+    "a24_group_boundary": ("mz", 40, 24, 30, {}),
+    "a32_group_boundary": ("mz", 24, 32, 40, {}),
+    "a33": ("ez", 24, 33, 40, {}),
+    "a64_group_boundary": ("mz", 12, 64, 70, {}),
+    "a128_group_boundary": ("mz", 6, 128, 140, {}),
+    "a129_first_generic": ("mz", 6, 129, 140, {}),
+    "single_legal_action": ("mz", 9, 9, 20, dict(legal=[[k] for k in range(9)])),
+    "ragged_legal_lists": ("ez", 7, 12, 40, dict(legal=[list(range(k + 1)) for k in range(7)])),
+    "partial_last_block": ("mz", 129, 18, 20, {}),
+    "gumbel_one_root": ("gmz", 1, 5, 16, dict(max_considered=2)),
+    "gumbel_more_considered_than_actions": ("gmz", 9, 4, 24, dict(max_considered=16)),
+    "sampled_one_dim": ("sez", 9, 5, 20, dict(K=5, D=1)),
+}
+
+
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("name", sorted(EDGE_SHAPES))
+def test_edge_shapes_match_oracle(name, fused):
+    variant, n, A, S, kw = EDGE_SHAPES[name]
+    compare(Scenario(variant, n, A, S, seed=900 + len(name), **kw), fused=fused)
+
+
+def test_many_simulations_long_search():  # visit counts well past one byte, 800-simulation AlphaZero-style budget
+    compare(Scenario("mz", 4, 5, 800, seed=77), fused=True)
+
+
 def test_trajectories_follow_best_actions():
     sc = Scenario("mz", 16, 6, 30, seed=31)
     rec = []
