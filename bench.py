@@ -447,8 +447,13 @@ def run_b200_arm(a):
     # ---- value leg: inputs resident in HBM, the whole search replayed as one CUDA graph
     mcts = make_driver(a, device, graph=not a.no_graph)
 
-    def dev_step():
+    mids = []
+
+    def dev_step(timed=False):
         _, visits, values = one_search(a, mcts, model, inp, rank=rank)
+        if timed and world > 1:  # where the search ends and the exchange begins (diagnostic: config.exchange_ms_per_step)
+            mids.append(torch.cuda.Event(enable_timing=True))
+            mids[-1].record()
         return exchange(visits, values)
 
     for _ in range(max(a.warmup, 3)):
@@ -458,15 +463,19 @@ def run_b200_arm(a):
     if rank == 0:
         clocks.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    align = torch.zeros(1, device=device)
     t_wall = time.perf_counter()
     for e0, e1 in ev:
         flush.fill_(1)  # L2 flush between timed steps (512 MB write > 126 MB L2), outside the event pair
+        if world > 1:  # ranks leave the (untimed) flush together (stream-ordered, the host keeps queueing), so the
+            dist.all_reduce(align)  # exchange inside the timed region does not absorb the flush skew between ranks
         e0.record()
-        visits, values = dev_step()
+        visits, values = dev_step(timed=True)
         e1.record()
     barrier()
     t_wall = time.perf_counter() - t_wall
     dev_ms = sum(x.elapsed_time(y) for x, y in ev)
+    exchange_ms = sum(m.elapsed_time(y) for m, (_, y) in zip(mids, ev)) / a.steps if mids else 0.0
     # sanity: a search spends exactly S visits below each root
     assert bool((visits[:N].sum(1) == S).all()), "visit counts do not sum to the number of simulations"
 
@@ -499,6 +508,17 @@ def run_b200_arm(a):
         barrier()
         e2e_ms = 1e3 * (time.perf_counter() - t0)
         assert int(host["visits_out"].sum()) == N * S
+        # context for the e2e figure: what this box's host->device link delivers for the largest input of a step
+        big = max((host[k] for k in host if not k.endswith("_out")), key=lambda t: t.numel() * t.element_size())
+        dst = torch.empty(big.shape, dtype=big.dtype, device=device)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dst.copy_(big, non_blocking=True)
+        ev0.record()
+        for _ in range(3):
+            dst.copy_(big, non_blocking=True)
+        ev1.record()
+        torch.cuda.synchronize()
+        h2d_gbs = 3 * big.numel() * big.element_size() / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
     clk = clocks.stop() if rank == 0 else None
 
     # ---- per-kernel pass (eager launches bracketed by events) for the roofline of the dominant kernel
@@ -536,7 +556,8 @@ def run_b200_arm(a):
                        "latent_f32": a.latent, "model": "table lookup in HBM (no NN time)", "scalar_transform": "identity",
                        "cuda_graph": not a.no_graph, "search_streams": 1 if a.no_graph else a.streams, "l2": "512 MB flush between timed steps; working set > L2",
                        "parallelism": "roots sharded x%d, all-gather of root outputs per search" % world,
-                       "wall_ms_per_step_incl_flush": round(1e3 * t_wall / a.steps, 3)},
+                       "wall_ms_per_step_incl_flush": round(1e3 * t_wall / a.steps, 3),
+                       "exchange_ms_per_step": round(exchange_ms, 4)},
             "gpu_launches": a.steps * (5 + S + 1) * (1 if a.no_graph else a.streams),  # init, minmax, prepare, root slots, select, S-1 steps, backup, outputs
             "clocks": clk,
             "roofline": roofline(a, per_kernel, depth, peak, src),
@@ -544,7 +565,8 @@ def run_b200_arm(a):
         if e2e_ms is not None:
             line["e2e"] = {"value": round(total_sims / (e2e_tot / a.steps * 1e-3), 1), "unit": "simulations/s",
                            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                           "ms_per_step": round(e2e_tot / a.steps, 4), "clock": "host wall clock incl. Python, max over ranks"}
+                           "ms_per_step": round(e2e_tot / a.steps, 4), "clock": "host wall clock incl. Python, max over ranks",
+                           "h2d_link_gbs": round(h2d_gbs, 1)}
         if world == 1 and not a.no_cpu_baseline:
             n = min(a.cpu_sample_roots, N)
             d = cpu_inputs(a, n, 1234)

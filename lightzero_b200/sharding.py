@@ -38,7 +38,21 @@ def all_gather_rows(local, counts=None, group=None):
 
 def gather_search_outputs(visits, values, counts=None, group=None, extras=()):
     """End-of-search exchange: visit counts [n_r, A] int32 and root values [n_r] f32 (plus Gumbel policies /
-    Sampled action tables in `extras`) -> the full batch on every rank."""
-    out = [all_gather_rows(visits, counts, group), all_gather_rows(values, counts, group)]
-    out += [all_gather_rows(e, counts, group) for e in extras]
-    return out
+    Sampled action tables in `extras`) -> the full batch on every rank.  Everything is 32-bit, so the pieces travel
+    as ONE [n_r, A + 1 + ...] int32 all-gather (the exchange is launch-latency bound: 0.6 MB per rank at the headline
+    shape) and are split again on arrival."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return [visits, values] + list(extras)
+    parts = [visits, values] + list(extras)
+    if all(p.element_size() == 4 for p in parts):
+        n = visits.shape[0]
+        cols = [p.reshape(n, -1).view(torch.int32) for p in parts]
+        widths = [c.shape[1] for c in cols]
+        full = all_gather_rows(torch.cat(cols, dim=1), counts, group)
+        out, at = [], 0
+        for p, w in zip(parts, widths):
+            piece = full[:, at:at + w].contiguous().view(p.dtype)
+            out.append(piece.reshape((full.shape[0],) + tuple(p.shape[1:])))
+            at += w
+        return out
+    return [all_gather_rows(p, counts, group) for p in parts]

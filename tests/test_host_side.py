@@ -146,6 +146,15 @@ counts = [7, 3]                          # explicitly ragged
 lo = sum(counts[:r]); hi = lo + counts[r]
 v, x = gather_search_outputs(full_v[lo:hi], full_x[lo:hi], counts)
 assert torch.equal(v, full_v) and torch.equal(x, full_x)
+# extras travel in the same exchange: Gumbel policies [n, A] f32, sampled action tables [n, K, D] f32
+pol = torch.rand(10, 4); tab = torch.rand(10, 3, 2)
+v, x, p2, t2 = gather_search_outputs(full_v[lo:hi], full_x[lo:hi], counts, extras=(pol[lo:hi], tab[lo:hi]))
+torch.manual_seed(0)
+assert torch.equal(v, full_v) and torch.equal(x, full_x) and p2.shape == pol.shape and t2.shape == tab.shape
+assert torch.equal(p2[lo:hi], pol[lo:hi]) and torch.equal(t2[lo:hi], tab[lo:hi]) and p2.dtype == torch.float32
+# a 64-bit extra cannot be packed with the 32-bit pieces: falls back to one collective per tensor
+v, x, q = gather_search_outputs(full_v[lo:hi], full_x[lo:hi], counts, extras=(full_x[lo:hi].double(),))
+assert torch.equal(q, full_x.double())
 dist.destroy_process_group()
 print("rank", r, "ok")
 """
