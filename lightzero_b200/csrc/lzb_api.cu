@@ -574,7 +574,7 @@ bool launch_grouped(int which, const Pool &p, const BackupArgs *b, const SelectA
     case LZB_MZ: return reuse ? launch_group_for<LZB_MZ, true>(which, p, b, a, st) : launch_group_for<LZB_MZ, false>(which, p, b, a, st);
     case LZB_EZ: return reuse ? launch_group_for<LZB_EZ, true>(which, p, b, a, st) : launch_group_for<LZB_EZ, false>(which, p, b, a, st);
     case LZB_SEZ: return launch_group_for<LZB_SEZ, false>(which, p, b, a, st);
-    default: return false; // Gumbel MuZero keeps its shared-memory selection
+    default: return launch_group_for<LZB_GMZ, false>(which, p, b, a, st);
     }
 }
 

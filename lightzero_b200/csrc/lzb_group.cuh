@@ -54,6 +54,18 @@ struct Grp {
         for (int o = G / 2; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(kFull, v, o, G));
         return v;
     }
+    __device__ __forceinline__ int isum(int v) const
+    {
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o, G);
+        return v;
+    }
+    __device__ __forceinline__ int imax(int v) const
+    {
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(kFull, v, o, G));
+        return v;
+    }
 };
 
 // Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-serialization attribute may start
@@ -321,6 +333,193 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     }
 }
 
+// csoftmax (gmz cnode.cpp:904-933) over the n values a lane group holds as x[r] for j = lane + G*r:
+// exp(x - max - log(sum)) with the sum taken strictly in index order.
+template <int G, int R>
+__device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, const Grp<G> &grp)
+{
+    const int lane = grp.lane;
+    float m = -INFINITY;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+        if (lane + G * r < n) m = fmaxf(m, x[r]);
+    m = grp.fmax(m);
+    float sum = 0.0f;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const float ex = (lane + G * r < n) ? glibc_expf(x[r] - m) : 0.0f;
+#pragma unroll
+        for (int l = 0; l < G; ++l) sum += grp.shfl(ex, l); // index order; +0.0f beyond n is exact
+    }
+    const float ls = glibc_logf(sum);
+#pragma unroll
+    for (int r = 0; r < R; ++r) x[r] = glibc_expf(x[r] - m - ls);
+}
+
+// Gumbel MuZero traverse of tree i by a lane group: sequential halving at the root (cselect_root_child, gmz
+// cnode.cpp:701-745, score_considered :1097-1132), improved-policy selection below it (cselect_interior_child
+// :747-790), both on completed Q values (qtransform_completed_by_mix_value :989-1040 with the header defaults).
+// Semantics and evaluation order are those of select_gumbel_tree in lzb_select.cuh; every group of a warp is at
+// the root in the first round and below it afterwards, so the root / interior branch is warp-uniform.
+template <int G, int R>
+__device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs &a, int i, bool live, const Grp<G> &grp)
+{
+    const int B = p.B, A = p.A, lane = grp.lane;
+    const int4 *tree = p.tree(i);
+    int4 *pa = p.path_a + (size_t)i * (p.S + 1);
+    int2 *pb = p.path_b + (size_t)i * (p.S + 1);
+    const float g = a.discount;
+    const int vtp = a.to_play[i]; // never flipped (gmz cnode.cpp:870-885)
+    float gum[R];                 // root only: the shared Gumbel noise by position
+#pragma unroll
+    for (int r = 0; r < R; ++r) gum[r] = (lane + G * r < A) ? p.gumbel[lane + G * r] : 0.0f;
+    int e = 0, depth = 0, pos = 0;
+    bool going = live, at_root = true;
+
+    while (__any_sync(kFull, going)) {
+        const int4 *blk = tree + (size_t)e * B;
+        const int4 h = blk[0];
+        int4 c[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) c[r] = (lane + G * r < A) ? blk[1 + lane + G * r] : make_int4(0, 0, 0, 0);
+        const int n = h.x;
+        const float raw_value = __int_as_float(h.w);
+
+        // ---- get_q (:181-197), priors, visit statistics
+        float q[R], sp[R];
+        int vc[R], vsum_i = 0, vmax_i = 0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const bool in = lane + G * r < n;
+            vc[r] = in ? child_visits(c[r].x) : 0;
+            const float val = vc[r] ? __int_as_float(c[r].y) / (float)vc[r] : 0.0f;
+            q[r] = __int_as_float(c[r].w) + g * val;
+            sp[r] = __int_as_float(c[r].z);
+            vsum_i += vc[r];
+            vmax_i = max(vmax_i, vc[r]);
+        }
+        vsum_i = grp.isum(vsum_i);
+        vmax_i = grp.imax(vmax_i);
+        csoftmax_g<G, R>(sp, n, grp); // priors (probabilities) are soft-maxed again (:1014) - reproduced as is
+
+        // ---- compute_mixed_value (:935-970): serial sums over visited children in index order
+        float probs_sum = 0.0f;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const float pc = (sp[r] < -10e7f) ? -10e7f : sp[r]; // std::max(prior, min_num)
+            const float t = (vc[r] > 0) ? pc : 0.0f;
+#pragma unroll
+            for (int l = 0; l < G; ++l) probs_sum += grp.shfl(t, l);
+        }
+        float wq = 0.0f;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const float pc = (sp[r] < -10e7f) ? -10e7f : sp[r];
+            const float t = (vc[r] > 0) ? pc * q[r] / probs_sum : 0.0f;
+#pragma unroll
+            for (int l = 0; l < G; ++l) wq += grp.shfl(t, l);
+        }
+        const float vsum_f = (float)vsum_i;
+        const float mixed = (raw_value + vsum_f * wq) / (vsum_f + 1);
+        float cq[R];
+        float mx = -INFINITY, mn = INFINITY;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            cq[r] = (vc[r] > 0) ? q[r] : mixed;
+            if (lane + G * r < n) { mx = fmaxf(mx, cq[r]); mn = fminf(mn, cq[r]); }
+        }
+        mx = grp.fmax(mx);
+        mn = grp.fmin(mn);
+        float gap = mx - mn; // rescale_qvalues (:972-987)
+        gap = (gap < 1e-8f) ? 1e-8f : gap;
+        const float visit_scale = 50.0f + (float)vmax_i;
+#pragma unroll
+        for (int r = 0; r < R; ++r) cq[r] = (cq[r] - mn) / gap * visit_scale * 0.1f;
+
+        // ---- scores
+        float sc[R];
+        if (at_root) { // cselect_root_child + score_considered
+            const int considered = p.vtable[vsum_i];
+            float ml = -INFINITY;
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                if (lane + G * r < n) ml = fmaxf(ml, __int_as_float(c[r].z));
+            ml = grp.fmax(ml);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float logit = __int_as_float(c[r].z) - ml;
+                float v = gum[r] + logit + cq[r];
+                v = (-1e9f < v) ? v : -1e9f;
+                v += (vc[r] == considered) ? 0.0f : -INFINITY;
+                sc[r] = v;
+            }
+        } else { // cselect_interior_child
+#pragma unroll
+            for (int r = 0; r < R; ++r) sc[r] = __int_as_float(c[r].z) + cq[r];
+            csoftmax_g<G, R>(sc, n, grp);
+            const float den = (float)(1 + vsum_i);
+#pragma unroll
+            for (int r = 0; r < R; ++r) sc[r] = sc[r] - (float)vc[r] / den;
+        }
+
+        // ---- first index attaining the maximum under a strict '>' scan from -inf (:733-742,778-787); 0 if none
+        float lmax = -INFINITY;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            sc[r] = (lane + G * r < n) ? sc[r] : -INFINITY;
+            lmax = fmaxf(lmax, sc[r]);
+        }
+        const float gmax = grp.fmax(lmax);
+        int newpos = 0;
+#pragma unroll
+        for (int r = R - 1; r >= 0; --r) {
+            const unsigned m = grp.ballot(sc[r] == gmax && gmax > -INFINITY);
+            newpos = m ? (__ffs(m) - 1) + G * r : newpos;
+        }
+
+        // ---- the chosen child's record lives in lane newpos % G, register newpos / G
+        const int rsel = newpos / G;
+        int4 mine = c[0];
+#pragma unroll
+        for (int r = 1; r < R; ++r) {
+            mine.x = (rsel == r) ? c[r].x : mine.x;
+            mine.y = (rsel == r) ? c[r].y : mine.y;
+            mine.w = (rsel == r) ? c[r].w : mine.w;
+        }
+        int4 ch;
+        ch.x = grp.shfl(mine.x, newpos & (G - 1));
+        ch.y = grp.shfl(mine.y, newpos & (G - 1));
+        ch.w = grp.shfl(mine.w, newpos & (G - 1));
+        ch.z = 0;
+        if (going) {
+            pos = newpos;
+            if (lane == 0) {
+                pa[depth] = make_int4(e * B + 1 + pos, ch.x, ch.y, ch.w);
+                pb[depth] = make_int2(h.y, h.z);
+                p.best[(size_t)i * p.E + e] = pos;
+            }
+            depth += 1;
+            const int ce = child_expansion(ch.x);
+            if (ce < 0) going = false;
+            else e = ce;
+        }
+        at_root = false;
+    }
+
+    int root_action = 0;
+    if (e == 0) root_action = p.legal[(size_t)i * A + pos];
+    pdl_release();
+    if (live) gather_rows_g<G>(p, a, i, e, 0, lane);
+    if (live && lane == 0) {
+        p.res[i] = make_int4(depth, e, pos, vtp);
+        if (a.ix) a.ix[i] = e;
+        if (a.iy) a.iy[i] = i;
+        if (a.search_len) a.search_len[i] = depth;
+        if (a.vtp) a.vtp[i] = vtp;
+        if (a.last_action) a.last_action[i] = (long long)((e == 0) ? root_action : pos);
+    }
+}
+
 // REUSE = cbatch_backpropagate_with_reuse (cnode.cpp:502-549; ez :603-644): a tree whose traverse ended on an expanded
 // node is not expanded again and backs up reuse_value; a tree that expanded the root's true-action child backs up
 // reuse_value instead of the model's value.
@@ -487,7 +686,8 @@ __global__ void __launch_bounds__(128, 7) k_select_g(Pool p, SelectArgs a)
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
     const bool live = i < p.N;
     pdl_wait();
-    select_puct_g<VAR, G, R, REUSE>(p, a, live ? i : 0, live, grp);
+    if constexpr (VAR == LZB_GMZ) select_gumbel_g<G, R>(p, a, live ? i : 0, live, grp);
+    else select_puct_g<VAR, G, R, REUSE>(p, a, live ? i : 0, live, grp);
 }
 
 template <int VAR, int G, int R, bool REUSE>
@@ -513,7 +713,8 @@ __global__ void __launch_bounds__(128, 7) k_step_g(Pool p, BackupArgs b, SelectA
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
     expand_backup_g<VAR, G, R, REUSE>(p, b, live ? i : 0, live, grp);
     __syncwarp(); // the warp's own global writes (records, root, MinMax) are ordered before its reads below
-    select_puct_g<VAR, G, R, REUSE>(p, a, live ? i : 0, live, grp);
+    if constexpr (VAR == LZB_GMZ) select_gumbel_g<G, R>(p, a, live ? i : 0, live, grp);
+    else select_puct_g<VAR, G, R, REUSE>(p, a, live ? i : 0, live, grp);
 }
 
 } // namespace lzb

@@ -235,6 +235,18 @@ def test_warp_per_tree_kernels_on_small_action_space(monkeypatch):
     monkeypatch.setenv("LZB_FORCE_WARP_PER_TREE", "1")
     compare(Scenario("mz", 64, 18, 50, seed=34), fused=True)
     compare(Scenario("ez", 32, 6, 50, seed=35))
+    compare(Scenario("gmz", 16, 9, 30, seed=36, discount=1.0, max_considered=3), rng_mode=1, fused=True)
+    compare(Scenario("gmz", 8, 18, 40, seed=37, max_considered=16), rng_mode=1)
+
+
+def test_gumbel_wide_action_spaces():  # lane groups of 32 x 2 / 32 x 4 records, and the warp-per-tree kernels past 128
+    compare(Scenario("gmz", 8, 40, 60, seed=38, max_considered=8), rng_mode=1, fused=True)
+    compare(Scenario("gmz", 4, 100, 60, seed=39, max_considered=16), rng_mode=1)
+    compare(Scenario("gmz", 4, 140, 50, seed=40, max_considered=16), rng_mode=1, fused=True)
+
+
+def test_gumbel_many_roots():  # more than one block per group width, partial last block
+    compare(Scenario("gmz", 1100, 18, 30, seed=41, max_considered=8), rng_mode=1, fused=True)
 
 
 def test_efficientzero_pong_shape():  # C2: A=6, 50 sims, value_prefix + lstm_horizon_len=5 resets
