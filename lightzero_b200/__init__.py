@@ -4,4 +4,4 @@
 
 Importing the package does not need a GPU; creating roots or searching does (there is no CPU fallback)."""
 from .tree_search import (EfficientZeroMCTSCtree, GumbelMuZeroMCTSCtree, MuZeroMCTSCtree,  # noqa: F401
-                          SampledEfficientZeroMCTSCtree)
+                          MuZeroRNNFullObsMCTSCtree, SampledEfficientZeroMCTSCtree, UniZeroMCTSCtree)

@@ -388,6 +388,99 @@ class MuZeroMCTSCtree(_CtreeDriver):
             api.backprop_tensors(results, simulation_index + 1, discount, reward, value, net.policy_logits, o["vtp"])
 
 
+class UniZeroMCTSCtree(MuZeroMCTSCtree):
+    """lzero/mcts/tree_search/mcts_ctree.py:19-170: the MuZero tree driven by a world model that is called with the
+    search's whole state-action history, ``model.recurrent_inference(state_action_history, simulation_index,
+    latent_state_index_in_search_path)``.  The tree work is the fused device path of MuZeroMCTSCtree; what the world
+    model's key-value cache lookup needs on the host (the leaf latents as numpy, the parent indices as a list,
+    :143,153) is copied out once per simulation, as the reference does.  ``cfg.history_on_device=True`` hands the
+    history over as device tensors instead (no device->host copy inside the loop) for models that accept it."""
+
+    def search(self, roots, model, latent_state_roots, to_play_batch):
+        return self._search(roots, model, latent_state_roots, None, to_play_batch)
+
+    def search_with_reuse(self, *args, **kw):
+        raise NotImplementedError("the reference has no search_with_reuse for UniZero")
+
+    def _search(self, roots, model, latent_state_roots, hidden_roots, to_play_batch, reuse_lists=None):
+        with torch.no_grad():
+            forest, scfg, tp, results, S = self._begin(roots, model, to_play_batch)
+            discount = self._cfg.discount_factor
+            on_device = bool(_get(self._cfg, "history_on_device", False))
+            lat0 = self._on_device(forest, latent_state_roots)
+            if not self._rows_ok(lat0):
+                raise ValueError("latent rows must be a multiple of 4 bytes")
+            forest.set_slots(0, [lat0])
+            leaf = torch.empty_like(lat0)
+            gathers = [(None, leaf)]
+            state_action_history = []
+            o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers)
+            for simulation_index in range(S):
+                last_actions = o["last_action"].clone()  # the traverse buffers are reused by the next step
+                if on_device:
+                    state_action_history.append((leaf.clone(), last_actions))
+                    ix = o["ix"].clone()
+                else:
+                    state_action_history.append((leaf.cpu().numpy(), last_actions))  # mcts_ctree.py:143
+                    ix = o["ix"].tolist()
+                net = model.recurrent_inference(state_action_history, simulation_index, ix)
+                value = self.inverse_scalar_transform_handle(net.value)
+                reward = self.inverse_scalar_transform_handle(net.reward)
+                new_lat = self._slot_tensor(self._on_device(forest, net.latent_state).reshape(lat0.shape), leaf)
+                e = simulation_index + 1
+                if e < S:
+                    o = forest.step(scfg, e, discount, reward, value, net.policy_logits, o["vtp"], tp, out=o,
+                                    gathers=gathers, new_slots=[new_lat])
+                else:
+                    forest.backprop(e, discount, reward, value, net.policy_logits, o["vtp"], new_slots=[new_lat])
+                forest.sims_done += 1
+
+
+class MuZeroRNNFullObsMCTSCtree(MuZeroMCTSCtree):
+    """lzero/mcts/tree_search/mcts_ctree.py:422-620: the MuZero tree with a second per-node state, the world model's
+    latent history ``[1, N, H]``, gathered next to the latent; ``model.recurrent_inference(latent_states,
+    world_model_latent_history, last_actions[, ready_env_id=...])`` returns ``predict_next_latent_state``,
+    ``policy_logits``, ``value``, ``value_prefix`` (backed up as the reward, :596) and ``reward_hidden_state`` (the
+    next history, :604-605).  Both states are slot tables in HBM; nothing is copied to the host."""
+
+    def search(self, roots, model, latent_state_roots, world_model_latent_history_roots, to_play_batch,
+               ready_env_id=None):
+        return self._search(roots, model, latent_state_roots, world_model_latent_history_roots, to_play_batch,
+                            ready_env_id=ready_env_id)
+
+    def search_with_reuse(self, *args, **kw):
+        raise NotImplementedError("the reference has no search_with_reuse for the RNN full-observation driver")
+
+    def _search(self, roots, model, latent_state_roots, hidden_roots, to_play_batch, reuse_lists=None, ready_env_id=None):
+        with torch.no_grad():
+            forest, scfg, tp, results, S = self._begin(roots, model, to_play_batch)
+            discount = self._cfg.discount_factor
+            N = roots.num
+            lat0 = self._on_device(forest, latent_state_roots)
+            hist = hidden_roots[0] if isinstance(hidden_roots, (tuple, list)) else hidden_roots
+            h0 = self._on_device(forest, hist).reshape(N, -1)  # world_model_latent_history_batch[ix][0][iy] (:562)
+            if not (self._rows_ok(lat0) and self._rows_ok(h0)):
+                raise ValueError("latent / history rows must be a multiple of 4 bytes")
+            forest.set_slots(0, [lat0, h0])
+            leaf, leaf_h = torch.empty_like(lat0), torch.empty_like(h0)
+            gathers = [(None, leaf), (None, leaf_h)]
+            kw = {} if ready_env_id is None else dict(ready_env_id=ready_env_id)
+            o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers)
+            for simulation_index in range(S):
+                net = model.recurrent_inference(leaf, leaf_h.unsqueeze(0), o["last_action"], **kw)
+                value = self.inverse_scalar_transform_handle(net.value)
+                value_prefix = self.inverse_scalar_transform_handle(net.value_prefix)
+                slots = [self._slot_tensor(net.predict_next_latent_state.reshape(lat0.shape), leaf),
+                         self._slot_tensor(net.reward_hidden_state.reshape(N, -1), leaf_h)]
+                e = simulation_index + 1
+                if e < S:
+                    o = forest.step(scfg, e, discount, value_prefix, value, net.policy_logits, o["vtp"], tp, out=o,
+                                    gathers=gathers, new_slots=slots)
+                else:
+                    forest.backprop(e, discount, value_prefix, value, net.policy_logits, o["vtp"], new_slots=slots)
+                forest.sims_done += 1
+
+
 class GumbelMuZeroMCTSCtree(MuZeroMCTSCtree):
     """lzero/mcts/tree_search/mcts_ctree.py:956-1122: same loop, Gumbel tree module, actions as [N, 1]."""
     tree = _gmz_module()

@@ -268,6 +268,95 @@ def test_search_with_reuse_is_not_offered_for_gumbel():
         lzb.GumbelMuZeroMCTSCtree(driver_cfg(sc)).search_with_reuse(None, None, None, None, [0] * 4, [0.0] * 4)
 
 
+@pytest.mark.parametrize("on_device", [False, True])
+def test_unizero_driver_matches_oracle_and_hands_over_the_history(on_device):
+    """mcts_ctree.py:19-170: same tree as MuZero; the world model receives (state_action_history, simulation_index,
+    latent_state_index_in_search_path)."""
+    import torch
+    import lightzero_b200 as lzb
+    sc = Scenario("mz", 24, 6, 30, seed=60)
+    orc, rec = oracle_run(sc)
+    dev = torch.device("cuda")
+    base = ScenarioModel(sc, dev)
+
+    class WorldModel:
+        def __init__(self):
+            self.seen = []
+
+        def eval(self):
+            base.eval()
+
+        def recurrent_inference(self, state_action_history, simulation_index, latent_state_index_in_search_path):
+            assert len(state_action_history) == simulation_index + 1
+            latent, actions = state_action_history[-1]
+            if on_device:
+                assert isinstance(latent, torch.Tensor) and latent.is_cuda and isinstance(latent_state_index_in_search_path, torch.Tensor)
+                ix = latent_state_index_in_search_path.cpu().tolist()
+                lat = latent
+            else:
+                assert isinstance(latent, np.ndarray) and isinstance(latent_state_index_in_search_path, list)
+                ix = latent_state_index_in_search_path
+                lat = torch.from_numpy(latent).to(dev)
+            assert actions.dtype == torch.int64 and actions.is_cuda
+            self.seen.append((ix, actions.cpu().tolist(), lat[:, 0].cpu().tolist()))
+            return base.recurrent_inference(lat, actions)
+
+    model = WorldModel()
+    mcts = identity(lzb.UniZeroMCTSCtree(driver_cfg(sc, history_on_device=on_device)))
+    roots = lzb.UniZeroMCTSCtree.roots(sc.n, sc.legal)
+    roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_logits.tolist(), sc.to_play.tolist())
+    mcts.search(roots, model, np.zeros((sc.n, 16), np.float32), sc.to_play.tolist())
+    check_roots(roots, orc, sc)
+    for s, (ix, actions, lat0) in enumerate(model.seen):
+        assert ix == rec[s]["ix"].tolist() and actions == rec[s]["last_action"].tolist()
+        assert lat0 == rec[s]["ix"].astype(np.float32).tolist()  # slot e is filled with e: the parents' latents arrived
+    # earlier history entries are not overwritten by later simulations
+    assert model.seen[0][1] == rec[0]["last_action"].tolist()
+
+
+def test_rnn_full_obs_driver_matches_oracle_and_gathers_the_history():
+    """mcts_ctree.py:422-620: MuZero tree, value_prefix backed up as the reward, world-model history gathered next to
+    the latent and replaced by reward_hidden_state."""
+    import torch
+    import lightzero_b200 as lzb
+    sc = Scenario("mz", 24, 6, 30, seed=61)
+    orc, rec = oracle_run(sc)
+    dev = torch.device("cuda")
+    base = ScenarioModel(sc, dev)
+    H = 8
+
+    class RNNModel:
+        def __init__(self):
+            self.seen, self.kw = [], []
+
+        def eval(self):
+            base.eval()
+
+        def recurrent_inference(self, latent, history, actions, **kw):
+            s = base.s
+            assert history.shape == (1, sc.n, H)
+            self.seen.append((latent[:, 0].cpu().tolist(), history[0, :, 0].cpu().tolist(), actions.cpu().tolist()))
+            self.kw.append(kw)
+            o = base.recurrent_inference(latent, actions)
+            o.predict_next_latent_state = o.latent_state
+            o.reward_hidden_state = torch.full((1, sc.n, H), -float(s + 1), device=dev)
+            o.value_prefix = o.reward
+            del o.reward, o.latent_state
+            return o
+
+    model = RNNModel()
+    mcts = identity(lzb.MuZeroRNNFullObsMCTSCtree(driver_cfg(sc)))
+    roots = lzb.MuZeroRNNFullObsMCTSCtree.roots(sc.n, sc.legal)
+    roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_logits.tolist(), sc.to_play.tolist())
+    mcts.search(roots, model, np.zeros((sc.n, 16), np.float32), np.zeros((1, sc.n, H), np.float32), sc.to_play.tolist(),
+                ready_env_id=[3, 4])
+    check_roots(roots, orc, sc)
+    for s, (lat0, hist0, actions) in enumerate(model.seen):
+        want = rec[s]["ix"].astype(np.float32)
+        assert lat0 == want.tolist() and hist0 == (-want).tolist() and actions == rec[s]["last_action"].tolist()
+    assert all(k == dict(ready_env_id=[3, 4]) for k in model.kw)
+
+
 def test_reference_unit_test_shapes_with_zero_model():
     """test_mcts_ctree.py:155-179,240-281: all-zero fake model, 16 x 9 mask; output shapes, per-root distribution
     length == legal count, and argmax action is legal."""
