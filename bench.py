@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--no-graph", action="store_true", help="value leg: launch per call instead of one CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--nccl-exchange", action="store_true", help="end-of-search exchange through NCCL instead of the peer-memory kernel")
     ap.add_argument("--cpu-sample-roots", type=int, default=1024)
     return ap.parse_args()
 
@@ -441,8 +442,18 @@ def run_b200_arm(a):
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=device)
     counts = [N] * world
 
-    def exchange(visits, values):  # the one collective of a search; identity at world == 1
-        return sharding.gather_search_outputs(visits, values, counts) if world > 1 else (visits, values)
+    # the one exchange of a search; identity at world == 1.  Default: one NVLink peer-memory kernel per
+    # rank (lzb_peer_allgather); --nccl-exchange: one packed NCCL all-gather
+    peer = None
+    if world > 1 and not a.nccl_exchange:
+        try:
+            peer = sharding.PeerExchange(N, A + 1)  # raises on every rank together if any rank cannot map its peers
+        except RuntimeError as exc:  # e.g. CUDA IPC not permitted in this container: the NCCL route, stated in config
+            print("rank %d: %s; using NCCL for the exchange" % (rank, exc), file=sys.stderr)
+            a.nccl_exchange = True
+
+    def exchange(visits, values):
+        return sharding.gather_search_outputs(visits, values, counts, peer=peer) if world > 1 else (visits, values)
 
     # ---- value leg: inputs resident in HBM, the whole search replayed as one CUDA graph
     mcts = make_driver(a, device, graph=not a.no_graph)
@@ -555,10 +566,12 @@ def run_b200_arm(a):
             "config": {"workload": workload_name(a), "roots_total": N * world, "sims": S, "actions": A,
                        "latent_f32": a.latent, "model": "table lookup in HBM (no NN time)", "scalar_transform": "identity",
                        "cuda_graph": not a.no_graph, "search_streams": 1 if a.no_graph else a.streams, "l2": "512 MB flush between timed steps; working set > L2",
-                       "parallelism": "roots sharded x%d, all-gather of root outputs per search" % world,
+                       "parallelism": "roots sharded x%d, all-gather of root outputs per search (%s)" % (
+                           world, "single GPU" if world == 1 else ("NCCL" if a.nccl_exchange else "NVLink peer-memory kernel")),
                        "wall_ms_per_step_incl_flush": round(1e3 * t_wall / a.steps, 3),
                        "exchange_ms_per_step": round(exchange_ms, 4)},
-            "gpu_launches": a.steps * (5 + S + 1) * (1 if a.no_graph else a.streams),  # init, minmax, prepare, root slots, select, S-1 steps, backup, outputs
+            # init, minmax, prepare, root slots, select, S-1 steps, backup, outputs (+ the exchange kernel when sharded)
+            "gpu_launches": a.steps * ((5 + S + 1) * (1 if a.no_graph else a.streams) + (1 if peer is not None else 0)),
             "clocks": clk,
             "roofline": roofline(a, per_kernel, depth, peak, src),
         }
@@ -578,6 +591,11 @@ def run_b200_arm(a):
             line["cpu_baseline"] = {"value": round(n * S / best, 1), "unit": "simulations/s", "cores": 1, "kind": kind,
                                     "sample": "%d of %d roots x %d sims, best of 3, tree + Python leaf gather, no NN" % (n, N, S)}
         print(json.dumps(line))
+    if peer is not None:
+        if peer.error():
+            raise SystemExit("peer exchange: rank %d did not arrive" % (peer.error() - 1))
+        dist.barrier()
+        peer.close()
     if world > 1:
         dist.destroy_process_group()
 

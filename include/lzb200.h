@@ -260,6 +260,32 @@ int lzb_select_action(const lzb_select_action_t *args, void *stream);
 int lzb_target_policies(const int32_t *visits_dev, const int32_t *legal_count_dev, const int32_t *legal_actions_dev,
                         const int32_t *policy_mask_dev, int num_roots, int action_space, float *policy_dev, void *stream);
 
+/* ---- End-of-search exchange over NVLink / NVSwitch peer memory ----
+ * The one place a sharded search crosses GPUs: every rank's root outputs (visit counts [n, A] i32, values [n] f32,
+ * Gumbel policies ...) -> the full batch on every rank.  One kernel per rank packs its pieces row-wise, stores them
+ * straight into every peer's receive buffer and runs a flag barrier over the same mapping (no NCCL call, no staging
+ * copy).  Buffers are cudaMalloc'ed by the library so that they can be shared through CUDA IPC handles:
+ *   lzb_peer_bytes   size of one rank's receive buffer for `world` ranks x rows_per_rank rows x row_words 32-bit words
+ *   lzb_peer_alloc / lzb_peer_free          the buffer (zeroed)
+ *   lzb_peer_export / lzb_peer_import / lzb_peer_unimport   64-byte IPC handle out; a peer's handle in (the caller
+ *                    moves the handles between processes, e.g. with torch.distributed.all_gather_object)
+ *   lzb_peer_allgather  bufs_host[world]: every rank's buffer as mapped in THIS process (own buffer at [rank]);
+ *                    pieces_dev[n_pieces]: local [rows_per_rank, piece_words[k]] 32-bit tensors, concatenated per row;
+ *                    epoch: 1, 2, 3 ... the same sequence on every rank; *result_dev: [world * rows_per_rank,
+ *                    row_words] in the caller's own buffer, valid until the next-but-one exchange.  A peer that does
+ *                    not arrive within timeout_ms is reported by lzb_peer_error instead of hanging the GPU.
+ *   lzb_peer_error   0, or 1 + the rank that timed out (synchronises the stream). */
+int lzb_peer_bytes(int world, int64_t rows_per_rank, int row_words, size_t *bytes);
+int lzb_peer_alloc(size_t bytes, void **buf_dev);
+int lzb_peer_free(void *buf_dev);
+int lzb_peer_export(void *buf_dev, void *handle_64_bytes);
+int lzb_peer_import(const void *handle_64_bytes, void **buf_dev);
+int lzb_peer_unimport(void *buf_dev);
+int lzb_peer_allgather(void *const *bufs_host, int rank, int world, int64_t rows_per_rank, const void *const *pieces_dev,
+                       const int32_t *piece_words, int n_pieces, uint32_t epoch, int64_t timeout_ms, void **result_dev,
+                       void *stream);
+int lzb_peer_error(void *own_buf_dev, int world, int64_t rows_per_rank, int row_words, int *error_host, void *stream);
+
 /* Gumbel constants exposed for tests (gmz_tree.pyx:134-152): host buffers. */
 int lzb_gumbel_table(int max_num_considered_actions, int num_simulations, int32_t *out_host);
 int lzb_gumbel_noise(float scale, int shape, float *out_host);

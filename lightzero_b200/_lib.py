@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "liblzb200.so")
-SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_group.cuh", "lzb_sample.cuh", "lzb_collect.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
+SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_group.cuh", "lzb_sample.cuh", "lzb_collect.cuh", "lzb_peer.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",  # B200 only
@@ -124,6 +124,15 @@ _PROTOS = {
     "lzb_dirichlet_noise": (C.c_int, [C.c_float, _P, _P, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint32, _P]),
     "lzb_select_action": (C.c_int, [C.POINTER(SelectAction), _P]),
     "lzb_target_policies": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
+    "lzb_peer_bytes": (C.c_int, [C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_size_t)]),
+    "lzb_peer_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
+    "lzb_peer_free": (C.c_int, [_P]),
+    "lzb_peer_export": (C.c_int, [_P, _P]),
+    "lzb_peer_import": (C.c_int, [_P, C.POINTER(_P)]),
+    "lzb_peer_unimport": (C.c_int, [_P]),
+    "lzb_peer_allgather": (C.c_int, [C.POINTER(_P), C.c_int, C.c_int, C.c_int64, C.POINTER(_P), C.POINTER(C.c_int32), C.c_int,
+                                     C.c_uint32, C.c_int64, C.POINTER(_P), _P]),
+    "lzb_peer_error": (C.c_int, [_P, C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_int), _P]),
     "lzb_gumbel_table": (C.c_int, [C.c_int, C.c_int, _P]),
     "lzb_gumbel_noise": (C.c_int, [C.c_float, C.c_int, _P]),
     "lzb_test_expf": (C.c_int, [_P, _P, C.c_int64, _P]),

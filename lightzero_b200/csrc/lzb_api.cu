@@ -11,6 +11,7 @@
 #include "lzb_group.cuh"
 #include "lzb_sample.cuh"
 #include "lzb_collect.cuh"
+#include "lzb_peer.cuh"
 #include "lzb_step.cuh"
 
 using namespace lzb;
@@ -836,6 +837,111 @@ int lzb_target_policies(const int32_t *visits_dev, const int32_t *legal_count_de
     k_target_policies<<<(num_roots + 3) / 4, 128, 0, (cudaStream_t)stream>>>(visits_dev, legal_count_dev, legal_actions_dev, policy_mask_dev,
                                                                              num_roots, action_space, policy_dev);
     LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+// ---- peer exchange (lzb_peer.cuh).  Layout of one rank's buffer: [2][world*rows][row_words] data, [world] flags, [2] ctl
+namespace {
+struct PeerLayout { size_t epoch_words, flags_at, ctl_at, total; };
+PeerLayout peer_layout(int world, int64_t rows, int row_words)
+{
+    PeerLayout l;
+    l.epoch_words = (size_t)world * (size_t)rows * (size_t)row_words;
+    l.flags_at = 2 * l.epoch_words;
+    l.ctl_at = l.flags_at + (size_t)world;
+    l.total = (l.ctl_at + 2) * sizeof(uint32_t);
+    return l;
+}
+} // namespace
+
+int lzb_peer_bytes(int world, int64_t rows_per_rank, int row_words, size_t *bytes)
+{
+    if (!bytes || world <= 0 || world > kMaxPeers || rows_per_rank <= 0 || row_words <= 0) return fail(LZB_E_ARG, "peer_bytes: bad argument (1..%d ranks)", kMaxPeers);
+    *bytes = peer_layout(world, rows_per_rank, row_words).total;
+    return LZB_OK;
+}
+
+int lzb_peer_alloc(size_t bytes, void **buf_dev)
+{
+    if (!buf_dev || bytes == 0) return fail(LZB_E_ARG, "peer_alloc: bad argument");
+    LZB_CUDA(cudaMalloc(buf_dev, bytes)); // plain cudaMalloc: shareable through cudaIpcGetMemHandle
+    LZB_CUDA(cudaMemset(*buf_dev, 0, bytes));
+    LZB_CUDA(cudaDeviceSynchronize());
+    return LZB_OK;
+}
+
+int lzb_peer_free(void *buf_dev)
+{
+    if (buf_dev) LZB_CUDA(cudaFree(buf_dev));
+    return LZB_OK;
+}
+
+int lzb_peer_export(void *buf_dev, void *handle_64_bytes)
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    if (!buf_dev || !handle_64_bytes) return fail(LZB_E_ARG, "peer_export: bad argument");
+    cudaIpcMemHandle_t h;
+    LZB_CUDA(cudaIpcGetMemHandle(&h, buf_dev));
+    memcpy(handle_64_bytes, &h, sizeof(h));
+    return LZB_OK;
+}
+
+int lzb_peer_import(const void *handle_64_bytes, void **buf_dev)
+{
+    if (!buf_dev || !handle_64_bytes) return fail(LZB_E_ARG, "peer_import: bad argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle_64_bytes, sizeof(h));
+    LZB_CUDA(cudaIpcOpenMemHandle(buf_dev, h, cudaIpcMemLazyEnablePeerAccess));
+    return LZB_OK;
+}
+
+int lzb_peer_unimport(void *buf_dev)
+{
+    if (buf_dev) LZB_CUDA(cudaIpcCloseMemHandle(buf_dev));
+    return LZB_OK;
+}
+
+int lzb_peer_allgather(void *const *bufs_host, int rank, int world, int64_t rows_per_rank, const void *const *pieces_dev,
+                       const int32_t *piece_words, int n_pieces, uint32_t epoch, int64_t timeout_ms, void **result_dev,
+                       void *stream)
+{
+    if (!bufs_host || !pieces_dev || !piece_words || !result_dev) return fail(LZB_E_ARG, "peer_allgather: NULL argument");
+    if (world <= 0 || world > kMaxPeers || rank < 0 || rank >= world || rows_per_rank <= 0) return fail(LZB_E_ARG, "peer_allgather: bad rank / world / rows");
+    if (n_pieces <= 0 || n_pieces > kMaxPieces) return fail(LZB_E_ARG, "peer_allgather: 1..%d pieces", kMaxPieces);
+    if (epoch == 0) return fail(LZB_E_ARG, "peer_allgather: epochs start at 1");
+    PeerArgs a = {};
+    for (int k = 0; k < n_pieces; ++k) {
+        if (!pieces_dev[k] || piece_words[k] <= 0) return fail(LZB_E_ARG, "peer_allgather: piece %d is empty", k);
+        a.piece[k] = (const uint32_t *)pieces_dev[k];
+        a.words[k] = piece_words[k];
+        a.row_words += piece_words[k];
+    }
+    const PeerLayout l = peer_layout(world, rows_per_rank, a.row_words);
+    for (int w = 0; w < world; ++w) {
+        if (!bufs_host[w]) return fail(LZB_E_ARG, "peer_allgather: buffer of rank %d is NULL", w);
+        uint32_t *base = (uint32_t *)bufs_host[w];
+        a.data[w] = base + (size_t)(epoch & 1u) * l.epoch_words;
+        a.flags[w] = base + l.flags_at;
+    }
+    a.ctl = (uint32_t *)bufs_host[rank] + l.ctl_at;
+    a.n_pieces = n_pieces; a.rows = (int)rows_per_rank; a.rank = rank; a.world = world; a.epoch = epoch;
+    a.timeout_ns = (timeout_ms > 0 ? timeout_ms : 2000) * 1000000LL;
+    const long long total = (long long)rows_per_rank * a.row_words;
+    const int blocks = (int)std::min<long long>((total + 255) / 256, 128);
+    k_peer_allgather<<<blocks, 256, 0, (cudaStream_t)stream>>>(a);
+    LZB_CUDA(cudaGetLastError());
+    *result_dev = a.data[rank];
+    return LZB_OK;
+}
+
+int lzb_peer_error(void *own_buf_dev, int world, int64_t rows_per_rank, int row_words, int *error_host, void *stream)
+{
+    if (!own_buf_dev || !error_host) return fail(LZB_E_ARG, "peer_error: bad argument");
+    const PeerLayout l = peer_layout(world, rows_per_rank, row_words);
+    uint32_t e = 0;
+    LZB_CUDA(cudaMemcpyAsync(&e, (uint32_t *)own_buf_dev + l.ctl_at + 1, sizeof(e), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    LZB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    *error_host = (int)e;
     return LZB_OK;
 }
 
