@@ -376,6 +376,55 @@ def test_reference_unit_test_shapes_with_zero_model():
         assert legal[i][int(np.argmax(d))] in legal[i]
 
 
+@pytest.mark.parametrize("policy", ["EfficientZero", "GumbelMuZero", "MuZero"])
+def test_reference_large_case_256_roots_500_simulations(policy):
+    """test_mcts_ctree.py:182-237 (test_mcts_vs_bot_to_play_large): 256 roots x 500 simulations x 20 actions with the
+    all-zero fake model and to_play = 0 for every root; output shapes as asserted there, plus the visit-count sum."""
+    import torch
+    import lightzero_b200 as lzb
+    n, A, S = 256, 20, 500
+    dev = torch.device("cuda")
+
+    class FakeModel:  # MuZeroModelFake of the reference test: zeros everywhere
+        def eval(self):
+            pass
+
+        def recurrent_inference(self, latent, *rest):
+            o = Out()
+            o.latent_state = torch.zeros_like(latent)
+            o.policy_logits = torch.zeros(n, A, device=dev)
+            o.value = torch.zeros(n, 1, device=dev)
+            o.reward = o.value_prefix = torch.zeros(n, 1, device=dev)
+            o.reward_hidden_state = (torch.zeros(1, n, 16, device=dev), torch.zeros(1, n, 16, device=dev))
+            return o
+
+    cfg = dict(num_simulations=S, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=0.997, value_delta_max=0.01,
+               device="cuda", lstm_horizon_len=5, max_num_considered_actions=6,
+               model=dict(support_scale=300, categorical_distribution=False))
+    legal = [list(range(A)) for _ in range(n)]
+    noises = [np.random.dirichlet([0.3] * A).astype(np.float32).tolist() for _ in range(n)]
+    zeros, logits, to_play = [0.0] * n, np.zeros((n, A), np.float32).tolist(), [0] * n
+    lat = np.zeros((n, 100), np.float32)
+    if policy == "EfficientZero":
+        mcts = identity(lzb.EfficientZeroMCTSCtree(cfg))
+        roots = lzb.EfficientZeroMCTSCtree.roots(n, legal)
+        roots.prepare(0.25, noises, zeros, logits, to_play)
+        mcts.search(roots, FakeModel(), lat, (np.zeros((1, n, 16), np.float32), np.zeros((1, n, 16), np.float32)), to_play)
+    elif policy == "GumbelMuZero":
+        mcts = identity(lzb.GumbelMuZeroMCTSCtree(cfg))
+        roots = lzb.GumbelMuZeroMCTSCtree.roots(n, legal)
+        roots.prepare(0.25, noises, zeros, zeros, logits, to_play)
+        mcts.search(roots, FakeModel(), lat, to_play)
+    else:
+        mcts = identity(lzb.MuZeroMCTSCtree(cfg))
+        roots = lzb.MuZeroMCTSCtree.roots(n, legal)
+        roots.prepare(0.25, noises, zeros, logits, to_play)
+        mcts.search(roots, FakeModel(), lat, to_play)
+    dist, vals = roots.get_distributions(), roots.get_values()
+    assert np.array(dist).shape == (n, A) and np.array(vals).shape == (n,)
+    assert (np.array(dist).sum(1) == S).all()
+
+
 def test_sampled_driver_continuous_shapes():
     """test_mcts_sampled_ctree.py:61-135: continuous K=6, D=2, 5 roots; distributions are (5, 6)."""
     import torch
