@@ -383,3 +383,86 @@ class RefForest(_ForestBase):
 
     def dump_tree(self, i, E):
         return _dump(lambda *a: self.L.ref_dump_tree(self.h, *a), i, E, self.A)
+
+
+class RefSampledForest(_ForestBase):
+    """The compiled Sampled-EfficientZero reference tree (oracle/ref_harness_sampled.cpp).  The reference samples each
+    node's K actions itself (wall-clock seeded); ``prepare`` and ``backprop`` RETURN the tables it drew ([n, K, D]) so
+    that the oracle and the CUDA path can be handed the same ones."""
+
+    variant = "sez"
+
+    def __init__(self, n, A, K, continuous=True, per_root=False):
+        self.L = ref_lib("sez")
+        if self.L is None:
+            raise RuntimeError("oracle/_ref/libref_sez.so is not built and /root/reference is absent")
+        self.n, self.A, self.K, self.W = n, A, K, K
+        self.D = A if continuous else 1
+        self.continuous, self.per_root = continuous, per_root
+        self.h = C.c_void_p(self.L.ref_new(n, A, K, int(continuous), int(per_root)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_free(self.h)
+            self.h = None
+
+    def set_delta(self, d):
+        self.L.ref_set_delta(self.h, C.c_float(d))
+
+    def set_rng(self, mode, seed, root_offset=0):
+        assert root_offset == 0
+        assert mode != 2 or self.per_root
+        self.L.ref_rng_mode(int(mode), C.c_uint64(seed))
+
+    def prepare(self, noise_w, noises, rewards, logits, to_play, values=None, sampled_actions=None):
+        nz = None if noises is None else _f(np.asarray(noises, np.float32).reshape(self.n, self.K))
+        rewards, logits, to_play = _f(rewards), _f(logits), _i(to_play)
+        out = np.zeros((self.n, self.K, self.D), np.float32)
+        self.L.ref_prepare(self.h, int(nz is not None), C.c_float(noise_w), _ptr(nz, C.c_float), _ptr(rewards, C.c_float),
+                           _ptr(logits, C.c_float), int(logits.shape[1]), _ptr(to_play, C.c_int), _ptr(out, C.c_float))
+        return out
+
+    def traverse(self, pb_c_base, pb_c_init, discount, to_play, num_simulations=0, max_considered=0, path_stride=0):
+        n = self.n
+        tp = _i(to_play)
+        o = {k: np.zeros(n, np.int32) for k in ("ix", "iy", "search_len", "vtp")}
+        laf = np.zeros((n, self.D), np.float32)
+        self.L.ref_traverse(self.h, int(pb_c_base), C.c_float(pb_c_init), C.c_float(discount), _ptr(tp, C.c_int),
+                            _ptr(o["ix"], C.c_int), _ptr(o["iy"], C.c_int), _ptr(laf, C.c_float),
+                            _ptr(o["search_len"], C.c_int), _ptr(o["vtp"], C.c_int))
+        o["last_action_f"] = laf
+        o["last_action"] = laf[:, 0].astype(np.int32)
+        return o
+
+    def backprop(self, latent_index, discount, rewards, values, logits, is_reset, to_play, sampled_actions=None):
+        rewards, values, logits = _f(rewards), _f(values), _f(logits)
+        is_reset, to_play = _i(is_reset), _i(to_play)
+        out = np.zeros((self.n, self.K, self.D), np.float32)
+        self.L.ref_backprop(self.h, int(latent_index), C.c_float(discount), _ptr(rewards, C.c_float),
+                            _ptr(values, C.c_float), _ptr(logits, C.c_float), int(logits.shape[1]),
+                            _ptr(is_reset, C.c_int), _ptr(to_play, C.c_int), _ptr(out, C.c_float))
+        return out
+
+    def distributions(self):
+        d = np.zeros((self.n, self.K), np.int32)
+        ln = np.zeros(self.n, np.int32)
+        self.L.ref_distributions(self.h, _ptr(d, C.c_int), _ptr(ln, C.c_int))
+        return d, ln
+
+    def values(self):
+        v = np.zeros(self.n, np.float32)
+        self.L.ref_values(self.h, _ptr(v, C.c_float))
+        return v
+
+    def minmax(self):
+        mn, mx = np.zeros(self.n, np.float32), np.zeros(self.n, np.float32)
+        self.L.ref_minmax(self.h, _ptr(mn, C.c_float), _ptr(mx, C.c_float))
+        return mn, mx
+
+    def root_stats(self):
+        vc, vs, rw = np.zeros(self.n, np.int32), np.zeros(self.n, np.float32), np.zeros(self.n, np.float32)
+        self.L.ref_root_stats(self.h, _ptr(vc, C.c_int), _ptr(vs, C.c_float), _ptr(rw, C.c_float))
+        return vc, vs, rw
+
+    def dump_tree(self, i, E):
+        return _dump(lambda *a: self.L.ref_dump_tree(self.h, *a), i, E, self.K)

@@ -11,7 +11,9 @@
  * fixtures generated from the compiled reference for machines where /root/reference is absent.
  * The Sampled-EfficientZero action SAMPLER is the one piece that is parity-unpinned by design
  * (wall-clock seeded std::default_random_engine, ctree_sampled_efficientzero/lib/cnode.cpp:251,336):
- * sampled action tables are injected on both sides instead.
+ * the compiled reference samples as it likes, oracle/ref_harness_sampled.cpp reads the K actions of every
+ * expanded node back out of its tree, and this restatement (and the CUDA path) are handed exactly those
+ * tables, so the Sampled tree's selection / backup logic IS pinned bit for bit; the fixtures carry the tables.
  */
 #ifndef LZB_ORACLE_H
 #define LZB_ORACLE_H

@@ -80,3 +80,35 @@ def run_cpu(forest, sc, rng_mode, seed, record=None, horizon=5):
     forest.run_search(sc.model_fn, sc.S, PB_C_BASE, PB_C_INIT, sc.discount, sc.to_play, max_considered=sc.m,
                       lstm_horizon_len=horizon, record=record)
     return forest
+
+
+def sez_logits(x, continuous):
+    """Policy head output the Sampled-EfficientZero reference can sample from: continuous heads are {mu[D], sigma[D]}
+    and sigma must be positive (std::normal_distribution, sez cnode.cpp:262-266)."""
+    x = np.array(x, np.float32, copy=True)
+    if continuous:
+        D = x.shape[-1] // 2
+        x[..., D:] = np.abs(x[..., D:]) * 0.5 + 0.1
+    return x
+
+
+def run_sez_reference(sc, rng_mode, seed, continuous=True, horizon=5):
+    """Drive the compiled Sampled-EfficientZero reference through one search of scenario ``sc`` and RECORD the action
+    tables it samples into ``sc.root_actions`` / ``sc.actions`` (what the oracle and the CUDA path are then handed).
+    Returns (forest, per-simulation records)."""
+    from oracle.binding import RefSampledForest
+    env_actions = sc.D if continuous else sc.A
+    ref = RefSampledForest(sc.n, env_actions, sc.K, continuous=continuous, per_root=(rng_mode == 2))
+    ref.set_delta(0.01)
+    ref.set_rng(rng_mode, seed)
+    sc.root_actions = ref.prepare(0.25, None, sc.root_reward, sez_logits(sc.root_logits, continuous), sc.to_play)
+    sc.actions = np.zeros((sc.S,) + sc.root_actions.shape, np.float32)
+    rec = []
+    tp = np.asarray(sc.to_play, np.int32)
+    for s in range(sc.S):
+        out = ref.traverse(PB_C_BASE, PB_C_INIT, sc.discount, tp)
+        is_reset = (out["search_len"] % horizon == 0).astype(np.int32)
+        rec.append(dict(out, is_reset=is_reset))
+        sc.actions[s] = ref.backprop(s + 1, sc.discount, sc.reward[s], sc.value[s], sez_logits(sc.logits[s], continuous),
+                                     is_reset, out["vtp"])
+    return ref, rec

@@ -14,15 +14,18 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 
 from oracle.binding import RefForest  # noqa: E402
-from tests.common import Scenario, run_cpu  # noqa: E402
-from tests.test_oracle_vs_reference import CASES, search_summary  # noqa: E402
+from tests.common import Scenario, run_cpu, run_sez_reference  # noqa: E402
+from tests.test_oracle_vs_reference import CASES, search_summary, sez_continuous  # noqa: E402
 
 if __name__ == "__main__":
     out_dir = os.path.dirname(os.path.abspath(__file__))
     for name, (kw, mode) in sorted(CASES.items()):
         sc = Scenario(**kw)
         rec = []
-        ref = run_cpu(RefForest(sc.variant, sc.n, sc.A, sc.legal, per_root=(mode == 2)), sc, mode, 2024, record=rec)
+        if sc.variant == "sez":  # the fixture carries the action tables the reference sampled in this run
+            ref, rec = run_sez_reference(sc, mode, 2024, continuous=sez_continuous(name))
+        else:
+            ref = run_cpu(RefForest(sc.variant, sc.n, sc.A, sc.legal, per_root=(mode == 2)), sc, mode, 2024, record=rec)
         summ = search_summary(ref, sc, rec)
         np.savez_compressed(os.path.join(out_dir, name + ".npz"), **summ)
         print(name, "mean depth %.2f" % summ["search_len"].mean(), "bytes", os.path.getsize(os.path.join(out_dir, name + ".npz")))

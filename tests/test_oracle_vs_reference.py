@@ -12,7 +12,7 @@ import numpy as np
 import pytest
 
 from oracle.binding import OracleForest, RefForest, ref_available
-from tests.common import TICTACTOE_MASKS, Scenario, assert_same, run_cpu
+from tests.common import TICTACTOE_MASKS, Scenario, assert_same, run_cpu, run_sez_reference
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LEGAL9 = [[a for a, x in enumerate(row) if x == 1] for row in TICTACTOE_MASKS]
@@ -40,15 +40,31 @@ CASES = {
     "ez_reuse_a6": (dict(variant="ez", n=32, A=6, S=50, seed=17, reuse=True), 2),
     "ez_reuse_two_player": (dict(variant="ez", n=16, A=9, S=30, seed=18, to_play=[2, 1] * 8, discount=1.0,
                                  reuse=True), 1),
+    # Sampled EfficientZero: the reference samples each node's K actions itself; its tables are recorded and handed to
+    # the oracle (tests/common.py:run_sez_reference), so the whole tree logic downstream of the sampler is compared
+    "sez_continuous_k20_d6": (dict(variant="sez", n=8, A=12, S=50, seed=19, K=20, D=6), 2),
+    "sez_continuous_batch_rng": (dict(variant="sez", n=16, A=4, S=40, seed=20, K=8, D=2), 1),
+    "sez_continuous_two_player": (dict(variant="sez", n=8, A=6, S=30, seed=21, K=6, D=3, to_play=[1, 2] * 4,
+                                       discount=1.0), 2),
+    "sez_discrete_k4_of_6": (dict(variant="sez", n=16, A=6, S=40, seed=22, K=4, D=1), 2),
 }
+SEZ_DISCRETE = {"sez_discrete_k4_of_6"}
+
+
+def sez_continuous(name):
+    return name not in SEZ_DISCRETE
 
 
 def search_summary(forest, sc, rec, trees=3):
     """Everything a parity check looks at, as a flat dict of numpy arrays."""
     out = {}
-    for k in ("ix", "iy", "last_action", "search_len", "vtp", "paths"):
+    keys = ("ix", "iy", "last_action_f", "search_len", "vtp", "is_reset") if sc.variant == "sez" else \
+        ("ix", "iy", "last_action", "search_len", "vtp", "paths")
+    for k in keys:
         if k in rec[0]:  # the ReZero traverse reports no paths
             out[k] = np.stack([r[k] for r in rec])
+    if sc.variant == "sez":  # the tables the reference sampled: part of the fixture, injected everywhere else
+        out["sez_root_actions"], out["sez_actions"] = sc.root_actions, sc.actions
     if getattr(sc, "reuse", False):
         out["infer_stats"] = np.asarray(forest.infer_stats, np.float64)
     d, ln = forest.distributions()
@@ -60,17 +76,23 @@ def search_summary(forest, sc, rec, trees=3):
     for i in range(min(trees, sc.n)):
         t = forest.dump_tree(i, sc.S + 1)
         for k in ("visit", "value_sum", "prior", "reward", "child_e", "hdr"):
+            if k == "prior" and sc.variant == "sez":
+                continue  # log-prob priors never reach selection (uniform branch, sez cnode.cpp:1054-1079): not restated
             out["tree%d_%s" % (i, k)] = t[k]
     if sc.variant == "gmz":
         out["gmz_policies"], out["gmz_child_values"] = forest.gumbel_outputs(sc.discount)
     return out
 
 
-def oracle_summary(name):
+def oracle_summary(name, tables=None):
+    """tables = (root_actions, actions): the Sampled-EfficientZero action tables to inject (from the compiled reference
+    or from its golden fixture)."""
     kw, mode = CASES[name]
     sc = Scenario(**kw)
+    if tables is not None:
+        sc.root_actions, sc.actions = np.asarray(tables[0], np.float32), np.asarray(tables[1], np.float32)
     rec = []
-    f = run_cpu(OracleForest(sc.variant, sc.n, sc.A, sc.legal), sc, mode, 2024, record=rec)
+    f = run_cpu(OracleForest(sc.variant, sc.n, sc.A, sc.legal, K=sc.K, D=sc.D), sc, mode, 2024, record=rec)
     return sc, search_summary(f, sc, rec)
 
 
@@ -79,7 +101,8 @@ def test_oracle_matches_golden_fixture(name):
     path = os.path.join(HERE, "golden", name + ".npz")
     assert os.path.exists(path), "missing fixture %s (run tests/golden/make_golden.py where /root/reference exists)" % path
     want = np.load(path)
-    sc, got = oracle_summary(name)
+    tables = (want["sez_root_actions"], want["sez_actions"]) if name.startswith("sez") else None
+    sc, got = oracle_summary(name, tables)
     assert sorted(want.files) == sorted(got)
     for k in want.files:
         assert_same(got[k], want[k], "%s/%s" % (name, k))
@@ -94,9 +117,16 @@ def test_oracle_matches_compiled_reference(name):
         pytest.skip("oracle/_ref not built and /root/reference absent")
     sc = Scenario(**kw)
     rec = []
-    ref = run_cpu(RefForest(sc.variant, sc.n, sc.A, sc.legal, per_root=(mode == 2)), sc, mode, 2024, record=rec)
-    want = search_summary(ref, sc, rec)
-    _, got = oracle_summary(name)
+    if sc.variant == "sez":
+        ref, rec = run_sez_reference(sc, mode, 2024, continuous=sez_continuous(name))
+        want = search_summary(ref, sc, rec)
+        _, got = oracle_summary(name, (sc.root_actions, sc.actions))
+        assert (np.abs(sc.root_actions) <= 1.0).all() if sez_continuous(name) else (sc.root_actions == np.round(sc.root_actions)).all()
+    else:
+        ref = run_cpu(RefForest(sc.variant, sc.n, sc.A, sc.legal, per_root=(mode == 2)), sc, mode, 2024, record=rec)
+        want = search_summary(ref, sc, rec)
+        _, got = oracle_summary(name)
+    assert sorted(want) == sorted(got)
     for k in want:
         assert_same(got[k], want[k], "%s/%s" % (name, k))
 
