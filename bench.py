@@ -29,6 +29,7 @@ import numpy as np  # noqa: E402
 PB_C_BASE, PB_C_INIT, DISCOUNT, DELTA, NOISE_W, ALPHA = 19652, 1.25, 0.997, 0.01, 0.25, 0.3
 TIE_SEED = 2024
 L2_FLUSH_BYTES = 512 << 20
+HIDDEN = {"ez": 512, "sez": 256}  # LSTM reward-hidden-state width of the EfficientZero flavours
 
 
 def parse_args():
@@ -41,7 +42,9 @@ def parse_args():
     ap.add_argument("--sims", type=int, default=50)
     ap.add_argument("--actions", type=int, default=18)
     ap.add_argument("--latent", type=int, default=1024, help="latent floats per root gathered / stored per simulation")
-    ap.add_argument("--variant", default="mz", choices=["mz", "ez", "gmz"])
+    ap.add_argument("--variant", default="mz", choices=["mz", "ez", "gmz", "sez"],
+                    help="sez = Sampled EfficientZero, continuous actions: --actions is K (sampled actions per node), --action-dim is D")
+    ap.add_argument("--action-dim", type=int, default=6)
     ap.add_argument("--two-player", action="store_true", help="to_play alternates 1/2 (board-game sign flips)")
     ap.add_argument("--streams", type=int, default=1, help="chunks of roots searched on concurrent CUDA streams (graph mode)")
     ap.add_argument("--no-graph", action="store_true", help="value leg: launch per call instead of one CUDA graph")
@@ -54,7 +57,8 @@ def parse_args():
 
 def workload_name(a):
     return "synthetic %s search: %d roots/GPU x %d sims x A=%d, latent %d f32" % (
-        {"mz": "MuZero", "ez": "EfficientZero", "gmz": "Gumbel MuZero (m=16)"}[a.variant] + (" 2-player" if a.two_player else ""),
+        {"mz": "MuZero", "ez": "EfficientZero", "gmz": "Gumbel MuZero (m=16)",
+         "sez": "Sampled EfficientZero (continuous, D=%d, A = K sampled actions)" % a.action_dim}[a.variant] + (" 2-player" if a.two_player else ""),
         a.roots, a.sims, a.actions, a.latent)
 
 
@@ -75,8 +79,12 @@ def make_inputs(a, rank, device):
         logits=rn(S, N, A), reward=rn(S, N) * 0.1, value=rn(S, N),
         latent_roots=rn(N, max(L, 1)), model_latent=rn(S, N, max(L, 1)),
     )
-    if a.variant == "ez":
+    if a.variant in ("ez", "sez"):
         inp["reward"] = rn(S, N)  # value prefixes
+    if a.variant == "sez":  # policy head = {mu[D], sigma[D] > 0} (sez cnode.cpp:239-247)
+        D = a.action_dim
+        head = lambda *shape: torch.cat([rn(*shape, D), rn(*shape, D).abs() * 0.5 + 0.1], dim=-1)
+        inp["root_logits"], inp["logits"] = head(N), head(S, N)
     return inp
 
 
@@ -132,8 +140,8 @@ class TableModel:
     def __init__(self, inp, variant):
         self.inp, self.variant, self.s = inp, variant, 0
         N = inp["model_latent"].shape[1]
-        if variant == "ez":
-            H = 512
+        if variant in ("ez", "sez"):
+            H = HIDDEN[variant]
             self.hidden = (inp["model_latent"][0, :, :1].expand(N, H).contiguous().unsqueeze(0),
                            inp["model_latent"][0, :, :1].expand(N, H).contiguous().unsqueeze(0))
 
@@ -185,11 +193,15 @@ def measure_depth(a, mcts, model, inp, rank):
 
 def make_driver(a, device, graph):
     import lightzero_b200 as lzb
-    cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree, "gmz": lzb.GumbelMuZeroMCTSCtree}[a.variant]
+    cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree, "gmz": lzb.GumbelMuZeroMCTSCtree,
+           "sez": lzb.SampledEfficientZeroMCTSCtree}[a.variant]
+    graph = graph and a.variant != "sez"  # not offered for the sampled tree: its sampler draws fresh numbers per search
     mcts = cls(dict(num_simulations=a.sims, max_num_considered_actions=16, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=DISCOUNT,
                     value_delta_max=DELTA, device=str(device), cuda_graph=graph, tie_break_seed=TIE_SEED,
                     search_streams=a.streams if graph else 1,
-                    model=dict(support_scale=300, categorical_distribution=False)))
+                    lstm_horizon_len=5,
+                    model=dict(support_scale=300, categorical_distribution=False, continuous_action_space=a.variant == "sez",
+                               action_space_size=a.action_dim if a.variant == "sez" else a.actions)))
     mcts.inverse_scalar_transform_handle = lambda x: x  # the synthetic model emits scalars, not categorical supports
     return mcts
 
@@ -199,13 +211,16 @@ def one_search(a, mcts, model, inp, host=None, rank=0):
     host=None: every input already in HBM, outputs stay in HBM.  host=dict of pinned tensors: inputs come from the
     host and the results are read back to the host (the e2e leg)."""
     src = host if host is not None else inp
-    roots = mcts.roots(a.roots, None)
+    if a.variant == "sez":
+        roots = mcts.roots(a.roots, None, a.action_dim, a.actions, True)
+    else:
+        roots = mcts.roots(a.roots, None)
     roots.root_offset = rank * a.roots  # global root index keys the tie-break stream (SURVEY.md 8e)
     if a.variant == "gmz":
         roots.prepare(NOISE_W, src["noise"], src["root_reward"], src["root_value"], src["root_logits"], src["to_play"])
     else:
         roots.prepare(NOISE_W, src["noise"], src["root_reward"], src["root_logits"], src["to_play"])
-    if a.variant == "ez":
+    if a.variant in ("ez", "sez"):
         mcts.search(roots, model, src["latent_roots"], (src["hidden_c"], src["hidden_h"]), src["to_play"])
     else:
         mcts.search(roots, model, src["latent_roots"], src["to_play"])
@@ -277,9 +292,12 @@ def roofline(a, per_kernel_ms, depth, peak_gbs, peak_src):
     """Algorithmic bytes per launch (per root per simulation, x N roots per launch).  The mean depth
     is measured over the whole search; note the leaf rows are read in place from the model's output tensors, so the
     gather moves 8 L bytes per root (4 L read + 4 L written) and there is no separate store into a pool."""
-    N, A, Lb = a.roots, a.actions, 8 * max(a.latent, 1) + (16 * 512 if a.variant == "ez" else 0)
+    N, A, Lb = a.roots, a.actions, 8 * max(a.latent, 1) + (16 * HIDDEN[a.variant] if a.variant in HIDDEN else 0)
     sel = depth * (16 * A + 16) + 8 + 4 * (depth + 1) + Lb
     bak = 4 * A + 16 * A + 28 + (depth + 1) * 20 + 8
+    if a.variant == "sez":  # K children per node; the new node's [K, D] action table is read and stored, the leaf's action read and written
+        sel += 8 * a.action_dim
+        bak += 8 * A * a.action_dim - 4 * A
     alg = {"step": N * (sel + bak), "traverse": N * sel, "backprop": N * bak}
     launches = {"step": a.sims - 1, "traverse": 1, "backprop": 1}  # per search
     avg = {k: sum(v) / len(v) for k, v in per_kernel_ms.items() if v}
@@ -289,7 +307,8 @@ def roofline(a, per_kernel_ms, depth, peak_gbs, peak_src):
     achieved = alg[top] / (avg_ms * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
+    headline = (a.variant, a.roots, a.sims, a.actions, a.latent, a.two_player) == ("mz", 8192, 50, 18, 1024, False)
+    if os.path.exists(tpath) and headline:  # the ncu capture is of the headline workload only
         try:
             traffic = json.load(open(tpath)).get(top)
         except Exception:
@@ -309,6 +328,12 @@ def cpu_inputs(a, n, seed):
     rng = np.random.default_rng(seed)
     S, A, L = a.sims, a.actions, max(a.latent, 1)
     f = lambda *s: rng.standard_normal(s).astype(np.float32)
+    if a.variant == "sez":
+        D = a.action_dim
+        head = lambda *s: np.concatenate([f(*s, D), np.abs(f(*s, D)) * np.float32(0.5) + np.float32(0.1)], axis=-1)
+        return dict(root_logits=head(n), root_reward=f(n) * np.float32(0.1), root_value=f(n), noises=None,
+                    to_play=np.full(n, -1, np.int32), logits=head(S, n), reward=f(S, n), value=f(S, n),
+                    latent_roots=f(n, L), model_latent=f(S, n, L))
     return dict(root_logits=f(n, A), root_reward=f(n) * np.float32(0.1), root_value=f(n),
                 noises=[r for r in rng.dirichlet([ALPHA] * A, size=n).astype(np.float32)],
                 to_play=(np.arange(n, dtype=np.int32) % 2 + 1) if getattr(a, "two_player", False) else np.full(n, -1, np.int32),
@@ -322,10 +347,31 @@ def cpu_search(a, d):
     batch_traverse -> Python gather of leaf latents + np.asarray (:283-286) -> (table-lookup model) ->
     batch_backpropagate.  Uses the compiled unmodified reference (oracle/_ref) when present, else the C port.
     Returns (seconds, kind, visit counts)."""
-    from oracle.binding import OracleForest, RefForest, ref_available
+    from oracle.binding import OracleForest, RefForest, RefSampledForest, ref_available
     n = len(d["to_play"])
     kind = "reference" if ref_available(a.variant) else "port"
     t0 = time.perf_counter()
+    if a.variant == "sez":  # K = a.actions sampled actions of dimension D; the reference samples them itself
+        D, K = a.action_dim, a.actions
+        if kind == "reference":
+            f = RefSampledForest(n, D, K, continuous=True)
+        else:
+            f = OracleForest("sez", n, 2 * D, None, K=K, D=D, continuous=True)
+        f.set_delta(DELTA)
+        f.set_rng(0 if kind == "reference" else 2, TIE_SEED)
+        table = lambda: np.tanh(np.random.default_rng(0).standard_normal((n, K, D))).astype(np.float32)
+        f.prepare(NOISE_W, None, d["root_reward"], d["root_logits"], d["to_play"], sampled_actions=table() if kind == "port" else None)
+        pool = [d["latent_roots"]]
+        for s in range(a.sims):
+            o = f.traverse(PB_C_BASE, PB_C_INIT, DISCOUNT, d["to_play"])
+            leaf = np.asarray([pool[ix][iy] for ix, iy in zip(o["ix"].tolist(), o["iy"].tolist())])  # noqa: F841
+            pool.append(d["model_latent"][s])
+            is_reset = (o["search_len"] % 5 == 0).astype(np.int32)
+            f.backprop(s + 1, DISCOUNT, d["reward"][s], d["value"][s], d["logits"][s], is_reset, o["vtp"],
+                       sampled_actions=table() if kind == "port" else None)
+        dist, _ = f.distributions()
+        f.values()
+        return time.perf_counter() - t0, kind, dist
     legal = [list(range(a.actions))] * n  # the policies always pass explicit legal-action lists (muzero.py:671)
     f = RefForest(a.variant, n, a.actions, legal) if kind == "reference" else OracleForest(a.variant, n, a.actions, legal)
     f.set_delta(DELTA)
@@ -435,9 +481,9 @@ def run_b200_arm(a):
 
     N, S, A = a.roots, a.sims, a.actions
     inp = make_inputs(a, rank, device)
-    if a.variant == "ez":
-        inp["hidden_c"] = torch.zeros(1, N, 512, device=device)
-        inp["hidden_h"] = torch.zeros(1, N, 512, device=device)
+    if a.variant in HIDDEN:
+        inp["hidden_c"] = torch.zeros(1, N, HIDDEN[a.variant], device=device)
+        inp["hidden_h"] = torch.zeros(1, N, HIDDEN[a.variant], device=device)
     model = TableModel(inp, a.variant)
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=device)
     counts = [N] * world
@@ -456,6 +502,8 @@ def run_b200_arm(a):
         return sharding.gather_search_outputs(visits, values, counts, peer=peer) if world > 1 else (visits, values)
 
     # ---- value leg: inputs resident in HBM, the whole search replayed as one CUDA graph
+    if a.variant == "sez":
+        a.no_graph = True
     mcts = make_driver(a, device, graph=not a.no_graph)
 
     mids = []
@@ -496,7 +544,7 @@ def run_b200_arm(a):
     if not a.no_e2e:
         pin = lambda t: t.detach().cpu().pin_memory()
         host = {k: pin(inp[k]) for k in ("root_logits", "noise", "root_reward", "root_value", "to_play", "latent_roots")}
-        if a.variant == "ez":
+        if a.variant in HIDDEN:
             host["hidden_c"], host["hidden_h"] = pin(inp["hidden_c"]), pin(inp["hidden_h"])
         host["visits_out"] = torch.empty((N, A), dtype=torch.int32).pin_memory()
         host["values_out"] = torch.empty(N, dtype=torch.float32).pin_memory()
@@ -571,7 +619,8 @@ def run_b200_arm(a):
                        "wall_ms_per_step_incl_flush": round(1e3 * t_wall / a.steps, 3),
                        "exchange_ms_per_step": round(exchange_ms, 4)},
             # init, minmax, prepare, root slots, select, S-1 steps, backup, outputs (+ the exchange kernel when sharded)
-            "gpu_launches": a.steps * ((5 + S + 1) * (1 if a.no_graph else a.streams) + (1 if peer is not None else 0)),
+            "gpu_launches": a.steps * ((5 + S + 1) * (1 if a.no_graph else a.streams) + (1 if peer is not None else 0)
+                                       + (S + 1 if a.variant == "sez" else 0)),  # + one action-sampling kernel per expansion
             "clocks": clk,
             "roofline": roofline(a, per_kernel, depth, peak, src),
         }
