@@ -195,7 +195,6 @@ def make_driver(a, device, graph):
     import lightzero_b200 as lzb
     cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree, "gmz": lzb.GumbelMuZeroMCTSCtree,
            "sez": lzb.SampledEfficientZeroMCTSCtree}[a.variant]
-    graph = graph and a.variant != "sez"  # not offered for the sampled tree: its sampler draws fresh numbers per search
     mcts = cls(dict(num_simulations=a.sims, max_num_considered_actions=16, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=DISCOUNT,
                     value_delta_max=DELTA, device=str(device), cuda_graph=graph, tie_break_seed=TIE_SEED,
                     search_streams=a.streams if graph else 1,
@@ -502,8 +501,6 @@ def run_b200_arm(a):
         return sharding.gather_search_outputs(visits, values, counts, peer=peer) if world > 1 else (visits, values)
 
     # ---- value leg: inputs resident in HBM, the whole search replayed as one CUDA graph
-    if a.variant == "sez":
-        a.no_graph = True
     mcts = make_driver(a, device, graph=not a.no_graph)
 
     mids = []

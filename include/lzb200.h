@@ -220,6 +220,11 @@ int lzb_root_stats(lzb_forest_t *f, int32_t *visit_dev, float *value_sum_dev, fl
 int lzb_sample_actions(const float *logits_dev, const float *uniforms_dev, float *out_dev, int num_roots, int num_sampled,
                        int action_dim, int action_space, int continuous, int root_offset, uint64_t seed, uint32_t counter,
                        void *stream);
+/* Same, with the seed read from device memory when seed_dev != NULL (a captured CUDA graph of a Sampled search then
+ * draws fresh numbers on every replay: the caller rewrites *seed_dev between replays). */
+int lzb_sample_actions_seeded(const float *logits_dev, const float *uniforms_dev, float *out_dev, int num_roots,
+                              int num_sampled, int action_dim, int action_space, int continuous, int root_offset,
+                              uint64_t seed, const uint64_t *seed_dev, uint32_t counter, void *stream);
 
 /* ---- Root-batch prologue / epilogue (what the callers of search() do per root in Python) ---- */
 

@@ -784,18 +784,26 @@ int lzb_root_stats(lzb_forest_t *f, int32_t *visit_dev, float *value_sum_dev, fl
     return LZB_OK;
 }
 
-int lzb_sample_actions(const float *logits_dev, const float *uniforms_dev, float *out_dev, int num_roots, int num_sampled,
-                       int action_dim, int action_space, int continuous, int root_offset, uint64_t seed, uint32_t counter,
-                       void *stream)
+int lzb_sample_actions_seeded(const float *logits_dev, const float *uniforms_dev, float *out_dev, int num_roots, int num_sampled,
+                              int action_dim, int action_space, int continuous, int root_offset, uint64_t seed,
+                              const uint64_t *seed_dev, uint32_t counter, void *stream)
 {
     if (!logits_dev || !out_dev || num_roots <= 0 || num_sampled <= 0) return fail(LZB_E_ARG, "sample_actions: bad argument");
     if (continuous ? action_dim <= 0 : (action_space <= 0 || action_space > 256 || action_dim != 1))
         return fail(LZB_E_ARG, "sample_actions: continuous needs action_dim > 0; discrete needs 0 < action_space <= 256 and action_dim == 1");
     if (!continuous && num_sampled > action_space) return fail(LZB_E_ARG, "sample_actions: cannot draw %d of %d actions without replacement", num_sampled, action_space);
-    SampleArgs a{logits_dev, uniforms_dev, out_dev, num_roots, num_sampled, action_dim, action_space, continuous, root_offset, seed, counter};
+    SampleArgs a{logits_dev, uniforms_dev, out_dev, num_roots, num_sampled, action_dim, action_space, continuous, root_offset, seed, counter, (const unsigned long long *)seed_dev};
     k_sample_actions<<<(num_roots + 3) / 4, 128, 0, (cudaStream_t)stream>>>(a);
     LZB_CUDA(cudaGetLastError());
     return LZB_OK;
+}
+
+int lzb_sample_actions(const float *logits_dev, const float *uniforms_dev, float *out_dev, int num_roots, int num_sampled,
+                       int action_dim, int action_space, int continuous, int root_offset, uint64_t seed, uint32_t counter,
+                       void *stream)
+{
+    return lzb_sample_actions_seeded(logits_dev, uniforms_dev, out_dev, num_roots, num_sampled, action_dim, action_space,
+                                     continuous, root_offset, seed, nullptr, counter, stream);
 }
 
 int lzb_legal_from_mask(const int8_t *mask_dev, int num_roots, int action_space, int32_t *legal_count_dev,

@@ -40,6 +40,8 @@ struct SampleArgs {
     int N, K, D, A, continuous, root_offset;
     unsigned long long seed;
     unsigned counter;      // which expansion of the search (0 = roots, s + 1 = simulation s)
+    const unsigned long long *seed_dev; // optional: the seed is read from device memory (a captured CUDA graph replays
+                                        // with fresh draws when the caller rewrites this word between replays)
 };
 
 // one warp per root
@@ -47,7 +49,7 @@ __global__ void k_sample_actions(SampleArgs a)
 {
     const int lane = threadIdx.x & 31, i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (i >= a.N) return;
-    const Philox rng(a.seed);
+    const Philox rng(a.seed_dev ? *a.seed_dev : a.seed);
     const uint32_t groot = (uint32_t)(a.root_offset + i);
     if (a.continuous) {
         const float *mu = a.logits + (size_t)i * 2 * a.D, *sg = mu + a.D;

@@ -169,8 +169,6 @@ class _CtreeDriver:
         and the bench) must offer ``model.chunk(lo, hi)`` returning the model for roots [lo, hi)."""
         if roots.forest is not None:
             raise RuntimeError("cuda_graph search needs roots that have not been traversed yet")
-        if self._sampled:
-            raise NotImplementedError("cuda_graph is not offered for the sampled tree (its sampler draws fresh numbers per search)")
         p = roots._prep
         if p is None:
             raise RuntimeError("Roots.prepare / prepare_no_noise must be called before search")
@@ -183,8 +181,10 @@ class _CtreeDriver:
         k = max(1, min(int(_get(self._cfg, "search_streams", 1) or 1), N))
         # players is batch-global (cnode.cpp:776-781): with several chunks it cannot be left to a per-chunk device reduction
         players = 0 if (tp.is_cuda and k == 1) else (1 if int(tp.max()) == -1 else 2)
+        sa = p.get("sampled_actions")  # sampled tree: the root action tables are one more prepared input
         key = (N, roots.action_space_size, S, tuple(lat0.shape), lat0.dtype, id(model), roots._legal is None,
-               p["noise"] is None, players, None if hid is None else tuple(hid[0].shape), str(dev), k)
+               p["noise"] is None, players, None if hid is None else tuple(hid[0].shape), str(dev), k,
+               None if sa is None else tuple(sa.shape[1:]))
         cache = self.__dict__.setdefault("_graphs", {})
         chunks = cache.get(key)
         if chunks is None:
@@ -219,7 +219,11 @@ class _SearchGraph:
         A = roots.action_space_size
         n = hi - lo
         self.driver, self.model, self.dev, self.lo, self.hi, self.stream = driver, model, dev, lo, hi, stream
-        self.static = {k: (None if p[k] is None else torch.empty_like(p[k][lo:hi])) for k in ("logits", "noise", "reward", "to_play", "value")}
+        keys = ("logits", "noise", "reward", "to_play", "value") + (("sampled_actions",) if "sampled_actions" in p else ())
+        self.static = {k: (None if p[k] is None else torch.empty_like(p[k][lo:hi])) for k in keys}
+        # sampled tree: the kernels read the sampler seed from this word, rewritten before every replay, so a replayed
+        # search draws fresh action tables (lzb_sample_actions_seeded)
+        self.seed_dev = torch.zeros(1, dtype=torch.int64, device=dev) if "sampled_actions" in p else None
         self.noise_weight = p["noise_weight"]
         self.lat0 = torch.empty((n,) + tuple(lat0.shape[1:]), dtype=lat0.dtype, device=dev)
         # hidden states come as [1, N, H] (mcts_ctree.py:727-728)
@@ -237,6 +241,7 @@ class _SearchGraph:
         self.shadow.forest = None
         self.shadow._prep = dict(self.static, noise_weight=self.noise_weight)
         self.shadow._players = players if players else None
+        self.shadow._seed_dev = self.seed_dev
         self.graph = None
         self.outs = None
 
@@ -258,6 +263,9 @@ class _SearchGraph:
             for d, s in zip(self.hid, hid):
                 d.copy_(s.reshape(roots.num, -1)[lo:hi], non_blocking=True)
         self.tp.copy_(to_play.reshape(-1)[lo:hi], non_blocking=True)
+        if self.seed_dev is not None:
+            seed = int(getattr(roots, "sample_seed", 0)) & 0xffffffffffffffff
+            self.seed_dev.fill_(seed if seed < (1 << 63) else seed - (1 << 64))
         if self.legal is not None:
             cnt, idx = legal_tensors(self._legal_slice(roots), hi - lo, roots.action_space_size, roots.variant, self.dev)
             self.legal[0].copy_(cnt, non_blocking=True)
@@ -271,6 +279,8 @@ class _SearchGraph:
             sh.forest.reset()
             sh._apply_prepare(reset=False)
         hidden = None if self.hid is None else tuple(self.hid)
+        if self.seed_dev is not None:
+            sh._expansions = 0  # the same (seed, expansion) stream as an eager search of these roots
         self.driver._search(sh, self.model, self.lat0, hidden, self.tp)
         gum = sh.variant == "gmz"
         return sh.forest.root_outputs(discount=float(self.driver._cfg.discount_factor) if gum else 0.0, gumbel=gum)

@@ -34,5 +34,6 @@ class SampledEfficientZeroMCTSCtree(EfficientZeroMCTSCtree):
         roots._expansions = getattr(roots, "_expansions", 0) + 1
         return dict(sampled_actions=sample_actions(net.policy_logits, roots.env_action_space_size,
                                                    roots.num_of_sampled_actions, self._continuous(roots),
-                                                   seed=getattr(roots, "sample_seed", 0), counter=roots._expansions,
+                                                   seed=getattr(roots, "_seed_dev", None) if getattr(roots, "_seed_dev", None) is not None
+                                                   else getattr(roots, "sample_seed", 0), counter=roots._expansions,
                                                    root_offset=roots.root_offset))

@@ -29,11 +29,13 @@ def sample_actions_cuda(policy_logits, action_space_size, num_of_sampled_actions
     D = x.shape[1] // 2 if continuous_action_space else 1
     out = torch.empty((N, K, D), dtype=torch.float32, device=x.device)
     u = None if uniforms is None else uniforms.float().contiguous()
+    seed_dev = seed if isinstance(seed, torch.Tensor) else None  # int64 device scalar: read by the kernel at run time
     with torch.cuda.device(x.device):
-        _lib.check(_lib.lib().lzb_sample_actions(
+        _lib.check(_lib.lib().lzb_sample_actions_seeded(
             C.c_void_p(x.data_ptr()), None if u is None else C.c_void_p(u.data_ptr()), C.c_void_p(out.data_ptr()), N, K, D,
-            x.shape[1], int(bool(continuous_action_space)), int(root_offset), C.c_uint64(int(seed)), C.c_uint32(int(counter)),
-            C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream)))
+            x.shape[1], int(bool(continuous_action_space)), int(root_offset),
+            C.c_uint64(0 if seed_dev is not None else int(seed)), None if seed_dev is None else C.c_void_p(seed_dev.data_ptr()),
+            C.c_uint32(int(counter)), C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream)))
     return out
 
 

@@ -461,3 +461,59 @@ def test_sampled_driver_continuous_shapes():
     acts = np.asarray(roots.get_sampled_actions())
     assert acts.shape == (n, K, D) and np.abs(acts).max() < 1.0
     assert len(roots.get_values()) == n
+
+
+def test_sampled_driver_cuda_graph_matches_eager_and_redraws():
+    """cfg.cuda_graph for the sampled tree: the captured search reads its sampler seed from device memory, so (1) a
+    replay under the seed of an eager search reproduces that search exactly, and (2) the next search draws new tables."""
+    import torch
+    import lightzero_b200 as lzb
+    from lightzero_b200.tree_search import sampling
+    import itertools
+    n, K, D, S, H = 64, 8, 3, 30, 8
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(3)
+    tab = dict(logits=torch.cat([torch.randn(S, n, D, generator=g, device=dev),
+                                 torch.rand(S, n, D, generator=g, device=dev) * 0.5 + 0.1], -1),
+               value=torch.randn(S, n, 1, generator=g, device=dev), prefix=torch.randn(S, n, 1, generator=g, device=dev))
+
+    class Model:
+        def eval(self):
+            self.s = 0
+
+        def recurrent_inference(self, latent, hidden, actions):
+            s = self.s
+            self.s += 1
+            o = Out()
+            o.latent_state = latent * 0.5 + actions.sum(1, keepdim=True)  # depends on the sampled action that was taken
+            o.policy_logits, o.value, o.value_prefix = tab["logits"][s], tab["value"][s] + o.latent_state[:, :1], tab["prefix"][s]
+            o.reward_hidden_state = (hidden[0] + 1, hidden[1] - 1)
+            return o
+
+    root_logits = torch.cat([torch.randn(n, D, generator=g, device=dev), torch.rand(n, D, generator=g, device=dev) * 0.5 + 0.1], -1)
+    lat = torch.randn(n, 16, generator=g, device=dev)
+    hid = (torch.zeros(1, n, H, device=dev), torch.zeros(1, n, H, device=dev))
+    tp = [-1] * n
+
+    def run(graph, ordinal):
+        sampling._search_counter = itertools.count(ordinal)  # the search ordinal is half of the sampler seed
+        cfg = dict(num_simulations=S, discount_factor=0.997, value_delta_max=0.01, device="cuda", lstm_horizon_len=5,
+                   cuda_graph=graph, tie_break_seed=SEED,
+                   model=dict(support_scale=300, categorical_distribution=False, continuous_action_space=True,
+                              num_of_sampled_actions=K, action_space_size=D))
+        mcts = run.cache.setdefault(graph, identity(lzb.SampledEfficientZeroMCTSCtree(cfg)))
+        roots = lzb.SampledEfficientZeroMCTSCtree.roots(n, None, D, K, True)
+        roots.prepare_no_noise(torch.zeros(n, device=dev), root_logits, tp)
+        mcts.search(roots, Model(), lat, hid, tp)
+        v, _ = roots.get_distributions_tensor()
+        return v.clone(), roots.get_values_tensor().clone(), roots.get_sampled_actions_tensor().clone()
+
+    run.cache = {}
+    e1, e2 = run(False, 101), run(False, 102)
+    g1 = run(True, 101)   # warm-up + capture + first replay
+    g2 = run(True, 102)   # pure replay with a new seed
+    g1b = run(True, 101)  # replay again under the first seed
+    for a, b in ((e1, g1), (e2, g2), (e1, g1b)):
+        assert torch.equal(a[2], b[2]) and torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    assert not torch.equal(g1[2], g2[2]) and not torch.equal(g1[0], g2[0])  # fresh root tables and a different search
+    assert (g2[0].sum(1) == S).all()
