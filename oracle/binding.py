@@ -14,8 +14,8 @@ import numpy as np
 from . import build as _build
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-VARIANTS = ("mz", "ez", "gmz", "sez")
-_VID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3}
+VARIANTS = ("mz", "ez", "gmz", "sez", "smz")
+_VID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3, "smz": 4}
 
 _f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
 _i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
@@ -70,6 +70,10 @@ def oracle_lib():
         L.orc_logf.argtypes = [C.c_float]
         L.orc_tiebreak_hash.restype = C.c_uint32
         L.orc_tiebreak_hash.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.orc_chance_bits.restype = C.c_uint64
+        L.orc_chance_bits.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]
+        L.orc_discrete_draw.restype = C.c_int
+        L.orc_discrete_draw.argtypes = [C.POINTER(C.c_double), C.c_int, C.c_double]
         for name in ("orc_expf_mismatch_range", "orc_logf_mismatch_range"):
             getattr(L, name).restype = C.c_long
             getattr(L, name).argtypes = [C.c_uint32, C.c_uint32]
@@ -157,11 +161,28 @@ class _ForestBase:
         return length, infer_sum / S
 
 
+    def run_search_chance(self, model_fn, S, pb_c_base, pb_c_init, discount, to_play, forced=None, record=None):
+        """Restates the Stochastic MuZero driver loop (lzero/mcts/tree_search/mcts_ctree_stochastic.py:117-251):
+        model_fn(sim, ix, iy, last_action, leaf_is_chance) -> dict(reward, value, logits [n, W]) where row i holds the
+        chance logits when leaf i is a chance node (afterstate dynamics + prediction) and policy logits otherwise.
+        ``forced``: per simulation an [n, stride] table of outcomes for the chance levels (oracle / CUDA side), or None
+        to draw; the compiled reference always draws and reports what it took in out["paths"]."""
+        tp = np.asarray(to_play, np.int32)
+        for s in range(S):
+            out = self.traverse_chance(pb_c_base, pb_c_init, discount, tp, forced=None if forced is None else forced[s],
+                                       path_stride=S + 1)
+            m = model_fn(s, out["ix"], out["iy"], out["last_action"], out["leaf_is_chance"])
+            if record is not None:
+                record.append(dict(out))
+            self.backprop(s + 1, discount, m["reward"], m["value"], m["logits"], None, out["vtp"])
+
+
 class OracleForest(_ForestBase):
     def __init__(self, variant, n, A, legal_actions=None, K=0, D=0, continuous=False):
+        """``K``: sampled actions per node (sez) or chance_space_size (smz)."""
         self.L = oracle_lib()
         self.variant, self.n, self.A, self.K, self.D = variant, n, A, K, D
-        self.W = K if variant == "sez" else A
+        self.W = K if variant == "sez" else (max(A, K) if variant == "smz" else A)
         if legal_actions is None:
             legal_actions = [[] for _ in range(n)]
         flat, off = _csr(legal_actions)
@@ -202,6 +223,21 @@ class OracleForest(_ForestBase):
             o["paths"] = paths
         if laf is not None:
             o["last_action_f"] = laf
+        return o
+
+    def traverse_chance(self, pb_c_base, pb_c_init, discount, to_play, forced=None, path_stride=0):
+        n = self.n
+        tp, forced = _i(to_play), _i(forced)
+        o = {k: np.zeros(n, np.int32) for k in ("ix", "iy", "last_action", "search_len", "vtp", "leaf_is_chance")}
+        paths = np.full((n, max(path_stride, 1)), -1, np.int32)
+        self.L.orc_traverse_chance(self.h, int(pb_c_base), C.c_float(pb_c_init), C.c_float(discount), _ptr(tp, C.c_int),
+                                   _ptr(forced, C.c_int), 0 if forced is None else int(forced.shape[1]),
+                                   _ptr(o["ix"], C.c_int), _ptr(o["iy"], C.c_int), _ptr(o["last_action"], C.c_int),
+                                   _ptr(o["search_len"], C.c_int), _ptr(o["vtp"], C.c_int),
+                                   _ptr(o["leaf_is_chance"], C.c_int), _ptr(paths, C.c_int) if path_stride else None,
+                                   int(path_stride))
+        if path_stride:
+            o["paths"] = paths
         return o
 
     def backprop(self, latent_index, discount, rewards, values, logits, is_reset, to_play, sampled_actions=None):
@@ -466,3 +502,93 @@ class RefSampledForest(_ForestBase):
 
     def dump_tree(self, i, E):
         return _dump(lambda *a: self.L.ref_dump_tree(self.h, *a), i, E, self.K)
+
+
+class RefStochasticForest(_ForestBase):
+    """The compiled Stochastic-MuZero reference tree (oracle/ref_harness_stochastic.cpp).  The reference draws its
+    chance outcomes itself (std::random_device); ``traverse_chance`` reports the action / outcome taken at every level
+    in out["paths"] so that the oracle and the CUDA path can be handed the same outcomes.  Every logits array is
+    [n, W], W = max(A, C)."""
+
+    variant = "smz"
+
+    def __init__(self, n, A, C_, legal_actions=None, per_root=False):
+        self.L = ref_lib("smz")
+        if self.L is None:
+            raise RuntimeError("oracle/_ref/libref_smz.so is not built and /root/reference is absent")
+        self.n, self.A, self.K, self.W = n, A, C_, max(A, C_)
+        if legal_actions is None:
+            legal_actions = [[] for _ in range(n)]
+        flat, off = _csr(legal_actions)
+        self.h = C.c_void_p(self.L.ref_new(n, A, C_, _ptr(flat, C.c_int), _ptr(off, C.c_int), int(per_root)))
+        self.per_root = per_root
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_free(self.h)
+            self.h = None
+
+    def set_delta(self, d):
+        self.L.ref_set_delta(self.h, C.c_float(d))
+
+    def set_rng(self, mode, seed, root_offset=0):
+        assert root_offset == 0
+        assert mode != 2 or self.per_root
+        self.L.ref_rng_mode(int(mode), C.c_uint64(seed))
+
+    def prepare(self, noise_w, noises, rewards, logits, to_play, values=None, sampled_actions=None):
+        with_noise = noises is not None
+        nf, no = _csr_f(noises) if with_noise else (None, None)
+        logits = _f(np.asarray(logits, np.float32)[:, :self.A])  # the reference takes [n, A] policy logits at the roots
+        rewards, to_play = _f(rewards), _i(to_play)
+        self.L.ref_prepare(self.h, int(with_noise), C.c_float(noise_w), _ptr(nf, C.c_float), _ptr(no, C.c_int),
+                           _ptr(rewards, C.c_float), _ptr(logits, C.c_float), _ptr(to_play, C.c_int))
+
+    def traverse_chance(self, pb_c_base, pb_c_init, discount, to_play, forced=None, path_stride=0):
+        assert forced is None, "the compiled reference draws its own outcomes"
+        n = self.n
+        tp = _i(to_play)
+        o = {k: np.zeros(n, np.int32) for k in ("ix", "iy", "last_action", "search_len", "vtp", "leaf_is_chance")}
+        paths = np.full((n, max(path_stride, 1)), -1, np.int32)
+        self.L.ref_traverse(self.h, int(pb_c_base), C.c_float(pb_c_init), C.c_float(discount), _ptr(tp, C.c_int),
+                            _ptr(o["ix"], C.c_int), _ptr(o["iy"], C.c_int), _ptr(o["last_action"], C.c_int),
+                            _ptr(o["search_len"], C.c_int), _ptr(o["vtp"], C.c_int), _ptr(o["leaf_is_chance"], C.c_int),
+                            _ptr(paths, C.c_int) if path_stride else None, int(path_stride))
+        if path_stride:
+            o["paths"] = paths
+        return o
+
+    def backprop(self, latent_index, discount, rewards, values, logits, is_reset, to_play, sampled_actions=None):
+        rewards, values, logits, to_play = _f(rewards), _f(values), _f(logits), _i(to_play)
+        assert logits.shape[1] == self.W
+        self.L.ref_backprop(self.h, int(latent_index), C.c_float(discount), _ptr(rewards, C.c_float),
+                            _ptr(values, C.c_float), _ptr(logits, C.c_float), int(self.W), _ptr(to_play, C.c_int))
+
+    def discrete(self, probs, w0, w1):
+        """libstdc++'s std::discrete_distribution<>(probs) under an engine that returns w0, then w1."""
+        p = np.ascontiguousarray(probs, np.float64)
+        return int(self.L.ref_discrete(_ptr(p, C.c_double), int(p.size), C.c_uint32(w0), C.c_uint32(w1)))
+
+    def distributions(self):
+        d = np.zeros((self.n, self.W), np.int32)
+        ln = np.zeros(self.n, np.int32)
+        self.L.ref_distributions(self.h, _ptr(d, C.c_int), _ptr(ln, C.c_int))
+        return d, ln
+
+    def values(self):
+        v = np.zeros(self.n, np.float32)
+        self.L.ref_values(self.h, _ptr(v, C.c_float))
+        return v
+
+    def minmax(self):
+        mn, mx = np.zeros(self.n, np.float32), np.zeros(self.n, np.float32)
+        self.L.ref_minmax(self.h, _ptr(mn, C.c_float), _ptr(mx, C.c_float))
+        return mn, mx
+
+    def root_stats(self):
+        vc, vs, rw = np.zeros(self.n, np.int32), np.zeros(self.n, np.float32), np.zeros(self.n, np.float32)
+        self.L.ref_root_stats(self.h, _ptr(vc, C.c_int), _ptr(vs, C.c_float), _ptr(rw, C.c_float))
+        return vc, vs, rw
+
+    def dump_tree(self, i, E):
+        return _dump(lambda *a: self.L.ref_dump_tree(self.h, *a), i, E, self.W)

@@ -1,6 +1,6 @@
 """TEST INFRASTRUCTURE ONLY: build recipe for the checker libraries.
 
-* ``oracle/_ref/libref_{mz,ez,gmz,sez}.so`` - the UNMODIFIED reference ctree
+* ``oracle/_ref/libref_{mz,ez,gmz,sez,smz}.so`` - the UNMODIFIED reference ctree
   (/root/reference/lzero/mcts/ctree/ctree_*/lib/cnode.cpp + common_lib/cminimax.cpp) compiled from
   where it lies, wrapped by oracle/ref_harness*.cpp and linked with oracle/rng_pin.c.  Only built when
   /root/reference exists (this container); the GPU box uses the prebuilt files that travel with the
@@ -24,6 +24,7 @@ VARIANTS = {
     "ez": ("ctree_efficientzero", "REF_EZ", "ref_harness.cpp"),
     "gmz": ("ctree_gumbel_muzero", "REF_GMZ", "ref_harness.cpp"),
     "sez": ("ctree_sampled_efficientzero", "REF_SEZ", "ref_harness_sampled.cpp"),
+    "smz": ("ctree_stochastic_muzero", "REF_SMZ", "ref_harness_stochastic.cpp"),
 }
 
 

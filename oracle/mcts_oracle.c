@@ -9,7 +9,8 @@
  *
  * File:line citations are relative to /root/reference/lzero/mcts/ctree/ ; "mz" = ctree_muzero/lib/cnode.cpp,
  * "ez" = ctree_efficientzero/lib/cnode.cpp, "gmz" = ctree_gumbel_muzero/lib/cnode.cpp,
- * "sez" = ctree_sampled_efficientzero/lib/cnode.cpp, "mm" = common_lib/cminimax.cpp.
+ * "sez" = ctree_sampled_efficientzero/lib/cnode.cpp, "smz" = ctree_stochastic_muzero/lib/cnode.cpp,
+ * "mm" = common_lib/cminimax.cpp.
  */
 #include <math.h>
 #include <stdlib.h>
@@ -22,6 +23,7 @@
 
 typedef struct Node {
     int visit_count, to_play, latent_index, batch_index, best_action, is_reset;
+    int is_chance; /* smz cnode.h:25: outcome node (children drawn from the priors), else decision node */
     float reward; /* `reward` (mz, gmz) or `value_prefix` (ez, sez) */
     float prior, value_sum, raw_value;
     int n_legal;   /* legal_actions.size() */
@@ -35,6 +37,7 @@ typedef struct { float maximum, minimum, value_delta_max; } MinMax; /* cminimax.
 
 struct OrcForest {
     int variant, n, A, K, D, continuous;
+    int C, W; /* smz: chance_space_size and the row stride max(A, C) of every logits array */
     Node *roots;
     MinMax *mm;
     float *gumbel; /* gmz: shared N(0)-seeded table, see orc_gumbel_noise */
@@ -157,6 +160,53 @@ static void node_expand_sampled(Node *nd, int to_play, int latent_index, int bat
     nd->children = (Node *)malloc(sizeof(Node) * (size_t)K);
     nd->n_children = K; /* children.size(); assumes no 6-decimal hash collisions (sez:79-111) */
     for (int j = 0; j < K; ++j) node_init(&nd->children[j], 0.0f);
+}
+
+/* Stochastic MuZero CNode::expand (smz:96-166): a chance node takes C chance logits, has its reward zeroed and
+ * decision children; a decision node takes A policy logits and has chance children.  The `child_is_chance`
+ * argument of the reference is overwritten before use (smz:115-122), so it is not restated. */
+static void node_expand_smz(Node *nd, int to_play, int latent_index, int batch_index, float reward, const float *logits,
+                            int A, int C)
+{
+    node_expand(nd, to_play, latent_index, batch_index, reward, 0.0f, logits, nd->is_chance ? C : A);
+    if (nd->is_chance) nd->reward = 0.0f;
+    for (int j = 0; j < nd->n_children; ++j) nd->children[j].is_chance = !nd->is_chance;
+}
+
+/* Counter-based source of the chance draws: 64 bits per (seed, simulation, global root, depth).  The reference
+ * seeds an mt19937 from std::random_device for every draw (smz:622-623), which nothing can reproduce; the
+ * contract here is explicit, like the tie-break stream's (include/lzb200.h). */
+uint64_t orc_chance_bits(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth)
+{
+    uint64_t x = mix64(seed + 0x9E3779B97F4A7C15ULL * (uint64_t)(sim + 1u));
+    return mix64(x ^ (((uint64_t)root << 32) | (uint64_t)depth) ^ 0xC2B2AE3D27D4EB4FULL);
+}
+
+/* std::discrete_distribution<>(probs)(gen) of libstdc++ 13 (bits/random.tcc:2657-2714) for a uniform u in [0, 1):
+ * probabilities normalised by their double sum, partial sums with the last one forced to 1.0, lower_bound.
+ * probs are the children's float priors widened to double (smz:617-620). */
+int orc_discrete_draw(const double *probs, int n, double u)
+{
+    if (n < 2) return 0;
+    double sum = 0.0;
+    for (int j = 0; j < n; ++j) sum += probs[j];
+    double cp = 0.0;
+    int pos = 0;
+    for (int j = 0; j < n; ++j) {
+        cp += probs[j] / sum;
+        double c = (j == n - 1) ? 1.0 : cp;
+        if (c < u) pos = j + 1; /* lower_bound over a sequence partitioned by (c < u) */
+    }
+    return pos < n ? pos : n - 1;
+}
+
+static int chance_outcome(const Node *nd, double u)
+{
+    double *p = (double *)malloc(sizeof(double) * (size_t)(nd->n_children > 0 ? nd->n_children : 1));
+    for (int j = 0; j < nd->n_children; ++j) p[j] = (double)nd->children[j].prior;
+    int pos = orc_discrete_draw(p, nd->n_children, u);
+    free(p);
+    return pos;
 }
 
 static void node_add_noise(Node *nd, float frac, const float *noises)
@@ -474,6 +524,8 @@ OrcForest *orc_new(int variant, int n, int A, const int *legal_flat, const int *
 { /* CRoots::CRoots (mz:301-317; sez:625-673) */
     OrcForest *f = (OrcForest *)calloc(1, sizeof(OrcForest));
     f->variant = variant; f->n = n; f->A = A; f->K = K; f->D = D; f->continuous = continuous;
+    f->C = (variant == ORC_SMZ) ? K : 0; /* smz: K carries chance_space_size (smz:327-347) */
+    f->W = (f->C > A) ? f->C : A;
     f->roots = (Node *)malloc(sizeof(Node) * (size_t)n);
     f->mm = (MinMax *)malloc(sizeof(MinMax) * (size_t)n);
     f->paths = (Node ***)calloc((size_t)n, sizeof(Node **));
@@ -519,6 +571,8 @@ void orc_prepare(OrcForest *f, int with_noise, float noise_w, const float *noise
         Node *r = &f->roots[i];
         if (f->variant == ORC_SEZ)
             node_expand_sampled(r, to_play[i], 0, i, rewards[i], sampled_actions + (size_t)i * f->K * f->D, f->K, f->D);
+        else if (f->variant == ORC_SMZ) /* smz:349-386; logits rows have stride W */
+            node_expand_smz(r, to_play[i], 0, i, rewards[i], logits + (size_t)i * f->W, f->A, f->C);
         else
             node_expand(r, to_play[i], 0, i, rewards[i], values ? values[i] : 0.0f, logits + (size_t)i * f->A, f->A);
         if (with_noise && f->variant != ORC_SEZ) node_add_noise(r, noise_w, noise_flat + noise_off[i]);
@@ -583,6 +637,69 @@ void orc_traverse(OrcForest *f, int pb_c_base, float pb_c_init, float discount, 
     f->sim += 1;
 }
 
+/* Stochastic MuZero cbatch_traverse (smz:713-787) + cselect_child (smz:596-660): decision levels are pUCT with the
+ * pinned tie-break stream (its position counts rand() calls, i.e. decision levels); chance levels take the outcome in
+ * forced[i * forced_stride + depth] when that is >= 0 (outcomes read back from the compiled reference), else draw
+ * it from the children's priors with orc_chance_bits / orc_discrete_draw.  compute_mean_q runs on both kinds. */
+void orc_traverse_chance(OrcForest *f, int pb_c_base, float pb_c_init, float discount, const int *to_play,
+                         const int *forced, int forced_stride, int *ix, int *iy, int *last_action, int *search_len,
+                         int *vtp, int *leaf_is_chance, int *path_actions, int path_stride)
+{
+    float parent_q = 0.0f;
+    int largest = to_play[0];
+    for (int i = 1; i < f->n; ++i)
+        if (to_play[i] > largest) largest = to_play[i];
+    int players = (largest == -1) ? 1 : 2;
+    int last = -1;
+    for (int i = 0; i < f->n; ++i) {
+        Node *node = &f->roots[i];
+        int is_root = 1, len = 0, cap = 8, v = to_play[i];
+        Node **path = (Node **)malloc(sizeof(Node *) * (size_t)cap);
+        int plen = 0;
+        path[plen++] = node;
+        if (f->rng_mode == 2) parent_q = 0.0f;
+        while (node->n_children > 0) {
+            float mean_q = compute_mean_q(f, node, is_root, parent_q, discount);
+            is_root = 0;
+            parent_q = mean_q;
+            int pos;
+            if (node->is_chance) {
+                int fo = (forced && len < forced_stride) ? forced[(size_t)i * forced_stride + len] : -1;
+                if (fo >= 0) {
+                    pos = fo;
+                } else {
+                    uint64_t bits = orc_chance_bits(f->rng_seed, f->sim, f->root_offset + (uint32_t)i, (uint32_t)len);
+                    pos = chance_outcome(node, (double)(bits >> 11) * (1.0 / 9007199254740992.0));
+                }
+            } else {
+                pos = select_child(f, node, &f->mm[i], pb_c_base, pb_c_init, discount, mean_q, players, (uint32_t)i,
+                                   (uint32_t)(len >> 1));
+                if (pos < 0) pos = 0;
+            }
+            if (players > 1) v = (v == 1) ? 2 : 1; /* smz:756-763: flips on chance levels too */
+            int action = node->legal[pos];
+            node->best_action = action;
+            if (path_actions && len < path_stride) path_actions[(size_t)i * path_stride + len] = action;
+            node = &node->children[pos];
+            last = action;
+            if (plen == cap) { cap *= 2; path = (Node **)realloc(path, sizeof(Node *) * (size_t)cap); }
+            path[plen++] = node;
+            len += 1;
+        }
+        Node *parent = path[plen - 2];
+        ix[i] = parent->latent_index;
+        iy[i] = parent->batch_index;
+        last_action[i] = last;
+        search_len[i] = len;
+        vtp[i] = v;
+        if (leaf_is_chance) leaf_is_chance[i] = node->is_chance; /* smz:782 */
+        free(f->paths[i]);
+        f->paths[i] = path;
+        f->path_len[i] = plen;
+    }
+    f->sim += 1;
+}
+
 static void backpropagate(const OrcForest *f, Node **path, int plen, MinMax *mm, int to_play, float value, float discount)
 { /* cbackpropagate (mz:419-478; ez:482-575; gmz:605-631; sez:860-945) */
     float bootstrap = value;
@@ -619,6 +736,8 @@ void orc_backprop(OrcForest *f, int latent_index, float discount, const float *r
         if (f->variant == ORC_SEZ)
             node_expand_sampled(leaf, to_play[i], latent_index, i, rewards[i], sampled_actions + (size_t)i * f->K * f->D,
                                 f->K, f->D);
+        else if (f->variant == ORC_SMZ) /* smz:559-593: the driver's two calls cover every tree exactly once */
+            node_expand_smz(leaf, to_play[i], latent_index, i, rewards[i], logits + (size_t)i * f->W, f->A, f->C);
         else
             node_expand(leaf, to_play[i], latent_index, i, rewards[i], values[i], logits + (size_t)i * f->A, f->A);
         if (is_vp(f)) leaf->is_reset = is_reset ? is_reset[i] : 0;
@@ -716,7 +835,7 @@ void orc_backprop_reuse(OrcForest *f, int latent_index, float discount, const fl
 
 void orc_distributions(OrcForest *f, int *dist, int *len)
 { /* get_distributions (mz:259-277,387-403): legal order, length n_legal; [] when not expanded */
-    int W = (f->variant == ORC_SEZ) ? f->K : f->A;
+    int W = (f->variant == ORC_SEZ) ? f->K : f->W;
     for (int i = 0; i < f->n; ++i) {
         Node *r = &f->roots[i];
         int m = r->n_children > 0 ? r->n_legal : 0;
@@ -753,7 +872,7 @@ void orc_gumbel_outputs(OrcForest *f, float discount, float *policies, float *ch
 void orc_dump_tree(OrcForest *f, int i, int E, int *visit, float *value_sum, float *prior, float *reward,
                    int *child_e, int *hdr, float *raw_value)
 { /* same layout as ref_dump_tree in oracle/ref_harness.cpp */
-    int W = (f->variant == ORC_SEZ) ? f->K : f->A;
+    int W = (f->variant == ORC_SEZ) ? f->K : f->W;
     int cap = 64, top = 0;
     Node **stack = (Node **)malloc(sizeof(Node *) * (size_t)cap);
     int *pes = (int *)malloc(sizeof(int) * (size_t)cap);
@@ -765,7 +884,7 @@ void orc_dump_tree(OrcForest *f, int i, int E, int *visit, float *value_sum, flo
         if (e < 0 || e >= E) continue;
         hdr[e * 4 + 0] = nd->n_legal;
         hdr[e * 4 + 1] = nd->to_play;
-        hdr[e * 4 + 2] = is_vp(f) ? nd->is_reset : 0;
+        hdr[e * 4 + 2] = is_vp(f) ? nd->is_reset : (f->variant == ORC_SMZ ? nd->is_chance : 0);
         hdr[e * 4 + 3] = pe;
         if (raw_value && f->variant == ORC_GMZ) raw_value[e] = nd->raw_value;
         for (int j = 0; j < nd->n_legal; ++j) {

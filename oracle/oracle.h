@@ -1,6 +1,7 @@
 /*
  * TEST INFRASTRUCTURE ONLY.  Plain-C CPU restatement of LightZero's batched ctree MCTS
- * (/root/reference/lzero/mcts/ctree/ctree_{muzero,efficientzero,gumbel_muzero,sampled_efficientzero}).
+ * (/root/reference/lzero/mcts/ctree/ctree_{muzero,efficientzero,gumbel_muzero,sampled_efficientzero,
+ * stochastic_muzero}).
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load
  * this library; nothing under lightzero_b200/ does.
  *
@@ -14,6 +15,10 @@
  * the compiled reference samples as it likes, oracle/ref_harness_sampled.cpp reads the K actions of every
  * expanded node back out of its tree, and this restatement (and the CUDA path) are handed exactly those
  * tables, so the Sampled tree's selection / backup logic IS pinned bit for bit; the fixtures carry the tables.
+ * The Stochastic-MuZero chance DRAW is unpinned in the same way (an mt19937 seeded from std::random_device per
+ * draw, ctree_stochastic_muzero/lib/cnode.cpp:622-623): oracle/ref_harness_stochastic.cpp reports the outcome the
+ * reference took at every chance level, this restatement and the CUDA path are handed those outcomes, and the draw's
+ * arithmetic (orc_discrete_draw) is pinned against libstdc++'s discrete_distribution under a scripted engine.
  */
 #ifndef LZB_ORACLE_H
 #define LZB_ORACLE_H
@@ -23,7 +28,7 @@
 extern "C" {
 #endif
 
-enum { ORC_MZ = 0, ORC_EZ = 1, ORC_GMZ = 2, ORC_SEZ = 3 };
+enum { ORC_MZ = 0, ORC_EZ = 1, ORC_GMZ = 2, ORC_SEZ = 3, ORC_SMZ = 4 };
 
 float orc_expf(float x);
 float orc_logf(float x);
@@ -50,6 +55,12 @@ void orc_traverse_reuse(OrcForest *f, int pb_c_base, float pb_c_init, float disc
 void orc_backprop_reuse(OrcForest *f, int latent_index, float discount, const float *rewards, const float *values,
                         const float *logits, const int *is_reset, const int *to_play, const int *no_inference_lst,
                         const int *reuse_lst, const float *reuse_value);
+/* Stochastic MuZero (ORC_SMZ: orc_new's K = chance_space_size C; every logits row has stride max(A, C)) */
+uint64_t orc_chance_bits(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth);
+int orc_discrete_draw(const double *probs, int n, double u);
+void orc_traverse_chance(OrcForest *f, int pb_c_base, float pb_c_init, float discount, const int *to_play,
+                         const int *forced, int forced_stride, int *ix, int *iy, int *last_action, int *search_len,
+                         int *vtp, int *leaf_is_chance, int *path_actions, int path_stride);
 void orc_distributions(OrcForest *f, int *dist, int *len);
 void orc_values(OrcForest *f, float *out);
 void orc_minmax(OrcForest *f, float *mn, float *mx);

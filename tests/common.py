@@ -18,17 +18,18 @@ class Scenario:
         rng = np.random.default_rng(seed)
         self.variant, self.n, self.A, self.S, self.discount, self.m = variant, n, A, S, discount, max_considered
         self.K, self.D = K, D
+        W = self.W = max(A, K) if variant == "smz" else A  # smz: K = chance_space_size, rows hold policy OR chance logits
         self.legal = legal if legal is not None else [list(range(A)) for _ in range(n)]
         self.to_play = np.asarray(to_play if to_play is not None else [-1] * n, np.int32)
         z = 0.0 if zero_model else 1.0
-        self.root_logits = (rng.standard_normal((n, A)) * z).astype(np.float32)
+        self.root_logits = (rng.standard_normal((n, W)) * z).astype(np.float32)
         self.root_reward = (rng.standard_normal(n) * reward_scale * z).astype(np.float32)
         self.root_value = (rng.standard_normal(n) * z).astype(np.float32)
         self.noises = [rng.dirichlet([0.3] * len(l)).astype(np.float32) for l in self.legal]
-        self.noise_pad = np.zeros((n, A), np.float32)
+        self.noise_pad = np.zeros((n, W), np.float32)
         for i, nz in enumerate(self.noises):
             self.noise_pad[i, :len(nz)] = nz
-        self.logits = (rng.standard_normal((S, n, A)) * z).astype(np.float32)
+        self.logits = (rng.standard_normal((S, n, W)) * z).astype(np.float32)
         self.reward = (rng.standard_normal((S, n)) * reward_scale * z).astype(np.float32)
         if variant in ("ez", "sez"):  # value prefixes accumulate along a path in a real model; any floats do here
             self.reward = (rng.standard_normal((S, n)) * z).astype(np.float32)
@@ -41,6 +42,11 @@ class Scenario:
         if reuse:  # ReZero: the action the trajectory took at each root and the value searched at the next state
             self.true_action = np.asarray([l[rng.integers(len(l))] for l in self.legal], np.int32)
             self.reuse_value = (rng.standard_normal(n) * z).astype(np.float32)
+
+        self.forced = None  # smz: per simulation, the [n, S+1] outcome tables to take at the chance levels
+
+    def model_fn_chance(self, s, ix, iy, last_action, leaf_is_chance):
+        return dict(reward=self.reward[s], value=self.value[s], logits=self.logits[s])
 
     def model_fn(self, s, ix, iy, last_action):
         out = dict(reward=self.reward[s], value=self.value[s], logits=self.logits[s])
@@ -72,6 +78,10 @@ def run_cpu(forest, sc, rng_mode, seed, record=None, horizon=5):
         kw["sampled_actions"] = sc.root_actions
     forest.prepare(0.25, sc.noises if sc.variant != "sez" else None, sc.root_reward, sc.root_logits, sc.to_play,
                    values=sc.root_value, **kw)
+    if sc.variant == "smz":
+        forest.run_search_chance(sc.model_fn_chance, sc.S, PB_C_BASE, PB_C_INIT, sc.discount, sc.to_play,
+                                 forced=None if forest.__class__.__name__.startswith("Ref") else sc.forced, record=record)
+        return forest
     if getattr(sc, "reuse", False):
         forest.infer_stats = forest.run_search_reuse(sc.model_fn, sc.S, PB_C_BASE, PB_C_INIT, sc.discount, sc.to_play,
                                                      sc.true_action, sc.reuse_value, lstm_horizon_len=horizon,

@@ -11,7 +11,7 @@ import os
 import numpy as np
 import pytest
 
-from oracle.binding import OracleForest, RefForest, ref_available
+from oracle.binding import OracleForest, RefForest, RefStochasticForest, ref_available
 from tests.common import TICTACTOE_MASKS, Scenario, assert_same, run_cpu, run_sez_reference
 
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -47,6 +47,12 @@ CASES = {
     "sez_continuous_two_player": (dict(variant="sez", n=8, A=6, S=30, seed=21, K=6, D=3, to_play=[1, 2] * 4,
                                        discount=1.0), 2),
     "sez_discrete_k4_of_6": (dict(variant="sez", n=16, A=6, S=40, seed=22, K=4, D=1), 2),
+    # Stochastic MuZero (K = chance_space_size): the reference draws its chance outcomes itself; the outcomes it took
+    # are recorded per level ("paths") and handed to the oracle, so everything but the draw is compared
+    "smz_2048_a4_c32": (dict(variant="smz", n=16, A=4, S=50, seed=23, K=32), 2),
+    "smz_a6_c2_batch": (dict(variant="smz", n=32, A=6, S=50, seed=24, K=2), 1),
+    "smz_masks_two_player": (dict(variant="smz", n=16, A=9, S=40, seed=25, K=5, legal=LEGAL9, to_play=[1, 2] * 8,
+                                  discount=1.0), 2),
 }
 SEZ_DISCRETE = {"sez_discrete_k4_of_6"}
 
@@ -59,7 +65,7 @@ def search_summary(forest, sc, rec, trees=3):
     """Everything a parity check looks at, as a flat dict of numpy arrays."""
     out = {}
     keys = ("ix", "iy", "last_action_f", "search_len", "vtp", "is_reset") if sc.variant == "sez" else \
-        ("ix", "iy", "last_action", "search_len", "vtp", "paths")
+        ("ix", "iy", "last_action", "search_len", "vtp", "paths", "leaf_is_chance")
     for k in keys:
         if k in rec[0]:  # the ReZero traverse reports no paths
             out[k] = np.stack([r[k] for r in rec])
@@ -84,11 +90,12 @@ def search_summary(forest, sc, rec, trees=3):
     return out
 
 
-def oracle_summary(name, tables=None):
+def oracle_summary(name, tables=None, forced=None):
     """tables = (root_actions, actions): the Sampled-EfficientZero action tables to inject (from the compiled reference
-    or from its golden fixture)."""
+    or from its golden fixture); forced = [S, n, S+1] Stochastic-MuZero path tables whose chance levels are replayed."""
     kw, mode = CASES[name]
     sc = Scenario(**kw)
+    sc.forced = forced
     if tables is not None:
         sc.root_actions, sc.actions = np.asarray(tables[0], np.float32), np.asarray(tables[1], np.float32)
     rec = []
@@ -102,7 +109,7 @@ def test_oracle_matches_golden_fixture(name):
     assert os.path.exists(path), "missing fixture %s (run tests/golden/make_golden.py where /root/reference exists)" % path
     want = np.load(path)
     tables = (want["sez_root_actions"], want["sez_actions"]) if name.startswith("sez") else None
-    sc, got = oracle_summary(name, tables)
+    sc, got = oracle_summary(name, tables, forced=want["paths"] if name.startswith("smz") else None)
     assert sorted(want.files) == sorted(got)
     for k in want.files:
         assert_same(got[k], want[k], "%s/%s" % (name, k))
@@ -122,6 +129,11 @@ def test_oracle_matches_compiled_reference(name):
         want = search_summary(ref, sc, rec)
         _, got = oracle_summary(name, (sc.root_actions, sc.actions))
         assert (np.abs(sc.root_actions) <= 1.0).all() if sez_continuous(name) else (sc.root_actions == np.round(sc.root_actions)).all()
+    elif sc.variant == "smz":
+        ref = run_cpu(RefStochasticForest(sc.n, sc.A, sc.K, sc.legal, per_root=(mode == 2)), sc, mode, 2024, record=rec)
+        want = search_summary(ref, sc, rec)
+        _, got = oracle_summary(name, forced=want["paths"])
+        assert want["leaf_is_chance"].any() and not want["leaf_is_chance"].all()
     else:
         ref = run_cpu(RefForest(sc.variant, sc.n, sc.A, sc.legal, per_root=(mode == 2)), sc, mode, 2024, record=rec)
         want = search_summary(ref, sc, rec)
@@ -160,6 +172,49 @@ def test_gumbel_constants_match_reference():
     O.orc_gumbel_noise(C.c_float(10.0), 700, a.ctypes.data_as(C.c_void_p))
     R.ref_gumbel_noise(C.c_float(10.0), C.c_float(0.0), 700, b.ctypes.data_as(C.c_void_p))
     assert_same(a, b, "gumbel noise table")
+
+
+def test_chance_draw_arithmetic_matches_libstdcxx():
+    """orc_discrete_draw (what the oracle and the CUDA kernels do at a chance node for a uniform u) against libstdc++'s
+    std::discrete_distribution driven by an engine scripted to produce exactly that u (ref_harness_stochastic.cpp)."""
+    if not ref_available("smz"):
+        pytest.skip("oracle/_ref not built and /root/reference absent")
+    import ctypes as C
+    from oracle.binding import oracle_lib
+    O = oracle_lib()
+    ref = RefStochasticForest(1, 2, 2)
+    rng = np.random.default_rng(5)
+    for n in (1, 2, 3, 5, 32, 100):
+        for _ in range(40):
+            p = rng.random(n).astype(np.float32).astype(np.float64) ** rng.integers(1, 6)  # float priors widened, some tiny
+            for _ in range(8):
+                m = int(rng.integers(0, 1 << 53))  # u = m / 2^53, the engine words that generate_canonical turns into it
+                got = O.orc_discrete_draw(p.ctypes.data_as(C.POINTER(C.c_double)), n, C.c_double(m / float(1 << 53)))
+                want = ref.discrete(p, (m << 11) & 0xffffffff, m >> 21)
+                assert got == want, (n, m, got, want)
+    # exact ties with a partial sum: lower_bound takes the first index whose cumulative probability is >= u
+    p = np.asarray([0.25, 0.25, 0.5])
+    for m, want in ((1 << 51, 0), ((1 << 51) + 1, 1), (1 << 52, 1), ((1 << 52) + 1, 2)):
+        assert O.orc_discrete_draw(p.ctypes.data_as(C.POINTER(C.c_double)), 3, C.c_double(m / float(1 << 53))) == want
+        assert ref.discrete(p, (m << 11) & 0xffffffff, m >> 21) == want
+
+
+def test_chance_draws_follow_the_priors():
+    """Unforced oracle search: outcome frequencies at the roots' first chance level follow that node's priors."""
+    kw, mode = CASES["smz_a6_c2_batch"]
+    sc = Scenario(**dict(kw, n=256, S=12, K=3))
+    f = run_cpu(OracleForest("smz", sc.n, sc.A, sc.legal, K=3), sc, 2, 99)
+    seen = np.zeros(3)
+    want = np.zeros(3)
+    for i in range(sc.n):
+        t = f.dump_tree(i, sc.S + 1)
+        for e in range(1, sc.S + 1):
+            if t["hdr"][e, 2] == 1 and t["hdr"][e, 3] == 0:  # a chance node directly below the root
+                v = t["visit"][e, :3].clip(min=0)
+                seen += v
+                want += v.sum() * t["prior"][e, :3]
+    assert seen.sum() > 500
+    assert np.abs(seen - want).max() < 4 * np.sqrt(seen.sum())
 
 
 def test_no_stray_fixtures():
