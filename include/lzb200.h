@@ -6,6 +6,7 @@
  *   lzero/mcts/ctree/ctree_efficientzero/ez_tree.pyx      batch_traverse, batch_backpropagate)
  *   lzero/mcts/ctree/ctree_gumbel_muzero/gmz_tree.pyx
  *   lzero/mcts/ctree/ctree_sampled_efficientzero/ezs_tree.pyx
+ *   lzero/mcts/ctree/ctree_stochastic_muzero/stochastic_mz_tree.pyx
  * (citations below are relative to /root/reference).  All pointers named *_dev are DEVICE pointers
  * on the current CUDA device; every call is asynchronous on `stream` (a cudaStream_t passed as
  * void*), takes plain pointers and sizes, never throws, never allocates device memory and keeps no
@@ -33,13 +34,14 @@
 extern "C" {
 #endif
 
-#define LZB_ABI_VERSION 2
+#define LZB_ABI_VERSION 3
 
 /* tree flavours */
 #define LZB_MZ 0  /* ctree_muzero */
 #define LZB_EZ 1  /* ctree_efficientzero: value_prefix + is_reset */
 #define LZB_GMZ 2 /* ctree_gumbel_muzero */
 #define LZB_SEZ 3 /* ctree_sampled_efficientzero: K sampled actions per node */
+#define LZB_SMZ 4 /* ctree_stochastic_muzero: decision and chance levels alternate */
 
 #define LZB_RNG_BATCH 1
 #define LZB_RNG_PER_ROOT 2
@@ -68,9 +70,16 @@ typedef struct {
 const char *lzb_last_error(void);
 int lzb_abi_version(void);
 uint32_t lzb_tiebreak_hash(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth);
+/* Source of the Stochastic-MuZero chance draws: 64 bits per (rng_seed, simulation, global root, depth of the chance
+ * node); the draw uses u = (bits >> 11) / 2^53.  The reference seeds an mt19937 from std::random_device for every draw
+ * (ctree_stochastic_muzero/lib/cnode.cpp:622-623). */
+uint64_t lzb_chance_bits(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth);
 
 /* Bytes of device workspace needed for N trees, children stride A (action space size; K for the
- * sampled tree), room for S simulations, D = action dimension (sampled tree only, else 0). */
+ * sampled tree), room for S simulations, D = action dimension (sampled tree), chance_space_size C (stochastic
+ * tree, Roots(root_num, legal_actions_list, chance_space_size), stochastic_mz_tree.pyx:31-33), else 0.
+ * Stochastic tree: nodes hold max(A, C) child records and EVERY logits / noise / visits row of this forest has
+ * max(A, C) columns; max(A, C) <= 128. */
 int lzb_forest_bytes(int variant, int num_roots, int action_space, int max_sims, int action_dim, size_t *bytes);
 
 /* Replaces Roots.__cinit__ (mz_tree.pyx:30-32 -> CRoots::CRoots, cnode.cpp:301-317) and
@@ -145,6 +154,24 @@ typedef struct {
     const int32_t *batch_index_dev;
 } lzb_reuse_t;
 
+/* Stochastic MuZero (stochastic_mz_tree.pyx:87-91 -> cbatch_traverse, ctree_stochastic_muzero/lib/cnode.cpp:713-787;
+ * cselect_child :596-660).  The root is a decision node; a decision node's children are chance nodes and vice
+ * versa, so a node at depth d is a chance node iff d is odd.  Decision levels are pUCT with the tie-break stream
+ * (its `depth` counts decision levels, as the reference's rand() calls do); at a chance level the outcome is drawn
+ * from the children's priors exactly as libstdc++'s std::discrete_distribution does for u = lzb_chance_bits-derived
+ * uniform (priors widened to double, normalised by their sum, partial sums, lower_bound).
+ *   forced_outcome_dev [N, forced_stride] (may be NULL): entry [i, d] >= 0 replaces the draw at depth d of tree i
+ *     (parity tests replay the outcomes the compiled reference drew).
+ *   leaf_is_chance_dev [N] (may be NULL): results.leaf_node_is_chance - which model head the leaf needs
+ *     (mcts_ctree_stochastic.py:150-176); equals search_len & 1.
+ * lzb_backprop / lzb_step expand a chance leaf with the first C entries of its logits row and reward 0
+ * (cnode.cpp:115-118), a decision leaf with the first A entries. */
+typedef struct {
+    const int32_t *forced_outcome_dev;
+    int32_t forced_stride;
+    int32_t *leaf_is_chance_dev;
+} lzb_chance_t;
+
 /* batch_traverse (mz_tree.pyx:95-100 -> cbatch_traverse, cnode.cpp:755-824; ez :886-963; gumbel
  * :834-898; sampled :1110-1187) + the leaf gather.  Outputs [N]: ix (latent_state_index_in_search_path),
  * iy (latent_state_index_in_batch, local index), search_len, vtp (virtual_to_play_batchs),
@@ -159,6 +186,7 @@ typedef struct {
     const lzb_gather_t *gathers;
     int32_t num_gathers;
     const lzb_reuse_t *reuse; /* NULL = plain batch_traverse */
+    const lzb_chance_t *chance; /* stochastic tree only; NULL = draw every outcome, no leaf_is_chance output */
 } lzb_traverse_io_t;
 int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse_io_t *io, void *stream);
 

@@ -71,6 +71,11 @@ class Reuse(C.Structure):
                 ("flags_dev", C.c_void_p), ("batch_index_dev", C.c_void_p)]
 
 
+class Chance(C.Structure):
+    """lzb_chance_t"""
+    _fields_ = [("forced_outcome_dev", C.c_void_p), ("forced_stride", C.c_int32), ("leaf_is_chance_dev", C.c_void_p)]
+
+
 class SelectAction(C.Structure):
     """lzb_select_action_t"""
     _fields_ = [("visits_dev", C.c_void_p), ("legal_count_dev", C.c_void_p), ("legal_actions_dev", C.c_void_p),
@@ -85,7 +90,7 @@ class TraverseIO(C.Structure):
     _fields_ = [("to_play_dev", C.c_void_p), ("ix_dev", C.c_void_p), ("iy_dev", C.c_void_p),
                 ("last_action_dev", C.c_void_p), ("last_action_f_dev", C.c_void_p), ("search_len_dev", C.c_void_p),
                 ("vtp_dev", C.c_void_p), ("gathers", C.POINTER(Gather)), ("num_gathers", C.c_int32),
-                ("reuse", C.POINTER(Reuse))]
+                ("reuse", C.POINTER(Reuse)), ("chance", C.POINTER(Chance))]
 
 
 class BackpropIO(C.Structure):
@@ -101,6 +106,7 @@ _PROTOS = {
     "lzb_last_error": (C.c_char_p, []),
     "lzb_abi_version": (C.c_int, []),
     "lzb_tiebreak_hash": (C.c_uint32, [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "lzb_chance_bits": (C.c_uint64, [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]),
     "lzb_forest_bytes": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
     "lzb_forest_create": (C.c_int, [C.POINTER(_P), _P, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                     _P, _P, _P]),
@@ -154,7 +160,7 @@ def lib():
             fn = getattr(L, name)  # AttributeError here == header and library disagree
             fn.restype = res
             fn.argtypes = args
-        if L.lzb_abi_version() != 2:
+        if L.lzb_abi_version() != 3:
             raise RuntimeError("liblzb200.so ABI version mismatch")
         _lib = L
     return _lib

@@ -84,13 +84,18 @@ Layout make_layout(int variant, int N, int A, int S, int D)
 
 int check_dims(int variant, int N, int A, int S, int D)
 {
-    if (variant < LZB_MZ || variant > LZB_SEZ) return fail(LZB_E_ARG, "unknown variant %d", variant);
+    if (variant < LZB_MZ || variant > LZB_SMZ) return fail(LZB_E_ARG, "unknown variant %d", variant);
     if (N <= 0 || A <= 0 || S <= 0) return fail(LZB_E_ARG, "num_roots, action_space and max_sims must be positive");
     if (S > 65000) return fail(LZB_E_UNSUPPORTED, "max_sims %d exceeds the 16-bit visit/expansion packing", S);
     if (variant == LZB_SEZ && D <= 0) return fail(LZB_E_ARG, "sampled tree needs action_dim > 0");
+    if (variant == LZB_SMZ && D <= 0) return fail(LZB_E_ARG, "stochastic tree needs chance_space_size > 0 (passed as action_dim)");
+    if (variant == LZB_SMZ && std::max(A, D) > 128) return fail(LZB_E_UNSUPPORTED, "stochastic tree supports max(action_space, chance_space) <= 128");
     if ((size_t)A * 28 > 200 * 1024) return fail(LZB_E_UNSUPPORTED, "action_space %d too large for shared-memory staging", A);
     return LZB_OK;
 }
+
+// child records per node: the stochastic tree's nodes hold policy OR chance children (action_dim carries C)
+int record_width(int variant, int A, int D) { return variant == LZB_SMZ ? std::max(A, D) : A; }
 
 // warps per block so that `bytes_per_warp` of dynamic shared memory fits the default 48 KB window
 int warps_for(size_t bytes_per_warp) { return (bytes_per_warp * kWarpsPerBlock <= 48 * 1024) ? kWarpsPerBlock : 1; }
@@ -112,7 +117,7 @@ __global__ void k_init(Pool p, const int *legal_count, const int *legal_actions)
     if (i >= p.N) return;
     int n = legal_count ? legal_count[i] : 0;
     const bool all = (n <= 0); // empty list == every action legal (cnode.cpp:101-107)
-    if (all) n = p.A;
+    if (all) n = p.Ad;
     for (int j = 0; j < p.A; ++j) p.legal[(size_t)i * p.A + j] = (all || !legal_actions) ? j : legal_actions[(size_t)i * p.A + j];
     p.block(i, 0)[0] = make_int4(n, 0, 0, 0);
     p.root[i] = make_int4(0, 0, 0, 0);
@@ -336,12 +341,13 @@ extern "C" {
 const char *lzb_last_error(void) { return g_err; }
 int lzb_abi_version(void) { return LZB_ABI_VERSION; }
 uint32_t lzb_tiebreak_hash(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth) { return tiebreak_hash(seed, sim, root, depth); }
+uint64_t lzb_chance_bits(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth) { return chance_bits(seed, sim, root, depth); }
 
 int lzb_forest_bytes(int variant, int num_roots, int action_space, int max_sims, int action_dim, size_t *bytes)
 {
     if (!bytes) return fail(LZB_E_ARG, "bytes is NULL");
     if (int rc = check_dims(variant, num_roots, action_space, max_sims, action_dim)) return rc;
-    *bytes = make_layout(variant, num_roots, action_space, max_sims, action_dim).total;
+    *bytes = make_layout(variant, num_roots, record_width(variant, action_space, action_dim), max_sims, action_dim).total;
     return LZB_OK;
 }
 
@@ -352,6 +358,9 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
     if (!out || !workspace_dev) return fail(LZB_E_ARG, "out / workspace is NULL");
     if (int rc = check_dims(variant, num_roots, action_space, max_sims, action_dim)) return rc;
     if (((uintptr_t)workspace_dev & (kAlign - 1)) != 0) return fail(LZB_E_ARG, "workspace must be %zu-byte aligned", kAlign);
+    const int decision_actions = action_space, chance_space = (variant == LZB_SMZ) ? action_dim : 0;
+    action_space = record_width(variant, action_space, action_dim);
+    if (variant == LZB_SMZ) action_dim = 0;
     const Layout l = make_layout(variant, num_roots, action_space, max_sims, action_dim);
     if (workspace_bytes < l.total) return fail(LZB_E_ARG, "workspace too small: %zu < %zu", workspace_bytes, l.total);
     if ((legal_count_dev == nullptr) != (legal_actions_dev == nullptr)) return fail(LZB_E_ARG, "legal_count / legal_actions must both be given or both NULL");
@@ -359,7 +368,7 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
     char *w = (char *)workspace_dev;
     Pool &p = f->pool;
     p.variant = variant; p.N = num_roots; p.A = action_space; p.S = max_sims; p.E = max_sims + 1; p.D = action_dim;
-    p.root_offset = root_offset; p.B = action_space + 1;
+    p.root_offset = root_offset; p.B = action_space + 1; p.Ad = decision_actions; p.C = chance_space;
     p.node = (int4 *)(w + l.node); p.root = (int4 *)(w + l.root); p.slots = (const char **)(w + l.slots); p.pbc = (float2 *)(w + l.pbc);
     p.legal = (int *)(w + l.legal); p.minmax = (float2 *)(w + l.minmax);
     p.path_a = (int4 *)(w + l.path_a); p.path_b = (int2 *)(w + l.path_b); p.res = (int4 *)(w + l.res);
@@ -462,6 +471,13 @@ int fill_select(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse
         if (!io->reuse->true_action_dev || !io->reuse->reuse_value_dev) return fail(LZB_E_ARG, "reuse: true_action / reuse_value is NULL");
         a.true_action = io->reuse->true_action_dev; a.reuse_value = io->reuse->reuse_value_dev; a.infer_count = io->reuse->infer_count_dev;
     }
+    if (io->chance) {
+        if (p.variant != LZB_SMZ) return fail(LZB_E_ARG, "chance arguments exist for the stochastic tree only");
+        if (io->chance->forced_outcome_dev && io->chance->forced_stride <= 0) return fail(LZB_E_ARG, "chance: forced_stride must be positive");
+        a.forced_outcome = io->chance->forced_outcome_dev; a.forced_stride = io->chance->forced_stride;
+        a.leaf_is_chance = io->chance->leaf_is_chance_dev;
+    }
+    if (p.variant == LZB_SMZ && getenv("LZB_FORCE_WARP_PER_TREE")) return fail(LZB_E_UNSUPPORTED, "the stochastic tree has lane-group kernels only");
     if (p.variant != LZB_GMZ && (f->pbc_base != cfg->pb_c_base || f->pbc_init != cfg->pb_c_init)) {
         k_pbc_table<<<(p.E + 128) / 128, 128, 0, st>>>(p, cfg->pb_c_base, cfg->pb_c_init);
         f->pbc_base = cfg->pb_c_base; f->pbc_init = cfg->pb_c_init;
@@ -575,6 +591,7 @@ bool launch_grouped(int which, const Pool &p, const BackupArgs *b, const SelectA
     case LZB_MZ: return reuse ? launch_group_for<LZB_MZ, true>(which, p, b, a, st) : launch_group_for<LZB_MZ, false>(which, p, b, a, st);
     case LZB_EZ: return reuse ? launch_group_for<LZB_EZ, true>(which, p, b, a, st) : launch_group_for<LZB_EZ, false>(which, p, b, a, st);
     case LZB_SEZ: return launch_group_for<LZB_SEZ, false>(which, p, b, a, st);
+    case LZB_SMZ: return launch_group_for<LZB_SMZ, false>(which, p, b, a, st);
     default: return launch_group_for<LZB_GMZ, false>(which, p, b, a, st);
     }
 }
@@ -607,6 +624,7 @@ int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_travers
         f->sim += 1;
         return LZB_OK;
     }
+    if (p.variant == LZB_SMZ) return fail(LZB_E_UNSUPPORTED, "the stochastic tree has lane-group kernels only");
     switch (p.variant) {
     case LZB_GMZ:
         if (int rc = launch_cfg(k_select_gumbel, bpw, p.N, grid, block, smem)) return rc;
@@ -643,6 +661,7 @@ int lzb_backprop(lzb_forest_t *f, const lzb_backprop_io_t *io, void *stream)
         if (io->latent_index > f->expanded) f->expanded = io->latent_index;
         return LZB_OK;
     }
+    if (p.variant == LZB_SMZ) return fail(LZB_E_UNSUPPORTED, "the stochastic tree has lane-group kernels only");
     switch (p.variant) {
     case LZB_MZ:
         if (int rc = launch_cfg(k_expand_backup<LZB_MZ>, bpw, p.N, grid, block, smem)) return rc;
@@ -688,6 +707,7 @@ int lzb_step(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_backprop_io
         f->sim += 1;
         return LZB_OK;
     }
+    if (p.variant == LZB_SMZ) return fail(LZB_E_UNSUPPORTED, "the stochastic tree has lane-group kernels only");
     switch (p.variant) {
     case LZB_MZ:
         if (int rc = launch_cfg(k_step<LZB_MZ>, bpw, p.N, grid, block, smem)) return rc;

@@ -38,6 +38,7 @@ struct Grp {
     }
     __device__ __forceinline__ float shfl(float v, int src) const { return __shfl_sync(kFull, v, src, G); }
     __device__ __forceinline__ int shfl(int v, int src) const { return __shfl_sync(kFull, v, src, G); }
+    __device__ __forceinline__ double shfl(double v, int src) const { return __shfl_sync(kFull, v, src, G); }
     __device__ __forceinline__ int4 shfl(int4 v, int src) const
     {
         return make_int4(shfl(v.x, src), shfl(v.y, src), shfl(v.z, src), shfl(v.w, src));
@@ -118,11 +119,48 @@ __device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a
     }
 }
 
+// Outcome of a chance node (Stochastic MuZero, ctree_stochastic_muzero/lib/cnode.cpp:610-630) for a uniform u in
+// [0, 1): libstdc++'s std::discrete_distribution (bits/random.tcc:2657-2714) over the n children's priors - widened
+// to double, normalised by their sum, partial sums in index order with the last one forced to 1.0, lower_bound.
+// The lane group holds prior j = lane + G*r in c[r].z; sums run strictly in index order (+0.0 beyond n is exact).
+template <int G, int R>
+__device__ __forceinline__ int chance_draw_g(const int4 (&c)[R], int n, double u, const Grp<G> &grp)
+{
+    const int lane = grp.lane;
+    double pr[R];
+    double sum = 0.0;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        pr[r] = (lane + G * r < n) ? (double)__int_as_float(c[r].z) : 0.0;
+#pragma unroll
+        for (int l = 0; l < G; ++l) sum += grp.shfl(pr[r], l);
+    }
+    double cp = 0.0;
+    int below = 0; // partial sums smaller than u == index lower_bound returns
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int j = lane + G * r;
+        const double q = (j < n) ? pr[r] / sum : 0.0;
+        double mine = 0.0;
+#pragma unroll
+        for (int l = 0; l < G; ++l) {
+            cp += grp.shfl(q, l);
+            mine = (lane == l) ? cp : mine;
+        }
+        const double cj = (j == n - 1) ? 1.0 : mine;
+        below += __popc(grp.ballot(j < n && cj < u));
+    }
+    return (n < 2) ? 0 : min(below, n - 1);
+}
+
 // pUCT traverse of tree i by a lane group (semantics and citations: select_puct_tree in lzb_select.cuh).
 // `live`: this group has a tree (i < N); dead groups run along on tree 0 with every write predicated off.
 // REUSE = cbatch_traverse_with_reuse (ReZero, cnode.cpp:826-928; ez :965-1073): at the root the child on the
 // trajectory's true action is scored by carm_score (cnode.cpp:700-753) and, when chosen, ends the walk even if it
 // is already expanded; such a tree needs no inference and reports ix = -1.
+// VAR = LZB_SMZ (Stochastic MuZero, smz cnode.cpp:596-660,713-787): nodes at odd depth are chance nodes whose outcome
+// is drawn from their priors (chance_draw_g) instead of scored; every going group of a warp is at the same depth, so
+// the decision / chance branch is warp-uniform.
 template <int VAR, int G, int R, bool REUSE = false>
 __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a, int i, bool live, const Grp<G> &grp)
 {
@@ -147,6 +185,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     bool is_root = true;
     bool going = live; // this group is still descending
     bool no_inference = false;
+    int level = 0;   // rounds of the loop below == depth of every group that is still going (warp-uniform)
     bool is_true[R]; // root position j holds the trajectory's action
     float reuse_v = 0.0f;
     if (REUSE) {
@@ -195,6 +234,16 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         }
         const float mean_q = (is_root && nvis > 0) ? total / (float)nvis : (parent_q + total) / (float)(nvis + 1);
 
+        int newpos = 0;
+        if (VAR == LZB_SMZ && (level & 1)) {
+            // ---- chance node: draw the outcome (or replay a given one)
+            const unsigned long long bits = chance_bits(a.seed, (unsigned)a.sim, (unsigned)(p.root_offset + i), (unsigned)depth);
+            newpos = chance_draw_g<G, R>(c, n, (double)(bits >> 11) * (1.0 / 9007199254740992.0), grp);
+            if (a.forced_outcome && going && depth < a.forced_stride) {
+                const int fo = a.forced_outcome[(size_t)i * a.forced_stride + depth];
+                newpos = (fo >= 0) ? fo : newpos;
+            }
+        } else {
         // ---- cucb_score
         const float2 pt = p.pbc[parent_visits - 1]; // {logf((T + c2 + 1) / c2) + c1, sqrtf(T)}, T = parent visits - 1
         const float pbc0 = pt.x, sqT = pt.y;
@@ -240,9 +289,11 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             tie[r] = grp.ballot(j > jstar && sc[r] >= thr); // sc is -inf beyond n
             later += __popc(tie[r]);
         }
-        int newpos = jstar;
+        newpos = jstar;
         if (__any_sync(kFull, later > 0)) { // warp-uniform: no group has a tie -> no draw
-            const unsigned rnd = tiebreak_hash(a.seed, (unsigned)a.sim, hroot, (a.rng_mode == LZB_RNG_PER_ROOT) ? (unsigned)depth : 0u);
+            // the stream position counts the reference's rand() calls: one per level, per DECISION level for smz
+            const unsigned hdepth = (VAR == LZB_SMZ) ? (unsigned)(depth >> 1) : (unsigned)depth;
+            const unsigned rnd = tiebreak_hash(a.seed, (unsigned)a.sim, hroot, (a.rng_mode == LZB_RNG_PER_ROOT) ? hdepth : 0u);
             const int k = (int)(rnd % (unsigned)(later + 1));
             int before = 0; // tie-set members in earlier registers
 #pragma unroll
@@ -256,6 +307,8 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             }
         }
         newpos = any_score ? newpos : 0;
+        }
+        level += 1;
 
         // ---- the chosen child's record lives in lane newpos % G, register newpos / G
         const int rsel = newpos / G;
@@ -280,7 +333,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         ch.z = 0;
         if (going) {
             pos = newpos;
-            parent_reset = h.z;
+            parent_reset = (VAR == LZB_SMZ) ? 0 : h.z; // smz headers carry is_chance in that slot
             if (players > 1) vtp = (vtp == 1) ? 2 : 1; // cnode.cpp:797-804
             if (lane == 0) {
                 pa[depth] = make_int4(e * B + 1 + pos, ch.x, ch.y, ch.w);
@@ -330,6 +383,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         if (a.search_len) a.search_len[i] = depth;
         if (a.vtp) a.vtp[i] = vtp;
         if (VAR != LZB_SEZ && a.last_action) a.last_action[i] = (long long)action;
+        if (VAR == LZB_SMZ && a.leaf_is_chance) a.leaf_is_chance[i] = depth & 1; // smz cnode.cpp:782
     }
 }
 
@@ -549,6 +603,10 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
         if (no_inference || reuse) value_propagate = a.reuse_value[i];
     }
     const bool grow = live && !no_inference; // this tree expands its leaf
+    // Stochastic MuZero (smz cnode.cpp:96-166): a leaf at odd depth is a chance node - C chance logits, reward 0,
+    // decision children; at even depth a decision node with Ad policy logits
+    const bool leaf_chance = (VAR == LZB_SMZ) && (depth & 1);
+    const int width = (VAR == LZB_SMZ) ? (leaf_chance ? p.C : p.Ad) : A;
     const int4 *pa = p.path_a + (size_t)i * (p.S + 1);
     const int2 *pb = p.path_b + (size_t)i * (p.S + 1);
     const int4 root_rec = p.root[i]; // independent of the depth: issued now
@@ -581,26 +639,26 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int j = lane + G * r;
-            lg[r] = (j < A) ? __ldcs(logits + j) : 0.0f;
-            if (j < A) mx = fmaxf(mx, lg[r]);
+            lg[r] = (j < width) ? __ldcs(logits + j) : 0.0f;
+            if (j < width) mx = fmaxf(mx, lg[r]);
         }
         mx = grp.fmax(mx);
         float sum = 0.0f;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int j = lane + G * r;
-            t[r] = (j < A) ? glibc_expf(lg[r] - mx) : 0.0f;
+            t[r] = (j < width) ? glibc_expf(lg[r] - mx) : 0.0f;
 #pragma unroll
-            for (int l = 0; l < G; ++l) sum += grp.shfl(t[r], l); // strictly left to right in action order; +0.0f beyond A
+            for (int l = 0; l < G; ++l) sum += grp.shfl(t[r], l); // strictly left to right in action order; +0.0f beyond the width
         }
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int j = lane + G * r;
-            if (j < A && grow) dst[j] = make_int4(0, 0, __float_as_int(t[r] / sum), 0);
+            if (j < width && grow) dst[j] = make_int4(0, 0, __float_as_int(t[r] / sum), 0);
         }
     }
     if (lane == 0 && grow) {
-        dst[-1] = make_int4(A, to_play, leaf_reset, __float_as_int(value));
+        dst[-1] = make_int4(width, to_play, (VAR == LZB_SMZ) ? (int)leaf_chance : leaf_reset, __float_as_int(value));
         p.best[(size_t)i * p.E + e_new] = -1;
         if (REUSE) p.bidx[(size_t)i * p.E + e_new] = a.batch_index ? a.batch_index[i] : i;
     }
@@ -622,7 +680,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
             } else {
                 const int4 r = pa[q - 1];
                 slot = r.x; x = r.y; vsum = __int_as_float(r.z); rew = __int_as_float(r.w);
-                if (q == depth && !no_inference) rew = leaf_reward; // expand() stamps the leaf's reward / value_prefix first
+                if (q == depth && !no_inference) rew = leaf_chance ? 0.0f : leaf_reward; // expand() stamps the leaf's reward / value_prefix first
             }
             if (two) node_tp = (q == depth) ? to_play : pb[q].x;
             if (VP && q >= 1) {

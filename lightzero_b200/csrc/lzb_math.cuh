@@ -105,6 +105,13 @@ __host__ __device__ __forceinline__ uint32_t tiebreak_hash(uint64_t seed, uint32
     return (uint32_t)(x >> 33);
 }
 
+// chance-draw bits of the stochastic tree (include/lzb200.h: lzb_chance_bits)
+__host__ __device__ __forceinline__ uint64_t chance_bits(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth)
+{
+    const uint64_t x = mix64(seed + 0x9E3779B97F4A7C15ULL * (uint64_t)(sim + 1u));
+    return mix64(x ^ (((uint64_t)root << 32) | (uint64_t)depth) ^ 0xC2B2AE3D27D4EB4FULL);
+}
+
 // ---------------------------------------------------------------- warp helpers
 constexpr unsigned kFull = 0xffffffffu;
 

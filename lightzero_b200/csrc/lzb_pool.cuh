@@ -29,6 +29,7 @@ __device__ __forceinline__ int child_pack(int visits, int expansion) { return (v
 
 struct Pool {
     int variant, N, A, S, E, D, root_offset;
+    int Ad, C;      // stochastic tree: decision actions / chance outcomes per node (A = max of the two); else Ad = A, C = 0
     int B;          // records per block = A + 1
     int4 *node;     // [N][E][B]  block e = {header, child 0 .. child A-1}
     int4 *root;     // [N]     {visit_count, value_sum bits, reward bits, unused}

@@ -28,6 +28,10 @@ struct SelectArgs {
     const int *true_action;    // [N] the trajectory's action at each root
     const float *reuse_value;  // [N] value found by the next state's search
     int *infer_count;          // += trees that stopped on an unexpanded leaf (need inference), or nullptr
+    // Stochastic MuZero (ctree_stochastic_muzero/lib/cnode.cpp:596-660,713-787), lane-group kernels only
+    const int *forced_outcome; // [N][forced_stride] outcome to take at a chance level when >= 0, or nullptr
+    int forced_stride;
+    int *leaf_is_chance;       // [N] or nullptr
 };
 
 // dst[i,:] = rows of the leaf's parent (expansion ix) with 16-byte accesses when rows allow it.  The source is

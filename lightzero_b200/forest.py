@@ -9,9 +9,9 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import BackpropIO, Gather, Reuse, SearchCfg, Slots, TraverseIO, check
+from ._lib import BackpropIO, Chance, Gather, Reuse, SearchCfg, Slots, TraverseIO, check
 
-VARIANT_ID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3}
+VARIANT_ID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3, "smz": 4}
 RNG_BATCH, RNG_PER_ROOT = 1, 2
 
 
@@ -58,7 +58,9 @@ def legal_tensors(legal_actions, N, A, variant, device):
 
 class Forest:
     def __init__(self, variant, num_roots, action_space, max_sims, legal_actions=None, action_dim=0, root_offset=0,
-                 device="cuda", workspace=None):
+                 device="cuda", workspace=None, chance_space=0):
+        """``chance_space``: chance_space_size of the stochastic tree ("smz"); its nodes hold max(action_space,
+        chance_space) child records and every [N, A] tensor of this forest has that many columns (``self.A``)."""
         if not torch.cuda.is_available():
             raise RuntimeError("lightzero_b200 needs a CUDA device (there is no CPU fallback)")
         self.L = _lib.lib()
@@ -67,9 +69,15 @@ class Forest:
             self.device = torch.device("cuda", torch.cuda.current_device())
         self.variant = variant
         self.N, self.A, self.S, self.D = int(num_roots), int(action_space), int(max_sims), int(action_dim)
+        self.Ad, self.C = self.A, int(chance_space)  # decision actions / chance outcomes per node
+        if variant == "smz":
+            if self.C <= 0:
+                raise ValueError("the stochastic tree needs chance_space > 0")
+            self.A = max(self.Ad, self.C)
+        extra = self.C if variant == "smz" else self.D  # the ABI's action_dim slot carries C for the stochastic tree
         self.root_offset = int(root_offset)
         nbytes = C.c_size_t(0)
-        check(self.L.lzb_forest_bytes(VARIANT_ID[variant], self.N, self.A, self.S, self.D, C.byref(nbytes)))
+        check(self.L.lzb_forest_bytes(VARIANT_ID[variant], self.N, self.Ad, self.S, extra, C.byref(nbytes)))
         if workspace is not None and (workspace.numel() < nbytes.value or workspace.device != self.device):
             raise ValueError("workspace must be a uint8 tensor of >= %d bytes on %s" % (nbytes.value, self.device))
         self.workspace = workspace if workspace is not None else torch.empty(nbytes.value, dtype=torch.uint8, device=self.device)
@@ -78,7 +86,7 @@ class Forest:
         h = C.c_void_p()
         with torch.cuda.device(self.device):
             check(self.L.lzb_forest_create(C.byref(h), _p(self.workspace), nbytes.value, VARIANT_ID[variant], self.N,
-                                           self.A, self.S, self.D, self.root_offset, _p(cnt), _p(idx),
+                                           self.Ad, self.S, extra, self.root_offset, _p(cnt), _p(idx),
                                            _stream(self.device)))
         self.h = h
         self._slot_keep = {}
@@ -142,7 +150,7 @@ class Forest:
                   _p(ts["batch_index"]))
         return C.pointer(r), (r, ts)
 
-    def _traverse_io(self, to_play, out, gathers, reuse=None):
+    def _traverse_io(self, to_play, out, gathers, reuse=None, forced_outcome=None):
         d = self.device
         N = self.N
         to_play = _dev(to_play, torch.int32, d)
@@ -154,6 +162,8 @@ class Forest:
             o["last_action"] = torch.empty(N, dtype=torch.int64, device=d)
         if self.variant == "sez" and "last_action_f" not in o:
             o["last_action_f"] = torch.empty((N, self.D), dtype=torch.float32, device=d)
+        if self.variant == "smz" and "leaf_is_chance" not in o:
+            o["leaf_is_chance"] = torch.empty(N, dtype=torch.int32, device=d)
         garr = (Gather * max(len(gathers), 1))()
         for k, g in enumerate(gathers):
             src, dst = g[0], g[1]
@@ -175,7 +185,17 @@ class Forest:
         rp, rkeep = self._reuse(reuse)
         if rp is not None:
             io.reuse = rp
-        return io, (garr, to_play, rkeep), o
+        ckeep = None
+        if self.variant == "smz":
+            forced = _dev(forced_outcome, torch.int32, d)
+            if forced is not None and (forced.dim() != 2 or forced.shape[0] != N):
+                raise ValueError("forced_outcome must be [N, stride]")
+            ch = Chance(_p(forced), 0 if forced is None else int(forced.shape[1]), o["leaf_is_chance"].data_ptr())
+            io.chance = C.pointer(ch)
+            ckeep = (ch, forced)
+        elif forced_outcome is not None:
+            raise ValueError("forced_outcome exists for the stochastic tree only")
+        return io, (garr, to_play, rkeep, ckeep), o
 
     def _slots(self, e, tensors):
         sl = Slots()
@@ -216,12 +236,13 @@ class Forest:
             io.reuse = rp
         return io, (reward, value, logits, to_play, is_reset, sampled_actions, rkeep)
 
-    def traverse(self, cfg, to_play, out=None, gathers=(), reuse=None):
+    def traverse(self, cfg, to_play, out=None, gathers=(), reuse=None, forced_outcome=None):
         """One batch_traverse. ``out``: optional dict of preallocated tensors (ix, iy, last_action, last_action_f,
         search_len, vtp); missing ones are allocated. ``gathers``: [(pool[E,N,...] | None, dst[N,...][, zero_if_reset])];
         None = rows come from the slot table with the gather's index.  ``reuse``: dict(true_action, reuse_value
-        [, infer_count]) of [N] device tensors = batch_traverse_with_reuse (ReZero)."""
-        io, keep, o = self._traverse_io(to_play, out, gathers, reuse)
+        [, infer_count]) of [N] device tensors = batch_traverse_with_reuse (ReZero).  ``forced_outcome`` (stochastic
+        tree): [N, stride] outcomes to take at the chance levels instead of drawing (entries < 0 draw)."""
+        io, keep, o = self._traverse_io(to_play, out, gathers, reuse, forced_outcome)
         check(self.L.lzb_traverse(self.h, C.byref(cfg), C.byref(io), _stream(self.device)))
         return o
 
@@ -234,11 +255,12 @@ class Forest:
         check(self.L.lzb_backprop(self.h, C.byref(io), _stream(self.device)))
 
     def step(self, cfg, latent_index, discount, reward, value, logits, vtp, to_play, out=None, gathers=(), is_reset=None,
-             lstm_horizon_len=0, is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None):
+             lstm_horizon_len=0, is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None,
+             forced_outcome=None):
         """backprop(latent_index, ..., vtp) of simulation s and traverse(to_play) of simulation s + 1 in ONE launch."""
         bio, keep_b = self._backprop_io(latent_index, discount, reward, value, logits, vtp, is_reset, lstm_horizon_len,
                                         is_reset_out, sampled_actions, new_slots, reuse)
-        tio, keep_t, o = self._traverse_io(to_play, out, gathers, reuse)
+        tio, keep_t, o = self._traverse_io(to_play, out, gathers, reuse, forced_outcome)
         check(self.L.lzb_step(self.h, C.byref(cfg), C.byref(bio), C.byref(tio), _stream(self.device)))
         return o
 

@@ -22,10 +22,12 @@ def test_cuda_path_matches_reference_golden(name, fused):
     sc = Scenario(**kw)
     if sc.variant == "sez":  # the action tables the compiled reference sampled when the fixture was made
         sc.root_actions, sc.actions = want["sez_root_actions"], want["sez_actions"]
+    if sc.variant == "smz":  # the chance outcomes the compiled reference drew when the fixture was made
+        sc.forced = want["paths"]
     rec = []
     # ReZero cases: hand the compacted batch index over, as the reference's caller does, so that iy compares too
     gpu = run_gpu(sc, mode, 2024, record=rec, fused=fused, compact=bool(kw.get("reuse")))
-    for k in ("ix", "iy", "search_len", "vtp", "paths"):
+    for k in ("ix", "iy", "search_len", "vtp", "paths", "leaf_is_chance"):
         if k in want.files:  # the ReZero traverse reports no paths
             assert_same(np.stack([r[k] for r in rec]), want[k], "%s/%s" % (name, k))
     if kw.get("reuse"):

@@ -20,7 +20,7 @@ def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=Fal
     import torch
     from lightzero_b200.forest import Forest
     f = Forest(sc.variant, sc.n, sc.K if sc.variant == "sez" else sc.A, sc.S, legal_actions=sc.legal, action_dim=sc.D,
-               root_offset=root_offset)
+               root_offset=root_offset, chance_space=sc.K if sc.variant == "smz" else 0)
     f.set_delta(0.01)
     dev = f.device
     t = lambda a: torch.as_tensor(a).to(dev)
@@ -48,6 +48,12 @@ def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=Fal
     infer_count = torch.zeros(sc.S, dtype=torch.int32, device=dev)
     if getattr(sc, "reuse", False):
         reuse = dict(true_action=t(sc.true_action), reuse_value=t(sc.reuse_value))
+
+    def chance_kw(s_traverse):
+        """Stochastic MuZero: the outcomes to replay at the chance levels of simulation s_traverse (None = draw)."""
+        if sc.variant != "smz" or sc.forced is None:
+            return {}
+        return dict(forced_outcome=t(np.ascontiguousarray(sc.forced[s_traverse], np.int32)))
 
     def reuse_for(s_traverse, o_prev=None):
         """reuse dict of one call: the traverse of simulation s_traverse counts its inferring trees; the backprop half
@@ -79,7 +85,7 @@ def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=Fal
             rec["paths"] = f.dump_paths(sc.S + 1)
             record.append(rec)
 
-    o = f.traverse(cfg, tp, gathers=gathers, reuse=reuse_for(0))
+    o = f.traverse(cfg, tp, gathers=gathers, reuse=reuse_for(0), **chance_kw(0))
     note(o, 0)
     for s in range(sc.S):
         m = sc.model_fn(s, None, None, None)
@@ -94,7 +100,7 @@ def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=Fal
         args = (s + 1, sc.discount, t(m["reward"]), t(m["value"]), t(m["logits"]), o["vtp"])
         last = s + 1 == sc.S
         if fused and not last:
-            o = f.step(cfg, *args, tp, out=o, gathers=gathers, reuse=reuse_for(s + 1, o), **kw)
+            o = f.step(cfg, *args, tp, out=o, gathers=gathers, reuse=reuse_for(s + 1, o), **chance_kw(s + 1), **kw)
         else:
             f.backprop(*args, reuse=reuse_for(None, o), **kw)
         if vp:
@@ -103,7 +109,7 @@ def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=Fal
                 record[-1]["is_reset"] = is_reset_out.cpu().numpy()
         if not last:
             if not fused:
-                o = f.traverse(cfg, tp, out=o, reuse=reuse_for(s + 1))
+                o = f.traverse(cfg, tp, out=o, reuse=reuse_for(s + 1), **chance_kw(s + 1))
             note(o, s + 1)
     torch.cuda.synchronize()
     f.infer_count = infer_count.cpu().numpy()
@@ -118,7 +124,7 @@ def compare(sc, rng_mode=2, seed=2024, trees=4, fused=False, compact=False):
     gpu = run_gpu(sc, rng_mode, seed, record=rec_g, fused=fused, compact=compact)
     is_reuse = getattr(sc, "reuse", False)
     for s, (c, g) in enumerate(zip(rec_c, rec_g)):
-        for k in ("search_len", "ix", "iy", "vtp", "paths"):
+        for k in ("search_len", "ix", "iy", "vtp", "paths", "leaf_is_chance"):
             if k == "iy" and is_reuse and not compact:  # model batches indexed by tree: every node's batch_index is its tree
                 assert_same(g[k], np.arange(sc.n, dtype=np.int32), "sim %d iy" % s)
             elif k in c:
@@ -272,6 +278,38 @@ def test_gumbel_m16_a18():
 
 def test_sampled_continuous_halfcheetah_shape():  # C3: K=20, D=6, 50 sims
     compare(Scenario("sez", 8, 12, 50, seed=14, K=20, D=6))
+
+
+# Stochastic MuZero (K = chance_space_size).  sc.forced is None: the oracle and the CUDA path DRAW their chance
+# outcomes from the same counter-based stream, so the draws themselves are compared too.
+SMZ_CASES = {
+    "2048_a4_c32": lambda: Scenario("smz", 64, 4, 50, seed=41, K=32),
+    "a6_c2": lambda: Scenario("smz", 200, 6, 50, seed=42, K=2),
+    "a18_c18_many_roots": lambda: Scenario("smz", 1200, 18, 30, seed=43, K=18),
+    "a3_c40_two_records_per_lane": lambda: Scenario("smz", 32, 3, 40, seed=44, K=40),
+    "a100_c70": lambda: Scenario("smz", 8, 100, 40, seed=45, K=70),
+    "masks_two_player": lambda: Scenario("smz", 16, 9, 40, seed=46, K=5, to_play=[1, 2] * 8, discount=1.0,
+                                         legal=[[a for a, x in enumerate(r) if x == 1] for r in TICTACTOE_MASKS]),
+    "single_outcome": lambda: Scenario("smz", 16, 5, 30, seed=47, K=1),
+    "zero_model_all_ties": lambda: Scenario("smz", 16, 4, 40, seed=48, K=4, zero_model=True),
+    "deep_a1_c1": lambda: Scenario("smz", 4, 1, 120, seed=49, K=1),
+}
+
+
+@pytest.mark.parametrize("rng_mode", [1, 2])
+@pytest.mark.parametrize("fused", [False, True])
+@pytest.mark.parametrize("name", sorted(SMZ_CASES))
+def test_stochastic_muzero_matches_oracle(name, fused, rng_mode):
+    compare(SMZ_CASES[name](), rng_mode=rng_mode, fused=fused)
+
+
+def test_stochastic_muzero_is_lane_group_only(monkeypatch):
+    from lightzero_b200._lib import LzbError
+    from lightzero_b200.forest import Forest
+    with pytest.raises(LzbError, match="<= 128"):
+        Forest("smz", 4, 4, 10, chance_space=200)
+    with pytest.raises(ValueError):
+        Forest("smz", 4, 4, 10)
 
 
 FUSED_CASES = {
