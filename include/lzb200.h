@@ -164,12 +164,16 @@ typedef struct {
  *     (parity tests replay the outcomes the compiled reference drew).
  *   leaf_is_chance_dev [N] (may be NULL): results.leaf_node_is_chance - which model head the leaf needs
  *     (mcts_ctree_stochastic.py:150-176); equals search_len & 1.
+ *   seed_dev (may be NULL): one 64-bit word in DEVICE memory used as the seed of lzb_chance_bits instead of
+ *     cfg->rng_seed, so that a search captured in a CUDA graph draws fresh outcomes on every replay (the caller
+ *     rewrites the word between replays); the tie-break stream keeps cfg->rng_seed.
  * lzb_backprop / lzb_step expand a chance leaf with the first C entries of its logits row and reward 0
  * (cnode.cpp:115-118), a decision leaf with the first A entries. */
 typedef struct {
     const int32_t *forced_outcome_dev;
     int32_t forced_stride;
     int32_t *leaf_is_chance_dev;
+    const uint64_t *seed_dev;
 } lzb_chance_t;
 
 /* batch_traverse (mz_tree.pyx:95-100 -> cbatch_traverse, cnode.cpp:755-824; ez :886-963; gumbel
@@ -207,6 +211,11 @@ typedef struct {
     const float *sampled_actions_dev;
     lzb_slots_t new_slots;
     const lzb_reuse_t *reuse; /* NULL = plain batch_backpropagate */
+    /* [N] or NULL.  Non-NULL: only trees with active[i] != 0 are expanded and backed up, the others are left
+     * untouched - the leaf_idx_list of the stochastic tree's cbatch_backpropagate (ctree_stochastic_muzero/lib/
+     * cnode.cpp:559-587), whose driver backs the chance leaves and the decision leaves up in two calls
+     * (mcts_ctree_stochastic.py:232-251).  Lane-group kernels only (every action space <= 128); not in lzb_step. */
+    const int32_t *active_dev;
 } lzb_backprop_io_t;
 int lzb_backprop(lzb_forest_t *f, const lzb_backprop_io_t *io, void *stream);
 

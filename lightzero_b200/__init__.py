@@ -4,4 +4,5 @@
 
 Importing the package does not need a GPU; creating roots or searching does (there is no CPU fallback)."""
 from .tree_search import (EfficientZeroMCTSCtree, GumbelMuZeroMCTSCtree, MuZeroMCTSCtree,  # noqa: F401
-                          MuZeroRNNFullObsMCTSCtree, SampledEfficientZeroMCTSCtree, UniZeroMCTSCtree)
+                          MuZeroRNNFullObsMCTSCtree, SampledEfficientZeroMCTSCtree, StochasticMuZeroMCTSCtree,
+                          UniZeroMCTSCtree)

@@ -73,7 +73,8 @@ class Reuse(C.Structure):
 
 class Chance(C.Structure):
     """lzb_chance_t"""
-    _fields_ = [("forced_outcome_dev", C.c_void_p), ("forced_stride", C.c_int32), ("leaf_is_chance_dev", C.c_void_p)]
+    _fields_ = [("forced_outcome_dev", C.c_void_p), ("forced_stride", C.c_int32), ("leaf_is_chance_dev", C.c_void_p),
+                ("seed_dev", C.c_void_p)]
 
 
 class SelectAction(C.Structure):
@@ -98,7 +99,8 @@ class BackpropIO(C.Structure):
     _fields_ = [("latent_index", C.c_int32), ("discount", C.c_float), ("reward_dev", C.c_void_p),
                 ("value_dev", C.c_void_p), ("logits_dev", C.c_void_p), ("to_play_dev", C.c_void_p),
                 ("is_reset_dev", C.c_void_p), ("lstm_horizon_len", C.c_int32), ("is_reset_out_dev", C.c_void_p),
-                ("sampled_actions_dev", C.c_void_p), ("new_slots", Slots), ("reuse", C.POINTER(Reuse))]
+                ("sampled_actions_dev", C.c_void_p), ("new_slots", Slots), ("reuse", C.POINTER(Reuse)),
+                ("active_dev", C.c_void_p)]
 
 
 _P = C.c_void_p

@@ -476,6 +476,7 @@ int fill_select(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse
         if (io->chance->forced_outcome_dev && io->chance->forced_stride <= 0) return fail(LZB_E_ARG, "chance: forced_stride must be positive");
         a.forced_outcome = io->chance->forced_outcome_dev; a.forced_stride = io->chance->forced_stride;
         a.leaf_is_chance = io->chance->leaf_is_chance_dev;
+        a.chance_seed = (const unsigned long long *)io->chance->seed_dev;
     }
     if (p.variant == LZB_SMZ && getenv("LZB_FORCE_WARP_PER_TREE")) return fail(LZB_E_UNSUPPORTED, "the stochastic tree has lane-group kernels only");
     if (p.variant != LZB_GMZ && (f->pbc_base != cfg->pb_c_base || f->pbc_init != cfg->pb_c_init)) {
@@ -513,6 +514,7 @@ int fill_backup(lzb_forest_t *f, const lzb_backprop_io_t *io, BackupArgs &b)
     b = BackupArgs{io->latent_index, io->lstm_horizon_len, io->discount, io->reward_dev, io->value_dev, io->logits_dev,
                    io->sampled_actions_dev, io->to_play_dev, io->is_reset_dev, io->is_reset_out_dev, io->new_slots.n, {}};
     for (int k = 0; k < io->new_slots.n; ++k) b.new_slot[k] = (const char *)io->new_slots.ptr[k];
+    b.active = io->active_dev;
     if (io->reuse) {
         if (int rc = check_reuse(p)) return rc;
         if (!io->reuse->reuse_value_dev || (!io->reuse->flags_dev && !io->reuse->true_action_dev))
@@ -662,6 +664,7 @@ int lzb_backprop(lzb_forest_t *f, const lzb_backprop_io_t *io, void *stream)
         return LZB_OK;
     }
     if (p.variant == LZB_SMZ) return fail(LZB_E_UNSUPPORTED, "the stochastic tree has lane-group kernels only");
+    if (io->active_dev) return fail(LZB_E_UNSUPPORTED, "backprop: the active mask needs the lane-group kernels (action space <= 128)");
     switch (p.variant) {
     case LZB_MZ:
         if (int rc = launch_cfg(k_expand_backup<LZB_MZ>, bpw, p.N, grid, block, smem)) return rc;
@@ -694,6 +697,7 @@ int lzb_step(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_backprop_io
     if (int rc = fill_backup(f, bio, b)) return rc;
     if (int rc = fill_select(f, cfg, tio, a, st)) return rc;
     if ((bio->reuse != nullptr) != (tio->reuse != nullptr)) return fail(LZB_E_ARG, "step: reuse must be given for both halves or neither");
+    if (bio->active_dev) return fail(LZB_E_ARG, "step: an active mask is accepted by lzb_backprop only");
     a.new_e = b.latent_index;
     for (int k = 0; k < kMaxGathers; ++k) a.new_slot[k] = b.new_slot[k];
     for (int k = 0; k < a.ng; ++k)

@@ -79,6 +79,7 @@ struct BackupArgs {
     const float *reuse_value;  // [N]
     const int *reuse_flags;    // [N] bit 0: tree is in no_inference_lst, bit 1: in reuse_lst; nullptr: derived from the traverse
     const int *batch_index;    // [N] count_b of tree i in the caller's compacted batch; nullptr: i
+    const int *active;         // [N] or nullptr: trees with active[i] == 0 are left untouched (lane-group backup kernel only)
 };
 
 // cbatch_backpropagate: CNode::expand of the leaf + cbackpropagate along the recorded path

@@ -186,6 +186,8 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     bool going = live; // this group is still descending
     bool no_inference = false;
     int level = 0;   // rounds of the loop below == depth of every group that is still going (warp-uniform)
+    unsigned long long chance_seed = a.seed;
+    if (VAR == LZB_SMZ && a.chance_seed) chance_seed = *a.chance_seed;
     bool is_true[R]; // root position j holds the trajectory's action
     float reuse_v = 0.0f;
     if (REUSE) {
@@ -237,7 +239,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         int newpos = 0;
         if (VAR == LZB_SMZ && (level & 1)) {
             // ---- chance node: draw the outcome (or replay a given one)
-            const unsigned long long bits = chance_bits(a.seed, (unsigned)a.sim, (unsigned)(p.root_offset + i), (unsigned)depth);
+            const unsigned long long bits = chance_bits(chance_seed, (unsigned)a.sim, (unsigned)(p.root_offset + i), (unsigned)depth);
             newpos = chance_draw_g<G, R>(c, n, (double)(bits >> 11) * (1.0 / 9007199254740992.0), grp);
             if (a.forced_outcome && going && depth < a.forced_stride) {
                 const int fo = a.forced_outcome[(size_t)i * a.forced_stride + depth];
@@ -753,8 +755,9 @@ __global__ void __launch_bounds__(128, 7) k_expand_backup_g(Pool p, BackupArgs b
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
-    const bool live = i < p.N;
+    bool live = i < p.N;
     pdl_wait();
+    if (b.active && live) live = b.active[i] != 0; // smz leaf_idx_list: the other trees are not touched by this call
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
     expand_backup_g<VAR, G, R, REUSE>(p, b, live ? i : 0, live, grp);
     pdl_release();

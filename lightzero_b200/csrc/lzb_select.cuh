@@ -32,6 +32,7 @@ struct SelectArgs {
     const int *forced_outcome; // [N][forced_stride] outcome to take at a chance level when >= 0, or nullptr
     int forced_stride;
     int *leaf_is_chance;       // [N] or nullptr
+    const unsigned long long *chance_seed; // device word replacing `seed` for the chance draws, or nullptr
 };
 
 // dst[i,:] = rows of the leaf's parent (expansion ix) with 16-byte accesses when rows allow it.  The source is

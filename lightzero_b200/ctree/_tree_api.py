@@ -181,6 +181,9 @@ class RootsBase:
     def _forest_dims(self):
         return self.action_space_size, 0
 
+    def _forest_kw(self):
+        return {}
+
     def _materialize(self, max_sims=None):
         if self._prep is None:
             raise RuntimeError("Roots.prepare / prepare_no_noise must be called before the roots are searched")
@@ -193,7 +196,7 @@ class RootsBase:
                 raise RuntimeError("search needs %d simulations but the forest was created for %d" % (need, self.forest.S))
             A, D = self._forest_dims()
             self.forest = Forest(self.variant, self.root_num, A, need, legal_actions=self._legal, action_dim=D,
-                                 root_offset=self.root_offset, device=self._device)
+                                 root_offset=self.root_offset, device=self._device, **self._forest_kw())
             self.forest.sims_done = 0
             self._apply_prepare(reset=False)
         return self.forest
@@ -233,13 +236,13 @@ def _search_cfg(forest, pb_c_base, pb_c_init, discount, to_play, num_simulations
 
 
 def traverse_tensors(roots, cfg, to_play, results, min_max_stats_lst=None, gathers=(), out=None, max_sims=None,
-                     reuse=None):
+                     reuse=None, **kw):
     """Device-tensor batch_traverse: returns the dict of [N] device tensors (ix, iy, last_action, search_len, vtp).
     ``reuse`` = dict(true_action, reuse_value[, infer_count]): batch_traverse_with_reuse."""
     f = roots._materialize(max_sims)
     if min_max_stats_lst is not None:
         min_max_stats_lst._bind(f)
-    o = f.traverse(cfg, to_play, out=out, gathers=gathers, reuse=reuse)
+    o = f.traverse(cfg, to_play, out=out, gathers=gathers, reuse=reuse, **kw)
     results.out = o
     results.forest = f
     results.roots = roots

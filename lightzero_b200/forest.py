@@ -190,9 +190,11 @@ class Forest:
             forced = _dev(forced_outcome, torch.int32, d)
             if forced is not None and (forced.dim() != 2 or forced.shape[0] != N):
                 raise ValueError("forced_outcome must be [N, stride]")
-            ch = Chance(_p(forced), 0 if forced is None else int(forced.shape[1]), o["leaf_is_chance"].data_ptr())
+            seed = getattr(self, "chance_seed_dev", None)  # [1] int64 device tensor, or None = cfg.rng_seed
+            ch = Chance(_p(forced), 0 if forced is None else int(forced.shape[1]), o["leaf_is_chance"].data_ptr(),
+                        _p(seed))
             io.chance = C.pointer(ch)
-            ckeep = (ch, forced)
+            ckeep = (ch, forced, seed)
         elif forced_outcome is not None:
             raise ValueError("forced_outcome exists for the stochastic tree only")
         return io, (garr, to_play, rkeep, ckeep), o
@@ -247,11 +249,17 @@ class Forest:
         return o
 
     def backprop(self, latent_index, discount, reward, value, logits, to_play, is_reset=None, lstm_horizon_len=0,
-                 is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None):
+                 is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None, active=None):
         """One batch_backpropagate; ``reuse``: dict(reuse_value, true_action | flags[, batch_index]) =
-        batch_backpropagate_with_reuse with reward / value / logits indexed by tree."""
+        batch_backpropagate_with_reuse with reward / value / logits indexed by tree.  ``active``: [N] int32, trees
+        with a zero entry are left untouched (the stochastic tree's leaf_idx_list)."""
         io, keep = self._backprop_io(latent_index, discount, reward, value, logits, to_play, is_reset, lstm_horizon_len,
                                      is_reset_out, sampled_actions, new_slots, reuse)
+        active = _dev(active, torch.int32, self.device)
+        if active is not None:
+            if active.numel() != self.N:
+                raise ValueError("active must have N elements")
+            io.active_dev = active.data_ptr()
         check(self.L.lzb_backprop(self.h, C.byref(io), _stream(self.device)))
 
     def step(self, cfg, latent_index, discount, reward, value, logits, vtp, to_play, out=None, gathers=(), is_reset=None,

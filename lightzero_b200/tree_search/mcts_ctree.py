@@ -223,7 +223,9 @@ class _SearchGraph:
         self.static = {k: (None if p[k] is None else torch.empty_like(p[k][lo:hi])) for k in keys}
         # sampled tree: the kernels read the sampler seed from this word, rewritten before every replay, so a replayed
         # search draws fresh action tables (lzb_sample_actions_seeded)
-        self.seed_dev = torch.zeros(1, dtype=torch.int64, device=dev) if "sampled_actions" in p else None
+        # (stochastic tree: the same for the seed of its chance draws, lzb_chance_t.seed_dev)
+        seeded = "sampled_actions" in p or roots.variant == "smz"
+        self.seed_dev = torch.zeros(1, dtype=torch.int64, device=dev) if seeded else None
         self.noise_weight = p["noise_weight"]
         self.lat0 = torch.empty((n,) + tuple(lat0.shape[1:]), dtype=lat0.dtype, device=dev)
         # hidden states come as [1, N, H] (mcts_ctree.py:727-728)
@@ -264,7 +266,7 @@ class _SearchGraph:
                 d.copy_(s.reshape(roots.num, -1)[lo:hi], non_blocking=True)
         self.tp.copy_(to_play.reshape(-1)[lo:hi], non_blocking=True)
         if self.seed_dev is not None:
-            seed = int(getattr(roots, "sample_seed", 0)) & 0xffffffffffffffff
+            seed = int(getattr(roots, "sample_seed", None) or getattr(roots, "chance_seed", None) or 0) & 0xffffffffffffffff
             self.seed_dev.fill_(seed if seed < (1 << 63) else seed - (1 << 64))
         if self.legal is not None:
             cnt, idx = legal_tensors(self._legal_slice(roots), hi - lo, roots.action_space_size, roots.variant, self.dev)

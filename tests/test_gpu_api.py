@@ -517,3 +517,126 @@ def test_sampled_driver_cuda_graph_matches_eager_and_redraws():
         assert torch.equal(a[2], b[2]) and torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
     assert not torch.equal(g1[2], g2[2]) and not torch.equal(g1[0], g2[0])  # fresh root tables and a different search
     assert (g2[0].sum(1) == S).all()
+
+
+# ---------------------------------------------------------------- Stochastic MuZero (chance nodes)
+class StochasticScenarioModel:
+    """model.recurrent_inference(latent, action, afterstate=...) of the stochastic drivers over a Scenario's tables.
+    Sub-batches arrive compacted, so column 1 of every latent row carries the tree index and the model looks its
+    rows up by it; every tree is inferred once per simulation (``calls_per_row`` times with dense inference)."""
+
+    def __init__(self, sc, dev, calls_per_row=1):
+        import torch
+        self.sc, self.dev, self.per_sim = sc, dev, sc.n * calls_per_row
+        t = lambda a: torch.as_tensor(a).to(dev)
+        self.logits, self.value, self.reward = t(sc.logits), t(sc.value), t(sc.reward)
+        self.rows_seen = 0
+        self.calls = []
+
+    def eval(self):
+        self.rows_seen = 0
+
+    def root_latents(self, L=8):
+        lat = np.zeros((self.sc.n, L), np.float32)
+        lat[:, 1] = np.arange(self.sc.n)
+        return lat
+
+    def recurrent_inference(self, latent, action, afterstate=False):
+        import torch
+        sc = self.sc
+        s = self.rows_seen // self.per_sim
+        self.rows_seen += latent.shape[0]
+        rows = latent[:, 1].long()
+        self.calls.append(dict(s=s, rows=rows.clone(), ix=latent[:, 0].clone(), action=action.clone(), afterstate=afterstate))
+        width = sc.A if afterstate else sc.K  # afterstate in -> decision node out (policy logits); else chance logits
+        o = Out()
+        o.latent_state = latent.clone()
+        o.latent_state[:, 0] = float(s + 1)
+        o.policy_logits = self.logits[s][rows, :width]
+        o.value = self.value[s][rows].unsqueeze(1)
+        o.reward = self.reward[s][rows].unsqueeze(1)
+        return o
+
+
+def test_stochastic_list_api_driven_like_the_reference_loop():
+    """stochastic_mz_tree driven the way mcts_ctree_stochastic.py:128-251 drives the Cython module: five lists out of
+    batch_traverse, then chance leaves and decision leaves backed up by two calls with compacted rows."""
+    from lightzero_b200.ctree.ctree_stochastic_muzero import stochastic_mz_tree as smz
+    sc = Scenario("smz", 24, 5, 30, seed=61, K=3)
+    orc, rec = oracle_run(sc)
+    smz.set_tie_break(SEED)
+    roots = smz.Roots(sc.n, sc.legal, sc.K)
+    roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_logits[:, :sc.A].tolist(),
+                  sc.to_play.tolist())
+    mm = smz.MinMaxStatsList(sc.n)
+    mm.set_delta(0.01)
+    both = 0
+    for s in range(sc.S):
+        results = smz.ResultsWrapper(sc.n)
+        is_chance, ix, iy, last_actions, vtp = smz.batch_traverse(roots, PB_C_BASE, PB_C_INIT, sc.discount, mm, results,
+                                                                  sc.to_play.tolist())
+        assert all(isinstance(x, bool) for x in is_chance)
+        assert is_chance == [bool(x) for x in rec[s]["leaf_is_chance"]]
+        assert ix == rec[s]["ix"].tolist() and last_actions == rec[s]["last_action"].tolist()
+        chance = [i for i, c in enumerate(is_chance) if c]
+        decision = [i for i, c in enumerate(is_chance) if not c]
+        both += bool(chance) and bool(decision)
+        for idx, width in ((chance, sc.K), (decision, sc.A)):
+            if idx:
+                smz.batch_backpropagate(s + 1, sc.discount, sc.reward[s][idx].tolist(), sc.value[s][idx].tolist(),
+                                        sc.logits[s][idx, :width].tolist(), mm, results, vtp, is_chance, idx)
+    assert both > 5  # mixed simulations happened: the subset calls were exercised
+    check_roots(roots, orc, sc)
+    assert roots.forest.sims_done == sc.S
+
+
+@pytest.mark.parametrize("mode", ["compact", "dense", "dense_graph"])
+def test_stochastic_driver_matches_oracle(mode):
+    import torch
+    import lightzero_b200 as lzb
+    legal = [[a for a, x in enumerate(r) if x == 1] for r in TICTACTOE_MASKS]
+    sc = Scenario("smz", 16, 9, 30, seed=62, K=4, legal=legal)
+    orc, rec = oracle_run(sc)
+    dense = mode != "compact"
+    mcts = identity(lzb.StochasticMuZeroMCTSCtree(driver_cfg(sc, stochastic_dense_inference=dense,
+                                                             cuda_graph=mode == "dense_graph")))
+    model = StochasticScenarioModel(sc, torch.device("cuda"), calls_per_row=2 if dense else 1)
+    first = None
+    for rep in range(3 if mode == "dense_graph" else 1):
+        roots = lzb.StochasticMuZeroMCTSCtree.roots(sc.n, sc.legal, sc.K)
+        if rep == 2:
+            roots.chance_seed = SEED  # replay of the captured search under the first search's chance stream
+        roots.prepare(0.25, [n.tolist() for n in sc.noises], sc.root_reward.tolist(), sc.root_logits[:, :sc.A].tolist(),
+                      sc.to_play.tolist())
+        mcts.search(roots, model, model.root_latents(), sc.to_play.tolist())
+        got = roots.get_distributions()
+        assert all(sum(r) == sc.S for r in got) and [len(r) for r in got] == [len(l) for l in legal]
+        if rep == 1:  # the next search of the driver draws other outcomes (seed + 1): not the same search again
+            assert got != first
+        else:
+            check_roots(roots, orc, sc)
+            first = got
+    if mode == "compact":  # the model saw the reference's call pattern: chance rows first, each leaf kind by itself
+        by_sim = {}
+        for c in model.calls:
+            by_sim.setdefault(c["s"], []).append(c)
+        for s in range(sc.S):
+            isc = rec[s]["leaf_is_chance"].astype(bool)
+            calls = by_sim[s]
+            assert [c["afterstate"] for c in calls] == ([False] if isc.all() else [True] if not isc.any() else [False, True])
+            for c in calls:
+                rows = c["rows"].cpu().numpy()
+                assert_same(rows, np.flatnonzero(isc != c["afterstate"]), "sim %d rows of afterstate=%s" % (s, c["afterstate"]))
+                assert_same(c["ix"].cpu().numpy(), rec[s]["ix"][rows].astype(np.float32), "sim %d gathered latents" % s)
+                assert_same(c["action"].cpu().numpy().astype(np.int32), rec[s]["last_action"][rows], "sim %d actions" % s)
+
+
+def test_stochastic_driver_rejects_graph_without_dense_inference():
+    import lightzero_b200 as lzb
+    sc = Scenario("smz", 4, 3, 5, seed=63, K=2)
+    mcts = lzb.StochasticMuZeroMCTSCtree(driver_cfg(sc, cuda_graph=True))
+    roots = lzb.StochasticMuZeroMCTSCtree.roots(sc.n, sc.legal)
+    assert roots.chance_space_size == 2  # the reference's default (mcts_ctree_stochastic.py:72)
+    roots.prepare_no_noise(sc.root_reward.tolist(), sc.root_logits[:, :sc.A].tolist(), sc.to_play.tolist())
+    with pytest.raises(ValueError, match="dense"):
+        mcts.search(roots, None, np.zeros((sc.n, 4), np.float32), sc.to_play.tolist())
