@@ -42,8 +42,10 @@ def parse_args():
     ap.add_argument("--sims", type=int, default=50)
     ap.add_argument("--actions", type=int, default=18)
     ap.add_argument("--latent", type=int, default=1024, help="latent floats per root gathered / stored per simulation")
-    ap.add_argument("--variant", default="mz", choices=["mz", "ez", "gmz", "sez"],
-                    help="sez = Sampled EfficientZero, continuous actions: --actions is K (sampled actions per node), --action-dim is D")
+    ap.add_argument("--variant", default="mz", choices=["mz", "ez", "gmz", "sez", "smz"],
+                    help="sez = Sampled EfficientZero, continuous actions: --actions is K (sampled actions per node), --action-dim is D; "
+                         "smz = Stochastic MuZero: --chance-space is the number of chance outcomes per chance node")
+    ap.add_argument("--chance-space", type=int, default=18)
     ap.add_argument("--action-dim", type=int, default=6)
     ap.add_argument("--two-player", action="store_true", help="to_play alternates 1/2 (board-game sign flips)")
     ap.add_argument("--streams", type=int, default=1, help="chunks of roots searched on concurrent CUDA streams (graph mode)")
@@ -58,7 +60,8 @@ def parse_args():
 def workload_name(a):
     return "synthetic %s search: %d roots/GPU x %d sims x A=%d, latent %d f32" % (
         {"mz": "MuZero", "ez": "EfficientZero", "gmz": "Gumbel MuZero (m=16)",
-         "sez": "Sampled EfficientZero (continuous, D=%d, A = K sampled actions)" % a.action_dim}[a.variant] + (" 2-player" if a.two_player else ""),
+         "sez": "Sampled EfficientZero (continuous, D=%d, A = K sampled actions)" % a.action_dim,
+         "smz": "Stochastic MuZero (%d chance outcomes per chance node, both model heads on the full batch)" % a.chance_space}[a.variant] + (" 2-player" if a.two_player else ""),
         a.roots, a.sims, a.actions, a.latent)
 
 
@@ -69,6 +72,7 @@ def make_inputs(a, rank, device):
     g = torch.Generator(device=device)
     g.manual_seed(1234 + rank)
     N, S, A, L = a.roots, a.sims, a.actions, a.latent
+    W = max(A, a.chance_space) if a.variant == "smz" else A  # smz: a row holds policy OR chance logits
     rn = lambda *shape: torch.randn(*shape, generator=g, device=device, dtype=torch.float32)
     gam = torch._standard_gamma(torch.full((N, A), ALPHA, device=device), generator=g)
     inp = dict(
@@ -76,7 +80,7 @@ def make_inputs(a, rank, device):
         noise=(gam / gam.sum(1, keepdim=True)).float().contiguous(),
         to_play=(torch.arange(N, device=device, dtype=torch.int32) % 2 + 1) if a.two_player
         else torch.full((N,), -1, dtype=torch.int32, device=device),
-        logits=rn(S, N, A), reward=rn(S, N) * 0.1, value=rn(S, N),
+        logits=rn(S, N, W), reward=rn(S, N) * 0.1, value=rn(S, N),
         latent_roots=rn(N, max(L, 1)), model_latent=rn(S, N, max(L, 1)),
     )
     if a.variant in ("ez", "sez"):
@@ -137,8 +141,9 @@ class TableModel:
     """recurrent_inference as a fixed table lookup (NN time excluded and stated as such): call s of a
     search returns row s of pre-generated logits / value / reward tables (a distinct next-latent tensor per simulation), all in HBM."""
 
-    def __init__(self, inp, variant):
+    def __init__(self, inp, variant, actions=0, chance_space=0, calls_per_sim=1):
         self.inp, self.variant, self.s = inp, variant, 0
+        self.A, self.C, self.calls_per_sim = actions, chance_space, calls_per_sim
         N = inp["model_latent"].shape[1]
         if variant in ("ez", "sez"):
             H = HIDDEN[variant]
@@ -155,15 +160,18 @@ class TableModel:
             sub[k] = self.inp[k][:, lo:hi]
         m = TableModel.__new__(TableModel)
         m.inp, m.variant, m.s = sub, self.variant, 0
+        m.A, m.C, m.calls_per_sim = self.A, self.C, self.calls_per_sim
         if hasattr(self, "hidden"):
             m.hidden = tuple(h[:, lo:hi].contiguous() for h in self.hidden)
         return m
 
-    def recurrent_inference(self, latent, *rest):
-        i, s = self.inp, self.s
+    def recurrent_inference(self, latent, *rest, afterstate=None):
+        i, s = self.inp, self.s // self.calls_per_sim
         self.s += 1
         o = NetOut()
         o.latent_state, o.policy_logits, o.value = i["model_latent"][s], i["logits"][s], i["value"][s].unsqueeze(1)
+        if afterstate is not None:  # stochastic model: afterstate in -> policy logits [A]; latent in -> chance logits [C]
+            o.policy_logits = o.policy_logits[:, :self.A if afterstate else self.C]
         o.reward = o.value_prefix = i["reward"][s].unsqueeze(1)
         o.reward_hidden_state = getattr(self, "hidden", None)
         return o
@@ -194,10 +202,10 @@ def measure_depth(a, mcts, model, inp, rank):
 def make_driver(a, device, graph):
     import lightzero_b200 as lzb
     cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree, "gmz": lzb.GumbelMuZeroMCTSCtree,
-           "sez": lzb.SampledEfficientZeroMCTSCtree}[a.variant]
+           "sez": lzb.SampledEfficientZeroMCTSCtree, "smz": lzb.StochasticMuZeroMCTSCtree}[a.variant]
     mcts = cls(dict(num_simulations=a.sims, max_num_considered_actions=16, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=DISCOUNT,
                     value_delta_max=DELTA, device=str(device), cuda_graph=graph, tie_break_seed=TIE_SEED,
-                    search_streams=a.streams if graph else 1,
+                    search_streams=a.streams if graph else 1, stochastic_dense_inference=True,
                     lstm_horizon_len=5,
                     model=dict(support_scale=300, categorical_distribution=False, continuous_action_space=a.variant == "sez",
                                action_space_size=a.action_dim if a.variant == "sez" else a.actions)))
@@ -212,6 +220,8 @@ def one_search(a, mcts, model, inp, host=None, rank=0):
     src = host if host is not None else inp
     if a.variant == "sez":
         roots = mcts.roots(a.roots, None, a.action_dim, a.actions, True)
+    elif a.variant == "smz":
+        roots = mcts.roots(a.roots, None, a.chance_space)
     else:
         roots = mcts.roots(a.roots, None)
     roots.root_offset = rank * a.roots  # global root index keys the tie-break stream
@@ -292,6 +302,8 @@ def roofline(a, per_kernel_ms, depth, peak_gbs, peak_src):
     is measured over the whole search; note the leaf rows are read in place from the model's output tensors, so the
     gather moves 8 L bytes per root (4 L read + 4 L written) and there is no separate store into a pool."""
     N, A, Lb = a.roots, a.actions, 8 * max(a.latent, 1) + (16 * HIDDEN[a.variant] if a.variant in HIDDEN else 0)
+    if a.variant == "smz":  # decision levels hold A children, chance levels C, alternating: the mean of the two per level
+        A = (a.actions + a.chance_space) / 2
     sel = depth * (16 * A + 16) + 8 + 4 * (depth + 1) + Lb
     bak = 4 * A + 16 * A + 28 + (depth + 1) * 20 + 8
     if a.variant == "sez":  # K children per node; the new node's [K, D] action table is read and stored, the leaf's action read and written
@@ -333,10 +345,11 @@ def cpu_inputs(a, n, seed):
         return dict(root_logits=head(n), root_reward=f(n) * np.float32(0.1), root_value=f(n), noises=None,
                     to_play=np.full(n, -1, np.int32), logits=head(S, n), reward=f(S, n), value=f(S, n),
                     latent_roots=f(n, L), model_latent=f(S, n, L))
+    W = max(A, a.chance_space) if a.variant == "smz" else A
     return dict(root_logits=f(n, A), root_reward=f(n) * np.float32(0.1), root_value=f(n),
                 noises=[r for r in rng.dirichlet([ALPHA] * A, size=n).astype(np.float32)],
                 to_play=(np.arange(n, dtype=np.int32) % 2 + 1) if getattr(a, "two_player", False) else np.full(n, -1, np.int32),
-                logits=f(S, n, A),
+                logits=f(S, n, W),
                 reward=(f(S, n) if a.variant == "ez" else f(S, n) * np.float32(0.1)), value=f(S, n),
                 latent_roots=f(n, L), model_latent=f(S, n, L))
 
@@ -372,6 +385,23 @@ def cpu_search(a, d):
         f.values()
         return time.perf_counter() - t0, kind, dist
     legal = [list(range(a.actions))] * n  # the policies always pass explicit legal-action lists (muzero.py:671)
+    if a.variant == "smz":  # mcts_ctree_stochastic.py:117-251; the model outputs of both leaf kinds share a [n, W] row table
+        from oracle.binding import RefStochasticForest
+        f = RefStochasticForest(n, a.actions, a.chance_space, legal) if kind == "reference" else \
+            OracleForest("smz", n, a.actions, legal, K=a.chance_space)
+        f.set_delta(DELTA)
+        f.set_rng(0 if kind == "reference" else 2, TIE_SEED)
+        f.prepare(NOISE_W, d["noises"], d["root_reward"], d["root_logits"], d["to_play"])
+        pool = [d["latent_roots"]]
+        for s in range(a.sims):
+            o = f.traverse_chance(PB_C_BASE, PB_C_INIT, DISCOUNT, d["to_play"])
+            leaf = np.asarray([pool[ix][iy] for ix, iy in zip(o["ix"].tolist(), o["iy"].tolist())])  # noqa: F841
+            chance = np.flatnonzero(o["leaf_is_chance"])  # noqa: F841  (the driver's split into two model batches, :165-176)
+            pool.append(d["model_latent"][s])
+            f.backprop(s + 1, DISCOUNT, d["reward"][s], d["value"][s], d["logits"][s], None, o["vtp"])
+        dist, _ = f.distributions()
+        f.values()
+        return time.perf_counter() - t0, kind, dist
     f = RefForest(a.variant, n, a.actions, legal) if kind == "reference" else OracleForest(a.variant, n, a.actions, legal)
     f.set_delta(DELTA)
     f.set_rng(0 if kind == "reference" else 2, TIE_SEED)  # reference: its own libc rand() stream
@@ -483,7 +513,8 @@ def run_b200_arm(a):
     if a.variant in HIDDEN:
         inp["hidden_c"] = torch.zeros(1, N, HIDDEN[a.variant], device=device)
         inp["hidden_h"] = torch.zeros(1, N, HIDDEN[a.variant], device=device)
-    model = TableModel(inp, a.variant)
+    model = TableModel(inp, a.variant, a.actions, a.chance_space, calls_per_sim=2 if a.variant == "smz" else 1)
+    W = max(A, a.chance_space) if a.variant == "smz" else A  # columns of the visit-count rows
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=device)
     counts = [N] * world
 
@@ -492,7 +523,7 @@ def run_b200_arm(a):
     peer = None
     if world > 1 and not a.nccl_exchange:
         try:
-            peer = sharding.PeerExchange(N, A + 1)  # raises on every rank together if any rank cannot map its peers
+            peer = sharding.PeerExchange(N, W + 1)  # raises on every rank together if any rank cannot map its peers
         except RuntimeError as exc:  # e.g. CUDA IPC not permitted in this container: the NCCL route, stated in config
             print("rank %d: %s; using NCCL for the exchange" % (rank, exc), file=sys.stderr)
             a.nccl_exchange = True
@@ -543,7 +574,7 @@ def run_b200_arm(a):
         host = {k: pin(inp[k]) for k in ("root_logits", "noise", "root_reward", "root_value", "to_play", "latent_roots")}
         if a.variant in HIDDEN:
             host["hidden_c"], host["hidden_h"] = pin(inp["hidden_c"]), pin(inp["hidden_h"])
-        host["visits_out"] = torch.empty((N, A), dtype=torch.int32).pin_memory()
+        host["visits_out"] = torch.empty((N, W), dtype=torch.int32).pin_memory()
         host["values_out"] = torch.empty(N, dtype=torch.float32).pin_memory()
         if a.variant != "gmz":
             host.pop("root_value")
