@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--action-dim", type=int, default=6)
     ap.add_argument("--two-player", action="store_true", help="to_play alternates 1/2 (board-game sign flips)")
     ap.add_argument("--streams", type=int, default=1, help="chunks of roots searched on concurrent CUDA streams (graph mode)")
+    ap.add_argument("--e2e-streams", type=int, default=4,
+                    help="search_streams of the e2e leg's driver: chunk c's host->device copies overlap chunk c-1's simulations")
     ap.add_argument("--no-graph", action="store_true", help="value leg: launch per call instead of one CUDA graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -199,13 +201,13 @@ def measure_depth(a, mcts, model, inp, rank):
     return float(torch.stack(acc).mean())
 
 
-def make_driver(a, device, graph):
+def make_driver(a, device, graph, streams=None):
     import lightzero_b200 as lzb
     cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree, "gmz": lzb.GumbelMuZeroMCTSCtree,
            "sez": lzb.SampledEfficientZeroMCTSCtree, "smz": lzb.StochasticMuZeroMCTSCtree}[a.variant]
     mcts = cls(dict(num_simulations=a.sims, max_num_considered_actions=16, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=DISCOUNT,
                     value_delta_max=DELTA, device=str(device), cuda_graph=graph, tie_break_seed=TIE_SEED,
-                    search_streams=a.streams if graph else 1, stochastic_dense_inference=True,
+                    search_streams=(streams or a.streams) if graph else 1, stochastic_dense_inference=True,
                     lstm_horizon_len=5,
                     model=dict(support_scale=300, categorical_distribution=False, continuous_action_space=a.variant == "sez",
                                action_space_size=a.action_dim if a.variant == "sez" else a.actions)))
@@ -581,8 +583,15 @@ def run_b200_arm(a):
         h2d = sum(host[k].numel() * host[k].element_size() for k in host if not k.endswith("_out")) + 4 * N  # to_play twice
         d2h = host["visits_out"].numel() * 4 + host["values_out"].numel() * 4
 
+        # the e2e leg's own driver: the batch is searched in chunks on concurrent streams so that the host->device copy of
+        # chunk c overlaps the simulations of chunk c-1 (same results; `value` above is the single-stream figure)
+        e2e_streams = max(a.streams, a.e2e_streams) if (not a.no_graph and a.variant in ("mz", "ez", "gmz")) else a.streams
+        if a.no_graph:
+            e2e_streams = 1
+        mcts_e2e = mcts if e2e_streams == a.streams else make_driver(a, device, graph=not a.no_graph, streams=e2e_streams)
+
         def e2e_step():
-            _, visits, values = one_search(a, mcts, model, inp, host=host, rank=rank)
+            _, visits, values = one_search(a, mcts_e2e, model, inp, host=host, rank=rank)
             exchange(visits, values)
             torch.cuda.synchronize()
 
@@ -656,7 +665,7 @@ def run_b200_arm(a):
             line["e2e"] = {"value": round(total_sims / (e2e_tot / a.steps * 1e-3), 1), "unit": "simulations/s",
                            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                            "ms_per_step": round(e2e_tot / a.steps, 4), "clock": "host wall clock incl. Python, max over ranks",
-                           "h2d_link_gbs": round(h2d_gbs, 1)}
+                           "h2d_link_gbs": round(h2d_gbs, 1), "search_streams": e2e_streams}
         if world == 1 and not a.no_cpu_baseline:
             n = min(a.cpu_sample_roots, N)
             d = cpu_inputs(a, n, 1234)

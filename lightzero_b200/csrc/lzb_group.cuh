@@ -243,7 +243,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             newpos = chance_draw_g<G, R>(c, n, (double)(bits >> 11) * (1.0 / 9007199254740992.0), grp);
             if (a.forced_outcome && going && depth < a.forced_stride) {
                 const int fo = a.forced_outcome[(size_t)i * a.forced_stride + depth];
-                newpos = (fo >= 0) ? fo : newpos;
+                newpos = (fo >= 0 && fo < n) ? fo : newpos; // an outcome the node does not have is ignored
             }
         } else {
         // ---- cucb_score
