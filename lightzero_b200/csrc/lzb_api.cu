@@ -340,6 +340,10 @@ extern "C" {
 
 const char *lzb_last_error(void) { return g_err; }
 int lzb_abi_version(void) { return LZB_ABI_VERSION; }
+#ifdef LZB_TIMELINE
+// tuning builds only (scripts/gpu_timeline.py): the buffer [launch][warp][24] of u64 the fused step kernel stamps
+int lzb_debug_timeline(void *buf_dev) { return cudaMemcpyToSymbol(g_timeline, &buf_dev, sizeof(buf_dev)) == cudaSuccess ? 0 : -1; }
+#endif
 uint32_t lzb_tiebreak_hash(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth) { return tiebreak_hash(seed, sim, root, depth); }
 uint64_t lzb_chance_bits(uint64_t seed, uint32_t sim, uint32_t root, uint32_t depth) { return chance_bits(seed, sim, root, depth); }
 

@@ -43,6 +43,18 @@ struct Grp {
     {
         return make_int4(shfl(v.x, src), shfl(v.y, src), shfl(v.z, src), shfl(v.w, src));
     }
+    // sum += v of lanes 0 .. cnt-1, strictly in lane order (cnt is warp-uniform; cnt == G: fully unrolled)
+    __device__ __forceinline__ float ordered_add(float sum, float v, int cnt) const
+    {
+        if (cnt >= G) {
+#pragma unroll
+            for (int l = 0; l < G; ++l) sum += shfl(v, l);
+        } else {
+#pragma unroll 1
+            for (int l = 0; l < cnt; ++l) sum += shfl(v, l);
+        }
+        return sum;
+    }
     __device__ __forceinline__ float fmax(float v) const
     {
 #pragma unroll
@@ -74,6 +86,36 @@ struct Grp {
 // (a no-op for a normally launched kernel), pdl_release() lets the successor's blocks be scheduled as ours exit.
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// Tuning aid, compiled only with -DLZB_TIMELINE (never in the shipped library): every warp of the fused step kernel
+// stamps clock64() at its phase boundaries into a caller-provided buffer [launch][warp][24] (scripts/gpu_timeline.py).
+// LZB_TLD takes the stamp only once `dep` has arrived (the clock read is predicated on it).
+#ifdef LZB_TIMELINE
+__device__ unsigned long long *g_timeline;
+__device__ __forceinline__ void tl_store(int row, int slot, unsigned long long v)
+{
+    if (row >= 0 && g_timeline && (threadIdx.x & 31) == 0)
+        g_timeline[(((size_t)row * gridDim.x + blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 24 + slot] = v;
+}
+__device__ __forceinline__ void tl_mark(int row, int slot)
+{
+    unsigned long long v;
+    if (slot == 1) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(v));
+    else v = clock64();
+    tl_store(row, slot, v);
+}
+__device__ __forceinline__ void tl_mark_dep(int row, int slot, int dep)
+{
+    unsigned long long v = 0;
+    asm volatile("{ .reg .pred p; setp.ne.s32 p, %1, 0x7ffffff1; @p mov.u64 %0, %clock64; }" : "+l"(v) : "r"(dep));
+    tl_store(row, slot, v);
+}
+#define LZB_TL(row, slot) tl_mark(row, slot)
+#define LZB_TLD(row, slot, dep) tl_mark_dep(row, slot, dep)
+#else
+#define LZB_TL(row, slot) ((void)0)
+#define LZB_TLD(row, slot, dep) ((void)0)
+#endif
 
 // Leaf rows of one tree moved by the G lanes of its group (same semantics as gather_rows in lzb_select.cuh).
 template <int G>
@@ -162,7 +204,7 @@ __device__ __forceinline__ int chance_draw_g(const int4 (&c)[R], int n, double u
 // is drawn from their priors (chance_draw_g) instead of scored; every going group of a warp is at the same depth, so
 // the decision / chance branch is warp-uniform.
 template <int VAR, int G, int R, bool REUSE = false>
-__device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a, int i, bool live, const Grp<G> &grp)
+__device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a, int i, bool live, const Grp<G> &grp, int tl = -1)
 {
     constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
     const int B = p.B, A = p.A, lane = grp.lane;
@@ -200,6 +242,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         }
     }
 
+    LZB_TL(tl, 5);
     while (__any_sync(kFull, going)) {
         // ---- one round of independent reads per level: the header (same address in every lane) and R records per lane
         const int4 *blk = tree + (size_t)e * B;
@@ -210,7 +253,9 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             const int j = lane + G * r;
             c[r] = (j < A) ? blk[1 + j] : make_int4(0, 0, 0, 0);
         }
+        const float2 pt = p.pbc[parent_visits - 1]; // {logf((T + c2 + 1) / c2) + c1, sqrtf(T)}, T = parent visits - 1; same round as the block
         const int n = h.x;
+        if (level == 0) LZB_TLD(tl, 6, n ^ c[0].x ^ c[R - 1].x);
 
         // ---- compute_mean_q: serial fp32 sum over visited children in legal order
         float val[R], tr[R];
@@ -230,11 +275,13 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
                 val[r] = vis ? __int_as_float(c[r].y) / (float)vc : 0.0f; // CNode::value()
                 const float qsa = vis ? tr[r] + g * val[r] : 0.0f;
                 nvis += __popc((wvis >> grp.shift) & ((G == 32) ? 0xffffffffu : ((1u << (G & 31)) - 1u)));
-#pragma unroll
-                for (int l = 0; l < G; ++l) total += grp.shfl(qsa, l); // j = l + G*r ascending; +0.0f for the rest is exact
+                // j = l + G*r ascending; +0.0f for the rest is exact; the last slice stops at the action space
+                total = (r == R - 1 && R > 1) ? grp.ordered_add(total, qsa, A - G * (R - 1)) : grp.ordered_add(total, qsa, G);
             }
         }
-        const float mean_q = (is_root && nvis > 0) ? total / (float)nvis : (parent_q + total) / (float)(nvis + 1);
+        const bool root_mean = is_root && nvis > 0; // one division: the two forms differ in numerator and count only
+        const float mean_q = (root_mean ? total : parent_q + total) / (float)(root_mean ? nvis : nvis + 1);
+        if (level == 0) LZB_TLD(tl, 7, __float_as_int(mean_q));
 
         int newpos = 0;
         if (VAR == LZB_SMZ && (level & 1)) {
@@ -247,7 +294,6 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             }
         } else {
         // ---- cucb_score
-        const float2 pt = p.pbc[parent_visits - 1]; // {logf((T + c2 + 1) / c2) + c1, sqrtf(T)}, T = parent visits - 1
         const float pbc0 = pt.x, sqT = pt.y;
         float sc[R];
         float lmax = -INFINITY;
@@ -272,6 +318,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             lmax = fmaxf(lmax, sc[r]);
         }
         const float gmax = grp.fmax(lmax);
+        if (level == 0) LZB_TLD(tl, 8, __float_as_int(gmax));
 
         // ---- order-dependent tie set + pinned draw (cselect_child, cnode.cpp:567-596), branch-free:
         // jstar = first index attaining the maximum; tie set = later indices within epsilon; draw k in [0, later]
@@ -310,6 +357,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         }
         newpos = any_score ? newpos : 0;
         }
+        if (level == 0) LZB_TLD(tl, 9, newpos);
         level += 1;
 
         // ---- the chosen child's record lives in lane newpos % G, register newpos / G
@@ -355,6 +403,8 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
                 e = ce;
             }
         }
+        if (level == 1) LZB_TLD(tl, 10, e ^ depth);
+        LZB_TL(tl, 11);
     }
 
     // ---- gather of the parent's rows, then the leaf bookkeeping (cnode.cpp:814-822).  The loads the bookkeeping
@@ -368,6 +418,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         if ((threadIdx.x & 31) == 0 && m) atomicAdd(a.infer_count, __popc(m));
     }
     pdl_release(); // the walk is over: a dependent launch may begin to take the place of exiting blocks
+    LZB_TL(tl, 12);
     if (live && !no_inference) { // nothing to infer: the tree's rows of the model batch are left as they are
         if (VAR == LZB_SEZ) {
             const float *act = p.actions + (((size_t)i * p.E + e) * A + pos) * p.D;
@@ -377,6 +428,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         }
         gather_rows_g<G>(p, a, i, e, parent_reset, lane);
     }
+    LZB_TL(tl, 13);
     if (live && lane == 0) {
         action = (VAR != LZB_SEZ && e == 0) ? root_action : pos;
         p.res[i] = make_int4(depth, no_inference ? -1 : e, pos, vtp);
@@ -387,6 +439,14 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         if (VAR != LZB_SEZ && a.last_action) a.last_action[i] = (long long)action;
         if (VAR == LZB_SMZ && a.leaf_is_chance) a.leaf_is_chance[i] = depth & 1; // smz cnode.cpp:782
     }
+#ifdef LZB_TIMELINE
+    {
+        unsigned sm;
+        asm volatile("mov.u32 %0, %smid;" : "=r"(sm));
+        tl_store(tl, 15, (unsigned long long)sm | ((unsigned long long)level << 16) | ((unsigned long long)depth << 32));
+    }
+#endif
+    LZB_TL(tl, 14);
 }
 
 // csoftmax (gmz cnode.cpp:904-933) over the n values a lane group holds as x[r] for j = lane + G*r:
@@ -580,7 +640,7 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
 // node is not expanded again and backs up reuse_value; a tree that expanded the root's true-action child backs up
 // reuse_value instead of the model's value.
 template <int VAR, int G, int R, bool REUSE = false>
-__device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs &a, int i, bool live, const Grp<G> &grp)
+__device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs &a, int i, bool live, const Grp<G> &grp, int tl = -1)
 {
     constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
     const int A = p.A, lane = grp.lane;
@@ -645,14 +705,17 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
             if (j < width) mx = fmaxf(mx, lg[r]);
         }
         mx = grp.fmax(mx);
+        LZB_TLD(tl, 16, __float_as_int(mx) ^ depth);
         float sum = 0.0f;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int j = lane + G * r;
             t[r] = (j < width) ? glibc_expf(lg[r] - mx) : 0.0f;
-#pragma unroll
-            for (int l = 0; l < G; ++l) sum += grp.shfl(t[r], l); // strictly left to right in action order; +0.0f beyond the width
+            if (r == R - 1) LZB_TLD(tl, 20, __float_as_int(t[r]));
+            // strictly left to right in action order; +0.0f beyond the width; the last slice stops at the action space
+            sum = (r == R - 1 && R > 1) ? grp.ordered_add(sum, t[r], A - G * (R - 1)) : grp.ordered_add(sum, t[r], G);
         }
+        LZB_TLD(tl, 17, __float_as_int(sum));
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int j = lane + G * r;
@@ -666,6 +729,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     }
     if (REUSE && lane == 0 && live && no_inference) dst[-1] = make_int4(0, 0, 0, 0); // this tree has no node e_new (tree dumps skip it)
 
+    LZB_TL(tl, 3);
     // ---- backup: node q = depth (leaf) ... 1 are path records q-1, node 0 is the root
     const bool two = (VAR != LZB_GMZ) && (to_play != -1); // cnode.cpp:432; gmz asserts -1 (compiled out)
     const float g = a.discount;
@@ -690,6 +754,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
                 parent_reset = pb[q - 1].y;
             }
         }
+        if (qhi == depth) LZB_TLD(tl, 18, __float_as_int(rew) ^ x);
         float r_pre = rew, r_boot = rew;
         if (VP) {
             r_pre = rew - parent_vp;                    // ez cnode.cpp:515
@@ -700,12 +765,14 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
         // serial leaf->root recurrence (cnode.cpp:447,473-475): lane l receives b_q, then b = r + g*b
         float my_b = 0.f;
         const int cnt = min(G, qhi + 1);
-#pragma unroll
-        for (int l = 0; l < G; ++l) {
+        const int cnt_w = __reduce_max_sync(kFull, live ? cnt : 0); // the longest path piece in the warp
+#pragma unroll 1
+        for (int l = 0; l < cnt_w; ++l) {
             const float rl = grp.shfl(r_signed, l);
             if (lane == l) my_b = b;
             b = (l < cnt) ? rl + g * b : b;
         }
+        if (qhi == depth) LZB_TLD(tl, 19, __float_as_int(b));
         if (valid) {
             const float add = (two && !same) ? -my_b : my_b;
             vsum += add;
@@ -729,12 +796,14 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     }
     cmin = grp.fmin(cmin);
     cmax = grp.fmax(cmax);
+    LZB_TLD(tl, 21, __float_as_int(cmin) ^ __float_as_int(cmax));
     if (lane == 0 && live) {
         float2 mm = p.minmax[i];
         mm.x = fminf(mm.x, cmin); // CMinMaxStats::update (cminimax.cpp:23-31)
         mm.y = fmaxf(mm.y, cmax);
         p.minmax[i] = mm;
     }
+    LZB_TL(tl, 4);
 }
 
 // ---------------------------------------------------------------------------------------------- kernels
@@ -770,12 +839,20 @@ __global__ void __launch_bounds__(128, 7) k_step_g(Pool p, BackupArgs b, SelectA
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
     const bool live = i < p.N;
+#ifdef LZB_TIMELINE
+    const int tl = b.latent_index;
+#else
+    const int tl = -1;
+#endif
+    LZB_TL(tl, 0);
+    LZB_TL(tl, 1);
     pdl_wait();
+    LZB_TL(tl, 2);
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
-    expand_backup_g<VAR, G, R, REUSE>(p, b, live ? i : 0, live, grp);
+    expand_backup_g<VAR, G, R, REUSE>(p, b, live ? i : 0, live, grp, tl);
     __syncwarp(); // the warp's own global writes (records, root, MinMax) are ordered before its reads below
     if constexpr (VAR == LZB_GMZ) select_gumbel_g<G, R>(p, a, live ? i : 0, live, grp);
-    else select_puct_g<VAR, G, R, REUSE>(p, a, live ? i : 0, live, grp);
+    else select_puct_g<VAR, G, R, REUSE>(p, a, live ? i : 0, live, grp, tl);
 }
 
 } // namespace lzb
