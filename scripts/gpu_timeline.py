@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--roots", type=int, default=8192)
     ap.add_argument("--sims", type=int, default=50)
     ap.add_argument("--build-only", action="store_true")
+    ap.add_argument("--no-save", action="store_true", help="print the summary only (the raw stamps are ~40 MB)")
     ap.add_argument("--analyse", default=None, help="only analyse a saved .npy")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "timeline.npy"))
     a = ap.parse_args()
@@ -64,8 +65,9 @@ def main():
     torch.cuda.synchronize()
     assert L.lzb_debug_timeline(C.c_void_p(0)) == 0
     t = buf.cpu().numpy().astype(np.uint64)
-    os.makedirs(os.path.dirname(a.out), exist_ok=True)
-    np.save(a.out, t)
+    if not a.no_save:
+        os.makedirs(os.path.dirname(a.out), exist_ok=True)
+        np.save(a.out, t)
     analyse(t, a.sims)
 
 
