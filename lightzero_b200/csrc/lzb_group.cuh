@@ -452,7 +452,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
 // csoftmax (gmz cnode.cpp:904-933) over the n values a lane group holds as x[r] for j = lane + G*r:
 // exp(x - max - log(sum)) with the sum taken strictly in index order.
 template <int G, int R>
-__device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, const Grp<G> &grp)
+__device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, int A, const Grp<G> &grp)
 {
     const int lane = grp.lane;
     float m = -INFINITY;
@@ -464,8 +464,8 @@ __device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, const Grp<G> &g
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const float ex = (lane + G * r < n) ? glibc_expf(x[r] - m) : 0.0f;
-#pragma unroll
-        for (int l = 0; l < G; ++l) sum += grp.shfl(ex, l); // index order; +0.0f beyond n is exact
+        // index order; +0.0f beyond n is exact; the last slice stops at the action space
+        sum = (r == R - 1 && R > 1) ? grp.ordered_add(sum, ex, A - G * (R - 1)) : grp.ordered_add(sum, ex, G);
     }
     const float ls = glibc_logf(sum);
 #pragma unroll
@@ -516,7 +516,7 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
         }
         vsum_i = grp.isum(vsum_i);
         vmax_i = grp.imax(vmax_i);
-        csoftmax_g<G, R>(sp, n, grp); // priors (probabilities) are soft-maxed again (:1014) - reproduced as is
+        csoftmax_g<G, R>(sp, n, A, grp); // priors (probabilities) are soft-maxed again (:1014) - reproduced as is
 
         // ---- compute_mixed_value (:935-970): serial sums over visited children in index order
         float probs_sum = 0.0f;
@@ -524,16 +524,16 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
         for (int r = 0; r < R; ++r) {
             const float pc = (sp[r] < -10e7f) ? -10e7f : sp[r]; // std::max(prior, min_num)
             const float t = (vc[r] > 0) ? pc : 0.0f;
-#pragma unroll
-            for (int l = 0; l < G; ++l) probs_sum += grp.shfl(t, l);
+            if (__any_sync(kFull, vc[r] > 0)) // warp-uniform: a slice without a visited child adds only +0.0f
+                probs_sum = (r == R - 1 && R > 1) ? grp.ordered_add(probs_sum, t, A - G * (R - 1)) : grp.ordered_add(probs_sum, t, G);
         }
         float wq = 0.0f;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const float pc = (sp[r] < -10e7f) ? -10e7f : sp[r];
             const float t = (vc[r] > 0) ? pc * q[r] / probs_sum : 0.0f;
-#pragma unroll
-            for (int l = 0; l < G; ++l) wq += grp.shfl(t, l);
+            if (__any_sync(kFull, vc[r] > 0))
+                wq = (r == R - 1 && R > 1) ? grp.ordered_add(wq, t, A - G * (R - 1)) : grp.ordered_add(wq, t, G);
         }
         const float vsum_f = (float)vsum_i;
         const float mixed = (raw_value + vsum_f * wq) / (vsum_f + 1);
@@ -572,7 +572,7 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
         } else { // cselect_interior_child
 #pragma unroll
             for (int r = 0; r < R; ++r) sc[r] = __int_as_float(c[r].z) + cq[r];
-            csoftmax_g<G, R>(sc, n, grp);
+            csoftmax_g<G, R>(sc, n, A, grp);
             const float den = (float)(1 + vsum_i);
 #pragma unroll
             for (int r = 0; r < R; ++r) sc[r] = sc[r] - (float)vc[r] / den;
