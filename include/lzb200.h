@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define LZB_ABI_VERSION 3
+#define LZB_ABI_VERSION 4
 
 /* tree flavours */
 #define LZB_MZ 0  /* ctree_muzero */
@@ -201,6 +201,21 @@ int lzb_traverse(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_travers
  * used as given; else if lstm_horizon_len > 0 is_reset = (search_len % lstm_horizon_len == 0) is
  * computed on device, written to is_reset_out_dev when non-NULL.  sampled_actions [N,K,D]: the new
  * nodes' action table (sampled tree).  new_slots: where the new nodes' latent / LSTM rows live. */
+/* Stochastic tree, both model heads run on the whole batch (no compacted sub-batches, nothing leaves the device:
+ * mcts_ctree_stochastic.py:165-251 calls the model once per leaf kind on Python-compacted rows).  The tree picks per
+ * leaf: a leaf that is a CHANCE node takes reward / value / logits from this struct (the head called with
+ * afterstate=False) and its new node's latent rows from latent_dev; a DECISION leaf takes the lzb_backprop_io_t's own
+ * reward / value / logits and new_slots.ptr[0].  Later gathers read a node's rows from the tensor of its kind, so no
+ * per-row select of the two heads' [N, row] outputs is ever materialised.
+ *   logits_stride: floats per row of logits_dev here (>= chance_space_size);
+ *   decision_logits_stride: floats per row of lzb_backprop_io_t::logits_dev (>= the decision action space; 0 = the
+ *     forest's padded width max(A, C), the layout without this struct). */
+typedef struct {
+    const float *reward_dev, *value_dev, *logits_dev;
+    int32_t logits_stride, decision_logits_stride;
+    const void *latent_dev;
+} lzb_chance_head_t;
+
 typedef struct {
     int32_t latent_index;
     float discount;
@@ -216,6 +231,7 @@ typedef struct {
      * cnode.cpp:559-587), whose driver backs the chance leaves and the decision leaves up in two calls
      * (mcts_ctree_stochastic.py:232-251).  Lane-group kernels only (every action space <= 128); not in lzb_step. */
     const int32_t *active_dev;
+    const lzb_chance_head_t *chance_head; /* stochastic tree only; NULL = one [N] batch holds every leaf's outputs */
 } lzb_backprop_io_t;
 int lzb_backprop(lzb_forest_t *f, const lzb_backprop_io_t *io, void *stream);
 

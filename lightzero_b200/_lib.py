@@ -94,13 +94,19 @@ class TraverseIO(C.Structure):
                 ("reuse", C.POINTER(Reuse)), ("chance", C.POINTER(Chance))]
 
 
+class ChanceHead(C.Structure):
+    """lzb_chance_head_t"""
+    _fields_ = [("reward_dev", C.c_void_p), ("value_dev", C.c_void_p), ("logits_dev", C.c_void_p),
+                ("logits_stride", C.c_int32), ("decision_logits_stride", C.c_int32), ("latent_dev", C.c_void_p)]
+
+
 class BackpropIO(C.Structure):
     """lzb_backprop_io_t"""
     _fields_ = [("latent_index", C.c_int32), ("discount", C.c_float), ("reward_dev", C.c_void_p),
                 ("value_dev", C.c_void_p), ("logits_dev", C.c_void_p), ("to_play_dev", C.c_void_p),
                 ("is_reset_dev", C.c_void_p), ("lstm_horizon_len", C.c_int32), ("is_reset_out_dev", C.c_void_p),
                 ("sampled_actions_dev", C.c_void_p), ("new_slots", Slots), ("reuse", C.POINTER(Reuse)),
-                ("active_dev", C.c_void_p)]
+                ("active_dev", C.c_void_p), ("chance_head", C.POINTER(ChanceHead))]
 
 
 _P = C.c_void_p
@@ -162,7 +168,7 @@ def lib():
             fn = getattr(L, name)  # AttributeError here == header and library disagree
             fn.restype = res
             fn.argtypes = args
-        if L.lzb_abi_version() != 3:
+        if L.lzb_abi_version() != 4:
             raise RuntimeError("liblzb200.so ABI version mismatch")
         _lib = L
     return _lib

@@ -24,6 +24,7 @@ struct lzb_forest {
     int pbc_base; float pbc_init; // pUCT constants the pbc table in the workspace was computed for
     const void *players_for; // to_play pointer whose batch maximum is in pool.scratch[0] for this search
     int expanded; // highest latent_index expanded so far
+    bool slot_by_kind; // stochastic tree: new nodes' rows were registered per kind (lzb_chance_head_t::latent_dev)
     int vt_m, vt_s;
     std::vector<int> vtable_host;
     std::vector<float> gumbel_host;
@@ -378,7 +379,7 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
     p.path_a = (int4 *)(w + l.path_a); p.path_b = (int2 *)(w + l.path_b); p.res = (int4 *)(w + l.res);
     p.best = (int *)(w + l.best); p.bidx = (int *)(w + l.bidx); p.actions = (float *)(w + l.actions); p.gumbel = (float *)(w + l.gumbel);
     p.vtable = (int *)(w + l.vtable); p.scratch = (int *)(w + l.scratch);
-    f->bytes = l.total; f->delta = 0.0f; f->sim = 0; f->expanded = -1; f->vt_m = -1; f->vt_s = -1; f->players_for = nullptr; f->pbc_base = -1; f->pbc_init = 0.0f;
+    f->bytes = l.total; f->delta = 0.0f; f->sim = 0; f->expanded = -1; f->slot_by_kind = false; f->vt_m = -1; f->vt_s = -1; f->players_for = nullptr; f->pbc_base = -1; f->pbc_init = 0.0f;
     cudaStream_t st = (cudaStream_t)stream;
     k_init<<<(num_roots + 127) / 128, 128, 0, st>>>(p, legal_count_dev, legal_actions_dev);
     if (variant == LZB_GMZ) {
@@ -403,6 +404,7 @@ int lzb_forest_reset(lzb_forest_t *f, const int32_t *legal_count_dev, const int3
     LZB_CUDA(cudaGetLastError());
     f->sim = 0;
     f->expanded = -1;
+    f->slot_by_kind = false;
     f->players_for = nullptr;
     return LZB_OK;
 }
@@ -432,6 +434,7 @@ int lzb_prepare(lzb_forest_t *f, const float *logits_dev, const float *noise_dev
     LZB_CUDA(cudaGetLastError());
     f->sim = 0;
     f->expanded = 0;
+    f->slot_by_kind = false;
     f->players_for = nullptr;
     return LZB_OK;
 }
@@ -462,6 +465,7 @@ int fill_select(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse
     a.c_base = cfg->pb_c_base; a.c_init = cfg->pb_c_init; a.discount = cfg->discount; a.delta = f->delta;
     a.players = (p.variant == LZB_GMZ) ? 1 : cfg->players; a.sim = f->sim; a.rng_mode = cfg->rng_mode; a.seed = cfg->rng_seed;
     a.num_simulations = cfg->num_simulations; a.ng = io->num_gathers; a.new_e = -1;
+    a.slot_by_kind = f->slot_by_kind ? 1 : 0;
     a.to_play = io->to_play_dev; a.ix = io->ix_dev; a.iy = io->iy_dev; a.search_len = io->search_len_dev; a.vtp = io->vtp_dev;
     a.last_action = (long long *)io->last_action_dev; a.last_action_f = io->last_action_f_dev;
     for (int k = 0; k < io->num_gathers; ++k) {
@@ -519,6 +523,20 @@ int fill_backup(lzb_forest_t *f, const lzb_backprop_io_t *io, BackupArgs &b)
                    io->sampled_actions_dev, io->to_play_dev, io->is_reset_dev, io->is_reset_out_dev, io->new_slots.n, {}};
     for (int k = 0; k < io->new_slots.n; ++k) b.new_slot[k] = (const char *)io->new_slots.ptr[k];
     b.active = io->active_dev;
+    if (io->chance_head) {
+        const lzb_chance_head_t &h = *io->chance_head;
+        if (p.variant != LZB_SMZ) return fail(LZB_E_ARG, "chance_head exists for the stochastic tree only");
+        if (!h.reward_dev || !h.value_dev || !h.logits_dev || h.logits_stride < p.C || (h.decision_logits_stride && h.decision_logits_stride < p.Ad))
+            return fail(LZB_E_ARG, "chance_head: NULL outputs or a logits stride below the node width");
+        b.reward_c = h.reward_dev; b.value_c = h.value_dev; b.logits_c = h.logits_dev;
+        b.logits_c_stride = h.logits_stride; b.logits_stride = h.decision_logits_stride;
+        if (h.latent_dev) { // slot row 1 of the new node = its rows if it is a chance node
+            if (io->new_slots.n != 1) return fail(LZB_E_ARG, "chance_head.latent_dev goes with exactly one new_slots pointer (the decision head's rows)");
+            b.new_slot[1] = (const char *)h.latent_dev;
+            b.n_slots = 2;
+            f->slot_by_kind = true;
+        }
+    }
     if (io->reuse) {
         if (int rc = check_reuse(p)) return rc;
         if (!io->reuse->reuse_value_dev || (!io->reuse->flags_dev && !io->reuse->true_action_dev))

@@ -80,6 +80,9 @@ struct BackupArgs {
     const int *reuse_flags;    // [N] bit 0: tree is in no_inference_lst, bit 1: in reuse_lst; nullptr: derived from the traverse
     const int *batch_index;    // [N] count_b of tree i in the caller's compacted batch; nullptr: i
     const int *active;         // [N] or nullptr: trees with active[i] == 0 are left untouched (lane-group backup kernel only)
+    // Stochastic tree, both heads on the whole batch (lzb_chance_head_t): a chance leaf's outputs; nullptr = one batch
+    const float *reward_c, *value_c, *logits_c;
+    int logits_c_stride, logits_stride; // floats per logits row (logits_stride 0 = the pool width)
 };
 
 // cbatch_backpropagate: CNode::expand of the leaf + cbackpropagate along the recorded path

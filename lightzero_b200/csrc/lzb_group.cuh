@@ -118,14 +118,16 @@ __device__ __forceinline__ void tl_mark_dep(int row, int slot, int dep)
 #endif
 
 // Leaf rows of one tree moved by the G lanes of its group (same semantics as gather_rows in lzb_select.cuh).
+// slot_row >= 0: the slot-table row to read instead of the gather's own index (stochastic tree: the row of the parent's kind)
 template <int G>
-__device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a, int i, int ix, int parent_reset, int lane)
+__device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a, int i, int ix, int parent_reset, int lane, int slot_row = -1)
 {
     for (int k = 0; k < a.ng; ++k) {
         const long long rb = a.g[k].row_bytes;
         const char *s;
+        const int ks = (slot_row >= 0) ? slot_row : k;
         if (a.g[k].src) s = a.g[k].src + ((long long)ix * p.N + i) * rb;
-        else s = ((ix == a.new_e) ? pick3(a.new_slot, k) : p.slots[(size_t)k * p.E + ix]) + (long long)i * rb;
+        else s = ((ix == a.new_e) ? pick3(a.new_slot, ks) : p.slots[(size_t)ks * p.E + ix]) + (long long)i * rb;
         char *d = a.g[k].dst + (long long)i * rb;
         const bool zero = a.g[k].zero_if_reset && parent_reset == 1;
         if ((rb & 15) == 0 && ((((unsigned long long)s) | ((unsigned long long)d)) & 15ull) == 0) {
@@ -223,6 +225,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     int parent_visits = rt.x;
     float parent_reward = __int_as_float(rt.z);
     int e = 0, depth = 0, pos = 0, action = 0, parent_reset = 0;
+    int parent_chance = 0; // smz: the node the last choice was made at is a chance node
     float parent_q = 0.0f;
     bool is_root = true;
     bool going = live; // this group is still descending
@@ -384,6 +387,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         if (going) {
             pos = newpos;
             parent_reset = (VAR == LZB_SMZ) ? 0 : h.z; // smz headers carry is_chance in that slot
+            if (VAR == LZB_SMZ) parent_chance = h.z;
             if (players > 1) vtp = (vtp == 1) ? 2 : 1; // cnode.cpp:797-804
             if (lane == 0) {
                 pa[depth] = make_int4(e * B + 1 + pos, ch.x, ch.y, ch.w);
@@ -426,7 +430,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
                 for (int d = lane; d < p.D; d += G) a.last_action_f[(size_t)i * p.D + d] = act[d];
             if (a.last_action && lane == 0) a.last_action[i] = (long long)act[0]; // discrete sampled: float(index)
         }
-        gather_rows_g<G>(p, a, i, e, parent_reset, lane);
+        gather_rows_g<G>(p, a, i, e, parent_reset, lane, (VAR == LZB_SMZ && a.slot_by_kind) ? (parent_chance ? 1 : 0) : -1);
     }
     LZB_TL(tl, 13);
     if (live && lane == 0) {
@@ -648,8 +652,12 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     const int depth = res.x; // search_len >= 1
     const int e_new = a.latent_index;
     const int to_play = a.to_play[i];
-    const float value = a.value[i];
-    const float leaf_reward = a.reward[i];
+    float value = a.value[i];
+    float leaf_reward = a.reward[i];
+    if (VAR == LZB_SMZ && a.value_c && (depth & 1)) { // a chance leaf takes the other head's outputs
+        value = a.value_c[i];
+        leaf_reward = a.reward_c[i];
+    }
     bool no_inference = false;
     float value_propagate = value;
     if (REUSE) {
@@ -695,7 +703,8 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
             for (int t = lane; t < KD; t += G) tab[t] = a.sampled_actions[(size_t)i * KD + t];
         }
     } else {
-        const float *logits = a.logits + (size_t)i * A;
+        const float *logits = a.logits + (size_t)i * ((VAR == LZB_SMZ && a.logits_stride) ? a.logits_stride : A);
+        if (VAR == LZB_SMZ && a.logits_c && leaf_chance) logits = a.logits_c + (size_t)i * a.logits_c_stride;
         float lg[R], t[R];
         float mx = kFloatMin; // cnode.cpp:118
 #pragma unroll

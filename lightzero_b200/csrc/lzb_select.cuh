@@ -33,6 +33,7 @@ struct SelectArgs {
     int forced_stride;
     int *leaf_is_chance;       // [N] or nullptr
     const unsigned long long *chance_seed; // device word replacing `seed` for the chance draws, or nullptr
+    int slot_by_kind;          // stochastic tree with two heads: a node's rows live in slot row 1 if it is a chance node, else row 0
 };
 
 // dst[i,:] = rows of the leaf's parent (expansion ix) with 16-byte accesses when rows allow it.  The source is

@@ -9,7 +9,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import BackpropIO, Chance, Gather, Reuse, SearchCfg, Slots, TraverseIO, check
+from ._lib import BackpropIO, Chance, ChanceHead, Gather, Reuse, SearchCfg, Slots, TraverseIO, check
 
 VARIANT_ID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3, "smz": 4}
 RNG_BATCH, RNG_PER_ROOT = 1, 2
@@ -219,7 +219,7 @@ class Forest:
         check(self.L.lzb_set_slots(self.h, int(latent_index), C.byref(sl), _stream(self.device)))
 
     def _backprop_io(self, latent_index, discount, reward, value, logits, to_play, is_reset, lstm_horizon_len,
-                     is_reset_out, sampled_actions, new_slots, reuse=None):
+                     is_reset_out, sampled_actions, new_slots, reuse=None, chance_head=None):
         d = self.device
         reward = _dev(reward, torch.float32, d).reshape(-1)
         value = _dev(value, torch.float32, d).reshape(-1)
@@ -229,14 +229,31 @@ class Forest:
         sampled_actions = _dev(sampled_actions, torch.float32, d)
         if reward.numel() != self.N or value.numel() != self.N:
             raise ValueError("reward / value must have N elements")
-        if logits is not None and (logits.numel() != self.N * self.A and self.variant != "sez"):
+        if logits is not None and chance_head is None and (logits.numel() != self.N * self.A and self.variant != "sez"):
             raise ValueError("logits must be [N, A]")
         io = BackpropIO(int(latent_index), float(discount), _p(reward), _p(value), _p(logits), _p(to_play), _p(is_reset),
                         int(lstm_horizon_len), _p(is_reset_out), _p(sampled_actions), self._slots(int(latent_index), new_slots))
         rp, rkeep = self._reuse(reuse)
         if rp is not None:
             io.reuse = rp
-        return io, (reward, value, logits, to_play, is_reset, sampled_actions, rkeep)
+        hkeep = None
+        if chance_head is not None:  # lzb_chance_head_t: the other head's outputs, used by the trees whose leaf is a chance node
+            if self.variant != "smz":
+                raise ValueError("chance_head exists for the stochastic tree only")
+            hr = _dev(chance_head["reward"], torch.float32, d).reshape(-1)
+            hv = _dev(chance_head["value"], torch.float32, d).reshape(-1)
+            hl = _dev(chance_head["logits"], torch.float32, d)
+            lat = chance_head.get("latent")
+            if hr.numel() != self.N or hv.numel() != self.N or hl.dim() != 2 or hl.shape[0] != self.N or logits.dim() != 2:
+                raise ValueError("chance_head: reward / value [N], logits [N, >= C]; decision logits [N, >= A]")
+            if lat is not None and not (lat.is_cuda and lat.is_contiguous()):
+                raise ValueError("chance_head latent must be a contiguous device tensor")
+            ch = ChanceHead(_p(hr), _p(hv), _p(hl), int(hl.shape[1]), int(logits.shape[1]), _p(lat))
+            io.chance_head = C.pointer(ch)
+            if lat is not None:
+                self._slot_keep[("chance", int(latent_index))] = lat
+            hkeep = (ch, hr, hv, hl, lat)
+        return io, (reward, value, logits, to_play, is_reset, sampled_actions, rkeep, hkeep)
 
     def traverse(self, cfg, to_play, out=None, gathers=(), reuse=None, forced_outcome=None):
         """One batch_traverse. ``out``: optional dict of preallocated tensors (ix, iy, last_action, last_action_f,
@@ -249,12 +266,12 @@ class Forest:
         return o
 
     def backprop(self, latent_index, discount, reward, value, logits, to_play, is_reset=None, lstm_horizon_len=0,
-                 is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None, active=None):
+                 is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None, active=None, chance_head=None):
         """One batch_backpropagate; ``reuse``: dict(reuse_value, true_action | flags[, batch_index]) =
         batch_backpropagate_with_reuse with reward / value / logits indexed by tree.  ``active``: [N] int32, trees
         with a zero entry are left untouched (the stochastic tree's leaf_idx_list)."""
         io, keep = self._backprop_io(latent_index, discount, reward, value, logits, to_play, is_reset, lstm_horizon_len,
-                                     is_reset_out, sampled_actions, new_slots, reuse)
+                                     is_reset_out, sampled_actions, new_slots, reuse, chance_head)
         active = _dev(active, torch.int32, self.device)
         if active is not None:
             if active.numel() != self.N:
@@ -264,10 +281,12 @@ class Forest:
 
     def step(self, cfg, latent_index, discount, reward, value, logits, vtp, to_play, out=None, gathers=(), is_reset=None,
              lstm_horizon_len=0, is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None,
-             forced_outcome=None):
-        """backprop(latent_index, ..., vtp) of simulation s and traverse(to_play) of simulation s + 1 in ONE launch."""
+             forced_outcome=None, chance_head=None):
+        """backprop(latent_index, ..., vtp) of simulation s and traverse(to_play) of simulation s + 1 in ONE launch.
+        ``chance_head`` (stochastic tree): dict(reward, value, logits[, latent]) = the outputs of the head run on chance
+        leaves over the whole batch; reward / value / logits / new_slots[0] are then the decision head's."""
         bio, keep_b = self._backprop_io(latent_index, discount, reward, value, logits, vtp, is_reset, lstm_horizon_len,
-                                        is_reset_out, sampled_actions, new_slots, reuse)
+                                        is_reset_out, sampled_actions, new_slots, reuse, chance_head)
         tio, keep_t, o = self._traverse_io(to_play, out, gathers, reuse, forced_outcome)
         check(self.L.lzb_step(self.h, C.byref(cfg), C.byref(bio), C.byref(tio), _stream(self.device)))
         return o

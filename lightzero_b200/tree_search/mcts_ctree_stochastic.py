@@ -15,7 +15,10 @@ Two inference modes (``cfg.stochastic_dense_inference``):
   True             both heads run on the full batch every simulation and a per-row select keeps the one each leaf
                    needs: twice the model rows, but nothing leaves the device inside the loop, so the whole search
                    is one CUDA graph (``cfg.cuda_graph``).  The action handed to the head a row does NOT use is
-                   clamped into that head's range.
+                   clamped into that head's range.  The select is done by the tree kernels themselves
+                   (lzb_chance_head_t: a chance leaf reads the chance head's reward / value / logits, a node's latent
+                   rows are gathered from the output tensor of its kind), so nothing of size [N, latent] is copied;
+                   ``cfg.stochastic_select_in_torch=True`` keeps the torch.where form (tests compare the two).
 """
 import torch
 
@@ -107,12 +110,25 @@ class StochasticMuZeroMCTSCtree(_CtreeDriver):
                               net_d.latent_state.reshape(leaf.shape).to(leaf.dtype))
         return reward, value, logits, new_lat
 
+    def _infer_heads(self, model, leaf, last_action, A, C):
+        """Both heads on the full batch; the tree picks per leaf (lzb_chance_head_t).  Returns the decision head's
+        (reward, value, logits, latent) and the chance head's dict."""
+        net_c = model.recurrent_inference(leaf, last_action.clamp(max=A - 1), afterstate=False)
+        net_d = model.recurrent_inference(leaf, last_action.clamp(max=C - 1), afterstate=True)
+        inv = self.inverse_scalar_transform_handle
+        shape = lambda t: t.reshape(leaf.shape).to(leaf.dtype)
+        head = dict(reward=inv(net_c.reward).reshape(-1).float(), value=inv(net_c.value).reshape(-1).float(),
+                    logits=net_c.policy_logits.float().contiguous(), latent=self._slot_tensor(shape(net_c.latent_state), leaf))
+        return (inv(net_d.reward).reshape(-1).float(), inv(net_d.value).reshape(-1).float(),
+                net_d.policy_logits.float().contiguous(), shape(net_d.latent_state), head)
+
     # ------------------------------------------------------------------ the loop
     def _search(self, roots, model, latent_state_roots, hidden_roots, to_play_batch, reuse_lists=None):
         with torch.no_grad():
             forest, scfg, tp, results, S = self._begin(roots, model, to_play_batch)
             discount = self._cfg.discount_factor
             dense = bool(_get(self._cfg, "stochastic_dense_inference", False))
+            in_tree = dense and not bool(_get(self._cfg, "stochastic_select_in_torch", False))
             lat0 = self._on_device(forest, latent_state_roots)
             if not self._rows_ok(lat0):
                 raise ValueError("latent rows must be a multiple of 4 bytes")
@@ -129,7 +145,10 @@ class StochasticMuZeroMCTSCtree(_CtreeDriver):
             gathers = [(None, leaf)]
             o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers)
             for simulation_index in range(S):
-                if dense:
+                head = None
+                if in_tree:
+                    reward, value, logits, new_lat, head = self._infer_heads(model, leaf, o["last_action"], A, C)
+                elif dense:
                     reward, value, logits, new_lat = self._infer_dense(model, leaf, o["last_action"],
                                                                        o["leaf_is_chance"], W, A, C)
                 else:
@@ -139,7 +158,7 @@ class StochasticMuZeroMCTSCtree(_CtreeDriver):
                 e = simulation_index + 1
                 if e < S:
                     o = forest.step(scfg, e, discount, reward, value, logits, o["vtp"], tp, out=o, gathers=gathers,
-                                    new_slots=[new_lat])
+                                    new_slots=[new_lat], chance_head=head)
                 else:
-                    forest.backprop(e, discount, reward, value, logits, o["vtp"], new_slots=[new_lat])
+                    forest.backprop(e, discount, reward, value, logits, o["vtp"], new_slots=[new_lat], chance_head=head)
                 forest.sims_done += 1

@@ -525,9 +525,12 @@ class StochasticScenarioModel:
     Sub-batches arrive compacted, so column 1 of every latent row carries the tree index and the model looks its
     rows up by it; every tree is inferred once per simulation (``calls_per_row`` times with dense inference)."""
 
-    def __init__(self, sc, dev, calls_per_row=1):
+    def __init__(self, sc, dev, calls_per_row=1, poison=None):
         import torch
         self.sc, self.dev, self.per_sim = sc, dev, sc.n * calls_per_row
+        # dense inference runs both heads on every row; ``poison`` = the oracle's per-simulation leaf kinds: the rows a
+        # head is NOT meant for then come back as garbage, so a tree that picks the wrong head cannot match the oracle
+        self.poison = None if poison is None else [torch.as_tensor(r["leaf_is_chance"].astype(np.bool_)).to(dev) for r in poison]
         t = lambda a: torch.as_tensor(a).to(dev)
         self.logits, self.value, self.reward = t(sc.logits), t(sc.value), t(sc.reward)
         self.rows_seen = 0
@@ -555,6 +558,12 @@ class StochasticScenarioModel:
         o.policy_logits = self.logits[s][rows, :width]
         o.value = self.value[s][rows].unsqueeze(1)
         o.reward = self.reward[s][rows].unsqueeze(1)
+        if self.poison is not None and s < len(self.poison):
+            wrong = self.poison[s][rows] == afterstate  # afterstate=False serves the chance leaves
+            o.latent_state[wrong, 0] = -777.0
+            o.policy_logits = torch.where(wrong.unsqueeze(1), o.policy_logits.flip(1) * 3.0 + 1.0, o.policy_logits)
+            o.value = torch.where(wrong.unsqueeze(1), o.value + 1000.0, o.value)
+            o.reward = torch.where(wrong.unsqueeze(1), o.reward - 1000.0, o.reward)
         return o
 
 
@@ -590,7 +599,7 @@ def test_stochastic_list_api_driven_like_the_reference_loop():
     assert roots.forest.sims_done == sc.S
 
 
-@pytest.mark.parametrize("mode", ["compact", "dense", "dense_graph"])
+@pytest.mark.parametrize("mode", ["compact", "dense", "dense_torch", "dense_graph"])
 def test_stochastic_driver_matches_oracle(mode):
     import torch
     import lightzero_b200 as lzb
@@ -599,8 +608,11 @@ def test_stochastic_driver_matches_oracle(mode):
     orc, rec = oracle_run(sc)
     dense = mode != "compact"
     mcts = identity(lzb.StochasticMuZeroMCTSCtree(driver_cfg(sc, stochastic_dense_inference=dense,
+                                                             stochastic_select_in_torch=mode == "dense_torch",
                                                              cuda_graph=mode == "dense_graph")))
-    model = StochasticScenarioModel(sc, torch.device("cuda"), calls_per_row=2 if dense else 1)
+    # "dense" / "dense_graph": the tree kernels pick each leaf's head (lzb_chance_head_t); "dense_torch": torch.where does
+    model = StochasticScenarioModel(sc, torch.device("cuda"), calls_per_row=2 if dense else 1,
+                                    poison=rec if mode in ("dense", "dense_torch") else None)
     first = None
     for rep in range(3 if mode == "dense_graph" else 1):
         roots = lzb.StochasticMuZeroMCTSCtree.roots(sc.n, sc.legal, sc.K)
@@ -616,6 +628,10 @@ def test_stochastic_driver_matches_oracle(mode):
         else:
             check_roots(roots, orc, sc)
             first = got
+    if mode in ("dense", "dense_torch"):  # every head saw, on the rows meant for it, the latent the oracle's leaf hangs below
+        for c in model.calls:
+            mine = rec[c["s"]]["leaf_is_chance"].astype(bool) != c["afterstate"]
+            assert_same(c["ix"].cpu().numpy()[mine], rec[c["s"]]["ix"][mine].astype(np.float32), "sim %d gathered latents" % c["s"])
     if mode == "compact":  # the model saw the reference's call pattern: chance rows first, each leaf kind by itself
         by_sim = {}
         for c in model.calls:
