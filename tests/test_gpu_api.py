@@ -539,6 +539,13 @@ class StochasticScenarioModel:
     def eval(self):
         self.rows_seen = 0
 
+    def chunk(self, lo, hi):
+        """The model of roots [lo, hi) (cfg.search_streams): rows are looked up by tree index, only the call counter is per chunk."""
+        import copy
+        m = copy.copy(self)
+        m.per_sim, m.rows_seen, m.calls = (hi - lo) * (self.per_sim // self.sc.n), 0, []
+        return m
+
     def root_latents(self, L=8):
         lat = np.zeros((self.sc.n, L), np.float32)
         lat[:, 1] = np.arange(self.sc.n)
@@ -599,7 +606,7 @@ def test_stochastic_list_api_driven_like_the_reference_loop():
     assert roots.forest.sims_done == sc.S
 
 
-@pytest.mark.parametrize("mode", ["compact", "dense", "dense_torch", "dense_graph"])
+@pytest.mark.parametrize("mode", ["compact", "dense", "dense_torch", "dense_graph", "dense_graph_3streams"])
 def test_stochastic_driver_matches_oracle(mode):
     import torch
     import lightzero_b200 as lzb
@@ -609,12 +616,13 @@ def test_stochastic_driver_matches_oracle(mode):
     dense = mode != "compact"
     mcts = identity(lzb.StochasticMuZeroMCTSCtree(driver_cfg(sc, stochastic_dense_inference=dense,
                                                              stochastic_select_in_torch=mode == "dense_torch",
-                                                             cuda_graph=mode == "dense_graph")))
+                                                             search_streams=3 if mode == "dense_graph_3streams" else 1,
+                                                             cuda_graph=mode.startswith("dense_graph"))))
     # "dense" / "dense_graph": the tree kernels pick each leaf's head (lzb_chance_head_t); "dense_torch": torch.where does
     model = StochasticScenarioModel(sc, torch.device("cuda"), calls_per_row=2 if dense else 1,
                                     poison=rec if mode in ("dense", "dense_torch") else None)
     first = None
-    for rep in range(3 if mode == "dense_graph" else 1):
+    for rep in range(3 if mode.startswith("dense_graph") else 1):
         roots = lzb.StochasticMuZeroMCTSCtree.roots(sc.n, sc.legal, sc.K)
         if rep == 2:
             roots.chance_seed = SEED  # replay of the captured search under the first search's chance stream
