@@ -113,8 +113,15 @@ class StochasticMuZeroMCTSCtree(_CtreeDriver):
     def _infer_heads(self, model, leaf, last_action, A, C):
         """Both heads on the full batch; the tree picks per leaf (lzb_chance_head_t).  Returns the decision head's
         (reward, value, logits, latent) and the chance head's dict."""
-        net_c = model.recurrent_inference(leaf, last_action.clamp(max=A - 1), afterstate=False)
-        net_d = model.recurrent_inference(leaf, last_action.clamp(max=C - 1), afterstate=True)
+        # a chance leaf was reached by a decision action (< A), a decision leaf by a chance outcome (< C): the action a
+        # head gets for a row it is not meant for is clamped into its range (both clamps in one launch)
+        lim = self.__dict__.get("_act_limits")
+        if lim is None or lim[0] != (A, C, last_action.device):
+            lim = ((A, C, last_action.device), torch.tensor([[A - 1], [C - 1]], dtype=last_action.dtype, device=last_action.device))
+            self._act_limits = lim
+        acts = torch.minimum(last_action.unsqueeze(0), lim[1])
+        net_c = model.recurrent_inference(leaf, acts[0], afterstate=False)
+        net_d = model.recurrent_inference(leaf, acts[1], afterstate=True)
         inv = self.inverse_scalar_transform_handle
         shape = lambda t: t.reshape(leaf.shape).to(leaf.dtype)
         head = dict(reward=inv(net_c.reward).reshape(-1).float(), value=inv(net_c.value).reshape(-1).float(),
