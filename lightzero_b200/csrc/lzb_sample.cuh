@@ -53,19 +53,28 @@ __global__ void k_sample_actions(SampleArgs a)
     const uint32_t groot = (uint32_t)(a.root_offset + i);
     if (a.continuous) {
         const float *mu = a.logits + (size_t)i * 2 * a.D, *sg = mu + a.D;
-        for (int t = lane; t < a.K * a.D; t += 32) {
-            const int d = t % a.D;
-            float u1, u2;
-            if (a.uniforms) {
-                u1 = a.uniforms[((size_t)i * a.K * a.D + t) * 2];
-                u2 = a.uniforms[((size_t)i * a.K * a.D + t) * 2 + 1];
-            } else {
-                const uint4 r = rng(a.counter, groot, (uint32_t)t, 0x5a3c0001u);
-                u1 = unit_open(r.x);
-                u2 = unit_open(r.y);
+        // one Philox block (four words) serves the two samples 2q and 2q + 1; `uniforms` keeps one (u1, u2) pair per sample
+        const int KD = a.K * a.D;
+        for (int q = lane; 2 * q < KD; q += 32) {
+            uint4 r = make_uint4(0, 0, 0, 0);
+            if (!a.uniforms) r = rng(a.counter, groot, (uint32_t)q, 0x5a3c0001u);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int t = 2 * q + h;
+                if (t < KD) {
+                    const int d = t - (t / a.D) * a.D;
+                    float u1, u2;
+                    if (a.uniforms) {
+                        u1 = a.uniforms[((size_t)i * KD + t) * 2];
+                        u2 = a.uniforms[((size_t)i * KD + t) * 2 + 1];
+                    } else {
+                        u1 = unit_open(h ? r.z : r.x);
+                        u2 = unit_open(h ? r.w : r.y);
+                    }
+                    const float z = sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2); // Box-Muller
+                    a.out[(size_t)i * KD + t] = tanhf(mu[d] + sg[d] * z);
+                }
             }
-            const float z = sqrtf(-2.0f * logf(u1)) * cospif(2.0f * u2); // Box-Muller
-            a.out[(size_t)i * a.K * a.D + t] = tanhf(mu[d] + sg[d] * z);
         }
         return;
     }
