@@ -379,6 +379,33 @@ def test_reuse_search_is_rejected_where_the_reference_has_none():
                                   reuse_value=torch.zeros(4, device=dev)))
 
 
+def test_chance_head_is_checked_at_the_abi():
+    """lzb_chance_head_t: stochastic tree only, non-NULL outputs, strides not below the node widths."""
+    import torch
+    from lightzero_b200.forest import Forest
+    n, A, S = 4, 6, 4
+    z = lambda *shape: torch.zeros(*shape, device="cuda")
+    tp = torch.full((n,), -1, dtype=torch.int32, device="cuda")
+    f = Forest("mz", n, A, S)
+    f.prepare(z(n, A), None, 0.0, z(n), tp)
+    cfg = f.make_cfg(num_simulations=S, players=1)
+    o = f.traverse(cfg, tp)
+    head = dict(reward=z(n), value=z(n), logits=z(n, A))
+    with pytest.raises(ValueError, match="stochastic"):
+        f.backprop(1, 0.997, z(n), z(n), z(n, A), o["vtp"], chance_head=head)
+    f = Forest("smz", n, A, S, chance_space=5)
+    f.prepare(z(n, f.A), None, 0.0, z(n), tp)
+    cfg = f.make_cfg(num_simulations=S, players=1)
+    o = f.traverse(cfg, tp)
+    with pytest.raises(RuntimeError, match="stride"):  # 3 < 5 chance outcomes
+        f.backprop(1, 0.997, z(n), z(n), z(n, A), o["vtp"], chance_head=dict(reward=z(n), value=z(n), logits=z(n, 3)))
+    with pytest.raises(RuntimeError, match="stride"):  # decision logits narrower than the decision action space
+        f.backprop(1, 0.997, z(n), z(n), z(n, A - 1), o["vtp"], chance_head=dict(reward=z(n), value=z(n), logits=z(n, 5)))
+    # exact widths (no padding to max(A, C)) are accepted
+    f.backprop(1, 0.997, z(n), z(n), z(n, A), o["vtp"], chance_head=dict(reward=z(n), value=z(n), logits=z(n, 5), latent=z(n, 8)),
+               new_slots=[z(n, 8)])
+
+
 EDGE_SHAPES = {  # smallest / boundary sizes of every kernel flavour: (variant, n, A, S, extra scenario kwargs)
     "one_root_one_action": ("mz", 1, 1, 12, {}),
     "one_simulation": ("mz", 33, 18, 1, {}),
