@@ -43,7 +43,39 @@ def build(force=False, verbose=False):
         raise RuntimeError("nvcc failed:\n%s\n%s" % (res.stdout, res.stderr))
     if verbose:
         print(res.stderr)
+    pylist()
     return LIB_PATH
+
+
+PYLIST_PATH = os.path.join(HERE, "_lzb_pylist.so")
+_pylist = False  # False: not tried yet; None: unavailable
+
+
+def pylist():
+    """lzb_pylist.c behind ctypes.PyDLL: list-of-lists <-> flat buffers at C speed (host marshalling of the reference's
+    list arguments, no arithmetic).  None when it cannot be built or loaded; the callers then walk the lists with numpy."""
+    global _pylist
+    if _pylist is False:
+        _pylist = None
+        try:
+            src = os.path.join(CSRC, "lzb_pylist.c")
+            if not os.path.exists(PYLIST_PATH) or (os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(PYLIST_PATH)):
+                import sysconfig
+                cc = shutil.which("gcc") or shutil.which("cc")
+                if cc:
+                    subprocess.run([cc, "-O2", "-shared", "-fPIC", "-I" + sysconfig.get_paths()["include"], src, "-o", PYLIST_PATH],
+                                   check=True, capture_output=True)
+            P = C.PyDLL(PYLIST_PATH)
+            P.lzb_rows_to_f32.restype = C.c_int
+            P.lzb_rows_to_f32.argtypes = [C.py_object, C.c_void_p, C.c_long, C.c_long, C.c_void_p]
+            P.lzb_seq_to_f32.restype = C.c_int
+            P.lzb_seq_to_f32.argtypes = [C.py_object, C.c_void_p, C.c_long]
+            P.lzb_rows_from_i32.restype = C.py_object
+            P.lzb_rows_from_i32.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_long]
+            _pylist = P
+        except Exception:
+            _pylist = None
+    return _pylist
 
 
 class SearchCfg(C.Structure):

@@ -1,0 +1,112 @@
+/* Host-side marshalling of the reference's list arguments (CPython C API, loaded through ctypes.PyDLL).
+ *
+ * The reference's tree modules take Python lists of lists and Cython copies them element by element into
+ * std::vector (mz_tree.pyx:34-39,74-82: `list noises`, `list policy_logits_pool`, ...), and hand lists of lists back
+ * (get_distributions, mz_tree.pyx:44-45).  An unmodified policy therefore calls this framework with lists
+ * (lzero/policy/muzero.py:672-719).  numpy needs ~50 ns per element to walk such lists; these loops need ~5:
+ * at 8192 roots x 18 actions a search call with lists in and out drops from 17 ms to a few ms.
+ * No GPU code here and no arithmetic: bytes in, bytes out. */
+#define PY_SSIZE_T_CLEAN
+#include <Python.h>
+#include <stdint.h>
+
+static int as_double(PyObject *o, double *v)
+{
+    if (PyFloat_CheckExact(o)) {
+        *v = PyFloat_AS_DOUBLE(o);
+        return 0;
+    }
+    *v = PyFloat_AsDouble(o); /* ints, numpy scalars, anything with __float__ */
+    return (*v == -1.0 && PyErr_Occurred()) ? -1 : 0;
+}
+
+/* rows: sequence of n sequences, row i of length lens[i] <= width  ->  out[n][width] float32, zero padded.
+ * Returns 0, or -1 with a Python exception set. */
+int lzb_rows_to_f32(PyObject *rows, float *out, long n, long width, int32_t *lens)
+{
+    PyObject *outer = PySequence_Fast(rows, "expected a sequence of rows");
+    if (!outer) return -1;
+    if (PySequence_Fast_GET_SIZE(outer) != n) {
+        Py_DECREF(outer);
+        PyErr_SetString(PyExc_ValueError, "wrong number of rows");
+        return -1;
+    }
+    for (long i = 0; i < n; ++i) {
+        PyObject *row = PySequence_Fast(PySequence_Fast_GET_ITEM(outer, i), "expected a sequence of numbers per row");
+        if (!row) {
+            Py_DECREF(outer);
+            return -1;
+        }
+        const Py_ssize_t m = PySequence_Fast_GET_SIZE(row);
+        if (m > width) {
+            Py_DECREF(row);
+            Py_DECREF(outer);
+            PyErr_SetString(PyExc_ValueError, "a row is longer than the action space");
+            return -1;
+        }
+        float *dst = out + (size_t)i * (size_t)width;
+        for (Py_ssize_t j = 0; j < m; ++j) {
+            double v;
+            if (as_double(PySequence_Fast_GET_ITEM(row, j), &v)) {
+                Py_DECREF(row);
+                Py_DECREF(outer);
+                return -1;
+            }
+            dst[j] = (float)v;
+        }
+        for (Py_ssize_t j = m; j < width; ++j) dst[j] = 0.0f;
+        if (lens) lens[i] = (int32_t)m;
+        Py_DECREF(row);
+    }
+    Py_DECREF(outer);
+    return 0;
+}
+
+/* seq: sequence of n numbers -> out[n] float32 */
+int lzb_seq_to_f32(PyObject *seq, float *out, long n)
+{
+    PyObject *s = PySequence_Fast(seq, "expected a sequence of numbers");
+    if (!s) return -1;
+    if (PySequence_Fast_GET_SIZE(s) != n) {
+        Py_DECREF(s);
+        PyErr_SetString(PyExc_ValueError, "wrong number of elements");
+        return -1;
+    }
+    for (long i = 0; i < n; ++i) {
+        double v;
+        if (as_double(PySequence_Fast_GET_ITEM(s, i), &v)) {
+            Py_DECREF(s);
+            return -1;
+        }
+        out[i] = (float)v;
+    }
+    Py_DECREF(s);
+    return 0;
+}
+
+/* data[n][stride] int32, counts[n] -> [[int] * counts[i]] (new reference), NULL on error */
+PyObject *lzb_rows_from_i32(const int32_t *data, const int32_t *counts, long n, long stride)
+{
+    PyObject *outer = PyList_New(n);
+    if (!outer) return NULL;
+    for (long i = 0; i < n; ++i) {
+        const long m = counts ? counts[i] : stride;
+        PyObject *row = PyList_New(m);
+        if (!row) {
+            Py_DECREF(outer);
+            return NULL;
+        }
+        const int32_t *src = data + (size_t)i * (size_t)stride;
+        for (long j = 0; j < m; ++j) {
+            PyObject *v = PyLong_FromLong(src[j]);
+            if (!v) {
+                Py_DECREF(row);
+                Py_DECREF(outer);
+                return NULL;
+            }
+            PyList_SET_ITEM(row, j, v);
+        }
+        PyList_SET_ITEM(outer, i, row);
+    }
+    return outer;
+}

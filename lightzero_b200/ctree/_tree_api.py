@@ -18,6 +18,7 @@ import itertools
 import numpy as np
 import torch
 
+from .. import _lib
 from ..forest import RNG_BATCH, RNG_PER_ROOT, Forest, _dev
 
 DEFAULT_MAX_SIMULATIONS = int(os.environ.get("LZB_DEFAULT_MAX_SIMULATIONS", "256"))
@@ -44,6 +45,12 @@ def _rows_to_padded(rows, width, dtype):
     if isinstance(rows, (np.ndarray, torch.Tensor)):
         return rows
     n = len(rows)
+    P = _lib.pylist() if dtype == np.float32 else None
+    if P is not None:  # C loops over the list objects (lzb_pylist.c): ~10x faster than numpy on lists of lists
+        out = np.empty((n, width), dtype=np.float32)
+        if P.lzb_rows_to_f32(rows, out.ctypes.data, n, width, None) != 0:
+            raise ValueError("could not read the rows")
+        return out
     lens = np.fromiter((len(r) for r in rows), dtype=np.int64, count=n)
     flat = np.fromiter(itertools.chain.from_iterable(rows), dtype=dtype, count=int(lens.sum()))  # ~30 % faster than np.asarray(rows)
     if n and (lens == width).all():
@@ -145,6 +152,10 @@ class RootsBase:
             return [[] for _ in range(self.root_num)]
         out = self._outputs()
         visits, cnt = out["visits"].cpu().numpy(), out["legal_count"].cpu().numpy()
+        P = _lib.pylist()
+        if P is not None and visits.dtype == np.int32 and cnt.dtype == np.int32:
+            visits, cnt = np.ascontiguousarray(visits), np.ascontiguousarray(cnt)
+            return P.lzb_rows_from_i32(visits.ctypes.data, cnt.ctypes.data, visits.shape[0], visits.shape[1])
         if (cnt == visits.shape[1]).all():
             return visits.tolist()
         return [row[:c] for row, c in zip(visits.tolist(), cnt.tolist())]

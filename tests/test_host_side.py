@@ -168,3 +168,28 @@ def test_end_of_search_exchange_gloo_world2(tmp_path):
                          capture_output=True, text=True, timeout=240)
     assert res.returncode == 0, res.stdout + res.stderr
     assert res.stdout.count("ok") == 2
+
+
+def test_list_marshalling_helper_matches_numpy():
+    """lzb_pylist.c (the C loops behind list-of-lists arguments and get_distributions) against the numpy walk."""
+    from lightzero_b200 import _lib
+    from lightzero_b200.ctree import _tree_api as api
+    P = _lib.pylist()
+    assert P is not None, "the list helper did not build (gcc + Python.h are in this image)"
+    rng = np.random.default_rng(3)
+    a = rng.standard_normal((257, 18)).astype(np.float32)
+    rows = [r[: i % 19] for i, r in enumerate(a.tolist())]  # ragged, including empty rows
+    got = api._rows_to_padded(rows, 18, np.float32)
+    want = np.zeros_like(a)
+    for i, r in enumerate(rows):
+        want[i, : len(r)] = r
+    assert got.dtype == np.float32 and np.array_equal(got, want)
+    assert np.array_equal(api._rows_to_padded([(1, 2.5), [3], ()], 3, np.float32), np.array([[1, 2.5, 0], [3, 0, 0], [0, 0, 0]], np.float32))
+    with pytest.raises(ValueError):
+        api._rows_to_padded([[1.0, 2.0, 3.0, 4.0]], 3, np.float32)  # longer than the action space
+    with pytest.raises(TypeError):
+        api._rows_to_padded([[1.0, "x"]], 3, np.float32)
+    v = rng.integers(0, 1000, (129, 9)).astype(np.int32)
+    c = rng.integers(0, 10, 129).astype(np.int32)
+    out = P.lzb_rows_from_i32(v.ctypes.data, c.ctypes.data, 129, 9)
+    assert out == [r[:k] for r, k in zip(v.tolist(), c.tolist())] and all(type(x) is int for r in out for x in r)
