@@ -160,3 +160,34 @@ def test_lane_group_widths_agree(monkeypatch):
         v, x = _search(T2, 256, 30)
         assert (v.sum(1) == 30).all()
     assert (base[0].sum(1) == S).all()
+
+
+@pytest.mark.parametrize("variant", ["ez", "gmz", "sez", "smz"])
+def test_headline_size_properties_of_the_other_trees(variant, monkeypatch):
+    """The bench.py workloads of the other trees at 8192 roots x 50 simulations: every root spends its whole budget,
+    values are finite, and one captured CUDA-graph replay gives the bits of the eager launches (the sampled and the
+    stochastic tree redraw per search, so there only the budget is compared)."""
+    import sys
+    import torch
+    import bench
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--variant", variant, "--latent", "64"])
+    a = bench.parse_args()
+    dev = torch.device("cuda", 0)
+    inp = bench.make_inputs(a, 0, dev)
+    if variant in ("ez", "sez"):  # as bench.run_b200_arm: zero LSTM state at the roots
+        inp["hidden_c"] = torch.zeros(1, a.roots, bench.HIDDEN[variant], device=dev)
+        inp["hidden_h"] = torch.zeros(1, a.roots, bench.HIDDEN[variant], device=dev)
+    outs = []
+    for graph in (False, True):
+        model = bench.TableModel(inp, a.variant, a.actions, a.chance_space, calls_per_sim=2 if variant == "smz" else 1)
+        mcts = bench.make_driver(a, dev, graph)
+        for _ in range(2 if graph else 1):  # second graphed search = a replay
+            _, visits, values = bench.one_search(a, mcts, model, inp)
+        torch.cuda.synchronize()
+        v, x = visits.cpu().numpy(), values.cpu().numpy()
+        assert v.shape[0] == a.roots and (v.sum(1) == a.sims).all() and (v >= 0).all(), "graph=%s" % graph
+        assert np.isfinite(x).all()
+        outs.append((v, x))
+    if variant in ("ez", "gmz"):
+        assert_same(outs[1][0], outs[0][0], variant + " graph visits")
+        assert_same(outs[1][1], outs[0][1], variant + " graph values")
