@@ -455,10 +455,19 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
 
 // csoftmax (gmz cnode.cpp:904-933) over the n values a lane group holds as x[r] for j = lane + G*r:
 // exp(x - max - log(sum)) with the sum taken strictly in index order.
+// `need[r]`: this lane's slot r of the result is used afterwards; a slice nobody in the warp needs is left as it is
+// (its final expf is skipped), and with no slice needed at all nothing is computed.
 template <int G, int R>
-__device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, int A, const Grp<G> &grp)
+__device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, int A, const Grp<G> &grp, const bool (&need)[R])
 {
     const int lane = grp.lane;
+    bool any_need[R], some = false; // warp-uniform
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        any_need[r] = __any_sync(kFull, need[r]);
+        some = some || any_need[r];
+    }
+    if (!some) return;
     float m = -INFINITY;
 #pragma unroll
     for (int r = 0; r < R; ++r)
@@ -473,7 +482,17 @@ __device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, int A, const Gr
     }
     const float ls = glibc_logf(sum);
 #pragma unroll
-    for (int r = 0; r < R; ++r) x[r] = glibc_expf(x[r] - m - ls);
+    for (int r = 0; r < R; ++r)
+        if (any_need[r]) x[r] = glibc_expf(x[r] - m - ls);
+}
+
+template <int G, int R>
+__device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, int A, const Grp<G> &grp)
+{
+    bool need[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) need[r] = true;
+    csoftmax_g<G, R>(x, n, A, grp, need);
 }
 
 // Gumbel MuZero traverse of tree i by a lane group: sequential halving at the root (cselect_root_child, gmz
@@ -520,7 +539,12 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
         }
         vsum_i = grp.isum(vsum_i);
         vmax_i = grp.imax(vmax_i);
-        csoftmax_g<G, R>(sp, n, A, grp); // priors (probabilities) are soft-maxed again (:1014) - reproduced as is
+        // priors (probabilities) are soft-maxed again (:1014) - reproduced as is; only the entries of visited children
+        // are read below (compute_mixed_value sums over them), so the rest is not evaluated
+        bool sp_need[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) sp_need[r] = going && vc[r] > 0;
+        csoftmax_g<G, R>(sp, n, A, grp, sp_need);
 
         // ---- compute_mixed_value (:935-970): serial sums over visited children in index order
         float probs_sum = 0.0f;
