@@ -29,6 +29,8 @@ def _dev(x, dtype, device):
     if x is None:
         return None
     if isinstance(x, torch.Tensor):
+        if x.dtype == dtype and x.device == device and x.is_contiguous():
+            return x  # the per-simulation case: nothing to do, and .to() / .contiguous() cost ~3 us of host time per tensor
         return x.to(device=device, dtype=dtype, non_blocking=True).contiguous()
     if dtype == torch.float32 and isinstance(x, (list, tuple)) and len(x):
         x = _floats_from_lists(x)
