@@ -260,10 +260,10 @@ class _SearchGraph:
         for k, t in self.static.items():
             if t is not None:
                 t.copy_(p[k][lo:hi], non_blocking=True)
-        self.lat0.copy_(lat0[lo:hi], non_blocking=True)  # host -> device when the caller hands host latents over
+        self._h2d(0, self.lat0, lat0[lo:hi])  # host -> device when the caller hands host latents over
         if self.hid is not None:
-            for d, s in zip(self.hid, hid):
-                d.copy_(s.reshape(roots.num, -1)[lo:hi], non_blocking=True)
+            for j, (d, s) in enumerate(zip(self.hid, hid)):
+                self._h2d(1 + j, d, s.reshape(roots.num, -1)[lo:hi])
         self.tp.copy_(to_play.reshape(-1)[lo:hi], non_blocking=True)
         if self.seed_dev is not None:
             seed = int(getattr(roots, "sample_seed", None) or getattr(roots, "chance_seed", None) or 0) & 0xffffffffffffffff
@@ -272,6 +272,26 @@ class _SearchGraph:
             cnt, idx = legal_tensors(self._legal_slice(roots), hi - lo, roots.action_space_size, roots.variant, self.dev)
             self.legal[0].copy_(cnt, non_blocking=True)
             self.legal[1].copy_(idx, non_blocking=True)
+
+    def _h2d(self, slot, dst, src):
+        """dst.copy_(src) on the current stream.  Pageable host memory (the numpy arrays the reference's callers pass) goes
+        through a pinned staging buffer of this chunk first: the host-side copy into it runs at memory speed on torch's
+        threads (0.3 ms for 33 MB) and the transfer out of it is asynchronous at link speed, where a pageable cudaMemcpy
+        is synchronous and half as fast - so the chunks' transfers overlap the other chunks' simulations as they do for
+        pinned inputs."""
+        if src.is_cuda or src.is_pinned() or src.numel() * src.element_size() < (1 << 20):
+            dst.copy_(src, non_blocking=True)
+            return
+        stage = self.__dict__.setdefault("_stage", {})
+        ent = stage.get(slot)
+        if ent is None or ent[0].shape != src.shape or ent[0].dtype != src.dtype:
+            ent = (torch.empty(src.shape, dtype=src.dtype, pin_memory=True), torch.cuda.Event())
+            stage[slot] = ent
+        else:
+            ent[1].synchronize()  # the previous search's transfer out of the buffer has finished
+        ent[0].copy_(src)
+        dst.copy_(ent[0].view(dst.shape) if ent[0].shape != dst.shape else ent[0], non_blocking=True)
+        ent[1].record()
 
     def _body(self):
         sh = self.shadow

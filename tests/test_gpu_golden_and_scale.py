@@ -98,7 +98,7 @@ class _Tables:
         return t
 
 
-def _search(T, n, S, graph=False, root_offset=0, seed=7, streams=1):
+def _search(T, n, S, graph=False, root_offset=0, seed=7, streams=1, host_latents=False):
     import torch
     import lightzero_b200 as lzb
     mcts = lzb.MuZeroMCTSCtree(dict(num_simulations=S, discount_factor=0.997, value_delta_max=0.01, device="cuda",
@@ -106,12 +106,13 @@ def _search(T, n, S, graph=False, root_offset=0, seed=7, streams=1):
                                     model=dict(support_scale=300, categorical_distribution=False)))
     mcts.inverse_scalar_transform_handle = lambda x: x
     tp = torch.full((n,), -1, dtype=torch.int32)
+    lat0 = T.lat0.cpu().numpy() if host_latents else T.lat0  # numpy = pageable host memory, what the reference's policies pass
     outs = []
     for _ in range(2 if graph else 1):
         roots = lzb.MuZeroMCTSCtree.roots(n, None)
         roots.root_offset = root_offset
         roots.prepare(0.25, T.noise, T.root_reward, T.root_logits, tp)
-        mcts.search(roots, T, T.lat0, tp)
+        mcts.search(roots, T, lat0, tp)
         v, _ = roots.get_distributions_tensor()
         outs.append((v.cpu().numpy(), roots.get_values_tensor().cpu().numpy()))
     return outs[-1]
@@ -137,6 +138,12 @@ def test_headline_size_properties_and_invariances():
         v5, x5 = _search(T, n, S, graph=True, streams=k)
         assert_same(v5, visits, "%d-stream visits" % k)
         assert_same(x5, values, "%d-stream values" % k)
+    # pageable host latents (2 MB here) reach the device through the chunks' pinned staging buffers; the second search
+    # of each call reuses them
+    for k in (1, 4):
+        v6, x6 = _search(T, n, S, graph=True, streams=k, host_latents=True)
+        assert_same(v6, visits, "host latents, %d streams: visits" % k)
+        assert_same(x6, values, "host latents, %d streams: values" % k)
     # sharding invariance: two half batches with global root offsets == the full batch
     h = n // 2
     va, xa = _search(T.rows(0, h), h, S, root_offset=0)
