@@ -87,6 +87,13 @@ class _CtreeDriver:
     def _on_device(forest, x):
         """Root latents / hidden states as one contiguous device tensor (one H2D copy when they come from the host)."""
         t = x if isinstance(x, torch.Tensor) else torch.as_tensor(np.asarray(x))
+        if not t.is_cuda and t.numel() * t.element_size() >= (1 << 20) and not t.is_pinned():
+            # pageable host memory: through a pinned buffer filled by torch's host threads (see _SearchGraph._h2d)
+            pin = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+            pin.copy_(t)
+            out = pin.to(forest.device, non_blocking=True).contiguous()
+            forest.__dict__.setdefault("_pinned_inputs", []).append(pin)  # alive until the forest goes
+            return out
         return t.to(forest.device, non_blocking=True).contiguous()
 
     @staticmethod

@@ -14,7 +14,7 @@ def main():
     dev = torch.device("cuda", 0)
     inp = bench.make_inputs(a, 0, dev)
     model = bench.TableModel(inp, a.variant, a.actions)
-    mcts = bench.make_driver(a, dev, graph=True, streams=a.e2e_streams)
+    mcts = bench.make_driver(a, dev, graph=not a.no_graph, streams=a.e2e_streams)
     host = {k: inp[k].cpu() for k in ("root_logits", "noise", "root_reward", "to_play", "latent_roots")}
     lists = {k: host[k].tolist() for k in ("root_logits", "noise", "root_reward", "to_play")}
     lat = host["latent_roots"].numpy()
