@@ -180,6 +180,21 @@ class Forest:
         d = self.device
         N = self.N
         to_play = _dev(to_play, torch.int32, d)
+        # the per-simulation case: the same output tensors, gathers and to_play as the previous call -> the same struct
+        # (keyed by every pointer that goes into it; the cached tuple keeps those tensors alive)
+        if out and reuse is None and forced_outcome is None:
+            try:
+                seed = getattr(self, "chance_seed_dev", None)
+                key = (to_play.data_ptr(), 0 if seed is None else seed.data_ptr()) + tuple(
+                    t.data_ptr() for t in out.values()) + tuple(
+                    (0 if g[0] is None else g[0].data_ptr(), g[1].data_ptr(), len(g) > 2 and bool(g[2])) for g in gathers)
+            except AttributeError:
+                key = None
+            hit = self.__dict__.get("_tio_cache")
+            if key is not None and hit is not None and hit[0] == key:
+                return hit[1], hit[2], dict(out)
+        else:
+            key = None
         o = dict(out) if out else {}
         for k in ("ix", "iy", "search_len", "vtp"):
             if k not in o:
@@ -223,7 +238,10 @@ class Forest:
             ckeep = (ch, forced, seed)
         elif forced_outcome is not None:
             raise ValueError("forced_outcome exists for the stochastic tree only")
-        return io, (garr, to_play, rkeep, ckeep), o
+        keep = (garr, to_play, rkeep, ckeep)
+        if key is not None and len(o) == len(out):  # nothing was allocated here: `out` named every output
+            self._tio_cache = (key, io, keep + (tuple(o.values()), tuple(gathers)))
+        return io, keep, o
 
     def _slots(self, e, tensors):
         sl = Slots()
