@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--latent", type=int, default=1024)
     ap.add_argument("--roots", type=int, default=8192)
     ap.add_argument("--sims", type=int, default=50)
+    ap.add_argument("--variant", default="mz", help="mz | ez (the pUCT step kernels carry the stamps)")
     ap.add_argument("--build-only", action="store_true")
     ap.add_argument("--no-save", action="store_true", help="print the summary only (the raw stamps are ~40 MB)")
     ap.add_argument("--analyse", default=None, help="only analyse a saved .npy")
@@ -48,11 +49,15 @@ def main():
     L = _lib.lib()
     L.lzb_debug_timeline.restype = C.c_int
     L.lzb_debug_timeline.argtypes = [C.c_void_p]
-    sys.argv = ["bench.py", "--roots", str(a.roots), "--sims", str(a.sims), "--latent", str(a.latent), "--no-graph"]
+    sys.argv = ["bench.py", "--roots", str(a.roots), "--sims", str(a.sims), "--latent", str(a.latent), "--no-graph",
+                "--variant", a.variant]
     ba = bench.parse_args()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
     inp = bench.make_inputs(ba, 0, dev)
+    if ba.variant in bench.HIDDEN:
+        inp["hidden_c"] = torch.zeros(1, a.roots, bench.HIDDEN[ba.variant], device=dev)
+        inp["hidden_h"] = torch.zeros(1, a.roots, bench.HIDDEN[ba.variant], device=dev)
     mcts = bench.make_driver(ba, dev, False)
     model = bench.TableModel(inp, ba.variant, ba.actions)
     for _ in range(3):
