@@ -14,6 +14,10 @@
 #include "lzb_expand.cuh"
 #include "lzb_select.cuh"
 
+#ifndef LZB_MIN_BLOCKS
+#define LZB_MIN_BLOCKS 7 // resident blocks of 128 threads per SM the lane-group kernels are compiled for (72 registers)
+#endif
+
 namespace lzb {
 
 // All 32 lanes of a warp execute every instruction of these kernels together (warp-synchronous style): exchanges
@@ -842,7 +846,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 // ---------------------------------------------------------------------------------------------- kernels
 // 128 threads = 128 / G trees per block; groups without a tree (tail of the last block) run along on tree 0, muted
 template <int VAR, int G, int R, bool REUSE>
-__global__ void __launch_bounds__(128, 7) k_select_g(Pool p, SelectArgs a)
+__global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_select_g(Pool p, SelectArgs a)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
@@ -853,7 +857,7 @@ __global__ void __launch_bounds__(128, 7) k_select_g(Pool p, SelectArgs a)
 }
 
 template <int VAR, int G, int R, bool REUSE>
-__global__ void __launch_bounds__(128, 7) k_expand_backup_g(Pool p, BackupArgs b)
+__global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_expand_backup_g(Pool p, BackupArgs b)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
@@ -867,7 +871,7 @@ __global__ void __launch_bounds__(128, 7) k_expand_backup_g(Pool p, BackupArgs b
 
 // fused simulation step (see lzb_step.cuh): expand + backup of simulation s, then select + gather of s + 1
 template <int VAR, int G, int R, bool REUSE>
-__global__ void __launch_bounds__(128, 7) k_step_g(Pool p, BackupArgs b, SelectArgs a)
+__global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_step_g(Pool p, BackupArgs b, SelectArgs a)
 {
     const Grp<G> grp;
     const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
