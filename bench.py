@@ -67,6 +67,14 @@ def workload_name(a):
         a.roots, a.sims, a.actions, a.latent)
 
 
+def workload_config(a, world):
+    """`config` of the JSON line: names the WORKLOAD only, so both arms (--impl b200 / reference) print the same dict;
+    how an arm ran it (graphs, streams, exchange, host CPU) goes to the line's `run` object."""
+    return {"workload": workload_name(a), "roots_total": a.roots * world, "roots_per_gpu": a.roots, "sims": a.sims,
+            "actions": a.actions, "latent_f32": a.latent, "model": "table lookup (no NN time)",
+            "scalar_transform": "identity"}
+
+
 # --------------------------------------------------------------------------------------------- synthetic inputs
 def make_inputs(a, rank, device):
     """seeded N(0,1) logits / values, N(0,0.1^2) rewards, Dirichlet(0.3) root noise, to_play=-1."""
@@ -201,12 +209,12 @@ def measure_depth(a, mcts, model, inp, rank):
     return float(torch.stack(acc).mean())
 
 
-def make_driver(a, device, graph, streams=None):
+def make_driver(a, device, graph, streams=None, tie_mode="per_root"):
     import lightzero_b200 as lzb
     cls = {"mz": lzb.MuZeroMCTSCtree, "ez": lzb.EfficientZeroMCTSCtree, "gmz": lzb.GumbelMuZeroMCTSCtree,
            "sez": lzb.SampledEfficientZeroMCTSCtree, "smz": lzb.StochasticMuZeroMCTSCtree}[a.variant]
     mcts = cls(dict(num_simulations=a.sims, max_num_considered_actions=16, pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, discount_factor=DISCOUNT,
-                    value_delta_max=DELTA, device=str(device), cuda_graph=graph, tie_break_seed=TIE_SEED,
+                    value_delta_max=DELTA, device=str(device), cuda_graph=graph, tie_break_seed=TIE_SEED, tie_break_mode=tie_mode,
                     search_streams=(streams or a.streams) if graph else 1, stochastic_dense_inference=True,
                     lstm_horizon_len=5,
                     model=dict(support_scale=300, categorical_distribution=False, continuous_action_space=a.variant == "sez",
@@ -356,11 +364,12 @@ def cpu_inputs(a, n, seed):
                 latent_roots=f(n, L), model_latent=f(S, n, L))
 
 
-def cpu_search(a, d):
+def cpu_search(a, d, rng_mode=0, want_values=False):
     """One whole search of the reference ctree on ONE host thread, driven the way mcts_ctree.py:241-321 drives it:
     batch_traverse -> Python gather of leaf latents + np.asarray (:283-286) -> (table-lookup model) ->
     batch_backpropagate.  Uses the compiled unmodified reference (oracle/_ref) when present, else the C port.
-    Returns (seconds, kind, visit counts)."""
+    rng_mode 0: the reference's own libc rand() ties (timing); 1: the pinned batch stream r(TIE_SEED, sim, 0, 0) that
+    the CUDA path reproduces (parity).  Returns (seconds, kind, visit counts[, root values])."""
     from oracle.binding import OracleForest, RefForest, RefSampledForest, ref_available
     n = len(d["to_play"])
     kind = "reference" if ref_available(a.variant) else "port"
@@ -406,7 +415,7 @@ def cpu_search(a, d):
         return time.perf_counter() - t0, kind, dist
     f = RefForest(a.variant, n, a.actions, legal) if kind == "reference" else OracleForest(a.variant, n, a.actions, legal)
     f.set_delta(DELTA)
-    f.set_rng(0 if kind == "reference" else 2, TIE_SEED)  # reference: its own libc rand() stream
+    f.set_rng(rng_mode if rng_mode else (0 if kind == "reference" else 2), TIE_SEED)  # mode 0 = the reference's own libc rand() stream
     f.prepare(NOISE_W, d["noises"], d["root_reward"], d["root_logits"], d["to_play"], values=d["root_value"])
     pool = [d["latent_roots"]]
     for s in range(a.sims):
@@ -416,8 +425,35 @@ def cpu_search(a, d):
         is_reset = (o["search_len"] % 5 == 0).astype(np.int32) if a.variant == "ez" else None
         f.backprop(s + 1, DISCOUNT, d["reward"][s], d["value"][s], d["logits"][s], is_reset, o["vtp"])
     dist, _ = f.distributions()
-    f.values()
-    return time.perf_counter() - t0, kind, dist
+    vals = f.values()
+    dt = time.perf_counter() - t0
+    return (dt, kind, dist, vals) if want_values else (dt, kind, dist)
+
+
+def parity_check(a, inp, model, device):
+    """Bit-exact comparison AT THE BENCH SHAPE: the CUDA path (reference-shaped driver, eager launches) against the
+    compiled unmodified reference tree on the very inputs the timed GPU arm searches (copied to the host), both under
+    the pinned batch tie-break stream r(TIE_SEED, sim, 0, 0) - the keying the unmodified batched reference API can be
+    pinned to (include/lzb200.h).  Visit counts must be identical and root values equal as raw fp32 bits."""
+    import torch
+    if a.variant not in ("mz", "ez", "gmz"):
+        return {"roots_compared": 0, "skipped": "the reference draws its own %s inside the tree; tree parity for this flavour is "
+                "pinned in tests/ with those draws injected" % ("action tables" if a.variant == "sez" else "chance outcomes")}
+    mcts = make_driver(a, device, graph=False, tie_mode="batch")
+    _, visits, values = one_search(a, mcts, model, inp, rank=0)
+    torch.cuda.synchronize()
+    h = lambda t: t.detach().cpu().numpy()
+    n, S = a.roots, a.sims
+    d = dict(root_logits=h(inp["root_logits"]), root_reward=h(inp["root_reward"]), root_value=h(inp["root_value"]),
+             noises=list(h(inp["noise"])), to_play=h(inp["to_play"]), logits=h(inp["logits"]), reward=h(inp["reward"]),
+             value=h(inp["value"]), latent_roots=np.zeros((n, 1), np.float32), model_latent=np.zeros((S, n, 1), np.float32))
+    dt, kind, dist, vals = cpu_search(a, d, rng_mode=1, want_values=True)
+    gv, gx = h(visits), h(values)
+    dist = np.where(dist < 0, 0, dist)
+    return {"roots_compared": int(n), "sims_per_root": int(S), "visit_mismatches": int((gv[:, :dist.shape[1]] != dist).sum()),
+            "value_bit_mismatches": int((gx.view(np.uint32) != np.ascontiguousarray(vals, np.float32).view(np.uint32)).sum()),
+            "checker": kind, "checker_seconds": round(dt, 2),
+            "stream": "pinned batch keying r(seed=%d, sim, 0, 0) on both sides" % TIE_SEED}
 
 
 def _cpu_worker(a, n, seed, conn):
@@ -443,6 +479,10 @@ def run_reference_arm(a):
     total = a.roots
     per = max(1, total // P)
     P = min(P, total // per)
+    # the compiled reference is loaded HERE, before the fork: the workers inherit the mapping and the driver's list of
+    # native libraries of this process shows oracle/_ref/libref_<variant>.so
+    from oracle.binding import ref_available
+    ref_available(a.variant)
     ctx = mp.get_context("fork")
     procs = []
     for r in range(P):
@@ -482,7 +522,9 @@ def run_reference_arm(a):
         "impl": "reference", "metric": "mcts_simulations_per_sec", "value": round(v, 1), "unit": "simulations/s",
         "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a), "host_cpu": cpu},
+        "config": workload_config(a, a.gpus),
+        "run": {"host_cpu": cpu, "processes": P, "marshalling": "flat arrays through oracle/ref_harness.cpp: Cython's list -> "
+                "std::vector copies (~9 % of the reference's time, SURVEY 6) are NOT included, which flatters the reference"},
         "cpu_baseline": {"value": round(v, 1), "unit": "simulations/s", "cores": P, "kind": kind, "sample": sample},
         "e2e": {"value": round(v, 1), "unit": "simulations/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -538,8 +580,11 @@ def run_b200_arm(a):
 
     mids = []
 
+    local_out = {}
+
     def dev_step(timed=False):
         _, visits, values = one_search(a, mcts, model, inp, rank=rank)
+        local_out["visits"], local_out["values"] = visits, values
         if timed and world > 1:  # where the search ends and the exchange begins (diagnostic: config.exchange_ms_per_step)
             mids.append(torch.cuda.Event(enable_timing=True))
             mids[-1].record()
@@ -565,8 +610,23 @@ def run_b200_arm(a):
     t_wall = time.perf_counter() - t_wall
     dev_ms = sum(x.elapsed_time(y) for x, y in ev)
     exchange_ms = sum(m.elapsed_time(y) for m, (_, y) in zip(mids, ev)) / a.steps if mids else 0.0
-    # sanity: a search spends exactly S visits below each root
-    assert bool((visits[:N].sum(1) == S).all()), "visit counts do not sum to the number of simulations"
+    # sanity: a search spends exactly S visits below each root - every row of the gathered batch, not just this shard
+    assert bool((visits.sum(1) == S).all()), "visit counts do not sum to the number of simulations"
+    # correctness of the exchange on real NVLink: the rows every rank RECEIVED (peer-memory kernel or packed NCCL
+    # all-gather) against a plain per-tensor NCCL all-gather of each rank's own shard, on every rank
+    exchange_check = None
+    if world > 1:
+        ref_v = torch.empty((N * world, W), dtype=torch.int32, device=device)
+        ref_x = torch.empty(N * world, dtype=torch.float32, device=device)
+        dist.all_gather_into_tensor(ref_v, local_out["visits"].contiguous())
+        dist.all_gather_into_tensor(ref_x, local_out["values"].contiguous())
+        bad = torch.stack([(visits != ref_v).any(1).sum(), (values.view(torch.int32) != ref_x.view(torch.int32)).sum()]).to(torch.int64)
+        dist.all_reduce(bad)  # summed over ranks: every rank checked every row it received
+        own = slice(rank * N, (rank + 1) * N)
+        assert torch.equal(visits[own], local_out["visits"]) and torch.equal(values[own], local_out["values"])
+        exchange_check = {"rows_checked_per_rank": N * world, "ranks": world, "visit_row_mismatches": int(bad[0]),
+                          "value_bit_mismatches": int(bad[1]),
+                          "against": "torch.distributed all_gather_into_tensor (NCCL) of every rank's own shard"}
 
     # ---- e2e leg: reference-shaped API, HOST inputs (pinned), outputs read back to the host, wall clock
     e2e_ms = None
@@ -648,19 +708,21 @@ def run_b200_arm(a):
             "metric": "mcts_simulations_per_sec", "value": round(total_sims / (ms_step * 1e-3), 1), "unit": "simulations/s",
             "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": round(ms_step, 4),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(a), "roots_total": N * world, "sims": S, "actions": A,
-                       "latent_f32": a.latent, "model": "table lookup in HBM (no NN time)", "scalar_transform": "identity",
-                       "cuda_graph": not a.no_graph, "search_streams": 1 if a.no_graph else a.streams, "l2": "512 MB flush between timed steps; working set > L2",
-                       "parallelism": "roots sharded x%d, all-gather of root outputs per search (%s)" % (
-                           world, "single GPU" if world == 1 else ("NCCL" if a.nccl_exchange else "NVLink peer-memory kernel")),
-                       "wall_ms_per_step_incl_flush": round(1e3 * t_wall / a.steps, 3),
-                       "exchange_ms_per_step": round(exchange_ms, 4)},
+            "config": workload_config(a, world),
+            "run": {"cuda_graph": not a.no_graph, "search_streams": 1 if a.no_graph else a.streams,
+                    "l2": "512 MB flush between timed steps; working set > L2",
+                    "parallelism": "roots sharded x%d, all-gather of root outputs per search (%s)" % (
+                        world, "single GPU" if world == 1 else ("NCCL" if a.nccl_exchange else "NVLink peer-memory kernel")),
+                    "wall_ms_per_step_incl_flush": round(1e3 * t_wall / a.steps, 3),
+                    "exchange_ms_per_step": round(exchange_ms, 4)},
             # init, minmax, prepare, root slots, select, S-1 steps, backup, outputs (+ the exchange kernel when sharded)
             "gpu_launches": a.steps * ((5 + S + 1) * (1 if a.no_graph else a.streams) + (1 if peer is not None else 0)
                                        + (S + 1 if a.variant == "sez" else 0)),  # + one action-sampling kernel per expansion
             "clocks": clk,
             "roofline": roofline(a, per_kernel, depth, peak, src),
         }
+        if exchange_check is not None:
+            line["exchange_check"] = exchange_check
         if e2e_ms is not None:
             line["e2e"] = {"value": round(total_sims / (e2e_tot / a.steps * 1e-3), 1), "unit": "simulations/s",
                            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
@@ -676,7 +738,13 @@ def run_b200_arm(a):
                 best = dt if best is None else min(best, dt)
             line["cpu_baseline"] = {"value": round(n * S / best, 1), "unit": "simulations/s", "cores": 1, "kind": kind,
                                     "sample": "%d of %d roots x %d sims, best of 3, tree + Python leaf gather, no NN" % (n, N, S)}
+            line["parity"] = parity_check(a, inp, model, device)
         print(json.dumps(line))
+        bad = line.get("parity", {})
+        if bad.get("visit_mismatches") or bad.get("value_bit_mismatches"):
+            raise SystemExit("parity: the CUDA search differs from the reference at the bench shape: %r" % bad)
+        if exchange_check and (exchange_check["visit_row_mismatches"] or exchange_check["value_bit_mismatches"]):
+            raise SystemExit("exchange: gathered rows differ from the NCCL all-gather of the shards: %r" % exchange_check)
     if peer is not None:
         if peer.error():
             raise SystemExit("peer exchange: rank %d did not arrive" % (peer.error() - 1))

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define LZB_ABI_VERSION 4
+#define LZB_ABI_VERSION 5
 
 /* tree flavours */
 #define LZB_MZ 0  /* ctree_muzero */
@@ -65,6 +65,10 @@ typedef struct {
     int32_t max_num_considered_actions; /* Gumbel */
     int32_t rng_mode;                   /* LZB_RNG_BATCH | LZB_RNG_PER_ROOT */
     uint64_t rng_seed;
+    /* May be NULL.  Non-NULL: one 64-bit word in DEVICE memory read by the kernels instead of rng_seed, so that a
+     * search captured in a CUDA graph breaks its ties with a fresh stream on every replay (the caller rewrites the
+     * word between replays).  The reference reseeds on every traverse (cnode.cpp:770). */
+    const uint64_t *rng_seed_dev;
 } lzb_search_cfg_t;
 
 const char *lzb_last_error(void);
@@ -166,7 +170,8 @@ typedef struct {
  *     (mcts_ctree_stochastic.py:150-176); equals search_len & 1.
  *   seed_dev (may be NULL): one 64-bit word in DEVICE memory used as the seed of lzb_chance_bits instead of
  *     cfg->rng_seed, so that a search captured in a CUDA graph draws fresh outcomes on every replay (the caller
- *     rewrites the word between replays); the tie-break stream keeps cfg->rng_seed.
+ *     rewrites the word between replays); NULL: the chance draws use the tie-break stream's seed (cfg->rng_seed, or
+ *     the word at cfg->rng_seed_dev when that is given).
  * lzb_backprop / lzb_step expand a chance leaf with the first C entries of its logits row and reward 0
  * (cnode.cpp:115-118), a decision leaf with the first A entries. */
 typedef struct {

@@ -11,6 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "liblzb200.so")
+ABI_VERSION = 5  # LZB_ABI_VERSION of include/lzb200.h
 SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_group.cuh", "lzb_sample.cuh", "lzb_collect.cuh", "lzb_peer.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
 
 NVCC_FLAGS = [
@@ -83,7 +84,7 @@ class SearchCfg(C.Structure):
     _fields_ = [
         ("pb_c_base", C.c_int32), ("pb_c_init", C.c_float), ("discount", C.c_float), ("players", C.c_int32),
         ("num_simulations", C.c_int32), ("max_num_considered_actions", C.c_int32), ("rng_mode", C.c_int32),
-        ("rng_seed", C.c_uint64),
+        ("rng_seed", C.c_uint64), ("rng_seed_dev", C.c_void_p),
     ]
 
 
@@ -200,7 +201,7 @@ def lib():
             fn = getattr(L, name)  # AttributeError here == header and library disagree
             fn.restype = res
             fn.argtypes = args
-        if L.lzb_abi_version() != 4:
+        if L.lzb_abi_version() != ABI_VERSION:
             raise RuntimeError("liblzb200.so ABI version mismatch")
         _lib = L
     return _lib

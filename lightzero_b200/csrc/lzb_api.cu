@@ -464,6 +464,7 @@ int fill_select(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse
     a = SelectArgs{};
     a.c_base = cfg->pb_c_base; a.c_init = cfg->pb_c_init; a.discount = cfg->discount; a.delta = f->delta;
     a.players = (p.variant == LZB_GMZ) ? 1 : cfg->players; a.sim = f->sim; a.rng_mode = cfg->rng_mode; a.seed = cfg->rng_seed;
+    a.seed_dev = (const unsigned long long *)cfg->rng_seed_dev;
     a.num_simulations = cfg->num_simulations; a.ng = io->num_gathers; a.new_e = -1;
     a.slot_by_kind = f->slot_by_kind ? 1 : 0;
     a.to_play = io->to_play_dev; a.ix = io->ix_dev; a.iy = io->iy_dev; a.search_len = io->search_len_dev; a.vtp = io->vtp_dev;

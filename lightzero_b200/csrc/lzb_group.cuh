@@ -235,7 +235,8 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     bool going = live; // this group is still descending
     bool no_inference = false;
     int level = 0;   // rounds of the loop below == depth of every group that is still going (warp-uniform)
-    unsigned long long chance_seed = a.seed;
+    const unsigned long long tie_seed = a.seed_dev ? *a.seed_dev : a.seed; // issued with the other entry loads
+    unsigned long long chance_seed = tie_seed;
     if (VAR == LZB_SMZ && a.chance_seed) chance_seed = *a.chance_seed;
     bool is_true[R]; // root position j holds the trajectory's action
     float reuse_v = 0.0f;
@@ -349,7 +350,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         if (__any_sync(kFull, later > 0)) { // warp-uniform: no group has a tie -> no draw
             // the stream position counts the reference's rand() calls: one per level, per DECISION level for smz
             const unsigned hdepth = (VAR == LZB_SMZ) ? (unsigned)(depth >> 1) : (unsigned)depth;
-            const unsigned rnd = tiebreak_hash(a.seed, (unsigned)a.sim, hroot, (a.rng_mode == LZB_RNG_PER_ROOT) ? hdepth : 0u);
+            const unsigned rnd = tiebreak_hash(tie_seed, (unsigned)a.sim, hroot, (a.rng_mode == LZB_RNG_PER_ROOT) ? hdepth : 0u);
             const int k = (int)(rnd % (unsigned)(later + 1));
             int before = 0; // tie-set members in earlier registers
 #pragma unroll

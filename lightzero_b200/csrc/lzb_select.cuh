@@ -17,6 +17,7 @@ struct SelectArgs {
     int c_base, players, sim, rng_mode, num_simulations, ng;
     float c_init, discount, delta;
     unsigned long long seed;
+    const unsigned long long *seed_dev; // device word replacing `seed` (lzb_search_cfg_t::rng_seed_dev), or nullptr
     const int *to_play;
     int *ix, *iy, *search_len, *vtp;
     long long *last_action;
@@ -113,6 +114,7 @@ __device__ __forceinline__ void select_puct_tree(const Pool &p, const SelectArgs
     const float g = a.discount;
     const float c_base = (float)a.c_base;
     const float mm_delta = mm.y - mm.x;
+    const unsigned long long tie_seed = a.seed_dev ? *a.seed_dev : a.seed;
 
     int parent_visits = rt.x;
     float parent_reward = __int_as_float(rt.z);
@@ -206,8 +208,8 @@ __device__ __forceinline__ void select_puct_tree(const Pool &p, const SelectArgs
             pos = jstar;
             if (later > 0) {
                 const unsigned r = (a.rng_mode == LZB_RNG_PER_ROOT)
-                                       ? tiebreak_hash(a.seed, (unsigned)a.sim, (unsigned)(p.root_offset + i), (unsigned)depth)
-                                       : tiebreak_hash(a.seed, (unsigned)a.sim, 0u, 0u);
+                                       ? tiebreak_hash(tie_seed, (unsigned)a.sim, (unsigned)(p.root_offset + i), (unsigned)depth)
+                                       : tiebreak_hash(tie_seed, (unsigned)a.sim, 0u, 0u);
                 int k = (int)(r % (unsigned)(later + 1));
                 if (k > 0) {
                     for (int j0 = 0; j0 < n; j0 += 32) {

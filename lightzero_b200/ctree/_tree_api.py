@@ -22,16 +22,38 @@ from .. import _lib
 from ..forest import RNG_BATCH, RNG_PER_ROOT, Forest, _dev
 
 DEFAULT_MAX_SIMULATIONS = int(os.environ.get("LZB_DEFAULT_MAX_SIMULATIONS", "256"))
-# Tie-break stream (include/lzb200.h): the reference draws rand() reseeded from the wall clock on every
-# traverse (cnode.cpp:592,770), i.e. a fresh stream per call; here the seed is explicit and reproducible.
-_tie_seed = [int(os.environ.get("LZB_TIE_BREAK_SEED", "0"))]
-_rng_mode = [RNG_PER_ROOT]
+# Tie-break stream (include/lzb200.h).  The reference draws rand() reseeded from the wall clock on every traverse
+# (cnode.cpp:592,770): a fresh stream per call, not reproducible.  Here the seed is explicit and belongs to the ROOTS
+# object (``roots.tie_break_seed`` / ``roots.tie_break_mode``), i.e. to one search:
+#   * default: every new Roots takes derive_seed(base, ordinal) - base from LZB_TIE_BREAK_SEED (default 0), ordinal =
+#     how many Roots this process has created - so consecutive searches break their ties differently, like the
+#     reference, yet a run is reproducible from its base seed;
+#   * pinned: after set_tie_break(seed[, mode]) every new Roots takes exactly ``seed`` (parity tests); a driver whose
+#     cfg carries ``tie_break_seed`` pins (or, with ``tie_break_advance=True``, derives per search from) that seed.
+_default = dict(seed=int(os.environ.get("LZB_TIE_BREAK_SEED", "0")), mode=RNG_PER_ROOT, pinned=False)
+_roots_ordinal = itertools.count(1)
+_M64 = 0xffffffffffffffff
+
+
+def derive_seed(base, ordinal):
+    """Seed of the ``ordinal``-th search of a run with base seed ``base`` (splitmix64 of base + golden * ordinal)."""
+    z = (int(base) + 0x9E3779B97F4A7C15 * int(ordinal)) & _M64
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & _M64
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & _M64
+    return z ^ (z >> 31)
+
+
+def _mode_id(mode):
+    return RNG_BATCH if mode in ("batch", RNG_BATCH) else RNG_PER_ROOT
 
 
 def set_tie_break(seed, mode="per_root"):
-    """Seed (and keying) of the tie-break stream used by every subsequent search of this process."""
-    _tie_seed[0] = int(seed)
-    _rng_mode[0] = RNG_BATCH if mode in ("batch", RNG_BATCH) else RNG_PER_ROOT
+    """Pin the tie-break seed (and keying) every Roots object created from now on starts with; ``seed=None`` returns
+    to the default of a fresh derived seed per Roots."""
+    _default["pinned"] = seed is not None
+    if seed is not None:
+        _default["seed"] = int(seed)
+    _default["mode"] = _mode_id(mode)
 
 
 def _device(device=None):
@@ -112,6 +134,11 @@ class RootsBase:
         self.forest = None
         self.root_offset = 0  # global index of root 0 when the env batch is sharded over GPUs
         self._cleared = False
+        # this search's tie-break stream (see the module comment); a driver may overwrite both before the search
+        self.tie_break_base = _default["seed"]
+        self.tie_break_seed = _default["seed"] if _default["pinned"] else derive_seed(_default["seed"], next(_roots_ordinal))
+        self.tie_break_mode = _default["mode"]
+        self._tie_seed_dev = None  # [1] int64 device tensor read by the kernels instead (CUDA-graph searches)
 
     # ------------------------------------------------------------------ reference surface
     @property
@@ -135,6 +162,7 @@ class RootsBase:
                           value=None if values is None else _dev(values, torch.float32, d).reshape(-1))
         self.action_space_size = A
         self._cleared = False
+        self._cached_outputs = None  # outputs of an earlier (graph) search do not describe the new roots
         if self.forest is not None:  # prepare() on a live object re-roots the same workspace
             self._apply_prepare()
 
@@ -180,6 +208,7 @@ class RootsBase:
         self._cleared = True
         self._prep = None
         self.forest = None
+        self._cached_outputs = None
 
     # ------------------------------------------------------------------ device-tensor twins (no host sync)
     def get_distributions_tensor(self):
@@ -230,9 +259,10 @@ class RootsBase:
         return f.root_outputs()
 
 
-def _search_cfg(forest, pb_c_base, pb_c_init, discount, to_play, num_simulations=0, max_considered=0, players=None):
+def _search_cfg(forest, pb_c_base, pb_c_init, discount, to_play, num_simulations=0, max_considered=0, players=None,
+                roots=None):
     """players is batch-global (cnode.cpp:776-781): derived on the host when to_play came as a host object,
-    else by one device reduction inside lzb_traverse (players = 0)."""
+    else by one device reduction inside lzb_traverse (players = 0).  The tie-break seed / keying are the roots' own."""
     if players is not None:
         pass
     elif forest.variant == "gmz":
@@ -244,8 +274,11 @@ def _search_cfg(forest, pb_c_base, pb_c_init, discount, to_play, num_simulations
         players = 1 if (tp.size and int(tp.max()) == -1) else 2
     elif not to_play.is_cuda:
         players = 1 if (to_play.numel() and int(to_play.max()) == -1) else 2
+    seed, mode, seed_dev = _default["seed"], _default["mode"], None
+    if roots is not None:
+        seed, mode, seed_dev = roots.tie_break_seed, roots.tie_break_mode, getattr(roots, "_tie_seed_dev", None)
     return forest.make_cfg(pb_c_base, pb_c_init, discount, players=players, num_simulations=num_simulations,
-                           max_num_considered_actions=max_considered, rng_mode=_rng_mode[0], rng_seed=_tie_seed[0])
+                           max_num_considered_actions=max_considered, rng_mode=mode, rng_seed=seed, rng_seed_dev=seed_dev)
 
 
 def traverse_tensors(roots, cfg, to_play, results, min_max_stats_lst=None, gathers=(), out=None, max_sims=None,
@@ -272,7 +305,7 @@ def batch_traverse(roots, pb_c_base, pb_c_init, discount_factor, min_max_stats_l
     """mz_tree.pyx:95-100 / ez_tree.pyx:108-114 -> cbatch_traverse.  Returns four Python lists like the reference
     (this list flavour costs one device->host sync per call; search() uses traverse_tensors instead)."""
     f = roots._materialize()
-    cfg = _search_cfg(f, pb_c_base, pb_c_init, discount_factor, virtual_to_play_batch)
+    cfg = _search_cfg(f, pb_c_base, pb_c_init, discount_factor, virtual_to_play_batch, roots=roots)
     o = traverse_tensors(roots, cfg, virtual_to_play_batch, results, min_max_stats_lst)
     return o["ix"].tolist(), o["iy"].tolist(), o["last_action"].tolist(), o["vtp"].tolist()
 
@@ -299,7 +332,7 @@ def batch_traverse_with_reuse(roots, pb_c_base, pb_c_init, discount_factor, min_
     """mz_tree.pyx:102-107 / ez_tree.pyx:116-121 -> cbatch_traverse_with_reuse (ReZero, cnode.cpp:826-928).  Same four
     lists as batch_traverse; a tree that needs no inference reports ix = -1 and iy = its own index."""
     f = roots._materialize()
-    cfg = _search_cfg(f, pb_c_base, pb_c_init, discount_factor, virtual_to_play_batch)
+    cfg = _search_cfg(f, pb_c_base, pb_c_init, discount_factor, virtual_to_play_batch, roots=roots)
     o = traverse_tensors(roots, cfg, virtual_to_play_batch, results, min_max_stats_lst,
                          reuse=dict(true_action=true_action, reuse_value=reuse_value))
     return o["ix"].tolist(), o["iy"].tolist(), o["last_action"].tolist(), o["vtp"].tolist()

@@ -46,7 +46,7 @@ def batch_traverse(roots, num_simulations, max_num_considered_actions, discount_
     """gmz_tree.pyx:91-95 -> cbatch_traverse (gmz cnode.cpp:834-898): no MinMax, no pUCT constants."""
     f = roots._materialize(num_simulations)
     cfg = _search_cfg(f, 0, 0.0, discount_factor, virtual_to_play_batch, num_simulations=num_simulations,
-                      max_considered=max_num_considered_actions)
+                      max_considered=max_num_considered_actions, roots=roots)
     o = traverse_tensors(roots, cfg, virtual_to_play_batch, results)
     return o["ix"].tolist(), o["iy"].tolist(), o["last_action"].tolist(), o["vtp"].tolist()
 

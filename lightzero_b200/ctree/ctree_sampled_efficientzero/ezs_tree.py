@@ -31,8 +31,7 @@ class Roots(RootsBase):
                        sampled_actions=None):
         if sampled_actions is None:
             from ...tree_search.sampling import new_sample_seed, sample_actions
-            from .._tree_api import _tie_seed
-            self.sample_seed = new_sample_seed(_tie_seed[0])
+            self.sample_seed = new_sample_seed(self.tie_break_base)
             sampled_actions = sample_actions(_dev(policy_logits_pool, torch.float32, self._device),
                                              self.env_action_space_size, self.num_of_sampled_actions,
                                              self.continuous_action_space, seed=self.sample_seed, counter=0,
@@ -47,6 +46,7 @@ class Roots(RootsBase):
                           to_play=_dev(to_play_batch, torch.int32, d).reshape(-1), value=None, sampled_actions=sa)
         self.action_space_size = self.num_of_sampled_actions
         self._cleared = False
+        self._cached_outputs = None
         if self.forest is not None:
             self._apply_prepare()
 
@@ -70,7 +70,7 @@ def batch_traverse(roots, pb_c_base, pb_c_init, discount_factor, min_max_stats_l
                    continuous_action_space):
     """ezs_tree.pyx:114-119 -> cbatch_traverse (sez cnode.cpp:1110-1187); last_actions is [N][D] floats."""
     f = roots._materialize()
-    cfg = _search_cfg(f, pb_c_base, pb_c_init, discount_factor, virtual_to_play_batch)
+    cfg = _search_cfg(f, pb_c_base, pb_c_init, discount_factor, virtual_to_play_batch, roots=roots)
     o = traverse_tensors(roots, cfg, virtual_to_play_batch, results, min_max_stats_lst)
     return o["ix"].tolist(), o["iy"].tolist(), o["last_action_f"].tolist(), o["vtp"].tolist()
 

@@ -63,7 +63,7 @@ def batch_traverse(roots, pb_c_base, pb_c_init, discount_factor, min_max_stats_l
     """stochastic_mz_tree.pyx:87-91 -> cbatch_traverse (cnode.cpp:713-787).  Returns FIVE lists:
     (leaf_node_is_chance, ix, iy, last_actions, virtual_to_play)."""
     f = roots._materialize()
-    cfg = _search_cfg(f, pb_c_base, pb_c_init, discount_factor, virtual_to_play_batch)
+    cfg = _search_cfg(f, pb_c_base, pb_c_init, discount_factor, virtual_to_play_batch, roots=roots)
     o = traverse_tensors(roots, cfg, virtual_to_play_batch, results, min_max_stats_lst)
     return ([bool(x) for x in o["leaf_is_chance"].tolist()], o["ix"].tolist(), o["iy"].tolist(),
             o["last_action"].tolist(), o["vtp"].tolist())

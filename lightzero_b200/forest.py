@@ -154,9 +154,14 @@ class Forest:
                                  _p(sampled_actions), _stream(d)))
 
     def make_cfg(self, pb_c_base=19652, pb_c_init=1.25, discount=0.997, players=0, num_simulations=0,
-                 max_num_considered_actions=0, rng_mode=RNG_PER_ROOT, rng_seed=0):
-        return SearchCfg(int(pb_c_base), float(pb_c_init), float(discount), int(players), int(num_simulations),
-                         int(max_num_considered_actions), int(rng_mode), int(rng_seed))
+                 max_num_considered_actions=0, rng_mode=RNG_PER_ROOT, rng_seed=0, rng_seed_dev=None):
+        """``rng_seed_dev``: [1] int64 device tensor the kernels read the tie-break seed from instead of ``rng_seed``
+        (a search replayed as a CUDA graph then takes a new seed per replay)."""
+        cfg = SearchCfg(int(pb_c_base), float(pb_c_init), float(discount), int(players), int(num_simulations),
+                        int(max_num_considered_actions), int(rng_mode), int(rng_seed) & 0xffffffffffffffff,
+                        None if rng_seed_dev is None else rng_seed_dev.data_ptr())
+        cfg._keep = rng_seed_dev
+        return cfg
 
     def _reuse(self, reuse):
         """lzb_reuse_t from a dict(true_action, reuse_value[, infer_count, flags, batch_index]) of device tensors

@@ -7,7 +7,13 @@ outputs and four index lists through numpy / Python lists every simulation (mcts
 `cfg` is the same object the reference takes (an EasyDict or any mapping with attribute access): keys read are
 num_simulations, pb_c_base, pb_c_init, discount_factor, value_delta_max, env_type, device, lstm_horizon_len,
 max_num_considered_actions, model.{support_scale, categorical_distribution}.  Optional extra keys:
-tie_break_seed (int), tie_break_mode ('per_root' | 'batch').
+tie_break_seed (int), tie_break_mode ('per_root' | 'batch'), tie_break_advance (bool).
+
+Tie-break stream per search (ctree/_tree_api.py).  Without ``tie_break_seed`` every search breaks its ties with a fresh
+stream derived from (LZB_TIE_BREAK_SEED, ordinal), as the reference's per-traverse reseeding does (cnode.cpp:770).  With
+``tie_break_seed`` the stream is PINNED to that seed for every search (reproducible; what the parity tests and the
+bench use) unless ``tie_break_advance=True``, which derives search k's seed from (tie_break_seed, k).  A search
+replayed as a CUDA graph reads its seed from a device word, so the same rules hold across replays.
 """
 import copy
 
@@ -74,8 +80,7 @@ class _CtreeDriver:
         self.inverse_scalar_transform_handle = InverseScalarTransform(
             _get(model_cfg, "support_scale", 300), _get(self._cfg, "device", "cuda"),
             _get(model_cfg, "categorical_distribution", True))
-        if _get(self._cfg, "tie_break_seed") is not None:
-            api.set_tie_break(self._cfg.tie_break_seed, _get(self._cfg, "tie_break_mode", "per_root"))
+        self._search_ordinal = 0
 
     @classmethod
     def roots(cls, active_collect_env_num, legal_actions):
@@ -116,9 +121,26 @@ class _CtreeDriver:
         # device tensor that the kernels only read serves both env types.
         return _dev(to_play_batch, torch.int32, forest.device).reshape(-1)
 
+    def _stamp_tie_break(self, roots):
+        """This search's tie-break seed / keying on the roots object (see the module docstring)."""
+        if getattr(roots, "_tie_stamped", False):
+            return
+        cfg = self._cfg
+        base = _get(cfg, "tie_break_seed")
+        if _get(cfg, "tie_break_mode") is not None:
+            roots.tie_break_mode = api._mode_id(cfg.tie_break_mode)
+        if base is not None:
+            roots.tie_break_base = int(base)
+            advance = bool(_get(cfg, "tie_break_advance", False))
+            roots.tie_break_seed = api.derive_seed(base, self._search_ordinal) if advance else int(base)
+        self._search_ordinal += 1
+        roots._tie_stamped = True
+
     def _begin(self, roots, model, to_play_batch, num_simulations=0, max_considered=0):
         if hasattr(model, "eval"):
             model.eval()
+        self._stamp_tie_break(roots)
+        roots._cached_outputs = None  # whatever an earlier (graph) search left behind does not describe this one
         cfg = self._cfg
         N, S = roots.num, int(cfg.num_simulations)
         if isinstance(to_play_batch, int):
@@ -129,7 +151,7 @@ class _CtreeDriver:
         mm._bind(forest)
         scfg = api._search_cfg(forest, _get(cfg, "pb_c_base", 19652), _get(cfg, "pb_c_init", 1.25), cfg.discount_factor,
                                to_play_batch, num_simulations=num_simulations, max_considered=max_considered,
-                               players=getattr(roots, "_players", None))
+                               players=getattr(roots, "_players", None), roots=roots)
         return forest, scfg, self._to_play(to_play_batch, forest), api.ResultsWrapper(N), S
 
 
@@ -179,6 +201,7 @@ class _CtreeDriver:
         p = roots._prep
         if p is None:
             raise RuntimeError("Roots.prepare / prepare_no_noise must be called before search")
+        self._stamp_tie_break(roots)
         N, S, dev = roots.num, int(self._cfg.num_simulations), roots._device
         if isinstance(to_play_batch, int):
             to_play_batch = [to_play_batch] * N
@@ -191,9 +214,11 @@ class _CtreeDriver:
         sa = p.get("sampled_actions")  # sampled tree: the root action tables are one more prepared input
         key = (N, roots.action_space_size, S, tuple(lat0.shape), lat0.dtype, id(model), roots._legal is None,
                p["noise"] is None, players, None if hid is None else tuple(hid[0].shape), str(dev), k,
-               None if sa is None else tuple(sa.shape[1:]))
+               None if sa is None else tuple(sa.shape[1:]), roots.tie_break_mode)
         cache = self.__dict__.setdefault("_graphs", {})
         chunks = cache.get(key)
+        if chunks is not None and chunks[0].model_ref() is not model:
+            chunks = None  # id(model) was reused by a new object: the captured graph calls the old one
         if chunks is None:
             from ..sharding import shard_bounds
             chunks = []
@@ -201,7 +226,7 @@ class _CtreeDriver:
                 lo, hi = shard_bounds(N, k, c)
                 m = model.chunk(lo, hi) if (k > 1 and hasattr(model, "chunk")) else model
                 stream = torch.cuda.Stream(device=dev) if k > 1 else None
-                chunks.append(_SearchGraph(self, roots, m, lat0, hid, lo, hi, players, dev, stream))
+                chunks.append(_SearchGraph(self, roots, m, lat0, hid, lo, hi, players, dev, stream, roots_model=model))
             cache[key] = chunks
         main = torch.cuda.current_stream(dev)
         for g in chunks:
@@ -220,12 +245,19 @@ class _CtreeDriver:
 class _SearchGraph:
     """Static buffers + captured graph of one search shape for roots [lo, hi) (see _CtreeDriver._graphed)."""
 
-    def __init__(self, driver, roots, model, lat0, hid, lo, hi, players, dev, stream):
+    def __init__(self, driver, roots, model, lat0, hid, lo, hi, players, dev, stream, roots_model=None):
         from ..forest import legal_tensors
         p = roots._prep
         A = roots.action_space_size
         n = hi - lo
         self.driver, self.model, self.dev, self.lo, self.hi, self.stream = driver, model, dev, lo, hi, stream
+        import weakref
+        try:
+            self.model_ref = weakref.ref(roots_model) if roots_model is not None else (lambda: None)
+        except TypeError:  # objects without weak references: keep it alive instead
+            self.model_ref = (lambda m=roots_model: m)
+        # the tie-break seed is a device word rewritten before every replay (lzb_search_cfg_t::rng_seed_dev)
+        self.tie_seed_dev = torch.zeros(1, dtype=torch.int64, device=dev)
         keys = ("logits", "noise", "reward", "to_play", "value") + (("sampled_actions",) if "sampled_actions" in p else ())
         self.static = {k: (None if p[k] is None else torch.empty_like(p[k][lo:hi])) for k in keys}
         # sampled tree: the kernels read the sampler seed from this word, rewritten before every replay, so a replayed
@@ -251,6 +283,8 @@ class _SearchGraph:
         self.shadow._prep = dict(self.static, noise_weight=self.noise_weight)
         self.shadow._players = players if players else None
         self.shadow._seed_dev = self.seed_dev
+        self.shadow._tie_seed_dev = self.tie_seed_dev
+        self.shadow._tie_stamped = True  # the caller's roots carry this search's seed; _load copies it into the word
         self.graph = None
         self.outs = None
 
@@ -272,6 +306,8 @@ class _SearchGraph:
             for j, (d, s) in enumerate(zip(self.hid, hid)):
                 self._h2d(1 + j, d, s.reshape(roots.num, -1)[lo:hi])
         self.tp.copy_(to_play.reshape(-1)[lo:hi], non_blocking=True)
+        ts = int(roots.tie_break_seed) & 0xffffffffffffffff
+        self.tie_seed_dev.fill_(ts if ts < (1 << 63) else ts - (1 << 64))
         if self.seed_dev is not None:
             seed = int(getattr(roots, "sample_seed", None) or getattr(roots, "chance_seed", None) or 0) & 0xffffffffffffffff
             self.seed_dev.fill_(seed if seed < (1 << 63) else seed - (1 << 64))

@@ -49,7 +49,7 @@ class StochasticMuZeroMCTSCtree(_CtreeDriver):
         # every search draws its chance outcomes from its own stream: seed + number of searches this driver has run
         # (the reference seeds from std::random_device per draw, cnode.cpp:622-623); roots.chance_seed overrides
         if getattr(roots, "chance_seed", None) is None:
-            roots.chance_seed = api._tie_seed[0] + self._searches
+            roots.chance_seed = roots.tie_break_base + self._searches
         self._searches += 1
         if _get(self._cfg, "cuda_graph", False):
             if not _get(self._cfg, "stochastic_dense_inference", False):

@@ -116,9 +116,17 @@ def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=Fal
     return f
 
 
-def compare(sc, rng_mode=2, seed=2024, trees=4, fused=False, compact=False):
-    from oracle.binding import OracleForest
-    orc = OracleForest(sc.variant, sc.n, sc.A, sc.legal, K=sc.K, D=sc.D)
+def cpu_checker(sc, rng_mode, prefer_reference=False):
+    """The CPU side of a comparison: the plain-C oracle, or (prefer_reference, discrete trees) the compiled unmodified
+    reference tree from oracle/_ref when its library is there (it travels to the GPU box prebuilt)."""
+    from oracle.binding import OracleForest, RefForest, ref_available
+    if prefer_reference and sc.variant in ("mz", "ez", "gmz") and ref_available(sc.variant):
+        return RefForest(sc.variant, sc.n, sc.A, sc.legal, per_root=(rng_mode == 2))
+    return OracleForest(sc.variant, sc.n, sc.A, sc.legal, K=sc.K, D=sc.D)
+
+
+def compare(sc, rng_mode=2, seed=2024, trees=4, fused=False, compact=False, prefer_reference=False):
+    orc = cpu_checker(sc, rng_mode, prefer_reference)
     rec_c, rec_g = [], []
     run_cpu(orc, sc, rng_mode, seed, record=rec_c)
     gpu = run_gpu(sc, rng_mode, seed, record=rec_g, fused=fused, compact=compact)
