@@ -56,6 +56,10 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--nccl-exchange", action="store_true", help="end-of-search exchange through NCCL instead of the peer-memory kernel")
     ap.add_argument("--cpu-sample-roots", type=int, default=1024)
+    ap.add_argument("--categorical", action="store_true",
+                    help="the model emits CATEGORICAL value / reward heads ([N, 2 * support + 1] logits, every shipped Atari config) and "
+                         "the driver applies InverseScalarTransform every simulation (mcts_ctree.py:302-303) - the fused CUDA kernel")
+    ap.add_argument("--support", type=int, default=300, help="support_scale of the categorical heads (300 -> 601 bins)")
     return ap.parse_args()
 
 
@@ -72,7 +76,8 @@ def workload_config(a, world):
     how an arm ran it (graphs, streams, exchange, host CPU) goes to the line's `run` object."""
     return {"workload": workload_name(a), "roots_total": a.roots * world, "roots_per_gpu": a.roots, "sims": a.sims,
             "actions": a.actions, "latent_f32": a.latent, "model": "table lookup (no NN time)",
-            "scalar_transform": "identity"}
+            "scalar_transform": ("categorical heads, support %d (%d bins): InverseScalarTransform of value and reward every simulation"
+                                 % (a.support, 2 * a.support + 1)) if getattr(a, "categorical", False) else "identity"}
 
 
 # --------------------------------------------------------------------------------------------- synthetic inputs
@@ -99,6 +104,18 @@ def make_inputs(a, rank, device):
         D = a.action_dim
         head = lambda *shape: torch.cat([rn(*shape, D), rn(*shape, D).abs() * 0.5 + 0.1], dim=-1)
         inp["root_logits"], inp["logits"] = head(N), head(S, N)
+    if getattr(a, "categorical", False):
+        # categorical heads: N(0,1) logits over the support with one +8 bump per row at a bin drawn around the centre, so
+        # the expectations spread over a few tens of support units (2 x S x N x (2s+1) floats: ~2 GB at the headline shape)
+        Wb = 2 * a.support + 1
+
+        def head_table(spread):
+            t = rn(S, N, Wb)
+            centre = (rn(S, N) * spread).round().long().clamp(-a.support, a.support) + a.support
+            t.scatter_add_(2, centre.unsqueeze(2), torch.full((S, N, 1), 8.0, device=device))
+            return t
+
+        inp["value_logits"], inp["reward_logits"] = head_table(20.0), head_table(5.0)
     return inp
 
 
@@ -166,8 +183,9 @@ class TableModel:
     def chunk(self, lo, hi):
         """The same lookup restricted to roots [lo, hi) (a table is not a function of the latent it is handed)."""
         sub = dict(self.inp)
-        for k in ("logits", "value", "reward", "model_latent"):
-            sub[k] = self.inp[k][:, lo:hi]
+        for k in ("logits", "value", "reward", "model_latent", "value_logits", "reward_logits"):
+            if k in self.inp:
+                sub[k] = self.inp[k][:, lo:hi]
         m = TableModel.__new__(TableModel)
         m.inp, m.variant, m.s = sub, self.variant, 0
         m.A, m.C, m.calls_per_sim = self.A, self.C, self.calls_per_sim
@@ -183,6 +201,9 @@ class TableModel:
         if afterstate is not None:  # stochastic model: afterstate in -> policy logits [A]; latent in -> chance logits [C]
             o.policy_logits = o.policy_logits[:, :self.A if afterstate else self.C]
         o.reward = o.value_prefix = i["reward"][s].unsqueeze(1)
+        if "value_logits" in i:  # categorical heads: [N, 2 * support + 1] logits, transformed by the driver
+            o.value, o.reward = i["value_logits"][s], i["reward_logits"][s]
+            o.value_prefix = o.reward
         o.reward_hidden_state = getattr(self, "hidden", None)
         return o
 
@@ -217,9 +238,11 @@ def make_driver(a, device, graph, streams=None, tie_mode="per_root"):
                     value_delta_max=DELTA, device=str(device), cuda_graph=graph, tie_break_seed=TIE_SEED, tie_break_mode=tie_mode,
                     search_streams=(streams or a.streams) if graph else 1, stochastic_dense_inference=True,
                     lstm_horizon_len=5,
-                    model=dict(support_scale=300, categorical_distribution=False, continuous_action_space=a.variant == "sez",
+                    model=dict(support_scale=a.support, categorical_distribution=bool(a.categorical),
+                               continuous_action_space=a.variant == "sez",
                                action_space_size=a.action_dim if a.variant == "sez" else a.actions)))
-    mcts.inverse_scalar_transform_handle = lambda x: x  # the synthetic model emits scalars, not categorical supports
+    if not a.categorical:
+        mcts.inverse_scalar_transform_handle = lambda x: x  # the synthetic model emits scalars, not categorical supports
     return mcts
 
 
@@ -444,9 +467,14 @@ def parity_check(a, inp, model, device):
     torch.cuda.synchronize()
     h = lambda t: t.detach().cpu().numpy()
     n, S = a.roots, a.sims
+    value, reward = inp["value"], inp["reward"]
+    if a.categorical:  # the tree is compared, not the transform (tests/test_scaling.py pins that): the reference gets the
+        pairs = [mcts.inverse_scalar_transform_handle.pair(inp["value_logits"][s], inp["reward_logits"][s]) for s in range(S)]
+        value = torch.stack([v.reshape(-1) for v, _ in pairs])   # scalars the CUDA search consumed, simulation by simulation
+        reward = torch.stack([r.reshape(-1) for _, r in pairs])
     d = dict(root_logits=h(inp["root_logits"]), root_reward=h(inp["root_reward"]), root_value=h(inp["root_value"]),
-             noises=list(h(inp["noise"])), to_play=h(inp["to_play"]), logits=h(inp["logits"]), reward=h(inp["reward"]),
-             value=h(inp["value"]), latent_roots=np.zeros((n, 1), np.float32), model_latent=np.zeros((S, n, 1), np.float32))
+             noises=list(h(inp["noise"])), to_play=h(inp["to_play"]), logits=h(inp["logits"]), reward=h(reward),
+             value=h(value), latent_roots=np.zeros((n, 1), np.float32), model_latent=np.zeros((S, n, 1), np.float32))
     dt, kind, dist, vals = cpu_search(a, d, rng_mode=1, want_values=True)
     gv, gx = h(visits), h(values)
     dist = np.where(dist < 0, 0, dist)
@@ -690,6 +718,29 @@ def run_b200_arm(a):
         torch.cuda.synchronize()
     timer.remove()
     per_kernel = timer.summary()
+    transform = None
+    if a.categorical:
+        # the scalar-transform kernel alone: S launches back to back over the S distinct (HBM-cold) table rows, one event
+        # pair around them.  In the eager pass above a transform launch sits between every two step launches, so that
+        # pass's "step" figure is step + transform; the transform's own time is taken off it here.
+        handle = eager.inverse_scalar_transform_handle
+        for rep in range(3):
+            flush.fill_(1)
+            torch.cuda._sleep(int(3e7))
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record()
+            for s_ in range(S):
+                handle.pair(inp["value_logits"][s_], inp["reward_logits"][s_])
+            t1.record()
+            torch.cuda.synchronize()
+            us = 1e3 * t0.elapsed_time(t1) / S
+            transform = us if transform is None else min(transform, us)
+        per_kernel["step"] = [max(x - transform * 1e-3, 1e-6) for x in per_kernel["step"]]
+        tbytes = 2 * N * (2 * a.support + 1) * 4 + 2 * N * 4
+        transform = {"kernel": "k_inverse_scalar_transform (value + reward heads, one launch per simulation)",
+                     "avg_launch_us": round(transform, 2), "algorithmic_bytes_per_launch": tbytes,
+                     "achieved": round(tbytes / (transform * 1e-6) / 1e9, 1), "unit": "GB/s",
+                     "note": "the step figure of this line is the eager per-simulation time minus this kernel's"}
 
     # ---- reduce over ranks (max time), print on rank 0
     t = torch.tensor([dev_ms, e2e_ms or 0.0], dtype=torch.float64, device=device)
@@ -717,12 +768,16 @@ def run_b200_arm(a):
                     "exchange_ms_per_step": round(exchange_ms, 4)},
             # init, minmax, prepare, root slots, select, S-1 steps, backup, outputs (+ the exchange kernel when sharded)
             "gpu_launches": a.steps * ((5 + S + 1) * (1 if a.no_graph else a.streams) + (1 if peer is not None else 0)
-                                       + (S + 1 if a.variant == "sez" else 0)),  # + one action-sampling kernel per expansion
+                                       + (S + 1 if a.variant == "sez" else 0)   # + one action-sampling kernel per expansion
+                                       + (S * (2 if a.variant == "smz" else 1) * (1 if a.no_graph else a.streams) if a.categorical else 0)),  # + the scalar-transform kernel
             "clocks": clk,
             "roofline": roofline(a, per_kernel, depth, peak, src),
         }
         if exchange_check is not None:
             line["exchange_check"] = exchange_check
+        if transform is not None:
+            transform["frac"] = round(transform["achieved"] / peak, 4)
+            line["roofline"]["scalar_transform"] = transform
         if e2e_ms is not None:
             line["e2e"] = {"value": round(total_sims / (e2e_tot / a.steps * 1e-3), 1), "unit": "simulations/s",
                            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),

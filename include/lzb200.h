@@ -284,6 +284,24 @@ int lzb_sample_actions_seeded(const float *logits_dev, const float *uniforms_dev
                               int num_sampled, int action_dim, int action_space, int continuous, int root_offset,
                               uint64_t seed, const uint64_t *seed_dev, uint32_t counter, void *stream);
 
+/* ---- InverseScalarTransform of the model's categorical heads (lzero/policy/scaling_transform.py:97-128 with ensure_softmax
+ * :36-62), applied by the reference driver to value and reward / value_prefix every simulation (mcts_ctree.py:302-303;
+ * :797-798 EfficientZero): logits [N, 2 * support_size + 1] over the support {-s .. s} -> softmax (unless EVERY row of
+ * the head already sums to 1 within torch.allclose's atol = rtol = 1e-5, then the rows are taken as probabilities) ->
+ * expectation -> h^-1 with `epsilon` -> scalar_dev [N], the tensor lzb_backprop / lzb_step take as value_dev / reward_dev.
+ * Up to two heads per launch; every logit is read once.  row_stride: floats between rows (>= 2 * support_size + 1).
+ * workspace_dev: lzb_scalar_workspace_bytes(n_heads, num_rows) bytes, 16-byte aligned, ZEROED once before its first use
+ * (the call leaves it ready for the next one); one workspace serves one stream at a time.
+ * Not bit-pinned (torch fixes no summation order): agrees with the reference class to 1e-5 relative. */
+typedef struct {
+    const float *logits_dev;
+    int64_t row_stride;
+    float *scalar_dev;
+} lzb_support_head_t;
+int lzb_scalar_workspace_bytes(int n_heads, int num_rows, size_t *bytes);
+int lzb_inverse_scalar_transform(const lzb_support_head_t *heads, int n_heads, int num_rows, int support_size, float epsilon,
+                                 void *workspace_dev, void *stream);
+
 /* ---- Root-batch prologue / epilogue (what the callers of search() do per root in Python) ---- */
 
 /* legal_actions = [a for a, x in enumerate(action_mask[j]) if x == 1] (lzero/policy/muzero.py:671;

@@ -12,7 +12,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "liblzb200.so")
 ABI_VERSION = 5  # LZB_ABI_VERSION of include/lzb200.h
-SOURCES = ["lzb_api.cu", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_group.cuh", "lzb_sample.cuh", "lzb_collect.cuh", "lzb_peer.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
+SOURCES = ["lzb_api.cu", "lzb_scaling.cuh", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_group.cuh", "lzb_sample.cuh", "lzb_collect.cuh", "lzb_peer.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",  # B200 only
@@ -30,20 +30,39 @@ def _stale():
 
 
 def build(force=False, verbose=False):
-    """Compile lightzero_b200/csrc/lzb_api.cu for sm_100a into lightzero_b200/liblzb200.so."""
+    """Compile lightzero_b200/csrc/lzb_api.cu for sm_100a into lightzero_b200/liblzb200.so.
+
+    One process per GPU may get here at the same time (torchrun, bench.py --gpus 8) with a stale or missing library:
+    the build runs under an exclusive file lock, compiles to a temporary file in the same directory and renames it
+    into place, so no rank ever maps a half-written library and only the first rank compiles."""
     if not force and not _stale():
         return LIB_PATH
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
         if os.path.exists(LIB_PATH):
+            import warnings
+            warnings.warn("lightzero_b200: sources are newer than %s but nvcc is not available; loading the existing "
+                          "library (the ABI version is still checked)" % LIB_PATH)
             return LIB_PATH
         raise RuntimeError("nvcc not found and %s is not built" % LIB_PATH)
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [os.path.join(CSRC, "lzb_api.cu"), "-o", LIB_PATH]
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n%s\n%s" % (res.stdout, res.stderr))
-    if verbose:
-        print(res.stderr)
+    import fcntl
+    with open(LIB_PATH + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not _stale():  # another rank built it while this one waited for the lock
+                return LIB_PATH
+            tmp = "%s.tmp.%d" % (LIB_PATH, os.getpid())
+            cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + [os.path.join(CSRC, "lzb_api.cu"), "-o", tmp]
+            res = subprocess.run(cmd, capture_output=True, text=True)
+            if res.returncode != 0:
+                if os.path.exists(tmp):
+                    os.unlink(tmp)
+                raise RuntimeError("nvcc failed:\n%s\n%s" % (res.stdout, res.stderr))
+            os.replace(tmp, LIB_PATH)
+            if verbose:
+                print(res.stderr)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     pylist()
     return LIB_PATH
 
@@ -119,6 +138,11 @@ class SelectAction(C.Structure):
                 ("seed", C.c_uint64), ("counter", C.c_uint32)]
 
 
+class SupportHead(C.Structure):
+    """lzb_support_head_t"""
+    _fields_ = [("logits_dev", C.c_void_p), ("row_stride", C.c_int64), ("scalar_dev", C.c_void_p)]
+
+
 class TraverseIO(C.Structure):
     """lzb_traverse_io_t"""
     _fields_ = [("to_play_dev", C.c_void_p), ("ix_dev", C.c_void_p), ("iy_dev", C.c_void_p),
@@ -173,6 +197,8 @@ _PROTOS = {
     "lzb_dirichlet_noise": (C.c_int, [C.c_float, _P, _P, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint32, _P]),
     "lzb_select_action": (C.c_int, [C.POINTER(SelectAction), _P]),
     "lzb_target_policies": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
+    "lzb_scalar_workspace_bytes": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
+    "lzb_inverse_scalar_transform": (C.c_int, [C.POINTER(SupportHead), C.c_int, C.c_int, C.c_int, C.c_float, _P, _P]),
     "lzb_peer_bytes": (C.c_int, [C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_size_t)]),
     "lzb_peer_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
     "lzb_peer_free": (C.c_int, [_P]),
@@ -195,7 +221,12 @@ def lib():
     """The loaded library with prototypes declared; builds it first when the sources are newer."""
     global _lib
     if _lib is None:
-        path = os.environ.get("LZB200_LIB") or build()  # LZB200_LIB: tuning hook, load another build of the library
+        path = os.environ.get("LZB200_LIB")  # tuning hook (A/B and timeline builds): load another build of the library
+        if path:
+            import sys
+            print("lightzero_b200: LZB200_LIB is set - loading %s instead of %s" % (path, LIB_PATH), file=sys.stderr)
+        else:
+            path = build()
         L = C.CDLL(path)
         for name, (res, args) in _PROTOS.items():
             fn = getattr(L, name)  # AttributeError here == header and library disagree

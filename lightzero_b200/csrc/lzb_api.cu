@@ -12,6 +12,7 @@
 #include "lzb_sample.cuh"
 #include "lzb_collect.cuh"
 #include "lzb_peer.cuh"
+#include "lzb_scaling.cuh"
 #include "lzb_step.cuh"
 
 using namespace lzb;
@@ -557,19 +558,42 @@ enum { kSelect = 0, kBackup = 1, kStep = 2 };
 template <int VAR, int G, int R, bool REUSE>
 void launch_group(int which, const Pool &p, const BackupArgs *b, const SelectArgs *a, cudaStream_t st)
 {
-    const int per_block = 128 / G;
+    const int per_block = 4 * (32 / G); // four warps of 32 / G trees (lzb_group.cuh: group_tree)
     // programmatic dependent launch: the kernel may be scheduled while its predecessor drains; it reads nothing
     // before its griddepcontrol.wait (LZB_NO_PDL=1 launches it the ordinary way)
     static const bool pdl = getenv("LZB_NO_PDL") == nullptr;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int n_attr = 0;
+    if (pdl) {
+        attr[n_attr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[n_attr].val.programmaticStreamSerializationAllowed = 1;
+        n_attr += 1;
+    }
+    // experiment (LZB_L2_PERSIST_MB=<MB>, default off): the node pool as a persisting L2 window, so that the 2 x 4 KB of
+    // leaf rows per tree streamed through L2 every step do not evict the blocks the next step walks
+    static const long long persist_mb = getenv("LZB_L2_PERSIST_MB") ? atoll(getenv("LZB_L2_PERSIST_MB")) : 0;
+    if (persist_mb > 0) {
+        static bool limit_set = false;
+        if (!limit_set) { cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)persist_mb << 20); limit_set = true; }
+        int max_win = 0, dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+        const size_t pool_bytes = (size_t)p.N * p.E * p.B * sizeof(int4);
+        const size_t win = std::min(pool_bytes, (size_t)max_win);
+        attr[n_attr].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[n_attr].val.accessPolicyWindow.base_ptr = (void *)p.node;
+        attr[n_attr].val.accessPolicyWindow.num_bytes = win;
+        attr[n_attr].val.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)((size_t)persist_mb << 20) / (double)win);
+        attr[n_attr].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[n_attr].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        n_attr += 1;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((p.N + per_block - 1) / per_block);
     cfg.blockDim = dim3(128);
     cfg.stream = st;
     cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
+    cfg.numAttrs = n_attr;
     if (which == kSelect) cudaLaunchKernelEx(&cfg, k_select_g<VAR, G, R, REUSE>, p, *a);
     else if (which == kBackup) cudaLaunchKernelEx(&cfg, k_expand_backup_g<VAR, G, R, REUSE>, p, *b);
     else cudaLaunchKernelEx(&cfg, k_step_g<VAR, G, R, REUSE>, p, *b, *a);
@@ -582,14 +606,21 @@ template <int VAR, bool REUSE>
 bool launch_group_for(int which, const Pool &p, const BackupArgs *b, const SelectArgs *a, cudaStream_t st)
 {
     const int A = p.A;
-    static const int forced = getenv("LZB_GROUP_LANES") ? atoi(getenv("LZB_GROUP_LANES")) : 0; // tuning hook: 8, 16 or 32
+    // tuning hook: 8, 10, 16 or 32 lanes per tree (LZB_GROUP_LANES=0 / unset: chosen below)
+    static const int forced = getenv("LZB_GROUP_LANES") ? atoi(getenv("LZB_GROUP_LANES")) : 0;
     const long long one_wave = 148LL * 28; // warps: __launch_bounds__(128, 7) keeps 7 blocks of 4 warps resident per SM
-    auto fits = [&](int G) { return forced ? forced == G : ((long long)p.N * G + 31) / 32 <= one_wave; };
+    auto fits = [&](int G) { return forced ? forced == G : ((long long)p.N + (32 / G) - 1) / (32 / G) <= one_wave; };
     if (A <= 8) {
         launch_group<VAR, 8, 1, REUSE>(which, p, b, a, st);
+    } else if (A <= 10 && forced == 10) {
+        launch_group<VAR, 10, 1, REUSE>(which, p, b, a, st); // experiment: three trees per warp
     } else if (A <= 16) {
         if (fits(16)) launch_group<VAR, 16, 1, REUSE>(which, p, b, a, st);
         else launch_group<VAR, 8, 2, REUSE>(which, p, b, a, st);
+    } else if (A <= 20 && forced == 10) {
+        // experiment (round 2, measured and rejected as a default: 22.4 vs 17.4 us per step at 8192 x A=18):
+        // 10 lanes x 2 records = the chain of 16 x 2 with two thirds of the warps, three trees per warp
+        launch_group<VAR, 10, 2, REUSE>(which, p, b, a, st);
     } else if (A <= 24) {
         if (fits(32)) launch_group<VAR, 32, 1, REUSE>(which, p, b, a, st);
         else if (fits(16)) launch_group<VAR, 16, 2, REUSE>(which, p, b, a, st);
@@ -891,6 +922,40 @@ int lzb_target_policies(const int32_t *visits_dev, const int32_t *legal_count_de
     if (!visits_dev || !policy_dev || num_roots <= 0 || action_space <= 0) return fail(LZB_E_ARG, "target_policies: bad argument");
     k_target_policies<<<(num_roots + 3) / 4, 128, 0, (cudaStream_t)stream>>>(visits_dev, legal_count_dev, legal_actions_dev, policy_mask_dev,
                                                                              num_roots, action_space, policy_dev);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_scalar_workspace_bytes(int n_heads, int num_rows, size_t *bytes)
+{
+    if (!bytes || n_heads <= 0 || n_heads > kMaxScalarHeads || num_rows <= 0) return fail(LZB_E_ARG, "scalar_workspace_bytes: 1..%d heads, num_rows > 0", kMaxScalarHeads);
+    *bytes = 16 + (size_t)n_heads * (size_t)num_rows * sizeof(float);
+    return LZB_OK;
+}
+
+int lzb_inverse_scalar_transform(const lzb_support_head_t *heads, int n_heads, int num_rows, int support_size, float epsilon,
+                                 void *workspace_dev, void *stream)
+{
+    if (!heads || n_heads <= 0 || n_heads > kMaxScalarHeads || num_rows <= 0 || support_size <= 0 || !workspace_dev)
+        return fail(LZB_E_ARG, "inverse_scalar_transform: 1..%d heads, num_rows > 0, support_size > 0, workspace required", kMaxScalarHeads);
+    if (((uintptr_t)workspace_dev & 15) != 0) return fail(LZB_E_ARG, "inverse_scalar_transform: workspace must be 16-byte aligned");
+    if (!(epsilon > 0.0f)) return fail(LZB_E_ARG, "inverse_scalar_transform: epsilon must be positive");
+    const int W = 2 * support_size + 1;
+    ScalarHeads a = {};
+    for (int h = 0; h < n_heads; ++h) {
+        if (!heads[h].logits_dev || !heads[h].scalar_dev || heads[h].row_stride < W)
+            return fail(LZB_E_ARG, "inverse_scalar_transform: head %d has a NULL pointer or a row stride below %d", h, W);
+        a.logits[h] = heads[h].logits_dev; a.out[h] = heads[h].scalar_dev; a.stride[h] = heads[h].row_stride;
+    }
+    a.n_heads = n_heads; a.N = num_rows; a.support = support_size; a.eps = epsilon;
+    a.ctl = (unsigned *)workspace_dev; a.raw = (float *)((char *)workspace_dev + 16);
+    const long long rows = (long long)n_heads * num_rows;
+    const int blocks = (int)std::min<long long>((rows + 7) / 8, 148LL * 8); // 8 warps per block, one wave of 8 blocks per SM
+    cudaStream_t st = (cudaStream_t)stream;
+    if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, 256, 0, st>>>(a);
+    else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, 256, 0, st>>>(a);
+    else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, 256, 0, st>>>(a); // support 300: 601 logits per row
+    else k_inverse_scalar_transform<0><<<blocks, 256, 0, st>>>(a);
     LZB_CUDA(cudaGetLastError());
     return LZB_OK;
 }

@@ -25,14 +25,20 @@ namespace lzb {
 // finished (reached its leaf, or has no tree) keeps executing with its writes predicated off.  Sub-warp member
 // masks would let groups diverge, but the compiler then wraps every shuffle in a convergence protocol
 // (WARPSYNC.COLLECTIVE / REDUX / BSSY...BSYNC) that more than doubled the instruction count when measured.
+// G need not be a power of two: 10-lane groups put THREE trees into a warp (lanes 30, 31 idle) and serve action
+// spaces up to 10 (R = 1) / 20 (R = 2) with the same chain length as 16-lane groups but two thirds of the warps.
+// Power-of-two groups exchange with shuffles of width G and butterfly reductions; the others address the source lane
+// absolutely (first lane of the group + index) and reduce over a ring (offsets 1, 2, 4, 8: windows double, and for the
+// idempotent max / min an overlapping last window is harmless).
 template <int G>
 struct Grp {
+    static constexpr bool kPow2 = (G & (G - 1)) == 0;
     int lane;  // 0 .. G-1 within the group
     int shift; // first warp lane of the group
     __device__ __forceinline__ Grp()
     {
         const int wl = threadIdx.x & 31;
-        lane = wl & (G - 1);
+        lane = kPow2 ? (wl & (G - 1)) : (wl % G);
         shift = wl - lane;
     }
     __device__ __forceinline__ unsigned ballot(bool pred) const
@@ -40,9 +46,21 @@ struct Grp {
         const unsigned m = __ballot_sync(kFull, pred) >> shift;
         return (G == 32) ? m : (m & ((1u << (G & 31)) - 1u));
     }
-    __device__ __forceinline__ float shfl(float v, int src) const { return __shfl_sync(kFull, v, src, G); }
-    __device__ __forceinline__ int shfl(int v, int src) const { return __shfl_sync(kFull, v, src, G); }
-    __device__ __forceinline__ double shfl(double v, int src) const { return __shfl_sync(kFull, v, src, G); }
+    // lane of the warp that holds group member (lane + o) mod G
+    __device__ __forceinline__ int ring(int o) const
+    {
+        const int t = lane + o;
+        return shift + (t >= G ? t - G : t);
+    }
+    template <typename T>
+    __device__ __forceinline__ T shfl_(T v, int src) const
+    {
+        if constexpr (kPow2) return __shfl_sync(kFull, v, src, G);
+        else return __shfl_sync(kFull, v, shift + src);
+    }
+    __device__ __forceinline__ float shfl(float v, int src) const { return shfl_(v, src); }
+    __device__ __forceinline__ int shfl(int v, int src) const { return shfl_(v, src); }
+    __device__ __forceinline__ double shfl(double v, int src) const { return shfl_(v, src); }
     __device__ __forceinline__ int4 shfl(int4 v, int src) const
     {
         return make_int4(shfl(v.x, src), shfl(v.y, src), shfl(v.z, src), shfl(v.w, src));
@@ -61,29 +79,68 @@ struct Grp {
     }
     __device__ __forceinline__ float fmax(float v) const
     {
+        if constexpr (kPow2) {
 #pragma unroll
-        for (int o = G / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o, G));
+            for (int o = G / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o, G));
+        } else {
+#pragma unroll
+            for (int o = 1; o < G; o <<= 1) v = fmaxf(v, __shfl_sync(kFull, v, ring(o)));
+        }
         return v;
     }
     __device__ __forceinline__ float fmin(float v) const
     {
+        if constexpr (kPow2) {
 #pragma unroll
-        for (int o = G / 2; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(kFull, v, o, G));
+            for (int o = G / 2; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(kFull, v, o, G));
+        } else {
+#pragma unroll
+            for (int o = 1; o < G; o <<= 1) v = fminf(v, __shfl_sync(kFull, v, ring(o)));
+        }
         return v;
     }
     __device__ __forceinline__ int isum(int v) const
     {
+        if constexpr (kPow2) {
 #pragma unroll
-        for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o, G);
-        return v;
+            for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o, G);
+            return v;
+        } else { // exact ring windows: w[k] = sum over 2^k members from this lane on; G = sum of its binary digits' windows
+            int total = 0, at = 0, w = v;
+#pragma unroll
+            for (int o = 1; o <= G; o <<= 1) {
+                if (G & o) { // take the window of o members that starts `at` members further on
+                    total += (at == 0) ? w : __shfl_sync(kFull, w, ring(at));
+                    at += o;
+                }
+                if ((o << 1) <= G) w += __shfl_sync(kFull, w, ring(o));
+            }
+            return total;
+        }
     }
     __device__ __forceinline__ int imax(int v) const
     {
+        if constexpr (kPow2) {
 #pragma unroll
-        for (int o = G / 2; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(kFull, v, o, G));
+            for (int o = G / 2; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(kFull, v, o, G));
+        } else {
+#pragma unroll
+            for (int o = 1; o < G; o <<= 1) v = max(v, __shfl_sync(kFull, v, ring(o)));
+        }
         return v;
     }
 };
+
+// tree handled by this thread's lane group: (32 / G) trees per warp, four warps per block; lanes of a warp beyond the
+// last whole group (G = 10: lanes 30, 31) form a group without a tree
+template <int G>
+__device__ __forceinline__ int group_tree(bool &has_tree)
+{
+    constexpr int kPerWarp = 32 / G;
+    const int g = (threadIdx.x & 31) / G;
+    has_tree = g < kPerWarp;
+    return (blockIdx.x * 4 + (threadIdx.x >> 5)) * kPerWarp + g;
+}
 
 // Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-serialization attribute may start
 // while its predecessor in the stream drains; pdl_wait() is the point past which the predecessor's writes are visible
@@ -224,6 +281,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     const float g = a.discount;
     const float mm_delta = mm.y - mm.x;
     const float mm_den = (mm_delta < a.delta) ? a.delta : mm_delta; // CMinMaxStats::normalize (cminimax.cpp:33-45)
+    const float mm_safe = (mm_delta > 0) ? mm_den : 1.0f;            // the divisor every lane can divide by
     const unsigned hroot = (a.rng_mode == LZB_RNG_PER_ROOT) ? (unsigned)(p.root_offset + i) : 0u;
 
     int parent_visits = rt.x;
@@ -280,7 +338,12 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             val[r] = 0.0f;
             const unsigned wvis = __ballot_sync(kFull, vis);
             if (wvis) { // warp-uniform: slices without a visited child in any group add nothing
+#ifdef LZB_X_BRANCHY_DIV // round-1 form: the compiler branches around the division (BSSY / divergent BRA per slice)
                 val[r] = vis ? __int_as_float(c[r].y) / (float)vc : 0.0f; // CNode::value()
+#else // every lane divides (by 1 where there is nothing to divide) and selects: no divergent branch on the chain
+                const float vq = __int_as_float(c[r].y) / (float)max(vc, 1);
+                val[r] = vis ? vq : 0.0f; // CNode::value()
+#endif
                 const float qsa = vis ? tr[r] + g * val[r] : 0.0f;
                 nvis += __popc((wvis >> grp.shift) & ((G == 32) ? 0xffffffffu : ((1u << (G & 31)) - 1u)));
                 // j = l + G*r ascending; +0.0f for the rest is exact; the last slice stops at the action space
@@ -319,7 +382,12 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             float vs;
             if (vc == 0) vs = mean_q;
             else vs = (players == 1) ? tr[r] + g * cv : tr[r] + g * (-cv);
+#ifdef LZB_X_BRANCHY_DIV
             if (mm_delta > 0) vs = (vs - mm.x) / mm_den;
+#else
+            const float vn = (vs - mm.x) / mm_safe; // CMinMaxStats::normalize; discarded while the bounds are unset
+            vs = (mm_delta > 0) ? vn : vs;
+#endif
             if (vs < 0) vs = 0;
             if (vs > 1) vs = 1;
             sc[r] = (j < n) ? (arm ? vs : prior_score + vs) : -INFINITY;
@@ -369,7 +437,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         level += 1;
 
         // ---- the chosen child's record lives in lane newpos % G, register newpos / G
-        const int rsel = newpos / G;
+        const int rsel = newpos / G, lsel = newpos - rsel * G;
         int4 mine = c[0];
         bool mine_true = REUSE && is_true[0];
 #pragma unroll
@@ -381,13 +449,13 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         }
         bool chose_true = false; // cnode.cpp:895-898
         if (REUSE) { // the shuffle is executed by every lane (no short-circuit around a full-mask exchange)
-            const int sel_true = grp.shfl((int)mine_true, newpos & (G - 1));
+            const int sel_true = grp.shfl((int)mine_true, lsel);
             chose_true = is_root && sel_true != 0;
         }
         int4 ch; // the prior (z) of the chosen child is not needed below
-        ch.x = grp.shfl(mine.x, newpos & (G - 1));
-        ch.y = grp.shfl(mine.y, newpos & (G - 1));
-        ch.w = grp.shfl(mine.w, newpos & (G - 1));
+        ch.x = grp.shfl(mine.x, lsel);
+        ch.y = grp.shfl(mine.y, lsel);
+        ch.w = grp.shfl(mine.w, lsel);
         ch.z = 0;
         if (going) {
             pos = newpos;
@@ -627,7 +695,7 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
         }
 
         // ---- the chosen child's record lives in lane newpos % G, register newpos / G
-        const int rsel = newpos / G;
+        const int rsel = newpos / G, lsel = newpos - rsel * G;
         int4 mine = c[0];
 #pragma unroll
         for (int r = 1; r < R; ++r) {
@@ -636,9 +704,9 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
             mine.w = (rsel == r) ? c[r].w : mine.w;
         }
         int4 ch;
-        ch.x = grp.shfl(mine.x, newpos & (G - 1));
-        ch.y = grp.shfl(mine.y, newpos & (G - 1));
-        ch.w = grp.shfl(mine.w, newpos & (G - 1));
+        ch.x = grp.shfl(mine.x, lsel);
+        ch.y = grp.shfl(mine.y, lsel);
+        ch.w = grp.shfl(mine.w, lsel);
         ch.z = 0;
         if (going) {
             pos = newpos;
@@ -845,13 +913,15 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 }
 
 // ---------------------------------------------------------------------------------------------- kernels
-// 128 threads = 128 / G trees per block; groups without a tree (tail of the last block) run along on tree 0, muted
+// 128 threads = 4 * (32 / G) trees per block; groups without a tree (tail of the last block, spare lanes of a warp) run
+// along on tree 0, muted
 template <int VAR, int G, int R, bool REUSE>
 __global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_select_g(Pool p, SelectArgs a)
 {
     const Grp<G> grp;
-    const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
-    const bool live = i < p.N;
+    bool has_tree;
+    const int i = group_tree<G>(has_tree);
+    const bool live = has_tree && i < p.N;
     pdl_wait();
     if constexpr (VAR == LZB_GMZ) select_gumbel_g<G, R>(p, a, live ? i : 0, live, grp);
     else select_puct_g<VAR, G, R, REUSE>(p, a, live ? i : 0, live, grp);
@@ -861,8 +931,9 @@ template <int VAR, int G, int R, bool REUSE>
 __global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_expand_backup_g(Pool p, BackupArgs b)
 {
     const Grp<G> grp;
-    const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
-    bool live = i < p.N;
+    bool has_tree;
+    const int i = group_tree<G>(has_tree);
+    bool live = has_tree && i < p.N;
     pdl_wait();
     if (b.active && live) live = b.active[i] != 0; // smz leaf_idx_list: the other trees are not touched by this call
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
@@ -875,8 +946,9 @@ template <int VAR, int G, int R, bool REUSE>
 __global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_step_g(Pool p, BackupArgs b, SelectArgs a)
 {
     const Grp<G> grp;
-    const int i = blockIdx.x * (128 / G) + (threadIdx.x / G);
-    const bool live = i < p.N;
+    bool has_tree;
+    const int i = group_tree<G>(has_tree);
+    const bool live = has_tree && i < p.N;
 #ifdef LZB_TIMELINE
     const int tl = b.latent_index;
 #else

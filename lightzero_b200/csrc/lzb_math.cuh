@@ -13,7 +13,19 @@
 
 namespace lzb {
 
-__device__ __constant__ uint64_t kExpTab[32] = {
+// The two lookup tables are indexed by a DIFFERENT entry in every lane.  In __constant__ memory such a load (LDC with a
+// register index) is replayed once per distinct address in the warp - up to 18 replays per expf of a softmax over 18
+// logits; as ordinary global memory read through the read-only path (LDG.CONSTANT) the 256 bytes are two cache lines
+// and a warp's lookups are one or two L1 hits.  -DLZB_TABLES_IN_CONSTANT restores the round-1 placement for A/B runs.
+#ifdef LZB_TABLES_IN_CONSTANT
+#define LZB_TABLE __device__ __constant__
+#define LZB_TABLE_AT(tab, i) (tab[i])
+#else
+#define LZB_TABLE __device__
+#define LZB_TABLE_AT(tab, i) __ldg(&tab[i])
+#endif
+
+LZB_TABLE uint64_t kExpTab[32] = {
     0x3ff0000000000000ULL, 0x3fefd9b0d3158574ULL, 0x3fefb5586cf9890fULL, 0x3fef9301d0125b51ULL,
     0x3fef72b83c7d517bULL, 0x3fef54873168b9aaULL, 0x3fef387a6e756238ULL, 0x3fef1e9df51fdee1ULL,
     0x3fef06fe0a31b715ULL, 0x3feef1a7373aa9cbULL, 0x3feedea64c123422ULL, 0x3feece086061892dULL,
@@ -25,7 +37,7 @@ __device__ __constant__ uint64_t kExpTab[32] = {
 };
 
 // {1/c, log c} pairs of glibc's __logf_data
-__device__ __constant__ double kLogTab[32] = {
+LZB_TABLE double kLogTab[32] = {
     0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2, 0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2,
     0x1.49539f0f010bp+0,  -0x1.01eae7f513a67p-2, 0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3,
     0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3, 0x1.25e227b0b8eap+0,  -0x1.1aa2bc79c81p-3,
@@ -53,7 +65,7 @@ __device__ __forceinline__ float glibc_expf(float x)
     const uint64_t ki = (uint64_t)__double_as_longlong(kd);
     kd = __dsub_rn(kd, 0x1.8p+52);
     const double r = fma(0x1.71547652b82fep+5, xd, -kd);
-    const double s = __longlong_as_double((long long)(kExpTab[ki & 31u] + (ki << 47)));
+    const double s = __longlong_as_double((long long)(LZB_TABLE_AT(kExpTab, ki & 31u) + (ki << 47)));
     const double z = fma(0x1.c6af84b912394p-20, r, 0x1.ebfce50fac4f3p-13);
     const double r2 = __dmul_rn(r, r);
     double y = fma(0x1.62e42ff0c52d6p-6, r, 1.0);
@@ -78,7 +90,7 @@ __device__ __forceinline__ float glibc_logf(float x)
     const int i = (int)((tmp >> 19) & 15u);
     const int k = (int)tmp >> 23;
     const uint32_t iz = ix - (tmp & 0xff800000u);
-    const double invc = kLogTab[2 * i], logc = kLogTab[2 * i + 1];
+    const double invc = LZB_TABLE_AT(kLogTab, 2 * i), logc = LZB_TABLE_AT(kLogTab, 2 * i + 1);
     const double z = (double)__uint_as_float(iz);
     const double r = fma(z, invc, -1.0);
     const double y0 = fma((double)k, 0x1.62e42fefa39efp-1, logc);

@@ -88,6 +88,15 @@ class _CtreeDriver:
         return cls.tree.Roots(active_collect_env_num, legal_actions)
 
     # ------------------------------------------------------------------ pieces of the loop
+    def _scalars(self, value_head, reward_head):
+        """inverse_scalar_transform_handle of the value and the reward / value_prefix head (mcts_ctree.py:302-303): one
+        fused launch for both when the handle is the device transform, else the handle twice (a caller may replace it)."""
+        h = self.inverse_scalar_transform_handle
+        pair = getattr(h, "pair", None)
+        if pair is not None:
+            return pair(value_head, reward_head)
+        return h(value_head), h(reward_head)
+
     @staticmethod
     def _on_device(forest, x):
         """Root latents / hidden states as one contiguous device tensor (one H2D copy when they come from the host)."""
@@ -432,8 +441,7 @@ class MuZeroMCTSCtree(_CtreeDriver):
                 # stage 2: expansion inputs from the model, still on the device (mcts_ctree.py:298-303);
                 # Gumbel MuZero passes the action as [N, 1] (:1090)
                 net = model.recurrent_inference(leaf, o["last_action"].unsqueeze(1) if self.gumbel else o["last_action"])
-                value = self.inverse_scalar_transform_handle(net.value)
-                reward = self.inverse_scalar_transform_handle(net.reward)
+                value, reward = self._scalars(net.value, net.reward)
                 new_lat = self._slot_tensor(net.latent_state, leaf)
                 e = simulation_index + 1
                 if e < S:
@@ -457,8 +465,7 @@ class MuZeroMCTSCtree(_CtreeDriver):
             o = api.traverse_tensors(roots, scfg, tp, results, out=o)
             leaf = pool[o["ix"].long(), o["iy"].long()]
             net = model.recurrent_inference(leaf, o["last_action"].unsqueeze(1) if self.gumbel else o["last_action"])
-            value = self.inverse_scalar_transform_handle(net.value)
-            reward = self.inverse_scalar_transform_handle(net.reward)
+            value, reward = self._scalars(net.value, net.reward)
             pool[simulation_index + 1].copy_(net.latent_state.reshape(lat0.shape))
             api.backprop_tensors(results, simulation_index + 1, discount, reward, value, net.policy_logits, o["vtp"])
 
@@ -499,8 +506,7 @@ class UniZeroMCTSCtree(MuZeroMCTSCtree):
                     state_action_history.append((leaf.cpu().numpy(), last_actions))  # mcts_ctree.py:143
                     ix = o["ix"].tolist()
                 net = model.recurrent_inference(state_action_history, simulation_index, ix)
-                value = self.inverse_scalar_transform_handle(net.value)
-                reward = self.inverse_scalar_transform_handle(net.reward)
+                value, reward = self._scalars(net.value, net.reward)
                 new_lat = self._slot_tensor(self._on_device(forest, net.latent_state).reshape(lat0.shape), leaf)
                 e = simulation_index + 1
                 if e < S:
@@ -543,8 +549,7 @@ class MuZeroRNNFullObsMCTSCtree(MuZeroMCTSCtree):
             o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers)
             for simulation_index in range(S):
                 net = model.recurrent_inference(leaf, leaf_h.unsqueeze(0), o["last_action"], **kw)
-                value = self.inverse_scalar_transform_handle(net.value)
-                value_prefix = self.inverse_scalar_transform_handle(net.value_prefix)
+                value, value_prefix = self._scalars(net.value, net.value_prefix)
                 slots = [self._slot_tensor(net.predict_next_latent_state.reshape(lat0.shape), leaf),
                          self._slot_tensor(net.reward_hidden_state.reshape(N, -1), leaf_h)]
                 e = simulation_index + 1
@@ -610,8 +615,7 @@ class EfficientZeroMCTSCtree(_CtreeDriver):
             o = api.traverse_tensors(roots, scfg, tp, results, gathers=gathers, reuse=self._reuse_at(reuse, 0))
             for simulation_index in range(S):
                 net = model.recurrent_inference(leaf, (leaf_c.unsqueeze(0), leaf_h.unsqueeze(0)), self._leaf_action(roots, o))
-                value = self.inverse_scalar_transform_handle(net.value)
-                value_prefix = self.inverse_scalar_transform_handle(net.value_prefix)
+                value, value_prefix = self._scalars(net.value, net.value_prefix)
                 slots = [self._slot_tensor(net.latent_state, leaf),
                          self._slot_tensor(net.reward_hidden_state[0].reshape(N, -1), leaf_c),
                          self._slot_tensor(net.reward_hidden_state[1].reshape(N, -1), leaf_h)]

@@ -86,6 +86,7 @@ def test_headline_shape_through_the_driver(variant, graph):
                     cuda_graph=graph, tie_break_seed=seed, tie_break_advance=False, max_num_considered_actions=16,
                     pb_c_base=PB_C_BASE, pb_c_init=PB_C_INIT, lstm_horizon_len=5,
                     model=dict(support_scale=300, categorical_distribution=False)))
+    mcts.inverse_scalar_transform_handle = lambda x: x  # the scenario's model emits scalars as they are
     model = _ScenarioModel(sc, dev, 64)
     lat0 = torch.randn(sc.n, 64, device=dev)
     tp = torch.as_tensor(sc.to_play).to(dev)
