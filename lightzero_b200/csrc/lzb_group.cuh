@@ -281,7 +281,9 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     const float g = a.discount;
     const float mm_delta = mm.y - mm.x;
     const float mm_den = (mm_delta < a.delta) ? a.delta : mm_delta; // CMinMaxStats::normalize (cminimax.cpp:33-45)
+#ifdef LZB_X_BRANCHFREE_DIV
     const float mm_safe = (mm_delta > 0) ? mm_den : 1.0f;            // the divisor every lane can divide by
+#endif
     const unsigned hroot = (a.rng_mode == LZB_RNG_PER_ROOT) ? (unsigned)(p.root_offset + i) : 0u;
 
     int parent_visits = rt.x;
@@ -338,9 +340,11 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             val[r] = 0.0f;
             const unsigned wvis = __ballot_sync(kFull, vis);
             if (wvis) { // warp-uniform: slices without a visited child in any group add nothing
-#ifdef LZB_X_BRANCHY_DIV // round-1 form: the compiler branches around the division (BSSY / divergent BRA per slice)
+#ifndef LZB_X_BRANCHFREE_DIV // the compiler branches around the division (BSSY / divergent BRA per slice)
                 val[r] = vis ? __int_as_float(c[r].y) / (float)vc : 0.0f; // CNode::value()
-#else // every lane divides (by 1 where there is nothing to divide) and selects: no divergent branch on the chain
+#else // experiment (round 2, measured and rejected: 18.2 vs 17.5 us per step; ez 30.1 vs 29.7): every lane divides (by 1
+      // where there is nothing to divide) and selects - no divergent branch, but the full-precision division's ~10
+      // dependent instructions then sit on every lane's chain instead of on the lanes that need them
                 const float vq = __int_as_float(c[r].y) / (float)max(vc, 1);
                 val[r] = vis ? vq : 0.0f; // CNode::value()
 #endif
@@ -382,7 +386,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             float vs;
             if (vc == 0) vs = mean_q;
             else vs = (players == 1) ? tr[r] + g * cv : tr[r] + g * (-cv);
-#ifdef LZB_X_BRANCHY_DIV
+#ifndef LZB_X_BRANCHFREE_DIV
             if (mm_delta > 0) vs = (vs - mm.x) / mm_den;
 #else
             const float vn = (vs - mm.x) / mm_safe; // CMinMaxStats::normalize; discarded while the bounds are unset

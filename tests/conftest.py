@@ -24,3 +24,16 @@ def pytest_collection_modifyitems(config, items):
     for item in items:
         if "gpu" in item.keywords:
             item.add_marker(skip)
+
+
+@pytest.fixture(autouse=True)
+def _fresh_tie_break_default():
+    """tree_module.set_tie_break(seed) pins the seed every Roots object created afterwards starts with - a process-wide
+    default by design (the module-level API has no driver object to carry it).  Tests that pin it must not leak the pin
+    into the tests that run after them in the same process."""
+    yield
+    try:
+        from lightzero_b200.ctree import _tree_api
+        _tree_api.set_tie_break(None)
+    except Exception:
+        pass
