@@ -302,6 +302,22 @@ int lzb_scalar_workspace_bytes(int n_heads, int num_rows, size_t *bytes);
 int lzb_inverse_scalar_transform(const lzb_support_head_t *heads, int n_heads, int num_rows, int support_size, float epsilon,
                                  void *workspace_dev, void *stream);
 
+/* lzb_inverse_scalar_transform without a caller workspace and WITHOUT ANY ALLOCATION.  This entry point has no counterpart
+ * in the reference: it was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernel, same results; its scratch (one ticket
+ * word, one counter per head and num_rows floats per head) lives in a file-scope `static __device__` array of
+ * 256 + 2 * LZB_STATIC_SCALAR_MAX_ROWS * 4 = 524,544 bytes that every GPU which loads the library holds until the process
+ * exits.  The call itself performs no cudaMalloc / cudaFree and uses no allocating library routine; inputs and outputs are
+ * still the caller's.  num_rows > LZB_STATIC_SCALAR_MAX_ROWS is rejected with LZB_E_ARG (use the workspace flavour above).
+ * The array is resolved once per device (cudaGetSymbolAddress with that device current) on the first call made there.
+ * EVERY call on a device shares the one array, which keeps the previous call's contents: the words that must start at zero
+ * are cleared on `stream` ahead of the kernel, but two calls that OVERLAP on the GPU (different streams, or two host
+ * threads launching at once) race on it and give undefined results - serialise them, or give each stream its own
+ * workspace through lzb_inverse_scalar_transform. */
+#define LZB_STATIC_SCALAR_MAX_ROWS 65536
+int lzb_inverse_scalar_transform_static(const lzb_support_head_t *heads, int n_heads, int num_rows, int support_size,
+                                        float epsilon, void *stream);
+
 /* ---- Root-batch prologue / epilogue (what the callers of search() do per root in Python) ---- */
 
 /* legal_actions = [a for a, x in enumerate(action_mask[j]) if x == 1] (lzero/policy/muzero.py:671;

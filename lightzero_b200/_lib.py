@@ -199,6 +199,7 @@ _PROTOS = {
     "lzb_target_policies": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
     "lzb_scalar_workspace_bytes": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
     "lzb_inverse_scalar_transform": (C.c_int, [C.POINTER(SupportHead), C.c_int, C.c_int, C.c_int, C.c_float, _P, _P]),
+    "lzb_inverse_scalar_transform_static": (C.c_int, [C.POINTER(SupportHead), C.c_int, C.c_int, C.c_int, C.c_float, _P]),
     "lzb_peer_bytes": (C.c_int, [C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_size_t)]),
     "lzb_peer_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
     "lzb_peer_free": (C.c_int, [_P]),

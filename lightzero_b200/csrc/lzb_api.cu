@@ -4,6 +4,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <random>
 #include <vector>
 
@@ -955,6 +956,74 @@ int lzb_inverse_scalar_transform(const lzb_support_head_t *heads, int n_heads, i
     if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, 256, 0, st>>>(a);
     else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, 256, 0, st>>>(a);
     else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, 256, 0, st>>>(a); // support 300: 601 logits per row
+    else k_inverse_scalar_transform<0><<<blocks, 256, 0, st>>>(a);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+// ---- lzb_inverse_scalar_transform_static: the same kernel with its scratch in a file-scope device array, for callers that
+// cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+namespace {
+constexpr int kStaticScalarRows = LZB_STATIC_SCALAR_MAX_ROWS;
+constexpr size_t kStaticScalarCtlBytes = 256; // ticket + per-head counters, padded so that the scalars behind stay aligned
+constexpr size_t kStaticScalarBytes = kStaticScalarCtlBytes + (size_t)kMaxScalarHeads * kStaticScalarRows * sizeof(float);
+}
+// 524,544 bytes in every GPU context that loads the library, until the process exits.  In HOST code this name is only a
+// stand-in for the symbol, not a device address: the address comes from cudaGetSymbolAddress (below), per device.
+static __device__ __align__(256) unsigned char g_static_scalar_scratch[kStaticScalarBytes];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void *g_static_scalar_ptr[kMaxDevices]; // device address of the array on each device, resolved on first use
+std::mutex g_static_scalar_mutex;
+
+// the array's address on the CURRENT device (resolved once per device, with that device current)
+int static_scalar_scratch(void **out)
+{
+    int dev = -1;
+    LZB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(LZB_E_UNSUPPORTED, "inverse_scalar_transform_static: device ordinal %d outside 0..%d", dev, kMaxDevices - 1);
+    std::lock_guard<std::mutex> lock(g_static_scalar_mutex);
+    if (!g_static_scalar_ptr[dev]) {
+        void *ptr = nullptr;
+        LZB_CUDA(cudaGetSymbolAddress(&ptr, g_static_scalar_scratch));
+        if (!ptr) return fail(LZB_E_CUDA, "inverse_scalar_transform_static: cudaGetSymbolAddress returned a NULL address");
+        g_static_scalar_ptr[dev] = ptr;
+    }
+    *out = g_static_scalar_ptr[dev];
+    return LZB_OK;
+}
+} // namespace
+
+int lzb_inverse_scalar_transform_static(const lzb_support_head_t *heads, int n_heads, int num_rows, int support_size, float epsilon,
+                                        void *stream)
+{
+    if (!heads || n_heads <= 0 || n_heads > kMaxScalarHeads || num_rows <= 0 || support_size <= 0)
+        return fail(LZB_E_ARG, "inverse_scalar_transform_static: 1..%d heads, num_rows > 0, support_size > 0", kMaxScalarHeads);
+    if (num_rows > kStaticScalarRows)
+        return fail(LZB_E_ARG, "inverse_scalar_transform_static: num_rows %d exceeds the static scratch (LZB_STATIC_SCALAR_MAX_ROWS = %d rows "
+                               "per head); use lzb_inverse_scalar_transform with a caller-owned workspace", num_rows, kStaticScalarRows);
+    if (!(epsilon > 0.0f)) return fail(LZB_E_ARG, "inverse_scalar_transform_static: epsilon must be positive");
+    const int W = 2 * support_size + 1;
+    ScalarHeads a = {};
+    for (int h = 0; h < n_heads; ++h) {
+        if (!heads[h].logits_dev || !heads[h].scalar_dev || heads[h].row_stride < W)
+            return fail(LZB_E_ARG, "inverse_scalar_transform_static: head %d has a NULL pointer or a row stride below %d", h, W);
+        a.logits[h] = heads[h].logits_dev; a.out[h] = heads[h].scalar_dev; a.stride[h] = heads[h].row_stride;
+    }
+    void *scratch = nullptr;
+    if (int rc = static_scalar_scratch(&scratch)) return rc;
+    a.n_heads = n_heads; a.N = num_rows; a.support = support_size; a.eps = epsilon;
+    a.ctl = (unsigned *)scratch; a.raw = (float *)((char *)scratch + kStaticScalarCtlBytes);
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array keeps whatever the last call (of any caller, possibly one that was aborted) left in it: the ticket and the
+    // per-head counters must start at zero; the scalars behind them are written before they are read
+    LZB_CUDA(cudaMemsetAsync(scratch, 0, 16, st));
+    const long long rows = (long long)n_heads * num_rows;
+    const int blocks = (int)std::min<long long>((rows + 7) / 8, 148LL * 8);
+    if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, 256, 0, st>>>(a);
+    else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, 256, 0, st>>>(a);
+    else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, 256, 0, st>>>(a);
     else k_inverse_scalar_transform<0><<<blocks, 256, 0, st>>>(a);
     LZB_CUDA(cudaGetLastError());
     return LZB_OK;
