@@ -703,6 +703,39 @@ def run_b200_arm(a):
         ev1.record()
         torch.cuda.synchronize()
         h2d_gbs = 3 * big.numel() * big.element_size() / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
+
+    # ---- e2e_lists leg: the call pattern of an UNMODIFIED lzero policy (lzero/policy/muzero.py:671-719): per-root legal
+    # action lists, noises / logits / rewards / to_play as Python lists (the policy calls .tolist() before prepare),
+    # root latents as a pageable numpy array, and Python lists back from get_distributions() / get_values().
+    lists_ms = None
+    if not a.no_e2e and world == 1 and a.variant in ("mz", "ez", "gmz"):
+        cpu = lambda t: t.detach().cpu()
+        L = dict(noise=cpu(inp["noise"]).tolist(), reward=cpu(inp["root_reward"]).tolist(), logits=cpu(inp["root_logits"]).tolist(),
+                 value=cpu(inp["root_value"]).tolist(), to_play=cpu(inp["to_play"]).tolist(),
+                 legal=[list(range(A)) for _ in range(N)], latent=cpu(inp["latent_roots"]).numpy())
+        if a.variant == "ez":
+            L["hidden"] = (cpu(inp["hidden_c"]).numpy(), cpu(inp["hidden_h"]).numpy())
+
+        def lists_step():
+            roots = mcts_e2e.roots(N, L["legal"])
+            if a.variant == "gmz":
+                roots.prepare(NOISE_W, L["noise"], L["reward"], L["value"], L["logits"], L["to_play"])
+            else:
+                roots.prepare(NOISE_W, L["noise"], L["reward"], L["logits"], L["to_play"])
+            if a.variant == "ez":
+                mcts_e2e.search(roots, model, L["latent"], L["hidden"], L["to_play"])
+            else:
+                mcts_e2e.search(roots, model, L["latent"], L["to_play"])
+            return roots.get_distributions(), roots.get_values()
+
+        for _ in range(3):
+            d_, v_ = lists_step()
+        assert len(d_) == N and len(v_) == N and all(sum(r) == S for r in d_[:64])
+        t0 = time.perf_counter()
+        for _ in range(a.steps):
+            lists_step()
+        torch.cuda.synchronize()
+        lists_ms = 1e3 * (time.perf_counter() - t0) / a.steps
     clk = clocks.stop() if rank == 0 else None
 
     # ---- per-kernel pass (eager launches bracketed by events) for the roofline of the dominant kernel
@@ -783,6 +816,10 @@ def run_b200_arm(a):
                            "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                            "ms_per_step": round(e2e_tot / a.steps, 4), "clock": "host wall clock incl. Python, max over ranks",
                            "h2d_link_gbs": round(h2d_gbs, 1), "search_streams": e2e_streams}
+        if lists_ms is not None:
+            line["e2e_lists"] = {"value": round(total_sims / (lists_ms * 1e-3), 1), "unit": "simulations/s", "ms_per_step": round(lists_ms, 4),
+                                 "what": "unmodified-policy call pattern: Python lists of lists in (legal actions, noises, logits, rewards, to_play), "
+                                         "pageable numpy latents, Python lists out (get_distributions / get_values); host wall clock"}
         if world == 1 and not a.no_cpu_baseline:
             n = min(a.cpu_sample_roots, N)
             d = cpu_inputs(a, n, 1234)

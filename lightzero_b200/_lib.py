@@ -90,6 +90,10 @@ def pylist():
             P.lzb_rows_to_f32.argtypes = [C.py_object, C.c_void_p, C.c_long, C.c_long, C.c_void_p]
             P.lzb_seq_to_f32.restype = C.c_int
             P.lzb_seq_to_f32.argtypes = [C.py_object, C.c_void_p, C.c_long]
+            P.lzb_rows_to_i32.restype = C.c_int
+            P.lzb_rows_to_i32.argtypes = [C.py_object, C.c_void_p, C.c_long, C.c_long, C.c_void_p]
+            P.lzb_seq_to_i32.restype = C.c_int
+            P.lzb_seq_to_i32.argtypes = [C.py_object, C.c_void_p, C.c_long]
             P.lzb_rows_from_i32.restype = C.py_object
             P.lzb_rows_from_i32.argtypes = [C.c_void_p, C.c_void_p, C.c_long, C.c_long]
             _pylist = P

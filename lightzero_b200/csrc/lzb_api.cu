@@ -927,6 +927,17 @@ int lzb_target_policies(const int32_t *visits_dev, const int32_t *legal_count_de
     return LZB_OK;
 }
 
+namespace {
+int scalar_blocks(long long rows)
+{
+#ifdef LZB_X_SCALAR_PIPELINED
+    return (int)std::min<long long>((rows + 7) / 8, 148LL * 4);
+#else
+    return (int)std::min<long long>((rows + 7) / 8, 1LL << 22);
+#endif
+}
+} // namespace
+
 int lzb_scalar_workspace_bytes(int n_heads, int num_rows, size_t *bytes)
 {
     if (!bytes || n_heads <= 0 || n_heads > kMaxScalarHeads || num_rows <= 0) return fail(LZB_E_ARG, "scalar_workspace_bytes: 1..%d heads, num_rows > 0", kMaxScalarHeads);
@@ -951,12 +962,14 @@ int lzb_inverse_scalar_transform(const lzb_support_head_t *heads, int n_heads, i
     a.n_heads = n_heads; a.N = num_rows; a.support = support_size; a.eps = epsilon;
     a.ctl = (unsigned *)workspace_dev; a.raw = (float *)((char *)workspace_dev + 16);
     const long long rows = (long long)n_heads * num_rows;
-    const int blocks = (int)std::min<long long>((rows + 7) / 8, 148LL * 8); // 8 warps per block, one wave of 8 blocks per SM
+    // one row per warp, 8 warps per block (lzb_scaling.cuh; -DLZB_X_SCALAR_PIPELINED: 4 persistent blocks per SM)
+    const int blocks = scalar_blocks(rows);
+    const int iters = (int)((rows + 8LL * blocks - 1) / (8LL * blocks));
     cudaStream_t st = (cudaStream_t)stream;
-    if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, 256, 0, st>>>(a);
-    else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, 256, 0, st>>>(a);
-    else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, 256, 0, st>>>(a); // support 300: 601 logits per row
-    else k_inverse_scalar_transform<0><<<blocks, 256, 0, st>>>(a);
+    if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, 256, 0, st>>>(a, iters);
+    else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, 256, 0, st>>>(a, iters);
+    else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, 256, 0, st>>>(a, iters); // support 300: 601 logits per row
+    else k_inverse_scalar_transform<0><<<blocks, 256, 0, st>>>(a, iters);
     LZB_CUDA(cudaGetLastError());
     return LZB_OK;
 }
@@ -1020,11 +1033,13 @@ int lzb_inverse_scalar_transform_static(const lzb_support_head_t *heads, int n_h
     // per-head counters must start at zero; the scalars behind them are written before they are read
     LZB_CUDA(cudaMemsetAsync(scratch, 0, 16, st));
     const long long rows = (long long)n_heads * num_rows;
-    const int blocks = (int)std::min<long long>((rows + 7) / 8, 148LL * 8);
-    if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, 256, 0, st>>>(a);
-    else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, 256, 0, st>>>(a);
-    else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, 256, 0, st>>>(a);
-    else k_inverse_scalar_transform<0><<<blocks, 256, 0, st>>>(a);
+    // one row per warp, 8 warps per block (lzb_scaling.cuh; -DLZB_X_SCALAR_PIPELINED: 4 persistent blocks per SM)
+    const int blocks = scalar_blocks(rows);
+    const int iters = (int)((rows + 8LL * blocks - 1) / (8LL * blocks));
+    if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, 256, 0, st>>>(a, iters);
+    else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, 256, 0, st>>>(a, iters);
+    else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, 256, 0, st>>>(a, iters);
+    else k_inverse_scalar_transform<0><<<blocks, 256, 0, st>>>(a, iters);
     LZB_CUDA(cudaGetLastError());
     return LZB_OK;
 }

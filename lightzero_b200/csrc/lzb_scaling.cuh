@@ -12,8 +12,14 @@
 // block; the counters are reset by that block, so the workspace stays ready for the next call).
 //
 // This is not bit-pinned by the tree (torch's own reductions fix no summation order); tests/ hold it to 1e-5 relative
-// against the reference class loaded from its file.  exp is ex2.approx (2 ulp), the row sums are taken per lane in
-// fp32 over <= ceil(W / 32) terms and across lanes in fp64.
+// against the reference class loaded from its file.  exp is ex2.approx (2 ulp); the row sums are fp32 like the
+// reference's own tensor arithmetic (per lane over <= 4 * ceil(W / 128) terms with explicit FMAs, then a butterfly).
+//
+// Round 2 profile (profiles/r02_scalar_*): the first version (one 4-byte load and ~35 instructions per logit, fp64
+// butterflies) executed 12.4 M warp-instructions per launch of 8192 x 2 rows x 601 bins and took 21-22 us for 39 MB -
+// issue-bound, not bandwidth-bound.  This version reads 16-byte vectors (the row's unaligned head and tail through
+// predicated scalar loads, so nothing outside a row is ever read), folds the support value into compile-time
+// constants and defers the probability-branch h^-1 to the epilogue.  -DLZB_X_SCALAR_ROWLOADS restores the first version.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -29,15 +35,30 @@ struct ScalarHeads {
     long long stride[kMaxScalarHeads];
     int n_heads, N, support;              // W = 2 * support + 1
     float eps;
-    float *raw;                           // workspace: [n_heads][N] probability-branch scalars
+    float *raw;                           // workspace: [n_heads][N] probability-branch expectations (h^-1 not applied yet)
     unsigned *ctl;                        // workspace: [0] ticket, [1 + h] un-normalised rows seen for head h
+    // head h of the per-head arrays without indexing kernel parameters by a run-time value (which would copy the
+    // whole struct to local memory)
+    __device__ __forceinline__ const float *row_of(int h, int i) const
+    {
+        return (h == 0 ? logits[0] : logits[1]) + (long long)i * (h == 0 ? stride[0] : stride[1]);
+    }
+    __device__ __forceinline__ float *out_of(int h) const { return h == 0 ? out[0] : out[1]; }
 };
+static_assert(kMaxScalarHeads == 2, "row_of / out_of select between two heads");
 
 __device__ __forceinline__ double warp_sum_d(double v)
 {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
     return v;
+}
+
+__device__ __forceinline__ float exp2f_approx(float x)
+{
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
 
 // h^-1 (scaling_transform.py:124-126): sign(x) * (((sqrt(1 + 4 eps (|x| + 1 + eps)) - 1) / (2 eps))^2 - 1), in fp32
@@ -53,7 +74,7 @@ template <int T> // T = loads per lane held in registers: W <= 32 * T
 __device__ __forceinline__ void scalar_row(const ScalarHeads &a, int h, int i, int lane, bool &not_normalised)
 {
     const int W = 2 * a.support + 1;
-    const float *row = a.logits[h] + (long long)i * a.stride[h];
+    const float *row = a.row_of(h, i);
     float x[T];
 #pragma unroll
     for (int t = 0; t < T; ++t) { // all loads of the row in flight together; streamed: read once
@@ -80,18 +101,105 @@ __device__ __forceinline__ void scalar_row(const ScalarHeads &a, int h, int i, i
     const double dse = warp_sum_d((double)se), dte = warp_sum_d((double)te);
     const double dsx = warp_sum_d((double)sx), dtx = warp_sum_d((double)tx);
     if (lane == 0) {
-        a.out[h][i] = inverse_h((float)(dte / dse), a.eps);
-        a.raw[(size_t)h * a.N + i] = inverse_h((float)dtx, a.eps);
+        a.out_of(h)[i] = inverse_h((float)(dte / dse), a.eps);
+        a.raw[(size_t)h * a.N + i] = (float)dtx;
         // torch.allclose(sum, 1, atol=1e-5) with the default rtol=1e-5: |sum - 1| <= 1e-5 + 1e-5 * 1; NaN is not close
         not_normalised = !(fabs(dsx - 1.0) <= 2e-5);
     }
 }
 
+__device__ __forceinline__ float warp_sum_f(float v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o);
+    return v;
+}
+
+// One row by one warp with 16-byte loads.  The row starts `off` floats past a 16-byte boundary (off = 0..3, any row
+// stride); vector v of the row covers positions 4v - off .. 4v - off + 3 and lane l takes vectors l, l + 32, ...
+// Vectors that lie wholly inside the row are one LDG.128; the (at most two) vectors that straddle the row's ends are
+// read element by element under predicates, so no byte outside [row, row + W) is touched.  V = vectors per lane:
+// 4 * 32 * V >= W + 3.  Positions outside the row hold -inf (their exp is 0) and a clear bit in the lane's mask.
+template <int V>
+struct RowRegs {
+    float x[V][4];
+    unsigned vm[V]; // which of a vector's four positions belong to the row
+    int off;
+};
+
+template <int V>
+__device__ __forceinline__ void load_row_v4(const float *row, int W, int lane, RowRegs<V> &r)
+{
+    r.off = (int)((reinterpret_cast<unsigned long long>(row) >> 2) & 3ull);
+    const float *base = row - r.off; // 16-byte aligned
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+        const int lo = 4 * (lane + 32 * j) - r.off;
+        const bool inside = lo >= 0 && lo + 3 < W;
+        r.vm[j] = inside ? 0xfu : 0u;
+        float4 v = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        if (inside) v = __ldcs(reinterpret_cast<const float4 *>(base) + lane + 32 * j);
+        r.x[j][0] = v.x; r.x[j][1] = v.y; r.x[j][2] = v.z; r.x[j][3] = v.w;
+    }
+    // the straddling vectors: lane 0's first one when the row is not 16-byte aligned, and the row's last one - both
+    // conditions are warp-uniform, so rows and slices without a straddling vector skip the element-wise code
+    const int jend = ((r.off + W - 1) >> 2) >> 5;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+        if ((j == 0 && r.off != 0) || j == jend) {
+            const int lo = 4 * (lane + 32 * j) - r.off;
+            if (r.vm[j] == 0u && lo + 3 >= 0 && lo < W) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    if (lo + c >= 0 && lo + c < W) { r.x[j][c] = __ldcs(row + lo + c); r.vm[j] |= 1u << c; }
+            }
+        }
+    }
+}
+
+// softmax expectation and raw (probability-branch) expectation of the row held in r; the support value of position p is
+// p - support = (4l - off - support) + (128 j + c): the second term is a compile-time constant, so the weighted sums are
+// sum e * (128 j + c)  +  (4l - off - support) * sum e.
+template <int V>
+__device__ __forceinline__ void reduce_row_v4(const ScalarHeads &a, const RowRegs<V> &r, int h, int i, int lane, bool live, bool &not_normalised)
+{
+    float m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < V; ++j) m = fmaxf(fmaxf(fmaxf(r.x[j][0], r.x[j][1]), fmaxf(r.x[j][2], r.x[j][3])), m);
+    m = warp_max(m);
+    const float kLog2e = 1.4426950408889634f;
+    const float mneg = -m * kLog2e;
+    float se = 0.0f, te = 0.0f, sx = 0.0f, tx = 0.0f;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float rel = (float)(128 * j + c); // compile-time constant
+            const float e = exp2f_approx(__fmaf_rn(r.x[j][c], kLog2e, mneg)); // -inf outside the row: e = 0
+            const float xr = ((r.vm[j] >> c) & 1u) ? r.x[j][c] : 0.0f;         // the raw sums skip positions outside the row
+            se += e;
+            te = __fmaf_rn(e, rel, te);
+            sx += xr;
+            tx = __fmaf_rn(xr, rel, tx);
+        }
+    }
+    const float lane_sup = (float)(4 * lane - r.off - a.support);
+    te = __fmaf_rn(lane_sup, se, te);
+    tx = __fmaf_rn(lane_sup, sx, tx);
+    se = warp_sum_f(se); te = warp_sum_f(te); sx = warp_sum_f(sx); tx = warp_sum_f(tx);
+    const float scalar = inverse_h(te / se, a.eps);
+    if (lane == 0 && live) {
+        a.out_of(h)[i] = scalar;
+        a.raw[(size_t)h * a.N + i] = tx;
+        not_normalised = !(fabsf(sx - 1.0f) <= 2e-5f); // torch.allclose(sum, 1, atol=1e-5) + default rtol=1e-5; NaN is not close
+    }
+}
+
 // wide supports: the row is walked twice (max, then sums) instead of held in registers
-__device__ __forceinline__ void scalar_row_wide(const ScalarHeads &a, int h, int i, int lane, bool &not_normalised)
+__device__ __forceinline__ void scalar_row_wide(const ScalarHeads &a, int h, int i, int lane, bool live, bool &not_normalised)
 {
     const int W = 2 * a.support + 1;
-    const float *row = a.logits[h] + (long long)i * a.stride[h];
+    const float *row = a.row_of(h, i);
     float m = -INFINITY;
     for (int k = lane; k < W; k += 32) m = fmaxf(m, row[k]);
     m = warp_max(m);
@@ -101,31 +209,93 @@ __device__ __forceinline__ void scalar_row_wide(const ScalarHeads &a, int h, int
         se += e; te += (double)(e * sup); sx += v; tx += (double)(v * sup);
     }
     se = warp_sum_d(se); te = warp_sum_d(te); sx = warp_sum_d(sx); tx = warp_sum_d(tx);
-    if (lane == 0) {
-        a.out[h][i] = inverse_h((float)(te / se), a.eps);
-        a.raw[(size_t)h * a.N + i] = inverse_h((float)tx, a.eps);
+    if (lane == 0 && live) {
+        a.out_of(h)[i] = inverse_h((float)(te / se), a.eps);
+        a.raw[(size_t)h * a.N + i] = (float)tx;
         not_normalised = !(fabs(sx - 1.0) <= 2e-5);
     }
 }
 
-// one warp per row; rows of head 0 first, then head 1 (the grid strides over n_heads * N rows)
+// Default: ONE row per warp, the grid holds a warp for every row and `iters` = 1.  There is no branch around the row
+// pass: a warp without a row (tail of the last block) recomputes the last row with its stores predicated off, and the
+// trip count `iters` is a kernel argument - warp-uniform BY CONSTRUCTION - so the compiler keeps the 25 shuffles of a
+// row as plain SHFL (inside a loop bounded by a per-thread value each one is wrapped in a WARPSYNC.COLLECTIVE protocol).
+// Measured at 8192 x 2 rows x 601 bins (profiles/r02_scalar_transform.md): 4-byte loads + fp64 butterflies in a
+// grid-stride loop 12.4 M warp-instructions / 21.5 us; this form 7.7 M / 16.0 us; persistent warps (-DLZB_X_SCALAR_PIPELINED:
+// 4 blocks per SM, several rows per warp, the vectors of row it + 1 requested before row it is reduced) 9.7 M / 17.7 us -
+// the dead iterations of the last pass and the register copies cost more than the prefetch hides.
+#ifdef LZB_X_SCALAR_PIPELINED
+#define LZB_SCALAR_MIN_BLOCKS 4
+#else
+#define LZB_SCALAR_MIN_BLOCKS 6 // 40 registers: 48 resident warps per SM
+#endif
 template <int T>
-__global__ void __launch_bounds__(256) k_inverse_scalar_transform(ScalarHeads a)
+__global__ void __launch_bounds__(256, LZB_SCALAR_MIN_BLOCKS) k_inverse_scalar_transform(ScalarHeads a, int iters)
 {
     __shared__ unsigned s_bad[kMaxScalarHeads];
     __shared__ unsigned s_last;
     if (threadIdx.x < kMaxScalarHeads) s_bad[threadIdx.x] = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31;
-    const int warps = gridDim.x * (blockDim.x >> 5);
     const int total = a.n_heads * a.N;
-    for (int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < total; r += warps) {
-        const int h = r / a.N, i = r - h * a.N;
-        bool bad = false;
-        if constexpr (T > 0) scalar_row<T>(a, h, i, lane, bad);
-        else scalar_row_wide(a, h, i, lane, bad);
-        if (lane == 0 && bad) s_bad[h] = 1; // benign race: every writer stores 1
+    const int warps = gridDim.x * (blockDim.x >> 5);
+    const int gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    bool bad0 = false, bad1 = false;
+#ifndef LZB_X_SCALAR_ROWLOADS
+    if constexpr (T > 0) {
+        constexpr int V = (32 * T + 3 + 127) / 128; // W <= 32 T; the vectors cover W + 3 positions
+        const int W = 2 * a.support + 1;
+#ifdef LZB_X_SCALAR_PIPELINED
+        RowRegs<V> cur, nxt;
+        {
+            const int r = min(gw, total - 1);
+            const int h = (r >= a.N) ? 1 : 0;
+            load_row_v4<V>(a.row_of(h, r - h * a.N), W, lane, nxt);
+        }
+#endif
+#pragma unroll 1
+        for (int it = 0; it < iters; ++it) {
+            const int r0 = it * warps + gw;
+            const bool live = r0 < total;
+            const int r = live ? r0 : total - 1;
+            const int h = (r >= a.N) ? 1 : 0;
+#ifdef LZB_X_SCALAR_PIPELINED
+            cur = nxt;
+            if (it + 1 < iters) { // warp-uniform
+                const int rn = min((it + 1) * warps + gw, total - 1);
+                const int hn = (rn >= a.N) ? 1 : 0;
+                load_row_v4<V>(a.row_of(hn, rn - hn * a.N), W, lane, nxt);
+            }
+#else
+            RowRegs<V> cur;
+            load_row_v4<V>(a.row_of(h, r - h * a.N), W, lane, cur);
+#endif
+            bool bad = false;
+            reduce_row_v4<V>(a, cur, h, r - h * a.N, lane, live, bad);
+            bad0 = bad0 || (bad && h == 0);
+            bad1 = bad1 || (bad && h == 1);
+        }
+    } else
+#endif
+    {
+#pragma unroll 1
+        for (int it = 0; it < iters; ++it) {
+            const int r0 = it * warps + gw;
+            const bool live = r0 < total;
+            const int r = live ? r0 : total - 1;
+            const int h = (r >= a.N) ? 1 : 0;
+            bool bad = false;
+#ifdef LZB_X_SCALAR_ROWLOADS
+            if constexpr (T > 0) scalar_row<T>(a, h, r - h * a.N, lane, bad);
+            else
+#endif
+            scalar_row_wide(a, h, r - h * a.N, lane, live, bad);
+            bad0 = bad0 || (bad && h == 0);
+            bad1 = bad1 || (bad && h == 1);
+        }
     }
+    if (lane == 0 && bad0) s_bad[0] = 1; // benign race: every writer stores 1
+    if (lane == 0 && bad1) s_bad[1] = 1;
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int h = 0; h < a.n_heads; ++h)
@@ -139,7 +309,7 @@ __global__ void __launch_bounds__(256) k_inverse_scalar_transform(ScalarHeads a)
     for (int h = 0; h < a.n_heads; ++h) {
         const unsigned bad = *((volatile unsigned *)(a.ctl + 1 + h));
         if (bad == 0) // every row of this head sums to 1: the head emitted probabilities (ensure_softmax's else branch)
-            for (int i = threadIdx.x; i < a.N; i += blockDim.x) a.out[h][i] = __ldcg(a.raw + (size_t)h * a.N + i);
+            for (int i = threadIdx.x; i < a.N; i += blockDim.x) a.out_of(h)[i] = inverse_h(__ldcg(a.raw + (size_t)h * a.N + i), a.eps);
     }
     __syncthreads();
     if (threadIdx.x <= a.n_heads) a.ctl[threadIdx.x] = 0; // ready for the next call

@@ -34,7 +34,20 @@ def _dev(x, dtype, device):
         return x.to(device=device, dtype=dtype, non_blocking=True).contiguous()
     if dtype == torch.float32 and isinstance(x, (list, tuple)) and len(x):
         x = _floats_from_lists(x)
+    elif dtype == torch.int32 and isinstance(x, (list, tuple)) and len(x):
+        x = _ints_from_list(x)
     return torch.as_tensor(x, dtype=dtype).to(device, non_blocking=True).contiguous()
+
+
+def _ints_from_list(x):
+    """[N] Python list of ints (to_play_batch) -> int32 array through lzb_pylist.c; anything else is returned as it came."""
+    P = _lib.pylist()
+    if P is None or not isinstance(x[0], int):
+        return x
+    arr = np.empty(len(x), np.int32)
+    if P.lzb_seq_to_i32(x, arr.ctypes.data, len(x)) != 0:
+        raise ValueError("could not read the integers")
+    return arr
 
 
 def _floats_from_lists(x):
@@ -67,6 +80,13 @@ def legal_tensors(legal_actions, N, A, variant, device):
             cnt, idx = legal_actions
             cnt, idx = _dev(cnt, torch.int32, device), _dev(idx, torch.int32, device)
         else:
+            P = _lib.pylist()
+            if P is not None and isinstance(legal_actions, (list, tuple)):
+                # C loops over the list objects (lzb_pylist.c): 0.5 ms at 8192 x 18 where torch.as_tensor needs 150 ms
+                idx_a, cnt_a = np.empty((N, A), np.int32), np.empty(N, np.int32)
+                if P.lzb_rows_to_i32(legal_actions, idx_a.ctypes.data, N, A, cnt_a.ctypes.data) != 0:
+                    raise ValueError("could not read the legal-action lists")
+                return (torch.from_numpy(cnt_a).to(device, non_blocking=True), torch.from_numpy(idx_a).to(device, non_blocking=True))
             lens = [len(l) for l in legal_actions]
             if max(lens, default=0) > A:
                 raise ValueError("a root has more legal actions than the action space")
