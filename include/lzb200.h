@@ -357,6 +357,23 @@ int lzb_select_action(const lzb_select_action_t *args, void *stream);
 int lzb_target_policies(const int32_t *visits_dev, const int32_t *legal_count_dev, const int32_t *legal_actions_dev,
                         const int32_t *policy_mask_dev, int num_roots, int action_space, float *policy_dev, void *stream);
 
+/* Reanalyze value / reward targets (lzero/mcts/buffer/game_buffer_muzero.py:463-513, the tail of
+ * _compute_target_reward_value): for segment b and unroll step u, with t = b * (U + 1) + u and current = pos[b] + u,
+ *   v = root_values[t] * discount ** td_steps[t] (negated for odd td_steps when board_games) * value_mask[t]
+ *       + sum_i (+|-) rewards[b][current + i] * discount ** i   over the Python slice [current : current + td_steps[t]]
+ *   target_values[t] = v and target_rewards[t] = rewards[b][current] if current < segment_len[b], else 0 and 0.
+ * float64 arithmetic in the reference's order.  pow_table_dev[k] = discount ** k for k < pow_len (computed by the caller
+ * on the HOST, so that it is the host libm's pow like Python's `**`); pow_len must exceed every td_steps entry.
+ * to_play_dev [B, to_play_stride] is read only when board_games != 0 (:494-499, indexed exactly as the reference does). */
+typedef struct {
+    const float *root_values_dev, *value_mask_dev, *rewards_dev;
+    const int32_t *td_steps_dev, *reward_len_dev, *segment_len_dev, *pos_dev, *to_play_dev;
+    const double *pow_table_dev;
+    double *target_values_dev, *target_rewards_dev;
+    int32_t num_segments, num_unroll_steps, reward_stride, to_play_stride, pow_len, board_games;
+} lzb_value_targets_t;
+int lzb_value_targets(const lzb_value_targets_t *args, void *stream);
+
 /* ---- End-of-search exchange over NVLink / NVSwitch peer memory ----
  * The one place a sharded search crosses GPUs: every rank's root outputs (visit counts [n, A] i32, values [n] f32,
  * Gumbel policies ...) -> the full batch on every rank.  One kernel per rank packs its pieces row-wise, stores them

@@ -6,3 +6,4 @@ Importing the package does not need a GPU; creating roots or searching does (the
 from .tree_search import (EfficientZeroMCTSCtree, GumbelMuZeroMCTSCtree, MuZeroMCTSCtree,  # noqa: F401
                           MuZeroRNNFullObsMCTSCtree, SampledEfficientZeroMCTSCtree, StochasticMuZeroMCTSCtree,
                           UniZeroMCTSCtree)
+from . import callers  # noqa: F401,E402  (collect_search / reanalyze_policy_targets / reanalyze_value_targets)

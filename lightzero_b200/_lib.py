@@ -147,6 +147,16 @@ class SupportHead(C.Structure):
     _fields_ = [("logits_dev", C.c_void_p), ("row_stride", C.c_int64), ("scalar_dev", C.c_void_p)]
 
 
+class ValueTargets(C.Structure):
+    """lzb_value_targets_t"""
+    _fields_ = [("root_values_dev", C.c_void_p), ("value_mask_dev", C.c_void_p), ("rewards_dev", C.c_void_p),
+                ("td_steps_dev", C.c_void_p), ("reward_len_dev", C.c_void_p), ("segment_len_dev", C.c_void_p),
+                ("pos_dev", C.c_void_p), ("to_play_dev", C.c_void_p), ("pow_table_dev", C.c_void_p),
+                ("target_values_dev", C.c_void_p), ("target_rewards_dev", C.c_void_p), ("num_segments", C.c_int32),
+                ("num_unroll_steps", C.c_int32), ("reward_stride", C.c_int32), ("to_play_stride", C.c_int32),
+                ("pow_len", C.c_int32), ("board_games", C.c_int32)]
+
+
 class TraverseIO(C.Structure):
     """lzb_traverse_io_t"""
     _fields_ = [("to_play_dev", C.c_void_p), ("ix_dev", C.c_void_p), ("iy_dev", C.c_void_p),
@@ -204,6 +214,7 @@ _PROTOS = {
     "lzb_scalar_workspace_bytes": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_size_t)]),
     "lzb_inverse_scalar_transform": (C.c_int, [C.POINTER(SupportHead), C.c_int, C.c_int, C.c_int, C.c_float, _P, _P]),
     "lzb_inverse_scalar_transform_static": (C.c_int, [C.POINTER(SupportHead), C.c_int, C.c_int, C.c_int, C.c_float, _P]),
+    "lzb_value_targets": (C.c_int, [C.POINTER(ValueTargets), _P]),
     "lzb_peer_bytes": (C.c_int, [C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_size_t)]),
     "lzb_peer_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
     "lzb_peer_free": (C.c_int, [_P]),

@@ -196,4 +196,57 @@ __global__ void k_target_policies(const int *visits, const int *count, const int
     }
 }
 
+// ------------------------------------------------------------------------------------------------ value targets
+// The n-step value targets of the reanalyze buffer (lzero/mcts/buffer/game_buffer_muzero.py:463-513), one thread per
+// transition (segment b, unroll step u).  Everything is float64 like the reference's Python floats / numpy arrays
+// (-fmad=false: mul and add stay separate roundings); discount ** k comes from a host table so that it is the host
+// libm's pow().  board_games reproduces the reference's to_play indexing as written (:496: the reward's OFFSET i, not
+// its position, indexes to_play_list).
+struct ValueTargetArgs {
+    const float *root_values;   // [B * (U + 1)] searched root values (use_root_value) or predicted values
+    const int *td_steps;        // [B * (U + 1)]
+    const float *value_mask;    // [B * (U + 1)]
+    const float *rewards;       // [B, reward_stride] reward_list of each game segment, padded
+    const int *reward_len;      // [B] len(reward_list)
+    const int *segment_len;     // [B] game_segment_lens
+    const int *pos;             // [B] pos_in_game_segment_list
+    const int *to_play;         // [B, to_play_stride] to_play_segment (board games), or nullptr
+    const double *pow_table;    // [pow_len] discount ** k
+    double *target_values;      // [B, U + 1]
+    double *target_rewards;     // [B, U + 1]
+    int B, U, reward_stride, to_play_stride, pow_len, board_games;
+};
+
+__global__ void k_value_targets(ValueTargetArgs a)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int per = a.U + 1;
+    if (t >= a.B * per) return;
+    const int b = t / per, u = t - b * per;
+    const int state_index = a.pos[b], current_index = state_index + u;
+    const int td = a.td_steps[t];
+    const double dpow = a.pow_table[min(max(td, 0), a.pow_len - 1)];
+    double v = (double)a.root_values[t];
+    if (a.board_games) v = __dmul_rn(v, (td % 2 == 0) ? dpow : -dpow); // :466-473
+    else v = __dmul_rn(v, dpow);                                       // :474-477
+    v = __dmul_rn(v, (double)a.value_mask[t]);                          // :479
+    const int len = a.reward_len[b];
+    const float *rew = a.rewards + (size_t)b * a.reward_stride;
+    // reward_list[current_index:bootstrap_index]: Python slice clipping (:490-491)
+    const int lo = min(max(current_index, 0), len), hi = min(max(current_index + td, 0), len);
+    for (int k = lo; k < hi; ++k) {
+        const int i = k - lo;
+        const double term = __dmul_rn((double)rew[k], a.pow_table[min(i, a.pow_len - 1)]);
+        bool same = true;
+        if (a.board_games) {
+            const int *tp = a.to_play + (size_t)b * a.to_play_stride;
+            same = tp[min(state_index, a.to_play_stride - 1)] == tp[min(i, a.to_play_stride - 1)]; // to_play_list[base_index] == to_play_list[i] (:496)
+        }
+        v = same ? __dadd_rn(v, term) : __dadd_rn(v, -term);
+    }
+    const bool in_segment = current_index < a.segment_len[b]; // :505-510
+    a.target_values[t] = in_segment ? v : 0.0;
+    a.target_rewards[t] = in_segment ? (double)rew[min(current_index, a.reward_stride - 1)] : 0.0;
+}
+
 } // namespace lzb
