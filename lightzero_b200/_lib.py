@@ -83,7 +83,7 @@ def pylist():
                 import sysconfig
                 cc = shutil.which("gcc") or shutil.which("cc")
                 if cc:
-                    subprocess.run([cc, "-O2", "-shared", "-fPIC", "-I" + sysconfig.get_paths()["include"], src, "-o", PYLIST_PATH],
+                    subprocess.run([cc, "-O2", "-shared", "-fPIC", "-pthread", "-I" + sysconfig.get_paths()["include"], src, "-o", PYLIST_PATH],
                                    check=True, capture_output=True)
             P = C.PyDLL(PYLIST_PATH)
             P.lzb_rows_to_f32.restype = C.c_int

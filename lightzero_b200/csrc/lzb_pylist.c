@@ -8,7 +8,9 @@
  * No GPU code here and no arithmetic: bytes in, bytes out. */
 #define PY_SSIZE_T_CLEAN
 #include <Python.h>
+#include <pthread.h>
 #include <stdint.h>
+#include <unistd.h>
 
 static int as_double(PyObject *o, double *v)
 {
@@ -20,10 +22,76 @@ static int as_double(PyObject *o, double *v)
     return (*v == -1.0 && PyErr_Occurred()) ? -1 : 0;
 }
 
+/* ---- parallel fast path for the common shape: a LIST of LISTS of exact floats (what `.tolist()` of a float array
+ * gives, lzero/policy/muzero.py:669,672-677).  The calling thread keeps the GIL for the whole call, so no Python code
+ * can run or mutate the lists; the workers only READ list item pointers and the ob_fval of exact floats - no reference
+ * count is touched and no Python API is called from them.  Anything else in the data (ints, numpy scalars, tuples)
+ * makes a worker report "not this shape" and the serial loops below redo the call. */
+typedef struct {
+    PyObject **rows;
+    float *out;
+    int32_t *lens;
+    long lo, hi, width;
+    int status; /* 0 ok, 1 = a row that is not a list of exact floats, 2 = a row longer than the width */
+} f32_job;
+
+static void *f32_worker(void *arg)
+{
+    f32_job *j = (f32_job *)arg;
+    for (long i = j->lo; i < j->hi; ++i) {
+        PyObject *row = j->rows[i];
+        if (!PyList_CheckExact(row)) { j->status = 1; return NULL; }
+        const Py_ssize_t m = PyList_GET_SIZE(row);
+        if (m > j->width) { j->status = 2; return NULL; }
+        PyObject **items = ((PyListObject *)row)->ob_item;
+        float *dst = j->out + (size_t)i * (size_t)j->width;
+        for (Py_ssize_t k = 0; k < m; ++k) {
+            if (!PyFloat_CheckExact(items[k])) { j->status = 1; return NULL; }
+            dst[k] = (float)PyFloat_AS_DOUBLE(items[k]);
+        }
+        for (Py_ssize_t k = m; k < j->width; ++k) dst[k] = 0.0f;
+        if (j->lens) j->lens[i] = (int32_t)m;
+    }
+    return NULL;
+}
+
+/* 1 = done in parallel, 0 = not the fast shape (nothing reported, caller falls back), -1 = error set */
+static int rows_to_f32_parallel(PyObject *rows, float *out, long n, long width, int32_t *lens)
+{
+    enum { kMaxThreads = 8 };
+    if (!PyList_CheckExact(rows) || PyList_GET_SIZE(rows) != n || n * width < 32768) return 0;
+    long cores = sysconf(_SC_NPROCESSORS_ONLN);
+    int nt = (int)(cores < 2 ? 1 : (cores > kMaxThreads ? kMaxThreads : cores));
+    if (nt < 2) return 0;
+    f32_job jobs[kMaxThreads];
+    pthread_t tid[kMaxThreads];
+    int started[kMaxThreads];
+    PyObject **items = ((PyListObject *)rows)->ob_item;
+    for (int t = 0; t < nt; ++t) {
+        jobs[t].rows = items; jobs[t].out = out; jobs[t].lens = lens; jobs[t].width = width; jobs[t].status = 0;
+        jobs[t].lo = n * t / nt; jobs[t].hi = n * (t + 1) / nt;
+        started[t] = (t > 0) && pthread_create(&tid[t], NULL, f32_worker, &jobs[t]) == 0;
+    }
+    f32_worker(&jobs[0]);
+    for (int t = 1; t < nt; ++t) {
+        if (started[t]) pthread_join(tid[t], NULL);
+        else f32_worker(&jobs[t]);
+    }
+    int worst = 0;
+    for (int t = 0; t < nt; ++t) worst = jobs[t].status > worst ? jobs[t].status : worst;
+    if (worst == 2) {
+        PyErr_SetString(PyExc_ValueError, "a row is longer than the action space");
+        return -1;
+    }
+    return worst == 0 ? 1 : 0;
+}
+
 /* rows: sequence of n sequences, row i of length lens[i] <= width  ->  out[n][width] float32, zero padded.
  * Returns 0, or -1 with a Python exception set. */
 int lzb_rows_to_f32(PyObject *rows, float *out, long n, long width, int32_t *lens)
 {
+    const int fast = rows_to_f32_parallel(rows, out, n, width, lens);
+    if (fast != 0) return fast < 0 ? -1 : 0;
     PyObject *outer = PySequence_Fast(rows, "expected a sequence of rows");
     if (!outer) return -1;
     if (PySequence_Fast_GET_SIZE(outer) != n) {
@@ -96,10 +164,75 @@ static int as_long(PyObject *o, long *v)
     return 0;
 }
 
+/* the same parallel fast path for a list of lists of exact SMALL ints (CPython >= 3.12 keeps them "compact": the value
+ * is read from the object without any API call); anything else falls back to the serial loop */
+#if PY_VERSION_HEX >= 0x030C0000
+typedef struct {
+    PyObject **rows;
+    int32_t *out, *lens;
+    long lo, hi, width;
+    int status;
+} i32_job;
+
+static void *i32_worker(void *arg)
+{
+    i32_job *j = (i32_job *)arg;
+    for (long i = j->lo; i < j->hi; ++i) {
+        PyObject *row = j->rows[i];
+        if (!PyList_CheckExact(row)) { j->status = 1; return NULL; }
+        const Py_ssize_t m = PyList_GET_SIZE(row);
+        if (m > j->width) { j->status = 2; return NULL; }
+        PyObject **items = ((PyListObject *)row)->ob_item;
+        int32_t *dst = j->out + (size_t)i * (size_t)j->width;
+        for (Py_ssize_t k = 0; k < m; ++k) {
+            if (!PyLong_CheckExact(items[k]) || !PyUnstable_Long_IsCompact((PyLongObject *)items[k])) { j->status = 1; return NULL; }
+            dst[k] = (int32_t)PyUnstable_Long_CompactValue((PyLongObject *)items[k]);
+        }
+        for (Py_ssize_t k = m; k < j->width; ++k) dst[k] = 0;
+        if (j->lens) j->lens[i] = (int32_t)m;
+    }
+    return NULL;
+}
+
+static int rows_to_i32_parallel(PyObject *rows, int32_t *out, long n, long width, int32_t *lens)
+{
+    enum { kMaxThreads = 8 };
+    if (!PyList_CheckExact(rows) || PyList_GET_SIZE(rows) != n || n * width < 32768) return 0;
+    long cores = sysconf(_SC_NPROCESSORS_ONLN);
+    int nt = (int)(cores < 2 ? 1 : (cores > kMaxThreads ? kMaxThreads : cores));
+    if (nt < 2) return 0;
+    i32_job jobs[kMaxThreads];
+    pthread_t tid[kMaxThreads];
+    int started[kMaxThreads];
+    PyObject **items = ((PyListObject *)rows)->ob_item;
+    for (int t = 0; t < nt; ++t) {
+        jobs[t].rows = items; jobs[t].out = out; jobs[t].lens = lens; jobs[t].width = width; jobs[t].status = 0;
+        jobs[t].lo = n * t / nt; jobs[t].hi = n * (t + 1) / nt;
+        started[t] = (t > 0) && pthread_create(&tid[t], NULL, i32_worker, &jobs[t]) == 0;
+    }
+    i32_worker(&jobs[0]);
+    for (int t = 1; t < nt; ++t) {
+        if (started[t]) pthread_join(tid[t], NULL);
+        else i32_worker(&jobs[t]);
+    }
+    int worst = 0;
+    for (int t = 0; t < nt; ++t) worst = jobs[t].status > worst ? jobs[t].status : worst;
+    if (worst == 2) {
+        PyErr_SetString(PyExc_ValueError, "a root has more legal actions than the action space");
+        return -1;
+    }
+    return worst == 0 ? 1 : 0;
+}
+#else
+static int rows_to_i32_parallel(PyObject *rows, int32_t *out, long n, long width, int32_t *lens) { return 0; }
+#endif
+
 /* rows: sequence of n sequences of ints, row i of length lens[i] <= width -> out[n][width] int32, zero padded (the
  * per-root legal-action lists every policy passes to Roots(...), lzero/policy/muzero.py:671).  0, or -1 with an exception. */
 int lzb_rows_to_i32(PyObject *rows, int32_t *out, long n, long width, int32_t *lens)
 {
+    const int fast = rows_to_i32_parallel(rows, out, n, width, lens);
+    if (fast != 0) return fast < 0 ? -1 : 0;
     PyObject *outer = PySequence_Fast(rows, "expected a sequence of rows");
     if (!outer) return -1;
     if (PySequence_Fast_GET_SIZE(outer) != n) {

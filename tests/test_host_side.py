@@ -193,3 +193,52 @@ def test_list_marshalling_helper_matches_numpy():
     c = rng.integers(0, 10, 129).astype(np.int32)
     out = P.lzb_rows_from_i32(v.ctypes.data, c.ctypes.data, 129, 9)
     assert out == [r[:k] for r, k in zip(v.tolist(), c.tolist())] and all(type(x) is int for r in out for x in r)
+
+
+def test_list_marshalling_parallel_paths_and_int_lists():
+    """The threaded fast paths of lzb_pylist.c (lists of lists of exact floats / small ints, large enough to be split over
+    threads) against numpy, the serial fallbacks for every other shape, and the int readers behind legal-action lists and
+    to_play (Roots(root_num, legal_actions_list), lzero/policy/muzero.py:671,680)."""
+    import gc
+    from lightzero_b200 import _lib
+    from lightzero_b200.forest import _floats_from_lists, _ints_from_list
+    P = _lib.pylist()
+    rng = np.random.default_rng(5)
+    N, A = 4096, 18
+    x = rng.standard_normal((N, A)).astype(np.float32)
+    L = x.tolist()
+    assert np.array_equal(_floats_from_lists(L), x)                       # threaded
+    assert np.array_equal(_floats_from_lists([tuple(r) for r in L]), x)  # serial: tuples
+    mixed = [list(r) for r in L]
+    mixed[77][3] = 2                                                      # an int among the floats: serial fallback
+    got = _floats_from_lists(mixed)
+    assert got[77, 3] == 2.0 and np.array_equal(got[78], x[78])
+    ragged = [r[: 1 + i % A] for i, r in enumerate(L)]
+    out, lens = np.empty((N, A), np.float32), np.empty(N, np.int32)
+    assert P.lzb_rows_to_f32(ragged, out.ctypes.data, N, A, lens.ctypes.data) == 0
+    assert lens.tolist() == [len(r) for r in ragged]
+    assert all(np.array_equal(out[i, :len(r)], np.asarray(r, np.float32)) and (out[i, len(r):] == 0).all() for i, r in enumerate(ragged))
+    # legal-action lists
+    legal = [sorted(rng.choice(A, size=1 + i % A, replace=False).tolist()) for i in range(N)]
+    idx, cnt = np.full((N, A), -7, np.int32), np.empty(N, np.int32)
+    assert P.lzb_rows_to_i32(legal, idx.ctypes.data, N, A, cnt.ctypes.data) == 0     # threaded
+    assert cnt.tolist() == [len(l) for l in legal]
+    assert all(idx[i, :len(l)].tolist() == l and (idx[i, len(l):] == 0).all() for i, l in enumerate(legal))
+    idx2, cnt2 = np.empty((N, A), np.int32), np.empty(N, np.int32)
+    assert P.lzb_rows_to_i32([tuple(l) for l in legal], idx2.ctypes.data, N, A, cnt2.ctypes.data) == 0  # serial
+    assert np.array_equal(idx, idx2) and np.array_equal(cnt, cnt2)
+    floats = [[float(v) for v in l] for l in legal]                      # a float mask's .tolist(): integers stored as floats
+    assert P.lzb_rows_to_i32(floats, idx2.ctypes.data, N, A, cnt2.ctypes.data) == 0 and np.array_equal(idx, idx2)
+    with pytest.raises(ValueError):
+        P.lzb_rows_to_i32([list(range(A + 1))] * N, idx2.ctypes.data, N, A, cnt2.ctypes.data)
+    assert _ints_from_list([-1] * 100).tolist() == [-1] * 100 and _ints_from_list([1, 2] * 50).dtype == np.int32
+    # building the output lists pauses the cyclic collector and puts it back the way it was
+    v = rng.integers(0, 60, (N, A)).astype(np.int32)
+    for enabled in (True, False):
+        (gc.enable if enabled else gc.disable)()
+        try:
+            rows = P.lzb_rows_from_i32(v.ctypes.data, cnt.ctypes.data, N, A)
+            assert gc.isenabled() == enabled
+        finally:
+            gc.enable()
+        assert rows[5] == v[5, :cnt[5]].tolist()
