@@ -387,8 +387,10 @@ int lzb_value_targets(const lzb_value_targets_t *args, void *stream);
  *                    pieces_dev[n_pieces]: local [rows_per_rank, piece_words[k]] 32-bit tensors, concatenated per row;
  *                    epoch: 1, 2, 3 ... the same sequence on every rank; *result_dev: [world * rows_per_rank,
  *                    row_words] in the caller's own buffer, valid until the next-but-one exchange.  A peer that does
- *                    not arrive within timeout_ms is reported by lzb_peer_error instead of hanging the GPU.
- *   lzb_peer_error   0, or 1 + the rank that timed out (synchronises the stream). */
+ *                    not arrive within timeout_ms (<= 0: 30 s) is reported by lzb_peer_error instead of hanging the
+ *                    GPU, and its rows of the result are filled with 0x80000000 (INT_MIN as a count) - never left
+ *                    holding an earlier epoch's data.
+ *   lzb_peer_error   0, or 1 + the rank that timed out (synchronises the stream); a reported error is cleared. */
 int lzb_peer_bytes(int world, int64_t rows_per_rank, int row_words, size_t *bytes);
 int lzb_peer_alloc(size_t bytes, void **buf_dev);
 int lzb_peer_free(void *buf_dev);

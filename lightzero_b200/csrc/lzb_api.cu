@@ -1146,7 +1146,7 @@ int lzb_peer_allgather(void *const *bufs_host, int rank, int world, int64_t rows
     }
     a.ctl = (uint32_t *)bufs_host[rank] + l.ctl_at;
     a.n_pieces = n_pieces; a.rows = (int)rows_per_rank; a.rank = rank; a.world = world; a.epoch = epoch;
-    a.timeout_ns = (timeout_ms > 0 ? timeout_ms : 2000) * 1000000LL;
+    a.timeout_ns = (timeout_ms > 0 ? timeout_ms : 30000) * 1000000LL;
     const long long total = (long long)rows_per_rank * a.row_words;
     const int blocks = (int)std::min<long long>((total + 255) / 256, 128);
     k_peer_allgather<<<blocks, 256, 0, (cudaStream_t)stream>>>(a);
@@ -1163,6 +1163,8 @@ int lzb_peer_error(void *own_buf_dev, int world, int64_t rows_per_rank, int row_
     LZB_CUDA(cudaMemcpyAsync(&e, (uint32_t *)own_buf_dev + l.ctl_at + 1, sizeof(e), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     LZB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
     *error_host = (int)e;
+    if (e != 0) // reported once: the word is cleared so that a later failure can be told from this one
+        LZB_CUDA(cudaMemsetAsync((uint32_t *)own_buf_dev + l.ctl_at + 1, 0, sizeof(uint32_t), (cudaStream_t)stream));
     return LZB_OK;
 }
 

@@ -77,7 +77,15 @@ __global__ void k_peer_allgather(PeerArgs a)
         st_release_sys(a.flags[w] + a.rank, a.epoch); // my shard of this epoch is complete in rank w's buffer
         const long long t0 = global_ns();
         while ((int32_t)(ld_acquire_sys(a.flags[a.rank] + w) - a.epoch) < 0) { // rank w's shard has not landed here yet
-            if (global_ns() - t0 > a.timeout_ns) { a.ctl[1] = 1u + (uint32_t)w; break; } // a peer never arrived: report, do not hang
+            if (global_ns() - t0 > a.timeout_ns) {
+                // a peer never arrived: report it instead of hanging the GPU, and POISON its rows of this epoch's result
+                // (0x80000000 = INT_MIN as a visit count, -0.0f as a value) so that a caller who does not read the error
+                // word cannot mistake a previous epoch's rows for this search's
+                a.ctl[1] = 1u + (uint32_t)w;
+                uint32_t *mine = a.data[a.rank] + (long long)w * a.rows * a.row_words;
+                for (long long t = 0; t < (long long)a.rows * a.row_words; ++t) mine[t] = 0x80000000u;
+                break;
+            }
             __nanosleep(64);
         }
     }

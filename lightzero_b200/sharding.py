@@ -38,6 +38,10 @@ def all_gather_rows(local, counts=None, group=None):
     return torch.cat([out[r * m:r * m + c] for r, c in enumerate(counts)], dim=0)
 
 
+class PeerTimeout(RuntimeError):
+    """A rank's shard did not reach this rank's receive buffer in time (PeerExchange.gather)."""
+
+
 class _RawCuda:
     """A device allocation owned by liblzb200 as something torch.as_tensor can alias (no copy)."""
 
@@ -116,12 +120,22 @@ class PeerExchange:
             x.buf, x.bufs, x.owner = bufs[r], bufs, True
         return ranks
 
-    def gather(self, pieces, timeout_ms=2000):
+    def gather(self, pieces, timeout_ms=30000, check=True):
         """pieces: 32-bit tensors [rows_per_rank, ...] of this rank -> the same tensors for all ranks, [world * rows,
-        ...] (copied out of this rank's receive buffer, which the next-but-one gather reuses)."""
-        return self.collect(self.launch(pieces, timeout_ms))
+        ...] (copied out of this rank's receive buffer, which the next-but-one gather reuses).
 
-    def launch(self, pieces, timeout_ms=2000):
+        ``check`` (default): read the kernel's error word back (one stream synchronisation - the caller reads the
+        results on the host next anyway) and RAISE if a peer did not arrive within ``timeout_ms``: its rows would
+        otherwise be consumed as visit counts.  ``check=False`` leaves that to the caller (``error()``); the rows of a
+        missing peer are poisoned with INT_MIN by the kernel either way."""
+        out = self.collect(self.launch(pieces, timeout_ms))
+        if check:
+            e = self.error()
+            if e:
+                raise PeerTimeout("peer exchange: the shard of rank %d did not arrive within %d ms (epoch %d)" % (e - 1, timeout_ms, self.epoch))
+        return out
+
+    def launch(self, pieces, timeout_ms=30000):
         """First half of ``gather``: enqueue the exchange kernel on the current stream."""
         rows = self.rows
         flat = [p.reshape(rows, -1).contiguous() for p in pieces]
@@ -164,17 +178,17 @@ class PeerExchange:
         self.buf = None
 
 
-def gather_search_outputs(visits, values, counts=None, group=None, extras=(), peer=None):
+def gather_search_outputs(visits, values, counts=None, group=None, extras=(), peer=None, check=True):
     """End-of-search exchange: visit counts [n_r, A] int32 and root values [n_r] f32 (plus Gumbel policies /
     Sampled action tables in `extras`) -> the full batch on every rank.  Everything is 32-bit, so the pieces travel
     together: through ``peer`` (a PeerExchange: one NVLink kernel per rank) when given and the shards are equal,
     else as ONE [n_r, A + 1 + ...] int32 NCCL / gloo all-gather (the exchange is launch-latency bound: 0.6 MB per rank
-    at the headline shape); they are split again on arrival."""
+    at the headline shape); they are split again on arrival.  ``check`` (peer route): see PeerExchange.gather."""
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return [visits, values] + list(extras)
     parts = [visits, values] + list(extras)
     if peer is not None and (counts is None or len(set(counts)) == 1) and all(p.element_size() == 4 for p in parts):
-        return peer.gather(parts)
+        return peer.gather(parts, check=check)  # raises PeerTimeout when a rank's shard did not arrive (check=True)
     if all(p.element_size() == 4 for p in parts):
         n = visits.shape[0]
         cols = [p.reshape(n, -1).view(torch.int32) for p in parts]

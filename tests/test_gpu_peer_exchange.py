@@ -49,10 +49,17 @@ def test_in_process_ranks_exchange_bit_exact(world, rows, A):
 def test_a_missing_peer_times_out_instead_of_hanging():
     import torch
     from lightzero_b200.sharding import PeerExchange
+    from lightzero_b200.sharding import PeerTimeout
     ranks = PeerExchange.local_group(2, 8, 4)
     try:
-        ranks[0].gather([torch.zeros(8, 4, dtype=torch.int32, device="cuda")], timeout_ms=50)  # rank 1 never calls
+        mine = torch.arange(32, dtype=torch.int32, device="cuda").reshape(8, 4)
+        with pytest.raises(PeerTimeout, match="rank 1"):  # rank 1 never calls: the library path raises ...
+            ranks[0].gather([mine], timeout_ms=50)
+        assert ranks[0].error() == 0  # ... and a reported error is cleared
+        (out,) = ranks[0].gather([mine], timeout_ms=50, check=False)  # the caller-checked flavour
         assert ranks[0].error() == 2  # 1 + the rank that did not arrive
+        assert torch.equal(out[:8], mine)
+        assert (out[8:] == -2 ** 31).all(), "the missing rank's rows must be poisoned, never an earlier epoch's data"
     finally:
         for x in ranks:
             x.close()
