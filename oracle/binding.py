@@ -74,11 +74,29 @@ def oracle_lib():
         L.orc_chance_bits.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32]
         L.orc_discrete_draw.restype = C.c_int
         L.orc_discrete_draw.argtypes = [C.POINTER(C.c_double), C.c_int, C.c_double]
+        L.orc_tanhf.restype = C.c_float
+        L.orc_tanhf.argtypes = [C.c_float]
+        L.orc_tanhf_mismatch_range.restype = C.c_long
+        L.orc_tanhf_mismatch_range.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
+        L.orc_libstdcxx_normal.argtypes = [C.c_uint32, C.c_float, C.c_float, C.c_int, C.c_void_p]
+        L.orc_libstdcxx_uniform.argtypes = [C.c_uint32, C.c_int, C.c_void_p]
+        L.orc_sample_libstdcxx.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_void_p]
         for name in ("orc_expf_mismatch_range", "orc_logf_mismatch_range"):
             getattr(L, name).restype = C.c_long
             getattr(L, name).argtypes = [C.c_uint32, C.c_uint32]
         _oracle_lib = L
     return _oracle_lib
+
+
+def sample_libstdcxx(logits, K, D, A, continuous, seed_base):
+    """oracle/libstdcxx_rng.c: the action tables [n, K, D] the reference's expand() draws when its k-th call of a batch
+    sees the clock value seed_base + k (continuous: logits [n, 2D]; discrete: logits [n, A], D = 1)."""
+    logits = _f(logits)
+    n = logits.shape[0]
+    out = np.zeros((n, K, D if continuous else 1), np.float32)
+    oracle_lib().orc_sample_libstdcxx(logits.ctypes.data, n, int(K), int(D), int(A), int(bool(continuous)),
+                                      C.c_uint64(int(seed_base)), out.ctypes.data)
+    return out
 
 
 _ref_libs = {}
@@ -435,7 +453,20 @@ class RefSampledForest(_ForestBase):
         self.n, self.A, self.K, self.W = n, A, K, K
         self.D = A if continuous else 1
         self.continuous, self.per_root = continuous, per_root
+        # None: the reference seeds its sampler from the real clock.  An int: the clock is pinned for the duration of
+        # prepare / backprop so that root i's expand() of expansion e (0 = prepare, s + 1 = simulation s) is seeded with
+        # (unsigned)(clock_base + e * n + i) - the convention oracle/libstdcxx_rng.c and the CUDA parity sampler share
+        self.clock_base = None
+        self.L.ref_clock_pin.argtypes = [C.c_int, C.c_uint64]
         self.h = C.c_void_p(self.L.ref_new(n, A, K, int(continuous), int(per_root)))
+
+    def _pin(self, expansion):
+        if self.clock_base is not None:
+            self.L.ref_clock_pin(1, C.c_uint64((int(self.clock_base) + int(expansion) * self.n) & 0xffffffffffffffff))
+
+    def _unpin(self):
+        if self.clock_base is not None:
+            self.L.ref_clock_pin(0, C.c_uint64(0))
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -454,8 +485,10 @@ class RefSampledForest(_ForestBase):
         nz = None if noises is None else _f(np.asarray(noises, np.float32).reshape(self.n, self.K))
         rewards, logits, to_play = _f(rewards), _f(logits), _i(to_play)
         out = np.zeros((self.n, self.K, self.D), np.float32)
+        self._pin(0)
         self.L.ref_prepare(self.h, int(nz is not None), C.c_float(noise_w), _ptr(nz, C.c_float), _ptr(rewards, C.c_float),
                            _ptr(logits, C.c_float), int(logits.shape[1]), _ptr(to_play, C.c_int), _ptr(out, C.c_float))
+        self._unpin()
         return out
 
     def traverse(self, pb_c_base, pb_c_init, discount, to_play, num_simulations=0, max_considered=0, path_stride=0):
@@ -474,9 +507,11 @@ class RefSampledForest(_ForestBase):
         rewards, values, logits = _f(rewards), _f(values), _f(logits)
         is_reset, to_play = _i(is_reset), _i(to_play)
         out = np.zeros((self.n, self.K, self.D), np.float32)
+        self._pin(latent_index)
         self.L.ref_backprop(self.h, int(latent_index), C.c_float(discount), _ptr(rewards, C.c_float),
                             _ptr(values, C.c_float), _ptr(logits, C.c_float), int(logits.shape[1]),
                             _ptr(is_reset, C.c_int), _ptr(to_play, C.c_int), _ptr(out, C.c_float))
+        self._unpin()
         return out
 
     def distributions(self):

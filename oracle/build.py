@@ -71,7 +71,7 @@ def build_oracle(force=False):
     """Compile the plain-C restatement into oracle/_build/liboracle.so."""
     os.makedirs(ORC_OUT, exist_ok=True)
     so = os.path.join(ORC_OUT, "liboracle.so")
-    srcs = [os.path.join(HERE, f) for f in ("mcts_oracle.c", "glibc_flt32.c", "oracle.h")]
+    srcs = [os.path.join(HERE, f) for f in ("mcts_oracle.c", "glibc_flt32.c", "libstdcxx_rng.c", "oracle.h")]
     srcs = [s for s in srcs if os.path.exists(s)]
     if force or not _newer(so, srcs + [__file__]):
         # -ffp-contract=off: the restatement states every fma() explicitly; nothing else may fuse.

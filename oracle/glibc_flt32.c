@@ -135,3 +135,107 @@ long orc_logf_mismatch_range(uint32_t lo, uint32_t hi)
     }
     return bad;
 }
+
+/* ---------------------------------------------------------------------------------------------------------------
+ * tanhf, as the Sampled-EfficientZero tree calls it on every sampled action (ctree_sampled_efficientzero/lib/
+ * cnode.cpp:268: tanh() on a float resolves to the float overload, i.e. tanhf@GLIBC_2.2.5).  glibc 2.39 still ships
+ * the Sun fdlibm routines for it (sysdeps/ieee754/flt-32/s_tanhf.c on top of s_expm1f.c; no FMA ifunc variant):
+ * plain float arithmetic, restated here operation for operation.  tests/test_sampler_oracle.py pins it against the
+ * live libm (orc_tanhf_mismatch_range).  Constants are the published fdlibm ones.
+ */
+static float orc_expm1f(float x)
+{
+    static const float one = 1.0f, huge = 1.0e+30f, tiny = 1.0e-30f, o_threshold = 8.8721679688e+01f,
+                       ln2_hi = 6.9313812256e-01f, ln2_lo = 9.0580006145e-06f, invln2 = 1.4426950216e+00f,
+                       Q1 = -3.3333335072e-02f, Q2 = 1.5873016091e-03f, Q3 = -7.9365076090e-05f,
+                       Q4 = 4.0082177293e-06f, Q5 = -2.0109921195e-07f;
+    float y, hi, lo, c = 0.0f, t, e, hxs, hfx, r1;
+    int32_t k;
+    uint32_t hx = f2u(x);
+    const uint32_t xsb = hx & 0x80000000u;
+    hx &= 0x7fffffffu;
+    if (hx >= 0x4195b844u) { /* |x| >= 27 ln2 */
+        if (hx >= 0x42b17218u) {
+            if (hx > 0x7f800000u) return x + x;
+            if (hx == 0x7f800000u) return xsb == 0 ? x : -1.0f;
+            if (x > o_threshold) return huge * huge;
+        }
+        if (xsb != 0) return tiny - one;
+    }
+    if (hx > 0x3eb17218u) { /* |x| > 0.5 ln2 */
+        if (hx < 0x3F851592u) { /* |x| < 1.5 ln2 */
+            if (xsb == 0) { hi = x - ln2_hi; lo = ln2_lo; k = 1; }
+            else { hi = x + ln2_hi; lo = -ln2_lo; k = -1; }
+        } else {
+            k = (int32_t)(invln2 * x + (xsb == 0 ? 0.5f : -0.5f));
+            t = (float)k;
+            hi = x - t * ln2_hi;
+            lo = t * ln2_lo;
+        }
+        x = hi - lo;
+        c = (hi - x) - lo;
+    } else if (hx < 0x33000000u) { /* |x| < 2^-25 */
+        t = huge + x;
+        return x - (t - (huge + x));
+    } else k = 0;
+    hfx = 0.5f * x;
+    hxs = x * hfx;
+    r1 = one + hxs * (Q1 + hxs * (Q2 + hxs * (Q3 + hxs * (Q4 + hxs * Q5))));
+    t = 3.0f - r1 * hfx;
+    e = hxs * ((r1 - t) / (6.0f - x * t));
+    if (k == 0) return x - (x * e - hxs);
+    e = (x * (e - c) - c);
+    e -= hxs;
+    if (k == -1) return 0.5f * (x - e) - 0.5f;
+    if (k == 1) return x < -0.25f ? -2.0f * (e - (x + 0.5f)) : one + 2.0f * (x - e);
+    if (k <= -2 || k > 56) {
+        y = one - (e - x);
+        y = u2f(f2u(y) + ((uint32_t)k << 23));
+        return y - one;
+    }
+    if (k < 23) {
+        t = u2f(0x3f800000u - (0x1000000u >> k));
+        y = t - (e - x);
+        y = u2f(f2u(y) + ((uint32_t)k << 23));
+    } else {
+        t = u2f((uint32_t)(0x7f - k) << 23);
+        y = x - (e + t);
+        y += one;
+        y = u2f(f2u(y) + ((uint32_t)k << 23));
+    }
+    return y;
+}
+
+float orc_tanhf(float x)
+{
+    const float one = 1.0f, two = 2.0f, tiny = 1.0e-30f;
+    float t, z;
+    const int32_t jx = (int32_t)f2u(x), ix = jx & 0x7fffffff;
+    if (ix >= 0x7f800000) return jx >= 0 ? one / x + one : one / x - one;
+    if (ix < 0x41b00000) { /* |x| < 22 */
+        if (ix == 0) return x;
+        if (ix < 0x24000000) return x * (one + x);
+        if (ix >= 0x3f800000) {
+            t = orc_expm1f(two * fabsf(x));
+            z = one - two / (t + two);
+        } else {
+            t = orc_expm1f(-two * fabsf(x));
+            z = -t / (t + two);
+        }
+    } else z = one - tiny;
+    return jx >= 0 ? z : -z;
+}
+
+void orc_tanhf_array(const float *x, float *out, long n) { for (long i = 0; i < n; ++i) out[i] = orc_tanhf(x[i]); }
+
+/* bit mismatches against the live libm over the raw float bit range [lo, hi), every `stride`-th pattern */
+long orc_tanhf_mismatch_range(uint32_t lo, uint32_t hi, uint32_t stride)
+{
+    long bad = 0;
+    for (uint64_t u = lo; u < hi; u += stride ? stride : 1) {
+        float x = u2f((uint32_t)u);
+        float a = orc_tanhf(x), b = tanhf(x);
+        if (f2u(a) != f2u(b) && !(a != a && b != b)) ++bad;
+    }
+    return bad;
+}

@@ -30,6 +30,48 @@
 
 extern "C" void ref_rng_set(uint32_t sim, uint32_t root);
 
+// ---- pinned wall clock.  CNode::expand seeds its std::default_random_engine with
+//   unsigned seed = std::chrono::system_clock::now().time_since_epoch().count();          (cnode.cpp:251,336)
+// system_clock::now() is an out-of-line function of libstdc++; this translation unit (which #includes the reference
+// source) defines it, and the library is linked with -Wl,-Bsymbolic, so the reference's calls bind HERE.  Unarmed it
+// reads the real clock; armed (ref_clock_pin) the k-th call returns base + k nanoseconds, which makes the seed of the
+// k-th expand() of a batched call (roots are expanded in index order, cnode.cpp:690-700, 960-967) equal to
+// (unsigned)(base + k).  No reference source is edited.
+#include <time.h>
+namespace {
+bool g_clock_pinned = false;
+uint64_t g_clock_next = 0;
+}
+namespace std { namespace chrono { inline namespace _V2 {
+system_clock::time_point system_clock::now() noexcept
+{
+    if (g_clock_pinned) return time_point(duration(static_cast<rep>(g_clock_next++)));
+    timespec ts;
+    clock_gettime(CLOCK_REALTIME, &ts);
+    return time_point(duration(static_cast<rep>(ts.tv_sec) * 1000000000LL + ts.tv_nsec));
+}
+}}}
+extern "C" void ref_clock_pin(int on, uint64_t next_ns) { g_clock_pinned = on != 0; g_clock_next = next_ns; }
+
+// libstdc++'s own engine + distributions, exposed so that tests can pin the oracle's restatement of their arithmetic
+// against the library itself (independent of the tree): count draws of normal_distribution<float>(mu, sigma), a fresh
+// distribution object per draw exactly as cnode.cpp:262-263 constructs it, from one default_random_engine(seed);
+// and count draws of uniform_real_distribution<double>(0, 1) as cnode.cpp:369,377 uses it.
+extern "C" void ref_libstdcxx_normal(unsigned seed, float mu, float sigma, int count, float *out)
+{
+    std::default_random_engine gen(seed);
+    for (int i = 0; i < count; ++i) {
+        std::normal_distribution<float> d(mu, sigma);
+        out[i] = d(gen);
+    }
+}
+extern "C" void ref_libstdcxx_uniform(unsigned seed, int count, double *out)
+{
+    std::default_random_engine gen(seed);
+    std::uniform_real_distribution<double> d(0.0, 1.0);
+    for (int i = 0; i < count; ++i) out[i] = d(gen);
+}
+
 namespace {
 
 struct Ref {

@@ -102,13 +102,14 @@ def sez_logits(x, continuous):
     return x
 
 
-def run_sez_reference(sc, rng_mode, seed, continuous=True, horizon=5):
+def run_sez_reference(sc, rng_mode, seed, continuous=True, horizon=5, clock_base=None):
     """Drive the compiled Sampled-EfficientZero reference through one search of scenario ``sc`` and RECORD the action
     tables it samples into ``sc.root_actions`` / ``sc.actions`` (what the oracle and the CUDA path are then handed).
     Returns (forest, per-simulation records)."""
     from oracle.binding import RefSampledForest
     env_actions = sc.D if continuous else sc.A
     ref = RefSampledForest(sc.n, env_actions, sc.K, continuous=continuous, per_root=(rng_mode == 2))
+    ref.clock_base = clock_base  # not None: the sampler's wall-clock seed is pinned (oracle/binding.py)
     ref.set_delta(0.01)
     ref.set_rng(rng_mode, seed)
     sc.root_actions = ref.prepare(0.25, None, sc.root_reward, sez_logits(sc.root_logits, continuous), sc.to_play)
