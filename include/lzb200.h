@@ -284,6 +284,17 @@ int lzb_sample_actions_seeded(const float *logits_dev, const float *uniforms_dev
                               int num_sampled, int action_dim, int action_space, int continuous, int root_offset,
                               uint64_t seed, const uint64_t *seed_dev, uint32_t counter, void *stream);
 
+/* PARITY flavour of the sampler: the reference's own draws instead of the counter-based production stream.  Restates what
+ * CNode::expand computes with libstdc++ (GCC 13): std::default_random_engine(seed) = minstd_rand0, per action dimension a
+ * fresh std::normal_distribution<float>(mu, sigma) (Marsaglia polar over generate_canonical<float, 24>) and tanhf
+ * (sez cnode.cpp:251-271), or std::uniform_real_distribution<double> keys pow(u, 1. / p) sorted descending (:336-397).
+ * Root i is seeded with (unsigned)(seed_base + i) - the value the reference's i-th expand() of a batched call takes from
+ * a wall clock that reads seed_base + i nanoseconds.  Continuous tables are bit-identical to the reference's (glibc
+ * 2.39 logf / tanhf restated on the device); discrete tables are identical unless two keys lie within the device
+ * pow()'s 2 ulp of each other.  One thread per root: a test / reproducibility mode, not the fast path. */
+int lzb_sample_actions_libstdcxx(const float *logits_dev, float *out_dev, int num_roots, int num_sampled, int action_dim,
+                                 int action_space, int continuous, uint64_t seed_base, void *stream);
+
 /* ---- InverseScalarTransform of the model's categorical heads (lzero/policy/scaling_transform.py:97-128 with ensure_softmax
  * :36-62), applied by the reference driver to value and reward / value_prefix every simulation (mcts_ctree.py:302-303;
  * :797-798 EfficientZero): logits [N, 2 * support_size + 1] over the support {-s .. s} -> softmax (unless EVERY row of

@@ -207,6 +207,7 @@ _PROTOS = {
     "lzb_sample_actions": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint32, _P]),
     "lzb_sample_actions_seeded": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, _P,
                                             C.c_uint32, _P]),
+    "lzb_sample_actions_libstdcxx": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, _P]),
     "lzb_legal_from_mask": (C.c_int, [_P, C.c_int, C.c_int, _P, _P, _P]),
     "lzb_dirichlet_noise": (C.c_int, [C.c_float, _P, _P, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_uint32, _P]),
     "lzb_select_action": (C.c_int, [C.POINTER(SelectAction), _P]),

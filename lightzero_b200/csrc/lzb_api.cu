@@ -877,6 +877,19 @@ int lzb_sample_actions_seeded(const float *logits_dev, const float *uniforms_dev
     return LZB_OK;
 }
 
+int lzb_sample_actions_libstdcxx(const float *logits_dev, float *out_dev, int num_roots, int num_sampled, int action_dim,
+                                 int action_space, int continuous, uint64_t seed_base, void *stream)
+{
+    if (!logits_dev || !out_dev || num_roots <= 0 || num_sampled <= 0) return fail(LZB_E_ARG, "sample_actions_libstdcxx: bad argument");
+    if (continuous ? action_dim <= 0 : (action_space <= 0 || action_space > 256 || action_dim != 1))
+        return fail(LZB_E_ARG, "sample_actions_libstdcxx: continuous needs action_dim > 0; discrete needs 0 < action_space <= 256 and action_dim == 1");
+    if (!continuous && num_sampled > action_space) return fail(LZB_E_ARG, "sample_actions_libstdcxx: cannot draw %d of %d actions without replacement", num_sampled, action_space);
+    ParitySampleArgs a{logits_dev, out_dev, num_roots, num_sampled, action_dim, action_space, continuous, seed_base};
+    k_sample_actions_libstdcxx<<<(num_roots + 63) / 64, 64, 0, (cudaStream_t)stream>>>(a);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
 int lzb_sample_actions(const float *logits_dev, const float *uniforms_dev, float *out_dev, int num_roots, int num_sampled,
                        int action_dim, int action_space, int continuous, int root_offset, uint64_t seed, uint32_t counter,
                        void *stream)

@@ -102,6 +102,92 @@ __device__ __forceinline__ float glibc_logf(float x)
     return __double2float_rn(y);
 }
 
+// tanhf as glibc 2.39 computes it (sysdeps/ieee754/flt-32/s_tanhf.c over s_expm1f.c: the Sun fdlibm routines, plain
+// float arithmetic, no FMA variant): what the Sampled-EfficientZero tree applies to every sampled action (sez
+// cnode.cpp:268).  Same operations in the same order (this TU never contracts a * b + c); pinned against the host
+// restatement oracle/glibc_flt32.c:orc_tanhf, itself pinned against the live libm.  Used by the parity sampler only.
+__device__ __forceinline__ float glibc_expm1f(float x)
+{
+    const float one = 1.0f, huge = 1.0e+30f, tiny = 1.0e-30f, o_threshold = 8.8721679688e+01f, ln2_hi = 6.9313812256e-01f,
+                ln2_lo = 9.0580006145e-06f, invln2 = 1.4426950216e+00f, Q1 = -3.3333335072e-02f, Q2 = 1.5873016091e-03f,
+                Q3 = -7.9365076090e-05f, Q4 = 4.0082177293e-06f, Q5 = -2.0109921195e-07f;
+    float y, hi, lo, c = 0.0f, t, e, hxs, hfx, r1;
+    int k;
+    uint32_t hx = __float_as_uint(x);
+    const uint32_t xsb = hx & 0x80000000u;
+    hx &= 0x7fffffffu;
+    if (hx >= 0x4195b844u) {
+        if (hx >= 0x42b17218u) {
+            if (hx > 0x7f800000u) return x + x;
+            if (hx == 0x7f800000u) return xsb == 0 ? x : -1.0f;
+            if (x > o_threshold) return huge * huge;
+        }
+        if (xsb != 0) return tiny - one;
+    }
+    if (hx > 0x3eb17218u) {
+        if (hx < 0x3F851592u) {
+            if (xsb == 0) { hi = x - ln2_hi; lo = ln2_lo; k = 1; }
+            else { hi = x + ln2_hi; lo = -ln2_lo; k = -1; }
+        } else {
+            k = __float2int_rz(invln2 * x + (xsb == 0 ? 0.5f : -0.5f));
+            t = (float)k;
+            hi = x - t * ln2_hi;
+            lo = t * ln2_lo;
+        }
+        x = hi - lo;
+        c = (hi - x) - lo;
+    } else if (hx < 0x33000000u) {
+        t = huge + x;
+        return x - (t - (huge + x));
+    } else k = 0;
+    hfx = 0.5f * x;
+    hxs = x * hfx;
+    r1 = one + hxs * (Q1 + hxs * (Q2 + hxs * (Q3 + hxs * (Q4 + hxs * Q5))));
+    t = 3.0f - r1 * hfx;
+    e = hxs * __fdiv_rn(r1 - t, 6.0f - x * t);
+    if (k == 0) return x - (x * e - hxs);
+    e = (x * (e - c) - c);
+    e -= hxs;
+    if (k == -1) return 0.5f * (x - e) - 0.5f;
+    if (k == 1) return x < -0.25f ? -2.0f * (e - (x + 0.5f)) : one + 2.0f * (x - e);
+    if (k <= -2 || k > 56) {
+        y = one - (e - x);
+        y = __uint_as_float(__float_as_uint(y) + ((uint32_t)k << 23));
+        return y - one;
+    }
+    if (k < 23) {
+        t = __uint_as_float(0x3f800000u - (0x1000000u >> k));
+        y = t - (e - x);
+        y = __uint_as_float(__float_as_uint(y) + ((uint32_t)k << 23));
+    } else {
+        t = __uint_as_float((uint32_t)(0x7f - k) << 23);
+        y = x - (e + t);
+        y += one;
+        y = __uint_as_float(__float_as_uint(y) + ((uint32_t)k << 23));
+    }
+    return y;
+}
+
+__device__ __forceinline__ float glibc_tanhf(float x)
+{
+    const float one = 1.0f, two = 2.0f, tiny = 1.0e-30f;
+    float t, z;
+    const int jx = __float_as_int(x), ix = jx & 0x7fffffff;
+    if (ix >= 0x7f800000) return jx >= 0 ? __fdiv_rn(one, x) + one : __fdiv_rn(one, x) - one;
+    if (ix < 0x41b00000) {
+        if (ix == 0) return x;
+        if (ix < 0x24000000) return x * (one + x);
+        if (ix >= 0x3f800000) {
+            t = glibc_expm1f(two * fabsf(x));
+            z = one - __fdiv_rn(two, t + two);
+        } else {
+            t = glibc_expm1f(-two * fabsf(x));
+            z = __fdiv_rn(-t, t + two);
+        }
+    } else z = one - tiny;
+    return jx >= 0 ? z : -z;
+}
+
 // ---------------------------------------------------------------- tie-break stream (include/lzb200.h)
 __host__ __device__ __forceinline__ uint64_t mix64(uint64_t z)
 {

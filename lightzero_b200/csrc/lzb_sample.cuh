@@ -94,13 +94,16 @@ __global__ void k_sample_actions(SampleArgs a)
             key[r] = (p > 0.0f) ? logf(u) / p : -INFINITY; // log of u^(1/p); larger = earlier in the descending sort
         }
     }
+    unsigned taken = 0; // bit r: this lane's action lane + 32 r has been drawn
     for (int k = 0; k < a.K; ++k) {
         float best = -INFINITY;
         int bj = 0x7fffffff;
 #pragma unroll
         for (int r = 0; r < kMaxPerLane; ++r) {
             const int j = lane + 32 * r;
-            if (j < a.A && (key[r] > best || (key[r] == best && j < bj))) { best = key[r]; bj = j; }
+            // actions whose key is -inf (p underflowed to 0, or log(u) / p overflowed) stay candidates until drawn: they
+            // fill the table, lowest id first, once the finite keys are used up - K distinct actions like the reference's sort
+            if (j < a.A && !((taken >> r) & 1u) && (key[r] > best || (key[r] == best && j < bj))) { best = key[r]; bj = j; }
         }
         // warp arg-max, lowest action id on equal keys (std::sort on equal keys is unspecified in the reference)
 #pragma unroll
@@ -109,11 +112,91 @@ __global__ void k_sample_actions(SampleArgs a)
             const int oj = __shfl_xor_sync(kFull, bj, o);
             if (ob > best || (ob == best && oj < bj)) { best = ob; bj = oj; }
         }
-        if (bj == 0x7fffffff) bj = k; // fewer than K actions with p > 0: fill deterministically
+        if (bj == 0x7fffffff) bj = 0; // unreachable for K <= A (checked by the C ABI)
         if (lane == 0) a.out[(size_t)i * a.K + k] = (float)bj;
 #pragma unroll
         for (int r = 0; r < kMaxPerLane; ++r)
-            if (lane + 32 * r == bj) key[r] = -INFINITY; // without replacement
+            if (lane + 32 * r == bj) taken |= 1u << r; // without replacement
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ parity sampler
+// The reference's OWN draws (sez cnode.cpp:251-283, :336-406): std::default_random_engine (minstd_rand0) seeded with the
+// truncated wall clock, std::normal_distribution<float> (Marsaglia polar, a fresh object per draw) or
+// std::uniform_real_distribution<double>, as GCC 13's libstdc++ computes them - restated in oracle/libstdcxx_rng.c (where
+// the algorithm is described and pinned against libstdc++ itself) and here for the device.  Root i is seeded with
+// (unsigned)(seed_base + i): what the reference's i-th expand() of a batched call sees when its clock reads seed_base + i.
+// One thread per root (the engine is a serial chain with data-dependent rejections); production sampling is
+// k_sample_actions above - this mode exists so that the sampler itself is testable bit for bit against the reference.
+struct ParitySampleArgs {
+    const float *logits; // [N, 2D] continuous | [N, A] discrete
+    float *out;          // [N, K, D]
+    int N, K, D, A, continuous;
+    unsigned long long seed_base;
+};
+
+struct MinStd { // linear_congruential_engine<uint_fast32_t, 16807, 0, 2147483647>
+    unsigned long long x;
+    __device__ __forceinline__ explicit MinStd(unsigned seed)
+    {
+        x = (unsigned long long)seed % 2147483647ull;
+        if (x == 0) x = 1;
+    }
+    __device__ __forceinline__ unsigned long long next() { return x = (16807ull * x) % 2147483647ull; }
+    // std::generate_canonical<float, 24>: one draw, float(x - 1) / float(R), R = 2147483646 rounds to 2^31
+    __device__ __forceinline__ float canonical_f32()
+    {
+        const float r = __fdiv_rn(__uint2float_rn((unsigned)(next() - 1ull)), 2147483648.0f);
+        return r >= 1.0f ? __uint_as_float(0x3f7fffffu) : r;
+    }
+    // std::generate_canonical<double, 53>: two draws, (x1 - 1 + (x2 - 1) R) / double(R * R)
+    __device__ __forceinline__ double canonical_f64()
+    {
+        double sum = (double)(next() - 1ull);
+        sum = __dadd_rn(sum, __dmul_rn((double)(next() - 1ull), 2147483646.0));
+        const double r = __ddiv_rn(sum, 0x1.fffffff000000p+61); // double(2147483646^2)
+        return r >= 1.0 ? __longlong_as_double(0x3fefffffffffffffLL) : r;
+    }
+    __device__ __forceinline__ float normal(float mean, float stddev)
+    {
+        float a, b, r2;
+        do {
+            a = 2.0f * canonical_f32() - 1.0f;
+            b = 2.0f * canonical_f32() - 1.0f;
+            r2 = a * a + b * b;
+        } while (r2 > 1.0f || r2 == 0.0f);
+        const float mult = __fsqrt_rn(__fdiv_rn(-2.0f * glibc_logf(r2), r2));
+        return (b * mult) * stddev + mean;
+    }
+};
+
+__global__ void k_sample_actions_libstdcxx(ParitySampleArgs a)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.N) return;
+    MinStd gen((unsigned)(a.seed_base + (unsigned long long)i));
+    if (a.continuous) {
+        const float *mu = a.logits + (size_t)i * 2 * a.D, *sg = mu + a.D;
+        for (int k = 0; k < a.K; ++k)
+            for (int d = 0; d < a.D; ++d) a.out[((size_t)i * a.K + k) * a.D + d] = glibc_tanhf(gen.normal(mu[d], sg[d]));
+        return;
+    }
+    const float *l = a.logits + (size_t)i * a.A;
+    float sum = 0.0f;
+    for (int j = 0; j < a.A; ++j) sum += glibc_expf(l[j]);
+    double key[256];
+    const double den = __dadd_rn((double)sum, 1e-6);
+    for (int j = 0; j < a.A; ++j) {
+        const float p = __double2float_rn(__ddiv_rn((double)glibc_expf(l[j]), den));
+        key[j] = pow(gen.canonical_f64(), __ddiv_rn(1.0, (double)p)); // std::pow(u, 1. / prob), sez cnode.cpp:377
+    }
+    for (int k = 0; k < a.K; ++k) { // the K largest keys, descending (:391-397); equal keys: the lower index first
+        int best = -1;
+        for (int j = 0; j < a.A; ++j)
+            if (key[j] >= 0.0 && (best < 0 || key[j] > key[best])) best = j;
+        if (best < 0) best = 0;
+        key[best] = -1.0; // taken (keys are >= 0)
+        a.out[(size_t)i * a.K + k] = (float)best;
     }
 }
 

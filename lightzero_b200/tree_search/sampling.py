@@ -39,6 +39,22 @@ def sample_actions_cuda(policy_logits, action_space_size, num_of_sampled_actions
     return out
 
 
+def sample_actions_parity(policy_logits, action_space_size, num_of_sampled_actions, continuous_action_space, seed_base):
+    """The reference's own draws (libstdc++ minstd_rand0 + normal_distribution<float> / uniform_real<double>, C ABI
+    lzb_sample_actions_libstdcxx): root i is seeded with (unsigned)(seed_base + i), what the reference's expand() takes from
+    a wall clock reading seed_base + i ns.  A test / reproducibility mode (one thread per root)."""
+    from .. import _lib
+    x = policy_logits.float().contiguous()
+    N, K = x.shape[0], int(num_of_sampled_actions)
+    D = x.shape[1] // 2 if continuous_action_space else 1
+    out = torch.empty((N, K, D), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().lzb_sample_actions_libstdcxx(
+            C.c_void_p(x.data_ptr()), C.c_void_p(out.data_ptr()), N, K, D, x.shape[1], int(bool(continuous_action_space)),
+            C.c_uint64(int(seed_base) & 0xffffffffffffffff), C.c_void_p(torch.cuda.current_stream(x.device).cuda_stream)))
+    return out
+
+
 def sample_actions(policy_logits, action_space_size, num_of_sampled_actions, continuous_action_space, generator=None,
                    seed=None, counter=0, root_offset=0):
     """policy_logits [N, 2D] (mu | sigma) for continuous, [N, A] for discrete.  Returns float32 [N, K, D] (D=1 discrete).

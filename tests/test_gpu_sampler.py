@@ -76,3 +76,74 @@ def test_draws_are_counter_based():
     assert not torch.equal(a, sample_actions_cuda(logits, 4, 6, True, seed=10, counter=2))
     # sharding: roots [16, 32) drawn as a shard with root_offset 16 equal the same roots of the full batch
     assert torch.equal(a[16:], sample_actions_cuda(logits[16:], 4, 6, True, seed=9, counter=2, root_offset=16))
+
+
+# ------------------------------------------------------------------------------------------------ parity sampler (a15)
+def test_device_tanhf_matches_the_oracle_restatement():
+    """glibc_tanhf on the device == oracle/glibc_flt32.c:orc_tanhf (itself pinned against the live libm) bit for bit,
+    through the parity sampler: sigma = 0 makes every draw equal mu, so out = tanhf(mu)."""
+    import ctypes as C
+    import torch
+    from lightzero_b200.tree_search.sampling import sample_actions_parity
+    from oracle.binding import oracle_lib
+    rng = np.random.default_rng(3)
+    xs = np.concatenate([rng.standard_normal(20000).astype(np.float32) * 3, np.linspace(-25, 25, 5001, dtype=np.float32),
+                         np.array([0.0, -0.0, 1e-10, -1e-10, 0.34, 0.35, 1.0, -1.0, 1.04, 21.9, 22.0, 22.1, 88.0, -88.0], np.float32)])
+    D = len(xs)
+    logits = np.concatenate([xs, np.zeros(D, np.float32)])[None, :]  # one root: mu = xs, sigma = 0
+    got = sample_actions_parity(torch.from_numpy(logits).cuda(), D, 1, True, seed_base=1).cpu().numpy().reshape(-1)
+    want = np.empty_like(xs)
+    O = oracle_lib()
+    O.orc_tanhf_array.argtypes = [C.c_void_p, C.c_void_p, C.c_long]
+    O.orc_tanhf_array(xs.ctypes.data, want.ctypes.data, D)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), "%d of %d differ" % ((got.view(np.uint32) != want.view(np.uint32)).sum(), D)
+
+
+@pytest.mark.parametrize("name", ["sez_sampler_continuous_k20_d6", "sez_sampler_discrete_k4_of_6", "sez_sampler_discrete_k5_of_18"])
+def test_cuda_sampler_reproduces_the_reference_tables_and_search(name):
+    """Row a15 closed: the CUDA sampler itself - not an injected table - reproduces the action tables the compiled,
+    unmodified reference tree sampled under a pinned clock (tests/golden/sez_sampler_*.npz), bit for bit, and the search
+    run on the CUDA-sampled tables matches the reference's leaf indices, last actions, visit counts and root values."""
+    import os
+    import torch
+    from lightzero_b200.tree_search.sampling import sample_actions_parity
+    from tests.common import Scenario, assert_same, sez_logits
+    from tests.test_gpu_tree_parity import run_gpu
+    from tests.test_sampler_oracle import SAMPLER_CASES
+    kw, continuous = SAMPLER_CASES[name]
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name + ".npz"))
+    sc = Scenario(**kw)
+    clock = int(g["clock_base"])
+    dev = torch.device("cuda", 0)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    root = sample_actions_parity(t(sez_logits(sc.root_logits, continuous)), sc.A, sc.K, continuous, seed_base=clock)
+    sims = torch.stack([sample_actions_parity(t(sez_logits(sc.logits[s], continuous)), sc.A, sc.K, continuous,
+                                              seed_base=clock + (s + 1) * sc.n) for s in range(sc.S)])
+    assert_same(root.cpu().numpy(), g["root_actions"], name + ": root action tables")
+    assert_same(sims.cpu().numpy(), g["actions"], name + ": per-simulation action tables")
+    # the search on the tables the CUDA sampler drew
+    sc.root_actions, sc.actions = root.cpu().numpy(), sims.cpu().numpy()
+    rec = []
+    gpu = run_gpu(sc, 1, 2024, record=rec, fused=True)
+    for k in ("ix", "search_len", "vtp", "last_action_f", "is_reset"):
+        assert_same(np.stack([r[k] for r in rec]), g[k], "%s/%s" % (name, k))
+    out = gpu.root_outputs(sc.discount)
+    assert_same(out["visits"].cpu().numpy(), np.where(g["dist"] < 0, 0, g["dist"]), name + "/visit counts")
+    assert_same(out["values"].cpu().numpy(), g["values"], name + "/root values")
+
+
+def test_discrete_sampler_never_repeats_an_action_when_probabilities_underflow():
+    """K larger than the number of actions with a usable key (masked / extreme logits: p underflows to 0, or log(u) / p
+    overflows to -inf): the table still holds K DISTINCT action ids, the finite keys first."""
+    import torch
+    from lightzero_b200.tree_search.sampling import sample_actions_cuda
+    N, A, K = 64, 40, 12
+    logits = torch.full((N, A), -200.0)           # exp(-200 - max) underflows: p == 0 for all but three actions
+    logits[:, 5], logits[:, 17], logits[:, 33] = 3.0, 2.0, 2.5
+    for counter in range(4):
+        a = sample_actions_cuda(logits.cuda(), A, K, False, seed=9, counter=counter).cpu().numpy()[:, :, 0].astype(int)
+        assert a.shape == (N, K) and a.min() >= 0 and a.max() < A
+        for row in a:
+            assert len(set(row.tolist())) == K, row
+            assert set(row[:3].tolist()) == {5, 17, 33}
+            assert row[3:].tolist() == sorted(row[3:].tolist()), "zero-probability actions fill the tail lowest id first"
