@@ -309,6 +309,12 @@ class OracleForest(_ForestBase):
         self.L.orc_root_stats(self.h, _ptr(vc, C.c_int), _ptr(vs, C.c_float), _ptr(rw, C.c_float))
         return vc, vs, rw
 
+    def trajectories(self, stride):
+        out = np.full((self.n, stride), -1, np.int32)
+        ln = np.zeros(self.n, np.int32)
+        self.L.orc_trajectories(self.h, _ptr(out, C.c_int), int(stride), _ptr(ln, C.c_int))
+        return out, ln
+
     def sampled_actions(self):
         out = np.zeros((self.n, self.K, self.D), np.float32)
         self.L.orc_sampled_actions(self.h, _ptr(out, C.c_float))
@@ -434,6 +440,12 @@ class RefForest(_ForestBase):
         vc, vs, rw = np.zeros(self.n, np.int32), np.zeros(self.n, np.float32), np.zeros(self.n, np.float32)
         self.L.ref_root_stats(self.h, _ptr(vc, C.c_int), _ptr(vs, C.c_float), _ptr(rw, C.c_float))
         return vc, vs, rw
+
+    def trajectories(self, stride):
+        out = np.full((self.n, stride), -1, np.int32)
+        ln = np.zeros(self.n, np.int32)
+        self.L.ref_trajectories(self.h, _ptr(out, C.c_int), int(stride), _ptr(ln, C.c_int))
+        return out, ln
 
     def dump_tree(self, i, E):
         return _dump(lambda *a: self.L.ref_dump_tree(self.h, *a), i, E, self.A)

@@ -908,6 +908,27 @@ void orc_dump_tree(OrcForest *f, int i, int E, int *visit, float *value_sum, flo
     free(stack); free(pes);
 }
 
+/* CRoots::get_trajectories -> CNode::get_trajectory (mz:237-257, 369-385): follow best_action (an action id, set by
+ * every traverse that selected from the node, mz:806) from the root until a node that was never selected from.
+ * out [n, stride] (entries beyond stride dropped), len[i] = the true length. */
+void orc_trajectories(OrcForest *f, int *out, int stride, int *len)
+{
+    for (int i = 0; i < f->n; ++i) {
+        Node *nd = &f->roots[i];
+        int d = 0;
+        while (nd->best_action >= 0) {
+            if (d < stride) out[(size_t)i * stride + d] = nd->best_action;
+            d += 1;
+            Node *next = NULL; /* get_child(action): the child stored under that action id (mz:279-288) */
+            for (int j = 0; j < nd->n_children; ++j)
+                if (nd->legal[j] == nd->best_action) { next = &nd->children[j]; break; }
+            if (!next) break;
+            nd = next;
+        }
+        len[i] = d;
+    }
+}
+
 void orc_root_stats(OrcForest *f, int *visit, float *value_sum, float *reward)
 {
     for (int i = 0; i < f->n; ++i) {

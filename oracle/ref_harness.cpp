@@ -380,6 +380,20 @@ void ref_dump_tree(void *h, int i, int E, int *visit, float *value_sum, float *p
     }
 }
 
+// CRoots::get_trajectories (cnode.cpp:369-385; Gumbel :563-579): out [n, stride], len[i] = true length
+void ref_trajectories(void *h, int *out, int stride, int *len)
+{
+    Ref *r = (Ref *)h;
+    for (int g = 0; g < r->groups(); ++g) {
+        std::vector<std::vector<int> > t = r->roots[g]->get_trajectories();
+        for (int k = 0; k < r->gsize(); ++k) {
+            int i = g * r->gsize() + k;
+            len[i] = (int)t[k].size();
+            for (int d = 0; d < (int)t[k].size() && d < stride; ++d) out[(size_t)i * stride + d] = t[k][d];
+        }
+    }
+}
+
 void ref_root_stats(void *h, int *visit, float *value_sum, float *reward)
 {
     Ref *r = (Ref *)h;

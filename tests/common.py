@@ -14,10 +14,12 @@ class Scenario:
     """Seeded inputs of one search: root logits / rewards / values / noise and per-simulation model outputs."""
 
     def __init__(self, variant, n, A, S, seed=0, legal=None, to_play=None, discount=0.997, max_considered=4,
-                 reward_scale=0.1, zero_model=False, K=0, D=0, reuse=False):
+                 reward_scale=0.1, zero_model=False, K=0, D=0, reuse=False, no_noise=False, trajectories=False):
         rng = np.random.default_rng(seed)
         self.variant, self.n, self.A, self.S, self.discount, self.m = variant, n, A, S, discount, max_considered
         self.K, self.D = K, D
+        self.no_noise = no_noise          # the evaluation path: Roots.prepare_no_noise (lzero/policy/muzero.py:831)
+        self.trajectories = trajectories  # the fixture also carries get_trajectories()
         W = self.W = max(A, K) if variant == "smz" else A  # smz: K = chance_space_size, rows hold policy OR chance logits
         self.legal = legal if legal is not None else [list(range(A)) for _ in range(n)]
         self.to_play = np.asarray(to_play if to_play is not None else [-1] * n, np.int32)
@@ -76,8 +78,9 @@ def run_cpu(forest, sc, rng_mode, seed, record=None, horizon=5):
     kw = {}
     if sc.variant == "sez":
         kw["sampled_actions"] = sc.root_actions
-    forest.prepare(0.25, sc.noises if sc.variant != "sez" else None, sc.root_reward, sc.root_logits, sc.to_play,
-                   values=sc.root_value, **kw)
+    with_noise = sc.variant != "sez" and not getattr(sc, "no_noise", False)
+    forest.prepare(0.25 if with_noise or sc.variant == "sez" else 0.0, sc.noises if with_noise else None, sc.root_reward,
+                   sc.root_logits, sc.to_play, values=sc.root_value, **kw)
     if sc.variant == "smz":
         forest.run_search_chance(sc.model_fn_chance, sc.S, PB_C_BASE, PB_C_INIT, sc.discount, sc.to_play,
                                  forced=None if forest.__class__.__name__.startswith("Ref") else sc.forced, record=record)

@@ -52,6 +52,10 @@ def test_cuda_path_matches_reference_golden(name, fused):
         for k in ("visit", "value_sum", "prior", "reward", "child_e", "hdr"):
             if "tree%d_%s" % (i, k) in want.files:  # sampled tree: priors never reach selection and are not kept
                 assert_same(t[k], want["tree%d_%s" % (i, k)], "%s/tree%d_%s" % (name, i, k))
+    if "trajectories" in want.files:  # get_trajectories against the compiled reference's (cnode.cpp:237-257, 369-385)
+        acts, ln = gpu.trajectories()
+        assert_same(ln.cpu().numpy(), want["trajectory_len"], name + "/trajectory lengths")
+        assert_same(acts.cpu().numpy(), want["trajectories"], name + "/trajectories")
     if sc.variant == "gmz":
         assert_same(out["policies"].cpu().numpy(), want["gmz_policies"], name + "/improved policy")
         assert_same(out["children_values"].cpu().numpy(), want["gmz_child_values"], name + "/completed child values")

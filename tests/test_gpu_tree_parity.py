@@ -27,8 +27,9 @@ def run_gpu(sc, rng_mode, seed, record=None, horizon=5, root_offset=0, fused=Fal
     if sc.variant == "sez":
         f.prepare(None, None, 0.25, t(sc.root_reward), t(sc.to_play), sampled_actions=t(sc.root_actions))
     else:
-        f.prepare(t(sc.root_logits), t(sc.noise_pad), 0.25, t(sc.root_reward), t(sc.to_play),
-                  value=t(sc.root_value) if sc.variant == "gmz" else None)
+        no_noise = getattr(sc, "no_noise", False)  # prepare_no_noise: no noise tensor, weight 0
+        f.prepare(t(sc.root_logits), None if no_noise else t(sc.noise_pad), 0.0 if no_noise else 0.25, t(sc.root_reward),
+                  t(sc.to_play), value=t(sc.root_value) if sc.variant == "gmz" else None)
     players = 1 if int(sc.to_play.max()) == -1 else 2
     cfg = f.make_cfg(PB_C_BASE, PB_C_INIT, sc.discount, players=players, num_simulations=sc.S,
                      max_num_considered_actions=sc.m, rng_mode=rng_mode, rng_seed=seed)

@@ -32,6 +32,14 @@ CASES = {
     "gmz_tictactoe": (dict(variant="gmz", n=16, A=9, S=30, seed=11, legal=LEGAL9, discount=1.0, max_considered=3), 1),
     "gmz_gomoku": (dict(variant="gmz", n=32, A=36, S=50, seed=12, discount=1.0, max_considered=6), 1),
     "gmz_m16": (dict(variant="gmz", n=16, A=18, S=50, seed=13, max_considered=16), 1),
+    # the evaluation path: Roots.prepare_no_noise (lzero/policy/muzero.py:831; cnode.cpp:340-358); these fixtures also
+    # carry CRoots::get_trajectories (cnode.cpp:237-257, 369-385)
+    "mz_eval_no_noise": (dict(variant="mz", n=32, A=18, S=50, seed=41, no_noise=True, trajectories=True), 2),
+    "mz_eval_no_noise_masks_two_player": (dict(variant="mz", n=16, A=9, S=40, seed=42, legal=LEGAL9, to_play=[1, 2] * 8,
+                                               discount=1.0, no_noise=True, trajectories=True), 1),
+    "ez_eval_no_noise": (dict(variant="ez", n=32, A=6, S=50, seed=43, no_noise=True, trajectories=True), 2),
+    "gmz_eval_no_noise": (dict(variant="gmz", n=16, A=9, S=30, seed=44, legal=LEGAL9, discount=1.0, max_considered=3,
+                               no_noise=True, trajectories=True), 1),
     # ReZero search_with_reuse (mcts_ctree.py:323-420, 829-953)
     "mz_reuse_a6": (dict(variant="mz", n=32, A=6, S=50, seed=14, reuse=True), 2),
     "mz_reuse_batch": (dict(variant="mz", n=16, A=18, S=50, seed=15, reuse=True), 1),
@@ -87,6 +95,8 @@ def search_summary(forest, sc, rec, trees=3):
             out["tree%d_%s" % (i, k)] = t[k]
     if sc.variant == "gmz":
         out["gmz_policies"], out["gmz_child_values"] = forest.gumbel_outputs(sc.discount)
+    if getattr(sc, "trajectories", False):
+        out["trajectories"], out["trajectory_len"] = forest.trajectories(sc.S + 1)
     return out
 
 
