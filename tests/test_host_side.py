@@ -203,6 +203,15 @@ def test_list_marshalling_parallel_paths_and_int_lists():
     from lightzero_b200 import _lib
     from lightzero_b200.forest import _floats_from_lists, _ints_from_list
     P = _lib.pylist()
+    _list_marshalling_checks(P, _floats_from_lists, _ints_from_list, gc)
+    os.environ["LZB_PYLIST_THREADS"] = "4"  # the opt-in threaded readers (read per call)
+    try:
+        _list_marshalling_checks(P, _floats_from_lists, _ints_from_list, gc)
+    finally:
+        del os.environ["LZB_PYLIST_THREADS"]
+
+
+def _list_marshalling_checks(P, _floats_from_lists, _ints_from_list, gc):
     rng = np.random.default_rng(5)
     N, A = 4096, 18
     x = rng.standard_normal((N, A)).astype(np.float32)
