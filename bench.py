@@ -60,7 +60,16 @@ def parse_args():
                     help="the model emits CATEGORICAL value / reward heads ([N, 2 * support + 1] logits, every shipped Atari config) and "
                          "the driver applies InverseScalarTransform every simulation (mcts_ctree.py:302-303) - the fused CUDA kernel")
     ap.add_argument("--support", type=int, default=300, help="support_scale of the categorical heads (300 -> 601 bins)")
-    return ap.parse_args()
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: --roots per GPU whatever N is (the contract's default); strong: --roots-total roots split over the N GPUs")
+    ap.add_argument("--roots-total", type=int, default=65536, help="roots of the whole job under --scaling strong")
+    a = ap.parse_args()
+    if a.scaling == "strong":
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        if a.roots_total % world:
+            ap.error("--roots-total must be a multiple of the number of GPUs")
+        a.roots = a.roots_total // world
+    return a
 
 
 def workload_name(a):
@@ -549,7 +558,7 @@ def run_reference_arm(a):
     print(json.dumps({
         "impl": "reference", "metric": "mcts_simulations_per_sec", "value": round(v, 1), "unit": "simulations/s",
         "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": a.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(a, a.gpus),
         "run": {"host_cpu": cpu, "processes": P, "marshalling": "flat arrays through oracle/ref_harness.cpp: Cython's list -> "
                 "std::vector copies (~9 % of the reference's time, SURVEY 6) are NOT included, which flatters the reference"},
@@ -791,7 +800,7 @@ def run_b200_arm(a):
         line = {
             "metric": "mcts_simulations_per_sec", "value": round(total_sims / (ms_step * 1e-3), 1), "unit": "simulations/s",
             "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": round(ms_step, 4),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": a.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(a, world),
             "run": {"cuda_graph": not a.no_graph, "search_streams": 1 if a.no_graph else a.streams,
                     "l2": "512 MB flush between timed steps; working set > L2",

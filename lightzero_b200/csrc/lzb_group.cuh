@@ -11,6 +11,9 @@
 // serial left-to-right sums in legal-action order (adding +0.0f for skipped entries is exact because a running
 // sum that starts at +0.0f can never become -0.0f), glibc-exact expf / logf.
 #pragma once
+#if defined(LZB_X_CARRY) && !defined(LZB_X_EARLY_PATH)
+#define LZB_X_EARLY_PATH
+#endif
 #include "lzb_expand.cuh"
 #include "lzb_select.cuh"
 
@@ -266,18 +269,31 @@ __device__ __forceinline__ int chance_draw_g(const int4 (&c)[R], int n, double u
 // VAR = LZB_SMZ (Stochastic MuZero, smz cnode.cpp:596-660,713-787): nodes at odd depth are chance nodes whose outcome
 // is drawn from their priors (chance_draw_g) instead of scored; every going group of a warp is at the same depth, so
 // the decision / chance branch is warp-uniform.
+// experiment LZB_X_CARRY (fused step kernel only): what the backup half already holds in registers and the select half
+// would otherwise load again - behind the backup's stores, so as one more exposed round trip at the head of the
+// simulation's dependent chain - is handed over instead: the tree's updated MinMax pair and root record, plus the
+// per-tree inputs no kernel of the search writes (to_play, the players word, the tie-break seed), which are requested at
+// the top of the kernel.
+struct Carry {
+    float2 mm;
+    int4 root;
+    int to_play, players_word;
+    unsigned long long tie_seed;
+};
+
 template <int VAR, int G, int R, bool REUSE = false>
-__device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a, int i, bool live, const Grp<G> &grp, int tl = -1)
+__device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a, int i, bool live, const Grp<G> &grp, int tl = -1,
+                                              const Carry *carry = nullptr)
 {
     constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
     const int B = p.B, A = p.A, lane = grp.lane;
     const int4 *tree = p.tree(i);
     int4 *pa = p.path_a + (size_t)i * (p.S + 1);
     int2 *pb = p.path_b + (size_t)i * (p.S + 1);
-    const float2 mm = p.minmax[i];
-    const int4 rt = p.root[i];
-    int vtp = a.to_play[i];
-    const int players = a.players ? a.players : ((p.scratch[0] == -1) ? 1 : 2); // cnode.cpp:776-781
+    const float2 mm = carry ? carry->mm : p.minmax[i];
+    const int4 rt = carry ? carry->root : p.root[i];
+    int vtp = carry ? carry->to_play : a.to_play[i];
+    const int players = a.players ? a.players : (((carry ? carry->players_word : p.scratch[0]) == -1) ? 1 : 2); // cnode.cpp:776-781
     const float g = a.discount;
     const float mm_delta = mm.y - mm.x;
     const float mm_den = (mm_delta < a.delta) ? a.delta : mm_delta; // CMinMaxStats::normalize (cminimax.cpp:33-45)
@@ -295,7 +311,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     bool going = live; // this group is still descending
     bool no_inference = false;
     int level = 0;   // rounds of the loop below == depth of every group that is still going (warp-uniform)
-    const unsigned long long tie_seed = a.seed_dev ? *a.seed_dev : a.seed; // issued with the other entry loads
+    const unsigned long long tie_seed = carry ? carry->tie_seed : (a.seed_dev ? *a.seed_dev : a.seed); // issued with the other entry loads
     unsigned long long chance_seed = tie_seed;
     if (VAR == LZB_SMZ && a.chance_seed) chance_seed = *a.chance_seed;
     bool is_true[R]; // root position j holds the trajectory's action
@@ -745,7 +761,8 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
 // node is not expanded again and backs up reuse_value; a tree that expanded the root's true-action child backs up
 // reuse_value instead of the model's value.
 template <int VAR, int G, int R, bool REUSE = false>
-__device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs &a, int i, bool live, const Grp<G> &grp, int tl = -1)
+__device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs &a, int i, bool live, const Grp<G> &grp, int tl = -1,
+                                                Carry *carry = nullptr)
 {
     constexpr bool VP = (VAR == LZB_EZ || VAR == LZB_SEZ);
     const int A = p.A, lane = grp.lane;
@@ -781,6 +798,28 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     const int4 *pa = p.path_a + (size_t)i * (p.S + 1);
     const int2 *pb = p.path_b + (size_t)i * (p.S + 1);
     const int4 root_rec = p.root[i]; // independent of the depth: issued now
+    constexpr bool kPow2G = (G & (G - 1)) == 0;
+    (void)kPow2G;
+#ifdef LZB_X_EARLY_PATH
+    // experiment: the first chunk's path records (one per lane) and the tree's MinMax pair are requested HERE, before the
+    // leaf's softmax, whose expf work then hides their round trip (they were requested after it: +1.0 k and +0.5 k cycles
+    // of exposed latency in profiles/r01_step_timeline_*.txt).  Nothing below writes what these loads read.
+    int4 pre_r = make_int4(0, 0, 0, 0);
+    int pre_tp = 0, pre_reset = 0;
+    float pre_vp = 0.0f;
+    {
+        const int q = depth - lane;
+        if (live && q >= 1) {
+            pre_r = pa[q - 1];
+            if (VAR != LZB_GMZ && to_play != -1 && q != depth) pre_tp = pb[q].x;
+            if (VP) {
+                if (q >= 2) pre_vp = __int_as_float(pa[q - 2].w);
+                pre_reset = pb[q - 1].y;
+            }
+        }
+    }
+    const float2 pre_mm = p.minmax[i];
+#endif
     int leaf_reset = 0;
     if (VP) {
         if (a.is_reset) leaf_reset = a.is_reset[i];
@@ -845,6 +884,9 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     const float g = a.discount;
     float b = value_propagate; // bootstrap_value entering the current chunk
     float cmin = kFloatMax, cmax = kFloatMin;
+#ifdef LZB_X_CARRY
+    int4 new_root = root_rec;
+#endif
     for (int qhi = depth; __any_sync(kFull, qhi >= 0); qhi -= G) { // every group runs as many chunks as the deepest one
         const int q = qhi - lane;
         const bool valid = live && q >= 0;
@@ -854,15 +896,27 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
             if (q == 0) {
                 x = root_rec.x; vsum = __int_as_float(root_rec.y); rew = __int_as_float(root_rec.z);
             } else {
+#ifdef LZB_X_EARLY_PATH
+                const int4 r = (qhi == depth) ? pre_r : pa[q - 1];
+#else
                 const int4 r = pa[q - 1];
+#endif
                 slot = r.x; x = r.y; vsum = __int_as_float(r.z); rew = __int_as_float(r.w);
                 if (q == depth && !no_inference) rew = leaf_chance ? 0.0f : leaf_reward; // expand() stamps the leaf's reward / value_prefix first
             }
+#ifdef LZB_X_EARLY_PATH
+            if (two) node_tp = (q == depth) ? to_play : ((qhi == depth) ? pre_tp : pb[q].x);
+            if (VP && q >= 1) {
+                parent_vp = (q == 1) ? __int_as_float(root_rec.z) : ((qhi == depth) ? pre_vp : __int_as_float(pa[q - 2].w));
+                parent_reset = (qhi == depth) ? pre_reset : pb[q - 1].y;
+            }
+#else
             if (two) node_tp = (q == depth) ? to_play : pb[q].x;
             if (VP && q >= 1) {
                 parent_vp = (q == 1) ? __int_as_float(root_rec.z) : __int_as_float(pa[q - 2].w);
                 parent_reset = pb[q - 1].y;
             }
+#endif
         }
         if (qhi == depth) LZB_TLD(tl, 18, __float_as_int(rew) ^ x);
         float r_pre = rew, r_boot = rew;
@@ -896,6 +950,9 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
             cmax = fmaxf(cmax, cand);
             if (q == 0) {
                 p.root[i] = make_int4(visits, __float_as_int(vsum), __float_as_int(rew), 0);
+#ifdef LZB_X_CARRY
+                new_root = make_int4(visits, __float_as_int(vsum), __float_as_int(rew), 0);
+#endif
             } else {
                 int4 *rec = p.tree(i) + slot;
                 const int exp_idx = (q == depth && !no_inference) ? e_new : child_expansion(x);
@@ -907,12 +964,30 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     cmin = grp.fmin(cmin);
     cmax = grp.fmax(cmax);
     LZB_TLD(tl, 21, __float_as_int(cmin) ^ __float_as_int(cmax));
+#ifdef LZB_X_CARRY
+    {   // every lane holds the pair (same-address load above), so every lane can form the update; lane 0 stores it
+        float2 mm = pre_mm;
+        mm.x = fminf(mm.x, cmin); // CMinMaxStats::update (cminimax.cpp:23-31)
+        mm.y = fmaxf(mm.y, cmax);
+        if (lane == 0 && live) p.minmax[i] = mm;
+        if (carry) {
+            carry->mm = mm;
+            const int src = kPow2G ? (depth & (G - 1)) : (depth % G); // the lane that held node 0 in the last chunk
+            carry->root = grp.shfl(new_root, src);
+        }
+    }
+#else
     if (lane == 0 && live) {
+#ifdef LZB_X_EARLY_PATH
+        float2 mm = pre_mm;
+#else
         float2 mm = p.minmax[i];
+#endif
         mm.x = fminf(mm.x, cmin); // CMinMaxStats::update (cminimax.cpp:23-31)
         mm.y = fmaxf(mm.y, cmax);
         p.minmax[i] = mm;
     }
+#endif
     LZB_TL(tl, 4);
 }
 
@@ -963,6 +1038,19 @@ __global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_step_g(Pool p, BackupAr
     pdl_wait();
     LZB_TL(tl, 2);
     if (blockIdx.x == 0 && threadIdx.x < b.n_slots) p.slots[(size_t)threadIdx.x * p.E + b.latent_index] = pick3(b.new_slot, threadIdx.x);
+#ifdef LZB_X_CARRY
+    if constexpr (VAR != LZB_GMZ) {
+        Carry carry;
+        const int it = live ? i : 0;
+        carry.to_play = a.to_play[it];
+        carry.players_word = p.scratch[0];
+        carry.tie_seed = a.seed_dev ? *a.seed_dev : a.seed;
+        expand_backup_g<VAR, G, R, REUSE>(p, b, it, live, grp, tl, &carry);
+        __syncwarp();
+        select_puct_g<VAR, G, R, REUSE>(p, a, it, live, grp, tl, &carry);
+        return;
+    }
+#endif
     expand_backup_g<VAR, G, R, REUSE>(p, b, live ? i : 0, live, grp, tl);
     __syncwarp(); // the warp's own global writes (records, root, MinMax) are ordered before its reads below
     if constexpr (VAR == LZB_GMZ) select_gumbel_g<G, R>(p, a, live ? i : 0, live, grp);

@@ -7,6 +7,9 @@
 // them, pUCT arg-maxes.  So the same algorithm is evaluated here in fp64 with the fused operations
 // the x86-64 FMA build of glibc performs.  This translation unit is compiled with -fmad=false: the
 // only fused multiply-adds are the explicit fma() calls below.
+// Provenance and licences of the restated routines (Arm Optimized Routines / glibc expf, logf: MIT / LGPL-2.1+;
+// fdlibm tanhf, expm1f: Copyright (C) 1993 by Sun Microsystems, Inc., "Permission to use, copy, modify, and distribute
+// this software is freely granted, provided that this notice is preserved."): THIRD_PARTY_NOTICES.md at the repo root.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>

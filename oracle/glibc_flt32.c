@@ -11,6 +11,10 @@
  * fused operations below are the ones that build performs (read from its disassembly), so results
  * are bit-identical to the host libm on such machines.  tests/test_libm_restatement.py pins this
  * against the live libm over hundreds of millions of inputs.
+ *
+ * Provenance and licences (Arm Optimized Routines / glibc expf, logf: MIT / LGPL-2.1+; fdlibm tanhf, expm1f: Copyright (C)
+ * 1993 by Sun Microsystems, Inc., "Permission to use, copy, modify, and distribute this software is freely granted,
+ * provided that this notice is preserved."): THIRD_PARTY_NOTICES.md at the repo root.
  */
 #include <math.h>
 #include <stdint.h>
