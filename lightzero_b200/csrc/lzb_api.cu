@@ -57,8 +57,10 @@ constexpr size_t kAlign = 256;
 inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 
 struct Layout {
-    size_t node, root, legal, minmax, path_a, path_b, res, best, bidx, actions, gumbel, vtable, scratch, slots, pbc, total;
+    size_t node, root, legal, minmax, path_a, path_b, res, best, bidx, actions, gumbel, vtable, scratch, slots, pbc, pbc2, cval, total;
 };
+
+constexpr size_t kPbc2MaxW = 1024;
 
 Layout make_layout(int variant, int N, int A, int S, int D)
 {
@@ -81,6 +83,13 @@ Layout make_layout(int variant, int N, int A, int S, int D)
     l.scratch = take(4 * sizeof(int));
     l.slots = take((size_t)kMaxGathers * E * sizeof(char *));
     l.pbc = take((E + 1) * sizeof(float2));
+    l.pbc2 = l.cval = 0;
+#ifdef LZB_X_PBC2 // experiment: the whole pb_c factor from a table (searches of up to kPbc2MaxSims simulations)
+    l.pbc2 = take((variant != LZB_GMZ && E + 1 <= kPbc2MaxW) ? (E + 1) * (E + 1) * sizeof(float) : 0);
+#endif
+#ifdef LZB_X_CVAL // experiment: child values cached by the backup
+    l.cval = take(variant != LZB_GMZ ? (size_t)N * E * (A + 1) * sizeof(float) : 0);
+#endif
     l.total = o;
     return l;
 }
@@ -153,6 +162,19 @@ __global__ void k_pbc_table(Pool p, int c_base, float c_init)
     if (t > p.E) return;
     const float T = (float)t, c2 = (float)c_base;
     p.pbc[t] = make_float2(glibc_logf((T + c2 + 1) / c2) + c_init, sqrtf(T));
+}
+
+// experiment LZB_X_PBC2: pb_c = pbc0 * (sqrt(T) / (child visits + 1)) for every (T, child visits) pair, evaluated with the
+// very expression the selection kernels use (same fp32 operations, no contraction), so a lookup is bit-identical
+__global__ void k_pbc2_table(Pool p, int c_base, float c_init)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int W = p.pbc2_w;
+    if (t >= W * W) return;
+    const int Ti = t / W, vc = t - Ti * W;
+    const float T = (float)Ti, c2 = (float)c_base;
+    const float pbc0 = glibc_logf((T + c2 + 1) / c2) + c_init, sqT = sqrtf(T);
+    p.pbc2[t] = pbc0 * (sqT / (float)(vc + 1));
 }
 
 __global__ void k_set_slots(Pool p, int e, int n, const char *s0, const char *s1, const char *s2)
@@ -381,6 +403,13 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
     p.path_a = (int4 *)(w + l.path_a); p.path_b = (int2 *)(w + l.path_b); p.res = (int4 *)(w + l.res);
     p.best = (int *)(w + l.best); p.bidx = (int *)(w + l.bidx); p.actions = (float *)(w + l.actions); p.gumbel = (float *)(w + l.gumbel);
     p.vtable = (int *)(w + l.vtable); p.scratch = (int *)(w + l.scratch);
+    p.pbc2 = nullptr; p.pbc2_w = 0; p.cval = nullptr;
+#ifdef LZB_X_PBC2
+    if (variant != LZB_GMZ && (size_t)p.E + 1 <= kPbc2MaxW) { p.pbc2 = (float *)(w + l.pbc2); p.pbc2_w = p.E + 1; }
+#endif
+#ifdef LZB_X_CVAL
+    if (variant != LZB_GMZ) p.cval = (float *)(w + l.cval);
+#endif
     f->bytes = l.total; f->delta = 0.0f; f->sim = 0; f->expanded = -1; f->slot_by_kind = false; f->vt_m = -1; f->vt_s = -1; f->players_for = nullptr; f->pbc_base = -1; f->pbc_init = 0.0f;
     cudaStream_t st = (cudaStream_t)stream;
     k_init<<<(num_roots + 127) / 128, 128, 0, st>>>(p, legal_count_dev, legal_actions_dev);
@@ -492,6 +521,7 @@ int fill_select(lzb_forest_t *f, const lzb_search_cfg_t *cfg, const lzb_traverse
     if (p.variant == LZB_SMZ && getenv("LZB_FORCE_WARP_PER_TREE")) return fail(LZB_E_UNSUPPORTED, "the stochastic tree has lane-group kernels only");
     if (p.variant != LZB_GMZ && (f->pbc_base != cfg->pb_c_base || f->pbc_init != cfg->pb_c_init)) {
         k_pbc_table<<<(p.E + 128) / 128, 128, 0, st>>>(p, cfg->pb_c_base, cfg->pb_c_init);
+        if (p.pbc2) k_pbc2_table<<<(p.pbc2_w * p.pbc2_w + 255) / 256, 256, 0, st>>>(p, cfg->pb_c_base, cfg->pb_c_init);
         f->pbc_base = cfg->pb_c_base; f->pbc_init = cfg->pb_c_init;
     }
     if (a.players == 0 && f->players_for != (const void *)io->to_play_dev) {
@@ -958,13 +988,22 @@ int lzb_value_targets(const lzb_value_targets_t *x, void *stream)
 }
 
 namespace {
-int scalar_blocks(long long rows)
+// one row per warp, LZB_SCALAR_THREADS / 32 warps per block (lzb_scaling.cuh; -DLZB_X_SCALAR_PIPELINED: 4 persistent blocks per SM)
+int launch_scalar(const ScalarHeads &a, int W, long long rows, cudaStream_t st)
 {
+    constexpr long long wpb = kScalarThreads / 32;
 #ifdef LZB_X_SCALAR_PIPELINED
-    return (int)std::min<long long>((rows + 7) / 8, 148LL * 4);
+    const int blocks = (int)std::min<long long>((rows + wpb - 1) / wpb, 148LL * 4);
 #else
-    return (int)std::min<long long>((rows + 7) / 8, 1LL << 22);
+    const int blocks = (int)std::min<long long>((rows + wpb - 1) / wpb, 1LL << 22);
 #endif
+    const int iters = (int)((rows + wpb * blocks - 1) / (wpb * blocks));
+    if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, kScalarThreads, 0, st>>>(a, iters);
+    else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, kScalarThreads, 0, st>>>(a, iters);
+    else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, kScalarThreads, 0, st>>>(a, iters); // support 300: 601 logits per row
+    else k_inverse_scalar_transform<0><<<blocks, kScalarThreads, 0, st>>>(a, iters);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
 }
 } // namespace
 
@@ -991,17 +1030,7 @@ int lzb_inverse_scalar_transform(const lzb_support_head_t *heads, int n_heads, i
     }
     a.n_heads = n_heads; a.N = num_rows; a.support = support_size; a.eps = epsilon;
     a.ctl = (unsigned *)workspace_dev; a.raw = (float *)((char *)workspace_dev + 16);
-    const long long rows = (long long)n_heads * num_rows;
-    // one row per warp, 8 warps per block (lzb_scaling.cuh; -DLZB_X_SCALAR_PIPELINED: 4 persistent blocks per SM)
-    const int blocks = scalar_blocks(rows);
-    const int iters = (int)((rows + 8LL * blocks - 1) / (8LL * blocks));
-    cudaStream_t st = (cudaStream_t)stream;
-    if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, 256, 0, st>>>(a, iters);
-    else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, 256, 0, st>>>(a, iters);
-    else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, 256, 0, st>>>(a, iters); // support 300: 601 logits per row
-    else k_inverse_scalar_transform<0><<<blocks, 256, 0, st>>>(a, iters);
-    LZB_CUDA(cudaGetLastError());
-    return LZB_OK;
+    return launch_scalar(a, W, (long long)n_heads * num_rows, (cudaStream_t)stream);
 }
 
 // ---- lzb_inverse_scalar_transform_static: the same kernel with its scratch in a file-scope device array, for callers that
@@ -1062,16 +1091,7 @@ int lzb_inverse_scalar_transform_static(const lzb_support_head_t *heads, int n_h
     // the array keeps whatever the last call (of any caller, possibly one that was aborted) left in it: the ticket and the
     // per-head counters must start at zero; the scalars behind them are written before they are read
     LZB_CUDA(cudaMemsetAsync(scratch, 0, 16, st));
-    const long long rows = (long long)n_heads * num_rows;
-    // one row per warp, 8 warps per block (lzb_scaling.cuh; -DLZB_X_SCALAR_PIPELINED: 4 persistent blocks per SM)
-    const int blocks = scalar_blocks(rows);
-    const int iters = (int)((rows + 8LL * blocks - 1) / (8LL * blocks));
-    if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, 256, 0, st>>>(a, iters);
-    else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, 256, 0, st>>>(a, iters);
-    else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, 256, 0, st>>>(a, iters);
-    else k_inverse_scalar_transform<0><<<blocks, 256, 0, st>>>(a, iters);
-    LZB_CUDA(cudaGetLastError());
-    return LZB_OK;
+    return launch_scalar(a, W, (long long)n_heads * num_rows, st);
 }
 
 // ---- peer exchange (lzb_peer.cuh).  Layout of one rank's buffer: [2][world*rows][row_words] data, [world] flags, [2] ctl

@@ -327,17 +327,35 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     }
 
     LZB_TL(tl, 5);
+    int *const best_i = p.best + (size_t)i * p.E;
+#ifdef LZB_X_CVAL
+    const float *const cvt = p.cval + (size_t)i * p.E * B; // the tree's cached child values, indexed like its records
+#endif
     while (__any_sync(kFull, going)) {
         // ---- one round of independent reads per level: the header (same address in every lane) and R records per lane
-        const int4 *blk = tree + (size_t)e * B;
+        const int4 *blk = tree + e * B; // e * B < 2^31: the whole forest is indexed with size_t only across trees
         const int4 h = blk[0];
         int4 c[R];
+#ifdef LZB_X_CVAL
+        float cvl[R]; // experiment: CNode::value() of each child as the backup stored it, same round as the records
+#endif
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int j = lane + G * r;
             c[r] = (j < A) ? blk[1 + j] : make_int4(0, 0, 0, 0);
+#ifdef LZB_X_CVAL
+            cvl[r] = (j < A) ? cvt[e * B + 1 + j] : 0.0f;
+#endif
         }
+#ifdef LZB_X_PBC2
+        // experiment: pb_c of every (parent visits, child visits) pair from a table built with the same expression
+        const float *const pb_row = p.pbc2 ? p.pbc2 + (parent_visits - 1) * p.pbc2_w : nullptr;
+        float2 pt = make_float2(0.0f, 0.0f);
+        if (!pb_row) pt = p.pbc[parent_visits - 1];
+        float pbt[R];
+#else
         const float2 pt = p.pbc[parent_visits - 1]; // {logf((T + c2 + 1) / c2) + c1, sqrtf(T)}, T = parent visits - 1; same round as the block
+#endif
         const int n = h.x;
         if (level == 0) LZB_TLD(tl, 6, n ^ c[0].x ^ c[R - 1].x);
 
@@ -350,13 +368,18 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             const int j = lane + G * r;
             const int vc = child_visits(c[r].x);
             const bool vis = (j < n) && vc > 0;
+#ifdef LZB_X_PBC2
+            pbt[r] = pb_row ? __ldg(pb_row + vc) : 0.0f; // consumed by cucb_score below, after the mean_q work
+#endif
             const float rew = __int_as_float(c[r].w);
             tr[r] = rew;
             if (VP) tr[r] = (h.z == 1) ? rew : rew - parent_reward;
             val[r] = 0.0f;
             const unsigned wvis = __ballot_sync(kFull, vis);
             if (wvis) { // warp-uniform: slices without a visited child in any group add nothing
-#ifndef LZB_X_BRANCHFREE_DIV // the compiler branches around the division (BSSY / divergent BRA per slice)
+#if defined(LZB_X_CVAL)
+                val[r] = vis ? cvl[r] : 0.0f; // CNode::value() = value_sum / visit_count, divided once by the backup
+#elif !defined(LZB_X_BRANCHFREE_DIV) // the compiler branches around the division (BSSY / divergent BRA per slice)
                 val[r] = vis ? __int_as_float(c[r].y) / (float)vc : 0.0f; // CNode::value()
 #else // experiment (round 2, measured and rejected: 18.2 vs 17.5 us per step; ez 30.1 vs 29.7): every lane divides (by 1
       // where there is nothing to divide) and selects - no divergent branch, but the full-precision division's ~10
@@ -367,6 +390,22 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
                 const float qsa = vis ? tr[r] + g * val[r] : 0.0f;
                 nvis += __popc((wvis >> grp.shift) & ((G == 32) ? 0xffffffffu : ((1u << (G & 31)) - 1u)));
                 // j = l + G*r ascending; +0.0f for the rest is exact; the last slice stops at the action space
+#ifdef LZB_X_SPARSE_SUM
+                // experiment: below the root a node has one to three visited children, so add only the lanes that hold a
+                // visited child in SOME group of the warp (ascending, the other groups add +0.0f there)
+                unsigned u = 0;
+#pragma unroll
+                for (int s = 0; s < 32; s += G) u |= wvis >> s;
+                u &= (G == 32) ? 0xffffffffu : ((1u << (G & 31)) - 1u);
+                if (__popc(u) <= 4) {
+#pragma unroll 1
+                    while (u) {
+                        const int l = __ffs(u) - 1;
+                        u &= u - 1;
+                        total += grp.shfl(qsa, l);
+                    }
+                } else
+#endif
                 total = (r == R - 1 && R > 1) ? grp.ordered_add(total, qsa, A - G * (R - 1)) : grp.ordered_add(total, qsa, G);
             }
         }
@@ -392,7 +431,11 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         for (int r = 0; r < R; ++r) {
             const int j = lane + G * r;
             const int vc = child_visits(c[r].x);
+#ifdef LZB_X_PBC2
+            const float pb_c = pb_row ? pbt[r] : pbc0 * (sqT / (float)(vc + 1));
+#else
             const float pb_c = pbc0 * (sqT / (float)(vc + 1));
+#endif
             float prior_score;
             if (VAR == LZB_SEZ) prior_score = pb_c / (float)n; // uniform branch, sez cnode.cpp:1078
             else prior_score = pb_c * __int_as_float(c[r].z);
@@ -485,7 +528,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
             if (lane == 0) {
                 pa[depth] = make_int4(e * B + 1 + pos, ch.x, ch.y, ch.w);
                 pb[depth] = make_int2(h.y, h.z);
-                p.best[(size_t)i * p.E + e] = pos;
+                best_i[e] = pos;
             }
             depth += 1;
             const int ce = child_expansion(ch.x);
@@ -809,9 +852,9 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     float pre_vp = 0.0f;
     {
         const int q = depth - lane;
+        if (VAR != LZB_GMZ && live && to_play != -1 && q >= 0 && q != depth) pre_tp = pb[q].x; // node 0's too (the root's to_play)
         if (live && q >= 1) {
             pre_r = pa[q - 1];
-            if (VAR != LZB_GMZ && to_play != -1 && q != depth) pre_tp = pb[q].x;
             if (VP) {
                 if (q >= 2) pre_vp = __int_as_float(pa[q - 2].w);
                 pre_reset = pb[q - 1].y;
@@ -955,6 +998,9 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 #endif
             } else {
                 int4 *rec = p.tree(i) + slot;
+#ifdef LZB_X_CVAL
+                if (VAR != LZB_GMZ) p.cval[(size_t)i * p.E * p.B + slot] = nv; // what select would divide out again at every later visit
+#endif
                 const int exp_idx = (q == depth && !no_inference) ? e_new : child_expansion(x);
                 *reinterpret_cast<int2 *>(rec) = make_int2(child_pack(visits, exp_idx), __float_as_int(vsum));
                 if (q == depth) reinterpret_cast<int *>(rec)[3] = __float_as_int(rew);

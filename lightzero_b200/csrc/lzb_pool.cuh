@@ -47,6 +47,9 @@ struct Pool {
     int *vtable;    // [S]     considered-visit sequence of the current Gumbel config
     int *scratch;   // [4]     {max(to_play), ...}
     float2 *pbc;    // [S+2]   per parent visit count T: {logf((T + c2 + 1) / c2) + c1, sqrtf(T)} (cucb_score, cnode.cpp:673-674)
+    float *pbc2;    // experiment LZB_X_PBC2: [E+1][pbc2_w] pb_c of cucb_score per (parent visits - 1, child visits), or NULL
+    int pbc2_w;
+    float *cval;    // experiment LZB_X_CVAL: [N][E][B] CNode::value() of every child record as the backup last computed it, or NULL
     const char **slots; // [kMaxGathers][E] base pointer of the [N, row] tensor that holds the rows gathered for
                         //          leaves whose parent was expanded as e (latent, LSTM c, LSTM h)
 

@@ -70,6 +70,16 @@ __device__ __forceinline__ float inverse_h(float x, float eps)
     return sgn * (t * t - 1.0f);
 }
 
+// the same with the division by 2 eps as a multiplication by its reciprocal (one rounding apart: 1.2e-7 relative, inside
+// the cancellation noise sqrt(1 + d) - 1 already carries; the square root stays IEEE).  The hot path only: every lane of
+// a row's warp evaluates h^-1, so the ~20 instructions of two full-precision divisions are paid once per row.
+__device__ __forceinline__ float inverse_h_fast(float x, float eps, float inv_2eps)
+{
+    const float t = (sqrtf(1.0f + 4.0f * eps * (fabsf(x) + 1.0f + eps)) - 1.0f) * inv_2eps;
+    const float sgn = (x > 0.0f) ? 1.0f : ((x < 0.0f) ? -1.0f : 0.0f);
+    return sgn * (t * t - 1.0f);
+}
+
 template <int T> // T = loads per lane held in registers: W <= 32 * T
 __device__ __forceinline__ void scalar_row(const ScalarHeads &a, int h, int i, int lane, bool &not_normalised)
 {
@@ -161,7 +171,8 @@ __device__ __forceinline__ void load_row_v4(const float *row, int W, int lane, R
 // p - support = (4l - off - support) + (128 j + c): the second term is a compile-time constant, so the weighted sums are
 // sum e * (128 j + c)  +  (4l - off - support) * sum e.
 template <int V>
-__device__ __forceinline__ void reduce_row_v4(const ScalarHeads &a, const RowRegs<V> &r, int h, int i, int lane, bool live, bool &not_normalised)
+__device__ __forceinline__ void reduce_row_v4(const ScalarHeads &a, const RowRegs<V> &r, int h, int i, int lane, bool live, float inv_2eps,
+                                              bool &not_normalised)
 {
     float m = -INFINITY;
 #pragma unroll
@@ -170,24 +181,44 @@ __device__ __forceinline__ void reduce_row_v4(const ScalarHeads &a, const RowReg
     const float kLog2e = 1.4426950408889634f;
     const float mneg = -m * kLog2e;
     float se = 0.0f, te = 0.0f, sx = 0.0f, tx = 0.0f;
+    // vectors 1 .. jend - 1 lie inside the row in EVERY lane (jend: the slice that holds the row's last vector, warp-
+    // uniform), so only slice 0 and slice jend need the position masks, and slices beyond jend hold nothing
+    const int jend = ((r.off + 2 * a.support) >> 2) >> 5;
 #pragma unroll
     for (int j = 0; j < V; ++j) {
+        if (j > jend) continue;
+        if (j > 0 && j < jend) {
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const float rel = (float)(128 * j + c); // compile-time constant
-            const float e = exp2f_approx(__fmaf_rn(r.x[j][c], kLog2e, mneg)); // -inf outside the row: e = 0
-            const float xr = ((r.vm[j] >> c) & 1u) ? r.x[j][c] : 0.0f;         // the raw sums skip positions outside the row
-            se += e;
-            te = __fmaf_rn(e, rel, te);
-            sx += xr;
-            tx = __fmaf_rn(xr, rel, tx);
+            for (int c = 0; c < 4; ++c) {
+                const float rel = (float)(128 * j + c); // compile-time constant
+                const float e = exp2f_approx(__fmaf_rn(r.x[j][c], kLog2e, mneg));
+                se += e;
+                te = __fmaf_rn(e, rel, te);
+                sx += r.x[j][c];
+                tx = __fmaf_rn(r.x[j][c], rel, tx);
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float rel = (float)(128 * j + c);
+                const float e = exp2f_approx(__fmaf_rn(r.x[j][c], kLog2e, mneg)); // -inf outside the row: e = 0
+                const float xr = ((r.vm[j] >> c) & 1u) ? r.x[j][c] : 0.0f;         // the raw sums skip positions outside the row
+                se += e;
+                te = __fmaf_rn(e, rel, te);
+                sx += xr;
+                tx = __fmaf_rn(xr, rel, tx);
+            }
         }
     }
     const float lane_sup = (float)(4 * lane - r.off - a.support);
     te = __fmaf_rn(lane_sup, se, te);
     tx = __fmaf_rn(lane_sup, sx, tx);
     se = warp_sum_f(se); te = warp_sum_f(te); sx = warp_sum_f(sx); tx = warp_sum_f(tx);
+#ifdef LZB_X_SCALAR_PRECISE_DIV // round-2 first form: two IEEE divisions per row on every lane
     const float scalar = inverse_h(te / se, a.eps);
+#else
+    const float scalar = inverse_h_fast(__fdividef(te, se), a.eps, inv_2eps);
+#endif
     if (lane == 0 && live) {
         a.out_of(h)[i] = scalar;
         a.raw[(size_t)h * a.N + i] = tx;
@@ -224,18 +255,33 @@ __device__ __forceinline__ void scalar_row_wide(const ScalarHeads &a, int h, int
 // grid-stride loop 12.4 M warp-instructions / 21.5 us; this form 7.7 M / 16.0 us; persistent warps (-DLZB_X_SCALAR_PIPELINED:
 // 4 blocks per SM, several rows per warp, the vectors of row it + 1 requested before row it is reduced) 9.7 M / 17.7 us -
 // the dead iterations of the last pass and the register copies cost more than the prefetch hides.
+//
+// Epilogue: the block's warps meet at a barrier, thread 0 forwards the block's "un-normalised" flags and takes the global
+// ticket, a second barrier tells the block whether it is the grid's last.  ncu attributes 28 % of all warp-resident time
+// to those two barriers (profiles/r02_scalar_transform.md), so a form without them was tried (-DLZB_X_SCALAR_WARP_TICKET:
+// a warp that has stored its scalar fences, counts itself in a shared word and leaves; the block's last warp takes the
+// ticket; the grid's last warp does the rare rewrite alone) and REJECTED: 17.3 us against 14.4 us back to back in a CUDA
+// graph - one MEMBAR.GPU per warp (16,384 per launch instead of 2,048) costs more than the waiting it removes; blocks of
+// 128 threads 14.8 us, of 64 threads 20.0 us (-DLZB_SCALAR_THREADS=...).
+#ifndef LZB_SCALAR_THREADS
+#define LZB_SCALAR_THREADS 256
+#endif
+constexpr int kScalarThreads = LZB_SCALAR_THREADS;
 #ifdef LZB_X_SCALAR_PIPELINED
 #define LZB_SCALAR_MIN_BLOCKS 4
 #else
-#define LZB_SCALAR_MIN_BLOCKS 6 // 40 registers: 48 resident warps per SM
+#define LZB_SCALAR_MIN_BLOCKS (1536 / LZB_SCALAR_THREADS) // 40 registers: 48 resident warps per SM
 #endif
 template <int T>
-__global__ void __launch_bounds__(256, LZB_SCALAR_MIN_BLOCKS) k_inverse_scalar_transform(ScalarHeads a, int iters)
+__global__ void __launch_bounds__(kScalarThreads, LZB_SCALAR_MIN_BLOCKS) k_inverse_scalar_transform(ScalarHeads a, int iters)
 {
     __shared__ unsigned s_bad[kMaxScalarHeads];
     __shared__ unsigned s_last;
+    __shared__ unsigned s_arrived;
     if (threadIdx.x < kMaxScalarHeads) s_bad[threadIdx.x] = 0;
-    __syncthreads();
+    if (threadIdx.x == kMaxScalarHeads) s_arrived = 0;
+    __syncthreads(); // the block's warps start together: nobody waits here
+    const float inv_2eps = 1.0f / (2.0f * a.eps);
     const int lane = threadIdx.x & 31;
     const int total = a.n_heads * a.N;
     const int warps = gridDim.x * (blockDim.x >> 5);
@@ -271,7 +317,7 @@ __global__ void __launch_bounds__(256, LZB_SCALAR_MIN_BLOCKS) k_inverse_scalar_t
             load_row_v4<V>(a.row_of(h, r - h * a.N), W, lane, cur);
 #endif
             bool bad = false;
-            reduce_row_v4<V>(a, cur, h, r - h * a.N, lane, live, bad);
+            reduce_row_v4<V>(a, cur, h, r - h * a.N, lane, live, inv_2eps, bad);
             bad0 = bad0 || (bad && h == 0);
             bad1 = bad1 || (bad && h == 1);
         }
@@ -294,6 +340,7 @@ __global__ void __launch_bounds__(256, LZB_SCALAR_MIN_BLOCKS) k_inverse_scalar_t
             bad1 = bad1 || (bad && h == 1);
         }
     }
+#ifndef LZB_X_SCALAR_WARP_TICKET
     if (lane == 0 && bad0) s_bad[0] = 1; // benign race: every writer stores 1
     if (lane == 0 && bad1) s_bad[1] = 1;
     __syncthreads();
@@ -313,6 +360,31 @@ __global__ void __launch_bounds__(256, LZB_SCALAR_MIN_BLOCKS) k_inverse_scalar_t
     }
     __syncthreads();
     if (threadIdx.x <= a.n_heads) a.ctl[threadIdx.x] = 0; // ready for the next call
+#else
+    (void)s_last;
+    unsigned last = 0;
+    if (lane == 0) {
+        if (bad0) atomicOr(&s_bad[0], 1u);
+        if (bad1) atomicOr(&s_bad[1], 1u);
+        __threadfence(); // this warp's scalars (and its flags) are visible before its arrival is counted
+        if (atomicAdd(&s_arrived, 1u) == (blockDim.x >> 5) - 1) { // the block's last warp: every other warp's flags are in
+            for (int h = 0; h < a.n_heads; ++h)
+                if (*((volatile unsigned *)&s_bad[h])) atomicAdd(a.ctl + 1 + h, 1u);
+            __threadfence(); // the block's counters are visible before its ticket
+            last = (atomicAdd(a.ctl, 1u) == gridDim.x - 1) ? 1u : 0u;
+        }
+    }
+    last = __shfl_sync(kFull, last, 0);
+    if (!last) return;
+    __threadfence();
+    for (int h = 0; h < a.n_heads; ++h) {
+        const unsigned bad = *((volatile unsigned *)(a.ctl + 1 + h));
+        if (bad == 0) // every row of this head sums to 1: the head emitted probabilities (ensure_softmax's else branch)
+            for (int i = lane; i < a.N; i += 32) a.out_of(h)[i] = inverse_h(__ldcg(a.raw + (size_t)h * a.N + i), a.eps);
+    }
+    __syncwarp();
+    if (lane <= a.n_heads) a.ctl[lane] = 0; // ready for the next call
+#endif
 }
 
 } // namespace lzb

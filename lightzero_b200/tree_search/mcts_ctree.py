@@ -16,6 +16,7 @@ bench use) unless ``tie_break_advance=True``, which derives search k's seed from
 replayed as a CUDA graph reads its seed from a device word, so the same rules hold across replays.
 """
 import copy
+import gc
 
 import numpy as np
 import torch
@@ -372,8 +373,18 @@ class _SearchGraph:
                 self._body()  # eager warm-up: allocator, lazy uploads (Gumbel tables), cudaFuncSetAttribute
                 torch.cuda.synchronize(self.dev)
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
-                    self.outs = self._body()
+                # no cyclic garbage collection while the stream is capturing: a finaliser that frees device memory (an
+                # older search graph's pool, a peer buffer) is a prohibited call in global capture mode and invalidates
+                # the capture - seen as an order-dependent cudaErrorStreamCaptureInvalidated in the test suite
+                gc_was_on = gc.isenabled()
+                gc.collect()
+                gc.disable()
+                try:
+                    with torch.cuda.graph(g):
+                        self.outs = self._body()
+                finally:
+                    if gc_was_on:
+                        gc.enable()
                 self.graph = g
             self.graph.replay()
 
