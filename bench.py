@@ -819,6 +819,10 @@ def run_b200_arm(a):
             line["exchange_check"] = exchange_check
         if transform is not None:
             transform["frac"] = round(transform["achieved"] / peak, 4)
+            try:  # DRAM bytes per launch of this kernel from its ncu --set full capture (profiles/r02_scalar_ncu_raw.csv)
+                transform["traffic"] = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("scalar_transform") if a.support == 300 and N == 8192 else None
+            except Exception:
+                transform["traffic"] = None
             line["roofline"]["scalar_transform"] = transform
         if e2e_ms is not None:
             line["e2e"] = {"value": round(total_sims / (e2e_tot / a.steps * 1e-3), 1), "unit": "simulations/s",
