@@ -988,16 +988,53 @@ int lzb_value_targets(const lzb_value_targets_t *x, void *stream)
 }
 
 namespace {
-// one row per warp, LZB_SCALAR_THREADS / 32 warps per block (lzb_scaling.cuh; -DLZB_X_SCALAR_PIPELINED: 4 persistent blocks per SM)
+// Grid of the scalar-transform kernels: one row (or root) per warp, in as many waves of blocks as that takes.  16,384 rows are
+// 2.31 waves of 148 SMs x 48 resident warps and ncu shows the SMs active for 72 % of the launch, so a balanced grid was tried
+// (-DLZB_X_SCALAR_BALANCED: P = ceil(units / resident warps) passes over ceil(units / P) warps, every warp walks P rows and
+// all end together): 14.6-14.9 us against 14.5 us - no gain, because at 39 MB the launch is in the small-kernel regime where
+// even torch's plain row sum over the same bytes takes 13.6 us (profiles/r02_scalar_transform.md).
+void scalar_grid(long long units, int blocks_per_sm, long long wpb, int &blocks, int &iters)
+{
+#ifndef LZB_X_SCALAR_BALANCED
+    (void)blocks_per_sm;
+    blocks = (int)std::min<long long>((units + wpb - 1) / wpb, 1LL << 22);
+    iters = (int)((units + wpb * blocks - 1) / (wpb * blocks));
+#else
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0, n = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        sms = n;
+    }
+    const long long resident = (long long)sms * blocks_per_sm * wpb;
+    const long long passes = std::max<long long>(1, (units + resident - 1) / resident);
+    const long long warps = (units + passes - 1) / passes;
+    blocks = (int)((warps + wpb - 1) / wpb);
+    iters = (int)((units + wpb * blocks - 1) / (wpb * blocks));
+#endif
+}
+
+// LZB_SCALAR_THREADS / 32 warps per block (lzb_scaling.cuh; -DLZB_X_SCALAR_PIPELINED: 4 persistent blocks per SM)
 int launch_scalar(const ScalarHeads &a, int W, long long rows, cudaStream_t st)
 {
     constexpr long long wpb = kScalarThreads / 32;
-#ifdef LZB_X_SCALAR_PIPELINED
-    const int blocks = (int)std::min<long long>((rows + wpb - 1) / wpb, 148LL * 4);
-#else
-    const int blocks = (int)std::min<long long>((rows + wpb - 1) / wpb, 1LL << 22);
+    int blocks = 0, iters = 0;
+#if defined(LZB_X_SCALAR_PAIR) && !defined(LZB_X_SCALAR_PIPELINED) && !defined(LZB_X_SCALAR_ROWLOADS)
+    if (a.n_heads == 2 && W <= 32 * 19) { // experiment: both heads of a root by one warp, packed fp32 arithmetic (lzb_scaling.cuh)
+        scalar_grid(rows / 2, LZB_SCALAR_PAIR_MIN_BLOCKS, wpb, blocks, iters);
+        if (W <= 32 * 4) k_inverse_scalar_transform_pair<4><<<blocks, kScalarThreads, 0, st>>>(a, iters);
+        else if (W <= 32 * 8) k_inverse_scalar_transform_pair<8><<<blocks, kScalarThreads, 0, st>>>(a, iters);
+        else k_inverse_scalar_transform_pair<19><<<blocks, kScalarThreads, 0, st>>>(a, iters);
+        LZB_CUDA(cudaGetLastError());
+        return LZB_OK;
+    }
 #endif
-    const int iters = (int)((rows + wpb * blocks - 1) / (wpb * blocks));
+#ifdef LZB_X_SCALAR_PIPELINED
+    blocks = (int)std::min<long long>((rows + wpb - 1) / wpb, 148LL * 4);
+    iters = (int)((rows + wpb * blocks - 1) / (wpb * blocks));
+#else
+    scalar_grid(rows, LZB_SCALAR_MIN_BLOCKS, wpb, blocks, iters);
+#endif
     if (W <= 32 * 4) k_inverse_scalar_transform<4><<<blocks, kScalarThreads, 0, st>>>(a, iters);
     else if (W <= 32 * 8) k_inverse_scalar_transform<8><<<blocks, kScalarThreads, 0, st>>>(a, iters);
     else if (W <= 32 * 19) k_inverse_scalar_transform<19><<<blocks, kScalarThreads, 0, st>>>(a, iters); // support 300: 601 logits per row

@@ -226,6 +226,100 @@ __device__ __forceinline__ void reduce_row_v4(const ScalarHeads &a, const RowReg
     }
 }
 
+// ---------------------------------------------------------------------------------------------- two rows per warp
+// EXPERIMENT (-DLZB_X_SCALAR_PAIR; measured and not adopted: 14.3-16.3 us against 14.4 us, profiles/r02_scalar_transform.md
+// - at 39 MB per launch the instruction count is not what bounds the kernel).  The one-row kernel executes 586
+// warp-instructions per row, 7.75 per logit in the element loop.  Here a warp takes ROOT i's value row and
+// reward row together - ten 16-byte loads in flight per lane - and does the element arithmetic with sm_100's packed fp32
+// instructions (FFMA2 / FADD2 on register pairs): per 16-byte vector two FFMA2 (x * log2e - max * log2e), four MUFU.EX2 and
+// four FADD2 per accumulated quantity, with SUFFIX sums instead of per-position weights -
+//     sum_j j * e_j  =  sum_{k >= 1} R_k,   R_k = sum_{j >= k} e_j       (slices walked from the last to the first)
+// so the support values need no constants at all: sum_p e_p * (p - s) = 128 * sum_c Q_c + sum_c c * R_c(0) + (4 lane - off
+// - s) * sum_c R_c(0).  3.5 instead of 7.75 instructions per logit; the eight warp sums of the two rows are reduced as four
+// packed pairs, and h^-1 is evaluated once per warp (lane 0 for the value head, lane 1 for the reward head).
+__device__ __forceinline__ unsigned long long pk2(float lo, float hi)
+{
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void upk2(unsigned long long v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c)
+{
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ unsigned long long add2(unsigned long long a, unsigned long long b)
+{
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ unsigned long long warp_sum_2(unsigned long long v)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = add2(v, __shfl_xor_sync(kFull, v, o));
+    return v;
+}
+
+template <int V>
+__device__ __forceinline__ float row_max_v4(const RowRegs<V> &r)
+{
+    float m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < V; ++j) m = fmaxf(fmaxf(fmaxf(r.x[j][0], r.x[j][1]), fmaxf(r.x[j][2], r.x[j][3])), m);
+    return m;
+}
+
+// per-lane partial sums of one row: {sum e, sum e * (p - s), sum x, sum x * (p - s)} over the lane's positions p
+template <int V>
+__device__ __forceinline__ float4 row_sums_packed(const RowRegs<V> &r, int support, int lane, float m)
+{
+    const float kLog2e = 1.4426950408889634f;
+    const unsigned long long L2E = pk2(kLog2e, kLog2e), MN = pk2(-m * kLog2e, -m * kLog2e);
+    const int jend = ((r.off + 2 * support) >> 2) >> 5; // slice of the row's last vector (warp-uniform)
+    unsigned long long Re01 = 0ull, Re23 = 0ull, Qe01 = 0ull, Qe23 = 0ull; // 0ull = {+0.0f, +0.0f}
+    unsigned long long Rx01 = 0ull, Rx23 = 0ull, Qx01 = 0ull, Qx23 = 0ull;
+#pragma unroll
+    for (int j = V - 1; j >= 0; --j) {
+        if (j > jend) continue; // nothing of the row in this slice, in any lane
+        float t0, t1, t2, t3;
+        upk2(fma2(pk2(r.x[j][0], r.x[j][1]), L2E, MN), t0, t1);
+        upk2(fma2(pk2(r.x[j][2], r.x[j][3]), L2E, MN), t2, t3);
+        Re01 = add2(Re01, pk2(exp2f_approx(t0), exp2f_approx(t1))); // -inf outside the row: e = 0
+        Re23 = add2(Re23, pk2(exp2f_approx(t2), exp2f_approx(t3)));
+        if (j > 0 && j < jend) { // every lane's vector lies inside the row
+            Rx01 = add2(Rx01, pk2(r.x[j][0], r.x[j][1]));
+            Rx23 = add2(Rx23, pk2(r.x[j][2], r.x[j][3]));
+        } else { // the raw sums skip positions outside the row
+            const unsigned vm = r.vm[j];
+            Rx01 = add2(Rx01, pk2((vm & 1u) ? r.x[j][0] : 0.0f, (vm & 2u) ? r.x[j][1] : 0.0f));
+            Rx23 = add2(Rx23, pk2((vm & 4u) ? r.x[j][2] : 0.0f, (vm & 8u) ? r.x[j][3] : 0.0f));
+        }
+        if (j >= 1) { // Q = sum_{k >= 1} R_k
+            Qe01 = add2(Qe01, Re01); Qe23 = add2(Qe23, Re23);
+            Qx01 = add2(Qx01, Rx01); Qx23 = add2(Qx23, Rx23);
+        }
+    }
+    float e0, e1, e2, e3, q0, q1, q2, q3;
+    upk2(Re01, e0, e1); upk2(Re23, e2, e3);
+    upk2(add2(Qe01, Qe23), q0, q1);
+    const float lane_sup = (float)(4 * lane - r.off - support);
+    const float se = (e0 + e1) + (e2 + e3);
+    float te = __fmaf_rn(128.0f, q0 + q1, __fmaf_rn(3.0f, e3, __fmaf_rn(2.0f, e2, e1)));
+    te = __fmaf_rn(lane_sup, se, te);
+    upk2(Rx01, e0, e1); upk2(Rx23, e2, e3);
+    upk2(add2(Qx01, Qx23), q2, q3);
+    const float sx = (e0 + e1) + (e2 + e3);
+    float tx = __fmaf_rn(128.0f, q2 + q3, __fmaf_rn(3.0f, e3, __fmaf_rn(2.0f, e2, e1)));
+    tx = __fmaf_rn(lane_sup, sx, tx);
+    return make_float4(se, te, sx, tx);
+}
+
 // wide supports: the row is walked twice (max, then sums) instead of held in registers
 __device__ __forceinline__ void scalar_row_wide(const ScalarHeads &a, int h, int i, int lane, bool live, bool &not_normalised)
 {
@@ -385,6 +479,77 @@ __global__ void __launch_bounds__(kScalarThreads, LZB_SCALAR_MIN_BLOCKS) k_inver
     __syncwarp();
     if (lane <= a.n_heads) a.ctl[lane] = 0; // ready for the next call
 #endif
+}
+
+// the two-rows-per-warp kernel: n_heads == 2, one warp per root (see above).  Same epilogue as the one-row kernel.
+#ifndef LZB_SCALAR_PAIR_MIN_BLOCKS
+#define LZB_SCALAR_PAIR_MIN_BLOCKS 3
+#endif
+template <int T>
+__global__ void __launch_bounds__(kScalarThreads, LZB_SCALAR_PAIR_MIN_BLOCKS) k_inverse_scalar_transform_pair(ScalarHeads a, int iters)
+{
+    static_assert(T > 0, "the pair kernel holds both rows in registers");
+    __shared__ unsigned s_bad[kMaxScalarHeads];
+    __shared__ unsigned s_last;
+    if (threadIdx.x < kMaxScalarHeads) s_bad[threadIdx.x] = 0;
+    __syncthreads();
+    constexpr int V = (32 * T + 3 + 127) / 128;
+    const float inv_2eps = 1.0f / (2.0f * a.eps);
+    const int lane = threadIdx.x & 31;
+    const int W = 2 * a.support + 1;
+    const int warps = gridDim.x * (blockDim.x >> 5);
+    const int gw = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    bool bad0 = false, bad1 = false;
+#pragma unroll 1
+    for (int it = 0; it < iters; ++it) {
+        const int r0 = it * warps + gw;
+        const bool live = r0 < a.N;
+        const int i = live ? r0 : a.N - 1;
+        RowRegs<V> rv, rr;
+        load_row_v4<V>(a.logits[0] + (long long)i * a.stride[0], W, lane, rv);
+        load_row_v4<V>(a.logits[1] + (long long)i * a.stride[1], W, lane, rr);
+        float mv = row_max_v4<V>(rv), mr = row_max_v4<V>(rr);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mv = fmaxf(mv, __shfl_xor_sync(kFull, mv, o));
+            mr = fmaxf(mr, __shfl_xor_sync(kFull, mr, o));
+        }
+        const float4 pv = row_sums_packed<V>(rv, a.support, lane, mv);
+        const float4 pr = row_sums_packed<V>(rr, a.support, lane, mr);
+        float se0, se1, te0, te1, sx0, sx1, tx0, tx1; // head 0 = value row, head 1 = reward row
+        upk2(warp_sum_2(pk2(pv.x, pr.x)), se0, se1);
+        upk2(warp_sum_2(pk2(pv.y, pr.y)), te0, te1);
+        upk2(warp_sum_2(pk2(pv.z, pr.z)), sx0, sx1);
+        upk2(warp_sum_2(pk2(pv.w, pr.w)), tx0, tx1);
+        const bool second = lane & 1; // lane 0 finishes the value head, lane 1 the reward head
+        const float scalar = inverse_h_fast(__fdividef(second ? te1 : te0, second ? se1 : se0), a.eps, inv_2eps);
+        if (live && lane < 2) {
+            (second ? a.out[1] : a.out[0])[i] = scalar;
+            a.raw[(size_t)(second ? a.N : 0) + i] = second ? tx1 : tx0;
+        }
+        // torch.allclose(sum, 1, atol=1e-5) with the default rtol=1e-5; NaN is not close
+        bad0 = bad0 || (live && !(fabsf(sx0 - 1.0f) <= 2e-5f));
+        bad1 = bad1 || (live && !(fabsf(sx1 - 1.0f) <= 2e-5f));
+    }
+    if (lane == 0 && bad0) s_bad[0] = 1; // benign race: every writer stores 1
+    if (lane == 0 && bad1) s_bad[1] = 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int h = 0; h < 2; ++h)
+            if (s_bad[h]) atomicAdd(a.ctl + 1 + h, 1u);
+        __threadfence(); // this block's scalars and counters are visible before its ticket
+        s_last = (atomicAdd(a.ctl, 1u) == gridDim.x - 1) ? 1u : 0u;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    for (int h = 0; h < 2; ++h) {
+        const unsigned bad = *((volatile unsigned *)(a.ctl + 1 + h));
+        if (bad == 0) // every row of this head sums to 1: the head emitted probabilities (ensure_softmax's else branch)
+            for (int i = threadIdx.x; i < a.N; i += blockDim.x) a.out_of(h)[i] = inverse_h(__ldcg(a.raw + (size_t)h * a.N + i), a.eps);
+    }
+    __syncthreads();
+    if (threadIdx.x <= 2) a.ctl[threadIdx.x] = 0; // ready for the next call
 }
 
 } // namespace lzb

@@ -17,6 +17,7 @@ def main():
     ap.add_argument("--support", type=int, default=300)
     ap.add_argument("--sets", type=int, default=10)
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--probe", action="store_true", help="also time torch reductions over the same tensors")
     a = ap.parse_args()
     dev = torch.device("cuda", 0)
     W = 2 * a.support + 1
@@ -40,6 +41,26 @@ def main():
         torch.cuda.synchronize()
         us = 1e3 * t0.elapsed_time(t1) / a.sets
         best = us if best is None else min(best, us)
+    if a.probe:  # reference points on the same bytes: torch's row sum (two launches) and a whole-tensor max (two launches)
+        for name, fn in (("torch.sum(dim=1) x2", lambda s: (val[s].sum(1), rew[s].sum(1))), ("torch.amax() x2", lambda s: (val[s].amax(), rew[s].amax())),
+                         ("torch.softmax(dim=1) x2 (read + write)", lambda s: (torch.softmax(val[s], 1), torch.softmax(rew[s], 1)))):
+            for s in range(a.sets):
+                fn(s)
+            torch.cuda.synchronize()
+            g2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g2):
+                for s in range(a.sets):
+                    fn(s)
+            b2 = None
+            for _ in range(a.reps):
+                t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                t0.record()
+                g2.replay()
+                t1.record()
+                torch.cuda.synchronize()
+                us = 1e3 * t0.elapsed_time(t1) / a.sets
+                b2 = us if b2 is None else min(b2, us)
+            print("probe %-42s %.2f us per pair of heads" % (name, b2))
     nbytes = 2 * a.rows * W * 4 + 2 * a.rows * 4
     print("scalar transform: %.2f us per launch, %.1f MB, %.0f GB/s (%s)" % (best, nbytes / 1e6, nbytes / best / 1e3,
                                                                          os.environ.get("LZB200_LIB", "default build")))
