@@ -417,6 +417,39 @@ int lzb_peer_error(void *own_buf_dev, int world, int64_t rows_per_rank, int row_
 int lzb_gumbel_table(int max_num_considered_actions, int num_simulations, int32_t *out_host);
 int lzb_gumbel_noise(float scale, int shape, float *out_host);
 
+/* Single-node Gumbel MuZero helpers: the free functions gmz_tree.pyx:97-149 exposes to the reference's unit tests
+ * (softmax -> csoftmax, pcompute_mixed_value, prescale_qvalues, pqtransform_completed_by_mix_value, pscore_considered,
+ * select_root_child, select_interior_child; gmz cnode.cpp:701-790,904-1040,1097-1132) over vectors of n floats / ints in
+ * DEVICE memory, evaluated by one thread with the tree's own libm.  Vectors and scalars per op:
+ *   LZB_GH_SOFTMAX            a = x                                                            -> out[n]
+ *   LZB_GH_MIXED_VALUE        s0 = raw value, a = q values, v = child visits, b = child priors -> out[1]
+ *   LZB_GH_RESCALE            a = values, s0 = epsilon                                         -> out[n]
+ *   LZB_GH_QTRANSFORM         a = the node's get_q(discount), s0 = its raw value, v, b = child priors, s1 = maxvisit_init,
+ *                             s2 = value_scale, i0 = rescale_values, s3 = epsilon              -> out[n]
+ *   LZB_GH_SCORE_CONSIDERED   i0 = considered visit, a = gumbel, b = logits, c = normalised q, v = visits -> out[n]
+ *   LZB_GH_SELECT_ROOT        a = q, s0 = raw value, v, b = child priors, c = the node's gumbel noise, i0 = the considered
+ *                             visit count of this simulation (lzb_gumbel_table row min(m, S), column sum(v)) -> out_i[1]: POSITION
+ *   LZB_GH_SELECT_INTERIOR    a = q, s0 = raw value, v, b = child priors                       -> out_i[1]: POSITION
+ * tmp_dev: 3 n floats of scratch. */
+enum { LZB_GH_SOFTMAX = 0, LZB_GH_MIXED_VALUE = 1, LZB_GH_RESCALE = 2, LZB_GH_QTRANSFORM = 3, LZB_GH_SCORE_CONSIDERED = 4,
+       LZB_GH_SELECT_ROOT = 5, LZB_GH_SELECT_INTERIOR = 6 };
+typedef struct {
+    int op, n;
+    const float *a_dev, *b_dev, *c_dev;
+    const int32_t *v_dev;
+    float s0, s1, s2, s3;
+    int i0, i1;
+    float *out_dev;
+    int32_t *out_i_dev;
+    float *tmp_dev;
+} lzb_gumbel_helper_t;
+int lzb_gumbel_helper(const lzb_gumbel_helper_t *args, void *stream);
+
+/* Checked build (-DLZB_CHECKED, profiles/r02_sanitizer.md): the largest code of a violated index check since the forest
+ * was created / reset (0 = none; always 0 in the shipped build), and whether this library is a checked build.  No
+ * counterpart in the reference.  Synchronises the stream. */
+int lzb_check_word(lzb_forest_t *f, int32_t *word_host, int32_t *checked_build_host, void *stream);
+
 /* Device-side libm used by the tree, exposed for the parity tests: out[i] = expf/logf(x[i]). */
 int lzb_test_expf(const float *x_dev, float *out_dev, int64_t n, void *stream);
 int lzb_test_logf(const float *x_dev, float *out_dev, int64_t n, void *stream);

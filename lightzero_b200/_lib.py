@@ -157,6 +157,13 @@ class ValueTargets(C.Structure):
                 ("pow_len", C.c_int32), ("board_games", C.c_int32)]
 
 
+class GumbelHelper(C.Structure):
+    """lzb_gumbel_helper_t"""
+    _fields_ = [("op", C.c_int32), ("n", C.c_int32), ("a_dev", C.c_void_p), ("b_dev", C.c_void_p), ("c_dev", C.c_void_p),
+                ("v_dev", C.c_void_p), ("s0", C.c_float), ("s1", C.c_float), ("s2", C.c_float), ("s3", C.c_float),
+                ("i0", C.c_int32), ("i1", C.c_int32), ("out_dev", C.c_void_p), ("out_i_dev", C.c_void_p), ("tmp_dev", C.c_void_p)]
+
+
 class TraverseIO(C.Structure):
     """lzb_traverse_io_t"""
     _fields_ = [("to_play_dev", C.c_void_p), ("ix_dev", C.c_void_p), ("iy_dev", C.c_void_p),
@@ -227,6 +234,8 @@ _PROTOS = {
     "lzb_peer_error": (C.c_int, [_P, C.c_int, C.c_int64, C.c_int, C.POINTER(C.c_int), _P]),
     "lzb_gumbel_table": (C.c_int, [C.c_int, C.c_int, _P]),
     "lzb_gumbel_noise": (C.c_int, [C.c_float, C.c_int, _P]),
+    "lzb_gumbel_helper": (C.c_int, [_P, _P]),
+    "lzb_check_word": (C.c_int, [_P, _P, _P, _P]),
     "lzb_test_expf": (C.c_int, [_P, _P, C.c_int64, _P]),
     "lzb_test_logf": (C.c_int, [_P, _P, C.c_int64, _P]),
 }

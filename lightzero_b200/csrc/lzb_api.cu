@@ -15,6 +15,7 @@
 #include "lzb_peer.cuh"
 #include "lzb_scaling.cuh"
 #include "lzb_step.cuh"
+#include "lzb_gumbel_helpers.cuh"
 
 using namespace lzb;
 
@@ -127,6 +128,7 @@ __global__ void k_init(Pool p, const int *legal_count, const int *legal_actions)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.N) return;
+    if (i == 0) p.scratch[1] = 0; // the checked build's violation word (LZB_CHK)
     int n = legal_count ? legal_count[i] : 0;
     const bool all = (n <= 0); // empty list == every action legal (cnode.cpp:101-107)
     if (all) n = p.Ad;
@@ -412,6 +414,9 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
 #endif
     f->bytes = l.total; f->delta = 0.0f; f->sim = 0; f->expanded = -1; f->slot_by_kind = false; f->vt_m = -1; f->vt_s = -1; f->players_for = nullptr; f->pbc_base = -1; f->pbc_init = 0.0f;
     cudaStream_t st = (cudaStream_t)stream;
+#ifdef LZB_CHECKED // a slot that was never registered reads as NULL (check 11) instead of whatever the workspace held
+    LZB_CUDA(cudaMemsetAsync((void *)p.slots, 0, (size_t)kMaxGathers * p.E * sizeof(char *), st));
+#endif
     k_init<<<(num_roots + 127) / 128, 128, 0, st>>>(p, legal_count_dev, legal_actions_dev);
     if (variant == LZB_GMZ) {
         f->gumbel_host.resize(action_space);
@@ -881,6 +886,36 @@ int lzb_minmax(lzb_forest_t *f, float *min_dev, float *max_dev, void *stream)
 {
     if (!f || !min_dev || !max_dev) return fail(LZB_E_ARG, "minmax: bad argument");
     k_minmax<<<(f->pool.N + 127) / 128, 128, 0, (cudaStream_t)stream>>>(f->pool, min_dev, max_dev);
+    LZB_CUDA(cudaGetLastError());
+    return LZB_OK;
+}
+
+int lzb_check_word(lzb_forest_t *f, int32_t *word_host, int32_t *checked_build, void *stream)
+{
+    if (!f || !word_host) return fail(LZB_E_ARG, "check_word: bad argument");
+    LZB_CUDA(cudaMemcpyAsync(word_host, f->pool.scratch + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    LZB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    if (checked_build) {
+#ifdef LZB_CHECKED
+        *checked_build = 1;
+#else
+        *checked_build = 0;
+#endif
+    }
+    return LZB_OK;
+}
+
+int lzb_gumbel_helper(const lzb_gumbel_helper_t *h, void *stream)
+{
+    if (!h || h->n <= 0 || h->op < GH_SOFTMAX || h->op > GH_SELECT_INTERIOR || !h->tmp_dev) return fail(LZB_E_ARG, "gumbel_helper: bad argument");
+    const bool needs_out_i = h->op == GH_SELECT_ROOT || h->op == GH_SELECT_INTERIOR;
+    if (needs_out_i ? !h->out_i_dev : !h->out_dev) return fail(LZB_E_ARG, "gumbel_helper: the op's output pointer is NULL");
+    if (!h->a_dev) return fail(LZB_E_ARG, "gumbel_helper: a_dev is NULL");
+    const bool needs_vb = h->op == GH_MIXED_VALUE || h->op == GH_QTRANSFORM || h->op == GH_SCORE_CONSIDERED || needs_out_i;
+    if (needs_vb && (!h->v_dev || !h->b_dev)) return fail(LZB_E_ARG, "gumbel_helper: the op needs visit counts and a second vector");
+    if ((h->op == GH_SCORE_CONSIDERED || h->op == GH_SELECT_ROOT) && !h->c_dev) return fail(LZB_E_ARG, "gumbel_helper: the op needs a third vector");
+    GumbelHelperArgs a{h->op, h->n, h->a_dev, h->b_dev, h->c_dev, h->v_dev, h->s0, h->s1, h->s2, h->s3, h->i0, h->i1, h->out_dev, h->out_i_dev, h->tmp_dev};
+    k_gumbel_helper<<<1, 32, 0, (cudaStream_t)stream>>>(a);
     LZB_CUDA(cudaGetLastError());
     return LZB_OK;
 }

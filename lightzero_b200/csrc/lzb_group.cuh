@@ -186,12 +186,20 @@ __device__ __forceinline__ void tl_mark_dep(int row, int slot, int dep)
 template <int G>
 __device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a, int i, int ix, int parent_reset, int lane, int slot_row = -1)
 {
+    LZB_CHK(p, ix >= 0 && ix < p.E, 10);
     for (int k = 0; k < a.ng; ++k) {
         const long long rb = a.g[k].row_bytes;
         const char *s;
         const int ks = (slot_row >= 0) ? slot_row : k;
         if (a.g[k].src) s = a.g[k].src + ((long long)ix * p.N + i) * rb;
-        else s = ((ix == a.new_e) ? pick3(a.new_slot, ks) : p.slots[(size_t)ks * p.E + ix]) + (long long)i * rb;
+        else {
+            const char *slot = (ix == a.new_e) ? pick3(a.new_slot, ks) : p.slots[(size_t)ks * p.E + ix];
+            LZB_CHK(p, slot != nullptr, 11); // a slot that was never registered
+#ifdef LZB_CHECKED
+            if (slot == nullptr) continue; // reported above: do not fault on it
+#endif
+            s = slot + (long long)i * rb;
+        }
         char *d = a.g[k].dst + (long long)i * rb;
         const bool zero = a.g[k].zero_if_reset && parent_reset == 1;
         if ((rb & 15) == 0 && ((((unsigned long long)s) | ((unsigned long long)d)) & 15ull) == 0) {
@@ -357,6 +365,9 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         const float2 pt = p.pbc[parent_visits - 1]; // {logf((T + c2 + 1) / c2) + c1, sqrtf(T)}, T = parent visits - 1; same round as the block
 #endif
         const int n = h.x;
+        LZB_CHK(p, !going || (e >= 0 && e < p.E), 1);
+        LZB_CHK(p, !going || (n >= 0 && n <= A), 2);
+        LZB_CHK(p, !going || (parent_visits >= 1 && parent_visits - 1 <= p.E), 4);
         if (level == 0) LZB_TLD(tl, 6, n ^ c[0].x ^ c[R - 1].x);
 
         // ---- compute_mean_q: serial fp32 sum over visited children in legal order
@@ -520,6 +531,8 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         ch.y = grp.shfl(mine.y, lsel);
         ch.w = grp.shfl(mine.w, lsel);
         ch.z = 0;
+        LZB_CHK(p, !going || depth <= p.S, 3);
+        LZB_CHK(p, !going || (newpos >= 0 && newpos < (n > 0 ? n : 1)), 5);
         if (going) {
             pos = newpos;
             parent_reset = (VAR == LZB_SMZ) ? 0 : h.z; // smz headers carry is_chance in that slot
@@ -658,6 +671,9 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
 #pragma unroll
         for (int r = 0; r < R; ++r) c[r] = (lane + G * r < A) ? blk[1 + lane + G * r] : make_int4(0, 0, 0, 0);
         const int n = h.x;
+        LZB_CHK(p, !going || (e >= 0 && e < p.E), 1);
+        LZB_CHK(p, !going || (n >= 0 && n <= A), 2);
+        LZB_CHK(p, !going || depth <= p.S, 3);
         const float raw_value = __int_as_float(h.w);
 
         // ---- get_q (:181-197), priors, visit statistics
@@ -719,6 +735,7 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
         // ---- scores
         float sc[R];
         if (at_root) { // cselect_root_child + score_considered
+            LZB_CHK(p, !going || (vsum_i >= 0 && vsum_i < p.E), 6);
             const int considered = p.vtable[vsum_i];
             float ml = -INFINITY;
 #pragma unroll
@@ -811,7 +828,9 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
     const int A = p.A, lane = grp.lane;
     const int4 res = p.res[i];
     const int depth = res.x; // search_len >= 1
+    LZB_CHK(p, !live || (depth >= 1 && depth <= p.S), 7);
     const int e_new = a.latent_index;
+    LZB_CHK(p, e_new >= 1 && e_new < p.E, 8);
     const int to_play = a.to_play[i];
     float value = a.value[i];
     float leaf_reward = a.reward[i];
@@ -998,6 +1017,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 #endif
             } else {
                 int4 *rec = p.tree(i) + slot;
+                LZB_CHK(p, slot >= 1 && slot < p.E * p.B, 9);
 #ifdef LZB_X_CVAL
                 if (VAR != LZB_GMZ) p.cval[(size_t)i * p.E * p.B + slot] = nv; // what select would divide out again at every later visit
 #endif

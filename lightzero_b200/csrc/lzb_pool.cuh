@@ -57,6 +57,16 @@ struct Pool {
     __device__ __forceinline__ int4 *tree(int i) const { return node + (size_t)i * E * B; }
 };
 
+// Checked build (-DLZB_CHECKED; profiles/r02_sanitizer.md): every data-dependent index of the tree kernels is tested against
+// its bound and the largest violated check's code is left in scratch[1] (lzb_check_word reads it).  compute-sanitizer is
+// closed on the GPU pool this was developed on, and most of these indices stay INSIDE the forest's one allocation anyway,
+// where memcheck would see nothing.  Compiles to nothing by default.
+#ifdef LZB_CHECKED
+#define LZB_CHK(pool, cond, code) do { if (!(cond)) atomicMax((pool).scratch + 1, (int)(code)); } while (0)
+#else
+#define LZB_CHK(pool, cond, code) do { } while (0)
+#endif
+
 // k-th of up to kMaxGathers pointers without dynamically indexing kernel-parameter arrays (which costs a stack copy)
 __device__ __forceinline__ const char *pick3(const char *const (&v)[kMaxGathers], int k)
 {

@@ -259,6 +259,39 @@ class RootsBase:
         return f.root_outputs()
 
 
+class NodeBase:
+    """The single `Node` the reference's tree modules expose to their unit tests (mz_tree.pyx:60-72, ez_tree.pyx:70-81,
+    gmz_tree.pyx:68-79, ezs_tree.pyx:86-101): `Node(prior, legal_actions).expand(to_play, current_latent_state_index,
+    batch_index, value_prefix, policy_logits)`.  The `.pyx` constructors ignore their arguments (`__cinit__: pass`: the
+    wrapped CNode is default-constructed, so every action of the logits is legal).  Here a Node is a forest of ONE tree in
+    HBM: expand() is that tree's root expansion (the same k_prepare kernel the batched path runs), and `children()` reads
+    the expanded node back for tests."""
+    _roots_cls = None
+
+    def __init__(self, prior=0.0, legal_actions=None, *extra):
+        self.prior = float(prior)
+        self.legal_actions = [] if legal_actions is None else list(legal_actions)
+        self._extra = extra
+        self.roots = None
+
+    def _make_roots(self):
+        return self._roots_cls(1, [[]])
+
+    def expand(self, to_play, current_latent_state_index, batch_index, value_prefix, policy_logits):
+        self.roots = self._make_roots()
+        self.roots.prepare_no_noise([float(value_prefix)], [list(policy_logits)], [int(to_play)])
+        self.roots._materialize(1)
+
+    def children(self):
+        """dict(prior, visit, value_sum, reward: [A] arrays; n_children; raw_value) of the expanded node."""
+        if self.roots is None:
+            raise RuntimeError("Node.expand has not been called")
+        d = self.roots._materialize().dump_tree(0)
+        n = int(d["hdr"][0][0])
+        return dict(prior=d["prior"][0][:n], visit=d["visit"][0][:n], value_sum=d["value_sum"][0][:n],
+                    reward=d["reward"][0][:n], n_children=n, raw_value=float(d["raw_value"][0]))
+
+
 def _search_cfg(forest, pb_c_base, pb_c_init, discount, to_play, num_simulations=0, max_considered=0, players=None,
                 roots=None):
     """players is batch-global (cnode.cpp:776-781): derived on the host when to_play came as a host object,

@@ -8,7 +8,7 @@ the reference actually executes (sez cnode.cpp:1054-1079)."""
 import torch
 
 from ...forest import _dev
-from .._tree_api import MinMaxStatsList, ResultsWrapper, RootsBase, backprop_tensors, set_tie_break  # noqa: F401
+from .._tree_api import MinMaxStatsList, NodeBase, ResultsWrapper, RootsBase, backprop_tensors, set_tie_break  # noqa: F401
 from .._tree_api import _search_cfg, traverse_tensors
 
 
@@ -64,6 +64,34 @@ class Roots(RootsBase):
 
     def get_sampled_actions_tensor(self):
         return self._prep["sampled_actions"]
+
+
+class Action:
+    """ezs_tree.pyx:26-36: Action(value, is_root_action) - a holder of one sampled action's D-vector."""
+
+    def __init__(self, value=(), is_root_action=0):
+        self.value = [float(v) for v in value]
+        self.is_root_action = int(is_root_action)
+
+
+class Node(NodeBase):
+    """ezs_tree.pyx:86-101: Node(prior, legal_actions, action_space_size, num_of_sampled_actions, continuous_action_space);
+    expand() samples the node's K actions on the device like Roots.prepare_no_noise does."""
+    _roots_cls = Roots
+
+    def __init__(self, prior=0.0, legal_actions=None, action_space_size=1, num_of_sampled_actions=1,
+                 continuous_action_space=False):
+        super().__init__(prior, legal_actions)
+        self.action_space_size = int(action_space_size)
+        self.num_of_sampled_actions = int(num_of_sampled_actions)
+        self.continuous_action_space = bool(continuous_action_space)
+
+    def _make_roots(self):
+        return Roots(1, [[]], self.action_space_size, self.num_of_sampled_actions, self.continuous_action_space)
+
+    def sampled_actions(self):
+        """[K] Action objects of the expanded node (what CNode::legal_actions holds after expand)."""
+        return [Action(v, 1) for v in self.roots.get_sampled_actions()[0]]
 
 
 def batch_traverse(roots, pb_c_base, pb_c_init, discount_factor, min_max_stats_lst, results, virtual_to_play_batch,

@@ -5,12 +5,15 @@ list-based reference API (lightzero_b200/ctree/*.py) is a thin layer over it.  P
 device memory and the CUDA stream here.
 """
 import ctypes as C
+import os
 
 import numpy as np
 import torch
 
 from . import _lib
 from ._lib import BackpropIO, Chance, ChanceHead, Gather, Reuse, SearchCfg, Slots, TraverseIO, check
+
+_CHECKED_RUN = bool(os.environ.get("LZB_CHECKED"))  # with a -DLZB_CHECKED library: raise at the end of a search that broke a check
 
 VARIANT_ID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3, "smz": 4}
 RNG_BATCH, RNG_PER_ROOT = 1, 2
@@ -374,10 +377,22 @@ class Forest:
             cv = torch.empty((self.N, self.A), dtype=torch.float32, device=d)
         check(self.L.lzb_root_outputs(self.h, _p(visits), _p(legal_count), _p(values), float(discount), _p(pol), _p(cv),
                                       _stream(d)))
+        if _CHECKED_RUN and not torch.cuda.is_current_stream_capturing():  # scripts/gpu_checked.sh: every search ends here
+            word, _ = self.check_word()
+            if word:
+                raise RuntimeError("checked build: index check %d was violated during this search" % word)
         out = dict(visits=visits, legal_count=legal_count, values=values)
         if gumbel:
             out.update(policies=pol, children_values=cv)
         return out
+
+    def check_word(self):
+        """(code, checked_build): the largest code of a violated index check of a -DLZB_CHECKED library since the forest
+        was created / reset (0 = none; always 0 with the shipped build), and whether the loaded library is a checked one
+        (profiles/r02_sanitizer.md).  Synchronises."""
+        w, c = C.c_int32(0), C.c_int32(0)
+        check(self.L.lzb_check_word(self.h, C.byref(w), C.byref(c), _stream(self.device)))
+        return int(w.value), bool(c.value)
 
     def trajectories(self):
         """(actions [N, S+1] int32, lengths [N] int32): greedy best_action chains (get_trajectories)."""

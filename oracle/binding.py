@@ -99,6 +99,77 @@ def sample_libstdcxx(logits, K, D, A, continuous, seed_base):
     return out
 
 
+# ---- single-node Gumbel helpers (gmz_tree.pyx:97-149): the oracle's restatement and the compiled reference, same signatures
+def _gh_case(case):
+    f = lambda k: np.ascontiguousarray(case[k], np.float32)
+    return f("logits"), np.ascontiguousarray(case["child_visit"], np.int32), f("child_prior")
+
+
+def gumbel_helpers_oracle(case):
+    """case: dict(logits [A], to_play, value_prefix, value, discount, num_simulations, max_considered, child_visit [A],
+    child_prior [A], maxvisit_init, value_scale, rescale_values, epsilon, x [A], q [A], gumbel [A], nq [A], considered)
+    -> dict of what every helper returns, from oracle/mcts_oracle.c (node-taking helpers: a freshly expanded root)."""
+    O = oracle_lib()
+    O.orc_mixed_value.restype = C.c_float
+    logits, cv, cp = _gh_case(case)
+    A = logits.size
+    f32 = lambda k: np.ascontiguousarray(case[k], np.float32)
+    P = lambda a: a.ctypes.data_as(C.c_void_p)
+    out = {}
+    x = f32("x").copy(); O.orc_softmax(P(x), A); out["softmax"] = x
+    out["mixed_value"] = np.float32(O.orc_mixed_value(C.c_float(case["value"]), P(f32("q")), P(cv), P(cp), A))
+    x = f32("x").copy(); O.orc_rescale(P(x), A, C.c_float(case["epsilon"])); out["rescale"] = x
+    sc = np.zeros(A, np.float32)
+    O.orc_score_considered(int(case["considered"]), P(f32("gumbel")), P(logits), P(f32("nq")), P(cv), A, P(sc)); out["score_considered"] = sc
+    # the expanded node: priors = softmax of the logits (csoftmax form is NOT what expand uses: exp(l - max) / sum)
+    pri = node_priors_oracle(logits)
+    out["priors"] = pri
+    q0 = np.zeros(A, np.float32)  # fresh children: reward 0 + discount * value() 0
+    qt = np.zeros(A, np.float32)
+    O.orc_qtransform(P(q0), C.c_float(case["value"]), P(cv), P(cp), A, C.c_float(case["maxvisit_init"]), C.c_float(case["value_scale"]),
+                     int(case["rescale_values"]), C.c_float(case["epsilon"]), P(qt)); out["qtransform"] = qt
+    zero_v = np.zeros(A, np.int32)
+    gum = np.zeros(A, np.float32); O.orc_gumbel_noise(C.c_float(10.0), A, P(gum))
+    tab = np.zeros((int(case["max_considered"]) + 1, int(case["num_simulations"])), np.int32)
+    O.orc_gumbel_table(int(case["max_considered"]), int(case["num_simulations"]), P(tab))
+    considered = int(tab[min(int(case["max_considered"]), int(case["num_simulations"]))][0])
+    out["root_action"] = int(O.orc_select_root_arrays(P(q0), C.c_float(case["value"]), P(zero_v), P(pri), P(gum), A, considered))
+    out["interior_action"] = int(O.orc_select_interior_arrays(P(q0), C.c_float(case["value"]), P(zero_v), P(pri), A))
+    return out
+
+
+def node_priors_oracle(logits):
+    """CNode::expand's prior computation (gmz cnode.cpp:112-166: exp(l - max) / sum in fp32, serial) through a 1-root oracle forest."""
+    logits = np.ascontiguousarray(logits, np.float32)
+    f = OracleForest("gmz", 1, logits.size)
+    f.prepare(0.0, None, np.zeros(1, np.float32), logits[None, :], np.full(1, -1, np.int32), values=np.zeros(1, np.float32))
+    return f.dump_tree(0, 1)["prior"][0][:logits.size].copy()
+
+
+def gumbel_helpers_reference(case):
+    """The same dict from the compiled reference (oracle/_ref/libref_gmz.so)."""
+    R = ref_lib("gmz")
+    R.ref_mixed_value.restype = C.c_float
+    logits, cv, cp = _gh_case(case)
+    A = logits.size
+    f32 = lambda k: np.ascontiguousarray(case[k], np.float32)
+    P = lambda a: a.ctypes.data_as(C.c_void_p)
+    out = {}
+    x = f32("x").copy(); R.ref_softmax(P(x), A); out["softmax"] = x
+    out["mixed_value"] = np.float32(R.ref_mixed_value(C.c_float(case["value"]), P(f32("q")), P(cv), P(cp), A))
+    x = f32("x").copy(); R.ref_rescale(P(x), A, C.c_float(case["epsilon"])); out["rescale"] = x
+    sc = np.zeros(A, np.float32)
+    R.ref_score_considered(int(case["considered"]), P(f32("gumbel")), P(logits), P(f32("nq")), P(cv), A, P(sc)); out["score_considered"] = sc
+    pri, qt = np.zeros(A, np.float32), np.zeros(A, np.float32)
+    ra, ia = C.c_int(0), C.c_int(0)
+    R.ref_node_helpers(int(case["to_play"]), C.c_float(case["value_prefix"]), C.c_float(case["value"]), P(logits), A,
+                       C.c_float(case["discount"]), int(case["num_simulations"]), int(case["max_considered"]), P(cv), P(cp),
+                       C.c_float(case["maxvisit_init"]), C.c_float(case["value_scale"]), int(case["rescale_values"]),
+                       C.c_float(case["epsilon"]), P(pri), P(qt), C.byref(ra), C.byref(ia))
+    out.update(priors=pri, qtransform=qt, root_action=int(ra.value), interior_action=int(ia.value))
+    return out
+
+
 _ref_libs = {}
 
 

@@ -409,6 +409,91 @@ static void completed_q(const Node *nd, float discount, int *visit, float *prior
     free(p);
 }
 
+/* ---- the single-node helpers of gmz_tree.pyx:97-149 over plain arrays (tests/test_gumbel_helpers*.py) */
+float orc_mixed_value(float raw_value, const float *q, const int *visit, const float *prior, int n)
+{
+    float *p = (float *)malloc(sizeof(float) * (size_t)n);
+    memcpy(p, prior, sizeof(float) * (size_t)n);
+    float r = compute_mixed_value(raw_value, q, visit, p, n);
+    free(p);
+    return r;
+}
+
+void orc_rescale(float *x, int n, float epsilon)
+{ /* rescale_qvalues, gmz:972-987 */
+    float mx = x[0], mn = x[0];
+    for (int j = 1; j < n; ++j) {
+        if (x[j] > mx) mx = x[j];
+        if (x[j] < mn) mn = x[j];
+    }
+    float gap = mx - mn;
+    gap = (gap < epsilon) ? epsilon : gap;
+    for (int j = 0; j < n; ++j) x[j] = (x[j] - mn) / gap;
+}
+
+void orc_qtransform(const float *q, float raw_value, const int *visit, const float *prior, int n, float maxvisit_init,
+                    float value_scale, int rescale_values, float epsilon, float *out)
+{ /* qtransform_completed_by_mix_value, gmz:989-1040, with its arguments instead of the header defaults */
+    float *p = (float *)malloc(sizeof(float) * (size_t)n);
+    memcpy(p, prior, sizeof(float) * (size_t)n);
+    csoftmax(p, n);
+    float value = compute_mixed_value(raw_value, q, visit, p, n);
+    for (int j = 0; j < n; ++j) out[j] = visit[j] > 0 ? q[j] : value;
+    if (rescale_values) orc_rescale(out, n, epsilon);
+    int maxv = visit[0];
+    for (int j = 1; j < n; ++j)
+        if (visit[j] > maxv) maxv = visit[j];
+    float visit_scale = maxvisit_init + (float)maxv;
+    for (int j = 0; j < n; ++j) out[j] = out[j] * visit_scale * value_scale;
+    free(p);
+}
+
+void orc_score_considered(int considered_visit, const float *gumbel, const float *logits, const float *nq, const int *visit, int n,
+                          float *out)
+{ /* score_considered, gmz:1097-1132 */
+    float max_logit = logits[0];
+    for (int j = 1; j < n; ++j)
+        if (logits[j] > max_logit) max_logit = logits[j];
+    for (int j = 0; j < n; ++j) {
+        float penalty = (visit[j] == considered_visit) ? 0.0f : -INFINITY;
+        float s = gumbel[j] + (logits[j] - max_logit) + nq[j];
+        out[j] = ((-1e9f < s) ? s : -1e9f) + penalty;
+    }
+}
+
+static int first_argmax(const float *s, int n)
+{
+    float best = -INFINITY;
+    int pos = 0;
+    for (int j = 0; j < n; ++j)
+        if (s[j] > best) { best = s[j]; pos = j; }
+    return pos;
+}
+
+int orc_select_root_arrays(const float *q, float raw_value, const int *visit, const float *prior, const float *gumbel, int n,
+                           int considered_visit)
+{ /* cselect_root_child, gmz:701-745 */
+    float *cq = (float *)malloc(sizeof(float) * (size_t)n), *sc = (float *)malloc(sizeof(float) * (size_t)n);
+    orc_qtransform(q, raw_value, visit, prior, n, 50.0f, 0.1f, 1, 1e-8f, cq);
+    orc_score_considered(considered_visit, gumbel, prior, cq, visit, n, sc);
+    int pos = first_argmax(sc, n);
+    free(cq); free(sc);
+    return pos;
+}
+
+int orc_select_interior_arrays(const float *q, float raw_value, const int *visit, const float *prior, int n)
+{ /* cselect_interior_child, gmz:747-790 */
+    float *cq = (float *)malloc(sizeof(float) * (size_t)n);
+    orc_qtransform(q, raw_value, visit, prior, n, 50.0f, 0.1f, 1, 1e-8f, cq);
+    int vsum = 0;
+    for (int j = 0; j < n; ++j) { cq[j] = prior[j] + cq[j]; vsum += visit[j]; }
+    csoftmax(cq, n);
+    for (int j = 0; j < n; ++j) cq[j] = cq[j] - (float)visit[j] / (float)(1 + vsum);
+    int pos = first_argmax(cq, n);
+    free(cq);
+    return pos;
+}
+
 static int considered_seq(int m, int S, int *out)
 { /* get_sequence_of_considered_visits (gmz:1042-1077) */
     if (m <= 1) {

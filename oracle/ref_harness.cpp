@@ -334,6 +334,51 @@ void ref_softmax(float *x, int n)
     tree::csoftmax(v, n);
     for (int i = 0; i < n; ++i) x[i] = v[i];
 }
+
+// ---- the single-node helpers gmz_tree.pyx:97-149 hands to the reference's unit tests, called as they are
+float ref_mixed_value(float raw_value, const float *q, const int *visit, const float *prior, int n)
+{
+    std::vector<float> vq(q, q + n), vp(prior, prior + n);
+    std::vector<int> vv(visit, visit + n);
+    return tree::compute_mixed_value(raw_value, vq, vv, vp);
+}
+
+void ref_rescale(float *x, int n, float epsilon)
+{
+    std::vector<float> v(x, x + n);
+    tree::rescale_qvalues(v, epsilon);
+    for (int i = 0; i < n; ++i) x[i] = v[i];
+}
+
+void ref_score_considered(int considered_visit, const float *gumbel, const float *logits, const float *nq, const int *visit, int n,
+                          float *out)
+{
+    std::vector<float> s = tree::score_considered(considered_visit, std::vector<float>(gumbel, gumbel + n), std::vector<float>(logits, logits + n),
+                                                  std::vector<float>(nq, nq + n), std::vector<int>(visit, visit + n));
+    for (int i = 0; i < n; ++i) out[i] = s[i];
+}
+
+// One node built like CRoots builds a root (CNode(prior, legal_actions): the constructor that draws the node's gumbel
+// noise - the .pyx Node wraps a default-constructed CNode whose gumbel vector is EMPTY, so select_root_child on it reads
+// past the end), expanded, then handed to the three node-taking helpers.  child_visit / child_prior are the caller's
+// vectors for qtransform (pqtransform_completed_by_mix_value's arguments); the selections read the node's own children.
+void ref_node_helpers(int to_play, float value_prefix, float value, const float *logits, int A, float discount, int num_simulations,
+                      int max_num_considered_actions, const int *child_visit, const float *child_prior, float maxvisit_init,
+                      float value_scale, int rescale_values, float epsilon, float *priors_out, float *qtransform_out, int *root_action,
+                      int *interior_action)
+{
+    std::vector<int> legal(A);
+    for (int i = 0; i < A; ++i) legal[i] = i;
+    tree::CNode node(0.0f, legal);
+    node.expand(to_play, 0, 0, value_prefix, value, std::vector<float>(logits, logits + A));
+    for (int i = 0; i < A; ++i) priors_out[i] = node.get_child(i)->prior;
+    std::vector<int> cv(child_visit, child_visit + A);
+    std::vector<float> cp(child_prior, child_prior + A);
+    std::vector<float> t = tree::qtransform_completed_by_mix_value(&node, cv, cp, discount, maxvisit_init, value_scale, rescale_values != 0, epsilon);
+    for (int i = 0; i < A; ++i) qtransform_out[i] = t[i];
+    *root_action = tree::cselect_root_child(&node, discount, num_simulations, max_num_considered_actions);
+    *interior_action = tree::cselect_interior_child(&node, discount);
+}
 #endif
 
 // Whole-tree dump keyed by current_latent_state_index e (unique per tree, 0 = root): children of the
