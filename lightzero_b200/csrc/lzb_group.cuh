@@ -183,6 +183,23 @@ __device__ __forceinline__ void tl_mark_dep(int row, int slot, int dep)
 
 // Leaf rows of one tree moved by the G lanes of its group (same semantics as gather_rows in lzb_select.cuh).
 // slot_row >= 0: the slot-table row to read instead of the gather's own index (stochastic tree: the row of the parent's kind)
+// experiment LZB_X_GATHER_STCS: the gathered rows written with the streaming (evict-first) policy, so that 33 MB of rows per
+// step do not push the node pool out of L2
+// experiments LZB_X_GATHER_LDG / LZB_X_GATHER_LDNC: the row loads with the default policy / through the read-only path instead
+// of the streaming (evict-first) one
+#if defined(LZB_X_GATHER_LDG)
+#define LZB_GATHER_LD(ptr) (*(ptr))
+#elif defined(LZB_X_GATHER_LDNC)
+#define LZB_GATHER_LD(ptr) __ldg(ptr)
+#else
+#define LZB_GATHER_LD(ptr) __ldcs(ptr)
+#endif
+#ifdef LZB_X_GATHER_STCS
+#define LZB_GATHER_ST(ptr, val) __stcs((ptr), (val))
+#else
+#define LZB_GATHER_ST(ptr, val) (*(ptr) = (val))
+#endif
+
 template <int G>
 __device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a, int i, int ix, int parent_reset, int lane, int slot_row = -1)
 {
@@ -213,18 +230,28 @@ __device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a
                 for (; t + 11 * G < n4; t += 12 * G) { // 12 independent 16-byte loads in flight per lane
                     int4 v[12];
 #pragma unroll
-                    for (int u = 0; u < 12; ++u) v[u] = __ldcs(s4 + t + u * G);
+                    for (int u = 0; u < 12; ++u) v[u] = LZB_GATHER_LD(s4 + t + u * G);
 #pragma unroll
-                    for (int u = 0; u < 12; ++u) d4[t + u * G] = v[u];
+                    for (int u = 0; u < 12; ++u) LZB_GATHER_ST(d4 + t + u * G, v[u]);
                 }
+#ifndef LZB_X_NO_GATHER8 // rows of 8 vectors per lane (the EfficientZero LSTM rows: 2 KB per 16-lane group) in one round trip instead of
+                          // two: ez 29.65 -> 29.45 us, its tree + LSTM rows alone 19.08 -> 18.60 us (round 2; -DLZB_X_NO_GATHER8 = before)
+                for (; t + 7 * G < n4; t += 8 * G) {
+                    int4 v[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) v[u] = LZB_GATHER_LD(s4 + t + u * G);
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) LZB_GATHER_ST(d4 + t + u * G, v[u]);
+                }
+#endif
                 for (; t + 3 * G < n4; t += 4 * G) {
                     int4 v[4];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) v[u] = __ldcs(s4 + t + u * G);
+                    for (int u = 0; u < 4; ++u) v[u] = LZB_GATHER_LD(s4 + t + u * G);
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) d4[t + u * G] = v[u];
+                    for (int u = 0; u < 4; ++u) LZB_GATHER_ST(d4 + t + u * G, v[u]);
                 }
-                for (; t < n4; t += G) d4[t] = __ldcs(s4 + t);
+                for (; t < n4; t += G) d4[t] = LZB_GATHER_LD(s4 + t);
             }
         } else {
             const int *s1 = reinterpret_cast<const int *>(s);
