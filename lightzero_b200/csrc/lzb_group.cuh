@@ -183,6 +183,28 @@ __device__ __forceinline__ void tl_mark_dep(int row, int slot, int dep)
 
 // Leaf rows of one tree moved by the G lanes of its group (same semantics as gather_rows in lzb_select.cuh).
 // slot_row >= 0: the slot-table row to read instead of the gather's own index (stochastic tree: the row of the parent's kind)
+// experiment LZB_X_ROW_PREFETCH: a walk that ENTERS a node with visit count 1 ends there for certain (none of its children has
+// been visited, so whichever is chosen is unexpanded), i.e. the rows this tree will gather are that node's - known one whole
+// level (block read + scores, ~3.6 k cycles) before the gather starts.  The group asks L2 for them right away
+// (prefetch.global.L2: no registers, no wasted traffic since the prediction is exact); the deepest trees - the ones that set
+// the launch time - almost always end on such a node.
+template <int G>
+__device__ __forceinline__ void prefetch_rows_g(const Pool &p, const SelectArgs &a, int i, int ix, int lane)
+{
+    for (int k = 0; k < a.ng; ++k) {
+        const long long rb = a.g[k].row_bytes;
+        const char *s;
+        if (a.g[k].src) s = a.g[k].src + ((long long)ix * p.N + i) * rb;
+        else {
+            const char *slot = (ix == a.new_e) ? pick3(a.new_slot, k) : p.slots[(size_t)k * p.E + ix];
+            if (slot == nullptr) continue;
+            s = slot + (long long)i * rb;
+        }
+        for (long long off = (long long)lane * 128; off < rb; off += (long long)G * 128)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(s + off));
+    }
+}
+
 // experiment LZB_X_GATHER_STCS: the gathered rows written with the streaming (evict-first) policy, so that 33 MB of rows per
 // step do not push the node pool out of L2
 // experiments LZB_X_GATHER_LDG / LZB_X_GATHER_LDNC: the row loads with the default policy / through the read-only path instead
@@ -370,6 +392,9 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
         // ---- one round of independent reads per level: the header (same address in every lane) and R records per lane
         const int4 *blk = tree + e * B; // e * B < 2^31: the whole forest is indexed with size_t only across trees
         const int4 h = blk[0];
+#if defined(LZB_X_ROW_PREFETCH) && !defined(LZB_X_ROW_PREFETCH_AT_DESCENT)
+        if (VAR != LZB_SMZ && going && !is_root && parent_visits <= LZB_X_ROW_PREFETCH) prefetch_rows_g<G>(p, a, i, e, lane);
+#endif
         int4 c[R];
 #ifdef LZB_X_CVAL
         float cvl[R]; // experiment: CNode::value() of each child as the backup stored it, same round as the records
@@ -581,6 +606,9 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
                 parent_q = mean_q;
                 is_root = false;
                 e = ce;
+#if defined(LZB_X_ROW_PREFETCH) && defined(LZB_X_ROW_PREFETCH_AT_DESCENT) // the same request from inside the branch that descends
+                if (VAR != LZB_SMZ && parent_visits <= LZB_X_ROW_PREFETCH) prefetch_rows_g<G>(p, a, i, e, lane);
+#endif
             }
         }
         if (level == 1) LZB_TLD(tl, 10, e ^ depth);
