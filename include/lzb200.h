@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define LZB_ABI_VERSION 5
+#define LZB_ABI_VERSION 6
 
 /* tree flavours */
 #define LZB_MZ 0  /* ctree_muzero */
@@ -375,13 +375,19 @@ int lzb_target_policies(const int32_t *visits_dev, const int32_t *legal_count_de
  *   target_values[t] = v and target_rewards[t] = rewards[b][current] if current < segment_len[b], else 0 and 0.
  * float64 arithmetic in the reference's order.  pow_table_dev[k] = discount ** k for k < pow_len (computed by the caller
  * on the HOST, so that it is the host libm's pow like Python's `**`); pow_len must exceed every td_steps entry.
- * to_play_dev [B, to_play_stride] is read only when board_games != 0 (:494-499, indexed exactly as the reference does). */
+ * to_play_dev [B, to_play_stride] is read only when board_games != 0 (:494-499, indexed exactly as the reference does).
+ * lstm_horizon_len > 0 selects EfficientZero's flavour (game_buffer_efficientzero.py:261-316; ABI v6): target_rewards holds
+ * the VALUE PREFIX - the running float64 sum of rewards[b][current] over the steps inside the segment since the last horizon
+ * reset, kept (not zeroed) past the segment's end - where a reset happens at every step whose index in the WHOLE transition
+ * batch, t, is a multiple of lstm_horizon_len (the reference's horizon_id is not restarted per segment, :278), and a reset
+ * also moves the base index of the board-games sign rule to that step (:298-300). */
 typedef struct {
     const float *root_values_dev, *value_mask_dev, *rewards_dev;
     const int32_t *td_steps_dev, *reward_len_dev, *segment_len_dev, *pos_dev, *to_play_dev;
     const double *pow_table_dev;
     double *target_values_dev, *target_rewards_dev;
     int32_t num_segments, num_unroll_steps, reward_stride, to_play_stride, pow_len, board_games;
+    int32_t lstm_horizon_len;
 } lzb_value_targets_t;
 int lzb_value_targets(const lzb_value_targets_t *args, void *stream);
 

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "liblzb200.so")
-ABI_VERSION = 5  # LZB_ABI_VERSION of include/lzb200.h
+ABI_VERSION = 6  # LZB_ABI_VERSION of include/lzb200.h
 SOURCES = ["lzb_api.cu", "lzb_scaling.cuh", "lzb_select.cuh", "lzb_expand.cuh", "lzb_step.cuh", "lzb_group.cuh", "lzb_sample.cuh", "lzb_collect.cuh", "lzb_peer.cuh", "lzb_pool.cuh", "lzb_math.cuh"]
 
 NVCC_FLAGS = [
@@ -154,7 +154,7 @@ class ValueTargets(C.Structure):
                 ("pos_dev", C.c_void_p), ("to_play_dev", C.c_void_p), ("pow_table_dev", C.c_void_p),
                 ("target_values_dev", C.c_void_p), ("target_rewards_dev", C.c_void_p), ("num_segments", C.c_int32),
                 ("num_unroll_steps", C.c_int32), ("reward_stride", C.c_int32), ("to_play_stride", C.c_int32),
-                ("pow_len", C.c_int32), ("board_games", C.c_int32)]
+                ("pow_len", C.c_int32), ("board_games", C.c_int32), ("lstm_horizon_len", C.c_int32)]
 
 
 class GumbelHelper(C.Structure):

@@ -33,15 +33,22 @@ def _search(mcts, model, action_mask, policy_logits, reward_roots, latent_state_
     """mask -> legal lists -> Roots -> prepare(+noise) -> search; returns (roots, legal_count, legal_ids)."""
     dev = policy_logits.device
     N, A = policy_logits.shape
-    cnt, ids = legal_from_mask(action_mask, device=dev)
-    roots = mcts.roots(N, (cnt, ids), *extra_roots_args)
+    if action_mask is None:  # no mask (continuous / sampled action spaces): the tree has no legal-action list
+        cnt = ids = None
+        roots = mcts.roots(N, None, *extra_roots_args)
+    else:
+        cnt, ids = legal_from_mask(action_mask, device=dev)
+        roots = mcts.roots(N, (cnt, ids), *extra_roots_args)
     roots.root_offset = int(root_offset)
     to_play = _dev(to_play, torch.int32, dev).reshape(-1)
     reward = _dev(reward_roots, torch.float32, dev).reshape(-1)
     gumbel = getattr(roots, "variant", "mz") == "gmz"
     vals = (() if not gumbel else (_dev(root_values, torch.float32, dev).reshape(-1),))
     if noise_weight and noise_weight > 0:
-        noise = dirichlet_noise(alpha, cnt, A, seed=seed, counter=counter, root_offset=root_offset, device=dev)
+        width = int(getattr(roots, "num_of_sampled_actions", A))  # the Sampled tree's noise is over its K sampled actions
+        if cnt is None:
+            cnt = torch.full((N,), width, dtype=torch.int32, device=dev)
+        noise = dirichlet_noise(alpha, cnt, width, seed=seed, counter=counter, root_offset=root_offset, device=dev)
         roots.prepare(noise_weight, noise, reward, *vals, policy_logits, to_play)
     else:
         roots.prepare_no_noise(reward, *vals, policy_logits, to_play)
@@ -82,7 +89,7 @@ def collect_search(mcts, model, latent_state_roots, reward_roots, policy_logits,
 
 def reanalyze_policy_targets(mcts, model, latent_state_roots, reward_pool, policy_logits_pool, action_mask, to_play,
                              policy_mask, num_unroll_steps, fixed_action_space=True, reanalyze_noise=None,
-                             root_values=None, hidden_state_roots=None, seed=0, counter=None, root_offset=0):
+                             root_values=None, hidden_state_roots=None, seed=0, counter=None, root_offset=0, roots_args=()):
     """_compute_target_policy_reanalyzed (game_buffer_muzero.py:519-660) for a transition batch of
     T = batch_size * (num_unroll_steps + 1) roots whose ``initial_inference`` outputs are on the device.
 
@@ -91,7 +98,12 @@ def reanalyze_policy_targets(mcts, model, latent_state_roots, reward_pool, polic
     :611-656   per root: visits / sum(visits) placed at the legal action ids, zero rows where policy_mask == 0
                                                       -> lzb_target_policies (float64 division, float32 result)
     Returns dict(target_policies [B, U+1, A] f32, child_visits [T, A] f32 (the normalised distributions the reference
-    writes back into ``child_visit_segment``, in legal-action order), root_values [T] f32, visit_counts, legal_count)."""
+    writes back into ``child_visit_segment``, in legal-action order), root_values [T] f32, visit_counts, legal_count).
+
+    EfficientZero (game_buffer_efficientzero.py:337-464): pass ``hidden_state_roots``.  Sampled EfficientZero
+    (game_buffer_sampled_efficientzero.py:437-585): ``roots_args=(action_space_size, num_of_sampled_actions,
+    continuous_action_space)`` as its ``roots()`` takes them, ``action_mask=None`` for continuous actions; the targets are
+    then over the K sampled actions and ``root_sampled_actions`` [T, K, D] comes back with them (:526-533)."""
     logits = policy_logits_pool
     dev = logits.device
     T_, A = logits.shape
@@ -103,18 +115,21 @@ def reanalyze_policy_targets(mcts, model, latent_state_roots, reward_pool, polic
     w = float(_cfg(mcts, "root_noise_weight", 0.25)) if reanalyze_noise else 0.0
     roots, cnt, ids = _search(mcts, model, action_mask, logits, reward_pool, latent_state_roots, to_play, w,
                               float(_cfg(mcts, "root_dirichlet_alpha", 0.3)), root_values, hidden_state_roots, seed, counter,
-                              root_offset)
+                              root_offset, extra_roots_args=tuple(roots_args))
     visits, legal_count = roots.get_distributions_tensor()
     pm = _dev(policy_mask, torch.int32, dev)
     pol = target_policies(visits, legal_count, None if fixed_action_space else ids, pm)
     child = target_policies(visits, legal_count, None, pm)  # in legal-action order, as child_visit stores it (:625-626)
-    return dict(target_policies=pol.reshape(T_ // per, per, A), child_visits=child, root_values=roots.get_values_tensor(),
-                visit_counts=visits, legal_count=legal_count, roots=roots)
+    out = dict(target_policies=pol.reshape(T_ // per, per, pol.shape[1]), child_visits=child, root_values=roots.get_values_tensor(),
+               visit_counts=visits, legal_count=legal_count, roots=roots)
+    if hasattr(roots, "get_sampled_actions_tensor"):  # Sampled EfficientZero (game_buffer_sampled_efficientzero.py:526-533)
+        out["root_sampled_actions"] = roots.get_sampled_actions_tensor()
+    return out
 
 
 def reanalyze_value_targets(root_values, td_steps, value_mask, rewards, reward_lens, game_segment_lens,
                             pos_in_game_segment, num_unroll_steps, discount_factor, to_play_segments=None,
-                            board_games=False):
+                            board_games=False, lstm_horizon_len=0):
     """The tail of _compute_target_reward_value (game_buffer_muzero.py:463-513): bootstrapped n-step value targets and
     reward targets of a transition batch, one kernel (lzb_value_targets), float64 like the reference's Python floats.
 
@@ -122,7 +137,11 @@ def reanalyze_value_targets(root_values, td_steps, value_mask, rewards, reward_l
     in reanalyze_policy_targets) or the model's predicted values.  td_steps [T] int, value_mask [T]; rewards [B, Lmax]
     f32 = each game segment's reward list zero-padded, reward_lens [B] their true lengths; game_segment_lens [B];
     pos_in_game_segment [B]; to_play_segments [B, Lmax] int for board games (env_type == 'board_games' and to_play in
-    {1, 2}).  Returns (target_rewards [B, U+1] f64, target_values [B, U+1] f64) on the device."""
+    {1, 2}).  Returns (target_rewards [B, U+1] f64, target_values [B, U+1] f64) on the device.
+
+    ``lstm_horizon_len`` > 0 is EfficientZero's flavour (game_buffer_efficientzero.py:261-316; the Sampled buffer's is the
+    same code): the first result is then the target VALUE PREFIX - the running sum of rewards since the last horizon reset,
+    with the reference's batch-wide reset counter - instead of the per-step reward."""
     rv = root_values if isinstance(root_values, torch.Tensor) and root_values.is_cuda else _dev(
         root_values, torch.float32, torch.device("cuda", torch.cuda.current_device()))
     dev = rv.device
@@ -154,7 +173,8 @@ def reanalyze_value_targets(root_values, td_steps, value_mask, rewards, reward_l
     args = _lib.ValueTargets(rv.data_ptr(), vm.data_ptr(), rew.data_ptr(), td.data_ptr(), rl.data_ptr(), sl.data_ptr(),
                              pos.data_ptr(), None if tp is None else tp.data_ptr(), table.data_ptr(), tv.data_ptr(),
                              tr.data_ptr(), B, int(num_unroll_steps), int(rew.shape[1]),
-                             0 if tp is None else int(tp.shape[1]), int(table.numel()), int(bool(board_games)))
+                             0 if tp is None else int(tp.shape[1]), int(table.numel()), int(bool(board_games)),
+                             int(lstm_horizon_len))
     with torch.cuda.device(dev):
         _lib.check(_lib.lib().lzb_value_targets(C.byref(args), _stream(dev)))
     return tr, tv

@@ -1015,7 +1015,8 @@ int lzb_value_targets(const lzb_value_targets_t *x, void *stream)
     if (x->board_games && (!x->to_play_dev || x->to_play_stride <= 0)) return fail(LZB_E_ARG, "value_targets: board_games needs to_play [B, to_play_stride]");
     ValueTargetArgs a{x->root_values_dev, x->td_steps_dev, x->value_mask_dev, x->rewards_dev, x->reward_len_dev, x->segment_len_dev, x->pos_dev,
                       x->to_play_dev, x->pow_table_dev, x->target_values_dev, x->target_rewards_dev, x->num_segments, x->num_unroll_steps,
-                      x->reward_stride, x->to_play_stride, x->pow_len, x->board_games};
+                      x->reward_stride, x->to_play_stride, x->pow_len, x->board_games, x->lstm_horizon_len};
+    if (x->lstm_horizon_len < 0) return fail(LZB_E_ARG, "value_targets: lstm_horizon_len must be >= 0");
     const long long total = (long long)x->num_segments * (x->num_unroll_steps + 1);
     k_value_targets<<<(int)((total + 127) / 128), 128, 0, (cudaStream_t)stream>>>(a);
     LZB_CUDA(cudaGetLastError());

@@ -215,6 +215,7 @@ struct ValueTargetArgs {
     double *target_values;      // [B, U + 1]
     double *target_rewards;     // [B, U + 1]
     int B, U, reward_stride, to_play_stride, pow_len, board_games;
+    int horizon;                // EfficientZero: lstm_horizon_len (value-prefix targets), 0 = MuZero's reward targets
 };
 
 __global__ void k_value_targets(ValueTargetArgs a)
@@ -232,6 +233,17 @@ __global__ void k_value_targets(ValueTargetArgs a)
     v = __dmul_rn(v, (double)a.value_mask[t]);                          // :479
     const int len = a.reward_len[b];
     const float *rew = a.rewards + (size_t)b * a.reward_stride;
+    // EfficientZero (game_buffer_efficientzero.py:278,298-301): horizon_id == t runs over the whole batch; the reset of step u'
+    // takes effect AFTER that step's value sum, so this step's base index is the last reset strictly before u, its value
+    // prefix restarts at the last reset at or before u
+    int base_index = state_index, prefix_from = 0;
+    if (a.horizon > 0) {
+        for (int w = 0; w <= u; ++w)
+            if ((b * per + w) % a.horizon == 0) {
+                if (w < u) base_index = state_index + w;
+                prefix_from = w;
+            }
+    }
     // reward_list[current_index:bootstrap_index]: Python slice clipping (:490-491)
     const int lo = min(max(current_index, 0), len), hi = min(max(current_index + td, 0), len);
     for (int k = lo; k < hi; ++k) {
@@ -240,12 +252,19 @@ __global__ void k_value_targets(ValueTargetArgs a)
         bool same = true;
         if (a.board_games) {
             const int *tp = a.to_play + (size_t)b * a.to_play_stride;
-            same = tp[min(state_index, a.to_play_stride - 1)] == tp[min(i, a.to_play_stride - 1)]; // to_play_list[base_index] == to_play_list[i] (:496)
+            same = tp[min(base_index, a.to_play_stride - 1)] == tp[min(i, a.to_play_stride - 1)]; // to_play_list[base_index] == to_play_list[i] (:496)
         }
         v = same ? __dadd_rn(v, term) : __dadd_rn(v, -term);
     }
     const bool in_segment = current_index < a.segment_len[b]; // :505-510
     a.target_values[t] = in_segment ? v : 0.0;
+    if (a.horizon > 0) { // value_prefix += reward_list[current_index] for the steps inside the segment (:303-311)
+        double prefix = 0.0;
+        for (int w = prefix_from; w <= u; ++w)
+            if (state_index + w < a.segment_len[b]) prefix = __dadd_rn(prefix, (double)rew[min(state_index + w, a.reward_stride - 1)]);
+        a.target_rewards[t] = prefix;
+        return;
+    }
     a.target_rewards[t] = in_segment ? (double)rew[min(current_index, a.reward_stride - 1)] : 0.0;
 }
 

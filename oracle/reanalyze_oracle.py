@@ -81,3 +81,55 @@ def value_targets(roots_values, td_steps_list, value_mask, rewards_list, game_se
         batch_rewards.append(target_rewards)
         batch_target_values.append(target_values)
     return batch_rewards, batch_target_values
+
+
+def value_prefix_targets(roots_values, td_steps_list, value_mask, rewards_list, game_segment_lens, pos_in_game_segment_list,
+                         to_play_segment, num_unroll_steps, discount_factor, lstm_horizon_len, board_games=False):
+    """EfficientZero: game_buffer_efficientzero.py:261-316 (_compute_target_reward_value after the search).  The reward
+    target is the VALUE PREFIX: the running sum of rewards since the last horizon reset, where the reset counter
+    ``horizon_id`` runs over the whole transition batch (it is not restarted per game segment, :278) and a reset also moves
+    ``base_index`` of the board-games sign rule.  Returns (batch_value_prefixs [B][U+1], batch_target_values [B][U+1])."""
+    transition_batch_size = len(roots_values)
+    value_list = np.array([float(v) for v in roots_values])
+    if board_games:  # :262-270
+        value_list = value_list.reshape(-1) * np.array([
+            discount_factor ** td_steps_list[i] if int(td_steps_list[i]) % 2 == 0 else -discount_factor ** td_steps_list[i]
+            for i in range(transition_batch_size)])
+    else:  # :271-274
+        value_list = value_list.reshape(-1) * (
+            np.array([discount_factor for _ in range(transition_batch_size)]) ** np.asarray(td_steps_list))
+    value_list = value_list * np.array(value_mask)  # :276
+    value_list = value_list.tolist()
+    horizon_id, value_index = 0, 0  # :278
+    batch_value_prefixs, batch_target_values = [], []
+    for game_segment_len_non_re, reward_list, state_index, to_play_list in zip(game_segment_lens, rewards_list,
+                                                                               pos_in_game_segment_list, to_play_segment):
+        target_values, target_value_prefixs = [], []
+        value_prefix = 0.0
+        base_index = state_index
+        reward_list = [float(r) for r in reward_list]
+        for current_index in range(state_index, state_index + num_unroll_steps + 1):
+            bootstrap_index = current_index + td_steps_list[value_index]
+            for i, reward in enumerate(reward_list[current_index:bootstrap_index]):  # :287
+                if board_games:
+                    if to_play_list[base_index] == to_play_list[i]:  # :290
+                        value_list[value_index] += reward * discount_factor ** i
+                    else:
+                        value_list[value_index] += -reward * discount_factor ** i
+                else:
+                    value_list[value_index] += reward * discount_factor ** i  # :295
+            if horizon_id % lstm_horizon_len == 0:  # :298-300 reset every lstm_horizon_len
+                value_prefix = 0.0
+                base_index = current_index
+            horizon_id += 1
+            if current_index < game_segment_len_non_re:  # :303-311
+                target_values.append(value_list[value_index])
+                value_prefix += reward_list[current_index]
+                target_value_prefixs.append(value_prefix)
+            else:
+                target_values.append(0)
+                target_value_prefixs.append(value_prefix)
+            value_index += 1
+        batch_value_prefixs.append(target_value_prefixs)
+        batch_target_values.append(target_values)
+    return batch_value_prefixs, batch_target_values

@@ -1,6 +1,6 @@
 """Generates tests/golden/reanalyze_targets.npz by EXECUTING the reference's own source lines - not a restatement -
-on seeded inputs: /root/reference/lzero/mcts/buffer/game_buffer_muzero.py:464-512 (value / reward targets) and :606-656
-(policy targets), the code after the search call in _compute_target_reward_value / _compute_target_policy_reanalyzed.
+on seeded inputs: /root/reference/lzero/mcts/buffer/game_buffer_muzero.py:464-512 (value / reward targets), :606-656
+(policy targets) and game_buffer_efficientzero.py:261-316 (value-prefix targets -> tests/golden/reanalyze_prefix_targets.npz), the code after the search call in _compute_target_reward_value / _compute_target_policy_reanalyzed.
 The module itself cannot be imported here (it needs DI-engine); the two line ranges only use numpy, `self._cfg`, and the
 search results, which this script supplies (a stand-in `roots` whose getters return the given lists).
 Run in the authoring container only:   python tests/golden/make_reanalyze_golden.py
@@ -50,6 +50,35 @@ def value_case(rng, board_games, B=48, U=5):
                 out_rewards=np.asarray(ns["batch_rewards"], np.float64))
 
 
+SRC_EZ = os.path.join(os.path.dirname(SRC), "game_buffer_efficientzero.py")
+
+
+def value_prefix_case(rng, board_games, B=40, U=5, H=5):
+    """EfficientZero: game_buffer_efficientzero.py:261-316 executed as it stands (value-prefix targets, horizon resets)."""
+    gamma = 1.0 if board_games else 0.997
+    T = B * (U + 1)
+    seg_len = rng.integers(3, 40, B)
+    reward_len = seg_len + rng.integers(0, 12, B)
+    pos = np.asarray([rng.integers(0, max(l - 2, 1)) for l in seg_len])  # reward_list[current_index] is read while inside the segment
+    rewards = [rng.standard_normal(l).astype(np.float32) for l in reward_len]
+    to_play = [[1 + (k % 2) for k in range(l + 8)] for l in reward_len]
+    td = rng.integers(0, 6, T).astype(np.int64)
+    vmask = (rng.random(T) < 0.85).astype(np.float32)
+    values = rng.standard_normal(T).astype(np.float32)
+    ns = dict(np=np, self=types.SimpleNamespace(_cfg=cfg(env_type="board_games" if board_games else "not_board_games",
+                                                         discount_factor=gamma, num_unroll_steps=U, lstm_horizon_len=H)),
+              value_list=np.array([float(v) for v in values]), td_steps_list=td.tolist(), transition_batch_size=T,
+              value_mask=vmask.tolist(), to_play_segment=to_play if board_games else [[-1] * len(x) for x in to_play],
+              game_segment_lens=seg_len.tolist(), rewards_list=[[float(r) for r in x] for x in rewards],
+              pos_in_game_segment_list=pos.tolist(), batch_target_values=[], batch_value_prefixs=[])
+    lines = open(SRC_EZ).read().split("\n")[261 - 1:316]
+    exec(textwrap.dedent("\n".join(lines)), ns)
+    return dict(values=values, td=td.astype(np.int32), vmask=vmask, seg_len=seg_len.astype(np.int32), reward_len=reward_len.astype(np.int32),
+                pos=pos.astype(np.int32), rewards=np.concatenate(rewards), to_play=np.concatenate([np.asarray(x, np.int32) for x in to_play]),
+                U=np.int32(U), H=np.int32(H), gamma=np.float64(gamma), out_values=np.asarray(ns["batch_target_values"], np.float64),
+                out_prefixes=np.asarray(ns["batch_value_prefixs"], np.float64))
+
+
 def policy_case(rng, fixed, B=32, U=5, S=50):
     A = 6 if fixed else 9
     T = B * (U + 1)
@@ -80,6 +109,15 @@ def main():
         for k, v in case.items():
             data[name + "/" + k] = v
     np.savez_compressed(os.path.join(HERE, "reanalyze_targets.npz"), **data)
+    print("wrote", sorted(data))
+    # EfficientZero's value-prefix targets: their own file and generator, so that the MuZero fixtures above stay byte-identical
+    rng = np.random.default_rng(20261106)
+    data = {}
+    for name, case in (("prefix_single_player", value_prefix_case(rng, False)), ("prefix_board_games", value_prefix_case(rng, True)),
+                       ("prefix_horizon3", value_prefix_case(rng, False, U=7, H=3))):
+        for k, v in case.items():
+            data[name + "/" + k] = v
+    np.savez_compressed(os.path.join(HERE, "reanalyze_prefix_targets.npz"), **data)
     print("wrote", sorted(data))
 
 

@@ -198,3 +198,75 @@ def test_target_policies_kernel_matches_the_reference_golden(name):
     pol = target_policies(torch.as_tensor(visits).to(dev), cnt, None if name == "policy_fixed" else ids,
                           torch.as_tensor(g("pmask")).to(dev))
     assert_same(pol.cpu().numpy().reshape(g("out").shape), g("out").astype(np.float32), name)
+
+
+@pytest.mark.parametrize("name", ["prefix_single_player", "prefix_board_games", "prefix_horizon3"])
+def test_value_prefix_targets_kernel_matches_the_reference_golden(name):
+    """EfficientZero's flavour of lzb_value_targets (lstm_horizon_len > 0) against tests/golden/reanalyze_prefix_targets.npz:
+    the outputs of game_buffer_efficientzero.py:261-316 executed as it stands (value prefixes with the batch-wide horizon
+    counter, the base index of the board-games rule moving with the resets), float64 bit for bit."""
+    import torch
+    from lightzero_b200 import callers
+    from tests.test_reanalyze_oracle import GOLD_EZ, split
+    g = lambda k: GOLD_EZ[name + "/" + k]
+    rewards = split(g("rewards"), g("reward_len"))
+    to_play = split(g("to_play"), g("reward_len") + 8)
+    B = len(rewards)
+    rew_pad = np.zeros((B, max(len(r) for r in rewards)), np.float32)
+    tp_pad = np.zeros((B, max(len(x) for x in to_play)), np.int32)
+    for b in range(B):
+        rew_pad[b, :len(rewards[b])] = rewards[b]
+        tp_pad[b, :len(to_play[b])] = to_play[b]
+    board = name.endswith("board_games")
+    dev = torch.device("cuda", 0)
+    t = lambda a: torch.as_tensor(a).to(dev)
+    tp, tv = callers.reanalyze_value_targets(t(g("values")), g("td"), t(g("vmask")), t(rew_pad), g("reward_len"), g("seg_len"),
+                                             g("pos"), int(g("U")), float(g("gamma")), to_play_segments=tp_pad if board else None,
+                                             board_games=board, lstm_horizon_len=int(g("H")))
+    assert np.array_equal(tv.cpu().numpy().view(np.uint64), g("out_values").view(np.uint64)), "value targets"
+    assert np.array_equal(tp.cpu().numpy().view(np.uint64), g("out_prefixes").view(np.uint64)), "value-prefix targets"
+
+
+def test_reanalyze_policy_targets_for_the_sampled_tree():
+    """game_buffer_sampled_efficientzero.py:437-585: the Sampled buffer's reanalyze - roots(n, legal, A, K, continuous),
+    5-argument search, targets over the K sampled actions, root_sampled_actions returned with them."""
+    import torch
+    import lightzero_b200 as lzb
+    from lightzero_b200 import callers
+    B, U, K, D, S, H = 8, 5, 6, 2, 20, 4
+    T = B * (U + 1)
+    dev = torch.device("cuda", 0)
+
+    class Out:
+        pass
+
+    class Model:
+        def eval(self):
+            pass
+
+        def recurrent_inference(self, latent, hidden, actions):
+            o = Out()
+            o.latent_state = latent * 0.5 + actions.sum(1, keepdim=True)
+            o.policy_logits = torch.cat([torch.tanh(latent[:, :D]), torch.full((T, D), 0.5, device=dev)], 1)
+            o.value = latent[:, :1] * 0.1
+            o.value_prefix = latent[:, 1:2] * 0.05
+            o.reward_hidden_state = (hidden[0] * 0.9, hidden[1] * 0.9)
+            return o
+
+    cfg = dict(num_simulations=S, discount_factor=0.997, value_delta_max=0.01, device="cuda", lstm_horizon_len=5, tie_break_seed=SEED,
+               reanalyze_noise=False, model=dict(support_scale=300, categorical_distribution=False, continuous_action_space=True,
+                                                 num_of_sampled_actions=K, action_space_size=D))
+    mcts = identity(lzb.SampledEfficientZeroMCTSCtree(cfg))
+    g = torch.Generator(device=dev).manual_seed(9)
+    logits = torch.cat([torch.randn(T, D, generator=g, device=dev) * 0.3, torch.full((T, D), 0.4, device=dev)], 1)
+    pmask = (torch.rand(T, generator=g, device=dev) < 0.8).to(torch.int32)
+    hidden = (torch.zeros(1, T, H, device=dev), torch.zeros(1, T, H, device=dev))
+    out = callers.reanalyze_policy_targets(mcts, Model(), torch.randn(T, 3, generator=g, device=dev), torch.zeros(T, device=dev), logits,
+                                           None, torch.full((T,), -1, dtype=torch.int32, device=dev), pmask, U,
+                                           hidden_state_roots=hidden, roots_args=(D, K, True))
+    pol, acts = out["target_policies"], out["root_sampled_actions"]
+    assert tuple(pol.shape) == (B, U + 1, K) and tuple(acts.shape) == (T, K, D) and float(acts.abs().max()) <= 1.0
+    visits = out["visit_counts"].cpu().numpy()
+    assert (visits.sum(1) == S).all()
+    want = np.where(pmask.cpu().numpy()[:, None] != 0, (visits.astype(np.float64) / S).astype(np.float32), np.float32(0))
+    assert np.array_equal(pol.reshape(T, K).cpu().numpy().view(np.uint32), want.view(np.uint32))

@@ -46,3 +46,20 @@ def test_policy_targets_match_the_reference_lines(name):
     got, _ = ro.policy_targets(dists, legal, g("pmask").tolist(), len(legal) // (U + 1), U, mask.shape[1],
                                fixed_action_space=name == "policy_fixed")
     assert np.array_equal(np.asarray(got, np.float64).view(np.uint64), g("out").view(np.uint64))
+
+
+GOLD_EZ = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reanalyze_prefix_targets.npz"))
+
+
+@pytest.mark.parametrize("name", ["prefix_single_player", "prefix_board_games", "prefix_horizon3"])
+def test_value_prefix_targets_match_the_reference_lines(name):
+    """EfficientZero (game_buffer_efficientzero.py:261-316 executed by the golden maker): value-prefix targets with the
+    batch-wide horizon counter."""
+    g = lambda k: GOLD_EZ[name + "/" + k]
+    rewards = split(g("rewards"), g("reward_len"))
+    to_play = split(g("to_play"), g("reward_len") + 8)
+    p, v = ro.value_prefix_targets(g("values").tolist(), g("td").tolist(), g("vmask").tolist(), rewards, g("seg_len").tolist(),
+                                   g("pos").tolist(), [x.tolist() for x in to_play], int(g("U")), float(g("gamma")), int(g("H")),
+                                   board_games=name.endswith("board_games"))
+    assert np.array_equal(np.asarray(v, np.float64).view(np.uint64), g("out_values").view(np.uint64))
+    assert np.array_equal(np.asarray(p, np.float64).view(np.uint64), g("out_prefixes").view(np.uint64))
