@@ -58,7 +58,7 @@ constexpr size_t kAlign = 256;
 inline size_t align_up(size_t x) { return (x + kAlign - 1) / kAlign * kAlign; }
 
 struct Layout {
-    size_t node, root, legal, minmax, path_a, path_b, res, best, bidx, actions, gumbel, vtable, scratch, slots, pbc, pbc2, cval, total;
+    size_t node, root, legal, minmax, path_a, path_b, res, best, bidx, actions, gumbel, vtable, scratch, slots, pbc, pbc2, cval, gstat, total;
 };
 
 constexpr size_t kPbc2MaxW = 1024;
@@ -90,6 +90,10 @@ Layout make_layout(int variant, int N, int A, int S, int D)
 #endif
 #ifdef LZB_X_CVAL // experiment: child values cached by the backup
     l.cval = take(variant != LZB_GMZ ? (size_t)N * E * (A + 1) * sizeof(float) : 0);
+#endif
+    l.gstat = 0;
+#ifndef LZB_X_NO_GMZ_STATS // per-node constants of the Gumbel tree's softmax over priors, computed once (round 2: 24.1 -> 23.0 us per step)
+    l.gstat = take(variant == LZB_GMZ ? (size_t)N * E * sizeof(float2) : 0);
 #endif
     l.total = o;
     return l;
@@ -405,7 +409,10 @@ int lzb_forest_create(lzb_forest_t **out, void *workspace_dev, size_t workspace_
     p.path_a = (int4 *)(w + l.path_a); p.path_b = (int2 *)(w + l.path_b); p.res = (int4 *)(w + l.res);
     p.best = (int *)(w + l.best); p.bidx = (int *)(w + l.bidx); p.actions = (float *)(w + l.actions); p.gumbel = (float *)(w + l.gumbel);
     p.vtable = (int *)(w + l.vtable); p.scratch = (int *)(w + l.scratch);
-    p.pbc2 = nullptr; p.pbc2_w = 0; p.cval = nullptr;
+    p.pbc2 = nullptr; p.pbc2_w = 0; p.cval = nullptr; p.gstat = nullptr;
+#ifndef LZB_X_NO_GMZ_STATS
+    if (variant == LZB_GMZ) p.gstat = (float2 *)(w + l.gstat);
+#endif
 #ifdef LZB_X_PBC2
     if (variant != LZB_GMZ && (size_t)p.E + 1 <= kPbc2MaxW) { p.pbc2 = (float *)(w + l.pbc2); p.pbc2_w = p.E + 1; }
 #endif
@@ -464,6 +471,7 @@ int lzb_prepare(lzb_forest_t *f, const float *logits_dev, const float *noise_dev
     if (p.variant == LZB_SEZ ? !sampled_actions_dev : !logits_dev) return fail(LZB_E_ARG, "logits (or sampled_actions for the sampled tree) is NULL");
     if (p.variant == LZB_GMZ && !value_dev) return fail(LZB_E_ARG, "the Gumbel tree needs root values");
     PrepArgs a{logits_dev, noise_dev, reward_dev, value_dev, sampled_actions_dev, to_play_dev, noise_weight};
+    if (p.gstat) LZB_CUDA(cudaMemsetAsync(p.gstat, 0xff, (size_t)p.N * p.E * sizeof(float2), (cudaStream_t)stream)); // NaN: nothing cached for the new roots' trees
     dim3 grid, block; size_t smem;
     if (int rc = launch_cfg(k_prepare, (size_t)p.A * sizeof(float), p.N, grid, block, smem)) return rc;
     k_prepare<<<grid, block, smem, (cudaStream_t)stream>>>(p, a);

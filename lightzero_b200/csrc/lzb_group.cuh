@@ -662,7 +662,8 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
 // `need[r]`: this lane's slot r of the result is used afterwards; a slice nobody in the warp needs is left as it is
 // (its final expf is skipped), and with no slice needed at all nothing is computed.
 template <int G, int R>
-__device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, int A, const Grp<G> &grp, const bool (&need)[R])
+__device__ __forceinline__ bool csoftmax_g(float (&x)[R], int n, int A, const Grp<G> &grp, const bool (&need)[R], float *m_out = nullptr,
+                                           float *ls_out = nullptr)
 {
     const int lane = grp.lane;
     bool any_need[R], some = false; // warp-uniform
@@ -671,7 +672,7 @@ __device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, int A, const Gr
         any_need[r] = __any_sync(kFull, need[r]);
         some = some || any_need[r];
     }
-    if (!some) return;
+    if (!some) return false;
     float m = -INFINITY;
 #pragma unroll
     for (int r = 0; r < R; ++r)
@@ -685,9 +686,11 @@ __device__ __forceinline__ void csoftmax_g(float (&x)[R], int n, int A, const Gr
         sum = (r == R - 1 && R > 1) ? grp.ordered_add(sum, ex, A - G * (R - 1)) : grp.ordered_add(sum, ex, G);
     }
     const float ls = glibc_logf(sum);
+    if (m_out) { *m_out = m; *ls_out = ls; }
 #pragma unroll
     for (int r = 0; r < R; ++r)
         if (any_need[r]) x[r] = glibc_expf(x[r] - m - ls);
+    return true;
 }
 
 template <int G, int R>
@@ -751,7 +754,34 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
         bool sp_need[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) sp_need[r] = going && vc[r] > 0;
+#ifndef LZB_X_NO_GMZ_STATS
+        // a node's priors never change after its expansion, so the maximum and the log-sum-exp of this softmax are
+        // per-node constants: computed the first time they are needed, kept in gstat, and every later visit evaluates only
+        // expf(prior - max - lse) for the visited children (no reduction, no ordered sum, no logf)
+        {
+            float2 st = make_float2(0.0f, 0.0f);
+            bool have = true;
+            if (p.gstat) {
+                st = p.gstat[(size_t)i * p.E + e];
+                have = !(st.x != st.x);
+            }
+            bool want = false;
+#pragma unroll
+            for (int r = 0; r < R; ++r) want = want || sp_need[r];
+            want = grp.ballot(want) != 0u; // the group needs the softmax at all
+            if (p.gstat && !__any_sync(kFull, want && !have)) { // warp-uniform: every group that needs it has it
+#pragma unroll
+                for (int r = 0; r < R; ++r)
+                    if (__any_sync(kFull, sp_need[r])) sp[r] = glibc_expf(sp[r] - st.x - st.y);
+            } else {
+                float m_out, ls_out;
+                const bool done = csoftmax_g<G, R>(sp, n, A, grp, sp_need, &m_out, &ls_out);
+                if (p.gstat && done && want && !have && lane == 0) p.gstat[(size_t)i * p.E + e] = make_float2(m_out, ls_out);
+            }
+        }
+#else
         csoftmax_g<G, R>(sp, n, A, grp, sp_need);
+#endif
 
         // ---- compute_mixed_value (:935-970): serial sums over visited children in index order
         float probs_sum = 0.0f;

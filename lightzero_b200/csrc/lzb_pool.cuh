@@ -50,6 +50,7 @@ struct Pool {
     float *pbc2;    // experiment LZB_X_PBC2: [E+1][pbc2_w] pb_c of cucb_score per (parent visits - 1, child visits), or NULL
     int pbc2_w;
     float *cval;    // experiment LZB_X_CVAL: [N][E][B] CNode::value() of every child record as the backup last computed it, or NULL
+    float2 *gstat;  // [N][E] {max, log-sum-exp} of csoftmax over a node's priors (Gumbel), NaN = not computed yet; or NULL
     const char **slots; // [kMaxGathers][E] base pointer of the [N, row] tensor that holds the rows gathered for
                         //          leaves whose parent was expanded as e (latent, LSTM c, LSTM h)
 
