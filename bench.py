@@ -10,7 +10,10 @@ counts + values.  `value` = roots * sims / step time with every input resident i
 as one CUDA graph); `e2e` = the same search through the reference-shaped public API
 (lightzero_b200.MuZeroMCTSCtree.search) with HOST inputs in pinned memory and the results read back to the host
 inside the timed region.  Multi-GPU: roots shard by env batch, one forest per rank, no collective inside the
-search loop, one NCCL all-gather of visit counts / values at the end of each search.
+search loop, one exchange of visit counts / values at the end of each search: the NVLink peer-memory
+kernel of csrc/lzb_peer.cuh (--nccl-exchange: one packed NCCL all-gather instead); every rank's gathered rows are checked
+against an NCCL all-gather of the shards (`exchange_check`).  `--scaling strong` splits --roots-total over the ranks.
+Every N=1 line also carries `parity`: the CUDA search against the compiled reference at the bench shape, bit for bit.
 """
 import argparse
 import json

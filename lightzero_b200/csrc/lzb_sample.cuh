@@ -53,8 +53,34 @@ __global__ void k_sample_actions(SampleArgs a)
     const uint32_t groot = (uint32_t)(a.root_offset + i);
     if (a.continuous) {
         const float *mu = a.logits + (size_t)i * 2 * a.D, *sg = mu + a.D;
-        // one Philox block (four words) serves the two samples 2q and 2q + 1; `uniforms` keeps one (u1, u2) pair per sample
         const int KD = a.K * a.D;
+#ifndef LZB_X_SAMPLER_ONE_PER_PAIR
+        // Philox path: one block (four words) serves FOUR samples - each (u1, u2) pair gives both Box-Muller variates
+        // (radius * cos and radius * sin), halving the Philox / log / sqrt work per sample (round 2: the sampler kernel was
+        // 26 % of a Sampled search).  Injected uniforms (tests) keep one pair per sample and the cosine variate, below.
+        if (!a.uniforms) {
+            for (int q = lane; 4 * q < KD; q += 32) {
+                const uint4 r = rng(a.counter, groot, (uint32_t)q, 0x5a3c0001u);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const float u1 = unit_open(h ? r.z : r.x), u2 = unit_open(h ? r.w : r.y);
+                    const float rad = sqrtf(-2.0f * logf(u1));
+                    float sn, cs;
+                    sincospif(2.0f * u2, &sn, &cs);
+#pragma unroll
+                    for (int w = 0; w < 2; ++w) {
+                        const int t = 4 * q + 2 * h + w;
+                        if (t < KD) {
+                            const int d = t - (t / a.D) * a.D;
+                            a.out[(size_t)i * KD + t] = tanhf(mu[d] + sg[d] * (rad * (w ? sn : cs)));
+                        }
+                    }
+                }
+            }
+            return;
+        }
+#endif
+        // one Philox block (four words) serves the two samples 2q and 2q + 1; `uniforms` keeps one (u1, u2) pair per sample
         for (int q = lane; 2 * q < KD; q += 32) {
             uint4 r = make_uint4(0, 0, 0, 0);
             if (!a.uniforms) r = rng(a.counter, groot, (uint32_t)q, 0x5a3c0001u);
