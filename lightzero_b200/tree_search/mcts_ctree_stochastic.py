@@ -115,11 +115,14 @@ class StochasticMuZeroMCTSCtree(_CtreeDriver):
         (reward, value, logits, latent) and the chance head's dict."""
         # a chance leaf was reached by a decision action (< A), a decision leaf by a chance outcome (< C): the action a
         # head gets for a row it is not meant for is clamped into its range (both clamps in one launch)
-        lim = self.__dict__.get("_act_limits")
-        if lim is None or lim[0] != (A, C, last_action.device):
-            lim = ((A, C, last_action.device), torch.tensor([[A - 1], [C - 1]], dtype=last_action.dtype, device=last_action.device))
-            self._act_limits = lim
-        acts = torch.minimum(last_action.unsqueeze(0), lim[1])
+        if A == C:  # every action / outcome index is in range for both heads: no clamp, one launch less per simulation
+            acts = (last_action, last_action)
+        else:
+            lim = self.__dict__.get("_act_limits")
+            if lim is None or lim[0] != (A, C, last_action.device):
+                lim = ((A, C, last_action.device), torch.tensor([[A - 1], [C - 1]], dtype=last_action.dtype, device=last_action.device))
+                self._act_limits = lim
+            acts = torch.minimum(last_action.unsqueeze(0), lim[1])
         net_c = model.recurrent_inference(leaf, acts[0], afterstate=False)
         net_d = model.recurrent_inference(leaf, acts[1], afterstate=True)
         inv = self.inverse_scalar_transform_handle
