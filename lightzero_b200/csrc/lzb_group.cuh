@@ -248,6 +248,30 @@ __device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a
             if (zero) {
                 for (int t = lane; t < n4; t += G) d4[t] = make_int4(0, 0, 0, 0);
             } else {
+#ifdef LZB_X_GATHER_PREFETCH
+                // experiment: what the first round of loads does not cover - the tail of this row, and (from row 0) the
+                // whole of the tree's other rows - is requested into L2 now (no registers), so that the later rounds of this
+                // gather meet L2 instead of DRAM: 12 + 4 vectors per lane are two round trips, EfficientZero's three rows four
+                {
+                    const int first = (n4 >= 12 * G) ? 12 * G : ((n4 >= 8 * G) ? 8 * G : ((n4 >= 4 * G) ? 4 * G : n4));
+                    for (long long off = (long long)first * 16 + (long long)lane * 128; off < rb; off += (long long)G * 128)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(s + off));
+                    if (k == 0)
+                        for (int kk = 1; kk < a.ng; ++kk) {
+                            const long long rb2 = a.g[kk].row_bytes;
+                            const int ks2 = (slot_row >= 0) ? slot_row : kk;
+                            const char *s2;
+                            if (a.g[kk].src) s2 = a.g[kk].src + ((long long)ix * p.N + i) * rb2;
+                            else {
+                                const char *slot2 = (ix == a.new_e) ? pick3(a.new_slot, ks2) : p.slots[(size_t)ks2 * p.E + ix];
+                                if (slot2 == nullptr) continue;
+                                s2 = slot2 + (long long)i * rb2;
+                            }
+                            for (long long off = (long long)lane * 128; off < rb2; off += (long long)G * 128)
+                                asm volatile("prefetch.global.L2 [%0];" ::"l"(s2 + off));
+                        }
+                }
+#endif
                 int t = lane;
                 for (; t + 11 * G < n4; t += 12 * G) { // 12 independent 16-byte loads in flight per lane
                     int4 v[12];
