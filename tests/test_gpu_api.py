@@ -159,6 +159,26 @@ def test_gumbel_driver_matches_oracle(graph):
         assert model.calls[0][1][0].shape == (sc.n, 1)  # Gumbel passes actions as [N, 1] (mcts_ctree.py:1090)
 
 
+def test_gumbel_roots_prepared_again_forget_the_cached_softmax_constants():
+    """The Gumbel kernels memoise, per node, the maximum and log-sum-exp of the softmax over its priors (Pool::gstat).
+    prepare() on a LIVE Roots object re-roots the same workspace with other priors: the cache must not survive it."""
+    import torch
+    import lightzero_b200 as lzb
+    legal = [[a for a, x in enumerate(r) if x == 1] for r in TICTACTOE_MASKS]
+    first = Scenario("gmz", 16, 9, 30, seed=91, legal=legal, discount=1.0, max_considered=3)
+    sc = Scenario("gmz", 16, 9, 30, seed=44, legal=legal, discount=1.0, max_considered=3)
+    orc, _ = oracle_run(sc)
+    mcts = identity(lzb.GumbelMuZeroMCTSCtree(driver_cfg(sc)))
+    roots = lzb.GumbelMuZeroMCTSCtree.roots(sc.n, sc.legal)
+    for s_ in (first, sc):  # same object, same forest: searched with `first`, then prepared again and searched with `sc`
+        roots.prepare(0.25, [n.tolist() for n in s_.noises], s_.root_reward.tolist(), s_.root_value.tolist(),
+                      s_.root_logits.tolist(), s_.to_play.tolist())
+        mcts.search(roots, ScenarioModel(s_, torch.device("cuda")), np.zeros((sc.n, 16), np.float32), s_.to_play.tolist())
+    check_roots(roots, orc, sc)
+    p_, v_ = orc.gumbel_outputs(sc.discount)
+    assert_same(np.asarray(roots.get_policies(sc.discount, sc.A), np.float32), p_, "improved policies")
+
+
 def test_list_api_module_level_calls_match_oracle():
     """The tree modules driven exactly like the reference loop drives the Cython ones (Python lists in and out)."""
     from lightzero_b200.ctree.ctree_muzero import mz_tree
