@@ -213,6 +213,10 @@ __device__ __forceinline__ void prefetch_rows_g(const Pool &p, const SelectArgs 
 #define LZB_GATHER_LD(ptr) (*(ptr))
 #elif defined(LZB_X_GATHER_LDNC)
 #define LZB_GATHER_LD(ptr) __ldg(ptr)
+#elif defined(LZB_X_GATHER_LDLU) // "last use"
+#define LZB_GATHER_LD(ptr) __ldlu(ptr)
+#elif defined(LZB_X_GATHER_LDCG) // L2 only
+#define LZB_GATHER_LD(ptr) __ldcg(ptr)
 #else
 #define LZB_GATHER_LD(ptr) __ldcs(ptr)
 #endif
