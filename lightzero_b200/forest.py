@@ -15,6 +15,30 @@ from ._lib import BackpropIO, Chance, ChanceHead, Gather, Reuse, SearchCfg, Slot
 
 _CHECKED_RUN = bool(os.environ.get("LZB_CHECKED"))  # with a -DLZB_CHECKED library: raise at the end of a search that broke a check
 
+_NVTX = bool(os.environ.get("LZB_NVTX"))  # NVTX ranges around every forest call (nsys / ncu --nvtx): lzb.prepare, lzb.step[e] ...
+
+
+def _ranged(name):
+    """With LZB_NVTX=1 the call runs inside an NVTX range `lzb.<name>` (plus the latent index for the per-simulation
+    calls), so a timeline shows tree work and model work apart; without it the method is returned untouched."""
+    def wrap(fn):
+        if not _NVTX:
+            return fn
+
+        def inner(self, *a, **kw):
+            tag = "lzb." + name
+            if name in ("step", "backprop") and len(a) > (1 if name == "step" else 0):
+                tag += "[%s]" % (a[1] if name == "step" else a[0])
+            torch.cuda.nvtx.range_push(tag)
+            try:
+                return fn(self, *a, **kw)
+            finally:
+                torch.cuda.nvtx.range_pop()
+        inner.__name__, inner.__doc__ = fn.__name__, fn.__doc__
+        return inner
+    return wrap
+
+
 VARIANT_ID = {"mz": 0, "ez": 1, "gmz": 2, "sez": 3, "smz": 4}
 RNG_BATCH, RNG_PER_ROOT = 1, 2
 
@@ -161,6 +185,7 @@ class Forest:
     def set_delta(self, value_delta_max):
         check(self.L.lzb_set_delta(self.h, float(value_delta_max), _stream(self.device)))
 
+    @_ranged("prepare")
     def prepare(self, logits, noise, noise_weight, reward, to_play, value=None, sampled_actions=None):
         d = self.device
         logits = _dev(logits, torch.float32, d)
@@ -327,6 +352,7 @@ class Forest:
             hkeep = (ch, hr, hv, hl, lat)
         return io, (reward, value, logits, to_play, is_reset, sampled_actions, rkeep, hkeep)
 
+    @_ranged("traverse")
     def traverse(self, cfg, to_play, out=None, gathers=(), reuse=None, forced_outcome=None):
         """One batch_traverse. ``out``: optional dict of preallocated tensors (ix, iy, last_action, last_action_f,
         search_len, vtp); missing ones are allocated. ``gathers``: [(pool[E,N,...] | None, dst[N,...][, zero_if_reset])];
@@ -337,6 +363,7 @@ class Forest:
         check(self.L.lzb_traverse(self.h, C.byref(cfg), C.byref(io), _stream(self.device)))
         return o
 
+    @_ranged("backprop")
     def backprop(self, latent_index, discount, reward, value, logits, to_play, is_reset=None, lstm_horizon_len=0,
                  is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None, active=None, chance_head=None):
         """One batch_backpropagate; ``reuse``: dict(reuse_value, true_action | flags[, batch_index]) =
@@ -351,6 +378,7 @@ class Forest:
             io.active_dev = active.data_ptr()
         check(self.L.lzb_backprop(self.h, C.byref(io), _stream(self.device)))
 
+    @_ranged("step")
     def step(self, cfg, latent_index, discount, reward, value, logits, vtp, to_play, out=None, gathers=(), is_reset=None,
              lstm_horizon_len=0, is_reset_out=None, sampled_actions=None, new_slots=None, reuse=None,
              forced_outcome=None, chance_head=None):
@@ -366,6 +394,7 @@ class Forest:
     def store_hidden(self, src, dst, is_reset):
         check(self.L.lzb_store_hidden(_p(src), _p(dst), _p(is_reset), self.N, src.numel() // self.N, _stream(self.device)))
 
+    @_ranged("root_outputs")
     def root_outputs(self, discount=0.0, gumbel=False):
         d = self.device
         visits = torch.empty((self.N, self.A), dtype=torch.int32, device=d)

@@ -42,3 +42,38 @@ def test_checked_build_reports_an_unregistered_slot():
     word, _ = f2.check_word()
     assert word == 11, word
     assert float(dst2.abs().sum()) == 0.0  # reported, not read
+
+
+def test_nvtx_ranges_do_not_change_a_search():
+    """LZB_NVTX=1 wraps every forest call in an NVTX range (lzb.prepare, lzb.traverse, lzb.step[e], lzb.backprop[e],
+    lzb.root_outputs) for nsys / ncu --nvtx timelines; a search under it gives the same visit counts."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys; sys.path.insert(0, %r)\n"
+        "import torch\n"
+        "from lightzero_b200 import forest as F\n"
+        "assert F._NVTX == bool(__import__('os').environ.get('LZB_NVTX'))\n"
+        "dev = torch.device('cuda', 0); N, A, S = 32, 5, 6\n"
+        "g = torch.Generator(device=dev).manual_seed(1)\n"
+        "f = F.Forest('mz', N, A, S, device=dev)\n"
+        "tp = torch.full((N,), -1, dtype=torch.int32, device=dev)\n"
+        "f.prepare(torch.randn(N, A, generator=g, device=dev), None, 0.0, torch.zeros(N, device=dev), tp)\n"
+        "cfg = f.make_cfg(rng_seed=3)\n"
+        "o = f.traverse(cfg, tp)\n"
+        "for e in range(1, S + 1):\n"
+        "    r, v, l = (torch.randn(N, generator=g, device=dev) * 0.1, torch.randn(N, generator=g, device=dev), torch.randn(N, A, generator=g, device=dev))\n"
+        "    if e < S: o = f.step(cfg, e, 0.997, r, v, l, o['vtp'], tp, out=o)\n"
+        "    else: f.backprop(e, 0.997, r, v, l, o['vtp'])\n"
+        "print(f.root_outputs()['visits'].cpu().numpy().tolist())\n" % root)
+    outs = []
+    for flag in ("", "1"):
+        env = dict(os.environ, LZB_NVTX=flag)
+        if not flag:
+            env.pop("LZB_NVTX")
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(r.stdout.strip().splitlines()[-1])
+    assert outs[0] == outs[1] and outs[0].startswith("[[")
