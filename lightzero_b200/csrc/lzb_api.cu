@@ -634,6 +634,9 @@ void launch_group(int which, const Pool &p, const BackupArgs *b, const SelectArg
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((p.N + per_block - 1) / per_block);
+#ifndef LZB_X_NO_SHARED_TABLES
+    cfg.dynamicSmemBytes = 64 * sizeof(unsigned long long); // the two libm tables (fill_shared_tables)
+#endif
     cfg.blockDim = dim3(128);
     cfg.stream = st;
     cfg.attrs = attr;

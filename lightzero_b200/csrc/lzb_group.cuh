@@ -709,15 +709,15 @@ __device__ __forceinline__ bool csoftmax_g(float (&x)[R], int n, int A, const Gr
     float sum = 0.0f;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        const float ex = (lane + G * r < n) ? glibc_expf(x[r] - m) : 0.0f;
+        const float ex = (lane + G * r < n) ? glibc_expf_s(x[r] - m) : 0.0f;
         // index order; +0.0f beyond n is exact; the last slice stops at the action space
         sum = (r == R - 1 && R > 1) ? grp.ordered_add(sum, ex, A - G * (R - 1)) : grp.ordered_add(sum, ex, G);
     }
-    const float ls = glibc_logf(sum);
+    const float ls = glibc_logf_s(sum);
     if (m_out) { *m_out = m; *ls_out = ls; }
 #pragma unroll
     for (int r = 0; r < R; ++r)
-        if (any_need[r]) x[r] = glibc_expf(x[r] - m - ls);
+        if (any_need[r]) x[r] = glibc_expf_s(x[r] - m - ls);
     return true;
 }
 
@@ -800,7 +800,7 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
             if (p.gstat && !__any_sync(kFull, want && !have)) { // warp-uniform: every group that needs it has it
 #pragma unroll
                 for (int r = 0; r < R; ++r)
-                    if (__any_sync(kFull, sp_need[r])) sp[r] = glibc_expf(sp[r] - st.x - st.y);
+                    if (__any_sync(kFull, sp_need[r])) sp[r] = glibc_expf_s(sp[r] - st.x - st.y);
             } else {
                 float m_out, ls_out;
                 const bool done = csoftmax_g<G, R>(sp, n, A, grp, sp_need, &m_out, &ls_out);
@@ -1034,7 +1034,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const int j = lane + G * r;
-            t[r] = (j < width) ? glibc_expf(lg[r] - mx) : 0.0f;
+            t[r] = (j < width) ? glibc_expf_s(lg[r] - mx) : 0.0f;
             if (r == R - 1) LZB_TLD(tl, 20, __float_as_int(t[r]));
             // strictly left to right in action order; +0.0f beyond the width; the last slice stops at the action space
             sum = (r == R - 1 && R > 1) ? grp.ordered_add(sum, t[r], A - G * (R - 1)) : grp.ordered_add(sum, t[r], G);
@@ -1176,6 +1176,7 @@ __device__ __forceinline__ void expand_backup_g(const Pool &p, const BackupArgs 
 template <int VAR, int G, int R, bool REUSE>
 __global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_select_g(Pool p, SelectArgs a)
 {
+    fill_shared_tables();
     const Grp<G> grp;
     bool has_tree;
     const int i = group_tree<G>(has_tree);
@@ -1188,6 +1189,7 @@ __global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_select_g(Pool p, Select
 template <int VAR, int G, int R, bool REUSE>
 __global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_expand_backup_g(Pool p, BackupArgs b)
 {
+    fill_shared_tables();
     const Grp<G> grp;
     bool has_tree;
     const int i = group_tree<G>(has_tree);
@@ -1203,6 +1205,7 @@ __global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_expand_backup_g(Pool p,
 template <int VAR, int G, int R, bool REUSE>
 __global__ void __launch_bounds__(128, LZB_MIN_BLOCKS) k_step_g(Pool p, BackupArgs b, SelectArgs a)
 {
+    fill_shared_tables();
     const Grp<G> grp;
     bool has_tree;
     const int i = group_tree<G>(has_tree);

@@ -51,8 +51,15 @@ LZB_TABLE double kLogTab[32] = {
     0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2,  0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2,
 };
 
+// Tables in shared memory (round 2; -DLZB_X_NO_SHARED_TABLES = before: mz 17.32 -> 17.23 us per step, ez 29.45 -> 29.03,
+// gmz 22.96 -> 22.40): the lane-group kernels copy the two libm tables (2 x 256 B) into dynamic shared memory
+// before they wait on the previous launch, and their expf / logf read them with LDS - the per-lane-indexed lookup is a
+// dependent load in the middle of every expf, and as a global load it depends on L1 residency next to the row traffic
+extern __shared__ unsigned long long lzb_tab_smem[]; // [0..32): kExpTab, [32..64): kLogTab bit patterns
+
 // expf as glibc 2.39 x86-64 (FMA ifunc variant) computes it.
-__device__ __forceinline__ float glibc_expf(float x)
+template <bool SH>
+__device__ __forceinline__ float glibc_expf_impl(float x)
 {
     const uint32_t ux = __float_as_uint(x);
     const uint32_t abstop = (ux >> 20) & 0x7ffu;
@@ -68,7 +75,8 @@ __device__ __forceinline__ float glibc_expf(float x)
     const uint64_t ki = (uint64_t)__double_as_longlong(kd);
     kd = __dsub_rn(kd, 0x1.8p+52);
     const double r = fma(0x1.71547652b82fep+5, xd, -kd);
-    const double s = __longlong_as_double((long long)(LZB_TABLE_AT(kExpTab, ki & 31u) + (ki << 47)));
+    const uint64_t tab = SH ? (uint64_t)lzb_tab_smem[ki & 31u] : LZB_TABLE_AT(kExpTab, ki & 31u);
+    const double s = __longlong_as_double((long long)(tab + (ki << 47)));
     const double z = fma(0x1.c6af84b912394p-20, r, 0x1.ebfce50fac4f3p-13);
     const double r2 = __dmul_rn(r, r);
     double y = fma(0x1.62e42ff0c52d6p-6, r, 1.0);
@@ -76,9 +84,19 @@ __device__ __forceinline__ float glibc_expf(float x)
     y = __dmul_rn(y, s);
     return __double2float_rn(y);
 }
+__device__ __forceinline__ float glibc_expf(float x) { return glibc_expf_impl<false>(x); }
+__device__ __forceinline__ float glibc_expf_s(float x) // lane-group kernels: table in shared memory when the experiment is on
+{
+#ifndef LZB_X_NO_SHARED_TABLES
+    return glibc_expf_impl<true>(x);
+#else
+    return glibc_expf_impl<false>(x);
+#endif
+}
 
 // logf as glibc 2.39 x86-64 (FMA ifunc variant) computes it.
-__device__ __forceinline__ float glibc_logf(float x)
+template <bool SH>
+__device__ __forceinline__ float glibc_logf_impl(float x)
 {
     uint32_t ix = __float_as_uint(x);
     if (ix == 0x3f800000u) return 0.0f;
@@ -93,7 +111,8 @@ __device__ __forceinline__ float glibc_logf(float x)
     const int i = (int)((tmp >> 19) & 15u);
     const int k = (int)tmp >> 23;
     const uint32_t iz = ix - (tmp & 0xff800000u);
-    const double invc = LZB_TABLE_AT(kLogTab, 2 * i), logc = LZB_TABLE_AT(kLogTab, 2 * i + 1);
+    const double invc = SH ? __longlong_as_double((long long)lzb_tab_smem[32 + 2 * i]) : LZB_TABLE_AT(kLogTab, 2 * i);
+    const double logc = SH ? __longlong_as_double((long long)lzb_tab_smem[32 + 2 * i + 1]) : LZB_TABLE_AT(kLogTab, 2 * i + 1);
     const double z = (double)__uint_as_float(iz);
     const double r = fma(z, invc, -1.0);
     const double y0 = fma((double)k, 0x1.62e42fefa39efp-1, logc);
@@ -103,6 +122,25 @@ __device__ __forceinline__ float glibc_logf(float x)
     y = fma(-0x1.00ea348b88334p-2, r2, y);
     y = fma(r2, y, hi);
     return __double2float_rn(y);
+}
+__device__ __forceinline__ float glibc_logf(float x) { return glibc_logf_impl<false>(x); }
+__device__ __forceinline__ float glibc_logf_s(float x)
+{
+#ifndef LZB_X_NO_SHARED_TABLES
+    return glibc_logf_impl<true>(x);
+#else
+    return glibc_logf_impl<false>(x);
+#endif
+}
+
+// the lane-group kernels call this first (before griddepcontrol.wait: the tables are constants)
+__device__ __forceinline__ void fill_shared_tables()
+{
+#ifndef LZB_X_NO_SHARED_TABLES
+    if (threadIdx.x < 32) lzb_tab_smem[threadIdx.x] = kExpTab[threadIdx.x];
+    else if (threadIdx.x < 64) lzb_tab_smem[threadIdx.x] = (unsigned long long)__double_as_longlong(kLogTab[threadIdx.x - 32]);
+    __syncthreads();
+#endif
 }
 
 // tanhf as glibc 2.39 computes it (sysdeps/ieee754/flt-32/s_tanhf.c over s_expm1f.c: the Sun fdlibm routines, plain
