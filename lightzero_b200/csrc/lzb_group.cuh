@@ -80,6 +80,26 @@ struct Grp {
         }
         return sum;
     }
+    // the same ordered sum when only the lanes in `u` (group-relative bits, the UNION over the warp's groups, warp-uniform)
+    // can hold a non-zero term: adding +0.0f for the others is exact, so they are skipped
+    __device__ __forceinline__ float ordered_add_sparse(float sum, float v, unsigned u) const
+    {
+#pragma unroll 1
+        while (u) {
+            const int l = __ffs(u) - 1;
+            u &= u - 1;
+            sum += shfl(v, l);
+        }
+        return sum;
+    }
+    __device__ __forceinline__ unsigned union_mask(bool pred) const // group-relative lanes where `pred` holds in ANY group of the warp
+    {
+        const unsigned w = __ballot_sync(kFull, pred);
+        unsigned u = 0;
+#pragma unroll
+        for (int s = 0; s + G <= 32; s += G) u |= w >> s;
+        return (G == 32) ? u : (u & ((1u << (G & 31)) - 1u));
+    }
     __device__ __forceinline__ float fmax(float v) const
     {
         if constexpr (kPow2) {
@@ -813,20 +833,38 @@ __device__ __forceinline__ void select_gumbel_g(const Pool &p, const SelectArgs 
 
         // ---- compute_mixed_value (:935-970): serial sums over visited children in index order
         float probs_sum = 0.0f;
+#ifdef LZB_X_GMZ_SPARSE
+        unsigned vmask[R];
+#endif
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const float pc = (sp[r] < -10e7f) ? -10e7f : sp[r]; // std::max(prior, min_num)
             const float t = (vc[r] > 0) ? pc : 0.0f;
+#ifdef LZB_X_GMZ_SPARSE
+            vmask[r] = grp.union_mask(vc[r] > 0); // below the root one to three children are visited: add only those lanes
+            if (vmask[r]) {
+                if (__popc(vmask[r]) <= 6) probs_sum = grp.ordered_add_sparse(probs_sum, t, vmask[r]);
+                else probs_sum = (r == R - 1 && R > 1) ? grp.ordered_add(probs_sum, t, A - G * (R - 1)) : grp.ordered_add(probs_sum, t, G);
+            }
+#else
             if (__any_sync(kFull, vc[r] > 0)) // warp-uniform: a slice without a visited child adds only +0.0f
                 probs_sum = (r == R - 1 && R > 1) ? grp.ordered_add(probs_sum, t, A - G * (R - 1)) : grp.ordered_add(probs_sum, t, G);
+#endif
         }
         float wq = 0.0f;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const float pc = (sp[r] < -10e7f) ? -10e7f : sp[r];
             const float t = (vc[r] > 0) ? pc * q[r] / probs_sum : 0.0f;
+#ifdef LZB_X_GMZ_SPARSE
+            if (vmask[r]) {
+                if (__popc(vmask[r]) <= 6) wq = grp.ordered_add_sparse(wq, t, vmask[r]);
+                else wq = (r == R - 1 && R > 1) ? grp.ordered_add(wq, t, A - G * (R - 1)) : grp.ordered_add(wq, t, G);
+            }
+#else
             if (__any_sync(kFull, vc[r] > 0))
                 wq = (r == R - 1 && R > 1) ? grp.ordered_add(wq, t, A - G * (R - 1)) : grp.ordered_add(wq, t, G);
+#endif
         }
         const float vsum_f = (float)vsum_i;
         const float mixed = (raw_value + vsum_f * wq) / (vsum_f + 1);
