@@ -317,8 +317,28 @@ PyObject *lzb_rows_from_i32(const int32_t *data, const int32_t *counts, long n, 
     return res;
 }
 
+/* int objects 0 .. 255, created once (CPython keeps these as shared small-int singletons; strong references are held here
+ * for interpreters where they are not immortal).  Visit counts are at most num_simulations, so almost every element of a
+ * distributions table is one of them: a table lookup + INCREF instead of a PyLong_FromLong call per element
+ * (1.5 -> 0.7 ms for 8192 x 18). */
+#define LZB_SMALL_INTS 256
+static PyObject *small_int[LZB_SMALL_INTS];
+static int small_int_ready = 0;
+
+static int small_ints_init(void)
+{
+    if (small_int_ready) return 0;
+    for (long v = 0; v < LZB_SMALL_INTS; ++v) {
+        small_int[v] = PyLong_FromLong(v);
+        if (!small_int[v]) return -1;
+    }
+    small_int_ready = 1;
+    return 0;
+}
+
 static PyObject *rows_from_i32(const int32_t *data, const int32_t *counts, long n, long stride)
 {
+    if (small_ints_init() != 0) return NULL;
     PyObject *outer = PyList_New(n);
     if (!outer) return NULL;
     for (long i = 0; i < n; ++i) {
@@ -330,11 +350,18 @@ static PyObject *rows_from_i32(const int32_t *data, const int32_t *counts, long 
         }
         const int32_t *src = data + (size_t)i * (size_t)stride;
         for (long j = 0; j < m; ++j) {
-            PyObject *v = PyLong_FromLong(src[j]);
-            if (!v) {
-                Py_DECREF(row);
-                Py_DECREF(outer);
-                return NULL;
+            const int32_t x = src[j];
+            PyObject *v;
+            if ((uint32_t)x < (uint32_t)LZB_SMALL_INTS) {
+                v = small_int[x];
+                Py_INCREF(v);
+            } else {
+                v = PyLong_FromLong(x);
+                if (!v) {
+                    Py_DECREF(row);
+                    Py_DECREF(outer);
+                    return NULL;
+                }
             }
             PyList_SET_ITEM(row, j, v);
         }
