@@ -251,3 +251,35 @@ def _list_marshalling_checks(P, _floats_from_lists, _ints_from_list, gc):
         finally:
             gc.enable()
         assert rows[5] == v[5, :cnt[5]].tolist()
+
+
+def test_every_experiment_flag_of_the_index_exists_in_the_sources():
+    """EXPERIMENTS.md lists each measured experiment with the build flag that re-creates it: every -DLZB_* flag named there
+    must still be tested for somewhere under csrc/ (scripts/check_flags.sh compiles them)."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "EXPERIMENTS.md")).read()
+    flags = set(re.findall(r"-D(LZB_[A-Z0-9_]+)", text))
+    assert len(flags) >= 25, sorted(flags)
+    src = ""
+    csrc = os.path.join(root, "lightzero_b200", "csrc")
+    for f in os.listdir(csrc):
+        src += open(os.path.join(csrc, f)).read()
+    missing = sorted(f for f in flags if f not in src and not any(f.startswith(x) and x in src for x in ("LZB_X_GATHER_", "LZB_X_ROW_PREFETCH")))
+    assert not missing, missing
+
+
+def test_strong_scaling_flag_splits_the_total_over_the_ranks(monkeypatch):
+    """bench.py --scaling strong: --roots-total roots divided over WORLD_SIZE ranks (strong-scaling row)."""
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import bench
+    monkeypatch.setenv("WORLD_SIZE", "8")
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--gpus", "8", "--scaling", "strong"])
+    a = bench.parse_args()
+    assert a.roots == 8192 and a.scaling == "strong" and bench.workload_config(a, 8)["roots_total"] == 65536
+    monkeypatch.setenv("WORLD_SIZE", "1")
+    monkeypatch.setattr(sys, "argv", ["bench.py"])
+    a = bench.parse_args()
+    assert a.roots == 8192 and a.scaling == "weak"
