@@ -17,7 +17,8 @@ TL_LIB = os.path.join(ROOT, "lightzero_b200", "liblzb200_tl.so")
 
 def build_tl():
     from lightzero_b200 import _lib
-    cmd = ["nvcc"] + _lib.NVCC_FLAGS + ["-DLZB_TIMELINE", os.path.join(_lib.CSRC, "lzb_api.cu"), "-o", TL_LIB]
+    extra = os.environ.get("LZB_TL_FLAGS", "").split()  # e.g. LZB_TL_FLAGS="-DLZB_X_CARRY": the timeline of an experiment build
+    cmd = ["nvcc"] + _lib.NVCC_FLAGS + ["-DLZB_TIMELINE"] + extra + [os.path.join(_lib.CSRC, "lzb_api.cu"), "-o", TL_LIB]
     subprocess.run(cmd, check=True)
 
 
@@ -110,6 +111,17 @@ def analyse(t, sims):
             for k, v in sorted(off.items(), key=lambda kv: kv[1]):
                 print("      %-28s %7.0f  (+%.0f)" % (label[k], v, v - prev))
                 prev = v
+    # the row gather as a function of WHEN a warp reaches it: how many warps start in each 2 k-cycle window after kernel entry
+    # and how long their gather takes - a gather that is bandwidth-bound in the crowded window shows as durations that follow
+    # the count, a latency-bound one as a flat line
+    sel = rows[(launch >= 20) & (launch < 30)]
+    if len(sel) and (sel[:, 12] > 0).all() and (sel[:, 13] > 0).all():
+        start, dur = sel[:, 12] - sel[:, 0], sel[:, 13] - sel[:, 12]
+        print("== row gather by start window (sims 20-29): window | warps (share) | mean gather cycles | p90")
+        for lo in range(0, 44000, 2000):
+            m = (start >= lo) & (start < lo + 2000)
+            if m.sum() >= 20:
+                print("   %5d-%5d | %6d (%4.1f%%) | %6.0f | %6.0f" % (lo, lo + 2000, m.sum(), 100.0 * m.mean(), dur[m].mean(), np.percentile(dur[m], 90)))
     # per launch: spread of starts / ends by globaltimer is not available per phase; use slot 1 (globaltimer at entry)
     for l in (3, 25, 45):
         sel = rows[launch == l]
