@@ -636,6 +636,11 @@ void launch_group(int which, const Pool &p, const BackupArgs *b, const SelectArg
     cfg.gridDim = dim3((p.N + per_block - 1) / per_block);
 #ifndef LZB_X_NO_SHARED_TABLES
     cfg.dynamicSmemBytes = 64 * sizeof(unsigned long long); // the two libm tables (fill_shared_tables)
+#ifndef LZB_X_NO_LONE_STAGE
+    // lone walker: one mbarrier and one staged row per warp (lzb_group.cuh, lone_stage_rows), only where the kernel can use them
+    if (which != kBackup && a && LoneWalker<VAR, G, R, REUSE>::value && VAR != LZB_SMZ && VAR != LZB_GMZ && lone_stage_rows(*a))
+        cfg.dynamicSmemBytes = kStageRowWord * 8 + 4 * (size_t)a->g[0].row_bytes;
+#endif
 #endif
     cfg.blockDim = dim3(128);
     cfg.stream = st;

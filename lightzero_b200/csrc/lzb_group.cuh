@@ -125,8 +125,29 @@ struct Grp {
         for (int s = 0; s + G <= 32; s += G) u |= w >> s;
         return (G == 32) ? u : (u & ((1u << (G & 31)) - 1u));
     }
+#ifndef LZB_X_NO_REDUX
+    // Group reductions by the warp-wide reduction unit (sm_100a: redux.sync.{max,min}.f32 -> CREDUX, integers REDUX) instead of
+    // log2(G) dependent shuffle + op steps (round 2; -DLZB_X_NO_REDUX = before: mz 16.66 -> 16.35 us per step, tree-only 13.20 ->
+    // 12.75, gmz 22.57 -> 22.09, ez 28.94 -> 28.77).  Two 16-lane groups = two independent full-mask reductions with
+    // the other group's lanes holding the operation's identity.  NaN handling as fmaxf / fminf (the number wins).
+    static __device__ __forceinline__ float rx_fmax(float v) { float r; asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v)); return r; }
+    static __device__ __forceinline__ float rx_fmin(float v) { float r; asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v)); return r; }
+    template <typename T, typename F>
+    __device__ __forceinline__ T rx_group(T v, T ident, F f) const
+    {
+        if constexpr (G == 32) return f(v);
+        else {
+            const bool hi = shift != 0;
+            const T lo_r = f(hi ? ident : v), hi_r = f(hi ? v : ident);
+            return hi ? hi_r : lo_r;
+        }
+    }
+#endif
     __device__ __forceinline__ float fmax(float v) const
     {
+#ifndef LZB_X_NO_REDUX
+        if constexpr (G == 32 || G == 16) return rx_group(v, -INFINITY, [](float x) { return rx_fmax(x); });
+#endif
         if constexpr (kPow2) {
 #pragma unroll
             for (int o = G / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(kFull, v, o, G));
@@ -138,6 +159,9 @@ struct Grp {
     }
     __device__ __forceinline__ float fmin(float v) const
     {
+#ifndef LZB_X_NO_REDUX
+        if constexpr (G == 32 || G == 16) return rx_group(v, INFINITY, [](float x) { return rx_fmin(x); });
+#endif
         if constexpr (kPow2) {
 #pragma unroll
             for (int o = G / 2; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(kFull, v, o, G));
@@ -149,6 +173,9 @@ struct Grp {
     }
     __device__ __forceinline__ int isum(int v) const
     {
+#ifndef LZB_X_NO_REDUX
+        if constexpr (G == 32 || G == 16) return rx_group(v, 0, [](int x) { return __reduce_add_sync(kFull, x); });
+#endif
         if constexpr (kPow2) {
 #pragma unroll
             for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(kFull, v, o, G);
@@ -168,6 +195,9 @@ struct Grp {
     }
     __device__ __forceinline__ int imax(int v) const
     {
+#ifndef LZB_X_NO_REDUX
+        if constexpr (G == 32 || G == 16) return rx_group(v, (int)0x80000000, [](int x) { return __reduce_max_sync(kFull, x); });
+#endif
         if constexpr (kPow2) {
 #pragma unroll
             for (int o = G / 2; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(kFull, v, o, G));
@@ -270,6 +300,44 @@ __device__ __forceinline__ void prefetch_rows_g(const Pool &p, const SelectArgs 
 #else
 #define LZB_GATHER_ST(ptr, val) (*(ptr) = (val))
 #endif
+
+// Lone walker, rows (round 2; -DLZB_X_NO_LONE_STAGE = before, -DLZB_X_LONE_STAGE_LSU = the cp.async form): when a warp's first tree
+// ends its walk, its row is requested from the bulk-copy engine into shared memory (one cp.async.bulk by one lane, completion on an
+// mbarrier: no registers, no load / store unit traffic) while the other tree walks on with all 32 lanes; afterwards the engine
+// writes it to the model batch and the walker's own row is gathered by all 32 lanes in ONE round trip (8 x 16 bytes per lane)
+// instead of the two (12 + 4 vectors per lane) of the 16-lane form.  One row of at most LZB_LONE_STAGE_BYTES per tree (the
+// MuZero case); anything else takes the ordinary path.  Measured: mz 16.66 -> 16.34 us per step; the same staging through
+// cp.async (LDGSTS, 16 requests per lane) was SLOWER, 18.1 us - it is the load / store path the early rows must stay out of.
+#if defined(LZB_X_NO_SHARED_TABLES) && !defined(LZB_X_NO_LONE_STAGE)
+#define LZB_X_NO_LONE_STAGE // the staging area sits behind the tables in dynamic shared memory
+#endif
+#ifndef LZB_LONE_STAGE_BYTES
+#define LZB_LONE_STAGE_BYTES 4096
+#endif
+// dynamic shared memory of the lane-group kernels, in 8-byte words: [0, 64) libm tables, [64, 68) one mbarrier per warp,
+// [68, ...) one staged row per warp
+constexpr int kStageBarWord = 64, kStageRowWord = 68;
+__host__ __device__ __forceinline__ bool lone_stage_rows(const SelectArgs &a)
+{
+    return a.ng == 1 && a.g[0].row_bytes <= LZB_LONE_STAGE_BYTES && (a.g[0].row_bytes & 15) == 0 && (((unsigned long long)a.g[0].dst) & 15ull) == 0;
+}
+template <int VAR, int G, int R, bool REUSE>
+struct LoneWalker {
+#if defined(LZB_X_LONE_WALKER_ALL)
+    static constexpr bool value = G == 16 && R == 2;
+#elif !defined(LZB_X_NO_LONE_WALKER)
+    static constexpr bool value = !REUSE && VAR != LZB_SMZ && G == 16 && R == 2;
+#else
+    static constexpr bool value = false;
+#endif
+};
+__device__ __forceinline__ const char *row_src_g(const Pool &p, const SelectArgs &a, int k, int i, int ix)
+{
+    const long long rb = a.g[k].row_bytes;
+    if (a.g[k].src) return a.g[k].src + ((long long)ix * p.N + i) * rb;
+    const char *slot = (ix == a.new_e) ? pick3(a.new_slot, k) : p.slots[(size_t)k * p.E + ix];
+    return slot ? slot + (long long)i * rb : nullptr;
+}
 
 template <int G>
 __device__ __forceinline__ void gather_rows_g(const Pool &p, const SelectArgs &a, int i, int ix, int parent_reset, int lane, int slot_row = -1)
@@ -711,13 +779,8 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     // (28.8 from 31.9 without the latent rows), ez 28.83 -> 28.94 (tree + LSTM rows 18.53 -> 17.91); the stochastic tree is
     // slower with it (18.48 -> 19.54: the chance draw's double-precision shuffles over 32 lanes, spills) and stays without,
     // -DLZB_X_LONE_WALKER_ALL switches it on for every flavour incl. reuse
-#if defined(LZB_X_LONE_WALKER_ALL)
-    constexpr bool kLone = G == 16 && R == 2;
-#elif !defined(LZB_X_NO_LONE_WALKER)
-    constexpr bool kLone = !REUSE && VAR != LZB_SMZ && G == 16 && R == 2;
-#else
-    constexpr bool kLone = false;
-#endif
+    constexpr bool kLone = LoneWalker<VAR, G, R, REUSE>::value;
+    bool rows_done = false; // lone-walker staging: the tree's row is already in the model batch
     while (__any_sync(kFull, going)) {
         if constexpr (kLone) {
             const unsigned gm = __ballot_sync(kFull, going);
@@ -727,6 +790,37 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
                 // the finished tree's results stay in its lanes: set aside what the code after the loop reads
                 const int s_e = e, s_depth = depth, s_pos = pos, s_reset = parent_reset, s_vtp = vtp, s_chance = parent_chance;
                 const bool s_noinf = no_inference;
+#ifndef LZB_X_NO_LONE_STAGE
+                bool s_staged = false;
+                if (VAR != LZB_SMZ && lone_stage_rows(a)) { // the same in every lane
+                    const long long rb0 = a.g[0].row_bytes;
+                    char *stage = reinterpret_cast<char *>(lzb_tab_smem + kStageRowWord) + (threadIdx.x >> 5) * rb0;
+                    if (!walker && live && !s_noinf && !(a.g[0].zero_if_reset && s_reset == 1)) {
+                        const char *ss = row_src_g(p, a, 0, i, s_e);
+                        if (ss != nullptr && (((unsigned long long)ss) & 15ull) == 0) {
+                            const unsigned sm = (unsigned)__cvta_generic_to_shared(stage);
+#ifndef LZB_X_LONE_STAGE_LSU // the same through the bulk-copy engine: one request by one lane, completion on an mbarrier
+                            if (lane == 0) {
+                                const unsigned mb = (unsigned)__cvta_generic_to_shared(lzb_tab_smem + kStageBarWord + (threadIdx.x >> 5));
+                                asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mb) : "memory");
+                                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"((unsigned)rb0) : "memory");
+                                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(sm), "l"(ss),
+                                             "r"((unsigned)rb0), "r"(mb)
+                                             : "memory");
+                            }
+#else
+                            for (int t = lane; t < (int)(rb0 >> 4); t += G)
+                                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sm + t * 16), "l"(ss + (long long)t * 16) : "memory");
+#endif
+                            s_staged = true;
+                        }
+                    }
+#ifdef LZB_X_LONE_STAGE_LSU
+                    asm volatile("cp.async.commit_group;" ::: "memory");
+#endif
+                }
+#endif
                 // the walker's state and per-tree constants, in all 32 lanes
                 ti = __shfl_sync(kFull, i, src);
                 e = __shfl_sync(kFull, e, src); depth = __shfl_sync(kFull, depth, src); pos = __shfl_sync(kFull, pos, src);
@@ -745,6 +839,51 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
                 is_root = false; going = true; no_inference = false;
                 const Grp<32> g32;
                 while (going) level_body(g32, std::integral_constant<int, 1>());
+#ifndef LZB_X_NO_LONE_STAGE
+                if (VAR != LZB_SMZ && lone_stage_rows(a)) { // every lane holds the walker's leaf here (nothing but s_staged kept across the walk)
+                    const long long rb0 = a.g[0].row_bytes;
+                    const char *stage = reinterpret_cast<const char *>(lzb_tab_smem + kStageRowWord) + (threadIdx.x >> 5) * rb0;
+                    const int l32 = threadIdx.x & 31, n4 = (int)(rb0 >> 4);
+                    const bool w_zero = a.g[0].zero_if_reset && parent_reset == 1;
+                    const char *ws = (no_inference || w_zero) ? nullptr : row_src_g(p, a, 0, ti, e);
+                    const bool w_fast = !no_inference && (w_zero || (ws != nullptr && (((unsigned long long)ws) & 15ull) == 0));
+                    int4 v[8];
+                    if (w_fast && !w_zero) {
+                        const int4 *s4 = reinterpret_cast<const int4 *>(ws);
+#pragma unroll
+                        for (int u = 0; u < 8; ++u)
+                            if (l32 + u * 32 < n4) v[u] = LZB_GATHER_LD(s4 + l32 + u * 32);
+                    }
+                    if (s_staged) { // the other tree's row: shared memory -> its row of the model batch
+#ifndef LZB_X_LONE_STAGE_LSU
+                        if (lane == 0) {
+                            const unsigned mb = (unsigned)__cvta_generic_to_shared(lzb_tab_smem + kStageBarWord + (threadIdx.x >> 5));
+                            const unsigned sm = (unsigned)__cvta_generic_to_shared(stage);
+                            unsigned ok = 0;
+                            while (!ok)
+                                asm volatile("{ .reg .pred q; mbarrier.try_wait.parity.shared::cta.b64 q, [%1], 0; selp.u32 %0, 1, 0, q; }" : "=r"(ok) : "r"(mb) : "memory");
+                            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.g[0].dst + (long long)i * rb0), "r"(sm),
+                                         "r"((unsigned)rb0)
+                                         : "memory");
+                            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); // the block may exit once the engine has read the row
+                        }
+#else
+                        asm volatile("cp.async.wait_all;" ::: "memory");
+                        const int4 *m4 = reinterpret_cast<const int4 *>(stage);
+                        int4 *d4 = reinterpret_cast<int4 *>(a.g[0].dst + (long long)i * rb0);
+                        for (int t = lane; t < n4; t += G) d4[t] = m4[t];
+#endif
+                    }
+                    if (w_fast) {
+                        int4 *d4 = reinterpret_cast<int4 *>(a.g[0].dst + (long long)ti * rb0);
+#pragma unroll
+                        for (int u = 0; u < 8; ++u)
+                            if (l32 + u * 32 < n4) LZB_GATHER_ST(d4 + l32 + u * 32, w_zero ? make_int4(0, 0, 0, 0) : v[u]);
+                    }
+                    rows_done = walker ? w_fast : s_staged;
+                }
+#endif
                 if (!walker) { e = s_e; depth = s_depth; pos = s_pos; parent_reset = s_reset; vtp = s_vtp; no_inference = s_noinf; parent_chance = s_chance; }
                 going = false;
                 break;
@@ -772,7 +911,7 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
                 for (int d = lane; d < p.D; d += G) a.last_action_f[(size_t)i * p.D + d] = act[d];
             if (a.last_action && lane == 0) a.last_action[i] = (long long)act[0]; // discrete sampled: float(index)
         }
-        gather_rows_g<G>(p, a, i, e, parent_reset, lane, (VAR == LZB_SMZ && a.slot_by_kind) ? (parent_chance ? 1 : 0) : -1);
+        if (!rows_done) gather_rows_g<G>(p, a, i, e, parent_reset, lane, (VAR == LZB_SMZ && a.slot_by_kind) ? (parent_chance ? 1 : 0) : -1);
     }
     LZB_TL(tl, 13);
     if (live && lane == 0) {
