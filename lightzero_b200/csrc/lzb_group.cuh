@@ -781,12 +781,14 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     // -DLZB_X_LONE_WALKER_ALL switches it on for every flavour incl. reuse
     constexpr bool kLone = LoneWalker<VAR, G, R, REUSE>::value;
     bool rows_done = false; // lone-walker staging: the tree's row is already in the model batch
+    bool lone_entered = false; // the warp's mbarrier has been used (LZB_X_PAIR_SPLIT)
     while (__any_sync(kFull, going)) {
         if constexpr (kLone) {
             const unsigned gm = __ballot_sync(kFull, going);
             if ((gm == 0x0000ffffu || gm == 0xffff0000u) && A <= 32 && level > 0) { // one of the warp's two trees is still walking
                 const int src = (gm & 1u) ? 0 : 16;
                 const bool walker = going;
+                lone_entered = true;
                 // the finished tree's results stay in its lanes: set aside what the code after the loop reads
                 const int s_e = e, s_depth = depth, s_pos = pos, s_reset = parent_reset, s_vtp = vtp, s_chance = parent_chance;
                 const bool s_noinf = no_inference;
@@ -904,6 +906,49 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
     }
     pdl_release(); // the walk is over: a dependent launch may begin to take the place of exiting blocks
     LZB_TL(tl, 12);
+#if defined(LZB_X_PAIR_SPLIT) && !defined(LZB_X_NO_LONE_STAGE)
+    // experiment LZB_X_PAIR_SPLIT: a warp whose two trees ended their walks together (no lone walker) moves the second tree's row
+    // through the bulk-copy engine (global -> shared -> global) while all 32 lanes gather the first tree's row in one round trip
+    if constexpr (kLone) {
+        const unsigned need = __ballot_sync(kFull, live && !no_inference && !rows_done);
+        if (need == 0xffffffffu && !lone_entered && VAR != LZB_SMZ && lone_stage_rows(a) && !a.g[0].zero_if_reset) {
+            const long long rb0 = a.g[0].row_bytes;
+            const int l32 = threadIdx.x & 31, n4 = (int)(rb0 >> 4);
+            const char *sb = row_src_g(p, a, 0, i, e);
+            if (__all_sync(kFull, sb != nullptr && (((unsigned long long)sb) & 15ull) == 0)) {
+                const unsigned sm = (unsigned)__cvta_generic_to_shared(reinterpret_cast<char *>(lzb_tab_smem + kStageRowWord) + (threadIdx.x >> 5) * rb0);
+                const unsigned mb = (unsigned)__cvta_generic_to_shared(lzb_tab_smem + kStageBarWord + (threadIdx.x >> 5));
+                if (l32 == 16) {
+                    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mb) : "memory");
+                    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"((unsigned)rb0) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(sm), "l"(sb),
+                                 "r"((unsigned)rb0), "r"(mb)
+                                 : "memory");
+                }
+                const int4 *s4 = reinterpret_cast<const int4 *>(__shfl_sync(kFull, (unsigned long long)sb, 0));
+                int4 *d4 = reinterpret_cast<int4 *>(a.g[0].dst + (long long)__shfl_sync(kFull, i, 0) * rb0);
+                int4 v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (l32 + u * 32 < n4) v[u] = LZB_GATHER_LD(s4 + l32 + u * 32);
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (l32 + u * 32 < n4) LZB_GATHER_ST(d4 + l32 + u * 32, v[u]);
+                if (l32 == 16) {
+                    unsigned ok = 0;
+                    while (!ok)
+                        asm volatile("{ .reg .pred q; mbarrier.try_wait.parity.shared::cta.b64 q, [%1], 0; selp.u32 %0, 1, 0, q; }" : "=r"(ok) : "r"(mb) : "memory");
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(a.g[0].dst + (long long)i * rb0), "r"(sm), "r"((unsigned)rb0)
+                                 : "memory");
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                }
+                rows_done = true;
+            }
+        }
+    }
+#endif
     if (live && !no_inference) { // nothing to infer: the tree's rows of the model batch are left as they are
         if (VAR == LZB_SEZ) {
             const float *act = p.actions + (((size_t)i * p.E + e) * A + pos) * p.D;
