@@ -1,3 +1,5 @@
+"""Tuning aid: cProfile of the host side of one eager (no CUDA graph) search at the headline shape - where the Python time of
+the driver loop goes between kernel launches."""
 import cProfile, pstats, sys, os, time
 sys.path.insert(0, os.getcwd())
 import bench, torch

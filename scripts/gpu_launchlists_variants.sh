@@ -1,3 +1,5 @@
+#!/bin/bash
+# Warm launch lists (per-kernel durations under ncu) of one eager search of the Sampled, Stochastic, Gumbel and EfficientZero trees
 mkdir -p gpurun_out
 for v in sez smz gmz ez; do
 CMD="python bench.py --steps 1 --warmup 1 --no-graph --no-cpu-baseline --no-e2e --variant $v"

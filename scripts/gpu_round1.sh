@@ -1,3 +1,5 @@
+#!/bin/bash
+# Round 1 GPU session: GPU suite, smoke, headline bench (graph / tree-only / eager), reference arm, host CPU description
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest.log 2>&1; echo pytest=$?
 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo smoke=$?
 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo bench=$?

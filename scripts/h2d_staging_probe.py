@@ -1,3 +1,5 @@
+"""Probe: host-to-device copy of one [8192, 1024] f32 latent batch from pageable, pinned and staged-through-pinned memory (what
+bounds the e2e leg of bench.py on the host side)."""
 import torch, time, numpy as np
 torch.cuda.init()
 x = torch.from_numpy(np.random.randn(8192,1024).astype(np.float32))
