@@ -841,6 +841,9 @@ __device__ __forceinline__ void select_puct_g(const Pool &p, const SelectArgs &a
                 is_root = false; going = true; no_inference = false;
                 const Grp<32> g32;
                 while (going) level_body(g32, std::integral_constant<int, 1>());
+#ifdef LZB_X_LONE_EARLY_RELEASE // experiment: the warp's walks are over here - let the dependent launch go before the row work below
+                pdl_release();
+#endif
 #ifndef LZB_X_NO_LONE_STAGE
                 if (VAR != LZB_SMZ && lone_stage_rows(a)) { // every lane holds the walker's leaf here (nothing but s_staged kept across the walk)
                     const long long rb0 = a.g[0].row_bytes;
